@@ -1,0 +1,169 @@
+/*
+ * hvcf.h -- C ABI of libhvcf.so: the B200-native replacement for HelloVulkan's
+ * clustered-forward light-culling pass pair (AABBGenerator.comp -> LightCulling.comp).
+ *
+ * The reference is a monolithic Vulkan executable with no FFI of its own
+ * (HelloVulkan/CMakeLists.txt:7-11); each entry point below therefore cites the C++
+ * method or shader it replaces.  Paths are relative to /root/reference/HelloVulkan.
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns HVCF_OK (0) or a negative hvcf_status; nothing throws
+ *     across this boundary; hvcf_last_error_string() describes the last failure on the
+ *     calling thread.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream);
+ *     all work is stream-ordered on it -- stream order replaces the reference's
+ *     vkCmdPipelineBarrier2 buffer barriers (Source/Pipelines/PipelineAABBGenerator.cpp:70-82,
+ *     Source/Pipelines/PipelineLightCulling.cpp:85-118).
+ *   - there is NO CPU fallback: every call fails with HVCF_ERR_CUDA when no sm_100 device
+ *     is usable.
+ *   - a context is owned by one host thread at a time (the reference records and submits
+ *     from a single thread, Source/Apps/AppBase.cpp:94-196).
+ */
+#ifndef HVCF_H
+#define HVCF_H
+
+#include "hvcf_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define HVCF_API __attribute__((visibility("default")))
+#else
+#define HVCF_API
+#endif
+
+typedef enum hvcf_status
+{
+	HVCF_OK = 0,
+	HVCF_ERR_INVALID_ARGUMENT = -1,
+	HVCF_ERR_CUDA = -2,
+	HVCF_ERR_OUT_OF_MEMORY = -3,
+	HVCF_ERR_CAPACITY = -4,   /* more lights than hvcf_config.max_lights */
+	HVCF_ERR_NOT_READY = -5,  /* e.g. cull before set_lights / set_ubo */
+	HVCF_ERR_UNSUPPORTED = -6
+} hvcf_status;
+
+/* Culling strategy.  Both produce byte-identical light cells / index lists. */
+typedef enum hvcf_mode
+{
+	HVCF_MODE_BRUTE = 0, /* every cluster x light pair is tested until the cluster holds max_lights_per_cluster hits */
+	HVCF_MODE_BINNED = 1 /* conservative block-level pre-filter, then the exact test on survivors */
+} hvcf_mode;
+
+typedef struct hvcf_ctx hvcf_ctx;
+
+/*
+ * Replaces the compile-time ClusterForwardConfig / AppConfig constants
+ * (Header/Configs.h:8-14, :46-56) with run-time fields; zero means "reference default".
+ */
+typedef struct hvcf_config
+{
+	uint32_t struct_size;            /* = sizeof(hvcf_config) */
+	int32_t device;                  /* CUDA ordinal; -1 = current device */
+	uint32_t slice_count_x;          /* ClusterForwardConfig::SliceCountX (16) */
+	uint32_t slice_count_y;          /* ClusterForwardConfig::SliceCountY (9) */
+	uint32_t slice_count_z;          /* ClusterForwardConfig::SliceCountZ (24) */
+	uint32_t max_lights_per_cluster; /* ClusterForwardConfig::maxLightPerCluster (150) */
+	uint32_t max_lights;             /* capacity of the light buffer (lights) */
+	uint32_t frame_count;            /* AppConfig::FrameCount (2) */
+	uint32_t mode;                   /* hvcf_mode */
+	/* z-slab shard owned by this context: slices [z_begin, z_end); 0,0 = whole grid. */
+	uint32_t z_begin;
+	uint32_t z_end;
+	uint32_t reserved[5];
+} hvcf_config;
+
+/* Device pointers in the reference's exact layouts (ResourcesClusterForward.h:24-30). */
+typedef struct hvcf_buffers
+{
+	hvcf_aabb* aabb;                    /* aabbBuffer_          : cluster_count x 32 B */
+	hvcf_light_cell* light_cells;       /* lightCellsBuffer_    : cluster_count x 8 B */
+	uint32_t* light_indices;            /* lightIndicesBuffer_  : max_lights_per_cluster x cluster_count x 4 B */
+	uint32_t* global_index_count;       /* globalIndexCountBuffers_[frame]: frame_count x 4 B (total indices of that frame) */
+	hvcf_light_data* lights;            /* ResourcesLight::storageBuffer_: max_lights x 48 B */
+	float* lights_view;                 /* view-space SoA float4 {x,y,z,r*r} of the last culled frame (library-internal cache) */
+	uint64_t light_indices_capacity;    /* elements */
+	uint32_t cluster_count;
+	uint32_t light_count;
+	uint32_t cluster_begin;             /* shard, in cluster indices */
+	uint32_t cluster_end;
+} hvcf_buffers;
+
+/* Work counters of the most recent hvcf_cull on `frame` (read back on request only). */
+typedef struct hvcf_stats
+{
+	uint64_t nominal_tests;   /* clusters x lights of the shard */
+	uint64_t executed_tests;  /* exact sphere-vs-AABB lane tests the kernels actually ran */
+	uint64_t prefilter_tests; /* conservative group tests (binned mode), else 0 */
+	uint32_t total_indices;   /* sum of counts */
+	uint32_t overflow_clusters; /* clusters whose count hit max_lights_per_cluster */
+	uint32_t kernel_launches; /* kernels launched by that hvcf_cull call */
+	uint32_t reserved;
+} hvcf_stats;
+
+HVCF_API const char* hvcf_last_error_string(void);
+HVCF_API const char* hvcf_version(void);
+
+/* ResourcesClusterForward::CreateBuffers (Source/Resources/ResourcesClusterForward.cpp:5-34)
+ * + pipeline construction (PipelineAABBGenerator.cpp:8-21, PipelineLightCulling.cpp:9-28). */
+HVCF_API int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx);
+/* ResourcesClusterForward::Destroy (ResourcesClusterForward.cpp:36-46) + pipeline destructors. */
+HVCF_API int hvcf_destroy(hvcf_ctx* ctx);
+
+/* ResourcesLight::AddLights (Source/Resources/ResourcesLight.cpp:8-18).  `lights` is n x 48 B
+ * (hvcf_light_data); src_is_device != 0 means a device pointer (device-to-device copy). */
+HVCF_API int hvcf_set_lights(hvcf_ctx* ctx, const void* lights, uint32_t n, int src_is_device, void* stream);
+/* ResourcesLight::UpdateLightPosition (ResourcesLight.cpp:20-29): writes xyz and w = 1;
+ * an out-of-range index is ignored and returns HVCF_OK, as the reference does. */
+HVCF_API int hvcf_update_light(hvcf_ctx* ctx, uint32_t index, const float xyz[3], void* stream);
+
+/* Pipeline{AABBGenerator,LightCulling}::SetClusterForwardUBO
+ * (Header/Pipelines/PipelineAABBGenerator.h:24-28, PipelineLightCulling.cpp:45-49): one call
+ * feeds both passes.  Marks the AABBs dirty when the inverse projection, near/far or the
+ * grid changed (the reference forgets to on zoom). */
+HVCF_API int hvcf_set_ubo(hvcf_ctx* ctx, uint32_t frame, const hvcf_cluster_forward_ubo* ubo, void* stream);
+/* PipelineAABBGenerator::OnWindowResized (PipelineAABBGenerator.cpp:31-34). */
+HVCF_API int hvcf_mark_aabb_dirty(hvcf_ctx* ctx);
+HVCF_API int hvcf_is_aabb_dirty(hvcf_ctx* ctx, int* out_dirty);
+
+/* PipelineAABBGenerator::Execute (PipelineAABBGenerator.cpp:49-83) running
+ * AABBGenerator.comp:39-90; unconditional -- the dirty gate lives in the C++ class
+ * (FillCommandBuffer, PipelineAABBGenerator.cpp:36-47) and in hvcf_cull. */
+HVCF_API int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream);
+
+/* PipelineLightCulling::ResetGlobalIndex + Execute (PipelineLightCulling.cpp:38-43, :58-119)
+ * running LightCulling.comp:59-88.  Regenerates the AABBs first if they are dirty. */
+HVCF_API int hvcf_cull(hvcf_ctx* ctx, uint32_t frame, void* stream);
+
+/* Sharded variant of hvcf_cull, split around the one exchange step of the path:
+ * begin  = transform + test + per-cluster counts; leaves this shard's total in
+ *          *hvcf_shard_total_ptr() on the device;
+ * finish = offsets (+ *d_index_base, a device uint32 holding the sum of the totals of the
+ *          lower-ranked shards; NULL = 0) + cells + indices written at their GLOBAL
+ *          positions, so shard segments concatenate without a fix-up pass. */
+HVCF_API int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream);
+HVCF_API int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base, void* stream);
+HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
+
+HVCF_API int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out);
+
+/* VulkanBuffer::DownloadBufferData (Source/Vulkan/VulkanBuffer.cpp:169-178): synchronous
+ * (they synchronise `stream` before returning). `bytes` must not exceed the buffer. */
+HVCF_API int hvcf_download_aabbs(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream);
+HVCF_API int hvcf_download_light_cells(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream);
+HVCF_API int hvcf_download_light_indices(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream);
+HVCF_API int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void* stream);
+HVCF_API int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream);
+
+/* Pinned host staging for callers that want asynchronous host<->device copies
+ * (VMA_MEMORY_USAGE_CPU_TO_GPU in the reference, ResourcesLight.cpp:14-16). */
+HVCF_API int hvcf_host_alloc(size_t bytes, void** out_ptr);
+HVCF_API int hvcf_host_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HVCF_H */
