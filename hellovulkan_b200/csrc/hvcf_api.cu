@@ -1,0 +1,549 @@
+// hvcf_api.cu -- the extern "C" boundary of libhvcf.so (include/hvcf.h).  Owns the device buffers in
+// the reference's layouts, stages UBOs through pinned memory, and strings the kernels of
+// hvcf_kernels.cu together on the caller's stream.  No CPU fallback: every entry point fails with
+// HVCF_ERR_CUDA when no sm_100 device is usable.
+#include "../../include/hvcf.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "hvcf_kernels.cuh"
+
+using namespace hvcf;
+
+namespace
+{
+thread_local char g_last_error[512] = "";
+
+int fail(int code, const char* fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define HVCF_CUDA(expr)                                                                                      \
+	do                                                                                                       \
+	{                                                                                                        \
+		cudaError_t e_ = (expr);                                                                             \
+		if (e_ != cudaSuccess)                                                                               \
+			return fail(e_ == cudaErrorMemoryAllocation ? HVCF_ERR_OUT_OF_MEMORY : HVCF_ERR_CUDA,            \
+				"%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_));                  \
+	} while (0)
+
+int env_int(const char* name, int dflt)
+{
+	const char* v = getenv(name);
+	return (v && *v) ? atoi(v) : dflt;
+}
+} // namespace
+
+struct hvcf_ctx
+{
+	hvcf_config cfg{};
+	int device = 0;
+	uint32_t X = 0, Y = 0, Z = 0;
+	uint32_t cluster_total = 0;  // whole grid
+	uint32_t cluster_begin = 0;  // shard [begin, end)
+	uint32_t cluster_end = 0;
+	uint32_t cluster_count = 0;  // shard size
+	uint32_t cap = 0;
+	uint32_t max_lights = 0;
+	uint32_t padded_capacity = 0; // max_lights rounded up to a tile
+	uint32_t frame_count = 0;
+	uint32_t num_lights = 0;
+	int variant = 1;
+	uint32_t max_segs = 1;
+	uint32_t count_blocks = 0;
+
+	// reference-layout buffers
+	hvcf_light_data* d_lights = nullptr;   // ResourcesLight::storageBuffer_
+	hvcf_aabb* d_aabb = nullptr;           // ResourcesClusterForward::aabbBuffer_
+	hvcf_light_cell* d_cells = nullptr;    // lightCellsBuffer_
+	uint32_t* d_indices = nullptr;         // lightIndicesBuffer_
+	uint32_t* d_global_index = nullptr;    // globalIndexCountBuffers_[frame]
+	hvcf_cluster_forward_ubo* d_ubo = nullptr; // cfUBOBuffers_[frame]
+	// library-internal
+	float4* d_lights_view = nullptr;
+	float* d_zplanes = nullptr;            // [frame][Z+1]
+	uint32_t* d_seg_counts = nullptr;
+	uint32_t* d_seg_lists = nullptr;
+	uint32_t* d_counts = nullptr;
+	uint32_t* d_block_sums = nullptr;
+	uint32_t* d_block_offsets = nullptr;
+	uint32_t* d_shard_total = nullptr;
+	DeviceStats* d_stats = nullptr;        // [frame]
+	// pinned staging
+	hvcf_cluster_forward_ubo* h_ubo = nullptr; // [frame]
+	float* h_zplanes = nullptr;                // [frame][Z+1]
+	hvcf_light_data* h_one_light = nullptr;    // hvcf_update_light staging ring
+	uint32_t one_light_cursor = 0;
+	cudaEvent_t one_light_events[16]{};
+
+	bool* ubo_set = nullptr;
+	bool aabb_dirty = true;
+	bool have_aabb_key = false;
+	float aabb_key[16 + 2]{}; // inverse projection + near/far of the last generated AABBs
+	uint32_t last_num_segs = 0;
+	uint32_t last_launches[8]{}; // per frame
+};
+
+static void free_ctx(hvcf_ctx* c)
+{
+	if (!c)
+		return;
+	cudaFree(c->d_lights);
+	cudaFree(c->d_aabb);
+	cudaFree(c->d_cells);
+	cudaFree(c->d_indices);
+	cudaFree(c->d_global_index);
+	cudaFree(c->d_ubo);
+	cudaFree(c->d_lights_view);
+	cudaFree(c->d_zplanes);
+	cudaFree(c->d_seg_counts);
+	cudaFree(c->d_seg_lists);
+	cudaFree(c->d_counts);
+	cudaFree(c->d_block_sums);
+	cudaFree(c->d_block_offsets);
+	cudaFree(c->d_shard_total);
+	cudaFree(c->d_stats);
+	cudaFreeHost(c->h_ubo);
+	cudaFreeHost(c->h_zplanes);
+	cudaFreeHost(c->h_one_light);
+	for (auto& e : c->one_light_events)
+		if (e)
+			cudaEventDestroy(e);
+	delete[] c->ubo_set;
+	delete c;
+}
+
+extern "C" {
+
+const char* hvcf_last_error_string(void) { return g_last_error; }
+const char* hvcf_version(void) { return "hvcf 0.1 (sm_100a)"; }
+
+int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
+{
+	if (!config || !out_ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: null argument");
+	if (config->struct_size != sizeof(hvcf_config))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: struct_size %u != %zu", config->struct_size, sizeof(hvcf_config));
+	*out_ctx = nullptr;
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+		return fail(HVCF_ERR_CUDA, "hvcf_create: no CUDA device (libhvcf has no CPU fallback)");
+	int dev = config->device;
+	if (dev < 0)
+		HVCF_CUDA(cudaGetDevice(&dev));
+	if (dev >= ndev)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: device %d of %d", dev, ndev);
+	cudaDeviceProp prop;
+	HVCF_CUDA(cudaGetDeviceProperties(&prop, dev));
+	if (prop.major != 10)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create: device %d is sm_%d%d; libhvcf is built for sm_100a only", dev,
+			prop.major, prop.minor);
+	HVCF_CUDA(cudaSetDevice(dev));
+
+	hvcf_ctx* c = new (std::nothrow) hvcf_ctx();
+	if (!c)
+		return fail(HVCF_ERR_OUT_OF_MEMORY, "hvcf_create: host allocation failed");
+	c->cfg = *config;
+	c->device = dev;
+	c->X = config->slice_count_x ? config->slice_count_x : HVCF_DEFAULT_SLICE_COUNT_X;
+	c->Y = config->slice_count_y ? config->slice_count_y : HVCF_DEFAULT_SLICE_COUNT_Y;
+	c->Z = config->slice_count_z ? config->slice_count_z : HVCF_DEFAULT_SLICE_COUNT_Z;
+	c->cap = config->max_lights_per_cluster ? config->max_lights_per_cluster : HVCF_DEFAULT_MAX_LIGHTS_PER_CLUSTER;
+	c->frame_count = config->frame_count ? config->frame_count : HVCF_DEFAULT_FRAME_COUNT;
+	c->max_lights = config->max_lights ? config->max_lights : 1024;
+	const uint64_t total64 = static_cast<uint64_t>(c->X) * c->Y * c->Z;
+	if (total64 == 0 || total64 > (1ull << 26) || c->frame_count > 8 || c->cap > (1u << 16) ||
+		total64 * c->cap >= (1ull << 32) || c->max_lights > 0xffff0000u)
+	{
+		delete c;
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: grid %ux%ux%u cap %u frames %u out of range", config->slice_count_x,
+			config->slice_count_y, config->slice_count_z, config->max_lights_per_cluster, config->frame_count);
+	}
+	c->cluster_total = static_cast<uint32_t>(total64);
+	uint32_t zb = config->z_begin, ze = config->z_end;
+	if (zb == 0 && ze == 0)
+		ze = c->Z;
+	if (zb >= ze || ze > c->Z)
+	{
+		delete c;
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: z shard [%u,%u) outside [0,%u)", zb, ze, c->Z);
+	}
+	if (config->mode != HVCF_MODE_BRUTE)
+	{
+		delete c;
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create: mode %u not implemented in this build", config->mode);
+	}
+	c->cluster_begin = zb * c->X * c->Y;
+	c->cluster_end = ze * c->X * c->Y;
+	c->cluster_count = c->cluster_end - c->cluster_begin;
+	c->padded_capacity = round_up_u32(c->max_lights, kTileLights);
+	c->variant = env_int("HVCF_CULL_VARIANT", 1);
+	if (c->variant < 0 || c->variant >= kNumCullVariants)
+		c->variant = 1;
+	// light segments: enough CTAs to fill 148 SMs x 4 resident CTAs about twice
+	const uint32_t per_cta = cull_variant_clusters_per_cta(c->variant);
+	const uint32_t groups = (c->cluster_count + per_cta - 1) / per_cta;
+	uint32_t segs = (2 * 148 * 4 + groups - 1) / groups;
+	segs = segs < 1 ? 1 : (segs > 32 ? 32 : segs);
+	const int env_segs = env_int("HVCF_SEGMENTS", 0);
+	if (env_segs > 0)
+		segs = static_cast<uint32_t>(env_segs > 64 ? 64 : env_segs);
+	c->max_segs = segs;
+	c->count_blocks = (c->cluster_count + 255) / 256;
+
+#define HVCF_ALLOC(ptr, bytes)                                                              \
+	do                                                                                      \
+	{                                                                                       \
+		cudaError_t e_ = cudaMalloc(reinterpret_cast<void**>(&(ptr)), (bytes) ? (bytes) : 16); \
+		if (e_ != cudaSuccess)                                                              \
+		{                                                                                   \
+			free_ctx(c);                                                                    \
+			return fail(HVCF_ERR_OUT_OF_MEMORY, "hvcf_create: cudaMalloc(%zu) for %s: %s", static_cast<size_t>(bytes), #ptr, \
+				cudaGetErrorString(e_));                                                    \
+		}                                                                                   \
+	} while (0)
+	const size_t C = c->cluster_total, Cs = c->cluster_count;
+	HVCF_ALLOC(c->d_lights, sizeof(hvcf_light_data) * static_cast<size_t>(c->max_lights));
+	HVCF_ALLOC(c->d_aabb, sizeof(hvcf_aabb) * C);
+	HVCF_ALLOC(c->d_cells, sizeof(hvcf_light_cell) * C);
+	HVCF_ALLOC(c->d_indices, sizeof(uint32_t) * C * c->cap);
+	HVCF_ALLOC(c->d_global_index, sizeof(uint32_t) * c->frame_count);
+	HVCF_ALLOC(c->d_ubo, sizeof(hvcf_cluster_forward_ubo) * c->frame_count);
+	HVCF_ALLOC(c->d_lights_view, static_cast<size_t>(c->padded_capacity) * 16);
+	HVCF_ALLOC(c->d_zplanes, sizeof(float) * (c->Z + 1) * c->frame_count);
+	HVCF_ALLOC(c->d_seg_counts, sizeof(uint32_t) * Cs * c->max_segs);
+	HVCF_ALLOC(c->d_seg_lists, sizeof(uint32_t) * Cs * c->max_segs * c->cap);
+	HVCF_ALLOC(c->d_counts, sizeof(uint32_t) * Cs);
+	HVCF_ALLOC(c->d_block_sums, sizeof(uint32_t) * c->count_blocks);
+	HVCF_ALLOC(c->d_block_offsets, sizeof(uint32_t) * c->count_blocks);
+	HVCF_ALLOC(c->d_shard_total, sizeof(uint32_t));
+	HVCF_ALLOC(c->d_stats, sizeof(DeviceStats) * c->frame_count);
+#undef HVCF_ALLOC
+	cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&c->h_ubo), sizeof(hvcf_cluster_forward_ubo) * c->frame_count);
+	if (e == cudaSuccess)
+		e = cudaMallocHost(reinterpret_cast<void**>(&c->h_zplanes), sizeof(float) * (c->Z + 1) * c->frame_count);
+	if (e == cudaSuccess)
+		e = cudaMallocHost(reinterpret_cast<void**>(&c->h_one_light), sizeof(hvcf_light_data) * 16);
+	for (int i = 0; i < 16 && e == cudaSuccess; ++i)
+		e = cudaEventCreateWithFlags(&c->one_light_events[i], cudaEventDisableTiming);
+	if (e == cudaSuccess)
+		e = cudaMemset(c->d_cells, 0, sizeof(hvcf_light_cell) * C);
+	if (e == cudaSuccess)
+		e = cudaMemset(c->d_aabb, 0, sizeof(hvcf_aabb) * C);
+	if (e == cudaSuccess)
+		e = cudaMemset(c->d_global_index, 0, sizeof(uint32_t) * c->frame_count);
+	if (e == cudaSuccess)
+		e = cudaMemset(c->d_stats, 0, sizeof(DeviceStats) * c->frame_count);
+	if (e == cudaSuccess)
+		e = cudaMemset(c->d_shard_total, 0, sizeof(uint32_t));
+	if (e != cudaSuccess)
+	{
+		free_ctx(c);
+		return fail(HVCF_ERR_CUDA, "hvcf_create: pinned staging / init: %s", cudaGetErrorString(e));
+	}
+	c->ubo_set = new bool[c->frame_count]();
+	*out_ctx = c;
+	return HVCF_OK;
+}
+
+int hvcf_destroy(hvcf_ctx* ctx)
+{
+	if (!ctx)
+		return HVCF_OK;
+	cudaSetDevice(ctx->device);
+	cudaDeviceSynchronize();
+	free_ctx(ctx);
+	return HVCF_OK;
+}
+
+int hvcf_set_lights(hvcf_ctx* ctx, const void* lights, uint32_t n, int src_is_device, void* stream)
+{
+	if (!ctx || (n && !lights))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_lights: null argument");
+	if (n > ctx->max_lights)
+		return fail(HVCF_ERR_CAPACITY, "hvcf_set_lights: %u lights > max_lights %u", n, ctx->max_lights);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	if (n)
+		HVCF_CUDA(cudaMemcpyAsync(ctx->d_lights, lights, sizeof(hvcf_light_data) * static_cast<size_t>(n),
+			src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+	ctx->num_lights = n;
+	return HVCF_OK;
+}
+
+int hvcf_update_light(hvcf_ctx* ctx, uint32_t index, const float xyz[3], void* stream)
+{
+	if (!ctx || !xyz)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_update_light: null argument");
+	if (index >= ctx->num_lights)
+		return HVCF_OK; // ResourcesLight::UpdateLightPosition ignores an out-of-range index (ResourcesLight.cpp:22-25)
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	const uint32_t slot = ctx->one_light_cursor++ & 15u;
+	HVCF_CUDA(cudaEventSynchronize(ctx->one_light_events[slot])); // slot's previous copy has been consumed
+	float* h = ctx->h_one_light[slot].position;
+	h[0] = xyz[0], h[1] = xyz[1], h[2] = xyz[2], h[3] = 1.0f;
+	HVCF_CUDA(cudaMemcpyAsync(ctx->d_lights[index].position, h, 16, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+	HVCF_CUDA(cudaEventRecord(ctx->one_light_events[slot], static_cast<cudaStream_t>(stream)));
+	return HVCF_OK;
+}
+
+int hvcf_set_ubo(hvcf_ctx* ctx, uint32_t frame, const hvcf_cluster_forward_ubo* ubo, void* stream)
+{
+	if (!ctx || !ubo)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_ubo: null argument");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_ubo: frame %u >= frame_count %u", frame, ctx->frame_count);
+	if (ubo->slice_count_x != ctx->X || ubo->slice_count_y != ctx->Y || ubo->slice_count_z != ctx->Z)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_ubo: ubo grid %ux%ux%u != context grid %ux%ux%u", ubo->slice_count_x,
+			ubo->slice_count_y, ubo->slice_count_z, ctx->X, ctx->Y, ctx->Z);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	ctx->h_ubo[frame] = *ubo;
+	HVCF_CUDA(cudaMemcpyAsync(&ctx->d_ubo[frame], &ctx->h_ubo[frame], sizeof(hvcf_cluster_forward_ubo), cudaMemcpyHostToDevice,
+		static_cast<cudaStream_t>(stream)));
+	ctx->ubo_set[frame] = true;
+	// AABBs depend on the inverse projection, near/far and the grid only
+	float key[18];
+	memcpy(key, ubo->camera_inverse_projection, 64);
+	key[16] = ubo->camera_near;
+	key[17] = ubo->camera_far;
+	if (!ctx->have_aabb_key || memcmp(key, ctx->aabb_key, sizeof(key)) != 0)
+		ctx->aabb_dirty = true;
+	return HVCF_OK;
+}
+
+int hvcf_mark_aabb_dirty(hvcf_ctx* ctx)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_mark_aabb_dirty: null context");
+	ctx->aabb_dirty = true;
+	return HVCF_OK;
+}
+
+int hvcf_is_aabb_dirty(hvcf_ctx* ctx, int* out_dirty)
+{
+	if (!ctx || !out_dirty)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_is_aabb_dirty: null argument");
+	*out_dirty = ctx->aabb_dirty ? 1 : 0;
+	return HVCF_OK;
+}
+
+int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_generate_aabbs: null context");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_generate_aabbs: frame %u >= frame_count %u", frame, ctx->frame_count);
+	if (!ctx->ubo_set[frame])
+		return fail(HVCF_ERR_NOT_READY, "hvcf_generate_aabbs: hvcf_set_ubo(frame %u) has not been called", frame);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	const hvcf_cluster_forward_ubo& u = ctx->h_ubo[frame];
+	// slice-plane table: tileNear(z) = -near * pow(far/near, float(z)/Z)  (AABBGenerator.comp:72-75)
+	float* hz = ctx->h_zplanes + static_cast<size_t>(frame) * (ctx->Z + 1);
+	for (uint32_t z = 0; z <= ctx->Z; ++z)
+		hz[z] = -u.camera_near * powf(u.camera_far / u.camera_near, static_cast<float>(z) / static_cast<float>(ctx->Z));
+	float* dz = ctx->d_zplanes + static_cast<size_t>(frame) * (ctx->Z + 1);
+	HVCF_CUDA(cudaMemcpyAsync(dz, hz, sizeof(float) * (ctx->Z + 1), cudaMemcpyHostToDevice, s));
+	HVCF_CUDA(launch_aabb_generate(&ctx->d_ubo[frame], dz, ctx->d_aabb, ctx->cluster_total, s));
+	memcpy(ctx->aabb_key, u.camera_inverse_projection, 64);
+	ctx->aabb_key[16] = u.camera_near;
+	ctx->aabb_key[17] = u.camera_far;
+	ctx->have_aabb_key = true;
+	ctx->aabb_dirty = false;
+	return HVCF_OK;
+}
+
+int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin: null context");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin: frame %u >= frame_count %u", frame, ctx->frame_count);
+	if (!ctx->ubo_set[frame])
+		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_begin: hvcf_set_ubo(frame %u) has not been called", frame);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	uint32_t launches = 0;
+	if (ctx->aabb_dirty)
+	{
+		const int rc = hvcf_generate_aabbs(ctx, frame, stream);
+		if (rc != HVCF_OK)
+			return rc;
+		++launches;
+	}
+	DeviceStats* stats = &ctx->d_stats[frame];
+	HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
+	const uint32_t n = ctx->num_lights;
+	const uint32_t padded = round_up_u32(n, kTileLights);
+	const uint32_t tiles_total = padded / kTileLights;
+	uint32_t num_segs = ctx->max_segs < tiles_total ? ctx->max_segs : tiles_total;
+	uint32_t tiles_per_seg = num_segs ? (tiles_total + num_segs - 1) / num_segs : 0;
+	if (tiles_per_seg)
+		num_segs = (tiles_total + tiles_per_seg - 1) / tiles_per_seg; // no empty segment
+	if (n)
+	{
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], ctx->d_lights, n, padded, ctx->d_lights_view, s));
+		CullParams p;
+		p.lights_view = ctx->d_lights_view;
+		p.aabbs = ctx->d_aabb;
+		p.cluster_begin = ctx->cluster_begin;
+		p.cluster_count = ctx->cluster_count;
+		p.tiles_total = tiles_total;
+		p.tiles_per_seg = tiles_per_seg;
+		p.cap = ctx->cap;
+		p.seg_counts = ctx->d_seg_counts;
+		p.seg_lists = ctx->d_seg_lists;
+		p.stats = stats;
+		HVCF_CUDA(launch_cull(ctx->variant, p, num_segs, s));
+		launches += 2;
+	}
+	ctx->last_num_segs = num_segs;
+	HVCF_CUDA(launch_count(ctx->d_seg_counts, num_segs, ctx->cluster_count, ctx->cap, ctx->d_counts, ctx->d_block_sums, stats, s));
+	HVCF_CUDA(launch_scan(ctx->d_block_sums, ctx->count_blocks, ctx->d_block_offsets, ctx->d_shard_total, stats, s));
+	launches += 2;
+	ctx->last_launches[frame] = launches;
+	return HVCF_OK;
+}
+
+int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_finish: null context");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_finish: frame %u >= frame_count %u", frame, ctx->frame_count);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	ScatterParams p;
+	p.counts = ctx->d_counts;
+	p.block_offsets = ctx->d_block_offsets;
+	p.index_base = d_index_base;
+	p.seg_counts = ctx->d_seg_counts;
+	p.seg_lists = ctx->d_seg_lists;
+	p.num_segs = ctx->last_num_segs;
+	p.cluster_begin = ctx->cluster_begin;
+	p.cluster_count = ctx->cluster_count;
+	p.cap = ctx->cap;
+	p.cells = ctx->d_cells;
+	p.indices = ctx->d_indices;
+	p.frame_total = &ctx->d_global_index[frame];
+	HVCF_CUDA(launch_scatter(p, static_cast<cudaStream_t>(stream)));
+	ctx->last_launches[frame] += 1;
+	return HVCF_OK;
+}
+
+int hvcf_cull(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	const int rc = hvcf_cull_begin(ctx, frame, stream);
+	if (rc != HVCF_OK)
+		return rc;
+	return hvcf_cull_finish(ctx, frame, nullptr, stream);
+}
+
+int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
+{
+	if (!ctx || !out_device_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shard_total_ptr: null argument");
+	*out_device_ptr = ctx->d_shard_total;
+	return HVCF_OK;
+}
+
+int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out)
+{
+	if (!ctx || !out)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_device_buffers: null argument");
+	memset(out, 0, sizeof(*out));
+	out->aabb = ctx->d_aabb;
+	out->light_cells = ctx->d_cells;
+	out->light_indices = ctx->d_indices;
+	out->global_index_count = ctx->d_global_index;
+	out->lights = ctx->d_lights;
+	out->lights_view = reinterpret_cast<float*>(ctx->d_lights_view);
+	out->light_indices_capacity = static_cast<uint64_t>(ctx->cluster_total) * ctx->cap;
+	out->cluster_count = ctx->cluster_total;
+	out->light_count = ctx->num_lights;
+	out->cluster_begin = ctx->cluster_begin;
+	out->cluster_end = ctx->cluster_end;
+	return HVCF_OK;
+}
+
+static int download(hvcf_ctx* ctx, void* dst, const void* src, size_t bytes, size_t limit, void* stream, const char* what)
+{
+	if (!ctx || (bytes && !dst))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null argument", what);
+	if (bytes > limit)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: %zu bytes > buffer size %zu", what, bytes, limit);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (bytes)
+		HVCF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
+	HVCF_CUDA(cudaStreamSynchronize(s));
+	return HVCF_OK;
+}
+
+int hvcf_download_aabbs(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
+{
+	return download(ctx, dst, ctx ? ctx->d_aabb : nullptr, bytes, ctx ? sizeof(hvcf_aabb) * ctx->cluster_total : 0, stream,
+		"hvcf_download_aabbs");
+}
+int hvcf_download_light_cells(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
+{
+	return download(ctx, dst, ctx ? ctx->d_cells : nullptr, bytes, ctx ? sizeof(hvcf_light_cell) * ctx->cluster_total : 0, stream,
+		"hvcf_download_light_cells");
+}
+int hvcf_download_light_indices(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
+{
+	return download(ctx, dst, ctx ? ctx->d_indices : nullptr, bytes,
+		ctx ? sizeof(uint32_t) * static_cast<size_t>(ctx->cluster_total) * ctx->cap : 0, stream, "hvcf_download_light_indices");
+}
+int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void* stream)
+{
+	if (ctx && frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_total: frame %u >= frame_count %u", frame, ctx->frame_count);
+	return download(ctx, out_total, ctx ? &ctx->d_global_index[frame] : nullptr, sizeof(uint32_t), sizeof(uint32_t), stream,
+		"hvcf_download_total");
+}
+
+int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
+{
+	if (!ctx || !out)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_stats: null argument");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_stats: frame %u >= frame_count %u", frame, ctx->frame_count);
+	DeviceStats ds;
+	const int rc = download(ctx, &ds, &ctx->d_stats[frame], sizeof(ds), sizeof(ds), stream, "hvcf_get_stats");
+	if (rc != HVCF_OK)
+		return rc;
+	memset(out, 0, sizeof(*out));
+	out->nominal_tests = static_cast<uint64_t>(ctx->cluster_count) * ctx->num_lights;
+	out->executed_tests = ds.executed_tests;
+	out->prefilter_tests = ds.prefilter_tests;
+	out->total_indices = ds.total_indices;
+	out->overflow_clusters = ds.overflow_clusters;
+	out->kernel_launches = ctx->last_launches[frame];
+	return HVCF_OK;
+}
+
+int hvcf_host_alloc(size_t bytes, void** out_ptr)
+{
+	if (!out_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_host_alloc: null argument");
+	HVCF_CUDA(cudaMallocHost(out_ptr, bytes ? bytes : 16));
+	return HVCF_OK;
+}
+
+int hvcf_host_free(void* ptr)
+{
+	if (ptr)
+		HVCF_CUDA(cudaFreeHost(ptr));
+	return HVCF_OK;
+}
+
+} // extern "C"

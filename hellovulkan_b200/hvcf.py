@@ -1,0 +1,247 @@
+"""ctypes binding of libhvcf.so (include/hvcf.h) -- the C ABI of the B200 light-culling path.
+
+This is plumbing only: it loads the in-tree CUDA library and exposes its entry points.  There is no
+CPU fallback; if the library is missing or no sm_100 device is present, every call raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libhvcf.so")
+
+LIGHT_DT = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("radius", "<f4"), ("pad_", "<f4", 3)])
+AABB_DT = np.dtype([("min_point", "<f4", 4), ("max_point", "<f4", 4)])
+CELL_DT = np.dtype([("offset", "<u4"), ("count", "<u4")])
+UBO_BYTES = 176
+
+HVCF_OK = 0
+MODE_BRUTE = 0
+MODE_BINNED = 1
+
+
+class HvcfError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"hvcf error {code}: {msg}")
+        self.code = code
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("struct_size", ctypes.c_uint32), ("device", ctypes.c_int32),
+                ("slice_count_x", ctypes.c_uint32), ("slice_count_y", ctypes.c_uint32), ("slice_count_z", ctypes.c_uint32),
+                ("max_lights_per_cluster", ctypes.c_uint32), ("max_lights", ctypes.c_uint32), ("frame_count", ctypes.c_uint32),
+                ("mode", ctypes.c_uint32), ("z_begin", ctypes.c_uint32), ("z_end", ctypes.c_uint32),
+                ("reserved", ctypes.c_uint32 * 5)]
+
+
+class Buffers(ctypes.Structure):
+    _fields_ = [("aabb", ctypes.c_void_p), ("light_cells", ctypes.c_void_p), ("light_indices", ctypes.c_void_p),
+                ("global_index_count", ctypes.c_void_p), ("lights", ctypes.c_void_p), ("lights_view", ctypes.c_void_p),
+                ("light_indices_capacity", ctypes.c_uint64), ("cluster_count", ctypes.c_uint32), ("light_count", ctypes.c_uint32),
+                ("cluster_begin", ctypes.c_uint32), ("cluster_end", ctypes.c_uint32)]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("nominal_tests", ctypes.c_uint64), ("executed_tests", ctypes.c_uint64), ("prefilter_tests", ctypes.c_uint64),
+                ("total_indices", ctypes.c_uint32), ("overflow_clusters", ctypes.c_uint32), ("kernel_launches", ctypes.c_uint32),
+                ("reserved", ctypes.c_uint32)]
+
+
+EXPORTS = [
+    "hvcf_last_error_string", "hvcf_version", "hvcf_create", "hvcf_destroy", "hvcf_set_lights", "hvcf_update_light",
+    "hvcf_set_ubo", "hvcf_mark_aabb_dirty", "hvcf_is_aabb_dirty", "hvcf_generate_aabbs", "hvcf_cull", "hvcf_cull_begin",
+    "hvcf_cull_finish", "hvcf_shard_total_ptr", "hvcf_get_device_buffers", "hvcf_download_aabbs",
+    "hvcf_download_light_cells", "hvcf_download_light_indices", "hvcf_download_total", "hvcf_get_stats",
+    "hvcf_host_alloc", "hvcf_host_free",
+]
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree libhvcf.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                f"or `make -C hellovulkan_b200/csrc`")
+    lib = ctypes.CDLL(LIB_PATH)
+    lib.hvcf_last_error_string.restype = ctypes.c_char_p
+    lib.hvcf_version.restype = ctypes.c_char_p
+    vp, u32, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int
+    lib.hvcf_create.argtypes = [ctypes.POINTER(Config), ctypes.POINTER(vp)]
+    lib.hvcf_destroy.argtypes = [vp]
+    lib.hvcf_set_lights.argtypes = [vp, vp, u32, i32, vp]
+    lib.hvcf_update_light.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float), vp]
+    lib.hvcf_set_ubo.argtypes = [vp, u32, vp, vp]
+    lib.hvcf_mark_aabb_dirty.argtypes = [vp]
+    lib.hvcf_is_aabb_dirty.argtypes = [vp, ctypes.POINTER(ctypes.c_int)]
+    lib.hvcf_generate_aabbs.argtypes = [vp, u32, vp]
+    lib.hvcf_cull.argtypes = [vp, u32, vp]
+    lib.hvcf_cull_begin.argtypes = [vp, u32, vp]
+    lib.hvcf_cull_finish.argtypes = [vp, u32, vp, vp]
+    lib.hvcf_shard_total_ptr.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.hvcf_get_device_buffers.argtypes = [vp, ctypes.POINTER(Buffers)]
+    for name in ("hvcf_download_aabbs", "hvcf_download_light_cells", "hvcf_download_light_indices"):
+        getattr(lib, name).argtypes = [vp, vp, ctypes.c_size_t, vp]
+    lib.hvcf_download_total.argtypes = [vp, u32, ctypes.POINTER(u32), vp]
+    lib.hvcf_get_stats.argtypes = [vp, u32, ctypes.POINTER(Stats), vp]
+    lib.hvcf_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(vp)]
+    lib.hvcf_host_free.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+def _check(rc):
+    if rc != HVCF_OK:
+        raise HvcfError(rc, load().hvcf_last_error_string().decode(errors="replace"))
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Context:
+    """One hvcf_ctx: the device buffers of ResourcesClusterForward + ResourcesLight and the two passes."""
+
+    def __init__(self, grid=(16, 9, 24), max_lights=1024, max_lights_per_cluster=150, frame_count=2, device=-1,
+                 mode=MODE_BRUTE, z_begin=0, z_end=0):
+        self.lib = load()
+        cfg = Config()
+        cfg.struct_size = ctypes.sizeof(Config)
+        cfg.device = device
+        cfg.slice_count_x, cfg.slice_count_y, cfg.slice_count_z = grid
+        cfg.max_lights_per_cluster = max_lights_per_cluster
+        cfg.max_lights = max_lights
+        cfg.frame_count = frame_count
+        cfg.mode = mode
+        cfg.z_begin, cfg.z_end = z_begin, z_end
+        self.handle = ctypes.c_void_p()
+        _check(self.lib.hvcf_create(ctypes.byref(cfg), ctypes.byref(self.handle)))
+        self.grid = tuple(grid)
+        self.cap = max_lights_per_cluster
+        self.cluster_total = grid[0] * grid[1] * grid[2]
+        self.frame_count = frame_count
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.hvcf_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- inputs ------------------------------------------------------------------------------------
+    def set_lights(self, lights, stream=None):
+        """lights: numpy array of LIGHT_DT (host) -- ResourcesLight::AddLights."""
+        lights = np.ascontiguousarray(lights)
+        assert lights.dtype == LIGHT_DT
+        _check(self.lib.hvcf_set_lights(self.handle, _ptr(lights), len(lights), 0, stream))
+
+    def set_lights_ptr(self, ptr, n, is_device, stream=None):
+        _check(self.lib.hvcf_set_lights(self.handle, ctypes.c_void_p(ptr), n, int(is_device), stream))
+
+    def update_light(self, index, xyz, stream=None):
+        arr = (ctypes.c_float * 3)(*[float(v) for v in xyz])
+        _check(self.lib.hvcf_update_light(self.handle, index, arr, stream))
+
+    def set_ubo(self, frame, ubo, stream=None):
+        ubo = np.ascontiguousarray(ubo).view(np.uint8)
+        assert ubo.nbytes == UBO_BYTES
+        _check(self.lib.hvcf_set_ubo(self.handle, frame, _ptr(ubo), stream))
+
+    def set_ubo_ptr(self, frame, ptr, stream=None):
+        _check(self.lib.hvcf_set_ubo(self.handle, frame, ctypes.c_void_p(ptr), stream))
+
+    def mark_aabb_dirty(self):
+        _check(self.lib.hvcf_mark_aabb_dirty(self.handle))
+
+    def is_aabb_dirty(self):
+        d = ctypes.c_int(0)
+        _check(self.lib.hvcf_is_aabb_dirty(self.handle, ctypes.byref(d)))
+        return bool(d.value)
+
+    # -- passes ------------------------------------------------------------------------------------
+    def generate_aabbs(self, frame=0, stream=None):
+        _check(self.lib.hvcf_generate_aabbs(self.handle, frame, stream))
+
+    def cull(self, frame=0, stream=None):
+        _check(self.lib.hvcf_cull(self.handle, frame, stream))
+
+    def cull_begin(self, frame=0, stream=None):
+        _check(self.lib.hvcf_cull_begin(self.handle, frame, stream))
+
+    def cull_finish(self, frame=0, index_base_ptr=None, stream=None):
+        _check(self.lib.hvcf_cull_finish(self.handle, frame, ctypes.c_void_p(index_base_ptr) if index_base_ptr else None, stream))
+
+    def shard_total_ptr(self):
+        p = ctypes.c_void_p()
+        _check(self.lib.hvcf_shard_total_ptr(self.handle, ctypes.byref(p)))
+        return p.value
+
+    # -- outputs -----------------------------------------------------------------------------------
+    def buffers(self):
+        b = Buffers()
+        _check(self.lib.hvcf_get_device_buffers(self.handle, ctypes.byref(b)))
+        return b
+
+    def download_aabbs(self, stream=None):
+        out = np.zeros(self.cluster_total, AABB_DT)
+        _check(self.lib.hvcf_download_aabbs(self.handle, _ptr(out), out.nbytes, stream))
+        return out
+
+    def download_light_cells(self, stream=None):
+        out = np.zeros(self.cluster_total, CELL_DT)
+        _check(self.lib.hvcf_download_light_cells(self.handle, _ptr(out), out.nbytes, stream))
+        return out
+
+    def download_light_indices(self, count=None, stream=None):
+        n = self.cluster_total * self.cap if count is None else int(count)
+        out = np.zeros(max(n, 1), np.uint32)
+        _check(self.lib.hvcf_download_light_indices(self.handle, _ptr(out), n * 4, stream))
+        return out[:n]
+
+    def download_total(self, frame=0, stream=None):
+        t = ctypes.c_uint32(0)
+        _check(self.lib.hvcf_download_total(self.handle, frame, ctypes.byref(t), stream))
+        return int(t.value)
+
+    def stats(self, frame=0, stream=None):
+        s = Stats()
+        _check(self.lib.hvcf_get_stats(self.handle, frame, ctypes.byref(s), stream))
+        return {k: int(getattr(s, k)) for k, _ in Stats._fields_ if k != "reserved"}
+
+
+class PinnedBuffer:
+    """hvcf_host_alloc'd pinned host memory viewed as a numpy array."""
+
+    def __init__(self, nbytes):
+        self.lib = load()
+        self.ptr = ctypes.c_void_p()
+        _check(self.lib.hvcf_host_alloc(nbytes, ctypes.byref(self.ptr)))
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(self.ptr.value))
+
+    def close(self):
+        if self.ptr:
+            self.lib.hvcf_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
