@@ -58,6 +58,7 @@ struct hvcf_ctx
 	uint32_t padded_capacity = 0; // max_lights rounded up to a tile
 	uint32_t frame_count = 0;
 	uint32_t num_lights = 0;
+	const hvcf_light_data* bound_lights = nullptr; // hvcf_bind_lights: external buffer, not owned
 	int variant = 1;
 	uint32_t max_segs = 1;
 	uint32_t count_blocks = 0;
@@ -92,6 +93,9 @@ struct hvcf_ctx
 	float aabb_key[16 + 2]{}; // inverse projection + near/far of the last generated AABBs
 	uint32_t last_num_segs = 0;
 	uint32_t last_launches[8]{}; // per frame
+	bool timing = false;
+	cudaEvent_t ev[8][4]{}; // per frame: call begin, kernel begin, kernel end, call end
+	bool ev_valid[8]{};
 };
 
 static void free_ctx(hvcf_ctx* c)
@@ -119,6 +123,10 @@ static void free_ctx(hvcf_ctx* c)
 	for (auto& e : c->one_light_events)
 		if (e)
 			cudaEventDestroy(e);
+	for (auto& fe : c->ev)
+		for (auto& e : fe)
+			if (e)
+				cudaEventDestroy(e);
 	delete[] c->ubo_set;
 	delete c;
 }
@@ -277,6 +285,18 @@ int hvcf_set_lights(hvcf_ctx* ctx, const void* lights, uint32_t n, int src_is_de
 		HVCF_CUDA(cudaMemcpyAsync(ctx->d_lights, lights, sizeof(hvcf_light_data) * static_cast<size_t>(n),
 			src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
 	ctx->num_lights = n;
+	ctx->bound_lights = nullptr;
+	return HVCF_OK;
+}
+
+int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_bind_lights: null context");
+	if (n > ctx->max_lights)
+		return fail(HVCF_ERR_CAPACITY, "hvcf_bind_lights: %u lights > max_lights %u", n, ctx->max_lights);
+	ctx->bound_lights = static_cast<const hvcf_light_data*>(device_lights);
+	ctx->num_lights = device_lights ? n : 0;
 	return HVCF_OK;
 }
 
@@ -291,7 +311,8 @@ int hvcf_update_light(hvcf_ctx* ctx, uint32_t index, const float xyz[3], void* s
 	HVCF_CUDA(cudaEventSynchronize(ctx->one_light_events[slot])); // slot's previous copy has been consumed
 	float* h = ctx->h_one_light[slot].position;
 	h[0] = xyz[0], h[1] = xyz[1], h[2] = xyz[2], h[3] = 1.0f;
-	HVCF_CUDA(cudaMemcpyAsync(ctx->d_lights[index].position, h, 16, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+	hvcf_light_data* base = ctx->bound_lights ? const_cast<hvcf_light_data*>(ctx->bound_lights) : ctx->d_lights;
+	HVCF_CUDA(cudaMemcpyAsync(base[index].position, h, 16, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
 	HVCF_CUDA(cudaEventRecord(ctx->one_light_events[slot], static_cast<cudaStream_t>(stream)));
 	return HVCF_OK;
 }
@@ -373,6 +394,9 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	uint32_t launches = 0;
+	ctx->ev_valid[frame] = false;
+	if (ctx->timing)
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][0], s));
 	if (ctx->aabb_dirty)
 	{
 		const int rc = hvcf_generate_aabbs(ctx, frame, stream);
@@ -391,7 +415,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		num_segs = (tiles_total + tiles_per_seg - 1) / tiles_per_seg; // no empty segment
 	if (n)
 	{
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], ctx->d_lights, n, padded, ctx->d_lights_view, s));
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], ctx->bound_lights ? ctx->bound_lights : ctx->d_lights, n, padded, ctx->d_lights_view, s));
 		CullParams p;
 		p.lights_view = ctx->d_lights_view;
 		p.aabbs = ctx->d_aabb;
@@ -403,7 +427,14 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		p.seg_counts = ctx->d_seg_counts;
 		p.seg_lists = ctx->d_seg_lists;
 		p.stats = stats;
+		if (ctx->timing)
+			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
 		HVCF_CUDA(launch_cull(ctx->variant, p, num_segs, s));
+		if (ctx->timing)
+		{
+			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
+			ctx->ev_valid[frame] = true;
+		}
 		launches += 2;
 	}
 	ctx->last_num_segs = num_segs;
@@ -435,6 +466,8 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	p.indices = ctx->d_indices;
 	p.frame_total = &ctx->d_global_index[frame];
 	HVCF_CUDA(launch_scatter(p, static_cast<cudaStream_t>(stream)));
+	if (ctx->timing)
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], static_cast<cudaStream_t>(stream)));
 	ctx->last_launches[frame] += 1;
 	return HVCF_OK;
 }
@@ -464,7 +497,7 @@ int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out)
 	out->light_cells = ctx->d_cells;
 	out->light_indices = ctx->d_indices;
 	out->global_index_count = ctx->d_global_index;
-	out->lights = ctx->d_lights;
+	out->lights = ctx->bound_lights ? const_cast<hvcf_light_data*>(ctx->bound_lights) : ctx->d_lights;
 	out->lights_view = reinterpret_cast<float*>(ctx->d_lights_view);
 	out->light_indices_capacity = static_cast<uint64_t>(ctx->cluster_total) * ctx->cap;
 	out->cluster_count = ctx->cluster_total;
@@ -528,6 +561,114 @@ int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
 	out->total_indices = ds.total_indices;
 	out->overflow_clusters = ds.overflow_clusters;
 	out->kernel_launches = ctx->last_launches[frame];
+	return HVCF_OK;
+}
+
+int hvcf_set_timing(hvcf_ctx* ctx, int enabled)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_timing: null context");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	if (enabled)
+		for (uint32_t f = 0; f < ctx->frame_count; ++f)
+			for (auto& e : ctx->ev[f])
+				if (!e)
+					HVCF_CUDA(cudaEventCreate(&e));
+	ctx->timing = enabled != 0;
+	return HVCF_OK;
+}
+
+int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms)
+{
+	if (!ctx || !out_cull_kernel_ms || !out_total_ms)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_timing: null argument");
+	if (frame >= ctx->frame_count || !ctx->timing)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_get_timing: timing disabled or bad frame");
+	HVCF_CUDA(cudaEventSynchronize(ctx->ev[frame][3]));
+	*out_cull_kernel_ms = 0.0f;
+	if (ctx->ev_valid[frame])
+		HVCF_CUDA(cudaEventElapsedTime(out_cull_kernel_ms, ctx->ev[frame][1], ctx->ev[frame][2]));
+	HVCF_CUDA(cudaEventElapsedTime(out_total_ms, ctx->ev[frame][0], ctx->ev[frame][3]));
+	return HVCF_OK;
+}
+
+int hvcf_measure_fp32_issue_rate(int device, double* out_lane_ops_per_second)
+{
+	if (!out_lane_ops_per_second)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_measure_fp32_issue_rate: null argument");
+	if (device >= 0)
+		HVCF_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	int dev = 0;
+	HVCF_CUDA(cudaGetDevice(&dev));
+	HVCF_CUDA(cudaGetDeviceProperties(&prop, dev));
+	float* sink = nullptr;
+	HVCF_CUDA(cudaMalloc(&sink, 16));
+	cudaEvent_t e0, e1;
+	HVCF_CUDA(cudaEventCreate(&e0));
+	HVCF_CUDA(cudaEventCreate(&e1));
+	const uint32_t blocks = static_cast<uint32_t>(prop.multiProcessorCount) * 8, iters = 1u << 15;
+	double best = 0.0;
+	for (int rep = 0; rep < 5; ++rep)
+	{
+		HVCF_CUDA(cudaEventRecord(e0, 0));
+		HVCF_CUDA(launch_fp32_issue_rate(sink, blocks, iters, 0));
+		HVCF_CUDA(cudaEventRecord(e1, 0));
+		HVCF_CUDA(cudaEventSynchronize(e1));
+		float ms = 0.0f;
+		HVCF_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+		const double ops = static_cast<double>(blocks) * 256.0 * iters * 16.0;
+		if (rep > 0 && ms > 0.0f && ops / (ms * 1e-3) > best)
+			best = ops / (ms * 1e-3);
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	cudaFree(sink);
+	*out_lane_ops_per_second = best;
+	return HVCF_OK;
+}
+
+int hvcf_device_alloc(int device, size_t bytes, void** out_device_ptr)
+{
+	if (!out_device_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_alloc: null argument");
+	if (device >= 0)
+		HVCF_CUDA(cudaSetDevice(device));
+	HVCF_CUDA(cudaMalloc(out_device_ptr, bytes ? bytes : 16));
+	return HVCF_OK;
+}
+
+int hvcf_device_free(void* device_ptr)
+{
+	if (device_ptr)
+		HVCF_CUDA(cudaFree(device_ptr));
+	return HVCF_OK;
+}
+
+int hvcf_device_upload(void* device_dst, size_t offset, const void* host_src, size_t bytes, void* stream)
+{
+	if (!device_dst || (bytes && !host_src))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_upload: null argument");
+	if (bytes)
+		HVCF_CUDA(cudaMemcpyAsync(static_cast<char*>(device_dst) + offset, host_src, bytes, cudaMemcpyHostToDevice,
+			static_cast<cudaStream_t>(stream)));
+	return HVCF_OK;
+}
+
+int hvcf_device_download(void* host_dst, const void* device_src, size_t offset, size_t bytes, void* stream)
+{
+	if (!device_src || (bytes && !host_dst))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_download: null argument");
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (bytes)
+		HVCF_CUDA(cudaMemcpyAsync(host_dst, static_cast<const char*>(device_src) + offset, bytes, cudaMemcpyDeviceToHost, s));
+	HVCF_CUDA(cudaStreamSynchronize(s));
+	return HVCF_OK;
+}
+
+int hvcf_stream_synchronize(void* stream)
+{
+	HVCF_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
 	return HVCF_OK;
 }
 

@@ -1,6 +1,6 @@
 // hvcf_device.cuh -- device-side helpers for libhvcf (sm_100a only).
 //
-// Arithmetic rules (oracle/hvcf_oracle.h): IEEE binary32, round-to-nearest-even,
+// Arithmetic rules: IEEE binary32, round-to-nearest-even,
 // NO contraction.  Every float op on the parity path goes through an explicit _rn intrinsic or an
 // explicit .rn PTX instruction, so the result does not depend on --fmad.
 #pragma once

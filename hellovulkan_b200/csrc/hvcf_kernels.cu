@@ -456,6 +456,39 @@ __global__ void __launch_bounds__(256) scatter_kernel(const ScatterParams p)
 }
 
 // ======================================================================================================
+// FP32 issue-rate microbenchmark: 8 independent mul/add chains per thread, explicit .rn (never
+// contracted), enough warps to saturate every SMSP.  Used only to state the roofline denominator.
+// ======================================================================================================
+__global__ void __launch_bounds__(256) fp32_issue_rate_kernel(float* __restrict__ sink, uint32_t iters, float c, float d)
+{
+	float a[8];
+#pragma unroll
+	for (int i = 0; i < 8; ++i)
+		a[i] = static_cast<float>(threadIdx.x + i);
+	for (uint32_t it = 0; it < iters; ++it)
+	{
+#pragma unroll
+		for (int i = 0; i < 8; ++i)
+			a[i] = __fmul_rn(a[i], c);
+#pragma unroll
+		for (int i = 0; i < 8; ++i)
+			a[i] = __fadd_rn(a[i], d);
+	}
+	float s = 0.0f;
+#pragma unroll
+	for (int i = 0; i < 8; ++i)
+		s += a[i];
+	if (s == 12345.678f)
+		sink[0] = s;
+}
+
+cudaError_t launch_fp32_issue_rate(float* sink, uint32_t blocks, uint32_t iters, cudaStream_t stream)
+{
+	fp32_issue_rate_kernel<<<blocks, 256, 0, stream>>>(sink, iters, 0.999f, 0.001f);
+	return cudaGetLastError();
+}
+
+// ======================================================================================================
 // launchers
 // ======================================================================================================
 cudaError_t launch_aabb_generate(const hvcf_cluster_forward_ubo* ubo, const float* zplanes, hvcf_aabb* out,

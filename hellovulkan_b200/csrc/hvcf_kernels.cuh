@@ -49,5 +49,7 @@ cudaError_t launch_count(const uint32_t* seg_counts, uint32_t num_segs, uint32_t
 cudaError_t launch_scan(const uint32_t* block_sums, uint32_t num_blocks, uint32_t* block_offsets,
 	uint32_t* shard_total, DeviceStats* stats, cudaStream_t stream);
 cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream);
+// 16 lane-ops per thread per iteration (8 FMUL + 8 FADD)
+cudaError_t launch_fp32_issue_rate(float* sink, uint32_t blocks, uint32_t iters, cudaStream_t stream);
 
 } // namespace hvcf

@@ -55,7 +55,9 @@ EXPORTS = [
     "hvcf_set_ubo", "hvcf_mark_aabb_dirty", "hvcf_is_aabb_dirty", "hvcf_generate_aabbs", "hvcf_cull", "hvcf_cull_begin",
     "hvcf_cull_finish", "hvcf_shard_total_ptr", "hvcf_get_device_buffers", "hvcf_download_aabbs",
     "hvcf_download_light_cells", "hvcf_download_light_indices", "hvcf_download_total", "hvcf_get_stats",
-    "hvcf_host_alloc", "hvcf_host_free",
+    "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
+    "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
+    "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate",
 ]
 
 _lib = None
@@ -92,6 +94,18 @@ def load():
     lib.hvcf_get_stats.argtypes = [vp, u32, ctypes.POINTER(Stats), vp]
     lib.hvcf_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(vp)]
     lib.hvcf_host_free.argtypes = [vp]
+    lib.hvcf_bind_lights.argtypes = [vp, vp, u32]
+    lib.hvcf_device_alloc.argtypes = [i32, ctypes.c_size_t, ctypes.POINTER(vp)]
+    lib.hvcf_device_free.argtypes = [vp]
+    lib.hvcf_device_upload.argtypes = [vp, ctypes.c_size_t, vp, ctypes.c_size_t, vp]
+    lib.hvcf_device_download.argtypes = [vp, vp, ctypes.c_size_t, ctypes.c_size_t, vp]
+    lib.hvcf_stream_synchronize.argtypes = [vp]
+    f3 = ctypes.POINTER(ctypes.c_float)
+    lib.hvcf_host_camera_ubo.argtypes = [f3, f3, ctypes.c_float, ctypes.c_float, u32, u32, u32, vp]
+    lib.hvcf_host_init_lights.argtypes = [u32, u32, vp]
+    lib.hvcf_set_timing.argtypes = [vp, i32]
+    lib.hvcf_get_timing.argtypes = [vp, u32, f3, f3]
+    lib.hvcf_measure_fp32_issue_rate.argtypes = [i32, ctypes.POINTER(ctypes.c_double)]
     _lib = lib
     return lib
 
@@ -103,6 +117,38 @@ def _check(rc):
 
 def _ptr(a):
     return a.ctypes.data_as(ctypes.c_void_p)
+
+
+# reference camera of AppPBRClusterForward::Init (AppPBRClusterForward.cpp:22)
+REF_CAMERA_POS = (0.0, 1.0, 6.0)
+REF_CAMERA_TARGET = (0.0, 2.5, 0.0)
+
+
+def host_camera_ubo(grid, screen, pos=REF_CAMERA_POS, target=REF_CAMERA_TARGET):
+    """Camera -> ClusterForwardUBO on the host (include/hv/Camera.h); returns 176 bytes as uint8."""
+    lib = load()
+    ubo = np.zeros(UBO_BYTES, np.uint8)
+    p = (ctypes.c_float * 3)(*[float(v) for v in pos])
+    t = (ctypes.c_float * 3)(*[float(v) for v in target])
+    _check(lib.hvcf_host_camera_ubo(p, t, float(screen[0]), float(screen[1]), grid[0], grid[1], grid[2], _ptr(ubo)))
+    return ubo
+
+
+def host_init_lights(count, seed=12345, out=None):
+    """AppPBRClusterForward::InitLights with an explicit seed; `out` may be a pinned LIGHT_DT array."""
+    lib = load()
+    if out is None:
+        out = np.zeros(count, LIGHT_DT)
+    assert out.dtype == LIGHT_DT and len(out) >= count
+    _check(lib.hvcf_host_init_lights(seed, count, _ptr(out)))
+    return out
+
+
+def measure_fp32_issue_rate(device=-1):
+    """lane-operations per second of a non-FMA FADD/FMUL loop on `device` (roofline denominator)."""
+    v = ctypes.c_double(0.0)
+    _check(load().hvcf_measure_fp32_issue_rate(device, ctypes.byref(v)))
+    return float(v.value)
 
 
 class Context:
@@ -153,6 +199,9 @@ class Context:
 
     def set_lights_ptr(self, ptr, n, is_device, stream=None):
         _check(self.lib.hvcf_set_lights(self.handle, ctypes.c_void_p(ptr), n, int(is_device), stream))
+
+    def bind_lights(self, device_ptr, n):
+        _check(self.lib.hvcf_bind_lights(self.handle, ctypes.c_void_p(device_ptr) if device_ptr else None, n))
 
     def update_light(self, index, xyz, stream=None):
         arr = (ctypes.c_float * 3)(*[float(v) for v in xyz])
@@ -218,6 +267,15 @@ class Context:
         t = ctypes.c_uint32(0)
         _check(self.lib.hvcf_download_total(self.handle, frame, ctypes.byref(t), stream))
         return int(t.value)
+
+    def set_timing(self, enabled=True):
+        _check(self.lib.hvcf_set_timing(self.handle, int(enabled)))
+
+    def timing(self, frame=0):
+        """(culling-kernel ms, whole-call ms) of the last hvcf_cull on `frame`; synchronises."""
+        a, b = ctypes.c_float(0), ctypes.c_float(0)
+        _check(self.lib.hvcf_get_timing(self.handle, frame, ctypes.byref(a), ctypes.byref(b)))
+        return float(a.value), float(b.value)
 
     def stats(self, frame=0, stream=None):
         s = Stats()

@@ -1,0 +1,148 @@
+"""z-slab sharding of the cluster grid across the GPUs of one box.
+
+The reference has no multi-GPU path; this is new plumbing around the one exchange step the algorithm
+has.  Clusters are independent given all lights (LightCulling.comp:59-88), and
+tileIndex = x + y*X + z*X*Y makes a z-range a contiguous cluster range, so rank r owns slices
+[z0_r, z1_r) and its light cells / index segment concatenate with its neighbours'.
+
+Per frame:
+  1. broadcast the light buffer (48 B x L) from rank 0                      -- dist.broadcast (NCCL)
+  2. local: transform + cull + count + scan      (engine.cull_begin)        -- no communication
+  3. all-gather the shard totals (4 B each); base_r = sum of totals below r -- dist.all_gather
+  4. local: cells + indices written at GLOBAL offsets (engine.cull_finish)
+  5. all-gather the light cells (equal slabs) and the index segments        -- dist.all_gather / broadcast
+so that every GPU holds the full light grid, as BASELINE.json's north_star asks.
+
+torch.distributed is plumbing only.  `engine` is duck-typed (begin/finish/views) so the host logic can be
+exercised on CPU tensors under gloo with a stand-in engine (tests/test_sharded_gloo.py); the product
+engine is HvcfEngine below, which has no CPU path.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def z_slabs(Z: int, world: int):
+    """Contiguous z-ranges, sizes differing by at most one slice; ranks beyond Z get empty ranges."""
+    base, rem = divmod(Z, world)
+    out, z = [], 0
+    for r in range(world):
+        n = base + (1 if r < rem else 0)
+        out.append((z, z + n))
+        z += n
+    return out
+
+
+class DevicePtrView:
+    """Zero-copy torch view of a raw device pointer (via __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+def as_tensor(ptr: int, nbytes: int, device) -> torch.Tensor:
+    return torch.as_tensor(DevicePtrView(ptr, nbytes), device=device)
+
+
+class HvcfEngine:
+    """One hvcf context restricted to this rank's z-slab; exposes its device buffers as torch tensors."""
+
+    def __init__(self, hvcf, grid, max_lights, z_range, device_index, cap=150):
+        self.hvcf = hvcf
+        self.device = torch.device("cuda", device_index)
+        self.ctx = hvcf.Context(grid=grid, max_lights=max_lights, max_lights_per_cluster=cap, device=device_index,
+                                z_begin=z_range[0], z_end=z_range[1])
+        b = self.ctx.buffers()
+        C = b.cluster_count
+        self.cluster_begin, self.cluster_end = b.cluster_begin, b.cluster_end
+        self.lights = as_tensor(b.lights, 48 * max_lights, self.device)
+        self.cells = as_tensor(b.light_cells, 8 * C, self.device).view(torch.int32).view(C, 2)
+        self.indices = as_tensor(b.light_indices, 4 * int(b.light_indices_capacity), self.device).view(torch.int32)
+        self.shard_total = as_tensor(self.ctx.shard_total_ptr(), 4, self.device).view(torch.int32)
+        self.base = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.num_lights = 0
+
+    def set_num_lights(self, n):
+        # the light bytes already sit in self.lights (broadcast target); just tell the context how many
+        b = self.ctx.buffers()
+        self.ctx.bind_lights(b.lights, n)
+        self.num_lights = n
+
+    def set_ubo(self, frame, ubo):
+        self.ctx.set_ubo(frame, ubo)
+
+    def cull_begin(self, frame):
+        self.ctx.cull_begin(frame)
+
+    def cull_finish(self, frame, base: torch.Tensor):
+        self.base.copy_(base.view(1))
+        self.ctx.cull_finish(frame, self.base.data_ptr())
+
+    def close(self):
+        self.ctx.close()
+
+
+class ShardedCuller:
+    """Runs steps 1-5 above on `engine`; every tensor lives on engine's device."""
+
+    def __init__(self, engine, grid, world=None, rank=None, group=None):
+        self.engine = engine
+        self.group = group
+        self.world = dist.get_world_size(group) if world is None else world
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.grid = tuple(grid)
+        self.slabs = z_slabs(grid[2], self.world)
+        xy = grid[0] * grid[1]
+        self.cluster_ranges = [(a * xy, b * xy) for a, b in self.slabs]
+        self.equal = len({b - a for a, b in self.slabs}) == 1
+
+    def broadcast_lights(self, n):
+        """step 1: rank 0's first 48*n bytes of engine.lights reach every rank."""
+        if self.world > 1:
+            dist.broadcast(self.engine.lights[: 48 * n], src=0, group=self.group)
+        self.engine.set_num_lights(n)
+
+    def frame(self, frame, gather=True):
+        e = self.engine
+        e.cull_begin(frame)                                           # step 2
+        totals = torch.zeros(self.world, dtype=torch.int32, device=e.shard_total.device)
+        if self.world > 1:                                            # step 3
+            dist.all_gather_into_tensor(totals, e.shard_total, group=self.group)
+        else:
+            totals.copy_(e.shard_total)
+        bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
+        e.cull_finish(frame, bases[self.rank])                        # step 4
+        if gather and self.world > 1:                                 # step 5
+            self._gather(totals, bases)
+        return totals, bases
+
+    def _gather(self, totals, bases):
+        e = self.engine
+        if self.equal:
+            a, b = self.cluster_ranges[self.rank]
+            dist.all_gather_into_tensor(e.cells.view(-1), e.cells[a:b].reshape(-1).clone(), group=self.group)
+        else:
+            for r, (a, b) in enumerate(self.cluster_ranges):
+                if b > a:
+                    dist.broadcast(e.cells[a:b], src=r, group=self.group)
+        # index segments are variable-sized: one broadcast per owner over its [base, base+total) range
+        host = torch.stack([bases, totals]).cpu().numpy()
+        for r in range(self.world):
+            o, n = int(host[0, r]), int(host[1, r])
+            if n:
+                dist.broadcast(e.indices[o: o + n], src=r, group=self.group)
+
+
+def merge_reference(cells_per_rank, indices_per_rank):
+    """Pure-numpy statement of what steps 3-5 must produce (used by tests)."""
+    totals = [int(c["count"].sum()) for c in cells_per_rank]
+    bases = np.concatenate([[0], np.cumsum(totals)[:-1]]).astype(np.int64)
+    cells = np.concatenate(cells_per_rank).copy()
+    off = 0
+    for c, b in zip(cells_per_rank, bases):
+        cells["offset"][off: off + len(c)] = c["offset"] + b
+        off += len(c)
+    return cells, np.concatenate(indices_per_rank)

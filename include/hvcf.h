@@ -158,6 +158,40 @@ HVCF_API int hvcf_download_light_indices(hvcf_ctx* ctx, void* dst, size_t bytes,
 HVCF_API int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void* stream);
 HVCF_API int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream);
 
+/* Binds an EXTERNAL device light buffer (n x 48 B) instead of copying into the context's own:
+ * the descriptor write of binding 1 in PipelineLightCulling::CreateDescriptor
+ * (PipelineLightCulling.cpp:121-141).  The caller keeps ownership; hvcf_cull reads it in place,
+ * so ResourcesLight::UpdateLightPosition writes are seen by the next frame without a copy.
+ * NULL rebinds the context's own buffer. */
+HVCF_API int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n);
+
+/* Raw device buffers for the C++ mirror of VulkanBuffer (include/hv/Context.h):
+ * VulkanBuffer::CreateBuffer / Destroy / UploadOffsetBufferData / DownloadBufferData
+ * (Source/Vulkan/VulkanBuffer.cpp:6-50, :148-178).  upload is stream-ordered and stages through
+ * pageable memory (synchronous w.r.t. the host buffer); download synchronises `stream`. */
+HVCF_API int hvcf_device_alloc(int device, size_t bytes, void** out_device_ptr);
+HVCF_API int hvcf_device_free(void* device_ptr);
+HVCF_API int hvcf_device_upload(void* device_dst, size_t offset, const void* host_src, size_t bytes, void* stream);
+HVCF_API int hvcf_device_download(void* host_dst, const void* device_src, size_t offset, size_t bytes, void* stream);
+HVCF_API int hvcf_stream_synchronize(void* stream);
+
+/* Host-side producers of the path's inputs, compiled from include/hv/Camera.h and
+ * hellovulkan_b200/host/hvcf_host.cpp (C++, CPU -- as in the reference):
+ *   Camera::SetPositionAndTarget + GetClusterForwardUBO (Source/Camera.cpp:81-93,113-139,178-197)
+ *   AppPBRClusterForward::InitLights with an explicit seed (Source/Apps/AppPBRClusterForward.cpp:81-118) */
+HVCF_API int hvcf_host_camera_ubo(const float position[3], const float target[3], float screen_width, float screen_height,
+	uint32_t slice_count_x, uint32_t slice_count_y, uint32_t slice_count_z, hvcf_cluster_forward_ubo* out);
+HVCF_API int hvcf_host_init_lights(uint32_t seed, uint32_t count, hvcf_light_data* out);
+
+/* Measurement hooks (TracyVkZone "Light_Culling", PipelineLightCulling.cpp:53, becomes CUDA events):
+ * with timing enabled hvcf_cull brackets the culling kernel and the whole call with events on `stream`;
+ * hvcf_get_timing synchronises the end event and returns milliseconds. */
+HVCF_API int hvcf_set_timing(hvcf_ctx* ctx, int enabled);
+HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms);
+/* Measured FP32 issue rate of the device (independent FADD/FMUL chains, no FMA), in lane-operations per
+ * second: the denominator of the FP32-issue roofline; MEASURED_PEAKS.json has none. */
+HVCF_API int hvcf_measure_fp32_issue_rate(int device, double* out_lane_ops_per_second);
+
 /* Pinned host staging for callers that want asynchronous host<->device copies
  * (VMA_MEMORY_USAGE_CPU_TO_GPU in the reference, ResourcesLight.cpp:14-16). */
 HVCF_API int hvcf_host_alloc(size_t bytes, void** out_ptr);
