@@ -1,0 +1,492 @@
+#!/usr/bin/env python
+"""bench.py -- cluster-light tests/s and light-culling ms/frame of the B200 path, against its roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one frame of the hot path (AABB generation if dirty + light transform + culling +
+offsets + scatter) over one synthetic scene (hvcf_host_init_lights, seed 12345; reference camera).
+
+  N = 1   workload A65k = BASELINE.json configs[1]: 16x9x24 clusters x 65,536 lights, 2560x1600.
+  N > 1   every rank culls its own frames of the same workload (the frame-partitioned mode of
+          configs[4]; no data-path collective) -> "scaling": "weak"; the line additionally carries
+          "sharded": the z-slab sharded grid of configs[3] (NCCL light broadcast + grid all-gather).
+
+Keys of the JSON line (rank 0 prints exactly one line on stdout):
+  value          nominal cluster x light tests per second, whole job, inputs resident in HBM
+  e2e            same metric through the C ABI with HOST buffers: pinned H2D of the light buffer and
+                 the UBO, the frame, D2H of light cells + index list, every step
+  roofline       the culling kernel: executed tests x 16 FP32-pipe lane-ops / kernel time (CUDA events
+                 inside libhvcf, live) against the FP32 issue rate measured on this GPU
+  cpu_baseline   the reference's own shader source compiled as C++ (oracle/_ref), all host threads
+
+--impl reference times that CPU build alone (rank 0 only under torchrun).
+Nothing here reads /root/reference at run time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# name -> (grid, screen, lights)     
+WORKLOADS = {
+    "A1k": ((16, 9, 24), (2560, 1600), 1000),            # configs[0]
+    "A65k": ((16, 9, 24), (2560, 1600), 65536),          # configs[1]  <- default at N=1
+    "A1M": ((16, 9, 24), (2560, 1600), 1 << 20),         # north_star "1M lights x 16x9x24"
+    "B1M": ((32, 18, 48), (3840, 2160), 1 << 20),        # configs[2]
+    "C16M": ((64, 36, 96), (3840, 2160), 1 << 24),       # configs[3] (sharded)
+}
+LANE_OPS_PER_TEST = 16  # 6 min/max + 3 sub + 3 mul + 3 add + 1 compare
+L2_FLUSH_BYTES = 256 << 20
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="A65k", choices=sorted(WORKLOADS))
+    ap.add_argument("--sharded-workload", default="C16M", choices=sorted(WORKLOADS))
+    ap.add_argument("--sharded-steps", type=int, default=3)
+    ap.add_argument("--no-sharded", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=4.0, help="wall-clock budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled in the background while the GPU loops run (B200_PROFILING.md)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, device_index):
+        self.samples = []  # (t, sm, smmax, power, [reasons])
+        self.proc = None
+        self.windows = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-lms", "50", "-i", str(device_index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm, smmax, power = float(parts[0]), float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            reasons = [n for n, v in zip(self.NAMES, parts[3:7]) if v.lower().startswith("active")]
+            self.samples.append((time.time(), sm, smmax, power, reasons))
+
+    def window(self, t0, t1):
+        self.windows.append((t0, t1))
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "window": "none"}
+        inwin = [s for s in self.samples if any(a <= s[0] <= b for a, b in self.windows)]
+        where = "timed"
+        if len(inwin) < 3:  # region shorter than the sampling period: use the loaded samples of the whole run
+            pmax = max(s[3] for s in self.samples)
+            inwin = [s for s in self.samples if s[3] >= 0.6 * pmax] or self.samples
+            where = "run"
+        reasons = sorted({r for s in inwin for r in s[4]})
+        return {"sm_mhz": float(np.median([s[1] for s in inwin])), "sm_max_mhz": float(max(s[2] for s in inwin)),
+                "power_w": float(np.median([s[3] for s in inwin])), "reasons": reasons, "samples": len(inwin), "window": where}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU side: the reference's own shader sources compiled as C++ (oracle/_ref) -- or, if that .so did
+# not travel, the oracle port.  The only places bench.py touches oracle/.
+# ------------------------------------------------------------------------------------------------
+def cpu_checker():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import cpu_checkers as cc
+    if cc.Reference.available():
+        ref = cc.Reference()
+        return "reference", ref, ref.max_threads()
+    orc = cc.Oracle()
+    return "port", orc, orc.max_threads()
+
+
+def cpu_frame_fn(kind, impl, grid, screen, n):
+    """Returns (fn, tests_per_call, sample_description): fn() culls one bounded sample on the host cores."""
+    ubo = impl.camera_ubo(grid, screen)
+    aabbs = impl.generate_aabbs(ubo)
+    lights = impl.init_lights(n)
+    C = len(aabbs)
+    threads = impl.max_threads()
+    full = C * n
+    # bound one call to ~3e8 nominal tests (a second or two on 8 cores): whole frame for A65k,
+    # an evenly strided cluster subset (every slab represented) for the larger grids
+    stride = max(1, int(np.ceil(full / 3.0e8)))
+    if stride == 1:
+        sub, desc = aabbs, f"whole frame: {C} clusters x {n} lights"
+    else:
+        sub = np.ascontiguousarray(aabbs[::stride])
+        desc = f"every {stride}th cluster ({len(sub)} of {C}) x {n} lights"
+    if kind == "reference":
+        # hvref_cull dispatches one workgroup per cluster of the grid in the UBO; a subset is run by
+        # shrinking the Z count of a copy of the UBO to cover len(sub) clusters (the shader only uses the
+        # counts to form the tile index)
+        u = ubo.copy()
+        if stride > 1:
+            X, Y = grid[0], grid[1]
+            m = (len(sub) // (X * Y)) * X * Y
+            sub = np.ascontiguousarray(sub[:m])
+            u.view(np.uint32)[40] = m // (X * Y)
+            desc = f"every {stride}th cluster ({m} of {C}) x {n} lights"
+
+        def fn():
+            impl.cull(u, sub, lights, threads=threads)
+    else:
+        def fn():
+            impl.cull(ubo, sub, lights, threads=threads)
+    return fn, len(sub) * n, desc, threads
+
+
+def time_cpu(kind, impl, workload, budget_s, min_calls=2, max_calls=64):
+    grid, screen, n = WORKLOADS[workload]
+    fn, tests, desc, threads = cpu_frame_fn(kind, impl, grid, screen, n)
+    fn()  # warm the pages
+    times = []
+    t_begin = time.perf_counter()
+    while len(times) < min_calls or (time.perf_counter() - t_begin < budget_s and len(times) < max_calls):
+        t0 = time.perf_counter()
+        fn()
+        times.append(time.perf_counter() - t0)
+    med = float(np.median(times))
+    return {"value": tests / med, "unit": "tests/s", "cores": threads, "kind": kind,
+            "sample": f"{desc}; {len(times)} calls, median {med * 1e3:.1f} ms/call", "ms_per_call": med * 1e3,
+            "tests_per_call": tests}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    kind, impl, threads = cpu_checker()
+    grid, screen, n = WORKLOADS[args.workload]
+    fn, tests, desc, threads = cpu_frame_fn(kind, impl, grid, screen, n)
+    for _ in range(max(1, min(args.warmup, 3))):
+        fn()
+    # bound the whole run to a few minutes whatever K the driver passes
+    steps, t_total, t_begin = 0, 0.0, time.perf_counter()
+    while steps < args.steps and (steps < 3 or time.perf_counter() - t_begin < 150.0):
+        t0 = time.perf_counter()
+        fn()
+        t_total += time.perf_counter() - t0
+        steps += 1
+    ms = t_total / steps * 1e3
+    value = tests / (ms * 1e-3)
+    full_frame_tests = grid[0] * grid[1] * grid[2] * n
+    line = {
+        "impl": "reference", "metric": "cluster-light tests/s", "value": value, "unit": "tests/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "ms_per_frame_equiv": full_frame_tests / value * 1e3,
+        "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
+                   "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)", "device": "host cpu"},
+        "cpu_baseline": {"value": value, "unit": "tests/s", "cores": threads, "kind": kind, "sample": desc},
+        "e2e": {"value": value, "unit": "tests/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": ("reference = HelloVulkan's AABBGenerator.comp/LightCulling.comp + Camera.cpp compiled as C++ with g++ "
+                 "(oracle/_ref), OpenMP over workgroups; its Vulkan path is unavailable on this box"
+                 if kind == "reference" else "oracle port (oracle/_ref not present)"),
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload):
+    """dram bytes per launch of the culling kernel from the committed ncu --set full capture, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(workload)
+    return None
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from hellovulkan_b200 import hvcf
+
+    hvcf.load()  # raises if libhvcf.so is missing: there is no fallback
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl ours needs a CUDA device (libhvcf has no CPU path)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}; using WORLD_SIZE")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    grid, screen, n = WORKLOADS[args.workload]
+    C = grid[0] * grid[1] * grid[2]
+    K, W = args.steps, max(args.warmup, 3)
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream  # libhvcf launches on torch's current stream, so torch events bracket its kernels
+
+    # ---- inputs (host side of the reference interface: Camera -> UBO, InitLights) -----------------
+    pinned = hvcf.PinnedBuffer(48 * n)
+    lights = pinned.array.view(hvcf.LIGHT_DT)
+    hvcf.host_init_lights(n, out=lights)
+    pos_a, pos_b = hvcf.REF_CAMERA_POS, (0.5, 1.0, 6.0)  # two views, same projection: AABBs stay valid
+    ubos = [hvcf.host_camera_ubo(grid, screen, pos=pos_a), hvcf.host_camera_ubo(grid, screen, pos=pos_b)]
+    pinned_ubo = hvcf.PinnedBuffer(2 * hvcf.UBO_BYTES)
+    for f in range(2):
+        pinned_ubo.array[f * hvcf.UBO_BYTES:(f + 1) * hvcf.UBO_BYTES] = ubos[f]
+
+    ctx = hvcf.Context(grid=grid, max_lights=n, device=local)
+    ctx.set_timing(True)
+    ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)
+    for f in range(2):
+        ctx.set_ubo(f, ubos[f], sp)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    sampler = ClockSampler(local) if rank == 0 else None
+
+    # ---- value: inputs resident in HBM, L2 flushed between steps, CUDA events per step ------------
+    for i in range(W):
+        ctx.cull(i & 1, sp)
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    kernel_ms, launches, executed, total_idx = [], 0, 0, 0
+    t_wall0 = time.time()
+    for i in range(K):
+        flush.zero_()
+        ev[i][0].record(stream)
+        ctx.cull(i & 1, sp)
+        ev[i][1].record(stream)
+        if i < 2 or i >= K - 2 or (i % 16) == 0:  # sampled read-back of the library's own kernel events + counters
+            km, _ = ctx.timing(i & 1)
+            kernel_ms.append(km)
+            st = ctx.stats(i & 1, sp)
+            launches_per_step, executed, total_idx = st["kernel_launches"], st["executed_tests"], st["total_indices"]
+    barrier()
+    t_wall1 = time.time()
+    if sampler:
+        sampler.window(t_wall0, t_wall1)
+    step_ms = np.array([a.elapsed_time(b) for a, b in ev])
+    t = torch.tensor([float(step_ms.sum())], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / K
+    nominal = C * n
+    value = world * nominal / (ms_per_step * 1e-3)
+    launches = launches_per_step * K
+
+    # ---- e2e: HOST buffers through the C ABI, H2D and D2H inside the timed region -------------------
+    cells_host = hvcf.PinnedBuffer(8 * C)
+    idx_host = hvcf.PinnedBuffer(4 * C * 150)
+    total_host = np.zeros(1, np.uint32)
+    lib = hvcf.load()
+    import ctypes
+
+    def e2e_step(f):
+        ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)                      # H2D 48*n
+        ctx.set_ubo_ptr(f, pinned_ubo.ptr.value + f * hvcf.UBO_BYTES, sp)        # H2D 176
+        ctx.cull(f, sp)
+        hvcf._check(lib.hvcf_download_total(ctx.handle, f, total_host.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), sp))
+        hvcf._check(lib.hvcf_download_light_cells(ctx.handle, cells_host.ptr, 8 * C, sp))
+        hvcf._check(lib.hvcf_download_light_indices(ctx.handle, idx_host.ptr, 4 * int(total_host[0]), sp))
+        return int(total_host[0])
+
+    for i in range(W):
+        e2e_step(i & 1)
+    barrier()
+    Ke = min(K, 200)
+    t0 = time.perf_counter()
+    t_wall0 = time.time()
+    for i in range(Ke):
+        tot = e2e_step(i & 1)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if sampler:
+        sampler.window(t_wall0, time.time())
+    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item()) / Ke * 1e3
+    e2e = {"value": world * nominal / (e2e_ms * 1e-3), "unit": "tests/s", "ms_per_step": e2e_ms, "steps": Ke,
+           "h2d_bytes_per_step": 48 * n + hvcf.UBO_BYTES, "d2h_bytes_per_step": 4 + 8 * C + 4 * tot,
+           "timer": "host perf_counter around the loop, synchronised both sides (the downloads block)"}
+
+    # ---- roofline of the dominant kernel (cull_kernel), live ------------------------------------------
+    k_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
+    issue_rate = hvcf.measure_fp32_issue_rate(local)          # lane-ops/s, FADD/FMUL chains, measured now
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    achieved = executed * LANE_OPS_PER_TEST / (k_ms * 1e-3)    # lane-ops/s
+    hbm_gbs, hbm_src = hbm_peak()
+    alg_bytes = 48 * n + 16 * n * 2 + 32 * C + 8 * C + 4 * total_idx   # AoS in, SoA out+in, AABB, cells, indices
+    roofline = {
+        "bound": "fp32",
+        "kernel": "cull_kernel",
+        "achieved": achieved / 1e12, "peak": issue_rate / 1e12, "unit": "TFLOP/s", "frac": achieved / issue_rate,
+        "peak_source": "hvcf_measure_fp32_issue_rate on this GPU, this run (non-FMA FADD/FMUL issue rate; MEASURED_PEAKS.json has no "
+                       "FP32 figure); nominal 148 SM x 128 lanes x 1.965 GHz = 37.2",
+        "flop_per_test": LANE_OPS_PER_TEST, "executed_tests_per_launch": executed, "nominal_tests_per_launch": nominal,
+        "kernel_ms": k_ms, "kernel_share_of_step": k_ms / ms_per_step,
+        "executed_tests_per_s": executed / (k_ms * 1e-3),
+        "traffic": ncu_traffic(args.workload),
+        "hbm": {"algorithmic_bytes_per_step": alg_bytes, "achieved_gbs": alg_bytes / (ms_per_step * 1e-3) / 1e9, "peak_gbs": hbm_gbs,
+                "peak_source": hbm_src, "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / hbm_gbs},
+    }
+
+    # ---- z-slab sharded grid (configs[3]): NCCL light broadcast + grid all-gather ------------------------
+    sharded = None
+    ctx.close()
+    del flush
+    if world > 1 and not args.no_sharded:
+        try:
+            sharded = run_sharded(args, hvcf, world, rank, local, dev, barrier)
+        except Exception as e:  # the headline line must still be printed
+            sharded = {"error": f"{type(e).__name__}: {e}"}
+
+    if sampler:
+        sampler.stop()
+    clocks = sampler.summary() if sampler else None
+
+    # ---- CPU baseline beside it (rank 0, N=1 only) -------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        kind, impl, _ = cpu_checker()
+        cpu = time_cpu(kind, impl, args.workload, args.cpu_seconds)
+
+    if world > 1:
+        dist.barrier(device_ids=[local])
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
+    line = {
+        "metric": "cluster-light tests/s", "value": value, "unit": "tests/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
+                   "max_lights_per_cluster": 150, "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)",
+                   "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
+                   "parallelism": "single GPU" if world == 1 else f"{world} ranks x own frames (no collective); z-slab sharding under 'sharded'",
+                   "tests": "nominal = clusters x lights; executed (early exit at 150 hits, LightCulling.comp:71) under roofline"},
+        "step_ms_min": float(step_ms.min()), "step_ms_median": float(np.median(step_ms)),
+        "executed_tests_per_step": executed, "total_indices": total_idx,
+        "e2e": e2e, "gpu_launches": launches, "gpu_launches_per_step": launches_per_step,
+        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "impl": "ours",
+    }
+    if sharded is not None:
+        line["sharded"] = sharded
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_sharded(args, hvcf, world, rank, local, dev, barrier):
+    """configs[3]: the cluster grid split into z-slabs, one per rank; per step: NCCL broadcast of the light
+    buffer from rank 0, local culling, all-gather of totals, scatter at global offsets, all-gather of the grid."""
+    import torch
+    import torch.distributed as dist
+    from hellovulkan_b200.sharded import HvcfEngine, ShardedCuller, z_slabs
+
+    grid, screen, n = WORKLOADS[args.sharded_workload]
+    C = grid[0] * grid[1] * grid[2]
+    slabs = z_slabs(grid[2], world)
+    eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
+    sc = ShardedCuller(eng, grid, world=world, rank=rank)
+    if rank == 0:
+        host = np.zeros(n, hvcf.LIGHT_DT)
+        hvcf.host_init_lights(n, out=host)
+        eng.lights.copy_(torch.from_numpy(host.view(np.uint8).reshape(-1)))
+        del host
+    ubo = hvcf.host_camera_ubo(grid, screen)
+    for f in range(2):
+        eng.set_ubo(f, ubo)
+    stream = torch.cuda.current_stream()
+    steps = max(1, args.sharded_steps)
+
+    def step(f):
+        sc.broadcast_lights(n)
+        return sc.frame(f, gather=True)
+
+    step(0)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(steps):
+        totals, _ = step(i & 1)
+    e1.record(stream)
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    st = eng.ctx.stats((steps - 1) & 1)
+    ex = torch.tensor([float(st["executed_tests"])], device=dev, dtype=torch.float64)
+    dist.all_reduce(ex, op=dist.ReduceOp.SUM)
+    total = int(totals.sum().item())
+    eng.close()
+    return {"workload": args.sharded_workload, "grid": list(grid), "lights": n, "steps": steps, "ms_per_frame": ms,
+            "value": C * n / (ms * 1e-3), "unit": "tests/s (nominal)", "scaling": "strong",
+            "executed_tests_per_frame": float(ex.item()), "total_indices": total, "z_slabs": slabs,
+            "collectives": "ncclBroadcast 48 B x L lights; all-gather totals; all-gather light cells; per-owner broadcast of index segments"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
