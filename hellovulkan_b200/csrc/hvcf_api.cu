@@ -62,6 +62,18 @@ struct hvcf_ctx
 	int variant = 1;
 	uint32_t max_segs = 1;
 	uint32_t count_blocks = 0;
+	// hierarchical mode
+	bool hier = false;
+	HierPlan hp{};
+	uint32_t h_max_segs = 0, h_max_chunks = 0;
+	int h_tps_override = 0;
+	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
+	uint32_t epoch = 0;
+	uint32_t* d_hseg_counts = nullptr;
+	uint32_t* d_hseg_prefix = nullptr;
+	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count] | chunk_done[h_max_chunks][ncb]
+	uint32_t* d_hoffsets = nullptr;
+	unsigned long long* d_scan_state = nullptr;
 
 	// reference-layout buffers
 	hvcf_light_data* d_lights = nullptr;   // ResourcesLight::storageBuffer_
@@ -117,6 +129,11 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_block_offsets);
 	cudaFree(c->d_shard_total);
 	cudaFree(c->d_stats);
+	cudaFree(c->d_hseg_counts);
+	cudaFree(c->d_hseg_prefix);
+	cudaFree(c->d_hscratch);
+	cudaFree(c->d_hoffsets);
+	cudaFree(c->d_scan_state);
 	cudaFreeHost(c->h_ubo);
 	cudaFreeHost(c->h_zplanes);
 	cudaFreeHost(c->h_one_light);
@@ -129,6 +146,39 @@ static void free_ctx(hvcf_ctx* c)
 				cudaEventDestroy(e);
 	delete[] c->ubo_set;
 	delete c;
+}
+
+static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
+{
+	HierParams p{};
+	p.lights_view = ctx->d_lights_view;
+	p.aabbs = ctx->d_aabb;
+	p.X = ctx->X;
+	p.Y = ctx->Y;
+	p.Zs = ctx->cluster_count / (ctx->X * ctx->Y);
+	p.cluster_begin = ctx->cluster_begin;
+	p.cluster_count = ctx->cluster_count;
+	p.bx = ctx->hp.bx, p.by = ctx->hp.by, p.bz = ctx->hp.bz;
+	p.nbx = ctx->hp.nbx, p.nby = ctx->hp.nby, p.nbz = ctx->hp.nbz;
+	p.nblocks = ctx->hp.nblocks;
+	p.ncb = ctx->hp.ncb;
+	p.tiles_total = ctx->h_tiles_total;
+	p.tiles_per_seg = ctx->h_tiles_per_seg;
+	p.num_segs = ctx->h_num_segs;
+	p.cap = ctx->cap;
+	p.seg_counts = ctx->d_hseg_counts;
+	p.seg_prefix = ctx->d_hseg_prefix;
+	p.cum = ctx->d_hscratch;
+	p.chunk_done = ctx->d_hscratch + static_cast<size_t>(ctx->cluster_count) * hier_num_chunks(ctx->h_num_segs);
+	p.offsets = ctx->d_hoffsets;
+	p.counts = ctx->d_counts;
+	p.index_base = nullptr;
+	p.shard_total = ctx->d_shard_total;
+	p.cells = ctx->d_cells;
+	p.indices = ctx->d_indices;
+	p.frame_total = &ctx->d_global_index[frame];
+	p.stats = &ctx->d_stats[frame];
+	return p;
 }
 
 extern "C" {
@@ -186,15 +236,22 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		delete c;
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: z shard [%u,%u) outside [0,%u)", zb, ze, c->Z);
 	}
-	if (config->mode != HVCF_MODE_BRUTE)
+	uint32_t mode = config->mode;
+	if (mode > HVCF_MODE_HIERARCHICAL)
 	{
 		delete c;
-		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create: mode %u not implemented in this build", config->mode);
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create: unknown mode %u", config->mode);
 	}
+	if (mode == HVCF_MODE_AUTO)
+	{
+		const char* m = getenv("HVCF_MODE");
+		mode = (m && !strcmp(m, "brute")) ? HVCF_MODE_BRUTE : HVCF_MODE_HIERARCHICAL;
+	}
+	c->hier = mode == HVCF_MODE_HIERARCHICAL;
 	c->cluster_begin = zb * c->X * c->Y;
 	c->cluster_end = ze * c->X * c->Y;
 	c->cluster_count = c->cluster_end - c->cluster_begin;
-	c->padded_capacity = round_up_u32(c->max_lights, kTileLights);
+	c->padded_capacity = round_up_u32(c->max_lights ? c->max_lights : 1, kTileLights);
 	c->variant = env_int("HVCF_CULL_VARIANT", 1);
 	if (c->variant < 0 || c->variant >= kNumCullVariants)
 		c->variant = 1;
@@ -208,6 +265,17 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		segs = static_cast<uint32_t>(env_segs > 64 ? 64 : env_segs);
 	c->max_segs = segs;
 	c->count_blocks = (c->cluster_count + 255) / 256;
+	if (c->hier)
+	{
+		uint32_t shape[3] = {0, 0, 0};
+		if (const char* sh = getenv("HVCF_HIER_SHAPE"))
+			sscanf(sh, "%u,%u,%u", &shape[0], &shape[1], &shape[2]);
+		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, &c->hp);
+		const uint32_t max_tiles = c->padded_capacity / kTileLights;
+		c->h_max_segs = max_tiles < 256 ? max_tiles : 256;
+		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
+		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
+	}
 
 #define HVCF_ALLOC(ptr, bytes)                                                              \
 	do                                                                                      \
@@ -229,8 +297,19 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	HVCF_ALLOC(c->d_ubo, sizeof(hvcf_cluster_forward_ubo) * c->frame_count);
 	HVCF_ALLOC(c->d_lights_view, static_cast<size_t>(c->padded_capacity) * 16);
 	HVCF_ALLOC(c->d_zplanes, sizeof(float) * (c->Z + 1) * c->frame_count);
-	HVCF_ALLOC(c->d_seg_counts, sizeof(uint32_t) * Cs * c->max_segs);
-	HVCF_ALLOC(c->d_seg_lists, sizeof(uint32_t) * Cs * c->max_segs * c->cap);
+	if (c->hier)
+	{
+		HVCF_ALLOC(c->d_hseg_counts, sizeof(uint32_t) * Cs * c->h_max_segs);
+		HVCF_ALLOC(c->d_hseg_prefix, sizeof(uint32_t) * Cs * c->h_max_segs);
+		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * (Cs + c->hp.ncb) * c->h_max_chunks);
+		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
+		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * c->count_blocks);
+	}
+	else
+	{
+		HVCF_ALLOC(c->d_seg_counts, sizeof(uint32_t) * Cs * c->max_segs);
+		HVCF_ALLOC(c->d_seg_lists, sizeof(uint32_t) * Cs * c->max_segs * c->cap);
+	}
 	HVCF_ALLOC(c->d_counts, sizeof(uint32_t) * Cs);
 	HVCF_ALLOC(c->d_block_sums, sizeof(uint32_t) * c->count_blocks);
 	HVCF_ALLOC(c->d_block_offsets, sizeof(uint32_t) * c->count_blocks);
@@ -254,6 +333,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		e = cudaMemset(c->d_stats, 0, sizeof(DeviceStats) * c->frame_count);
 	if (e == cudaSuccess)
 		e = cudaMemset(c->d_shard_total, 0, sizeof(uint32_t));
+	if (e == cudaSuccess && c->hier)
+		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * c->count_blocks);
 	if (e != cudaSuccess)
 	{
 		free_ctx(c);
@@ -407,6 +488,43 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	DeviceStats* stats = &ctx->d_stats[frame];
 	HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
 	const uint32_t n = ctx->num_lights;
+	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+	if (ctx->hier)
+	{
+		// at least one (all-padding) tile, so that pass 2 always writes the light cells
+		const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
+		const uint32_t tiles_total = padded / kTileLights;
+		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
+		ctx->h_tiles_total = tiles_total;
+		const uint32_t chunks = hier_num_chunks(ctx->h_num_segs);
+		HVCF_CUDA(cudaMemsetAsync(ctx->d_hscratch, 0, sizeof(uint32_t) * (static_cast<size_t>(ctx->cluster_count) + ctx->hp.ncb) * chunks, s));
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, s));
+		HierParams p = hier_params(ctx, frame);
+		if (ctx->timing)
+			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+		HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), false, p, s));
+		if (ctx->timing)
+		{
+			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
+			ctx->ev_valid[frame] = true;
+		}
+		FinalizeParams f;
+		f.seg_counts = ctx->d_hseg_counts;
+		f.seg_prefix = ctx->d_hseg_prefix;
+		f.num_segs = ctx->h_num_segs;
+		f.cluster_count = ctx->cluster_count;
+		f.cap = ctx->cap;
+		ctx->epoch = ctx->epoch >= 0x3fffffffu ? 1u : ctx->epoch + 1u;
+		f.epoch = ctx->epoch;
+		f.scan_state = ctx->d_scan_state;
+		f.counts = ctx->d_counts;
+		f.offsets = ctx->d_hoffsets;
+		f.shard_total = ctx->d_shard_total;
+		f.stats = stats;
+		HVCF_CUDA(launch_hier_finalize(f, s));
+		ctx->last_launches[frame] = launches + 3;
+		return HVCF_OK;
+	}
 	const uint32_t padded = round_up_u32(n, kTileLights);
 	const uint32_t tiles_total = padded / kTileLights;
 	uint32_t num_segs = ctx->max_segs < tiles_total ? ctx->max_segs : tiles_total;
@@ -415,7 +533,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		num_segs = (tiles_total + tiles_per_seg - 1) / tiles_per_seg; // no empty segment
 	if (n)
 	{
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], ctx->bound_lights ? ctx->bound_lights : ctx->d_lights, n, padded, ctx->d_lights_view, s));
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, s));
 		CullParams p;
 		p.lights_view = ctx->d_lights_view;
 		p.aabbs = ctx->d_aabb;
@@ -452,6 +570,16 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	if (frame >= ctx->frame_count)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_finish: frame %u >= frame_count %u", frame, ctx->frame_count);
 	HVCF_CUDA(cudaSetDevice(ctx->device));
+	if (ctx->hier)
+	{
+		HierParams hp = hier_params(ctx, frame);
+		hp.index_base = d_index_base;
+		HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+		if (ctx->timing)
+			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], static_cast<cudaStream_t>(stream)));
+		ctx->last_launches[frame] += 1;
+		return HVCF_OK;
+	}
 	ScatterParams p;
 	p.counts = ctx->d_counts;
 	p.block_offsets = ctx->d_block_offsets;

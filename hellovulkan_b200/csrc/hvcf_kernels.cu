@@ -414,6 +414,9 @@ __global__ void __launch_bounds__(256) scan_kernel(const uint32_t* __restrict__ 
 	}
 }
 
+// grid = (ceil(C/256), 8): every CTA redoes the (cheap) 256-wide scan of its cluster block, then copies the
+// lists of the 32 clusters blockIdx.y selects, 4 clusters per warp -- 8x the CTAs of a 1-D launch, so the
+// dependent seg_counts -> seg_lists -> indices chains of different clusters overlap.
 __global__ void __launch_bounds__(256) scatter_kernel(const ScatterParams p)
 {
 	__shared__ uint32_t s_off[256];
@@ -426,18 +429,21 @@ __global__ void __launch_bounds__(256) scatter_kernel(const ScatterParams p)
 	const uint32_t off = base + ex;
 	s_off[threadIdx.x] = off;
 	s_cnt[threadIdx.x] = v;
-	if (c < p.cluster_count)
+	if (blockIdx.y == 0)
 	{
-		// LightCulling.comp:86-87
-		*reinterpret_cast<uint2*>(p.cells + p.cluster_begin + c) = make_uint2(off, v);
+		if (c < p.cluster_count)
+		{
+			// LightCulling.comp:86-87
+			*reinterpret_cast<uint2*>(p.cells + p.cluster_begin + c) = make_uint2(off, v);
+		}
+		if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 255 && p.frame_total)
+			*p.frame_total = off + v; // globalIndex after the frame (LightCulling.comp:21,79)
 	}
-	if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 255 && p.frame_total)
-		*p.frame_total = off + v; // globalIndex after the frame (LightCulling.comp:21,79)
 	__syncthreads();
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	for (uint32_t j = 0; j < 32; ++j)
+	for (uint32_t j = 0; j < 4; ++j)
 	{
-		const uint32_t t = warp * 32 + j;
+		const uint32_t t = blockIdx.y * 32 + warp * 4 + j;
 		const uint32_t cc = blockIdx.x * 256 + t;
 		if (cc >= p.cluster_count)
 			break;
@@ -580,7 +586,7 @@ cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream)
 {
 	if (p.cluster_count == 0)
 		return cudaSuccess;
-	scatter_kernel<<<(p.cluster_count + 255) / 256, 256, 0, stream>>>(p);
+	scatter_kernel<<<dim3((p.cluster_count + 255) / 256, 8, 1), 256, 0, stream>>>(p);
 	return cudaGetLastError();
 }
 

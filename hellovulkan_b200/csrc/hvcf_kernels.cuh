@@ -52,4 +52,60 @@ cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream);
 // 16 lane-ops per thread per iteration (8 FMUL + 8 FADD)
 cudaError_t launch_fp32_issue_rate(float* sink, uint32_t blocks, uint32_t iters, cudaStream_t stream);
 
+// ---- HVCF_MODE_HIERARCHICAL (hvcf_hier.cu) -------------------------------------------------------------
+struct HierPlan
+{
+	uint32_t bx, by, bz;      // cluster block shape, bx * by * bz == 32 (one lane per cluster)
+	uint32_t nbx, nby, nbz;   // blocks per axis of the shard
+	uint32_t nblocks;
+	uint32_t K;               // blocks per warp (1, 2 or 4)
+	uint32_t ncb;             // CTAs per light segment
+};
+
+struct HierParams
+{
+	const float4* lights_view;
+	const hvcf_aabb* aabbs;        // whole grid
+	uint32_t X, Y, Zs;             // shard extent in clusters
+	uint32_t cluster_begin;        // shard, global cluster ids
+	uint32_t cluster_count;
+	uint32_t bx, by, bz, nbx, nby, nbz, nblocks, ncb;
+	uint32_t tiles_total, tiles_per_seg, num_segs;
+	uint32_t cap;
+	uint32_t* seg_counts;          // [num_segs][cluster_count]   pass 1 out, pass 2 in
+	uint32_t* seg_prefix;          // [num_segs][cluster_count]   finalize out, pass 2 in
+	uint32_t* cum;                 // [num_chunks][cluster_count] zeroed per frame
+	uint32_t* chunk_done;          // [num_chunks][ncb]           zeroed per frame
+	const uint32_t* offsets;       // [cluster_count] shard-local exclusive offsets
+	const uint32_t* counts;        // [cluster_count] capped counts
+	const uint32_t* index_base;    // device scalar or NULL
+	const uint32_t* shard_total;
+	hvcf_light_cell* cells;        // whole grid
+	uint32_t* indices;
+	uint32_t* frame_total;         // globalIndexCountBuffers_[frame] or NULL
+	DeviceStats* stats;
+};
+
+struct FinalizeParams
+{
+	uint32_t* seg_counts;
+	uint32_t* seg_prefix;
+	uint32_t num_segs;
+	uint32_t cluster_count;
+	uint32_t cap;
+	uint32_t epoch;                 // frame serial, > 0, < 2^30
+	unsigned long long* scan_state; // [ceil(cluster_count / 256)]
+	uint32_t* counts;
+	uint32_t* offsets;
+	uint32_t* shard_total;
+	DeviceStats* stats;
+};
+
+void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], HierPlan* out);
+void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
+	uint32_t* num_segs);
+uint32_t hier_num_chunks(uint32_t num_segs);
+cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream);
+cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream);
+
 } // namespace hvcf

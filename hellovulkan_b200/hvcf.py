@@ -19,8 +19,9 @@ CELL_DT = np.dtype([("offset", "<u4"), ("count", "<u4")])
 UBO_BYTES = 176
 
 HVCF_OK = 0
-MODE_BRUTE = 0
-MODE_BINNED = 1
+MODE_AUTO = 0
+MODE_BRUTE = 1
+MODE_HIERARCHICAL = 2
 
 
 class HvcfError(RuntimeError):
@@ -155,7 +156,7 @@ class Context:
     """One hvcf_ctx: the device buffers of ResourcesClusterForward + ResourcesLight and the two passes."""
 
     def __init__(self, grid=(16, 9, 24), max_lights=1024, max_lights_per_cluster=150, frame_count=2, device=-1,
-                 mode=MODE_BRUTE, z_begin=0, z_end=0):
+                 mode=MODE_AUTO, z_begin=0, z_end=0):
         self.lib = load()
         cfg = Config()
         cfg.struct_size = ctypes.sizeof(Config)

@@ -114,7 +114,7 @@ public:
 		cfg.max_lights_per_cluster = maxLightPerCluster_;
 		cfg.max_lights = lightCount ? lightCount : 1;
 		cfg.frame_count = AppConfig::FrameCount;
-		cfg.mode = HVCF_MODE_BRUTE;
+		cfg.mode = HVCF_MODE_AUTO;
 		hv::Check(hvcf_create(&cfg, &handle_), "hvcf_create");
 		hvcf_buffers b{};
 		hv::Check(hvcf_get_device_buffers(handle_, &b), "hvcf_get_device_buffers");

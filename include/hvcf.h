@@ -46,11 +46,12 @@ typedef enum hvcf_status
 	HVCF_ERR_UNSUPPORTED = -6
 } hvcf_status;
 
-/* Culling strategy.  Both produce byte-identical light cells / index lists. */
+/* Culling strategy.  All of them produce byte-identical light cells / index lists. */
 typedef enum hvcf_mode
 {
-	HVCF_MODE_BRUTE = 0, /* every cluster x light pair is tested until the cluster holds max_lights_per_cluster hits */
-	HVCF_MODE_BINNED = 1 /* conservative block-level pre-filter, then the exact test on survivors */
+	HVCF_MODE_AUTO = 0,        /* library default (hierarchical); the environment variable HVCF_MODE=brute|hier overrides it */
+	HVCF_MODE_BRUTE = 1,       /* every cluster x light pair is tested until the cluster holds max_lights_per_cluster hits */
+	HVCF_MODE_HIERARCHICAL = 2 /* exactly conservative union-box pre-filters (CTA, 32-cluster block), exact test on survivors */
 } hvcf_mode;
 
 typedef struct hvcf_ctx hvcf_ctx;
@@ -97,7 +98,7 @@ typedef struct hvcf_stats
 {
 	uint64_t nominal_tests;   /* clusters x lights of the shard */
 	uint64_t executed_tests;  /* exact sphere-vs-AABB lane tests the kernels actually ran */
-	uint64_t prefilter_tests; /* conservative group tests (binned mode), else 0 */
+	uint64_t prefilter_tests; /* union-box tests of the hierarchical mode (levels 0 and 1), else 0 */
 	uint32_t total_indices;   /* sum of counts */
 	uint32_t overflow_clusters; /* clusters whose count hit max_lights_per_cluster */
 	uint32_t kernel_launches; /* kernels launched by that hvcf_cull call */
