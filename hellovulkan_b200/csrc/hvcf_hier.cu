@@ -1,0 +1,592 @@
+// hvcf_hier.cu -- HVCF_MODE_HIERARCHICAL: hierarchical light culling that produces the same bytes as the
+// brute force path (and as LightCulling.comp:59-88) while running a small fraction of its tests.
+//
+// The hierarchy is over CLUSTERS, not lights, so light order -- and with it the reference's "first 150
+// hits in ascending light index" -- is preserved for free:
+//
+//   level 0  CTA  : union box of all its clusters (8 warps x K blocks x 32 clusters).  Every light of a
+//                   TMA-staged tile is tested once per CTA (lane = light pair, FADD2/FMUL2); survivors are
+//                   compacted, in light order, into shared memory (__ballot_sync/__popc + a CTA prefix).
+//   level 1  block: union box of one 8x4x1 block of clusters.  Lane = surviving light; ballot -> candidates.
+//   level 2  exact: lane = cluster.  Each candidate light is broadcast from shared memory and tested
+//                   against the lane's own AABB with the reference's arithmetic.
+//
+// The union tests use the SAME uncontracted float sequence as the exact test.  Rounding is monotone, so
+// lo_u <= lo_c and hi_u >= hi_c give d_u <= d_c per axis and sq_u <= sq_c in floating point: a light that
+// hits a cluster always passes the unions -- the filter is exactly conservative, no epsilon.
+//
+// Ordered output without scratch lists: pass 1 (WRITE = false) only COUNTS hits per (light segment,
+// cluster); hier_finalize_kernel turns the counts into per-segment prefixes, capped counts and an
+// exclusive scan over clusters (single pass, decoupled look-back); pass 2 (WRITE = true) re-runs the
+// hierarchy over the lanes that own output (tight unions, so it is far cheaper than pass 1) and stores
+// each index straight at offset[cluster] + prefix[segment] + k.  No global atomic append, no sorting.
+//
+// Early exit (LightCulling.comp:71, `lightIter < MAX_LIGHTS_PER_CLUSTER`) across concurrently running
+// segments: segments are grouped into chunks of doubling size; a finishing CTA adds its counts to
+// cum[chunk][cluster] and bumps chunk_done[chunk][cta]; a starting CTA sums the COMPLETE earlier chunks
+// and drops every cluster that already holds `cap` hits.  Knowledge only ever removes work that cannot
+// reach the first `cap` entries, so the result does not depend on scheduling.
+#include "hvcf_kernels.cuh"
+
+namespace hvcf
+{
+
+constexpr uint32_t kHWarps = 8;
+constexpr uint32_t kHStages = 2;
+constexpr uint32_t kHGroupsPerWarp = kTileGroups / kHWarps; // 2
+constexpr uint32_t kSkip = 0xffffffffu;
+static_assert(kTileGroups % kHWarps == 0, "level 0 splits a tile's groups evenly over the warps");
+
+// dynamic shared memory: light tile ring | survivor records (2 buffers) | survivor local indices (2 buffers)
+constexpr uint32_t kHSmemRing = kHStages * kTileBytes;
+constexpr uint32_t kHSmemS0f = 2 * kTileLights * 16;
+constexpr uint32_t kHSmemS0i = 2 * kTileLights * 2;
+constexpr uint32_t kHSmemBytes = kHSmemRing + kHSmemS0f + kHSmemS0i;
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p)
+{
+	uint32_t v;
+	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p)
+{
+	unsigned long long v;
+	asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v)
+{
+	asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// order-preserving float <-> int map, for redux.sync min/max over a warp
+__device__ __forceinline__ int float_to_ordered(float f)
+{
+	const int i = __float_as_int(f);
+	return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+__device__ __forceinline__ float warp_min_f(float v) { return ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(v))); }
+__device__ __forceinline__ float warp_max_f(float v) { return ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(v))); }
+
+// LightCulling.comp:26-47,56 on one light and one box; see cull_kernel for why max3(lo-v, v-hi, 0) is exact.
+__device__ __forceinline__ bool sphere_box_hit(float x, float y, float z, float r2, const float lo[3], const float hi[3])
+{
+	const float dx = fmaxf(fmaxf(__fsub_rn(lo[0], x), __fsub_rn(x, hi[0])), 0.0f);
+	const float dy = fmaxf(fmaxf(__fsub_rn(lo[1], y), __fsub_rn(y, hi[1])), 0.0f);
+	const float dz = fmaxf(fmaxf(__fsub_rn(lo[2], z), __fsub_rn(z, hi[2])), 0.0f);
+	const float s = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+	return s < r2;
+}
+
+// the same test on the lane's light PAIR of the packed culling layout (FADD2 / FMUL2; sums stay scalar so
+// that ptxas cannot contract them into FFMA2)
+__device__ __forceinline__ void sphere_box_hit2(const float4& a, const float4& b, const float lo[3], const float hi[3], bool& h0,
+	bool& h1)
+{
+	const f32x2 X = pack2(a.x, a.y), Y = pack2(a.z, a.w), Z = pack2(b.x, b.y);
+	float l0, l1, u0, u1;
+	unpack2(sub2(pack2(lo[0], lo[0]), X), l0, l1);
+	unpack2(sub2(X, pack2(hi[0], hi[0])), u0, u1);
+	const f32x2 dx = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
+	unpack2(sub2(pack2(lo[1], lo[1]), Y), l0, l1);
+	unpack2(sub2(Y, pack2(hi[1], hi[1])), u0, u1);
+	const f32x2 dy = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
+	unpack2(sub2(pack2(lo[2], lo[2]), Z), l0, l1);
+	unpack2(sub2(Z, pack2(hi[2], hi[2])), u0, u1);
+	const f32x2 dz = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
+	float sx0, sx1, sy0, sy1, sz0, sz1;
+	unpack2(mul2(dx, dx), sx0, sx1);
+	unpack2(mul2(dy, dy), sy0, sy1);
+	unpack2(mul2(dz, dz), sz0, sz1);
+	h0 = __fadd_rn(__fadd_rn(sx0, sy0), sz0) < b.z;
+	h1 = __fadd_rn(__fadd_rn(sx1, sy1), sz1) < b.w;
+}
+
+// segment -> chunk: chunk 0 = segments [0,4), chunk c >= 1 = segments [2^(c+1), 2^(c+2))
+__device__ __forceinline__ uint32_t hier_chunk_of(uint32_t seg) { return seg < 4 ? 0u : (30u - __clz(seg)); }
+__device__ __forceinline__ uint32_t hier_chunk_segs(uint32_t chunk, uint32_t num_segs)
+{
+	const uint32_t b = chunk == 0 ? 0u : (2u << chunk), e = 4u << chunk;
+	return min(e, num_segs) - min(b, num_segs);
+}
+
+template <int K, bool WRITE>
+__global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
+{
+	extern __shared__ __align__(128) unsigned char smem[];
+	__shared__ __align__(8) uint64_t full_bar[kHStages];
+	__shared__ uint32_t s_warp_n[2][kHWarps];
+	__shared__ float s_union[kHWarps][6];
+
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t cb = blockIdx.x % p.ncb, seg = blockIdx.x / p.ncb;
+	const uint32_t t_begin = seg * p.tiles_per_seg;
+	const uint32_t t_end = min(t_begin + p.tiles_per_seg, p.tiles_total);
+	const uint32_t ntiles = t_end - t_begin;
+	const unsigned char* src = reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(t_begin) * kTileBytes;
+	float4* const s0f = reinterpret_cast<float4*>(smem + kHSmemRing);
+	uint16_t* const s0i = reinterpret_cast<uint16_t*>(smem + kHSmemRing + kHSmemS0f);
+
+	if (threadIdx.x == 0)
+	{
+#pragma unroll
+		for (uint32_t s = 0; s < kHStages; ++s)
+			mbar_init(&full_bar[s], 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		for (uint32_t s = 0; s < kHStages && s < ntiles; ++s)
+		{
+			mbar_arrive_expect_tx(&full_bar[s], kTileBytes);
+			bulk_copy_g2s(smem + s * kTileBytes, src + static_cast<size_t>(s) * kTileBytes, kTileBytes, &full_bar[s]);
+		}
+	}
+
+	// ---- this lane's K clusters (one per block), while the first tiles are in flight ----------------
+	const uint32_t lx = lane % p.bx, ly = (lane / p.bx) % p.by, lz = lane / (p.bx * p.by);
+	const float kInf = __int_as_float(0x7f800000);
+	float lo[K][3], hi[K][3];
+	uint32_t cidx[K];    // cluster index inside the shard, kSkip = no cluster on this lane
+	uint32_t cnt[K];     // pass 1: hits counted in this segment; pass 2: entries written
+	uint32_t limit[K];   // pass 1: hits still missing before the cap; pass 2: entries this lane owns
+	uint32_t wbase[K];   // pass 2: first output slot
+	bool active[K];
+	const uint32_t chunk = hier_chunk_of(seg);
+	const uint32_t index_base = (WRITE && p.index_base) ? *p.index_base : 0u;
+	uint32_t complete = 0; // bit c: every segment of chunk c < chunk has published its counts
+	if (!WRITE)
+		for (uint32_t c = 0; c < chunk; ++c)
+			if (ld_acquire_u32(&p.chunk_done[c * p.ncb + cb]) == hier_chunk_segs(c, p.num_segs))
+				complete |= 1u << c;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		const uint32_t b = (cb * kHWarps + warp) * K + k;
+		const uint32_t bxi = b % p.nbx, byi = (b / p.nbx) % p.nby, bzi = b / (p.nbx * p.nby);
+		const uint32_t x = bxi * p.bx + lx, y = byi * p.by + ly, z = bzi * p.bz + lz;
+		const bool valid = b < p.nblocks && x < p.X && y < p.Y && z < p.Zs;
+		cidx[k] = valid ? x + y * p.X + z * p.X * p.Y : kSkip;
+		cnt[k] = 0;
+		limit[k] = 0;
+		wbase[k] = 0;
+		active[k] = false;
+		lo[k][0] = lo[k][1] = lo[k][2] = kInf;
+		hi[k][0] = hi[k][1] = hi[k][2] = -kInf;
+		if (valid)
+		{
+			if (WRITE)
+			{
+				const size_t sc = static_cast<size_t>(seg) * p.cluster_count + cidx[k];
+				const uint32_t n = p.seg_counts[sc], pfx = p.seg_prefix[sc];
+				const uint32_t off = p.offsets[cidx[k]] + index_base;
+				if (seg == 0) // LightCulling.comp:86-87
+					*reinterpret_cast<uint2*>(p.cells + p.cluster_begin + cidx[k]) = make_uint2(off, p.counts[cidx[k]]);
+				if (n != 0 && pfx != kSkip && pfx < p.cap)
+				{
+					active[k] = true;
+					limit[k] = min(n, p.cap - pfx);
+					wbase[k] = off + pfx;
+				}
+			}
+			else
+			{
+				uint32_t prior = 0;
+				for (uint32_t c = 0; c < chunk; ++c)
+					if ((complete >> c) & 1u)
+						prior += __ldcg(&p.cum[static_cast<size_t>(c) * p.cluster_count + cidx[k]]);
+				if (prior < p.cap)
+				{
+					active[k] = true;
+					limit[k] = p.cap - prior;
+				}
+			}
+			if (active[k])
+			{
+				const float4* a = reinterpret_cast<const float4*>(p.aabbs + p.cluster_begin + cidx[k]);
+				const float4 mn = __ldg(a), mx = __ldg(a + 1);
+				lo[k][0] = mn.x, lo[k][1] = mn.y, lo[k][2] = mn.z;
+				hi[k][0] = mx.x, hi[k][1] = mx.y, hi[k][2] = mx.z;
+			}
+		}
+	}
+	if (WRITE && blockIdx.x == 0 && threadIdx.x == 0 && p.frame_total)
+		*p.frame_total = index_base + *p.shard_total; // globalIndex after the frame (LightCulling.comp:21,79)
+
+	// ---- union boxes: per block (level 1), then per CTA (level 0) ---------------------------------------
+	float ulo[K][3], uhi[K][3];
+	bool blk_active[K];
+	float wlo0 = kInf, wlo1 = kInf, wlo2 = kInf, whi0 = -kInf, whi1 = -kInf, whi2 = -kInf;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		blk_active[k] = __any_sync(0xffffffffu, active[k]);
+		// a NaN bound makes every light hit that cluster (both shader comparisons are false): pass everything
+		const bool nan = active[k] && !(lo[k][0] == lo[k][0] && lo[k][1] == lo[k][1] && lo[k][2] == lo[k][2] &&
+			hi[k][0] == hi[k][0] && hi[k][1] == hi[k][1] && hi[k][2] == hi[k][2]);
+		const bool any_nan = __any_sync(0xffffffffu, nan);
+#pragma unroll
+		for (int i = 0; i < 3; ++i)
+		{
+			ulo[k][i] = any_nan ? -kInf : warp_min_f(lo[k][i]);
+			uhi[k][i] = any_nan ? kInf : warp_max_f(hi[k][i]);
+		}
+		wlo0 = fminf(wlo0, ulo[k][0]), wlo1 = fminf(wlo1, ulo[k][1]), wlo2 = fminf(wlo2, ulo[k][2]);
+		whi0 = fmaxf(whi0, uhi[k][0]), whi1 = fmaxf(whi1, uhi[k][1]), whi2 = fmaxf(whi2, uhi[k][2]);
+	}
+	if (lane == 0)
+	{
+		s_union[warp][0] = wlo0, s_union[warp][1] = wlo1, s_union[warp][2] = wlo2;
+		s_union[warp][3] = whi0, s_union[warp][4] = whi1, s_union[warp][5] = whi2;
+	}
+	bool warp_done = true;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+		warp_done = warp_done && !blk_active[k];
+	__syncthreads();
+	float clo[3] = {kInf, kInf, kInf}, chi[3] = {-kInf, -kInf, -kInf};
+#pragma unroll
+	for (uint32_t w = 0; w < kHWarps; ++w)
+#pragma unroll
+		for (int i = 0; i < 3; ++i)
+		{
+			clo[i] = fminf(clo[i], s_union[w][i]);
+			chi[i] = fmaxf(chi[i], s_union[w][3 + i]);
+		}
+
+	const uint32_t lt = lanemask_lt();
+	unsigned long long n_l0 = 0, n_l1 = 0, n_l2 = 0; // warp-uniform test counters (lane tests)
+	uint32_t it = 0;
+	for (; it < ntiles; ++it)
+	{
+		const uint32_t buf = it % kHStages, sb = it & 1u;
+		mbar_wait(&full_bar[buf], (it / kHStages) & 1u);
+		// ---- level 0: this warp's two groups of the tile against the CTA union ---------------------------
+		const float4* tile = reinterpret_cast<const float4*>(smem + buf * kTileBytes);
+		float4 ra[kHGroupsPerWarp], rb[kHGroupsPerWarp];
+		uint32_t m0[kHGroupsPerWarp], m1[kHGroupsPerWarp];
+		uint32_t n_w = 0;
+#pragma unroll
+		for (uint32_t q = 0; q < kHGroupsPerWarp; ++q)
+		{
+			const uint32_t g = warp * kHGroupsPerWarp + q;
+			ra[q] = tile[g * 64 + lane];
+			rb[q] = tile[g * 64 + 32 + lane];
+			bool h0, h1;
+			sphere_box_hit2(ra[q], rb[q], clo, chi, h0, h1);
+			m0[q] = __ballot_sync(0xffffffffu, h0);
+			m1[q] = __ballot_sync(0xffffffffu, h1);
+			n_w += __popc(m0[q]) + __popc(m1[q]);
+		}
+		if (lane == 0)
+			s_warp_n[sb][warp] = n_w;
+		// barrier 1: survivor counts are published, every warp is done reading ring slot `buf`, and the
+		// CTA-wide early-exit vote of the previous tile is taken
+		if (__syncthreads_and(warp_done))
+			break;
+		if (threadIdx.x == 0 && it + kHStages < ntiles)
+		{
+			mbar_arrive_expect_tx(&full_bar[buf], kTileBytes);
+			bulk_copy_g2s(smem + buf * kTileBytes, src + static_cast<size_t>(it + kHStages) * kTileBytes, kTileBytes, &full_bar[buf]);
+		}
+		uint32_t pos = 0, n0 = 0;
+#pragma unroll
+		for (uint32_t w = 0; w < kHWarps; ++w)
+		{
+			const uint32_t nw = s_warp_n[sb][w];
+			pos += w < warp ? nw : 0u;
+			n0 += nw;
+		}
+		n_l0 += kTileLights / kHWarps;
+		if (n0 == 0)
+			continue; // uniform over the CTA: nobody reaches barrier 2 of this tile
+		float4* const sf = s0f + sb * kTileLights;
+		uint16_t* const si = s0i + sb * kTileLights;
+#pragma unroll
+		for (uint32_t q = 0; q < kHGroupsPerWarp; ++q)
+		{
+			const uint32_t g = warp * kHGroupsPerWarp + q;
+			if (m0[q] & (1u << lane))
+			{
+				const uint32_t d = pos + __popc(m0[q] & lt);
+				sf[d] = make_float4(ra[q].x, ra[q].z, rb[q].x, rb[q].z);
+				si[d] = static_cast<uint16_t>(g * 64 + lane);
+			}
+			pos += __popc(m0[q]);
+			if (m1[q] & (1u << lane))
+			{
+				const uint32_t d = pos + __popc(m1[q] & lt);
+				sf[d] = make_float4(ra[q].y, ra[q].w, rb[q].y, rb[q].w);
+				si[d] = static_cast<uint16_t>(g * 64 + 32 + lane);
+			}
+			pos += __popc(m1[q]);
+		}
+		__syncthreads(); // barrier 2: the survivor list of this tile is complete
+		if (warp_done)
+			continue;
+		// ---- level 1 (lane = surviving light) and level 2 (lane = cluster) ---------------------------------
+		const uint32_t tile_base = (t_begin + it) * kTileLights;
+		for (uint32_t i = 0; i < n0; i += 32)
+		{
+			const uint32_t idx = i + lane;
+			const float4 r = idx < n0 ? sf[idx] : make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+#pragma unroll
+			for (int k = 0; k < K; ++k)
+			{
+				if (!blk_active[k])
+					continue;
+				uint32_t m = __ballot_sync(0xffffffffu, sphere_box_hit(r.x, r.y, r.z, r.w, ulo[k], uhi[k]));
+				n_l1 += 32;
+				n_l2 += 32u * __popc(m);
+				while (m)
+				{
+					const uint32_t j = i + __ffs(m) - 1;
+					m &= m - 1;
+					const float4 c = sf[j]; // broadcast
+					const bool hit = sphere_box_hit(c.x, c.y, c.z, c.w, lo[k], hi[k]) && active[k];
+					if (WRITE)
+					{
+						if (hit && cnt[k] < limit[k])
+						{
+							p.indices[wbase[k] + cnt[k]] = tile_base + si[j];
+							++cnt[k];
+						}
+					}
+					else
+						cnt[k] += hit ? 1u : 0u;
+				}
+			}
+		}
+		warp_done = true;
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+		{
+			if (blk_active[k])
+				blk_active[k] = !__all_sync(0xffffffffu, !active[k] || cnt[k] >= limit[k]);
+			warp_done = warp_done && !blk_active[k];
+		}
+	}
+	// bulk copies still in flight must land before this CTA's shared memory is handed on
+	if (threadIdx.x == 0)
+	{
+		// tiles [0, issued) were requested; tiles [0, it] have been waited for (tile `it` only if the loop broke)
+		const uint32_t issued = min(it + kHStages, ntiles);
+		for (uint32_t j = it + 1; j < issued; ++j)
+			mbar_wait(&full_bar[j % kHStages], (j / kHStages) & 1u);
+	}
+	if (!WRITE)
+	{
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+			if (cidx[k] != kSkip)
+			{
+				p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = cnt[k];
+				if (cnt[k])
+					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
+			}
+		__threadfence();
+		__syncthreads();
+		if (threadIdx.x == 0)
+			atomicAdd(&p.chunk_done[chunk * p.ncb + cb], 1u);
+	}
+	if (lane == 0 && (n_l0 | n_l1 | n_l2))
+	{
+		atomicAdd(&p.stats->prefilter_tests, n_l0 + n_l1);
+		atomicAdd(&p.stats->executed_tests, n_l2);
+	}
+}
+
+// ======================================================================================================
+// finalize: per-segment counts -> per-segment prefixes, capped counts, exclusive scan over clusters.
+// One thread per cluster; the scan across CTAs is a single pass with decoupled look-back.  The look-back
+// state words carry the frame's epoch, so they never need clearing.
+// ======================================================================================================
+__device__ __forceinline__ uint32_t hier_warp_inclusive_scan(uint32_t v, uint32_t lane)
+{
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1)
+	{
+		const uint32_t n = __shfl_up_sync(0xffffffffu, v, d);
+		if (lane >= static_cast<uint32_t>(d))
+			v += n;
+	}
+	return v;
+}
+
+__global__ void __launch_bounds__(256) hier_finalize_kernel(const FinalizeParams p)
+{
+	__shared__ uint32_t warp_sums[8];
+	__shared__ uint32_t s_prefix;
+	const uint32_t c = blockIdx.x * 256 + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint32_t run = 0;
+	if (c < p.cluster_count)
+	{
+#pragma unroll 4
+		for (uint32_t s = 0; s < p.num_segs; ++s)
+		{
+			const size_t i = static_cast<size_t>(s) * p.cluster_count + c;
+			const uint32_t n = p.seg_counts[i];
+			p.seg_prefix[i] = (n == 0 || run >= p.cap) ? kSkip : run;
+			run += n;
+		}
+	}
+	const uint32_t v = min(run, p.cap);
+	const uint32_t inc = hier_warp_inclusive_scan(v, lane);
+	if (lane == 31)
+		warp_sums[warp] = inc;
+	const uint32_t over = __syncthreads_count(c < p.cluster_count && v >= p.cap);
+	uint32_t before = 0, total = 0;
+#pragma unroll
+	for (uint32_t w = 0; w < 8; ++w)
+	{
+		const uint32_t s = warp_sums[w];
+		before += w < warp ? s : 0u;
+		total += s;
+	}
+	if (threadIdx.x == 0)
+	{
+		// state word: [epoch:30 | flag:2 | value:32]; flag 1 = aggregate of this CTA, 2 = inclusive prefix
+		const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
+		uint32_t prefix = 0;
+		if (blockIdx.x == 0)
+			st_release_u64(&p.scan_state[0], tag | (2ull << 32) | total);
+		else
+		{
+			st_release_u64(&p.scan_state[blockIdx.x], tag | (1ull << 32) | total);
+			for (int i = static_cast<int>(blockIdx.x) - 1; i >= 0;)
+			{
+				const unsigned long long w = ld_acquire_u64(&p.scan_state[i]);
+				if ((w >> 34) != p.epoch || ((w >> 32) & 3ull) == 0)
+					continue; // predecessor has not published yet
+				prefix += static_cast<uint32_t>(w);
+				if (((w >> 32) & 3ull) == 2)
+					break;
+				--i;
+			}
+			st_release_u64(&p.scan_state[blockIdx.x], tag | (2ull << 32) | (prefix + total));
+		}
+		s_prefix = prefix;
+		if (over)
+			atomicAdd(&p.stats->overflow_clusters, over);
+		if (blockIdx.x == gridDim.x - 1)
+		{
+			*p.shard_total = prefix + total;
+			p.stats->total_indices = prefix + total;
+		}
+	}
+	__syncthreads();
+	if (c < p.cluster_count)
+	{
+		p.counts[c] = v;
+		p.offsets[c] = s_prefix + before + inc - v;
+	}
+}
+
+// ======================================================================================================
+// host side: plan + launchers
+// ======================================================================================================
+static uint32_t pow2_ceil(uint32_t v)
+{
+	uint32_t r = 1;
+	while (r < v)
+		r <<= 1;
+	return r;
+}
+
+void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], HierPlan* out)
+{
+	HierPlan& h = *out;
+	h.bx = pow2_ceil(X) < 8 ? pow2_ceil(X) : 8;
+	const uint32_t rem = 32 / h.bx;
+	const uint32_t by_pref = h.bx == 8 ? 4 : rem;
+	h.by = pow2_ceil(Y) < by_pref ? pow2_ceil(Y) : by_pref;
+	h.bz = rem / h.by;
+	if (shape_override && shape_override[0] * shape_override[1] * shape_override[2] == 32)
+		h.bx = shape_override[0], h.by = shape_override[1], h.bz = shape_override[2];
+	h.nbx = (X + h.bx - 1) / h.bx;
+	h.nby = (Y + h.by - 1) / h.by;
+	h.nbz = (Zs + h.bz - 1) / h.bz;
+	h.nblocks = h.nbx * h.nby * h.nbz;
+	h.K = h.nblocks >= 2048 ? 4 : (h.nblocks >= 512 ? 2 : 1);
+	if (k_override == 1 || k_override == 2 || k_override == 4)
+		h.K = static_cast<uint32_t>(k_override);
+	h.ncb = (h.nblocks + kHWarps * h.K - 1) / (kHWarps * h.K);
+}
+
+void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
+	uint32_t* num_segs)
+{
+	// about 16 CTAs per SM over the whole launch; segments are whole tiles and at most max_segs of them
+	const uint64_t target = 148ull * 16ull;
+	const uint64_t tps = (static_cast<uint64_t>(tiles_total) * h.ncb) / target;
+	uint32_t t = 1;
+	while (static_cast<uint64_t>(t) * 2 <= tps)
+		t <<= 1;
+	if (tps_override > 0)
+		t = static_cast<uint32_t>(tps_override);
+	if (max_segs == 0)
+		max_segs = 1;
+	while ((tiles_total + t - 1) / t > max_segs)
+		t <<= 1;
+	*tiles_per_seg = t;
+	*num_segs = (tiles_total + t - 1) / t;
+}
+
+uint32_t hier_num_chunks(uint32_t num_segs)
+{
+	if (num_segs <= 4)
+		return 1;
+	uint32_t c = 0, s = num_segs - 1;
+	while (s >= 8)
+	{
+		s >>= 1;
+		++c;
+	}
+	return c + 2; // chunk_of(num_segs - 1) + 1
+}
+
+template <int K, bool WRITE>
+static cudaError_t launch_hier_t(const HierParams& p, cudaStream_t stream)
+{
+	static bool configured = false;
+	if (!configured)
+	{
+		cudaError_t e = cudaFuncSetAttribute(hier_kernel<K, WRITE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+			static_cast<int>(kHSmemBytes));
+		if (e != cudaSuccess)
+			return e;
+		configured = true;
+	}
+	hier_kernel<K, WRITE><<<p.ncb * p.num_segs, kHWarps * 32, kHSmemBytes, stream>>>(p);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream)
+{
+	if (p.ncb == 0 || p.num_segs == 0)
+		return cudaSuccess;
+	switch (K * 2 + (write ? 1 : 0))
+	{
+	case 2: return launch_hier_t<1, false>(p, stream);
+	case 3: return launch_hier_t<1, true>(p, stream);
+	case 4: return launch_hier_t<2, false>(p, stream);
+	case 5: return launch_hier_t<2, true>(p, stream);
+	case 8: return launch_hier_t<4, false>(p, stream);
+	case 9: return launch_hier_t<4, true>(p, stream);
+	default: return cudaErrorInvalidValue;
+	}
+}
+
+cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream)
+{
+	if (p.cluster_count == 0)
+		return cudaSuccess;
+	hier_finalize_kernel<<<(p.cluster_count + 255) / 256, 256, 0, stream>>>(p);
+	return cudaGetLastError();
+}
+
+} // namespace hvcf
