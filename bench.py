@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--workload", default="A65k", choices=sorted(WORKLOADS))
     ap.add_argument("--sharded-workload", default="C16M", choices=sorted(WORKLOADS))
     ap.add_argument("--sharded-steps", type=int, default=3)
+    ap.add_argument("--mode", default="auto", choices=["auto", "brute", "hier"], help="hvcf_mode of the culling context")
     ap.add_argument("--no-sharded", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=4.0, help="wall-clock budget of the cpu_baseline sample")
@@ -291,7 +292,8 @@ def run_ours(args):
     for f in range(2):
         pinned_ubo.array[f * hvcf.UBO_BYTES:(f + 1) * hvcf.UBO_BYTES] = ubos[f]
 
-    ctx = hvcf.Context(grid=grid, max_lights=n, device=local)
+    mode = {"auto": hvcf.MODE_AUTO, "brute": hvcf.MODE_BRUTE, "hier": hvcf.MODE_HIERARCHICAL}[args.mode]
+    ctx = hvcf.Context(grid=grid, max_lights=n, device=local, mode=mode)
     ctx.set_timing(True)
     ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)
     for f in range(2):
@@ -304,7 +306,7 @@ def run_ours(args):
         ctx.cull(i & 1, sp)
     barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    kernel_ms, launches, executed, total_idx = [], 0, 0, 0
+    kernel_ms, launches, executed, prefilter, total_idx = [], 0, 0, 0, 0
     t_wall0 = time.time()
     for i in range(K):
         flush.zero_()
@@ -315,7 +317,8 @@ def run_ours(args):
             km, _ = ctx.timing(i & 1)
             kernel_ms.append(km)
             st = ctx.stats(i & 1, sp)
-            launches_per_step, executed, total_idx = st["kernel_launches"], st["executed_tests"], st["total_indices"]
+            launches_per_step, total_idx = st["kernel_launches"], st["total_indices"]
+            executed, prefilter = st["executed_tests"] + st["prefilter_tests"], st["prefilter_tests"]
     barrier()
     t_wall1 = time.time()
     if sampler:
@@ -375,7 +378,8 @@ def run_ours(args):
     alg_bytes = 48 * n + 16 * n * 2 + 32 * C + 8 * C + 4 * total_idx   # AoS in, SoA out+in, AABB, cells, indices
     roofline = {
         "bound": "fp32",
-        "kernel": "cull_kernel",
+        "kernel": "hier_kernel<K,count> (pass 1)" if prefilter else "cull_kernel",
+        "prefilter_tests_per_launch": prefilter,
         "achieved": achieved / 1e12, "peak": issue_rate / 1e12, "unit": "TFLOP/s", "frac": achieved / issue_rate,
         "peak_source": "hvcf_measure_fp32_issue_rate on this GPU, this run (non-FMA FADD/FMUL issue rate; MEASURED_PEAKS.json has no "
                        "FP32 figure); nominal 148 SM x 128 lanes x 1.965 GHz = 37.2",

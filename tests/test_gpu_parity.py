@@ -9,6 +9,7 @@ from cpu_checkers import AABB_DT, LIGHT_DT, Oracle, same_light_sets
 
 pytestmark = pytest.mark.gpu
 
+MODES = {"brute": 1, "hier": 2}  # hvcf_mode: HVCF_MODE_BRUTE, HVCF_MODE_HIERARCHICAL
 GRIDS = {"A": ((16, 9, 24), (2560, 1600)), "B": ((32, 18, 48), (3840, 2160)), "C": ((64, 36, 96), (3840, 2160))}
 
 
@@ -64,13 +65,14 @@ def run_cull(hv, grid, ubo, lights, cap=150, frame=0, **kw):
     return cells, idx, total, stats
 
 
+@pytest.mark.parametrize("mode", list(MODES))
 @pytest.mark.parametrize("n", [0, 1, 31, 64, 1000, 1025, 65536])
-def test_cull_config_A(hv, oracle, n):
+def test_cull_config_A(hv, oracle, n, mode):
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen)
     aabb = oracle.generate_aabbs(ubo)
     lights = oracle.init_lights(n)
-    cells, idx, total, stats = run_cull(hv, grid, ubo, lights)
+    cells, idx, total, stats = run_cull(hv, grid, ubo, lights, mode=MODES[mode])
     oc, oi, ototal, oexec = oracle.cull(ubo, aabb, lights)
     assert total == ototal and stats["total_indices"] == ototal
     assert np.array_equal(cells["count"], oc["count"])
@@ -79,15 +81,21 @@ def test_cull_config_A(hv, oracle, n):
     check_invariants(cells, idx, total, n, 150)
     assert stats["nominal_tests"] == len(aabb) * n
     assert stats["overflow_clusters"] == int((oc["count"] == 150).sum())
-    assert stats["executed_tests"] >= oexec or n == 0  # tile-granular early exit never does less than the exact bound
+    if mode == "brute":
+        assert stats["executed_tests"] >= oexec or n == 0  # tile-granular early exit never does less than the exact bound
+        assert stats["prefilter_tests"] == 0
+    elif n:
+        assert stats["prefilter_tests"] > 0
+        assert stats["executed_tests"] + stats["prefilter_tests"] < stats["nominal_tests"] or n < 4096
 
 
-def test_cull_matches_golden_reference_lists(hv, oracle, golden):
+@pytest.mark.parametrize("mode", list(MODES))
+def test_cull_matches_golden_reference_lists(hv, oracle, golden, mode):
     meta, arrs = golden
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen)
     lights = oracle.init_lights(1000)
-    cells, idx, total, _ = run_cull(hv, grid, ubo, lights)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, mode=MODES[mode])
     assert total == meta["cull_A_1000"]["total"]
     assert np.array_equal(cells["count"], arrs["cull_A_1000_counts"])
     assert np.array_equal(idx, arrs["cull_A_1000_gathered"])
@@ -102,24 +110,57 @@ def test_cull_variants_agree(hv, oracle, variant, segs, monkeypatch):
     ubo = oracle.camera_ubo(grid, screen, pos=(4, 3, -5), target=(-1, 0.5, 2))
     aabb = oracle.generate_aabbs(ubo)
     lights = oracle.init_lights(20000, seed=7)
-    cells, idx, total, _ = run_cull(hv, grid, ubo, lights)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, mode=MODES["brute"])
     oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights)
     assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
 
 
+@pytest.mark.parametrize("k", ["1", "2", "4"])
+@pytest.mark.parametrize("tps", ["0", "1", "2", "8", "64"])
+@pytest.mark.parametrize("shape", ["", "4,4,2", "32,1,1", "2,2,8"])
+def test_hier_plans_agree(hv, oracle, k, tps, shape, monkeypatch):
+    """every block shape / blocks-per-warp / tiles-per-segment plan of the hierarchical mode gives the same bytes"""
+    monkeypatch.setenv("HVCF_HIER_K", k)
+    monkeypatch.setenv("HVCF_HIER_TPS", tps)
+    if shape:
+        monkeypatch.setenv("HVCF_HIER_SHAPE", shape)
+    grid, screen = GRIDS["A"]
+    ubo = oracle.camera_ubo(grid, screen, pos=(4, 3, -5), target=(-1, 0.5, 2))
+    aabb = oracle.generate_aabbs(ubo)
+    lights = oracle.init_lights(20000, seed=7)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, mode=MODES["hier"])
+    oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights)
+    assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
+    assert np.array_equal(cells["offset"], oc["offset"])
+
+
+@pytest.mark.parametrize("grid", [(1, 1, 1), (3, 2, 5), (5, 7, 3), (33, 2, 2), (16, 9, 1)])
+@pytest.mark.parametrize("mode", list(MODES))
+def test_odd_grids(hv, oracle, grid, mode):
+    ubo = oracle.camera_ubo(grid, (1280, 720))
+    aabb = oracle.generate_aabbs(ubo)
+    lights = oracle.init_lights(5000, seed=17)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, mode=MODES[mode])
+    oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights)
+    assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
+    assert np.array_equal(cells["offset"], oc["offset"])
+
+
+@pytest.mark.parametrize("mode", list(MODES))
 @pytest.mark.parametrize("cap", [1, 7, 64, 4096])
-def test_cap_values(hv, oracle, cap):
+def test_cap_values(hv, oracle, cap, mode):
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen)
     aabb = oracle.generate_aabbs(ubo)
     lights = oracle.init_lights(9000, seed=3)
-    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, cap=cap)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES[mode])
     oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights, cap=cap)
     assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
     check_invariants(cells, idx, total, len(lights), cap)
 
 
-def test_handmade_boundaries(hv, oracle):
+@pytest.mark.parametrize("mode", list(MODES))
+def test_handmade_boundaries(hv, oracle, mode):
     """strict '<', radius 0, light behind the camera, NaN/Inf positions."""
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen)
@@ -138,17 +179,18 @@ def test_handmade_boundaries(hv, oracle):
     lights["radius"][17::59] = np.float32(1e18)
     lights["position"][:, 3] = 1.0
     lights["position"][21::61, 3] = rng.uniform(0.5, 2.0, size=len(lights["position"][21::61, 3])).astype(np.float32)
-    cells, idx, total, _ = run_cull(hv, grid, ubo, lights)
+    cells, idx, total, _ = run_cull(hv, grid, ubo, lights, mode=MODES[mode])
     oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights)
     assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
 
 
-def test_frames_update_light_and_dirty_tracking(hv, oracle):
+@pytest.mark.parametrize("mode", list(MODES))
+def test_frames_update_light_and_dirty_tracking(hv, oracle, mode):
     grid, screen = GRIDS["A"]
     ubo0 = oracle.camera_ubo(grid, screen)
     ubo1 = oracle.camera_ubo(grid, screen, pos=(2, 1.5, 5), target=(0, 2, 0))
     lights = oracle.init_lights(3000, seed=21)
-    with hv.Context(grid=grid, max_lights=4000) as ctx:
+    with hv.Context(grid=grid, max_lights=4000, mode=MODES[mode]) as ctx:
         ctx.set_lights(lights)
         ctx.set_ubo(0, ubo0)
         ctx.cull(0)
@@ -172,7 +214,8 @@ def test_frames_update_light_and_dirty_tracking(hv, oracle):
     assert total == ototal and np.array_equal(cells["count"], oc["count"]) and np.array_equal(idx, oi)
 
 
-def test_sharded_contexts_concatenate(hv, oracle):
+@pytest.mark.parametrize("mode", list(MODES))
+def test_sharded_contexts_concatenate(hv, oracle, mode):
     """z-slab shards: each writes its cells/indices at GLOBAL positions given the base (sum of the
     lower shards' totals), so segments concatenate without a fix-up pass."""
     import torch
@@ -182,7 +225,7 @@ def test_sharded_contexts_concatenate(hv, oracle):
     lights = oracle.init_lights(30000, seed=9)
     oc, oi, ototal, _ = oracle.cull(ubo, aabb, lights)
     shards = [(0, 6), (6, 12), (12, 24)]
-    ctxs = [hv.Context(grid=grid, max_lights=len(lights), z_begin=a, z_end=b) for a, b in shards]
+    ctxs = [hv.Context(grid=grid, max_lights=len(lights), z_begin=a, z_end=b, mode=MODES[mode]) for a, b in shards]
     try:
         totals = []
         for c in ctxs:
@@ -211,14 +254,15 @@ def test_sharded_contexts_concatenate(hv, oracle):
             c.close()
 
 
+@pytest.mark.parametrize("mode", list(MODES))
 @pytest.mark.parametrize("name,n,sample", [("B", 1 << 20, 96), ("C", 200_000, 64)])
-def test_large_configs_sampled(hv, oracle, name, n, sample):
+def test_large_configs_sampled(hv, oracle, name, n, sample, mode):
     """Full-size grids: the oracle checks a seeded sample of clusters in full; invariants on everything."""
     grid, screen = GRIDS[name]
     ubo = oracle.camera_ubo(grid, screen)
     aabb = oracle.generate_aabbs(ubo)
     lights = oracle.init_lights(n)
-    cells, idx, total, stats = run_cull(hv, grid, ubo, lights)
+    cells, idx, total, stats = run_cull(hv, grid, ubo, lights, mode=MODES[mode])
     check_invariants(cells, idx, total, n, 150)
     rng = np.random.default_rng(123)
     for c in rng.choice(len(aabb), size=sample, replace=False):
@@ -226,3 +270,13 @@ def test_large_configs_sampled(hv, oracle, name, n, sample):
         got = idx[cells["offset"][c]: cells["offset"][c] + cells["count"][c]]
         assert np.array_equal(got, want), f"cluster {c}"
     assert stats["executed_tests"] <= stats["nominal_tests"] + len(aabb) * 1024
+
+
+def test_modes_give_identical_bytes(hv, oracle):
+    """brute force and hierarchical: the same light cells and the same index buffer, byte for byte (grid B)"""
+    grid, screen = GRIDS["B"]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(300_000, seed=5)
+    a = run_cull(hv, grid, ubo, lights, mode=MODES["brute"])
+    b = run_cull(hv, grid, ubo, lights, mode=MODES["hier"])
+    assert a[2] == b[2] and a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
