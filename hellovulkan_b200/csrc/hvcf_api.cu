@@ -71,7 +71,7 @@ struct hvcf_ctx
 	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
-	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count] | chunk_done[h_max_chunks][ncb]
+	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count]
 	uint32_t* d_hoffsets = nullptr;
 	unsigned long long* d_scan_state = nullptr;
 
@@ -169,7 +169,6 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.seg_counts = ctx->d_hseg_counts;
 	p.seg_prefix = ctx->d_hseg_prefix;
 	p.cum = ctx->d_hscratch;
-	p.chunk_done = ctx->d_hscratch + static_cast<size_t>(ctx->cluster_count) * hier_num_chunks(ctx->h_num_segs);
 	p.offsets = ctx->d_hoffsets;
 	p.counts = ctx->d_counts;
 	p.index_base = nullptr;
@@ -301,9 +300,9 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	{
 		HVCF_ALLOC(c->d_hseg_counts, sizeof(uint32_t) * Cs * c->h_max_segs);
 		HVCF_ALLOC(c->d_hseg_prefix, sizeof(uint32_t) * Cs * c->h_max_segs);
-		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * (Cs + c->hp.ncb) * c->h_max_chunks);
+		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * c->h_max_chunks);
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
-		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * c->count_blocks);
+		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
 	}
 	else
 	{
@@ -334,7 +333,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	if (e == cudaSuccess)
 		e = cudaMemset(c->d_shard_total, 0, sizeof(uint32_t));
 	if (e == cudaSuccess && c->hier)
-		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * c->count_blocks);
+		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32));
 	if (e != cudaSuccess)
 	{
 		free_ctx(c);
@@ -497,7 +496,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
 		ctx->h_tiles_total = tiles_total;
 		const uint32_t chunks = hier_num_chunks(ctx->h_num_segs);
-		HVCF_CUDA(cudaMemsetAsync(ctx->d_hscratch, 0, sizeof(uint32_t) * (static_cast<size_t>(ctx->cluster_count) + ctx->hp.ncb) * chunks, s));
+		HVCF_CUDA(cudaMemsetAsync(ctx->d_hscratch, 0, sizeof(uint32_t) * static_cast<size_t>(ctx->cluster_count) * chunks, s));
 		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, s));
 		HierParams p = hier_params(ctx, frame);
 		if (ctx->timing)

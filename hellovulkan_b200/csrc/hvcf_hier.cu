@@ -23,9 +23,11 @@
 //
 // Early exit (LightCulling.comp:71, `lightIter < MAX_LIGHTS_PER_CLUSTER`) across concurrently running
 // segments: segments are grouped into chunks of doubling size; a finishing CTA adds its counts to
-// cum[chunk][cluster] and bumps chunk_done[chunk][cta]; a starting CTA sums the COMPLETE earlier chunks
-// and drops every cluster that already holds `cap` hits.  Knowledge only ever removes work that cannot
-// reach the first `cap` entries, so the result does not depend on scheduling.
+// cum[chunk][cluster]; a starting CTA sums cum over the EARLIER chunks and drops every cluster that already
+// holds `cap` hits.  Whatever it reads is a lower bound of the hits in earlier segments (counts only grow
+// towards the true value), and a lower bound >= cap proves that the first `cap` entries lie before this
+// segment -- so knowledge only ever removes work that cannot matter, and the result does not depend on
+// scheduling.  No flags, no fences.
 #include "hvcf_kernels.cuh"
 
 namespace hvcf
@@ -35,6 +37,7 @@ constexpr uint32_t kHWarps = 8;
 constexpr uint32_t kHStages = 2;
 constexpr uint32_t kHGroupsPerWarp = kTileGroups / kHWarps; // 2
 constexpr uint32_t kSkip = 0xffffffffu;
+constexpr uint32_t kHMaxChunks = 8; // 256 segments at most (hier_num_chunks(256) == 7)
 static_assert(kTileGroups % kHWarps == 0, "level 0 splits a tile's groups evenly over the warps");
 
 // dynamic shared memory: light tile ring | survivor records (2 buffers) | survivor local indices (2 buffers)
@@ -43,12 +46,6 @@ constexpr uint32_t kHSmemS0f = 2 * kTileLights * 16;
 constexpr uint32_t kHSmemS0i = 2 * kTileLights * 2;
 constexpr uint32_t kHSmemBytes = kHSmemRing + kHSmemS0f + kHSmemS0i;
 
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p)
-{
-	uint32_t v;
-	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-	return v;
-}
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p)
 {
 	unsigned long long v;
@@ -106,12 +103,6 @@ __device__ __forceinline__ void sphere_box_hit2(const float4& a, const float4& b
 
 // segment -> chunk: chunk 0 = segments [0,4), chunk c >= 1 = segments [2^(c+1), 2^(c+2))
 __device__ __forceinline__ uint32_t hier_chunk_of(uint32_t seg) { return seg < 4 ? 0u : (30u - __clz(seg)); }
-__device__ __forceinline__ uint32_t hier_chunk_segs(uint32_t chunk, uint32_t num_segs)
-{
-	const uint32_t b = chunk == 0 ? 0u : (2u << chunk), e = 4u << chunk;
-	return min(e, num_segs) - min(b, num_segs);
-}
-
 template <int K, bool WRITE>
 __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 {
@@ -157,11 +148,6 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	bool active[K];
 	const uint32_t chunk = hier_chunk_of(seg);
 	const uint32_t index_base = (WRITE && p.index_base) ? *p.index_base : 0u;
-	uint32_t complete = 0; // bit c: every segment of chunk c < chunk has published its counts
-	if (!WRITE)
-		for (uint32_t c = 0; c < chunk; ++c)
-			if (ld_acquire_u32(&p.chunk_done[c * p.ncb + cb]) == hier_chunk_segs(c, p.num_segs))
-				complete |= 1u << c;
 #pragma unroll
 	for (int k = 0; k < K; ++k)
 	{
@@ -178,6 +164,9 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 		hi[k][0] = hi[k][1] = hi[k][2] = -kInf;
 		if (valid)
 		{
+			// every load below is independent of the others: one memory round trip for the whole prologue
+			const float4* a = reinterpret_cast<const float4*>(p.aabbs + p.cluster_begin + cidx[k]);
+			const float4 mn = __ldg(a), mx = __ldg(a + 1);
 			if (WRITE)
 			{
 				const size_t sc = static_cast<size_t>(seg) * p.cluster_count + cidx[k];
@@ -195,8 +184,9 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 			else
 			{
 				uint32_t prior = 0;
-				for (uint32_t c = 0; c < chunk; ++c)
-					if ((complete >> c) & 1u)
+#pragma unroll
+				for (uint32_t c = 0; c < kHMaxChunks; ++c)
+					if (c < chunk)
 						prior += __ldcg(&p.cum[static_cast<size_t>(c) * p.cluster_count + cidx[k]]);
 				if (prior < p.cap)
 				{
@@ -206,8 +196,6 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 			}
 			if (active[k])
 			{
-				const float4* a = reinterpret_cast<const float4*>(p.aabbs + p.cluster_begin + cidx[k]);
-				const float4 mn = __ldg(a), mx = __ldg(a + 1);
 				lo[k][0] = mn.x, lo[k][1] = mn.y, lo[k][2] = mn.z;
 				hi[k][0] = mx.x, hi[k][1] = mx.y, hi[k][2] = mx.z;
 			}
@@ -387,10 +375,6 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 				if (cnt[k])
 					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
 			}
-		__threadfence();
-		__syncthreads();
-		if (threadIdx.x == 0)
-			atomicAdd(&p.chunk_done[chunk * p.ncb + cb], 1u);
 	}
 	if (lane == 0 && (n_l0 | n_l1 | n_l2))
 	{
@@ -401,88 +385,98 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 
 // ======================================================================================================
 // finalize: per-segment counts -> per-segment prefixes, capped counts, exclusive scan over clusters.
-// One thread per cluster; the scan across CTAs is a single pass with decoupled look-back.  The look-back
-// state words carry the frame's epoch, so they never need clearing.
+// CTA = 32 clusters (lane) x 8 segment groups (warp): every count is loaded exactly once, all loads of a
+// thread are independent, rows are 128 B coalesced.  The scan across CTAs is a single pass with a
+// warp-wide decoupled look-back; the state words carry the frame's epoch, so they never need clearing.
 // ======================================================================================================
-__device__ __forceinline__ uint32_t hier_warp_inclusive_scan(uint32_t v, uint32_t lane)
+constexpr uint32_t kFinWarps = 8;
+constexpr uint32_t kFinMaxGroup = 256 / kFinWarps; // segments per warp at most (num_segs <= 256)
+
+__global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const FinalizeParams p)
 {
+	__shared__ uint32_t s_part[kFinWarps][32];
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t c = blockIdx.x * 32 + lane;
+	const bool valid = c < p.cluster_count;
+	const uint32_t group = (p.num_segs + kFinWarps - 1) / kFinWarps;
+	const uint32_t s0 = warp * group, s1 = min(s0 + group, p.num_segs);
+	uint32_t n[kFinMaxGroup];
+	uint32_t part = 0;
+#pragma unroll
+	for (uint32_t i = 0; i < kFinMaxGroup; ++i)
+	{
+		const uint32_t s = s0 + i;
+		n[i] = (valid && s < s1) ? p.seg_counts[static_cast<size_t>(s) * p.cluster_count + c] : 0u;
+		part += n[i];
+	}
+	s_part[warp][lane] = part;
+	__syncthreads();
+	uint32_t run = 0, total = 0;
+#pragma unroll
+	for (uint32_t w = 0; w < kFinWarps; ++w)
+	{
+		const uint32_t v = s_part[w][lane];
+		run += w < warp ? v : 0u;
+		total += v;
+	}
+#pragma unroll
+	for (uint32_t i = 0; i < kFinMaxGroup; ++i)
+	{
+		const uint32_t s = s0 + i;
+		if (valid && s < s1)
+			p.seg_prefix[static_cast<size_t>(s) * p.cluster_count + c] = (n[i] == 0 || run >= p.cap) ? kSkip : run;
+		run += n[i];
+	}
+	if (warp != 0)
+		return;
+	const uint32_t v = valid ? min(total, p.cap) : 0u;
+	uint32_t inc = v;
 #pragma unroll
 	for (int d = 1; d < 32; d <<= 1)
 	{
-		const uint32_t n = __shfl_up_sync(0xffffffffu, v, d);
+		const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
 		if (lane >= static_cast<uint32_t>(d))
-			v += n;
+			inc += t;
 	}
-	return v;
-}
-
-__global__ void __launch_bounds__(256) hier_finalize_kernel(const FinalizeParams p)
-{
-	__shared__ uint32_t warp_sums[8];
-	__shared__ uint32_t s_prefix;
-	const uint32_t c = blockIdx.x * 256 + threadIdx.x;
-	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	uint32_t run = 0;
-	if (c < p.cluster_count)
+	const uint32_t agg = __shfl_sync(0xffffffffu, inc, 31);
+	const uint32_t over = __popc(__ballot_sync(0xffffffffu, valid && v >= p.cap));
+	// state word: [epoch:30 | flag:2 | value:32]; flag 1 = aggregate of this CTA, 2 = inclusive prefix
+	const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
+	if (lane == 0)
+		st_release_u64(&p.scan_state[blockIdx.x], tag | ((blockIdx.x == 0 ? 2ull : 1ull) << 32) | agg);
+	uint32_t prefix = 0;
+	for (int base = static_cast<int>(blockIdx.x); base > 0; base -= 32)
 	{
-#pragma unroll 4
-		for (uint32_t s = 0; s < p.num_segs; ++s)
+		const int i = base - 1 - static_cast<int>(lane); // lane 0 looks at the nearest predecessor
+		unsigned long long w;
+		bool ok;
+		do
 		{
-			const size_t i = static_cast<size_t>(s) * p.cluster_count + c;
-			const uint32_t n = p.seg_counts[i];
-			p.seg_prefix[i] = (n == 0 || run >= p.cap) ? kSkip : run;
-			run += n;
-		}
+			w = i >= 0 ? ld_acquire_u64(&p.scan_state[i]) : (tag | (2ull << 32));
+			ok = (w >> 34) == p.epoch && ((w >> 32) & 3ull) != 0;
+		} while (!__all_sync(0xffffffffu, ok));
+		const uint32_t inclusive = __ballot_sync(0xffffffffu, ((w >> 32) & 3ull) == 2);
+		const uint32_t upto = inclusive ? static_cast<uint32_t>(__ffs(inclusive)) - 1u : 31u; // nearest inclusive prefix ends the walk
+		prefix += __reduce_add_sync(0xffffffffu, lane <= upto ? static_cast<uint32_t>(w) : 0u);
+		if (inclusive)
+			break;
 	}
-	const uint32_t v = min(run, p.cap);
-	const uint32_t inc = hier_warp_inclusive_scan(v, lane);
-	if (lane == 31)
-		warp_sums[warp] = inc;
-	const uint32_t over = __syncthreads_count(c < p.cluster_count && v >= p.cap);
-	uint32_t before = 0, total = 0;
-#pragma unroll
-	for (uint32_t w = 0; w < 8; ++w)
+	if (lane == 0)
 	{
-		const uint32_t s = warp_sums[w];
-		before += w < warp ? s : 0u;
-		total += s;
-	}
-	if (threadIdx.x == 0)
-	{
-		// state word: [epoch:30 | flag:2 | value:32]; flag 1 = aggregate of this CTA, 2 = inclusive prefix
-		const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
-		uint32_t prefix = 0;
-		if (blockIdx.x == 0)
-			st_release_u64(&p.scan_state[0], tag | (2ull << 32) | total);
-		else
-		{
-			st_release_u64(&p.scan_state[blockIdx.x], tag | (1ull << 32) | total);
-			for (int i = static_cast<int>(blockIdx.x) - 1; i >= 0;)
-			{
-				const unsigned long long w = ld_acquire_u64(&p.scan_state[i]);
-				if ((w >> 34) != p.epoch || ((w >> 32) & 3ull) == 0)
-					continue; // predecessor has not published yet
-				prefix += static_cast<uint32_t>(w);
-				if (((w >> 32) & 3ull) == 2)
-					break;
-				--i;
-			}
-			st_release_u64(&p.scan_state[blockIdx.x], tag | (2ull << 32) | (prefix + total));
-		}
-		s_prefix = prefix;
+		if (blockIdx.x != 0)
+			st_release_u64(&p.scan_state[blockIdx.x], tag | (2ull << 32) | (prefix + agg));
 		if (over)
 			atomicAdd(&p.stats->overflow_clusters, over);
 		if (blockIdx.x == gridDim.x - 1)
 		{
-			*p.shard_total = prefix + total;
-			p.stats->total_indices = prefix + total;
+			*p.shard_total = prefix + agg;
+			p.stats->total_indices = prefix + agg;
 		}
 	}
-	__syncthreads();
-	if (c < p.cluster_count)
+	if (valid)
 	{
 		p.counts[c] = v;
-		p.offsets[c] = s_prefix + before + inc - v;
+		p.offsets[c] = prefix + inc - v;
 	}
 }
 
@@ -520,8 +514,9 @@ void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const u
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs)
 {
-	// about 16 CTAs per SM over the whole launch; segments are whole tiles and at most max_segs of them
-	const uint64_t target = 148ull * 16ull;
+	// about 48 CTAs per SM over the whole launch (measured on B200: short segments win -- more CTAs in flight hide the
+	// per-tile barrier latency and earlier segments publish their counts sooner); segments are whole tiles
+	const uint64_t target = 148ull * 48ull;
 	const uint64_t tps = (static_cast<uint64_t>(tiles_total) * h.ncb) / target;
 	uint32_t t = 1;
 	while (static_cast<uint64_t>(t) * 2 <= tps)
@@ -585,7 +580,7 @@ cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream)
 {
 	if (p.cluster_count == 0)
 		return cudaSuccess;
-	hier_finalize_kernel<<<(p.cluster_count + 255) / 256, 256, 0, stream>>>(p);
+	hier_finalize_kernel<<<(p.cluster_count + 31) / 32, kFinWarps * 32, 0, stream>>>(p);
 	return cudaGetLastError();
 }
 

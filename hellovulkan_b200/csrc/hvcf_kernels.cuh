@@ -75,7 +75,6 @@ struct HierParams
 	uint32_t* seg_counts;          // [num_segs][cluster_count]   pass 1 out, pass 2 in
 	uint32_t* seg_prefix;          // [num_segs][cluster_count]   finalize out, pass 2 in
 	uint32_t* cum;                 // [num_chunks][cluster_count] zeroed per frame
-	uint32_t* chunk_done;          // [num_chunks][ncb]           zeroed per frame
 	const uint32_t* offsets;       // [cluster_count] shard-local exclusive offsets
 	const uint32_t* counts;        // [cluster_count] capped counts
 	const uint32_t* index_base;    // device scalar or NULL
@@ -94,7 +93,7 @@ struct FinalizeParams
 	uint32_t cluster_count;
 	uint32_t cap;
 	uint32_t epoch;                 // frame serial, > 0, < 2^30
-	unsigned long long* scan_state; // [ceil(cluster_count / 256)]
+	unsigned long long* scan_state; // [ceil(cluster_count / 32)]
 	uint32_t* counts;
 	uint32_t* offsets;
 	uint32_t* shard_total;
