@@ -73,6 +73,7 @@ struct hvcf_ctx
 	uint32_t* d_hseg_prefix = nullptr;
 	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count]
 	uint32_t* d_hoffsets = nullptr;
+	uint32_t* d_hlane_cluster = nullptr;
 	unsigned long long* d_scan_state = nullptr;
 
 	// reference-layout buffers
@@ -133,6 +134,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_hseg_prefix);
 	cudaFree(c->d_hscratch);
 	cudaFree(c->d_hoffsets);
+	cudaFree(c->d_hlane_cluster);
 	cudaFree(c->d_scan_state);
 	cudaFreeHost(c->h_ubo);
 	cudaFreeHost(c->h_zplanes);
@@ -153,14 +155,9 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	HierParams p{};
 	p.lights_view = ctx->d_lights_view;
 	p.aabbs = ctx->d_aabb;
-	p.X = ctx->X;
-	p.Y = ctx->Y;
-	p.Zs = ctx->cluster_count / (ctx->X * ctx->Y);
+	p.lane_cluster = ctx->d_hlane_cluster;
 	p.cluster_begin = ctx->cluster_begin;
 	p.cluster_count = ctx->cluster_count;
-	p.bx = ctx->hp.bx, p.by = ctx->hp.by, p.bz = ctx->hp.bz;
-	p.nbx = ctx->hp.nbx, p.nby = ctx->hp.nby, p.nbz = ctx->hp.nbz;
-	p.nblocks = ctx->hp.nblocks;
 	p.ncb = ctx->hp.ncb;
 	p.tiles_total = ctx->h_tiles_total;
 	p.tiles_per_seg = ctx->h_tiles_per_seg;
@@ -302,6 +299,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hseg_prefix, sizeof(uint32_t) * Cs * c->h_max_segs);
 		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * c->h_max_chunks);
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
+		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
 	}
 	else
@@ -332,6 +330,12 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		e = cudaMemset(c->d_stats, 0, sizeof(DeviceStats) * c->frame_count);
 	if (e == cudaSuccess)
 		e = cudaMemset(c->d_shard_total, 0, sizeof(uint32_t));
+	if (e == cudaSuccess && c->hier)
+	{
+		std::vector<uint32_t> map;
+		hier_build_lane_map(c->hp, c->X, c->Y, ze - zb, &map);
+		e = cudaMemcpy(c->d_hlane_cluster, map.data(), map.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+	}
 	if (e == cudaSuccess && c->hier)
 		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32));
 	if (e != cudaSuccess)

@@ -30,6 +30,8 @@
 // scheduling.  No flags, no fences.
 #include "hvcf_kernels.cuh"
 
+#include <vector>
+
 namespace hvcf
 {
 
@@ -138,7 +140,6 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	}
 
 	// ---- this lane's K clusters (one per block), while the first tiles are in flight ----------------
-	const uint32_t lx = lane % p.bx, ly = (lane / p.bx) % p.by, lz = lane / (p.bx * p.by);
 	const float kInf = __int_as_float(0x7f800000);
 	float lo[K][3], hi[K][3];
 	uint32_t cidx[K];    // cluster index inside the shard, kSkip = no cluster on this lane
@@ -151,11 +152,9 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 #pragma unroll
 	for (int k = 0; k < K; ++k)
 	{
-		const uint32_t b = (cb * kHWarps + warp) * K + k;
-		const uint32_t bxi = b % p.nbx, byi = (b / p.nbx) % p.nby, bzi = b / (p.nbx * p.nby);
-		const uint32_t x = bxi * p.bx + lx, y = byi * p.by + ly, z = bzi * p.bz + lz;
-		const bool valid = b < p.nblocks && x < p.X && y < p.Y && z < p.Zs;
-		cidx[k] = valid ? x + y * p.X + z * p.X * p.Y : kSkip;
+		// block -> lane -> cluster map, built once per context on the host (hier_build_lane_map)
+		cidx[k] = __ldg(&p.lane_cluster[(static_cast<size_t>((cb * kHWarps + warp) * K + k) << 5) + lane]);
+		const bool valid = cidx[k] != kSkip;
 		cnt[k] = 0;
 		limit[k] = 0;
 		wbase[k] = 0;
@@ -509,6 +508,24 @@ void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const u
 	if (k_override == 1 || k_override == 2 || k_override == 4)
 		h.K = static_cast<uint32_t>(k_override);
 	h.ncb = (h.nblocks + kHWarps * h.K - 1) / (kHWarps * h.K);
+}
+
+// cluster index (inside the shard) of every lane of every block, kSkip where the block sticks out of the grid;
+// padded to whole CTAs so the kernel needs no bounds check
+void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out)
+{
+	const size_t blocks = static_cast<size_t>(h.ncb) * kHWarps * h.K;
+	out->assign(blocks * 32, kSkip);
+	for (uint32_t b = 0; b < h.nblocks; ++b)
+	{
+		const uint32_t bxi = b % h.nbx, byi = (b / h.nbx) % h.nby, bzi = b / (h.nbx * h.nby);
+		for (uint32_t lane = 0; lane < 32; ++lane)
+		{
+			const uint32_t x = bxi * h.bx + lane % h.bx, y = byi * h.by + (lane / h.bx) % h.by, z = bzi * h.bz + lane / (h.bx * h.by);
+			if (x < X && y < Y && z < Zs)
+				(*out)[static_cast<size_t>(b) * 32 + lane] = x + y * X + z * X * Y;
+		}
+	}
 }
 
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,

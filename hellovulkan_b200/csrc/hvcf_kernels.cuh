@@ -3,6 +3,8 @@
 
 #include "hvcf_device.cuh"
 
+#include <vector>
+
 namespace hvcf
 {
 
@@ -66,10 +68,10 @@ struct HierParams
 {
 	const float4* lights_view;
 	const hvcf_aabb* aabbs;        // whole grid
-	uint32_t X, Y, Zs;             // shard extent in clusters
+	const uint32_t* lane_cluster;  // [ncb * 8 * K][32] shard-local cluster index of each lane, 0xffffffff = none
 	uint32_t cluster_begin;        // shard, global cluster ids
 	uint32_t cluster_count;
-	uint32_t bx, by, bz, nbx, nby, nbz, nblocks, ncb;
+	uint32_t ncb;
 	uint32_t tiles_total, tiles_per_seg, num_segs;
 	uint32_t cap;
 	uint32_t* seg_counts;          // [num_segs][cluster_count]   pass 1 out, pass 2 in
@@ -101,6 +103,7 @@ struct FinalizeParams
 };
 
 void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], HierPlan* out);
+void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out);
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs);
 uint32_t hier_num_chunks(uint32_t num_segs);
