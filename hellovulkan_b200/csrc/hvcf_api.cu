@@ -489,7 +489,8 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		++launches;
 	}
 	DeviceStats* stats = &ctx->d_stats[frame];
-	HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
+	if (!ctx->hier)
+		HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
 	const uint32_t n = ctx->num_lights;
 	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
 	if (ctx->hier)
@@ -500,8 +501,9 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
 		ctx->h_tiles_total = tiles_total;
 		const uint32_t chunks = hier_num_chunks(ctx->h_num_segs);
-		HVCF_CUDA(cudaMemsetAsync(ctx->d_hscratch, 0, sizeof(uint32_t) * static_cast<size_t>(ctx->cluster_count) * chunks, s));
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, s));
+		// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the transform kernel
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
+			ctx->cluster_count * chunks, stats, s));
 		HierParams p = hier_params(ctx, frame);
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
@@ -536,7 +538,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		num_segs = (tiles_total + tiles_per_seg - 1) / tiles_per_seg; // no empty segment
 	if (n)
 	{
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, s));
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, nullptr, 0, nullptr, s));
 		CullParams p;
 		p.lights_view = ctx->d_lights_view;
 		p.aabbs = ctx->d_aabb;

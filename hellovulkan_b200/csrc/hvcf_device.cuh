@@ -118,6 +118,13 @@ __device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gmem_s
 				 : "memory");
 }
 
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------
+// grid_dep_launch: lets the next kernel of the stream (launched with the programmatic-serialization
+// attribute) start as soon as every CTA of this grid has been scheduled; grid_dep_wait: blocks until the
+// previous grid has COMPLETED and its writes are visible.  Both are no-ops under a plain launch.
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t lanemask_lt()
 {
 	uint32_t m;

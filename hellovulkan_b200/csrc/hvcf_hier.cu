@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	float4* const s0f = reinterpret_cast<float4*>(smem + kHSmemRing);
 	uint16_t* const s0i = reinterpret_cast<uint16_t*>(smem + kHSmemRing + kHSmemS0f);
 
+	grid_dep_launch();
 	if (threadIdx.x == 0)
 	{
 #pragma unroll
@@ -130,6 +131,8 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 		mbar_fence_init();
 	}
 	__syncthreads();
+	// everything above overlaps the tail of the previous kernel of the frame (PDL); everything below reads what it wrote
+	grid_dep_wait();
 	if (threadIdx.x == 0)
 	{
 		for (uint32_t s = 0; s < kHStages && s < ntiles; ++s)
@@ -316,10 +319,11 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 			continue;
 		// ---- level 1 (lane = surviving light) and level 2 (lane = cluster) ---------------------------------
 		const uint32_t tile_base = (t_begin + it) * kTileLights;
-		for (uint32_t i = 0; i < n0; i += 32)
+		for (uint32_t i = 0; i < n0 && !warp_done; i += 32)
 		{
 			const uint32_t idx = i + lane;
 			const float4 r = idx < n0 ? sf[idx] : make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+			warp_done = true;
 #pragma unroll
 			for (int k = 0; k < K; ++k)
 			{
@@ -328,32 +332,37 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 				uint32_t m = __ballot_sync(0xffffffffu, sphere_box_hit(r.x, r.y, r.z, r.w, ulo[k], uhi[k]));
 				n_l1 += 32;
 				n_l2 += 32u * __popc(m);
+				// two candidates per trip: the trips are latency-bound (LDS -> 6-deep FP chain), not issue-bound
 				while (m)
 				{
-					const uint32_t j = i + __ffs(m) - 1;
+					const uint32_t j0 = i + __ffs(m) - 1;
 					m &= m - 1;
-					const float4 c = sf[j]; // broadcast
-					const bool hit = sphere_box_hit(c.x, c.y, c.z, c.w, lo[k], hi[k]) && active[k];
+					const bool two = m != 0;
+					const uint32_t j1 = two ? i + __ffs(m) - 1 : j0;
+					m &= m - 1; // 0 & 0xffffffff == 0 when the mask is already empty
+					const float4 c0 = sf[j0], c1 = sf[j1]; // broadcasts
+					const bool hit0 = sphere_box_hit(c0.x, c0.y, c0.z, c0.w, lo[k], hi[k]) && active[k];
+					const bool hit1 = sphere_box_hit(c1.x, c1.y, c1.z, c1.w, lo[k], hi[k]) && active[k] && two;
 					if (WRITE)
 					{
-						if (hit && cnt[k] < limit[k])
+						if (hit0 && cnt[k] < limit[k])
 						{
-							p.indices[wbase[k] + cnt[k]] = tile_base + si[j];
+							p.indices[wbase[k] + cnt[k]] = tile_base + si[j0];
+							++cnt[k];
+						}
+						if (hit1 && cnt[k] < limit[k])
+						{
+							p.indices[wbase[k] + cnt[k]] = tile_base + si[j1];
 							++cnt[k];
 						}
 					}
 					else
-						cnt[k] += hit ? 1u : 0u;
+						cnt[k] += (hit0 ? 1u : 0u) + (hit1 ? 1u : 0u);
 				}
-			}
-		}
-		warp_done = true;
-#pragma unroll
-		for (int k = 0; k < K; ++k)
-		{
-			if (blk_active[k])
+				// early exit inside the tile: a block whose lanes all hold their quota stops here
 				blk_active[k] = !__all_sync(0xffffffffu, !active[k] || cnt[k] >= limit[k]);
-			warp_done = warp_done && !blk_active[k];
+				warp_done = warp_done && !blk_active[k];
+			}
 		}
 	}
 	// bulk copies still in flight must land before this CTA's shared memory is handed on
@@ -397,6 +406,8 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const uint32_t c = blockIdx.x * 32 + lane;
 	const bool valid = c < p.cluster_count;
+	grid_dep_launch();
+	grid_dep_wait();
 	const uint32_t group = (p.num_segs + kFinWarps - 1) / kFinWarps;
 	const uint32_t s0 = warp * group, s1 = min(s0 + group, p.num_segs);
 	uint32_t n[kFinMaxGroup];
@@ -573,8 +584,17 @@ static cudaError_t launch_hier_t(const HierParams& p, cudaStream_t stream)
 			return e;
 		configured = true;
 	}
-	hier_kernel<K, WRITE><<<p.ncb * p.num_segs, kHWarps * 32, kHSmemBytes, stream>>>(p);
-	return cudaGetLastError();
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3(p.ncb * p.num_segs, 1, 1);
+	cfg.blockDim = dim3(kHWarps * 32, 1, 1);
+	cfg.dynamicSmemBytes = kHSmemBytes;
+	cfg.stream = stream;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_kernel<K, WRITE>, p);
 }
 
 cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream)
@@ -597,8 +617,16 @@ cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream)
 {
 	if (p.cluster_count == 0)
 		return cudaSuccess;
-	hier_finalize_kernel<<<(p.cluster_count + 31) / 32, kFinWarps * 32, 0, stream>>>(p);
-	return cudaGetLastError();
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3((p.cluster_count + 31) / 32, 1, 1);
+	cfg.blockDim = dim3(kFinWarps * 32, 1, 1);
+	cfg.stream = stream;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_finalize_kernel, p);
 }
 
 } // namespace hvcf

@@ -74,9 +74,22 @@ __global__ void __launch_bounds__(128) aabb_generate_kernel(const hvcf_cluster_f
 // (fully coalesced 128-bit stores).  HBM-bound: 64 B per light.
 // ======================================================================================================
 __global__ void __launch_bounds__(256) light_transform_kernel(const hvcf_cluster_forward_ubo* __restrict__ ubo,
-	const hvcf_light_data* __restrict__ lights, uint32_t num_lights, uint32_t num_pairs, float4* __restrict__ out)
+	const hvcf_light_data* __restrict__ lights, uint32_t num_lights, uint32_t num_pairs, float4* __restrict__ out,
+	uint32_t* __restrict__ zero, uint32_t zero_words, DeviceStats* __restrict__ stats)
 {
+	grid_dep_launch();
 	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	// per-frame scratch of the hierarchical mode (early-exit counters) and the work counters are cleared here
+	// instead of by memset nodes, so that transform -> pass 1 -> finalize -> pass 2 is an unbroken PDL chain
+	for (uint32_t i = p; i < zero_words; i += gridDim.x * blockDim.x)
+		zero[i] = 0u;
+	if (p == 0 && stats)
+	{
+		stats->executed_tests = 0ull;
+		stats->prefilter_tests = 0ull;
+		stats->total_indices = 0u;
+		stats->overflow_clusters = 0u;
+	}
 	if (p >= num_pairs)
 		return;
 	const uint32_t g = p >> 5, l = p & 31;
@@ -507,12 +520,14 @@ cudaError_t launch_aabb_generate(const hvcf_cluster_forward_ubo* ubo, const floa
 }
 
 cudaError_t launch_light_transform(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_data* lights,
-	uint32_t num_lights, uint32_t padded_lights, float4* out, cudaStream_t stream)
+	uint32_t num_lights, uint32_t padded_lights, float4* out, uint32_t* zero, uint32_t zero_words, DeviceStats* stats,
+	cudaStream_t stream)
 {
 	const uint32_t pairs = padded_lights / 2;
-	if (pairs == 0)
+	if (pairs == 0 && zero_words == 0 && !stats)
 		return cudaSuccess;
-	light_transform_kernel<<<(pairs + 255) / 256, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out);
+	const uint32_t blocks = pairs ? (pairs + 255) / 256 : 1;
+	light_transform_kernel<<<blocks, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out, zero, zero_words, stats);
 	return cudaGetLastError();
 }
 

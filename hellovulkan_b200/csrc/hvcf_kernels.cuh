@@ -40,8 +40,10 @@ struct ScatterParams
 
 cudaError_t launch_aabb_generate(const hvcf_cluster_forward_ubo* ubo, const float* zplanes, hvcf_aabb* out,
 	uint32_t cluster_count, cudaStream_t stream);
+// also clears `zero_words` words at `zero` and the work counters `stats` (either may be null / 0)
 cudaError_t launch_light_transform(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_data* lights,
-	uint32_t num_lights, uint32_t padded_lights, float4* out, cudaStream_t stream);
+	uint32_t num_lights, uint32_t padded_lights, float4* out, uint32_t* zero, uint32_t zero_words, DeviceStats* stats,
+	cudaStream_t stream);
 // variant: 0..2 = packed FP32x2 with 1/2/4 clusters per warp, 3..5 = scalar FP32 with 1/2/4
 constexpr int kNumCullVariants = 6;
 uint32_t cull_variant_clusters_per_cta(int variant);
