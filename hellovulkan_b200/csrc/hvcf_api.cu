@@ -67,6 +67,7 @@ struct hvcf_ctx
 	HierPlan hp{};
 	uint32_t h_max_segs = 0, h_max_chunks = 0;
 	int h_tps_override = 0;
+	uint32_t h_split_head = 0;
 	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
 	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
@@ -162,6 +163,8 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.tiles_total = ctx->h_tiles_total;
 	p.tiles_per_seg = ctx->h_tiles_per_seg;
 	p.num_segs = ctx->h_num_segs;
+	p.seg_begin = 0;
+	p.seg_end = ctx->h_num_segs;
 	p.cap = ctx->cap;
 	p.seg_counts = ctx->d_hseg_counts;
 	p.seg_prefix = ctx->d_hseg_prefix;
@@ -271,6 +274,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->h_max_segs = max_tiles < 256 ? max_tiles : 256;
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
+		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));
 	}
 
 #define HVCF_ALLOC(ptr, bytes)                                                              \
@@ -507,6 +511,17 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		HierParams p = hier_params(ctx, frame);
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+		// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
+		// later segments then begin with the dense clusters already known to be full (PDL-chained, one extra launch)
+		const uint32_t head = ctx->h_split_head < ctx->h_num_segs ? ctx->h_split_head : 0u;
+		if (head)
+		{
+			p.seg_end = head;
+			HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), false, p, s));
+			p.seg_begin = head;
+			p.seg_end = ctx->h_num_segs;
+			++launches;
+		}
 		HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), false, p, s));
 		if (ctx->timing)
 		{

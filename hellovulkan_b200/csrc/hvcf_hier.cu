@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	__shared__ float s_union[kHWarps][6];
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint32_t cb = blockIdx.x % p.ncb, seg = blockIdx.x / p.ncb;
+	const uint32_t cb = blockIdx.x % p.ncb, seg = p.seg_begin + blockIdx.x / p.ncb;
 	const uint32_t t_begin = seg * p.tiles_per_seg;
 	const uint32_t t_end = min(t_begin + p.tiles_per_seg, p.tiles_total);
 	const uint32_t ntiles = t_end - t_begin;
@@ -585,7 +585,7 @@ static cudaError_t launch_hier_t(const HierParams& p, cudaStream_t stream)
 		configured = true;
 	}
 	cudaLaunchConfig_t cfg{};
-	cfg.gridDim = dim3(p.ncb * p.num_segs, 1, 1);
+	cfg.gridDim = dim3(p.ncb * (p.seg_end - p.seg_begin), 1, 1);
 	cfg.blockDim = dim3(kHWarps * 32, 1, 1);
 	cfg.dynamicSmemBytes = kHSmemBytes;
 	cfg.stream = stream;
@@ -599,7 +599,7 @@ static cudaError_t launch_hier_t(const HierParams& p, cudaStream_t stream)
 
 cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream)
 {
-	if (p.ncb == 0 || p.num_segs == 0)
+	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
 		return cudaSuccess;
 	switch (K * 2 + (write ? 1 : 0))
 	{

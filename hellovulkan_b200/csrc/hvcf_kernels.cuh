@@ -75,6 +75,7 @@ struct HierParams
 	uint32_t cluster_count;
 	uint32_t ncb;
 	uint32_t tiles_total, tiles_per_seg, num_segs;
+	uint32_t seg_begin, seg_end;   // segments of this launch
 	uint32_t cap;
 	uint32_t* seg_counts;          // [num_segs][cluster_count]   pass 1 out, pass 2 in
 	uint32_t* seg_prefix;          // [num_segs][cluster_count]   finalize out, pass 2 in
