@@ -76,6 +76,7 @@ struct hvcf_ctx
 	uint32_t* d_hoffsets = nullptr;
 	uint32_t* d_hlane_cluster = nullptr;
 	unsigned long long* d_scan_state = nullptr;
+	unsigned long long* d_trace = nullptr;   // HVCF_HIER_TRACE=1: per-CTA timestamps (debug)
 
 	// reference-layout buffers
 	hvcf_light_data* d_lights = nullptr;   // ResourcesLight::storageBuffer_
@@ -137,6 +138,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_hoffsets);
 	cudaFree(c->d_hlane_cluster);
 	cudaFree(c->d_scan_state);
+	cudaFree(c->d_trace);
 	cudaFreeHost(c->h_ubo);
 	cudaFreeHost(c->h_zplanes);
 	cudaFreeHost(c->h_one_light);
@@ -177,6 +179,7 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.indices = ctx->d_indices;
 	p.frame_total = &ctx->d_global_index[frame];
 	p.stats = &ctx->d_stats[frame];
+	p.trace = ctx->d_trace;
 	return p;
 }
 
@@ -305,6 +308,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
+		if (env_int("HVCF_HIER_TRACE", 0))
+			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 8 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
 	}
 	else
 	{
@@ -709,6 +714,21 @@ int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
 	out->total_indices = ds.total_indices;
 	out->overflow_clusters = ds.overflow_clusters;
 	out->kernel_launches = ctx->last_launches[frame];
+	return HVCF_OK;
+}
+
+int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_words, size_t* out_ctas_per_pass)
+{
+	if (!ctx || !out_words || !out_ctas_per_pass)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_trace: null argument");
+	if (!ctx->d_trace)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_trace: create the context with HVCF_HIER_TRACE=1 (hierarchical mode)");
+	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * ctx->h_num_segs;
+	const size_t words = ctas * 8 < max_words ? ctas * 8 : max_words;
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(cudaDeviceSynchronize());
+	HVCF_CUDA(cudaMemcpy(out_words, ctx->d_trace, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+	*out_ctas_per_pass = ctas;
 	return HVCF_OK;
 }
 

@@ -39,6 +39,7 @@ constexpr uint32_t kHWarps = 8;
 constexpr uint32_t kHStages = 2;
 constexpr uint32_t kHGroupsPerWarp = kTileGroups / kHWarps; // 2
 constexpr uint32_t kSkip = 0xffffffffu;
+constexpr uint32_t kCand = 4;      // level-2 candidates in flight per trip
 constexpr uint32_t kHMaxChunks = 8; // 256 segments at most (hier_num_chunks(256) == 7)
 static_assert(kTileGroups % kHWarps == 0, "level 0 splits a tile's groups evenly over the warps");
 
@@ -133,6 +134,9 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	__syncthreads();
 	// everything above overlaps the tail of the previous kernel of the frame (PDL); everything below reads what it wrote
 	grid_dep_wait();
+	unsigned long long t_start = 0;
+	if (p.trace && threadIdx.x == 0)
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 	if (threadIdx.x == 0)
 	{
 		for (uint32_t s = 0; s < kHStages && s < ntiles; ++s)
@@ -209,15 +213,19 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	// ---- union boxes: per block (level 1), then per CTA (level 0) ---------------------------------------
 	float ulo[K][3], uhi[K][3];
 	bool blk_active[K];
+	uint32_t alive[K]; // lanes of the block that still want hits
+	bool blk_nan[K];   // the block holds a NaN box: its union stays 'pass everything'
 	float wlo0 = kInf, wlo1 = kInf, wlo2 = kInf, whi0 = -kInf, whi1 = -kInf, whi2 = -kInf;
 #pragma unroll
 	for (int k = 0; k < K; ++k)
 	{
-		blk_active[k] = __any_sync(0xffffffffu, active[k]);
+		alive[k] = __ballot_sync(0xffffffffu, active[k]);
+		blk_active[k] = alive[k] != 0;
 		// a NaN bound makes every light hit that cluster (both shader comparisons are false): pass everything
 		const bool nan = active[k] && !(lo[k][0] == lo[k][0] && lo[k][1] == lo[k][1] && lo[k][2] == lo[k][2] &&
 			hi[k][0] == hi[k][0] && hi[k][1] == hi[k][1] && hi[k][2] == hi[k][2]);
 		const bool any_nan = __any_sync(0xffffffffu, nan);
+		blk_nan[k] = any_nan;
 #pragma unroll
 		for (int i = 0; i < 3; ++i)
 		{
@@ -332,35 +340,56 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 				uint32_t m = __ballot_sync(0xffffffffu, sphere_box_hit(r.x, r.y, r.z, r.w, ulo[k], uhi[k]));
 				n_l1 += 32;
 				n_l2 += 32u * __popc(m);
-				// two candidates per trip: the trips are latency-bound (LDS -> 6-deep FP chain), not issue-bound
+				// kCand candidates per trip: a trip is latency-bound (LDS -> 6-deep FP chain), so independent chains are free
 				while (m)
 				{
-					const uint32_t j0 = i + __ffs(m) - 1;
-					m &= m - 1;
-					const bool two = m != 0;
-					const uint32_t j1 = two ? i + __ffs(m) - 1 : j0;
-					m &= m - 1; // 0 & 0xffffffff == 0 when the mask is already empty
-					const float4 c0 = sf[j0], c1 = sf[j1]; // broadcasts
-					const bool hit0 = sphere_box_hit(c0.x, c0.y, c0.z, c0.w, lo[k], hi[k]) && active[k];
-					const bool hit1 = sphere_box_hit(c1.x, c1.y, c1.z, c1.w, lo[k], hi[k]) && active[k] && two;
-					if (WRITE)
+					uint32_t j[kCand];
+					bool take[kCand];
+#pragma unroll
+					for (uint32_t q = 0; q < kCand; ++q)
 					{
-						if (hit0 && cnt[k] < limit[k])
+						take[q] = m != 0;
+						j[q] = take[q] ? i + __ffs(m) - 1 : j[0];
+						m &= m - 1; // 0 & 0xffffffff == 0 once the mask is empty
+					}
+					float4 c[kCand];
+#pragma unroll
+					for (uint32_t q = 0; q < kCand; ++q)
+						c[q] = sf[j[q]]; // broadcasts
+#pragma unroll
+					for (uint32_t q = 0; q < kCand; ++q)
+					{
+						const bool hit = sphere_box_hit(c[q].x, c[q].y, c[q].z, c[q].w, lo[k], hi[k]) && active[k] && take[q];
+						if (WRITE)
 						{
-							p.indices[wbase[k] + cnt[k]] = tile_base + si[j0];
-							++cnt[k];
+							if (hit && cnt[k] < limit[k])
+							{
+								p.indices[wbase[k] + cnt[k]] = tile_base + si[j[q]];
+								++cnt[k];
+							}
 						}
-						if (hit1 && cnt[k] < limit[k])
+						else
+							cnt[k] += hit ? 1u : 0u;
+					}
+				}
+				// early exit inside the tile, per lane: a cluster that holds its quota leaves the block's union box,
+				// so the remaining lanes see fewer candidates; a block with no lane left stops here
+				const uint32_t now_alive = __ballot_sync(0xffffffffu, active[k] && cnt[k] < limit[k]);
+				if (now_alive != alive[k])
+				{
+					alive[k] = now_alive;
+					active[k] = (now_alive >> lane) & 1u;
+					blk_active[k] = now_alive != 0;
+					if (now_alive && !blk_nan[k])
+					{
+#pragma unroll
+						for (int a = 0; a < 3; ++a)
 						{
-							p.indices[wbase[k] + cnt[k]] = tile_base + si[j1];
-							++cnt[k];
+							ulo[k][a] = warp_min_f(active[k] ? lo[k][a] : kInf);
+							uhi[k][a] = warp_max_f(active[k] ? hi[k][a] : -kInf);
 						}
 					}
-					else
-						cnt[k] += (hit0 ? 1u : 0u) + (hit1 ? 1u : 0u);
 				}
-				// early exit inside the tile: a block whose lanes all hold their quota stops here
-				blk_active[k] = !__all_sync(0xffffffffu, !active[k] || cnt[k] >= limit[k]);
 				warp_done = warp_done && !blk_active[k];
 			}
 		}
@@ -383,6 +412,20 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 				if (cnt[k])
 					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
 			}
+	}
+	if (p.trace)
+	{
+		// debug only (HVCF_HIER_TRACE): per CTA {start ns, end ns, SM id, level-2 lane tests of warp 0}
+		__syncthreads();
+		if (threadIdx.x == 0)
+		{
+			unsigned long long t_end;
+			uint32_t smid;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+			asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+			unsigned long long* t = p.trace + 4ull * (static_cast<size_t>(WRITE ? gridDim.x : 0) + blockIdx.x);
+			t[0] = t_start, t[1] = t_end, t[2] = smid, t[3] = n_l2;
+		}
 	}
 	if (lane == 0 && (n_l0 | n_l1 | n_l2))
 	{

@@ -88,6 +88,7 @@ struct HierParams
 	uint32_t* indices;
 	uint32_t* frame_total;         // globalIndexCountBuffers_[frame] or NULL
 	DeviceStats* stats;
+	unsigned long long* trace;     // debug: 4 words per CTA of pass 1, then of pass 2 (or NULL)
 };
 
 struct FinalizeParams

@@ -58,7 +58,7 @@ EXPORTS = [
     "hvcf_download_light_cells", "hvcf_download_light_indices", "hvcf_download_total", "hvcf_get_stats",
     "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
-    "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate",
+    "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
 ]
 
 _lib = None
@@ -105,6 +105,7 @@ def load():
     lib.hvcf_host_camera_ubo.argtypes = [f3, f3, ctypes.c_float, ctypes.c_float, u32, u32, u32, vp]
     lib.hvcf_host_init_lights.argtypes = [u32, u32, vp]
     lib.hvcf_set_timing.argtypes = [vp, i32]
+    lib.hvcf_debug_trace.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
     lib.hvcf_get_timing.argtypes = [vp, u32, f3, f3]
     lib.hvcf_measure_fp32_issue_rate.argtypes = [i32, ctypes.POINTER(ctypes.c_double)]
     _lib = lib
@@ -268,6 +269,14 @@ class Context:
         t = ctypes.c_uint32(0)
         _check(self.lib.hvcf_download_total(self.handle, frame, ctypes.byref(t), stream))
         return int(t.value)
+
+    def debug_trace(self):
+        """(pass1, pass2) arrays of per-CTA [start ns, end ns, SM id, level-2 lane tests]; needs HVCF_HIER_TRACE=1."""
+        buf = np.zeros(8 * 65536 * 4, np.uint64)
+        n = ctypes.c_size_t(0)
+        _check(self.lib.hvcf_debug_trace(self.handle, _ptr(buf), buf.size, ctypes.byref(n)))
+        n = n.value
+        return buf[: 4 * n].reshape(n, 4).copy(), buf[4 * n: 8 * n].reshape(n, 4).copy()
 
     def set_timing(self, enabled=True):
         _check(self.lib.hvcf_set_timing(self.handle, int(enabled)))
