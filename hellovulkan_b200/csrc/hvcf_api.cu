@@ -75,6 +75,12 @@ struct hvcf_ctx
 	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count]
 	uint32_t* d_hoffsets = nullptr;
 	uint32_t* d_hlane_cluster = nullptr;
+	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
+	float* d_cb_union = nullptr;             // [ncb][8]
+	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
+	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
+	uint16_t* d_bin_idx = nullptr;
+	uint32_t tiles_cap = 0;
 	unsigned long long* d_scan_state = nullptr;
 	unsigned long long* d_trace = nullptr;   // HVCF_HIER_TRACE=1: per-CTA timestamps (debug)
 
@@ -137,6 +143,10 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_hscratch);
 	cudaFree(c->d_hoffsets);
 	cudaFree(c->d_hlane_cluster);
+	cudaFree(c->d_cb_union);
+	cudaFree(c->d_bin_count);
+	cudaFree(c->d_bin_rec);
+	cudaFree(c->d_bin_idx);
 	cudaFree(c->d_scan_state);
 	cudaFree(c->d_trace);
 	cudaFreeHost(c->h_ubo);
@@ -180,6 +190,10 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.frame_total = &ctx->d_global_index[frame];
 	p.stats = &ctx->d_stats[frame];
 	p.trace = ctx->d_trace;
+	p.bin_count = ctx->d_bin_count;
+	p.bin_rec = ctx->d_bin_rec;
+	p.bin_idx = ctx->d_bin_idx;
+	p.tiles_cap = ctx->tiles_cap;
 	return p;
 }
 
@@ -278,6 +292,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
 		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));
+		c->hier_v1 = env_int("HVCF_HIER_V1", 0) != 0;
+		c->tiles_cap = max_tiles;
 	}
 
 #define HVCF_ALLOC(ptr, bytes)                                                              \
@@ -307,9 +323,17 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * c->h_max_chunks);
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
+		if (!c->hier_v1)
+		{
+			const size_t slots = static_cast<size_t>(c->hp.ncb) * c->tiles_cap;
+			HVCF_ALLOC(c->d_cb_union, sizeof(float) * 8 * c->hp.ncb);
+			HVCF_ALLOC(c->d_bin_count, sizeof(uint32_t) * slots);
+			HVCF_ALLOC(c->d_bin_rec, sizeof(float4) * slots * kBinCap);
+			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
+		}
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
 		if (env_int("HVCF_HIER_TRACE", 0))
-			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 8 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
+			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 16 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
 	}
 	else
 	{
@@ -468,6 +492,8 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	float* dz = ctx->d_zplanes + static_cast<size_t>(frame) * (ctx->Z + 1);
 	HVCF_CUDA(cudaMemcpyAsync(dz, hz, sizeof(float) * (ctx->Z + 1), cudaMemcpyHostToDevice, s));
 	HVCF_CUDA(launch_aabb_generate(&ctx->d_ubo[frame], dz, ctx->d_aabb, ctx->cluster_total, s));
+	if (ctx->hier && !ctx->hier_v1) // level-0 union boxes of the cluster groups follow the AABBs
+		HVCF_CUDA(launch_hier_unions(ctx->d_hlane_cluster, ctx->d_aabb, ctx->cluster_begin, ctx->hp.K, ctx->hp.ncb, ctx->d_cb_union, s));
 	memcpy(ctx->aabb_key, u.camera_inverse_projection, 64);
 	ctx->aabb_key[16] = u.camera_near;
 	ctx->aabb_key[17] = u.camera_far;
@@ -514,6 +540,20 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
 			ctx->cluster_count * chunks, stats, s));
 		HierParams p = hier_params(ctx, frame);
+		if (!ctx->hier_v1)
+		{
+			BinParams b{};
+			b.lights_view = ctx->d_lights_view;
+			b.cb_union = ctx->d_cb_union;
+			b.ncb = ctx->hp.ncb;
+			b.tiles_cap = ctx->tiles_cap;
+			b.bin_count = ctx->d_bin_count;
+			b.bin_rec = ctx->d_bin_rec;
+			b.bin_idx = ctx->d_bin_idx;
+			b.stats = stats;
+			HVCF_CUDA(launch_hier_bin(b, tiles_total, s));
+			++launches;
+		}
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
 		// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
@@ -522,12 +562,12 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		if (head)
 		{
 			p.seg_end = head;
-			HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), false, p, s));
+			HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
 			p.seg_begin = head;
 			p.seg_end = ctx->h_num_segs;
 			++launches;
 		}
-		HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), false, p, s));
+		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
 		if (ctx->timing)
 		{
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
@@ -599,7 +639,7 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	{
 		HierParams hp = hier_params(ctx, frame);
 		hp.index_base = d_index_base;
-		HVCF_CUDA(launch_hier(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], static_cast<cudaStream_t>(stream)));
 		ctx->last_launches[frame] += 1;
@@ -723,7 +763,7 @@ int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_wo
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_trace: null argument");
 	if (!ctx->d_trace)
 		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_trace: create the context with HVCF_HIER_TRACE=1 (hierarchical mode)");
-	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * ctx->h_num_segs;
+	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * (ctx->hier_v1 ? 1 : 2) * ctx->h_num_segs;
 	const size_t words = ctas * 8 < max_words ? ctas * 8 : max_words;
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	HVCF_CUDA(cudaDeviceSynchronize());

@@ -1,0 +1,510 @@
+// hvcf_bin.cu -- HVCF_MODE_HIERARCHICAL, second generation: level 0 of the cluster hierarchy is a streaming
+// "bin" kernel of its own, and the count / write passes are barrier-free warp programs.
+//
+//   hier_unions_kernel   once per AABB generation: union box of every cluster group (8 x K blocks x 32 clusters)
+//   hier_bin_kernel      per frame: each warp tests one TMA-staged light tile against ONE group's union box
+//                        (lane = light pair, FADD2/FMUL2, ballot/popc) and writes the survivors, in light order,
+//                        into that (group, tile) slot.  A slot holds kBinCap records; when more lights survive
+//                        the filter is not selective there and the consumers read the raw tile instead.
+//   hier2_kernel<K,W>    per frame, twice (count, then write): a WARP owns K blocks of 32 clusters (lane =
+//                        cluster) for one light segment and walks the group's survivor slots tile by tile:
+//                        level 1 (lane = surviving light vs the block union box) -> level 2 (lane = cluster,
+//                        candidate light broadcast from a per-warp shared-memory slab).  No CTA barrier, no
+//                        shared tile ring: warps only ever wait for their own loads.
+//
+// Exactness, ordering, early exit and the count -> finalize -> write scheme are those of hvcf_hier.cu (see its
+// header): union boxes are exactly conservative because they run the same uncontracted float sequence, light
+// order is never disturbed, and cum[chunk][cluster] lower bounds only remove work that cannot matter.
+#include "hvcf_hier.cuh"
+
+namespace hvcf
+{
+
+constexpr uint32_t kBinWarps = 8;  // hier_bin_kernel: groups per CTA (one per warp)
+constexpr uint32_t kMainWarps = 4; // hier2_kernel: warp programs per CTA
+
+// ======================================================================================================
+// union box of every cluster group; runs when the AABBs change.  One CTA of 256 threads per group.
+// layout: cb_union[group][8] = { lo.xyz, 0, hi.xyz, 0 }; a group holding a NaN box passes everything.
+// ======================================================================================================
+__global__ void __launch_bounds__(256) hier_unions_kernel(const uint32_t* __restrict__ lane_cluster, const hvcf_aabb* __restrict__ aabbs,
+	uint32_t cluster_begin, uint32_t K, float* __restrict__ cb_union)
+{
+	__shared__ float s_u[8][6];
+	__shared__ int s_nan;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const float kInf = __int_as_float(0x7f800000);
+	if (threadIdx.x == 0)
+		s_nan = 0;
+	__syncthreads();
+	float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+	bool nan = false;
+	for (uint32_t k = 0; k < K; ++k)
+	{
+		const uint32_t c = lane_cluster[(static_cast<size_t>((blockIdx.x * 8 + warp) * K + k) << 5) + lane];
+		if (c == kSkip)
+			continue;
+		const float4* a = reinterpret_cast<const float4*>(aabbs + cluster_begin + c);
+		const float4 mn = a[0], mx = a[1];
+		nan = nan || !(mn.x == mn.x && mn.y == mn.y && mn.z == mn.z && mx.x == mx.x && mx.y == mx.y && mx.z == mx.z);
+		lo[0] = fminf(lo[0], mn.x), lo[1] = fminf(lo[1], mn.y), lo[2] = fminf(lo[2], mn.z);
+		hi[0] = fmaxf(hi[0], mx.x), hi[1] = fmaxf(hi[1], mx.y), hi[2] = fmaxf(hi[2], mx.z);
+	}
+	if (__any_sync(0xffffffffu, nan) && lane == 0)
+		s_nan = 1;
+#pragma unroll
+	for (int i = 0; i < 3; ++i)
+	{
+		lo[i] = warp_min_f(lo[i]);
+		hi[i] = warp_max_f(hi[i]);
+	}
+	if (lane == 0)
+	{
+		s_u[warp][0] = lo[0], s_u[warp][1] = lo[1], s_u[warp][2] = lo[2];
+		s_u[warp][3] = hi[0], s_u[warp][4] = hi[1], s_u[warp][5] = hi[2];
+	}
+	__syncthreads();
+	if (threadIdx.x < 3)
+	{
+		float l = kInf, h = -kInf;
+		for (int w = 0; w < 8; ++w)
+		{
+			l = fminf(l, s_u[w][threadIdx.x]);
+			h = fmaxf(h, s_u[w][3 + threadIdx.x]);
+		}
+		float* u = cb_union + static_cast<size_t>(blockIdx.x) * 8;
+		u[threadIdx.x] = s_nan ? -kInf : l;
+		u[4 + threadIdx.x] = s_nan ? kInf : h;
+		if (threadIdx.x == 0)
+			u[3] = u[7] = 0.0f;
+	}
+}
+
+// ======================================================================================================
+// level 0: grid = (ceil(ncb / 8), tiles).  The tile is staged once per CTA by a TMA bulk copy; warp w tests
+// all of it against group cbg * 8 + w and appends survivors to the (group, tile) slot in light order.
+// ======================================================================================================
+__global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParams p)
+{
+	__shared__ __align__(128) unsigned char s_tile[kTileBytes];
+	__shared__ __align__(8) uint64_t bar;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t tile_id = blockIdx.y, cb = blockIdx.x * kBinWarps + warp;
+	grid_dep_launch();
+	if (threadIdx.x == 0)
+	{
+		mbar_init(&bar, 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	grid_dep_wait(); // the tile is written by the transform kernel of this frame
+	if (threadIdx.x == 0)
+	{
+		mbar_arrive_expect_tx(&bar, kTileBytes);
+		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
+	}
+	float lo[3] = {0.0f, 0.0f, 0.0f}, hi[3] = {0.0f, 0.0f, 0.0f};
+	if (cb < p.ncb)
+	{
+		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
+		const float4 a = __ldg(u), b = __ldg(u + 1);
+		lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
+		hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
+	}
+	mbar_wait(&bar, 0);
+	if (cb >= p.ncb)
+		return;
+	const float4* tile = reinterpret_cast<const float4*>(s_tile);
+	const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+	float4* const rec = p.bin_rec + slot;
+	uint16_t* const idx = p.bin_idx + slot;
+	const uint32_t lt = lanemask_lt();
+	uint32_t cnt = 0;
+#pragma unroll 4
+	for (uint32_t g = 0; g < kTileGroups; ++g)
+	{
+		const float4 a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+		bool h0, h1;
+		sphere_box_hit2(a, b, lo, hi, h0, h1);
+		const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+		if ((m0 | m1) == 0)
+			continue;
+		const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+		if (h0 && d0 < kBinCap)
+		{
+			rec[d0] = make_float4(a.x, a.z, b.x, b.z);
+			idx[d0] = static_cast<uint16_t>(g * 64 + lane);
+		}
+		if (h1 && d1 < kBinCap)
+		{
+			rec[d1] = make_float4(a.y, a.w, b.y, b.w);
+			idx[d1] = static_cast<uint16_t>(g * 64 + 32 + lane);
+		}
+		cnt += __popc(m0) + __popc(m1);
+	}
+	if (lane == 0)
+	{
+		p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
+		atomicAdd(&p.stats->prefilter_tests, static_cast<unsigned long long>(kTileLights));
+	}
+}
+
+// ======================================================================================================
+// levels 1 + 2, count pass (WRITE = false) and write pass (WRITE = true).
+// grid = segments x (ncb * 8 / kMainWarps) CTAs of kMainWarps independent warp programs; warp program
+// `unit` owns blocks unit * K .. unit * K + K - 1 (lane = cluster) and belongs to group unit / 8.
+// ======================================================================================================
+template <int K, bool WRITE>
+__global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
+{
+	__shared__ __align__(16) float4 s_rec[kMainWarps][64];
+	__shared__ uint16_t s_idx[kMainWarps][64];
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t seg = p.seg_begin + blockIdx.y;
+	const uint32_t unit = blockIdx.x * kMainWarps + warp;
+	const uint32_t cb = unit >> 3;
+	const uint32_t t_begin = seg * p.tiles_per_seg;
+	const uint32_t t_end = min(t_begin + p.tiles_per_seg, p.tiles_total);
+	const uint32_t ntiles = t_end - t_begin;
+	grid_dep_launch();
+	grid_dep_wait();
+	unsigned long long t_start = 0;
+	if (p.trace && threadIdx.x == 0)
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+
+	// ---- this lane's K clusters (one per block) -------------------------------------------------------
+	const float kInf = __int_as_float(0x7f800000);
+	float lo[K][3], hi[K][3];
+	uint32_t cidx[K];    // cluster index inside the shard, kSkip = no cluster on this lane
+	uint32_t cnt[K];     // pass 1: hits counted in this segment; pass 2: entries written
+	uint32_t limit[K];   // pass 1: hits still missing before the cap; pass 2: entries this lane owns
+	uint32_t wbase[K];   // pass 2: first output slot
+	bool active[K];
+	const uint32_t chunk = hier_chunk_of(seg);
+	const uint32_t index_base = (WRITE && p.index_base) ? *p.index_base : 0u;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		cidx[k] = __ldg(&p.lane_cluster[(static_cast<size_t>(unit * K + k) << 5) + lane]);
+		const bool valid = cidx[k] != kSkip;
+		cnt[k] = 0;
+		limit[k] = 0;
+		wbase[k] = 0;
+		active[k] = false;
+		lo[k][0] = lo[k][1] = lo[k][2] = kInf;
+		hi[k][0] = hi[k][1] = hi[k][2] = -kInf;
+		if (valid)
+		{
+			// every load below is independent of the others: one memory round trip for the whole prologue
+			const float4* a = reinterpret_cast<const float4*>(p.aabbs + p.cluster_begin + cidx[k]);
+			const float4 mn = __ldg(a), mx = __ldg(a + 1);
+			if (WRITE)
+			{
+				const size_t sc = static_cast<size_t>(seg) * p.cluster_count + cidx[k];
+				const uint32_t n = p.seg_counts[sc], pfx = p.seg_prefix[sc];
+				const uint32_t off = p.offsets[cidx[k]] + index_base;
+				if (seg == 0) // LightCulling.comp:86-87
+					*reinterpret_cast<uint2*>(p.cells + p.cluster_begin + cidx[k]) = make_uint2(off, p.counts[cidx[k]]);
+				if (n != 0 && pfx != kSkip && pfx < p.cap)
+				{
+					active[k] = true;
+					limit[k] = min(n, p.cap - pfx);
+					wbase[k] = off + pfx;
+				}
+			}
+			else
+			{
+				uint32_t prior = 0;
+#pragma unroll
+				for (uint32_t c = 0; c < kHMaxChunks; ++c)
+					if (c < chunk)
+						prior += __ldcg(&p.cum[static_cast<size_t>(c) * p.cluster_count + cidx[k]]);
+				if (prior < p.cap)
+				{
+					active[k] = true;
+					limit[k] = p.cap - prior;
+				}
+			}
+			if (active[k])
+			{
+				lo[k][0] = mn.x, lo[k][1] = mn.y, lo[k][2] = mn.z;
+				hi[k][0] = mx.x, hi[k][1] = mx.y, hi[k][2] = mx.z;
+			}
+		}
+	}
+	if (WRITE && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && p.frame_total)
+		*p.frame_total = index_base + *p.shard_total; // globalIndex after the frame (LightCulling.comp:21,79)
+
+	// ---- block union boxes (level 1) over the lanes that still want hits ------------------------------
+	float ulo[K][3], uhi[K][3];
+	uint32_t alive[K]; // lanes of the block that still want hits
+	bool blk_nan[K];   // the block holds a NaN box: its union stays 'pass everything'
+	bool warp_done = true;
+#pragma unroll
+	for (int k = 0; k < K; ++k)
+	{
+		alive[k] = __ballot_sync(0xffffffffu, active[k]);
+		// a NaN bound makes every light hit that cluster (both shader comparisons are false): pass everything
+		const bool nan = active[k] && !(lo[k][0] == lo[k][0] && lo[k][1] == lo[k][1] && lo[k][2] == lo[k][2] &&
+			hi[k][0] == hi[k][0] && hi[k][1] == hi[k][1] && hi[k][2] == hi[k][2]);
+		blk_nan[k] = __any_sync(0xffffffffu, nan);
+#pragma unroll
+		for (int i = 0; i < 3; ++i)
+		{
+			ulo[k][i] = blk_nan[k] ? -kInf : warp_min_f(lo[k][i]);
+			uhi[k][i] = blk_nan[k] ? kInf : warp_max_f(hi[k][i]);
+		}
+		warp_done = warp_done && alive[k] == 0;
+	}
+
+	unsigned long long n_l1 = 0, n_l2 = 0; // warp-uniform test counters (lane tests)
+	const size_t desc0 = static_cast<size_t>(cb) * p.tiles_cap + t_begin;
+	float4* const my_rec = s_rec[warp];
+	uint16_t* const my_idx = s_idx[warp];
+	for (uint32_t tb = 0; tb < ntiles && !warp_done; tb += 32)
+	{
+		// survivor counts of the next 32 tiles in one coalesced load
+		const uint32_t my_cnt = tb + lane < ntiles ? __ldg(&p.bin_count[desc0 + tb + lane]) : 0u;
+		const uint32_t tn = min(32u, ntiles - tb);
+		for (uint32_t ti = 0; ti < tn && !warp_done; ++ti)
+		{
+			const uint32_t n0 = __shfl_sync(0xffffffffu, my_cnt, ti);
+			if (n0 == 0)
+				continue;
+			const uint32_t tile_id = t_begin + tb + ti;
+			const uint32_t tile_base = tile_id * kTileLights;
+			// a slot that overflowed means the group's filter is not selective for this tile: read the raw tile
+			const bool raw = n0 > kBinCap;
+			const uint32_t nb = raw ? kTileGroups : (n0 + 63) / 64;
+			const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16);
+			const size_t slot = (desc0 + tb + ti) * kBinCap;
+			for (uint32_t bi = 0; bi < nb && !warp_done; ++bi)
+			{
+				// ---- a batch of up to 64 lights in ascending order: records r0 (lane) and r1 (32 + lane) ----
+				float4 r0, r1;
+				uint32_t id0, id1;
+				if (raw)
+				{
+					const float4 a = __ldg(lv + bi * 64 + lane), b = __ldg(lv + bi * 64 + 32 + lane);
+					r0 = make_float4(a.x, a.z, b.x, b.z);
+					r1 = make_float4(a.y, a.w, b.y, b.w);
+					id0 = bi * 64 + lane;
+					id1 = id0 + 32;
+				}
+				else
+				{
+					const uint32_t i0 = bi * 64 + lane, i1 = i0 + 32;
+					r0 = r1 = make_float4(0.0f, 0.0f, 0.0f, -1.0f); // r2 = -1: never a hit
+					id0 = id1 = 0;
+					if (i0 < n0)
+					{
+						r0 = __ldg(p.bin_rec + slot + i0);
+						id0 = __ldg(p.bin_idx + slot + i0);
+					}
+					if (i1 < n0)
+					{
+						r1 = __ldg(p.bin_rec + slot + i1);
+						id1 = __ldg(p.bin_idx + slot + i1);
+					}
+				}
+				// ---- level 1: lane = light, against the union box of each block -----------------------------
+				uint32_t mlo[K], mhi[K];
+				uint32_t any = 0;
+#pragma unroll
+				for (int k = 0; k < K; ++k)
+				{
+					mlo[k] = mhi[k] = 0;
+					if (alive[k])
+					{
+						mlo[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r0.x, r0.y, r0.z, r0.w, ulo[k], uhi[k]));
+						mhi[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r1.x, r1.y, r1.z, r1.w, ulo[k], uhi[k]));
+						n_l1 += 64;
+						any |= mlo[k] | mhi[k];
+					}
+				}
+				if (any == 0)
+					continue;
+				__syncwarp(); // the previous batch's broadcasts are done
+				my_rec[lane] = r0;
+				my_rec[32 + lane] = r1;
+				my_idx[lane] = static_cast<uint16_t>(id0);
+				my_idx[32 + lane] = static_cast<uint16_t>(id1);
+				__syncwarp();
+				// ---- level 2: lane = cluster, candidates broadcast from the slab -----------------------------
+				warp_done = true;
+#pragma unroll
+				for (int k = 0; k < K; ++k)
+				{
+					if (alive[k] == 0)
+						continue;
+					n_l2 += 32u * (__popc(mlo[k]) + __popc(mhi[k]));
+#pragma unroll
+					for (uint32_t half = 0; half < 2; ++half)
+					{
+						uint32_t m = half ? mhi[k] : mlo[k];
+						// kCand candidates per trip while the mask holds that many: a trip is latency-bound (LDS -> 6-deep
+						// FP chain), so independent chains are free; the remainder goes one by one
+						while (__popc(m) >= static_cast<int>(kCand))
+						{
+							uint32_t j[kCand];
+							float4 c[kCand];
+#pragma unroll
+							for (uint32_t q = 0; q < kCand; ++q)
+							{
+								j[q] = half * 32 + __ffs(m) - 1;
+								m &= m - 1;
+								c[q] = my_rec[j[q]]; // broadcast
+							}
+#pragma unroll
+							for (uint32_t q = 0; q < kCand; ++q)
+							{
+								const bool hit = sphere_box_hit(c[q].x, c[q].y, c[q].z, c[q].w, lo[k], hi[k]) && active[k];
+								if (WRITE)
+								{
+									if (hit && cnt[k] < limit[k])
+									{
+										p.indices[wbase[k] + cnt[k]] = tile_base + my_idx[j[q]];
+										++cnt[k];
+									}
+								}
+								else
+									cnt[k] += hit ? 1u : 0u;
+							}
+						}
+						while (m)
+						{
+							const uint32_t j = half * 32 + __ffs(m) - 1;
+							m &= m - 1;
+							const float4 c = my_rec[j]; // broadcast
+							const bool hit = sphere_box_hit(c.x, c.y, c.z, c.w, lo[k], hi[k]) && active[k];
+							if (WRITE)
+							{
+								if (hit && cnt[k] < limit[k])
+								{
+									p.indices[wbase[k] + cnt[k]] = tile_base + my_idx[j];
+									++cnt[k];
+								}
+							}
+							else
+								cnt[k] += hit ? 1u : 0u;
+						}
+					}
+					// early exit per lane: a cluster that holds its quota leaves the block's union box, so the remaining
+					// lanes see fewer candidates; a block with no lane left is finished
+					const uint32_t now_alive = __ballot_sync(0xffffffffu, active[k] && cnt[k] < limit[k]);
+					if (now_alive != alive[k])
+					{
+						alive[k] = now_alive;
+						active[k] = (now_alive >> lane) & 1u;
+						if (now_alive && !blk_nan[k])
+						{
+#pragma unroll
+							for (int a = 0; a < 3; ++a)
+							{
+								ulo[k][a] = warp_min_f(active[k] ? lo[k][a] : kInf);
+								uhi[k][a] = warp_max_f(active[k] ? hi[k][a] : -kInf);
+							}
+						}
+					}
+					warp_done = warp_done && alive[k] == 0;
+				}
+			}
+		}
+	}
+	if (!WRITE)
+	{
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+			if (cidx[k] != kSkip)
+			{
+				p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = cnt[k];
+				if (cnt[k])
+					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
+			}
+	}
+	if (p.trace)
+	{
+		// debug only (HVCF_HIER_TRACE): per CTA {start ns, end ns, SM id, level-2 lane tests of warp 0}
+		__syncthreads();
+		if (threadIdx.x == 0)
+		{
+			unsigned long long t_end;
+			uint32_t smid;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+			asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+			const size_t cta = static_cast<size_t>(blockIdx.y) * gridDim.x + blockIdx.x, ctas = static_cast<size_t>(gridDim.x) * gridDim.y;
+			unsigned long long* t = p.trace + 4ull * ((WRITE ? ctas : 0) + cta);
+			t[0] = t_start, t[1] = t_end, t[2] = smid, t[3] = n_l2;
+		}
+	}
+	if (lane == 0 && (n_l1 | n_l2))
+	{
+		atomicAdd(&p.stats->prefilter_tests, n_l1);
+		atomicAdd(&p.stats->executed_tests, n_l2);
+	}
+}
+
+// ======================================================================================================
+// launchers
+// ======================================================================================================
+static cudaLaunchAttribute pdl_attr()
+{
+	cudaLaunchAttribute a{};
+	a.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	a.val.programmaticStreamSerializationAllowed = 1;
+	return a;
+}
+
+cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
+	float* cb_union, cudaStream_t stream)
+{
+	if (ncb == 0)
+		return cudaSuccess;
+	hier_unions_kernel<<<ncb, 256, 0, stream>>>(lane_cluster, aabbs, cluster_begin, K, cb_union);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream)
+{
+	if (p.ncb == 0 || tiles == 0)
+		return cudaSuccess;
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3((p.ncb + kBinWarps - 1) / kBinWarps, tiles, 1);
+	cfg.blockDim = dim3(kBinWarps * 32, 1, 1);
+	cfg.stream = stream;
+	cudaLaunchAttribute attr = pdl_attr();
+	cfg.attrs = &attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
+}
+
+template <int K, bool WRITE>
+static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
+{
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3(p.ncb * 8 / kMainWarps, p.seg_end - p.seg_begin, 1); // x fastest: all units of a segment, then the next segment
+	cfg.blockDim = dim3(kMainWarps * 32, 1, 1);
+	cfg.stream = stream;
+	cudaLaunchAttribute attr = pdl_attr();
+	cfg.attrs = &attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE>, p);
+}
+
+cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
+{
+	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
+		return cudaSuccess;
+	switch (K * 2 + (write ? 1 : 0))
+	{
+	case 2: return launch_hier2_t<1, false>(p, stream);
+	case 3: return launch_hier2_t<1, true>(p, stream);
+	case 4: return launch_hier2_t<2, false>(p, stream);
+	case 5: return launch_hier2_t<2, true>(p, stream);
+	case 8: return launch_hier2_t<4, false>(p, stream);
+	case 9: return launch_hier2_t<4, true>(p, stream);
+	default: return cudaErrorInvalidValue;
+	}
+}
+
+} // namespace hvcf

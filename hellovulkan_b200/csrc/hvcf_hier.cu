@@ -28,7 +28,7 @@
 // towards the true value), and a lower bound >= cap proves that the first `cap` entries lie before this
 // segment -- so knowledge only ever removes work that cannot matter, and the result does not depend on
 // scheduling.  No flags, no fences.
-#include "hvcf_kernels.cuh"
+#include "hvcf_hier.cuh"
 
 #include <vector>
 
@@ -38,9 +38,6 @@ namespace hvcf
 constexpr uint32_t kHWarps = 8;
 constexpr uint32_t kHStages = 2;
 constexpr uint32_t kHGroupsPerWarp = kTileGroups / kHWarps; // 2
-constexpr uint32_t kSkip = 0xffffffffu;
-constexpr uint32_t kCand = 4;      // level-2 candidates in flight per trip
-constexpr uint32_t kHMaxChunks = 8; // 256 segments at most (hier_num_chunks(256) == 7)
 static_assert(kTileGroups % kHWarps == 0, "level 0 splits a tile's groups evenly over the warps");
 
 // dynamic shared memory: light tile ring | survivor records (2 buffers) | survivor local indices (2 buffers)
@@ -49,63 +46,6 @@ constexpr uint32_t kHSmemS0f = 2 * kTileLights * 16;
 constexpr uint32_t kHSmemS0i = 2 * kTileLights * 2;
 constexpr uint32_t kHSmemBytes = kHSmemRing + kHSmemS0f + kHSmemS0i;
 
-__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p)
-{
-	unsigned long long v;
-	asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-	return v;
-}
-__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v)
-{
-	asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-// order-preserving float <-> int map, for redux.sync min/max over a warp
-__device__ __forceinline__ int float_to_ordered(float f)
-{
-	const int i = __float_as_int(f);
-	return i ^ ((i >> 31) & 0x7fffffff);
-}
-__device__ __forceinline__ float ordered_to_float(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
-__device__ __forceinline__ float warp_min_f(float v) { return ordered_to_float(__reduce_min_sync(0xffffffffu, float_to_ordered(v))); }
-__device__ __forceinline__ float warp_max_f(float v) { return ordered_to_float(__reduce_max_sync(0xffffffffu, float_to_ordered(v))); }
-
-// LightCulling.comp:26-47,56 on one light and one box; see cull_kernel for why max3(lo-v, v-hi, 0) is exact.
-__device__ __forceinline__ bool sphere_box_hit(float x, float y, float z, float r2, const float lo[3], const float hi[3])
-{
-	const float dx = fmaxf(fmaxf(__fsub_rn(lo[0], x), __fsub_rn(x, hi[0])), 0.0f);
-	const float dy = fmaxf(fmaxf(__fsub_rn(lo[1], y), __fsub_rn(y, hi[1])), 0.0f);
-	const float dz = fmaxf(fmaxf(__fsub_rn(lo[2], z), __fsub_rn(z, hi[2])), 0.0f);
-	const float s = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-	return s < r2;
-}
-
-// the same test on the lane's light PAIR of the packed culling layout (FADD2 / FMUL2; sums stay scalar so
-// that ptxas cannot contract them into FFMA2)
-__device__ __forceinline__ void sphere_box_hit2(const float4& a, const float4& b, const float lo[3], const float hi[3], bool& h0,
-	bool& h1)
-{
-	const f32x2 X = pack2(a.x, a.y), Y = pack2(a.z, a.w), Z = pack2(b.x, b.y);
-	float l0, l1, u0, u1;
-	unpack2(sub2(pack2(lo[0], lo[0]), X), l0, l1);
-	unpack2(sub2(X, pack2(hi[0], hi[0])), u0, u1);
-	const f32x2 dx = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
-	unpack2(sub2(pack2(lo[1], lo[1]), Y), l0, l1);
-	unpack2(sub2(Y, pack2(hi[1], hi[1])), u0, u1);
-	const f32x2 dy = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
-	unpack2(sub2(pack2(lo[2], lo[2]), Z), l0, l1);
-	unpack2(sub2(Z, pack2(hi[2], hi[2])), u0, u1);
-	const f32x2 dz = pack2(fmaxf(fmaxf(l0, u0), 0.0f), fmaxf(fmaxf(l1, u1), 0.0f));
-	float sx0, sx1, sy0, sy1, sz0, sz1;
-	unpack2(mul2(dx, dx), sx0, sx1);
-	unpack2(mul2(dy, dy), sy0, sy1);
-	unpack2(mul2(dz, dz), sz0, sz1);
-	h0 = __fadd_rn(__fadd_rn(sx0, sy0), sz0) < b.z;
-	h1 = __fadd_rn(__fadd_rn(sx1, sy1), sz1) < b.w;
-}
-
-// segment -> chunk: chunk 0 = segments [0,4), chunk c >= 1 = segments [2^(c+1), 2^(c+2))
-__device__ __forceinline__ uint32_t hier_chunk_of(uint32_t seg) { return seg < 4 ? 0u : (30u - __clz(seg)); }
 template <int K, bool WRITE>
 __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 {
@@ -585,9 +525,9 @@ void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs,
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs)
 {
-	// about 48 CTAs per SM over the whole launch (measured on B200: short segments win -- more CTAs in flight hide the
+	// about 96 eight-unit groups per SM over the whole launch (measured on B200: short segments win -- more CTAs in flight hide the
 	// per-tile barrier latency and earlier segments publish their counts sooner); segments are whole tiles
-	const uint64_t target = 148ull * 48ull;
+	const uint64_t target = 148ull * 96ull;
 	const uint64_t tps = (static_cast<uint64_t>(tiles_total) * h.ncb) / target;
 	uint32_t t = 1;
 	while (static_cast<uint64_t>(t) * 2 <= tps)

@@ -89,6 +89,28 @@ struct HierParams
 	uint32_t* frame_total;         // globalIndexCountBuffers_[frame] or NULL
 	DeviceStats* stats;
 	unsigned long long* trace;     // debug: 4 words per CTA of pass 1, then of pass 2 (or NULL)
+	// second generation (hvcf_bin.cu): survivors of level 0, one slot per (group, tile)
+	const uint32_t* bin_count;     // [ncb][tiles_cap] lights that passed the group's union box (may exceed kBinCap)
+	const float4* bin_rec;         // [ncb][tiles_cap][kBinCap] {x, y, z, r*r} in light order
+	const uint16_t* bin_idx;       // [ncb][tiles_cap][kBinCap] light index inside the tile
+	uint32_t tiles_cap;
+};
+
+#ifndef HVCF_BIN_CAP
+#define HVCF_BIN_CAP 512
+#endif
+constexpr uint32_t kBinCap = HVCF_BIN_CAP;  // records per (group, tile) slot; more survivors -> consumers read the raw tile
+
+struct BinParams
+{
+	const float4* lights_view;
+	const float* cb_union;         // [ncb][8]
+	uint32_t ncb;
+	uint32_t tiles_cap;
+	uint32_t* bin_count;
+	float4* bin_rec;
+	uint16_t* bin_idx;
+	DeviceStats* stats;
 };
 
 struct FinalizeParams
@@ -113,5 +135,9 @@ void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs
 uint32_t hier_num_chunks(uint32_t num_segs);
 cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream);
 cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream);
+cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
+	float* cb_union, cudaStream_t stream);
+cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream);
+cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
 } // namespace hvcf

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libhvcf.so")
+LIB_PATH = os.environ.get("HVCF_LIB") or os.path.join(_HERE, "lib", "libhvcf.so")  # HVCF_LIB: experiment builds only
 
 LIGHT_DT = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("radius", "<f4"), ("pad_", "<f4", 3)])
 AABB_DT = np.dtype([("min_point", "<f4", 4), ("max_point", "<f4", 4)])

@@ -24,7 +24,7 @@ for name in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["A65k"]):
                 print(f"   decile {d}: start {st[sel].min()/1e3:6.1f}-{st[sel].max()/1e3:6.1f} us  dur mean {dur[sel].mean()/1e3:6.2f} max {dur[sel].max()/1e3:6.2f}  l2tests(w0) mean {t[sel,3].mean():8.0f}")
             ncb = ncta // max(1, (ncta // 18 if name == 'A65k' else ncta // 60))
             # by cb (cluster group)
-            per = 18 if name == "A65k" else 60
+            per = (18 if name == "A65k" else 60) * (1 if os.environ.get("HVCF_HIER_V1") else 2)
             cb = np.arange(ncta) % per
             print("   by cb (mean dur us):", " ".join(f"{dur[cb==c].mean()/1e3:.1f}" for c in range(per)))
             conc = [(np.sum((st <= x) & (en > x))) for x in np.linspace(0, en.max(), 12)[1:-1]]
