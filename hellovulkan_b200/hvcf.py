@@ -16,7 +16,9 @@ LIB_PATH = os.environ.get("HVCF_LIB") or os.path.join(_HERE, "lib", "libhvcf.so"
 LIGHT_DT = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("radius", "<f4"), ("pad_", "<f4", 3)])
 AABB_DT = np.dtype([("min_point", "<f4", 4), ("max_point", "<f4", 4)])
 CELL_DT = np.dtype([("offset", "<u4"), ("count", "<u4")])
+CMD_DT = np.dtype([("vertex_count", "<u4"), ("instance_count", "<u4"), ("first_vertex", "<u4"), ("first_instance", "<u4")])
 UBO_BYTES = 176
+FRUSTUM_BYTES = 224
 
 HVCF_OK = 0
 MODE_AUTO = 0
@@ -45,6 +47,24 @@ class Buffers(ctypes.Structure):
                 ("cluster_begin", ctypes.c_uint32), ("cluster_end", ctypes.c_uint32)]
 
 
+class GBuffer(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_uint32), ("height", ctypes.c_uint32), ("frag_depth", ctypes.c_void_p),
+                ("world_pos", ctypes.c_void_p), ("normal_rough", ctypes.c_void_p), ("albedo_metal", ctypes.c_void_p)]
+
+
+class PushConstPBR(ctypes.Structure):
+    """PushConstPBR defaults of Header/PushConstants.h:24-31."""
+    _fields_ = [("light_intensity", ctypes.c_float), ("base_reflectivity", ctypes.c_float), ("max_reflection_lod", ctypes.c_float),
+                ("light_falloff", ctypes.c_float), ("albedo_multipler", ctypes.c_float)]
+
+    def __init__(self, light_intensity=1.0, base_reflectivity=0.04, max_reflection_lod=4.0, light_falloff=1.0, albedo_multipler=0.0):
+        super().__init__(light_intensity, base_reflectivity, max_reflection_lod, light_falloff, albedo_multipler)
+
+    def as_array(self):
+        return np.array([self.light_intensity, self.base_reflectivity, self.max_reflection_lod, self.light_falloff,
+                         self.albedo_multipler], np.float32)
+
+
 class Stats(ctypes.Structure):
     _fields_ = [("nominal_tests", ctypes.c_uint64), ("executed_tests", ctypes.c_uint64), ("prefilter_tests", ctypes.c_uint64),
                 ("total_indices", ctypes.c_uint32), ("overflow_clusters", ctypes.c_uint32), ("kernel_launches", ctypes.c_uint32),
@@ -59,6 +79,7 @@ EXPORTS = [
     "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
+    "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
 _lib = None
@@ -108,6 +129,11 @@ def load():
     lib.hvcf_debug_trace.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
     lib.hvcf_get_timing.argtypes = [vp, u32, f3, f3]
     lib.hvcf_measure_fp32_issue_rate.argtypes = [i32, ctypes.POINTER(ctypes.c_double)]
+    lib.hvcf_shade.argtypes = [vp, u32, ctypes.POINTER(GBuffer), ctypes.POINTER(PushConstPBR), f3, vp, vp, vp]
+    lib.hvcf_host_init_gbuffer.argtypes = [u32, f3, f3, u32, u32, vp, vp, vp, vp]
+    lib.hvcf_frustum_cull.argtypes = [i32, vp, vp, u32, vp, vp]
+    lib.hvcf_host_frustum_ubo.argtypes = [f3, f3, ctypes.c_float, ctypes.c_float, vp]
+    lib.hvcf_host_init_boxes.argtypes = [u32, u32, ctypes.c_float, vp]
     _lib = lib
     return lib
 
@@ -144,6 +170,98 @@ def host_init_lights(count, seed=12345, out=None):
     assert out.dtype == LIGHT_DT and len(out) >= count
     _check(lib.hvcf_host_init_lights(seed, count, _ptr(out)))
     return out
+
+
+def host_init_gbuffer(width, height, pos=REF_CAMERA_POS, target=REF_CAMERA_TARGET, seed=7):
+    """Synthetic G-buffer (host arrays): dict of frag_depth [P], world_pos / normal_rough / albedo_metal [P,4]."""
+    lib = load()
+    P = width * height
+    g = {"width": width, "height": height, "frag_depth": np.zeros(P, np.float32), "world_pos": np.zeros((P, 4), np.float32),
+         "normal_rough": np.zeros((P, 4), np.float32), "albedo_metal": np.zeros((P, 4), np.float32)}
+    p = (ctypes.c_float * 3)(*[float(v) for v in pos])
+    t = (ctypes.c_float * 3)(*[float(v) for v in target])
+    _check(lib.hvcf_host_init_gbuffer(seed, p, t, width, height, _ptr(g["frag_depth"]), _ptr(g["world_pos"]),
+                                      _ptr(g["normal_rough"]), _ptr(g["albedo_metal"])))
+    return g
+
+
+def host_frustum_ubo(screen, pos=REF_CAMERA_POS, target=REF_CAMERA_TARGET):
+    """Camera::GetFrustumUBO on the host; returns 224 bytes as uint8."""
+    out = np.zeros(FRUSTUM_BYTES, np.uint8)
+    p = (ctypes.c_float * 3)(*[float(v) for v in pos])
+    t = (ctypes.c_float * 3)(*[float(v) for v in target])
+    _check(load().hvcf_host_frustum_ubo(p, t, float(screen[0]), float(screen[1]), _ptr(out)))
+    return out
+
+
+def host_init_boxes(count, extent=30.0, seed=4242):
+    out = np.zeros(count, AABB_DT)
+    _check(load().hvcf_host_init_boxes(seed, count, float(extent), _ptr(out)))
+    return out
+
+
+class DeviceBuffer:
+    """hvcf_device_alloc'd device memory (the VulkanBuffer stand-in of include/hv/Context.h)."""
+
+    def __init__(self, nbytes, device=-1):
+        self.lib = load()
+        self.ptr = ctypes.c_void_p()
+        self.nbytes = int(nbytes)
+        _check(self.lib.hvcf_device_alloc(device, max(self.nbytes, 16), ctypes.byref(self.ptr)))
+
+    @classmethod
+    def from_array(cls, arr, device=-1, stream=None):
+        arr = np.ascontiguousarray(arr)
+        b = cls(arr.nbytes, device)
+        b.upload(arr, stream=stream)
+        return b
+
+    def upload(self, arr, offset=0, stream=None):
+        arr = np.ascontiguousarray(arr)
+        _check(self.lib.hvcf_device_upload(self.ptr, offset, _ptr(arr), arr.nbytes, stream))
+
+    def download(self, dtype, count=None, offset=0, stream=None):
+        dt = np.dtype(dtype)
+        n = (self.nbytes - offset) // dt.itemsize if count is None else int(count)
+        out = np.zeros(n, dt)
+        _check(self.lib.hvcf_device_download(_ptr(out), self.ptr, offset, out.nbytes, stream))
+        return out
+
+    def close(self):
+        if self.ptr:
+            self.lib.hvcf_device_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceGBuffer:
+    """A host G-buffer (host_init_gbuffer) uploaded once; owns its device arrays and the two output buffers."""
+
+    def __init__(self, g, device=-1, want_cluster_index=True):
+        self.width, self.height = g["width"], g["height"]
+        P = self.width * self.height
+        self.bufs = {k: DeviceBuffer.from_array(g[k], device) for k in ("frag_depth", "world_pos", "normal_rough", "albedo_metal")}
+        self.out_color = DeviceBuffer(16 * P, device)
+        self.out_cluster = DeviceBuffer(4 * P, device) if want_cluster_index else None
+        self.desc = GBuffer(self.width, self.height, self.bufs["frag_depth"].ptr, self.bufs["world_pos"].ptr,
+                            self.bufs["normal_rough"].ptr, self.bufs["albedo_metal"].ptr)
+
+    def close(self):
+        for b in list(self.bufs.values()) + [self.out_color, self.out_cluster]:
+            if b is not None:
+                b.close()
+
+
+def frustum_cull(frustum, boxes_ptr, count, commands_ptr, device=-1, stream=None):
+    """FrustumCulling.comp over device boxes -> instance_count of device commands; frustum: 224 host bytes."""
+    frustum = np.ascontiguousarray(frustum).view(np.uint8)
+    assert frustum.nbytes == FRUSTUM_BYTES
+    _check(load().hvcf_frustum_cull(device, _ptr(frustum), boxes_ptr, count, commands_ptr, stream))
 
 
 def measure_fp32_issue_rate(device=-1):
@@ -237,6 +355,13 @@ class Context:
 
     def cull_finish(self, frame=0, index_base_ptr=None, stream=None):
         _check(self.lib.hvcf_cull_finish(self.handle, frame, ctypes.c_void_p(index_base_ptr) if index_base_ptr else None, stream))
+
+    def shade(self, frame, dg, pc=None, camera_position=REF_CAMERA_POS, stream=None):
+        """hvcf_shade over a DeviceGBuffer; results land in dg.out_color / dg.out_cluster."""
+        pc = pc or PushConstPBR()
+        cam = (ctypes.c_float * 3)(*[float(v) for v in camera_position])
+        _check(self.lib.hvcf_shade(self.handle, frame, ctypes.byref(dg.desc), ctypes.byref(pc), cam, dg.out_color.ptr,
+                                   dg.out_cluster.ptr if dg.out_cluster is not None else None, stream))
 
     def shard_total_ptr(self):
         p = ctypes.c_void_p()

@@ -1,5 +1,5 @@
 // hv/Camera.h -- headless restatement of the reference camera's ClusterForwardUBO producer
-// (HelloVulkan/Header/Camera.h, Source/Camera.cpp:32-39,81-111,113-139,178-197).  Host CPU code, as in
+// (HelloVulkan/Header/Camera.h, Source/Camera.cpp:32-39,81-111,113-139,178-234).  Host CPU code, as in
 // the reference.  Same method names; window/input handling is left out.  The arithmetic follows
 // glm 0.9.9.9 operation by operation (perspectiveRH_ZO, inverse, lookAtRH) so the UBO bytes are the
 // ones the reference feeds its shaders; build with -ffp-contract=off.
@@ -73,6 +73,25 @@ namespace detail
 			for (int r = 0; r < 4; ++r)
 				inv[c][r] = inv[c][r] * oneOverDet;
 		return inv;
+	}
+
+	// glm mat4 * mat4: Result[c] = ((A0*b0 + A1*b1) + A2*b2) + A3*b3 (left to right)
+	inline mat4 mul(const mat4& a, const mat4& b)
+	{
+		mat4 r{};
+		for (int c = 0; c < 4; ++c)
+			for (int k = 0; k < 4; ++k)
+				r[c][k] = ((a[0][k] * b[c][0] + a[1][k] * b[c][1]) + a[2][k] * b[c][2]) + a[3][k] * b[c][3];
+		return r;
+	}
+
+	// glm mat4 * vec4: (m0*x + m1*y) + (m2*z + m3*w)
+	inline vec4 mul(const mat4& m, const vec4& v)
+	{
+		vec4 r{};
+		for (int k = 0; k < 4; ++k)
+			r[k] = (m[0][k] * v.x + m[1][k] * v.y) + (m[2][k] * v.z + m[3][k] * v.w);
+		return r;
 	}
 
 	// glm::lookAt (right-handed)
@@ -168,6 +187,34 @@ public:
 		u.sliceCountY = sliceY_;
 		u.sliceCountZ = sliceZ_;
 		return u;
+	}
+
+	// Camera.cpp:199-234
+	FrustumUBO GetFrustumUBO() const
+	{
+		const hv::mat4 projView = hv::detail::mul(projectionMatrix_, viewMatrix_);
+		hv::mat4 t{}; // glm::transpose
+		for (int c = 0; c < 4; ++c)
+			for (int r = 0; r < 4; ++r)
+				t[c][r] = projView[r][c];
+		auto add4 = [](const hv::vec4& a, const hv::vec4& b) -> hv::vec4 { return { a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w }; };
+		auto sub4 = [](const hv::vec4& a, const hv::vec4& b) -> hv::vec4 { return { a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w }; };
+		FrustumUBO ubo{};
+		ubo.planes[0] = add4(t[3], t[0]); // left
+		ubo.planes[1] = sub4(t[3], t[0]); // right
+		ubo.planes[2] = add4(t[3], t[1]); // bottom
+		ubo.planes[3] = sub4(t[3], t[1]); // top
+		ubo.planes[4] = add4(t[3], t[2]); // near
+		ubo.planes[5] = sub4(t[3], t[2]); // far
+		const hv::mat4 invProjView = hv::detail::inverse(projView);
+		const hv::vec4 corners[8] = { { -1, -1, -1, 1 }, { 1, -1, -1, 1 }, { 1, 1, -1, 1 }, { -1, 1, -1, 1 },
+			{ -1, -1, 1, 1 }, { 1, -1, 1, 1 }, { 1, 1, 1, 1 }, { -1, 1, 1, 1 } };
+		for (int i = 0; i < 8; ++i)
+		{
+			const hv::vec4 q = hv::detail::mul(invProjView, corners[i]);
+			ubo.corners[i] = { q.x / q.w, q.y / q.w, q.z / q.w, q.w / q.w };
+		}
+		return ubo;
 	}
 
 private:

@@ -1,7 +1,8 @@
 // hv/Types.h -- C++ names of the reference's PODs and compile-time configs for the light-culling path.
 // Layout-identical to include/hvcf_types.h (the ABI) and to the reference structs:
 //   LightData / AABB / LightCell   HelloVulkan/Header/Resources/ResourcesLight.h:13-39
-//   ClusterForwardUBO              HelloVulkan/Header/UBOs.h:67-89
+//   ClusterForwardUBO, FrustumUBO  HelloVulkan/Header/UBOs.h:67-99
+//   PushConstPBR                   HelloVulkan/Header/PushConstants.h:24-31
 //   AppConfig / CameraConfig / ClusterForwardConfig   HelloVulkan/Header/Configs.h:8-56
 // glm is not shipped with this library; hv::vec/mat below are the minimal column-major stand-ins.
 #ifndef HV_TYPES_H
@@ -100,11 +101,39 @@ struct CameraUBO
 	alignas(4) float cameraFar;
 };
 
+// For compute-based frustum culling (HelloVulkan/Header/UBOs.h:92-99)
+struct FrustumUBO
+{
+	alignas(16) hv::vec4 planes[6];
+	alignas(16) hv::vec4 corners[8];
+};
+
+// Additional customization for PBR (HelloVulkan/Header/PushConstants.h:24-31)
+struct PushConstPBR
+{
+	float lightIntensity = 1.f;
+	float baseReflectivity = 0.04f;
+	float maxReflectionLod = 4.f;
+	float lightFalloff = 1.0f;
+	float albedoMultipler = 0.0f;
+};
+
+// VkDrawIndirectCommand as the culling shader sees it (HelloVulkan/Shaders/DrawIndirectCommand.glsl)
+struct DrawIndirectCommand
+{
+	uint32_t vertexCount;
+	uint32_t instanceCount;
+	uint32_t firstVertex;
+	uint32_t firstInstance;
+};
+
 struct UIData; // opaque here: no UI on this path
 
 static_assert(sizeof(LightData) == sizeof(hvcf_light_data) && offsetof(LightData, radius_) == offsetof(hvcf_light_data, radius));
 static_assert(sizeof(AABB) == sizeof(hvcf_aabb) && sizeof(LightCell) == sizeof(hvcf_light_cell));
 static_assert(sizeof(ClusterForwardUBO) == sizeof(hvcf_cluster_forward_ubo));
+static_assert(sizeof(FrustumUBO) == sizeof(hvcf_frustum_ubo) && sizeof(PushConstPBR) == sizeof(hvcf_push_const_pbr));
+static_assert(sizeof(DrawIndirectCommand) == sizeof(hvcf_draw_indirect_command));
 static_assert(offsetof(ClusterForwardUBO, screenSize) == 128 && offsetof(ClusterForwardUBO, sliceCountZ) == 160);
 
 #endif

@@ -196,6 +196,55 @@ HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kern
  * second: the denominator of the FP32-issue roofline; MEASURED_PEAKS.json has none. */
 HVCF_API int hvcf_measure_fp32_issue_rate(int device, double* out_lane_ops_per_second);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Consumer: the light loop of the PBR cluster-forward fragment pass as a CUDA kernel.
+ * Replaces, headless: PipelinePBRClusterForward::FillCommandBuffer (Source/Pipelines/PipelinePBRClusterForward.cpp
+ * :88-143) for the part of Shaders/ClusteredForward/Scene.frag that reads this library's outputs -- lines 55-78
+ * (gl_FragCoord -> cluster -> (count, offset)) and 103-134 (Lo = albedo*albedoMultipler + sum Radiance(light)),
+ * with Shaders/ClusteredForward/Radiance.glsl:2-57 and Shaders/PBR/PBRHeader.glsl:16-64.  What rasterisation and
+ * the material textures supply in the reference is a G-buffer in device memory here; ambient (IBL cubemaps) and
+ * emissive need textures and are out of scope.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct hvcf_gbuffer
+{
+	uint32_t width, height;        /* pixels; p = x + y * width, gl_FragCoord.xy = (x + 0.5, y + 0.5) */
+	const float* frag_depth;       /* [P]     gl_FragCoord.z in [0, 1) */
+	const float* world_pos;        /* [P][4]  worldPos.xyz (Scene.frag location 0), w ignored */
+	const float* normal_rough;     /* [P][4]  N.xyz after NormalTBN (:106), roughness (:101) */
+	const float* albedo_metal;     /* [P][4]  linear albedo.rgb (:97), metallic (:100) */
+} hvcf_gbuffer;
+
+/* out_color: [P][4] floats (Lo.rgb, 1); out_cluster_index: [P] uint32 clusterIdx (Scene.frag:73-76) or NULL.
+ * Reads ubo[frame], the light cells, the index list and the light buffer of the context (all device-resident;
+ * stream order after hvcf_cull replaces the compute->fragment barriers of PipelineLightCulling.cpp:85-118).
+ * All pointers are DEVICE pointers.  out_cluster_index is exact; out_color matches the shader to float
+ * tolerance (documented in tests/test_gpu_shade.py). */
+HVCF_API int hvcf_shade(hvcf_ctx* ctx, uint32_t frame, const hvcf_gbuffer* gbuffer, const hvcf_push_const_pbr* pc,
+	const float camera_position[3], float* out_color, uint32_t* out_cluster_index, void* stream);
+
+/* Synthetic G-buffer for the camera of hvcf_host_camera_ubo (host arrays, sizes as in hvcf_gbuffer): rays through
+ * the pixel centres hit the ground plane y = 0 or a cylinder of radius 12 around the light disc; materials are hashed
+ * from the pixel index and `seed`.  Pure input generation: there is no reference counterpart (the reference
+ * rasterises Sponza). */
+HVCF_API int hvcf_host_init_gbuffer(uint32_t seed, const float position[3], const float target[3], uint32_t width,
+	uint32_t height, float* frag_depth, float* world_pos, float* normal_rough, float* albedo_metal);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Compute frustum culling: Shaders/FrustumCulling.comp:14-57 over `count` world-space boxes,
+ * writing instanceCount = 0/1 of each 16-byte indirect command (the other three words are left untouched).
+ * Replaces PipelineFrustumCulling::Execute (Source/Pipelines/PipelineFrustumCulling.cpp:32-69).  Context-free:
+ * boxes/commands are DEVICE pointers (Scene::transformedBoundingBoxBuffer_ / indirectBuffer_), `frustum` is a
+ * HOST pointer (the per-frame FrustumUBO upload of PipelineFrustumCulling.h SetFrustumUBO), passed by value to
+ * the kernel.
+ * ------------------------------------------------------------------------------------------------- */
+HVCF_API int hvcf_frustum_cull(int device, const hvcf_frustum_ubo* frustum, const hvcf_aabb* boxes, uint32_t count,
+	hvcf_draw_indirect_command* commands, void* stream);
+/* Camera::GetFrustumUBO (Source/Camera.cpp:199-234) for the camera of hvcf_host_camera_ubo. */
+HVCF_API int hvcf_host_frustum_ubo(const float position[3], const float target[3], float screen_width, float screen_height,
+	hvcf_frustum_ubo* out);
+/* Synthetic instance boxes (host array): centres uniform in [-extent, extent]^3, half sizes in [0.05, 1.5]. */
+HVCF_API int hvcf_host_init_boxes(uint32_t seed, uint32_t count, float extent, hvcf_aabb* out);
+
 /* Pinned host staging for callers that want asynchronous host<->device copies
  * (VMA_MEMORY_USAGE_CPU_TO_GPU in the reference, ResourcesLight.cpp:14-16). */
 HVCF_API int hvcf_host_alloc(size_t bytes, void** out_ptr);

@@ -82,6 +82,36 @@ HVCF_STATIC_ASSERT(offsetof(hvcf_cluster_forward_ubo, slice_count_x) == 152, "ub
 HVCF_STATIC_ASSERT(offsetof(hvcf_cluster_forward_ubo, slice_count_y) == 156, "ubo.sliceCountY @156");
 HVCF_STATIC_ASSERT(offsetof(hvcf_cluster_forward_ubo, slice_count_z) == 160, "ubo.sliceCountZ @160");
 
+/* PushConstPBR (Header/PushConstants.h:24-31; GLSL Shaders/PBR/PBRPushConstants.glsl): consumer-side constants. */
+typedef struct hvcf_push_const_pbr
+{
+	float light_intensity;   /* default 1 */
+	float base_reflectivity; /* default 0.04 */
+	float max_reflection_lod; /* default 4 (unused by the light loop) */
+	float light_falloff;     /* default 1 */
+	float albedo_multipler;  /* default 0 (sic: the reference spells it this way) */
+} hvcf_push_const_pbr;
+
+/* FrustumUBO (Header/UBOs.h:92-99; GLSL Shaders/Frustum.glsl): six planes + eight corners, std140. */
+typedef struct hvcf_frustum_ubo
+{
+	HVCF_ALIGNAS(16) float planes[6][4];
+	HVCF_ALIGNAS(16) float corners[8][4];
+} hvcf_frustum_ubo;
+
+/* VkDrawIndirectCommand as Shaders/DrawIndirectCommand.glsl declares it (16 B). */
+typedef struct hvcf_draw_indirect_command
+{
+	uint32_t vertex_count;
+	uint32_t instance_count;
+	uint32_t first_vertex;
+	uint32_t first_instance;
+} hvcf_draw_indirect_command;
+
+HVCF_STATIC_ASSERT(sizeof(hvcf_push_const_pbr) == 20, "PushConstPBR must be 20 bytes");
+HVCF_STATIC_ASSERT(sizeof(hvcf_frustum_ubo) == 224, "FrustumUBO must be 224 bytes");
+HVCF_STATIC_ASSERT(sizeof(hvcf_draw_indirect_command) == 16, "DrawIndirectCommand must be 16 bytes");
+
 /* Defaults of the reference (Header/Configs.h:33-56, :8-14). */
 #define HVCF_DEFAULT_SLICE_COUNT_X 16u
 #define HVCF_DEFAULT_SLICE_COUNT_Y 9u

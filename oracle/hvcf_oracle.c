@@ -177,8 +177,9 @@ static void mat4_inverse(const float m[4][4], float out[4][4]) /* detail/func_ma
 #define HVO_CAMERA_FAR 100.0f
 #define HVO_CAMERA_ZOOM 0.785398f
 
-void hvo_camera_ubo(const float pos[3], const float target[3], float width, float height,
-	uint32_t X, uint32_t Y, uint32_t Z, hvcf_cluster_forward_ubo* out)
+/* Camera::SetPositionAndTarget + UpdateInternal: projection (Y-flipped), its inverse and the view matrix */
+static void camera_matrices(const float pos[3], const float target[3], float width, float height,
+	float proj[4][4], float inv[4][4], float view[4][4])
 {
 	/* Camera::SetPositionAndTarget, Camera.cpp:81-93.  The unqualified asin/atan2/cos/sin calls
 	 * in Camera.cpp bind to the C library's DOUBLE functions under g++ (verified with decltype);
@@ -204,15 +205,13 @@ void hvo_camera_ubo(const float pos[3], const float target[3], float width, floa
 	/* glm::perspective -> perspectiveRH_ZO (GLM_FORCE_DEPTH_ZERO_TO_ONE), ext/matrix_clip_space.inl:233-246 */
 	const float aspect = width / height;
 	const float tanHalfFovy = tanf(HVO_CAMERA_ZOOM / 2.0f);
-	float proj[4][4];
-	memset(proj, 0, sizeof(proj));
+	memset(proj, 0, 64);
 	proj[0][0] = 1.0f / (aspect * tanHalfFovy);
 	proj[1][1] = 1.0f / (tanHalfFovy);
 	proj[2][2] = HVO_CAMERA_FAR / (HVO_CAMERA_NEAR - HVO_CAMERA_FAR);
 	proj[2][3] = -1.0f;
 	proj[3][2] = -(HVO_CAMERA_FAR * HVO_CAMERA_NEAR) / (HVO_CAMERA_FAR - HVO_CAMERA_NEAR);
 	proj[1][1] *= -1; /* Camera.cpp:132 */
-	float inv[4][4];
 	mat4_inverse(proj, inv);
 
 	/* glm::lookAt -> lookAtRH(position, position + front, up), ext/matrix_transform.inl:153-173 */
@@ -221,8 +220,7 @@ void hvo_camera_ubo(const float pos[3], const float target[3], float width, floa
 	const v3 f = normalize3(cf);
 	const v3 s = normalize3(cross3(f, up));
 	const v3 u = cross3(s, f);
-	float view[4][4];
-	memset(view, 0, sizeof(view));
+	memset(view, 0, 64);
 	view[0][0] = view[1][1] = view[2][2] = view[3][3] = 1.0f;
 	view[0][0] = s.x; view[1][0] = s.y; view[2][0] = s.z;
 	view[0][1] = u.x; view[1][1] = u.y; view[2][1] = u.z;
@@ -230,7 +228,13 @@ void hvo_camera_ubo(const float pos[3], const float target[3], float width, floa
 	view[3][0] = -dot3(s, position);
 	view[3][1] = -dot3(u, position);
 	view[3][2] = dot3(f, position);
+}
 
+void hvo_camera_ubo(const float pos[3], const float target[3], float width, float height,
+	uint32_t X, uint32_t Y, uint32_t Z, hvcf_cluster_forward_ubo* out)
+{
+	float proj[4][4], inv[4][4], view[4][4];
+	camera_matrices(pos, target, width, height, proj, inv, view);
 	/* Camera::GetClusterForwardUBO, Camera.cpp:178-197 */
 	memset(out, 0, sizeof(*out));
 	memcpy(out->camera_inverse_projection, inv, 64);
@@ -500,6 +504,228 @@ uint32_t hvo_cluster_index(const hvcf_cluster_forward_ubo* ubo, float frag_x, fl
 	const uint32_t cx = (uint32_t)(frag_x / tileX);
 	const uint32_t cy = (uint32_t)(frag_y / tileY);
 	return cx + cy * ubo->slice_count_x + zIndex * ubo->slice_count_x * ubo->slice_count_y;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Consumer: light loop of the PBR cluster-forward fragment shader
+ * ------------------------------------------------------------------------------------------ */
+#define HVO_PI 3.1415926535897932384626433832795f /* Shaders/PBR/PBRHeader.glsl:10-12 (a 32-bit float literal in GLSL) */
+
+static float distribution_ggx(float NoH, float roughness) /* PBRHeader.glsl:16-27 */
+{
+	const float alpha = roughness * roughness;
+	const float alpha2 = alpha * alpha;
+	const float NoH2 = NoH * NoH;
+	const float nominator = alpha2;
+	float denominator = (NoH2 * (alpha2 - 1.0f) + 1.0f);
+	denominator = HVO_PI * denominator * denominator;
+	return nominator / denominator;
+}
+
+static float alpha_direct_lighting(float roughness) /* PBRHeader.glsl:30-35 */
+{
+	const float r = (roughness + 1.0f);
+	return (r * r) / 8.0f;
+}
+
+static float geometry_schlick_ggx(float NoL, float NoV, float alpha) /* PBRHeader.glsl:41-46 */
+{
+	const float GL = NoL / (NoL * (1.0f - alpha) + alpha);
+	const float GV = NoV / (NoV * (1.0f - alpha) + alpha);
+	return GL * GV;
+}
+
+static v3 fresnel_schlick(float cosTheta, v3 F0) /* PBRHeader.glsl:50-53 */
+{
+	const float c = fminf(fmaxf(1.0f - cosTheta, 0.0f), 1.0f);
+	const float p = powf(c, 5.0f);
+	v3 r = { F0.x + (1.0f - F0.x) * p, F0.y + (1.0f - F0.y) * p, F0.z + (1.0f - F0.z) * p };
+	return r;
+}
+
+/* Shaders/ClusteredForward/Radiance.glsl:2-57 */
+static v3 radiance(v3 worldPos, const hvcf_push_const_pbr* pc, v3 albedo, v3 N, v3 V, v3 F0, float metallic,
+	float roughness, float alphaRoughness, float NoV, const hvcf_light_data* light)
+{
+	const v3 toLight = { light->position[0] - worldPos.x, light->position[1] - worldPos.y, light->position[2] - worldPos.z };
+	const v3 L = normalize3(toLight);
+	const v3 VL = { V.x + L.x, V.y + L.y, V.z + L.z };
+	const v3 H = normalize3(VL);
+	const float NoH = fmaxf(dot3(N, H), 0.0f);
+	const float NoL = fmaxf(dot3(N, L), 0.0f);
+	const float HoV = fmaxf(dot3(H, V), 0.0f);
+	const float distance = sqrtf(dot3(toLight, toLight));
+	const float attenuation = fmaxf(1.0f - (distance / light->radius), 0.0f) / powf(distance, pc->light_falloff);
+	const v3 rad = { light->color[0] * attenuation * pc->light_intensity, light->color[1] * attenuation * pc->light_intensity,
+		light->color[2] * attenuation * pc->light_intensity };
+	const float D = distribution_ggx(NoH, roughness);
+	const float G = geometry_schlick_ggx(NoL, NoV, alphaRoughness);
+	const v3 F = fresnel_schlick(HoV, F0);
+	const float DG = D * G;
+	const float denominator = 4.0f * NoV * NoL + 0.0001f;
+	const v3 specular = { DG * F.x / denominator, DG * F.y / denominator, DG * F.z / denominator };
+	const float om = 1.0f - metallic;
+	const v3 kD = { (1.0f - F.x) * om, (1.0f - F.y) * om, (1.0f - F.z) * om };
+	const v3 diffuse = { kD.x * albedo.x / HVO_PI, kD.y * albedo.y / HVO_PI, kD.z * albedo.z / HVO_PI };
+	v3 Lo = { (diffuse.x + specular.x) * rad.x * NoL, (diffuse.y + specular.y) * rad.y * NoL, (diffuse.z + specular.z) * rad.z * NoL };
+	return Lo;
+}
+
+void hvo_shade(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_cell* cells, const uint32_t* indices,
+	const hvcf_light_data* lights, const hvcf_push_const_pbr* pc, const float camera_position[3],
+	uint32_t width, uint32_t height, uint64_t pixel_begin, uint64_t pixel_end, uint64_t pixel_stride,
+	const float* frag_depth, const float* world_pos, const float* normal_rough, const float* albedo_metal,
+	float* out_color, uint32_t* out_cluster, int threads)
+{
+	const int nt = threads > 1 ? threads : 1;
+	(void)nt;
+	(void)height;
+	if (pixel_stride == 0)
+		pixel_stride = 1;
+	const uint32_t X = ubo->slice_count_x, Y = ubo->slice_count_y, Z = ubo->slice_count_z;
+	const int64_t n = (int64_t)((pixel_end - pixel_begin + pixel_stride - 1) / pixel_stride);
+#pragma omp parallel for schedule(dynamic, 256) num_threads(nt)
+	for (int64_t k = 0; k < n; ++k)
+	{
+		const uint64_t p = pixel_begin + (uint64_t)k * pixel_stride;
+		const float fx = (float)(p % width) + 0.5f, fy = (float)(p / width) + 0.5f;
+		/* Scene.frag:64-78 */
+		uint32_t clusterIdx = hvo_cluster_index(ubo, fx, fy, frag_depth[p]);
+		if (clusterIdx >= X * Y * Z) /* guard, see header */
+			clusterIdx = (clusterIdx % (X * Y)) + (Z - 1) * X * Y;
+		const uint32_t lightCount = cells[clusterIdx].count;
+		const uint32_t lightIndexOffset = cells[clusterIdx].offset;
+		const v3 worldPos = { world_pos[4 * p], world_pos[4 * p + 1], world_pos[4 * p + 2] };
+		const v3 N = { normal_rough[4 * p], normal_rough[4 * p + 1], normal_rough[4 * p + 2] };
+		const float roughness = normal_rough[4 * p + 3];
+		const v3 albedo = { albedo_metal[4 * p], albedo_metal[4 * p + 1], albedo_metal[4 * p + 2] };
+		const float metallic = albedo_metal[4 * p + 3];
+		const float alphaRoughness = alpha_direct_lighting(roughness); /* Scene.frag:103 */
+		const v3 toCam = { camera_position[0] - worldPos.x, camera_position[1] - worldPos.y, camera_position[2] - worldPos.z };
+		const v3 V = normalize3(toCam); /* :107 */
+		const float NoV = fmaxf(dot3(N, V), 0.0f); /* :108 */
+		/* :112-113  F0 = mix(vec3(baseReflectivity), albedo, metallic) = x*(1-a) + y*a */
+		const float b = pc->base_reflectivity;
+		const v3 F0 = { b * (1.0f - metallic) + albedo.x * metallic, b * (1.0f - metallic) + albedo.y * metallic,
+			b * (1.0f - metallic) + albedo.z * metallic };
+		v3 Lo = { albedo.x * pc->albedo_multipler, albedo.y * pc->albedo_multipler, albedo.z * pc->albedo_multipler }; /* :117 */
+		for (uint32_t i = 0; i < lightCount; ++i) /* :119-134 */
+		{
+			const uint32_t lightIndex = indices[i + lightIndexOffset];
+			const v3 r = radiance(worldPos, pc, albedo, N, V, F0, metallic, roughness, alphaRoughness, NoV, &lights[lightIndex]);
+			Lo.x += r.x;
+			Lo.y += r.y;
+			Lo.z += r.z;
+		}
+		if (out_color)
+		{
+			out_color[4 * p] = Lo.x;
+			out_color[4 * p + 1] = Lo.y;
+			out_color[4 * p + 2] = Lo.z;
+			out_color[4 * p + 3] = 1.0f;
+		}
+		if (out_cluster)
+			out_cluster[p] = clusterIdx;
+	}
+}
+
+/* ------------------------------------------------------------------------------------------
+ * Frustum culling
+ * ------------------------------------------------------------------------------------------ */
+/* glm mat4 * mat4, detail/type_mat4x4.inl:630-648: Result[c] = ((A0*b0 + A1*b1) + A2*b2) + A3*b3 */
+static void mat4_mul_mat4(const float a[4][4], const float b[4][4], float out[4][4])
+{
+	for (int c = 0; c < 4; ++c)
+		for (int r = 0; r < 4; ++r)
+		{
+			const float t0 = a[0][r] * b[c][0], t1 = a[1][r] * b[c][1], t2 = a[2][r] * b[c][2], t3 = a[3][r] * b[c][3];
+			out[c][r] = ((t0 + t1) + t2) + t3;
+		}
+}
+
+/* Camera::GetFrustumUBO, Source/Camera.cpp:199-234 */
+void hvo_frustum_ubo(const float pos[3], const float target[3], float width, float height, hvcf_frustum_ubo* out)
+{
+	float proj[4][4], inv[4][4], view[4][4], projView[4][4], t[4][4], invProjView[4][4];
+	camera_matrices(pos, target, width, height, proj, inv, view);
+	mat4_mul_mat4(proj, view, projView);
+	for (int c = 0; c < 4; ++c) /* glm::transpose */
+		for (int r = 0; r < 4; ++r)
+			t[c][r] = projView[r][c];
+	memset(out, 0, sizeof(*out));
+	for (int k = 0; k < 4; ++k)
+	{
+		out->planes[0][k] = t[3][k] + t[0][k]; /* left */
+		out->planes[1][k] = t[3][k] - t[0][k]; /* right */
+		out->planes[2][k] = t[3][k] + t[1][k]; /* bottom */
+		out->planes[3][k] = t[3][k] - t[1][k]; /* top */
+		out->planes[4][k] = t[3][k] + t[2][k]; /* near */
+		out->planes[5][k] = t[3][k] - t[2][k]; /* far */
+	}
+	mat4_inverse(projView, invProjView);
+	static const float corners[8][4] = {
+		{ -1, -1, -1, 1 }, { 1, -1, -1, 1 }, { 1, 1, -1, 1 }, { -1, 1, -1, 1 },
+		{ -1, -1, 1, 1 }, { 1, -1, 1, 1 }, { 1, 1, 1, 1 }, { -1, 1, 1, 1 } };
+	for (int i = 0; i < 8; ++i)
+	{
+		float q[4];
+		mat4_mul_vec4(&invProjView[0][0], corners[i], q);
+		for (int k = 0; k < 4; ++k)
+			out->corners[i][k] = q[k] / q[3];
+	}
+}
+
+/* dot(vec4, vec4) as glm evaluates it off MSVC: (x + y) + (z + w), detail/func_geometric.inl:57-68 */
+static inline float plane_dot(const float p[4], float x, float y, float z)
+{
+	const float tx = p[0] * x, ty = p[1] * y, tz = p[2] * z, tw = p[3] * 1.0f;
+	return (tx + ty) + (tz + tw);
+}
+
+/* FrustumCulling.comp:14-44 */
+static int is_box_in_frustum(const hvcf_frustum_ubo* f, const hvcf_aabb* box)
+{
+	const float* mn = box->min_point;
+	const float* mx = box->max_point;
+	for (int i = 0; i < 6; i++)
+	{
+		int r = 0;
+		r += (plane_dot(f->planes[i], mn[0], mn[1], mn[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mx[0], mn[1], mn[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mn[0], mx[1], mn[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mx[0], mx[1], mn[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mn[0], mn[1], mx[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mx[0], mn[1], mx[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mn[0], mx[1], mx[2]) < 0.0f) ? 1 : 0;
+		r += (plane_dot(f->planes[i], mx[0], mx[1], mx[2]) < 0.0f) ? 1 : 0;
+		if (r == 8)
+			return 0;
+	}
+	for (int axis = 0; axis < 3; ++axis)
+	{
+		int r = 0;
+		for (int i = 0; i < 8; i++)
+			r += (f->corners[i][axis] > mx[axis]) ? 1 : 0;
+		if (r == 8)
+			return 0;
+		r = 0;
+		for (int i = 0; i < 8; i++)
+			r += (f->corners[i][axis] < mn[axis]) ? 1 : 0;
+		if (r == 8)
+			return 0;
+	}
+	return 1;
+}
+
+/* FrustumCulling.comp:46-58; only instanceCount is written */
+void hvo_frustum_cull(const hvcf_frustum_ubo* frustum, const hvcf_aabb* boxes, uint32_t count,
+	hvcf_draw_indirect_command* commands, int threads)
+{
+	const int nt = threads > 1 ? threads : 1;
+	(void)nt;
+#pragma omp parallel for schedule(static) num_threads(nt)
+	for (int64_t i = 0; i < (int64_t)count; ++i)
+		commands[i].instance_count = is_box_in_frustum(frustum, &boxes[i]) ? 1u : 0u;
 }
 
 int hvo_max_threads(void)

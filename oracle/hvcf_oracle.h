@@ -81,6 +81,35 @@ void hvo_boundary_report(const hvcf_cluster_forward_ubo* ubo, const hvcf_aabb* a
  * cluster index. */
 uint32_t hvo_cluster_index(const hvcf_cluster_forward_ubo* ubo, float frag_x, float frag_y, float frag_depth);
 
+/*
+ * Consumer: the light loop of the PBR cluster-forward fragment shader.
+ *   Shaders/ClusteredForward/Scene.frag:55-78   LinearDepth, zIndex, tile -> clusterIdx, (count, offset)
+ *   Scene.frag:103,107-108,112-113,117,119-134   alphaRoughness, V, NoV, F0, Lo = albedo*albedoMultipler + sum Radiance
+ *   Shaders/ClusteredForward/Radiance.glsl:2-57, Shaders/PBR/PBRHeader.glsl:16-64
+ * What the rasteriser and the material textures supply in the reference is a device-side G-buffer here
+ * (one record per pixel, row-major, gl_FragCoord = (x + 0.5, y + 0.5, frag_depth)):
+ *   frag_depth[p]      gl_FragCoord.z in [0, 1)
+ *   world_pos[p][4]    worldPos.xyz, w ignored
+ *   normal_rough[p][4] N.xyz (after NormalTBN), roughness
+ *   albedo_metal[p][4] albedo.rgb (after the sRGB->linear pow), metallic
+ * Outputs for pixels [pixel_begin, pixel_end): out_color[p] = (Lo.rgb, 1), out_cluster[p] = clusterIdx.
+ * Ambient (IBL cubemaps) and emissive need textures and are out of scope.  A zIndex beyond the grid (only
+ * reachable with frag_depth == 1) is clamped to Z-1 so that nothing is read out of bounds.
+ * Float parity of out_color is by tolerance (pow/sqrt/divide orders), out_cluster is exact.
+ */
+void hvo_shade(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_cell* cells, const uint32_t* indices,
+	const hvcf_light_data* lights, const hvcf_push_const_pbr* pc, const float camera_position[3],
+	uint32_t width, uint32_t height, uint64_t pixel_begin, uint64_t pixel_end, uint64_t pixel_stride,
+	const float* frag_depth, const float* world_pos, const float* normal_rough, const float* albedo_metal,
+	float* out_color, uint32_t* out_cluster, int threads);
+
+/* Camera::GetFrustumUBO (Source/Camera.cpp:199-234) for the camera of hvo_camera_ubo. */
+void hvo_frustum_ubo(const float pos[3], const float target[3], float width, float height, hvcf_frustum_ubo* out);
+
+/* FrustumCulling.comp:14-57: instance_count = IsBoxInFrustum ? 1 : 0 for boxes [0, count). */
+void hvo_frustum_cull(const hvcf_frustum_ubo* frustum, const hvcf_aabb* boxes, uint32_t count,
+	hvcf_draw_indirect_command* commands, int threads);
+
 int hvo_max_threads(void);
 
 #ifdef __cplusplus

@@ -3,7 +3,9 @@
 # lie under /root/reference, into oracle/_ref/libhvcf_ref.so.  TEST INFRASTRUCTURE ONLY.
 #
 #   * HelloVulkan/Source/Camera.cpp           (the UBO producer; real C++ of the reference)
-#   * Shaders/ClusteredForward/AABBGenerator.comp, LightCulling.comp (+ the .glsl they include)
+#   * Shaders/ClusteredForward/AABBGenerator.comp, LightCulling.comp, Shaders/FrustumCulling.comp (+ the .glsl they
+#     include), Shaders/ClusteredForward/Radiance.glsl, Shaders/PBR/PBRHeader.glsl and the light-loop lines of
+#     Shaders/ClusteredForward/Scene.frag
 #     compiled as C++ against the reference's vendored glm: the shader text is streamed through
 #     sed (drops `#version`, turns `layout(...) buffer/uniform` blocks into plain globals) straight
 #     into g++ on stdin -- no reference source is copied into this repo or into oracle/_ref/.
@@ -49,9 +51,34 @@ glsl_to_cxx() {
 	echo 'namespace hvref_lightcull { using namespace hvref_glsl; static thread_local Builtins gl;'
 	glsl_to_cxx "$HV/Shaders/ClusteredForward/LightCulling.comp"
 	echo '}'
+	# FrustumCulling.comp
+	echo '#define gl_GlobalInvocationID gl.gl_GlobalInvocationID'
+	echo 'namespace hvref_frustumcull { using namespace hvref_glsl; static thread_local Builtins gl;'
+	glsl_to_cxx "$HV/Shaders/FrustumCulling.comp"
+	echo '}'
+	echo '#undef gl_GlobalInvocationID'
 	echo '#undef main'
 	echo '#undef gl_WorkGroupID'
 	echo '#undef gl_NumWorkGroups'
+	# The consumer: Scene.frag cannot be compiled whole (textures, buffer references), so the
+	# lines of the path are streamed by number into a function body; Radiance.glsl and PBRHeader.glsl compile whole.
+	SF="$HV/Shaders/ClusteredForward/Scene.frag"
+	echo 'namespace hvref_scenefrag { using namespace hvref_glsl;'
+	cat "$HV/Shaders/LightData.glsl"; echo
+	cat "$HV/Shaders/ClusteredForward/Header.glsl"; echo
+	cat "$HV/Shaders/PBR/PBRPushConstants.glsl"; echo
+	echo 'struct CameraPositionOnly { vec4 position; };'
+	echo 'static thread_local PBRPushConstant pc; static thread_local vec3 worldPos; static thread_local vec4 gl_FragCoord;'
+	echo 'static thread_local CameraPositionOnly camUBO; static ClusterForwardUBO cfUBO;'
+	echo 'static SSBO<LightData> lights; static SSBO<LightCell> lightCells; static SSBO<uint> lightIndices;'
+	cat "$HV/Shaders/PBR/PBRHeader.glsl"; echo
+	glsl_to_cxx "$HV/Shaders/ClusteredForward/Radiance.glsl"; echo
+	sed -n '55,58p' "$SF"
+	echo 'static void fragment_light_loop(vec3 albedo, vec3 N, float metallic, float roughness, vec3& LoOut, uint& clusterIdxOut) {'
+	sed -n '64,78p' "$SF"
+	sed -n '103p;107,108p;112,113p;117p;119,134p' "$SF" | sed -E 's/\.xyz\b/.xyz()/g'
+	echo 'LoOut = Lo; clusterIdxOut = clusterIdx; }'
+	echo '}'
 	cat "$HERE/ref_api.inc"
 } | "$CXX" "${COMMON[@]}" -fsingle-precision-constant -DGLM_FORCE_SWIZZLE -fopenmp -I"$HERE" -x c++ -c - -o "$OUT/ref_shaders.o"
 

@@ -35,5 +35,6 @@ struct Builtins
 {
 	uvec3 gl_WorkGroupID{0, 0, 0};
 	uvec3 gl_NumWorkGroups{1, 1, 1};
+	uvec3 gl_GlobalInvocationID{0, 0, 0};
 };
 } // namespace hvref_glsl

@@ -18,6 +18,8 @@ REF_SO = os.path.join(ROOT, "oracle", "_ref", "libhvcf_ref.so")
 LIGHT_DT = np.dtype([("position", "<f4", 4), ("color", "<f4", 4), ("radius", "<f4"), ("pad_", "<f4", 3)])
 AABB_DT = np.dtype([("min_point", "<f4", 4), ("max_point", "<f4", 4)])
 CELL_DT = np.dtype([("offset", "<u4"), ("count", "<u4")])
+CMD_DT = np.dtype([("vertex_count", "<u4"), ("instance_count", "<u4"), ("first_vertex", "<u4"), ("first_instance", "<u4")])
+DEFAULT_PC = np.array([1.0, 0.04, 4.0, 1.0, 0.0], np.float32)  # PushConstPBR defaults (Header/PushConstants.h:24-31)
 assert LIGHT_DT.itemsize == 48 and AABB_DT.itemsize == 32 and CELL_DT.itemsize == 8
 
 # the reference camera of AppPBRClusterForward::Init (AppPBRClusterForward.cpp:22)
@@ -114,6 +116,37 @@ class Oracle:
     def cluster_index(self, ubo, x, y, depth):
         return int(self.lib.hvo_cluster_index(_vp(ubo), ctypes.c_float(x), ctypes.c_float(y), ctypes.c_float(depth)))
 
+    def shade(self, ubo, cells, indices, lights, g, pc=DEFAULT_PC, camera_position=REF_CAMERA_POS, begin=0, end=None,
+              stride=1, threads=None):
+        """Scene.frag light loop over the host G-buffer dict `g`; returns (color [P,4], cluster [P]); pixels outside the
+        sampled set stay zero."""
+        P = g["width"] * g["height"]
+        end = P if end is None else end
+        color = np.zeros((P, 4), np.float32)
+        cluster = np.zeros(P, np.uint32)
+        pc = np.ascontiguousarray(pc, np.float32)
+        idx = np.ascontiguousarray(indices if len(indices) else np.zeros(1, np.uint32))
+        if threads is None:
+            threads = self.max_threads()
+        self.lib.hvo_shade(_vp(ubo), _vp(cells), _vp(idx), _vp(lights), _vp(pc), _f3(camera_position),
+                           ctypes.c_uint32(g["width"]), ctypes.c_uint32(g["height"]), ctypes.c_uint64(begin), ctypes.c_uint64(end),
+                           ctypes.c_uint64(stride), _vp(g["frag_depth"]), _vp(g["world_pos"]), _vp(g["normal_rough"]),
+                           _vp(g["albedo_metal"]), _vp(color), _vp(cluster), ctypes.c_int(threads))
+        return color, cluster
+
+    def frustum_ubo(self, screen, pos=REF_CAMERA_POS, target=REF_CAMERA_TARGET):
+        out = np.zeros(224, np.uint8)
+        self.lib.hvo_frustum_ubo(_f3(pos), _f3(target), ctypes.c_float(screen[0]), ctypes.c_float(screen[1]), _vp(out))
+        return out
+
+    def frustum_cull(self, frustum, boxes, commands=None, threads=None):
+        """Returns the command array with instance_count rewritten (other words as passed in, zero by default)."""
+        cmds = np.zeros(len(boxes), CMD_DT) if commands is None else commands.copy()
+        if threads is None:
+            threads = self.max_threads()
+        self.lib.hvo_frustum_cull(_vp(frustum), _vp(boxes), ctypes.c_uint32(len(boxes)), _vp(cmds), ctypes.c_int(threads))
+        return cmds
+
 
 class Reference:
     """The reference's own sources compiled here (oracle/refbuild/build_ref.sh)."""
@@ -158,6 +191,35 @@ class Reference:
         self.lib.hvref_cull(_vp(ubo), _vp(aabbs), _vp(lights), ctypes.c_uint32(len(lights)), _vp(cells), _vp(indices),
                             _vp(g), ctypes.c_int(threads))
         return cells, indices[: int(g[0])].copy(), int(g[0])
+
+    def shade(self, ubo, cells, indices, lights, g, pc=DEFAULT_PC, camera_position=REF_CAMERA_POS, begin=0, end=None,
+              stride=1, threads=None):
+        P = g["width"] * g["height"]
+        end = P if end is None else end
+        color = np.zeros((P, 4), np.float32)
+        cluster = np.zeros(P, np.uint32)
+        pc = np.ascontiguousarray(pc, np.float32)
+        idx = np.ascontiguousarray(indices if len(indices) else np.zeros(1, np.uint32))
+        if threads is None:
+            threads = self.max_threads()
+        self.lib.hvref_shade(_vp(ubo), _vp(cells), _vp(idx), _vp(lights), ctypes.c_uint32(len(lights)), _vp(pc),
+                             _f3(camera_position), ctypes.c_uint32(g["width"]), ctypes.c_uint32(g["height"]),
+                             ctypes.c_uint64(begin), ctypes.c_uint64(end), ctypes.c_uint64(stride), _vp(g["frag_depth"]),
+                             _vp(g["world_pos"]), _vp(g["normal_rough"]), _vp(g["albedo_metal"]), _vp(color), _vp(cluster),
+                             ctypes.c_int(threads))
+        return color, cluster
+
+    def frustum_ubo(self, screen, pos=REF_CAMERA_POS, target=REF_CAMERA_TARGET):
+        out = np.zeros(224, np.uint8)
+        self.lib.hvref_frustum_ubo(_f3(pos), _f3(target), ctypes.c_float(screen[0]), ctypes.c_float(screen[1]), _vp(out))
+        return out
+
+    def frustum_cull(self, frustum, boxes, commands=None, threads=None):
+        cmds = np.zeros(len(boxes), CMD_DT) if commands is None else commands.copy()
+        if threads is None:
+            threads = self.max_threads()
+        self.lib.hvref_frustum_cull(_vp(frustum), _vp(boxes), ctypes.c_uint32(len(boxes)), _vp(cmds), ctypes.c_int(threads))
+        return cmds
 
 
 def lists_of(cells, indices):
