@@ -24,9 +24,18 @@ namespace
 constexpr uint32_t kShadeWarps = 8;
 constexpr float kPi = 3.1415926535897932384626433832795f; // PBRHeader.glsl:10-12
 
+// glm dot(vec3, vec3): (x*x' + y*y') + z*z', every product and sum rounded (detail/func_geometric.inl:48-55).  The
+// directions L, H, V and the cosines built from them are kept bit-identical to the shader compiled as C++: the GGX
+// denominator NoH^2 * (alpha^2 - 1) + 1 cancels down to ~alpha^2 at a highlight, so one ulp of NoH is percents of D.
 __device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz)
 {
-	return ax * bx + ay * by + az * bz;
+	return __fadd_rn(__fadd_rn(__fmul_rn(ax, bx), __fmul_rn(ay, by)), __fmul_rn(az, bz));
+}
+// glm inversesqrt = 1 / sqrt(x), both correctly rounded
+__device__ __forceinline__ float inv_sqrt_exact(float x, float* root)
+{
+	*root = __fsqrt_rn(x);
+	return __frcp_rn(*root);
 }
 
 // Scene.frag:55-58 with every operation rounded on its own
@@ -66,15 +75,16 @@ __global__ void __launch_bounds__(kShadeWarps * 32) cluster_shade_kernel(const S
 	const float roughness = nr.w, metallic = am.w;
 	const float ar = (roughness + 1.0f) * (roughness + 1.0f) / 8.0f; // AlphaDirectLighting
 	float vx = p.cam[0] - wp.x, vy = p.cam[1] - wp.y, vz = p.cam[2] - wp.z;
-	const float vinv = 1.0f / sqrtf(dot3(vx, vy, vz, vx, vy, vz));
-	vx *= vinv, vy *= vinv, vz *= vinv;
+	float vlen;
+	const float vinv = inv_sqrt_exact(dot3(vx, vy, vz, vx, vy, vz), &vlen);
+	vx = __fmul_rn(vx, vinv), vy = __fmul_rn(vy, vinv), vz = __fmul_rn(vz, vinv);
 	const float NoV = fmaxf(dot3(nr.x, nr.y, nr.z, vx, vy, vz), 0.0f);
 	const float b = p.pc.base_reflectivity;
 	const float f0x = b * (1.0f - metallic) + am.x * metallic, f0y = b * (1.0f - metallic) + am.y * metallic,
 				f0z = b * (1.0f - metallic) + am.z * metallic;
 	float lox = am.x * p.pc.albedo_multipler, loy = am.y * p.pc.albedo_multipler, loz = am.z * p.pc.albedo_multipler;
 	// loop invariants of Radiance()
-	const float alpha = roughness * roughness, alpha2 = alpha * alpha;
+	const float alpha = __fmul_rn(roughness, roughness), alpha2 = __fmul_rn(alpha, alpha), alpha2m1 = __fsub_rn(alpha2, 1.0f);
 	const float GV = NoV / (NoV * (1.0f - ar) + ar);
 	const float om = 1.0f - metallic;
 	const float falloff = p.pc.light_falloff, intensity = p.pc.light_intensity;
@@ -107,23 +117,24 @@ __global__ void __launch_bounds__(kShadeWarps * 32) cluster_shade_kernel(const S
 				for (uint32_t k = 0; k < n; ++k)
 				{
 					const float4 lp = s_pos[warp][k], lcol = s_col[warp][k];
-					const float lx = lp.x - wp.x, ly = lp.y - wp.y, lz = lp.z - wp.z;
+					const float lx = __fsub_rn(lp.x, wp.x), ly = __fsub_rn(lp.y, wp.y), lz = __fsub_rn(lp.z, wp.z);
 					const float d2 = dot3(lx, ly, lz, lx, ly, lz);
 					if (!(d2 < lcol.w))
 						continue; // attenuation = max(1 - d/r, 0) = 0
-					const float dinv = rsqrtf(d2), dist = d2 * dinv;
-					const float Lx = lx * dinv, Ly = ly * dinv, Lz = lz * dinv;
+					float dist;
+					const float dinv = inv_sqrt_exact(d2, &dist);
+					const float Lx = __fmul_rn(lx, dinv), Ly = __fmul_rn(ly, dinv), Lz = __fmul_rn(lz, dinv);
 					const float NoL = fmaxf(dot3(nr.x, nr.y, nr.z, Lx, Ly, Lz), 0.0f);
 					if (!(NoL > 0.0f))
 						continue; // the term is multiplied by NoL
-					float hx = vx + Lx, hy = vy + Ly, hz = vz + Lz;
-					const float hinv = rsqrtf(dot3(hx, hy, hz, hx, hy, hz));
-					hx *= hinv, hy *= hinv, hz *= hinv;
+					float hx = __fadd_rn(vx, Lx), hy = __fadd_rn(vy, Ly), hz = __fadd_rn(vz, Lz), hlen;
+					const float hinv = inv_sqrt_exact(dot3(hx, hy, hz, hx, hy, hz), &hlen);
+					hx = __fmul_rn(hx, hinv), hy = __fmul_rn(hy, hinv), hz = __fmul_rn(hz, hinv);
 					const float NoH = fmaxf(dot3(nr.x, nr.y, nr.z, hx, hy, hz), 0.0f);
 					const float HoV = fmaxf(dot3(hx, hy, hz, vx, vy, vz), 0.0f);
 					const float powd = unit_falloff ? dist : __powf(dist, falloff);
 					const float att = __fdividef(fmaxf(1.0f - dist * lp.w, 0.0f), powd) * intensity;
-					const float den = NoH * NoH * (alpha2 - 1.0f) + 1.0f;
+					const float den = __fadd_rn(__fmul_rn(__fmul_rn(NoH, NoH), alpha2m1), 1.0f);
 					const float D = __fdividef(alpha2, kPi * den * den);
 					const float G = __fdividef(NoL, NoL * (1.0f - ar) + ar) * GV;
 					const float c = fminf(fmaxf(1.0f - HoV, 0.0f), 1.0f), c2 = c * c, p5 = c2 * c2 * c;
