@@ -1,8 +1,10 @@
 // app_cluster_forward.cpp -- headless driver written in the shape of AppPBRClusterForward
 // (HelloVulkan/Source/Apps/AppPBRClusterForward.cpp:19-79 Init, :81-118 InitLights, :120-136 UpdateUBOs,
 // :160-182 MainLoop; AppBase::DrawFrame / FillCommandBuffer, Source/Apps/AppBase.cpp:94-229), reduced to the
-// two compute pipelines of the light-culling path.  No window, swapchain or UI: frames are a counted loop
-// and the results are written to files so a test can compare them with the oracle.
+// compute pipelines of the light-culling path plus its consumer (the PBR cluster-forward light loop over a synthetic
+// G-buffer) and, as in AppPBRBindless-style apps, compute frustum culling ahead of them (AppFrustumCulling.cpp).
+// No window, swapchain or UI: frames are a counted loop and the results are written to files so a test can compare
+// them with the oracle.
 //
 // usage: hv_cluster_forward_app <X> <Y> <Z> <width> <height> <lights> <seed> <frames> <out_prefix>
 #include <cstdio>
@@ -35,12 +37,38 @@ public:
 		resourcesCF_->sliceCountY_ = Y_;
 		resourcesCF_->sliceCountZ_ = Z_;
 		resourcesCF_->CreateBuffers(vulkanContext_, resourcesLight_->GetLightCount());
+		InitScene();
+		// pipeline order of AppPBRClusterForward::Init (AppPBRClusterForward.cpp:46-78), compute + consumer only
+		auto frustum = std::make_unique<PipelineFrustumCulling>(vulkanContext_, &scene_);
 		auto aabb = std::make_unique<PipelineAABBGenerator>(vulkanContext_, resourcesCF_.get());
 		auto cull = std::make_unique<PipelineLightCulling>(vulkanContext_, resourcesLight_.get(), resourcesCF_.get());
+		auto pbr = std::make_unique<PipelinePBRClusterForward>(vulkanContext_, resourcesGBuffer_.get(), resourcesLight_.get(), resourcesCF_.get());
+		frustumPtr_ = frustum.get();
 		aabbPtr_ = aabb.get();
 		lightCullPtr_ = cull.get();
+		pbrPtr_ = pbr.get();
+		pipelines_.push_back(std::move(frustum));
 		pipelines_.push_back(std::move(aabb));
 		pipelines_.push_back(std::move(cull));
+		pipelines_.push_back(std::move(pbr));
+	}
+
+	// synthetic stand-ins of what Scene / rasterisation provide in the reference
+	void InitScene()
+	{
+		const uint32_t w = static_cast<uint32_t>(width_), h = static_cast<uint32_t>(height_);
+		const size_t P = static_cast<size_t>(w) * h;
+		std::vector<float> depth(P), wp(4 * P), nr(4 * P), am(4 * P);
+		const float pos[3] = { 0.0f, 1.0f, 6.0f }, target[3] = { 0.0f, 2.5f, 0.0f };
+		hv::Check(hvcf_host_init_gbuffer(7, pos, target, w, h, depth.data(), wp.data(), nr.data(), am.data()), "hvcf_host_init_gbuffer");
+		resourcesGBuffer_ = std::make_unique<ResourcesGBufferCF>();
+		resourcesGBuffer_->Create(vulkanContext_, w, h, depth.data(), wp.data(), nr.data(), am.data());
+		std::vector<AABB> boxes(kBoxes);
+		hv::Check(hvcf_host_init_boxes(4242, kBoxes, 60.0f, reinterpret_cast<hvcf_aabb*>(boxes.data())), "hvcf_host_init_boxes");
+		std::vector<DrawIndirectCommand> commands(kBoxes);
+		for (uint32_t i = 0; i < kBoxes; ++i)
+			commands[i] = { 36u, 1u, 0u, i };
+		scene_.Create(vulkanContext_, boxes, commands);
 	}
 
 	void InitLights()
@@ -60,6 +88,9 @@ public:
 		aabbPtr_->SetClusterForwardUBO(vulkanContext_, cfUBO);
 		lightCullPtr_->ResetGlobalIndex(vulkanContext_);
 		lightCullPtr_->SetClusterForwardUBO(vulkanContext_, cfUBO);
+		pbrPtr_->SetClusterForwardUBO(vulkanContext_, cfUBO);
+		FrustumUBO frustumUBO = camera_->GetFrustumUBO(); // AppFrustumCulling::UpdateUBOs
+		frustumPtr_->SetFrustumUBO(vulkanContext_, frustumUBO);
 	}
 
 	void DrawFrame()
@@ -105,6 +136,21 @@ public:
 		Write(prefix + ".cells", cells.data(), C * sizeof(LightCell));
 		Write(prefix + ".indices", indices.data(), total * sizeof(uint32_t));
 		Write(prefix + ".lights", resourcesLight_->lights_.data(), resourcesLight_->lights_.size() * sizeof(LightData));
+		const size_t P = static_cast<size_t>(resourcesGBuffer_->width_) * resourcesGBuffer_->height_;
+		std::vector<float> color(4 * P);
+		std::vector<uint32_t> cluster(P);
+		resourcesGBuffer_->color_.DownloadBufferData(vulkanContext_, color.data(), 16 * P);
+		resourcesGBuffer_->clusterIndex_.DownloadBufferData(vulkanContext_, cluster.data(), 4 * P);
+		Write(prefix + ".color", color.data(), 16 * P);
+		Write(prefix + ".cluster", cluster.data(), 4 * P);
+		std::vector<DrawIndirectCommand> commands(kBoxes);
+		scene_.indirectBuffer_.DownloadBufferData(vulkanContext_, commands.data(), sizeof(DrawIndirectCommand) * kBoxes);
+		Write(prefix + ".commands", commands.data(), sizeof(DrawIndirectCommand) * kBoxes);
+		const hv::vec3 cp = camera_->Position();
+		const float camera[3] = { cp.x, cp.y, cp.z };
+		Write(prefix + ".camera", camera, sizeof(camera));
+		const FrustumUBO frustum = camera_->GetFrustumUBO();
+		Write(prefix + ".frustum", &frustum, sizeof(frustum));
 		std::printf("clusters %zu lights %u total_indices %u\n", C, resourcesLight_->GetLightCount(), total);
 	}
 
@@ -113,6 +159,8 @@ public:
 	{
 		resourcesLight_.reset();
 		resourcesCF_.reset();
+		resourcesGBuffer_.reset();
+		scene_.Destroy();
 		pipelines_.clear();
 	}
 
@@ -133,6 +181,11 @@ private:
 	std::vector<std::unique_ptr<PipelineBase>> pipelines_;
 	PipelineAABBGenerator* aabbPtr_ = nullptr;
 	PipelineLightCulling* lightCullPtr_ = nullptr;
+	PipelinePBRClusterForward* pbrPtr_ = nullptr;
+	PipelineFrustumCulling* frustumPtr_ = nullptr;
+	std::unique_ptr<ResourcesGBufferCF> resourcesGBuffer_;
+	Scene scene_;
+	static constexpr uint32_t kBoxes = 10000; // the instance count of the README's frustum-culling figure
 	uint32_t X_, Y_, Z_;
 	float width_, height_;
 	uint32_t lightCount_, seed_;

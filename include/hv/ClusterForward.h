@@ -6,6 +6,8 @@
 //   ResourcesClusterForward    Header/Resources/ResourcesClusterForward.h:11-31, Source/.../ResourcesClusterForward.cpp:5-46
 //   PipelineAABBGenerator      Header/Pipelines/PipelineAABBGenerator.h:14-39, Source/.../PipelineAABBGenerator.cpp:8-102
 //   PipelineLightCulling       Header/Pipelines/PipelineLightCulling.h:15-36, Source/.../PipelineLightCulling.cpp:9-141
+//   PipelinePBRClusterForward  Header/Pipelines/PipelinePBRClusterForward.h:17-67 (the light loop of Scene.frag, headless)
+//   PipelineFrustumCulling     Header/Pipelines/PipelineFrustumCulling.h:9-32, Source/.../PipelineFrustumCulling.cpp:5-84
 // Type substitutions only (hv/Context.h): VulkanContext -> hv::Context, VkCommandBuffer -> stream,
 // VulkanBuffer -> hv::DeviceBuffer.  Grid size / cap / light capacity are run-time members that default
 // to ClusterForwardConfig.  Ownership as in the reference: the app owns resources and pipelines,
@@ -230,6 +232,118 @@ private:
 			"hvcf_bind_lights");
 		hv::Check(hvcf_cull(resourcesCF_->Handle(), frameIndex, commandBuffer), "hvcf_cull");
 	}
+};
+
+// ---- rows next to the culling path ---------------------------------------------------------
+
+// What the rasteriser and the material textures hand the fragment shader in the reference, as device arrays
+// (include/hvcf.h hvcf_gbuffer); plus the colour attachment the pass writes (ResourcesShared::multiSampledColorImage_).
+struct ResourcesGBufferCF : ResourcesBase
+{
+	~ResourcesGBufferCF() override { Destroy(); }
+	void Destroy() override
+	{
+		fragDepth_.Destroy(), worldPos_.Destroy(), normalRough_.Destroy(), albedoMetal_.Destroy(), color_.Destroy(), clusterIndex_.Destroy();
+	}
+	// host arrays as hvcf_host_init_gbuffer fills them
+	void Create(VulkanContext& ctx, uint32_t width, uint32_t height, const float* fragDepth, const float* worldPos,
+		const float* normalRough, const float* albedoMetal)
+	{
+		width_ = width, height_ = height;
+		const size_t P = static_cast<size_t>(width) * height;
+		fragDepth_.CreateBuffer(ctx, 4 * P), worldPos_.CreateBuffer(ctx, 16 * P), normalRough_.CreateBuffer(ctx, 16 * P);
+		albedoMetal_.CreateBuffer(ctx, 16 * P), color_.CreateBuffer(ctx, 16 * P), clusterIndex_.CreateBuffer(ctx, 4 * P);
+		fragDepth_.UploadBufferData(ctx, fragDepth, 4 * P), worldPos_.UploadBufferData(ctx, worldPos, 16 * P);
+		normalRough_.UploadBufferData(ctx, normalRough, 16 * P), albedoMetal_.UploadBufferData(ctx, albedoMetal, 16 * P);
+		ctx.WaitIdle();
+	}
+	uint32_t width_ = 0, height_ = 0;
+	VulkanBuffer fragDepth_, worldPos_, normalRough_, albedoMetal_, color_, clusterIndex_;
+};
+
+// Render using PBR materials, clustered forward renderer: the light loop of Scene.frag over the G-buffer
+// (Header/Pipelines/PipelinePBRClusterForward.h:17-67; Scene*, ResourcesIBL*, ResourcesShared* and the material pass
+// arguments of the reference constructor are the G-buffer here)
+class PipelinePBRClusterForward final : public PipelineBase
+{
+public:
+	PipelinePBRClusterForward(VulkanContext&, ResourcesGBufferCF* gbuffer, ResourcesLight* lights, ResourcesClusterForward* resourcesCF)
+		: resourcesCF_(resourcesCF), resourcesLight_(lights), gbuffer_(gbuffer)
+	{
+	}
+	~PipelinePBRClusterForward() override = default;
+
+	void SetCameraUBO(VulkanContext&, CameraUBO& ubo) override { cameraPosition_ = ubo.position; }
+	void SetPBRPushConstants(const PushConstPBR& pbrPC) { pc_ = pbrPC; }
+	// the culling pipelines already uploaded this frame's UBO into the shared context (one copy instead of the
+	// reference's three, PipelinePBRClusterForward.h:33-37); kept for call-order parity
+	void SetClusterForwardUBO(VulkanContext&, ClusterForwardUBO&) {}
+
+	void FillCommandBuffer(VulkanContext& ctx, VkCommandBuffer commandBuffer) override
+	{
+		hvcf_gbuffer g{};
+		g.width = gbuffer_->width_, g.height = gbuffer_->height_;
+		g.frag_depth = static_cast<const float*>(gbuffer_->fragDepth_.buffer_);
+		g.world_pos = static_cast<const float*>(gbuffer_->worldPos_.buffer_);
+		g.normal_rough = static_cast<const float*>(gbuffer_->normalRough_.buffer_);
+		g.albedo_metal = static_cast<const float*>(gbuffer_->albedoMetal_.buffer_);
+		const float cam[3] = { cameraPosition_.x, cameraPosition_.y, cameraPosition_.z };
+		hv::Check(hvcf_shade(resourcesCF_->Handle(), ctx.GetFrameIndex(), &g, reinterpret_cast<const hvcf_push_const_pbr*>(&pc_), cam,
+					  static_cast<float*>(gbuffer_->color_.buffer_), static_cast<uint32_t*>(gbuffer_->clusterIndex_.buffer_), commandBuffer),
+			"hvcf_shade");
+	}
+
+private:
+	PushConstPBR pc_{};
+	ResourcesClusterForward* resourcesCF_;
+	ResourcesLight* resourcesLight_;
+	ResourcesGBufferCF* gbuffer_;
+	hv::vec4 cameraPosition_{};
+};
+
+// The three members of the reference Scene that frustum culling touches (Header/Scene/Scene.h: transformedBoundingBoxBuffer_,
+// indirectBuffer_, GetInstanceCount())
+struct Scene
+{
+	VulkanBuffer transformedBoundingBoxBuffer_; // AABB[instanceCount], world space
+	VulkanBuffer indirectBuffer_;               // DrawIndirectCommand[instanceCount]
+	uint32_t instanceCount_ = 0;
+	uint32_t GetInstanceCount() const { return instanceCount_; }
+	void Create(VulkanContext& ctx, const std::vector<AABB>& boxes, const std::vector<DrawIndirectCommand>& commands)
+	{
+		instanceCount_ = static_cast<uint32_t>(boxes.size());
+		transformedBoundingBoxBuffer_.CreateBuffer(ctx, sizeof(AABB) * boxes.size());
+		indirectBuffer_.CreateBuffer(ctx, sizeof(DrawIndirectCommand) * commands.size());
+		transformedBoundingBoxBuffer_.UploadBufferData(ctx, boxes.data(), sizeof(AABB) * boxes.size());
+		indirectBuffer_.UploadBufferData(ctx, commands.data(), sizeof(DrawIndirectCommand) * commands.size());
+		ctx.WaitIdle();
+	}
+	void Destroy() { transformedBoundingBoxBuffer_.Destroy(), indirectBuffer_.Destroy(); }
+};
+
+// Compute-based frustum culling (Header/Pipelines/PipelineFrustumCulling.h:9-32, Source/.../PipelineFrustumCulling.cpp:5-84)
+class PipelineFrustumCulling final : public PipelineBase
+{
+public:
+	PipelineFrustumCulling(VulkanContext&, Scene* scene) : scene_(scene) {}
+	~PipelineFrustumCulling() override = default;
+
+	void SetCameraUBO(VulkanContext&, CameraUBO&) override {}
+	void SetFrustumUBO(VulkanContext& ctx, FrustumUBO& ubo) { frustums_[ctx.GetFrameIndex()] = ubo; }
+
+	void FillCommandBuffer(VulkanContext& ctx, VkCommandBuffer commandBuffer) override { Execute(ctx, commandBuffer, ctx.GetFrameIndex()); }
+
+private:
+	void Execute(VulkanContext& ctx, VkCommandBuffer commandBuffer, uint32_t frameIndex)
+	{
+		hv::Check(hvcf_frustum_cull(ctx.GetDeviceOrdinal(), reinterpret_cast<const hvcf_frustum_ubo*>(&frustums_[frameIndex]),
+					  static_cast<const hvcf_aabb*>(scene_->transformedBoundingBoxBuffer_.buffer_), scene_->GetInstanceCount(),
+					  static_cast<hvcf_draw_indirect_command*>(scene_->indirectBuffer_.buffer_), commandBuffer),
+			"hvcf_frustum_cull");
+	}
+
+	Scene* scene_;
+	std::array<FrustumUBO, AppConfig::FrameCount> frustums_{};
 };
 
 #endif

@@ -192,3 +192,43 @@ def test_frustum_cull_golden_and_edges(hv, oracle, gold):
         assert np.array_equal(dc.download(CMD_DT, 4)["instance_count"], oracle.frustum_cull(nan_f, edge)["instance_count"])
     finally:
         db.close(), dc.close()
+
+
+def test_headless_app_end_to_end(hv, oracle, tmp_path):
+    """hellovulkan_b200/lib/hv_cluster_forward_app: the C++ drop-in classes (include/hv/ClusterForward.h) driven in the
+    order of AppPBRClusterForward::Init / UpdateUBOs / FillCommandBuffer for 3 frames (moving light 0 and the camera);
+    every buffer it dumps is compared with the oracle."""
+    import subprocess
+    from cpu_checkers import CELL_DT, LIGHT_DT
+    app = os.path.join(os.path.dirname(HERE), "hellovulkan_b200", "lib", "hv_cluster_forward_app")
+    assert os.path.exists(app), "build() did not produce the headless driver"
+    W, H, n = 640, 400, 5000
+    prefix = str(tmp_path / "run")
+    r = subprocess.run([app, "16", "9", "24", str(W), str(H), str(n), "12345", "3", prefix], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ubo = np.fromfile(prefix + ".ubo", np.uint8)
+    cam = np.fromfile(prefix + ".camera", np.float32)
+    assert np.allclose(cam, (1.0, 1.0, 6.0))                                  # frame 2 of MainLoop
+    assert ubo.tobytes() == oracle.camera_ubo((16, 9, 24), (W, H), pos=tuple(cam)).tobytes()
+    lights = np.fromfile(prefix + ".lights", LIGHT_DT)
+    want_lights = oracle.init_lights(n)
+    want_lights["position"][0] = (0.5, 2.0, 1.0, 1.0)                          # UpdateLightPosition of frame 2
+    assert lights.tobytes() == want_lights.tobytes()
+    aabb = np.fromfile(prefix + ".aabb", AABB_DT)
+    assert aabb.tobytes() == oracle.generate_aabbs(ubo).tobytes()
+    cells, idx = np.fromfile(prefix + ".cells", CELL_DT), np.fromfile(prefix + ".indices", np.uint32)
+    wc, wi, total, _ = oracle.cull(ubo, aabb, lights)
+    assert cells.tobytes() == wc.tobytes() and idx.tobytes() == wi.tobytes()
+    g = hv.host_init_gbuffer(W, H, seed=7)
+    color = np.fromfile(prefix + ".color", np.float32).reshape(-1, 4)
+    cluster = np.fromfile(prefix + ".cluster", np.uint32)
+    want, wcluster = oracle.shade(ubo, cells, idx, lights, g, camera_position=tuple(cam))
+    assert np.array_equal(cluster, wcluster)
+    assert_colors_close(color, want)
+    frustum = np.fromfile(prefix + ".frustum", np.uint8)
+    assert frustum.tobytes() == oracle.frustum_ubo((W, H), pos=tuple(cam)).tobytes()
+    cmds = np.fromfile(prefix + ".commands", CMD_DT)
+    boxes = hv.host_init_boxes(10000, 60.0, seed=4242)
+    seeded = np.zeros(10000, CMD_DT)
+    seeded["vertex_count"], seeded["instance_count"], seeded["first_instance"] = 36, 1, np.arange(10000)
+    assert cmds.tobytes() == oracle.frustum_cull(frustum, boxes, commands=seeded).tobytes()
