@@ -109,12 +109,27 @@ struct hvcf_ctx
 	uint32_t one_light_cursor = 0;
 	cudaEvent_t one_light_events[16]{};
 
+	// device-side light animation (hvcf_set_light_animation) and batched position updates (hvcf_update_lights)
+	float* d_anim_table = nullptr;
+	float* d_base_y = nullptr;                 // [max_lights]
+	uint32_t anim_len = 0;                     // 0 = off
+	float anim_amplitude = 0.0f;
+	uint32_t anim_step[8]{};                   // per frame slot
+	uint32_t* d_upd_idx = nullptr;             // device staging of hvcf_update_lights
+	float* d_upd_xyz = nullptr;
+	uint32_t* h_upd_idx[2]{};                  // pinned, double-buffered
+	float* h_upd_xyz[2]{};
+	uint32_t upd_capacity = 0;
+	uint32_t upd_cursor = 0;
+	cudaEvent_t upd_events[2]{};
+
 	// consumer (hvcf_shade): z-slice thresholds in linear depth, per frame slot, built lazily
 	float* d_slice_thr = nullptr;              // [frame][Z+1]
 	float* h_slice_thr = nullptr;              // pinned
 	float slice_key[8][2]{};                   // sliceScaling, sliceBias of the table in the slot
 	bool slice_valid[8]{};
 
+	cudaEvent_t ubo_events[8]{};               // per frame slot: the staged UBO has been consumed
 	bool* ubo_set = nullptr;
 	bool aabb_dirty = true;
 	bool have_aabb_key = false;
@@ -156,7 +171,21 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_bin_idx);
 	cudaFree(c->d_scan_state);
 	cudaFree(c->d_trace);
+	for (int i = 0; i < 8; ++i)
+		if (c->ubo_events[i])
+			cudaEventDestroy(c->ubo_events[i]);
 	cudaFree(c->d_slice_thr);
+	cudaFree(c->d_anim_table);
+	cudaFree(c->d_base_y);
+	cudaFree(c->d_upd_idx);
+	cudaFree(c->d_upd_xyz);
+	for (int i = 0; i < 2; ++i)
+	{
+		cudaFreeHost(c->h_upd_idx[i]);
+		cudaFreeHost(c->h_upd_xyz[i]);
+		if (c->upd_events[i])
+			cudaEventDestroy(c->upd_events[i]);
+	}
 	cudaFreeHost(c->h_slice_thr);
 	cudaFreeHost(c->h_ubo);
 	cudaFreeHost(c->h_zplanes);
@@ -412,6 +441,8 @@ int hvcf_set_lights(hvcf_ctx* ctx, const void* lights, uint32_t n, int src_is_de
 			src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
 	ctx->num_lights = n;
 	ctx->bound_lights = nullptr;
+	if (ctx->anim_len) // new lights, new rest positions
+		HVCF_CUDA(launch_capture_base_y(ctx->d_lights, n, ctx->d_base_y, static_cast<cudaStream_t>(stream)));
 	return HVCF_OK;
 }
 
@@ -443,6 +474,97 @@ int hvcf_update_light(hvcf_ctx* ctx, uint32_t index, const float xyz[3], void* s
 	return HVCF_OK;
 }
 
+int hvcf_update_lights(hvcf_ctx* ctx, const uint32_t* indices, const float* xyz, uint32_t count, void* stream)
+{
+	if (!ctx || (count && (!indices || !xyz)))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_update_lights: null argument");
+	if (count == 0)
+		return HVCF_OK;
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (count > ctx->upd_capacity)
+	{
+		// grow: everything in flight on the old staging must be done first
+		HVCF_CUDA(cudaDeviceSynchronize());
+		uint32_t cap = ctx->upd_capacity ? ctx->upd_capacity : 1024;
+		while (cap < count)
+			cap *= 2;
+		cudaFree(ctx->d_upd_idx), cudaFree(ctx->d_upd_xyz);
+		ctx->d_upd_idx = nullptr, ctx->d_upd_xyz = nullptr;
+		for (int i = 0; i < 2; ++i)
+		{
+			cudaFreeHost(ctx->h_upd_idx[i]), cudaFreeHost(ctx->h_upd_xyz[i]);
+			ctx->h_upd_idx[i] = nullptr, ctx->h_upd_xyz[i] = nullptr;
+		}
+		ctx->upd_capacity = 0;
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_upd_idx), sizeof(uint32_t) * 2 * cap));
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_upd_xyz), sizeof(float) * 3 * 2 * cap));
+		for (int i = 0; i < 2; ++i)
+		{
+			HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_upd_idx[i]), sizeof(uint32_t) * cap));
+			HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_upd_xyz[i]), sizeof(float) * 3 * cap));
+			if (!ctx->upd_events[i])
+				HVCF_CUDA(cudaEventCreateWithFlags(&ctx->upd_events[i], cudaEventDisableTiming));
+		}
+		ctx->upd_capacity = cap;
+	}
+	// double-buffered pinned staging: the caller's arrays are free again when this returns, and the copy of batch k
+	// overlaps whatever the GPU still does with batch k-1
+	const uint32_t slot = ctx->upd_cursor++ & 1u;
+	HVCF_CUDA(cudaEventSynchronize(ctx->upd_events[slot]));
+	memcpy(ctx->h_upd_idx[slot], indices, sizeof(uint32_t) * count);
+	memcpy(ctx->h_upd_xyz[slot], xyz, sizeof(float) * 3 * count);
+	uint32_t* di = ctx->d_upd_idx + static_cast<size_t>(slot) * ctx->upd_capacity;
+	float* dx = ctx->d_upd_xyz + static_cast<size_t>(slot) * 3 * ctx->upd_capacity;
+	HVCF_CUDA(cudaMemcpyAsync(di, ctx->h_upd_idx[slot], sizeof(uint32_t) * count, cudaMemcpyHostToDevice, s));
+	HVCF_CUDA(cudaMemcpyAsync(dx, ctx->h_upd_xyz[slot], sizeof(float) * 3 * count, cudaMemcpyHostToDevice, s));
+	HVCF_CUDA(cudaEventRecord(ctx->upd_events[slot], s));
+	hvcf_light_data* lights = const_cast<hvcf_light_data*>(ctx->bound_lights ? ctx->bound_lights : ctx->d_lights);
+	HVCF_CUDA(launch_scatter_positions(lights, ctx->num_lights, di, dx, count, ctx->anim_len ? ctx->d_base_y : nullptr, s));
+	return HVCF_OK;
+}
+
+int hvcf_set_light_animation(hvcf_ctx* ctx, const float* table, uint32_t table_len, float amplitude, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_light_animation: null context");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (!table || table_len == 0)
+	{
+		ctx->anim_len = 0; // off; the light buffer keeps the positions of the last animated frame
+		return HVCF_OK;
+	}
+	if (table_len & (table_len - 1))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_light_animation: table_len %u is not a power of two", table_len);
+	if (table_len != ctx->anim_len)
+	{
+		HVCF_CUDA(cudaStreamSynchronize(s));
+		cudaFree(ctx->d_anim_table);
+		ctx->d_anim_table = nullptr;
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_anim_table), sizeof(float) * table_len));
+	}
+	if (!ctx->d_base_y)
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_base_y), sizeof(float) * (ctx->max_lights ? ctx->max_lights : 1)));
+	HVCF_CUDA(cudaMemcpyAsync(ctx->d_anim_table, table, sizeof(float) * table_len, cudaMemcpyHostToDevice, s));
+	HVCF_CUDA(cudaStreamSynchronize(s)); // `table` may be pageable and go away
+	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+	HVCF_CUDA(launch_capture_base_y(lights, ctx->num_lights, ctx->d_base_y, s));
+	ctx->anim_len = table_len;
+	ctx->anim_amplitude = amplitude;
+	return HVCF_OK;
+}
+
+int hvcf_set_animation_step(hvcf_ctx* ctx, uint32_t frame, uint32_t step)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_animation_step: null context");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_animation_step: frame %u >= frame_count %u", frame, ctx->frame_count);
+	ctx->anim_step[frame] = step;
+	return HVCF_OK;
+}
+
 int hvcf_set_ubo(hvcf_ctx* ctx, uint32_t frame, const hvcf_cluster_forward_ubo* ubo, void* stream)
 {
 	if (!ctx || !ubo)
@@ -453,9 +575,16 @@ int hvcf_set_ubo(hvcf_ctx* ctx, uint32_t frame, const hvcf_cluster_forward_ubo* 
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_ubo: ubo grid %ux%ux%u != context grid %ux%ux%u", ubo->slice_count_x,
 			ubo->slice_count_y, ubo->slice_count_z, ctx->X, ctx->Y, ctx->Z);
 	HVCF_CUDA(cudaSetDevice(ctx->device));
+	// the slot's previous copy out of pinned staging must have executed before the slot is overwritten: the fence the
+	// reference takes at frame start (vkWaitForFences, AppBase.cpp:96-100), scoped to the UBO slot
+	if (!ctx->ubo_events[frame])
+		HVCF_CUDA(cudaEventCreateWithFlags(&ctx->ubo_events[frame], cudaEventDisableTiming));
+	else
+		HVCF_CUDA(cudaEventSynchronize(ctx->ubo_events[frame]));
 	ctx->h_ubo[frame] = *ubo;
 	HVCF_CUDA(cudaMemcpyAsync(&ctx->d_ubo[frame], &ctx->h_ubo[frame], sizeof(hvcf_cluster_forward_ubo), cudaMemcpyHostToDevice,
 		static_cast<cudaStream_t>(stream)));
+	HVCF_CUDA(cudaEventRecord(ctx->ubo_events[frame], static_cast<cudaStream_t>(stream)));
 	ctx->ubo_set[frame] = true;
 	// AABBs depend on the inverse projection, near/far and the grid only
 	float key[18];
@@ -537,6 +666,18 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
 	const uint32_t n = ctx->num_lights;
 	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+	LightAnim anim_storage{};
+	const LightAnim* anim = nullptr;
+	if (ctx->anim_len && n)
+	{
+		anim_storage.base_y = ctx->d_base_y;
+		anim_storage.table = ctx->d_anim_table;
+		anim_storage.mask = ctx->anim_len - 1;
+		anim_storage.step = ctx->anim_step[frame];
+		anim_storage.amplitude = ctx->anim_amplitude;
+		anim_storage.lights_rw = const_cast<hvcf_light_data*>(lights); // the moved position is written back, as UpdateLightPosition does
+		anim = &anim_storage;
+	}
 	if (ctx->hier)
 	{
 		// at least one (all-padding) tile, so that pass 2 always writes the light cells
@@ -547,7 +688,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		const uint32_t chunks = hier_num_chunks(ctx->h_num_segs);
 		// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the transform kernel
 		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
-			ctx->cluster_count * chunks, stats, s));
+			ctx->cluster_count * chunks, stats, s, anim));
 		HierParams p = hier_params(ctx, frame);
 		if (!ctx->hier_v1)
 		{
@@ -607,7 +748,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		num_segs = (tiles_total + tiles_per_seg - 1) / tiles_per_seg; // no empty segment
 	if (n)
 	{
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, nullptr, 0, nullptr, s));
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, nullptr, 0, nullptr, s, anim));
 		CullParams p;
 		p.lights_view = ctx->d_lights_view;
 		p.aabbs = ctx->d_aabb;

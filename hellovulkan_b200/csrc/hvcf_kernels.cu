@@ -73,9 +73,10 @@ __global__ void __launch_bounds__(128) aabb_generate_kernel(const hvcf_cluster_f
 // One thread per lane-pair of the culling layout (hvcf_device.cuh): two 48 B records in, two float4 out
 // (fully coalesced 128-bit stores).  HBM-bound: 64 B per light.
 // ======================================================================================================
+template <bool ANIM>
 __global__ void __launch_bounds__(256) light_transform_kernel(const hvcf_cluster_forward_ubo* __restrict__ ubo,
-	const hvcf_light_data* __restrict__ lights, uint32_t num_lights, uint32_t num_pairs, float4* __restrict__ out,
-	uint32_t* __restrict__ zero, uint32_t zero_words, DeviceStats* __restrict__ stats)
+	const hvcf_light_data* lights, uint32_t num_lights, uint32_t num_pairs, float4* __restrict__ out,
+	uint32_t* __restrict__ zero, uint32_t zero_words, DeviceStats* __restrict__ stats, const LightAnim anim)
 {
 	grid_dep_launch();
 	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -101,8 +102,13 @@ __global__ void __launch_bounds__(256) light_transform_kernel(const hvcf_cluster
 		const uint32_t i = g * kGroupLights + h * 32 + l;
 		if (i < num_lights)
 		{
-			const float4 pw = *reinterpret_cast<const float4*>(lights[i].position);
+			float4 pw = *reinterpret_cast<const float4*>(lights[i].position);
 			const float radius = lights[i].radius;
+			if (ANIM)
+			{
+				pw.y = __fadd_rn(__ldg(anim.base_y + i), __fmul_rn(anim.amplitude, __ldg(anim.table + ((anim.step + i) & anim.mask))));
+				anim.lights_rw[i].position[1] = pw.y;
+			}
 			x[h] = mat_row_dot(view, 0, pw.x, pw.y, pw.z, pw.w);
 			y[h] = mat_row_dot(view, 1, pw.x, pw.y, pw.z, pw.w);
 			z[h] = mat_row_dot(view, 2, pw.x, pw.y, pw.z, pw.w);
@@ -521,13 +527,58 @@ cudaError_t launch_aabb_generate(const hvcf_cluster_forward_ubo* ubo, const floa
 
 cudaError_t launch_light_transform(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_data* lights,
 	uint32_t num_lights, uint32_t padded_lights, float4* out, uint32_t* zero, uint32_t zero_words, DeviceStats* stats,
-	cudaStream_t stream)
+	cudaStream_t stream, const LightAnim* anim)
 {
 	const uint32_t pairs = padded_lights / 2;
 	if (pairs == 0 && zero_words == 0 && !stats)
 		return cudaSuccess;
 	const uint32_t blocks = pairs ? (pairs + 255) / 256 : 1;
-	light_transform_kernel<<<blocks, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out, zero, zero_words, stats);
+	if (anim)
+		light_transform_kernel<true><<<blocks, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out, zero, zero_words, stats, *anim);
+	else
+		light_transform_kernel<false><<<blocks, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out, zero, zero_words, stats, LightAnim{});
+	return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) capture_base_y_kernel(const hvcf_light_data* __restrict__ lights, uint32_t n, float* __restrict__ base_y)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n)
+		base_y[i] = lights[i].position[1];
+}
+
+cudaError_t launch_capture_base_y(const hvcf_light_data* lights, uint32_t num_lights, float* base_y, cudaStream_t stream)
+{
+	if (num_lights == 0)
+		return cudaSuccess;
+	capture_base_y_kernel<<<(num_lights + 255) / 256, 256, 0, stream>>>(lights, num_lights, base_y);
+	return cudaGetLastError();
+}
+
+// duplicates in `indices` resolve to the LAST occurrence, as a sequence of UpdateLightPosition calls would
+__global__ void __launch_bounds__(256) scatter_positions_kernel(hvcf_light_data* __restrict__ lights, uint32_t num_lights,
+	const uint32_t* __restrict__ indices, const float* __restrict__ xyz, uint32_t count, float* __restrict__ base_y)
+{
+	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= count)
+		return;
+	const uint32_t i = indices[k];
+	if (i >= num_lights)
+		return; // ResourcesLight::UpdateLightPosition ignores an out-of-range index
+	for (uint32_t j = k + 1; j < count && j < k + 64; ++j) // cheap local duplicate check; the API documents uniqueness beyond it
+		if (indices[j] == i)
+			return;
+	*reinterpret_cast<float4*>(lights[i].position) = make_float4(xyz[3 * k], xyz[3 * k + 1], xyz[3 * k + 2], 1.0f);
+	if (base_y)
+		base_y[i] = xyz[3 * k + 1];
+}
+
+cudaError_t launch_scatter_positions(hvcf_light_data* lights, uint32_t num_lights, const uint32_t* indices, const float* xyz,
+	uint32_t count, float* base_y, cudaStream_t stream)
+{
+	if (count == 0)
+		return cudaSuccess;
+	scatter_positions_kernel<<<(count + 255) / 256, 256, 0, stream>>>(lights, num_lights, indices, xyz, count, base_y);
 	return cudaGetLastError();
 }
 

@@ -38,12 +38,31 @@ struct ScatterParams
 	uint32_t* frame_total;         // globalIndexCountBuffers_[frame] or NULL
 };
 
+// Device-side light animation of the fly-through (BASELINE.json configs[4]):
+//   position.y = base_y[i] + amplitude * table[(step + i) & mask]
+// evaluated with one rounded multiply and one rounded add, so that a host evaluation of the same expression is
+// bit-identical; the transform kernel applies it on the fly and writes the moved position back into the light
+// buffer (what ResourcesLight::UpdateLightPosition does per light, ResourcesLight.cpp:21-29).
+struct LightAnim
+{
+	const float* base_y;          // [num_lights] position.y at hvcf_set_light_animation time
+	const float* table;           // [mask + 1]
+	uint32_t mask;
+	uint32_t step;
+	float amplitude;
+	hvcf_light_data* lights_rw;   // same buffer as `lights`
+};
+
 cudaError_t launch_aabb_generate(const hvcf_cluster_forward_ubo* ubo, const float* zplanes, hvcf_aabb* out,
 	uint32_t cluster_count, cudaStream_t stream);
 // also clears `zero_words` words at `zero` and the work counters `stats` (either may be null / 0)
 cudaError_t launch_light_transform(const hvcf_cluster_forward_ubo* ubo, const hvcf_light_data* lights,
 	uint32_t num_lights, uint32_t padded_lights, float4* out, uint32_t* zero, uint32_t zero_words, DeviceStats* stats,
-	cudaStream_t stream);
+	cudaStream_t stream, const LightAnim* anim = nullptr);
+cudaError_t launch_capture_base_y(const hvcf_light_data* lights, uint32_t num_lights, float* base_y, cudaStream_t stream);
+// lights[indices[k]].position = (xyz[3k], xyz[3k+1], xyz[3k+2], 1): a batch of ResourcesLight::UpdateLightPosition
+cudaError_t launch_scatter_positions(hvcf_light_data* lights, uint32_t num_lights, const uint32_t* indices, const float* xyz,
+	uint32_t count, float* base_y, cudaStream_t stream);
 // variant: 0..2 = packed FP32x2 with 1/2/4 clusters per warp, 3..5 = scalar FP32 with 1/2/4
 constexpr int kNumCullVariants = 6;
 uint32_t cull_variant_clusters_per_cta(int variant);

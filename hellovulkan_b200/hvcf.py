@@ -79,6 +79,7 @@ EXPORTS = [
     "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
+    "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -129,6 +130,9 @@ def load():
     lib.hvcf_debug_trace.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
     lib.hvcf_get_timing.argtypes = [vp, u32, f3, f3]
     lib.hvcf_measure_fp32_issue_rate.argtypes = [i32, ctypes.POINTER(ctypes.c_double)]
+    lib.hvcf_update_lights.argtypes = [vp, vp, vp, u32, vp]
+    lib.hvcf_set_light_animation.argtypes = [vp, vp, u32, ctypes.c_float, vp]
+    lib.hvcf_set_animation_step.argtypes = [vp, u32, u32]
     lib.hvcf_shade.argtypes = [vp, u32, ctypes.POINTER(GBuffer), ctypes.POINTER(PushConstPBR), f3, vp, vp, vp]
     lib.hvcf_host_init_gbuffer.argtypes = [u32, f3, f3, u32, u32, vp, vp, vp, vp]
     lib.hvcf_frustum_cull.argtypes = [i32, vp, vp, u32, vp, vp]
@@ -264,6 +268,35 @@ def frustum_cull(frustum, boxes_ptr, count, commands_ptr, device=-1, stream=None
     _check(load().hvcf_frustum_cull(device, _ptr(frustum), boxes_ptr, count, commands_ptr, stream))
 
 
+# ---- fly-through of BASELINE.json configs[4]: camera orbit + animated lights --------------
+FLY_FRAMES = 1024
+FLY_AMPLITUDE = 0.5
+
+
+def fly_table():
+    """T[k] = sin(2 pi k / 1024) as float32 (host libm, double -> float): y_f,i = y0_i + 0.5 * T[(4 f + i) mod 1024]."""
+    return np.sin(2.0 * np.pi * np.arange(FLY_FRAMES, dtype=np.float64) / FLY_FRAMES).astype(np.float32)
+
+
+def fly_step(f):
+    return (4 * f) % FLY_FRAMES
+
+
+def fly_camera_pos(f):
+    th = 2.0 * np.pi * f / FLY_FRAMES
+    return (float(np.float32(6.0 * np.sin(th))), float(np.float32(1.0 + 0.5 * np.sin(2.0 * th))), float(np.float32(6.0 * np.cos(th))))
+
+
+def fly_lights_host(base, f, table=None):
+    """Host statement of the device animation (numpy float32: one rounded multiply, one rounded add)."""
+    table = fly_table() if table is None else table
+    out = base.copy()
+    i = np.arange(len(base), dtype=np.uint32)
+    t = table[(np.uint32(fly_step(f)) + i) & np.uint32(len(table) - 1)]
+    out["position"][:, 1] = base["position"][:, 1] + np.float32(FLY_AMPLITUDE) * t
+    return out
+
+
 def measure_fp32_issue_rate(device=-1):
     """lane-operations per second of a non-FMA FADD/FMUL loop on `device` (roofline denominator)."""
     v = ctypes.c_double(0.0)
@@ -326,6 +359,30 @@ class Context:
     def update_light(self, index, xyz, stream=None):
         arr = (ctypes.c_float * 3)(*[float(v) for v in xyz])
         _check(self.lib.hvcf_update_light(self.handle, index, arr, stream))
+
+    def update_lights(self, indices, xyz, stream=None):
+        """A batch of ResourcesLight::UpdateLightPosition: indices [n] uint32, xyz [n,3] float32 (host)."""
+        indices = np.ascontiguousarray(indices, np.uint32)
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        assert len(indices) == len(xyz)
+        _check(self.lib.hvcf_update_lights(self.handle, _ptr(indices), _ptr(xyz), len(indices), stream))
+
+    def set_light_animation(self, table, amplitude, stream=None):
+        """position.y = y0 + amplitude * table[(step + i) & (len - 1)] from the next cull on; table=None switches it off."""
+        if table is None:
+            _check(self.lib.hvcf_set_light_animation(self.handle, None, 0, 0.0, stream))
+            return
+        table = np.ascontiguousarray(table, np.float32)
+        _check(self.lib.hvcf_set_light_animation(self.handle, _ptr(table), len(table), float(amplitude), stream))
+
+    def set_animation_step(self, frame, step):
+        _check(self.lib.hvcf_set_animation_step(self.handle, frame, int(step) & 0xffffffff))
+
+    def download_lights(self, n, stream=None):
+        out = np.zeros(n, LIGHT_DT)
+        b = self.buffers()
+        _check(self.lib.hvcf_device_download(_ptr(out), ctypes.c_void_p(b.lights), 0, out.nbytes, stream))
+        return out
 
     def set_ubo(self, frame, ubo, stream=None):
         ubo = np.ascontiguousarray(ubo).view(np.uint8)

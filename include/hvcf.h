@@ -197,6 +197,24 @@ HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kern
 HVCF_API int hvcf_measure_fp32_issue_rate(int device, double* out_lane_ops_per_second);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Light upload / animation path: what precedes the culling pass when lights move.
+ * ------------------------------------------------------------------------------------------------- */
+/* A batch of ResourcesLight::UpdateLightPosition (Source/Resources/ResourcesLight.cpp:21-29): for k < count,
+ * lights[indices[k]].position = (xyz[3k], xyz[3k+1], xyz[3k+2], 1).  Host arrays; staged through double-buffered
+ * pinned memory (free again on return), one scatter kernel on `stream`.  Out-of-range indices are ignored as in the
+ * reference.  Indices of one batch should be unique (of duplicates closer than 64 entries the last wins). */
+HVCF_API int hvcf_update_lights(hvcf_ctx* ctx, const uint32_t* indices, const float* xyz, uint32_t count, void* stream);
+/* Device-side animation for the fly-through of BASELINE.json configs[4] (synthetic; the reference only moves light 0
+ * from the UI, ResourcesLight.h:68-72): from now on every hvcf_cull(frame) first sets
+ *     lights[i].position.y = y0[i] + amplitude * table[(step[frame] + i) & (table_len - 1)]
+ * (one rounded multiply, one rounded add: a host evaluation of the same expression is bit-identical), y0 being
+ * position.y at the time of this call, and writes it back into the light buffer for the fragment pass.  The update is
+ * fused into the per-frame light transform: no extra pass over the lights, no host->device light traffic.
+ * table: host floats, table_len a power of two; NULL / 0 switches the animation off. */
+HVCF_API int hvcf_set_light_animation(hvcf_ctx* ctx, const float* table, uint32_t table_len, float amplitude, void* stream);
+HVCF_API int hvcf_set_animation_step(hvcf_ctx* ctx, uint32_t frame, uint32_t step);
+
+/* ---------------------------------------------------------------------------------------------------
  * Consumer: the light loop of the PBR cluster-forward fragment pass as a CUDA kernel.
  * Replaces, headless: PipelinePBRClusterForward::FillCommandBuffer (Source/Pipelines/PipelinePBRClusterForward.cpp
  * :88-143) for the part of Shaders/ClusteredForward/Scene.frag that reads this library's outputs -- lines 55-78
