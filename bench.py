@@ -413,6 +413,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_next_rows:
         try:
             next_rows = run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush)
+            next_rows.update(run_extras(args, hvcf, local, stream, sp, flush))
         except Exception as e:  # the headline line must still be printed
             next_rows = {"error": f"{type(e).__name__}: {e}"}
 
@@ -539,6 +540,59 @@ def run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush):
     fr["note"] = ("FrustumCulling.comp, one event pair around a single launch (launch latency included); the reference README "
                   "quotes < 25 us for 10,000 AABBs on unnamed hardware (README.md:63)")
     out["frustum"] = fr
+    return out
+
+
+def run_extras(args, hvcf, local, stream, sp, flush):
+    """Two figures SURVEY.md 8(d) asks for beside the headline:
+    aabb_generation  AABBGenerator.comp alone, in microseconds, grids A / B / C (runs only when the projection changes);
+    stress           the no-early-exit variant: grid A x 2^20 lights (north_star's target shape) with the cap raised from
+                     150 to 4,096 so that executed ~ nominal tests, brute-force mode -> the cull kernel's fraction of the
+                     measured FP32 issue rate when early exit cannot help."""
+    import torch
+    out = {"aabb_generation": {}}
+    for name, (grid, screen) in {"A": ((16, 9, 24), (2560, 1600)), "B": ((32, 18, 48), (3840, 2160)), "C": ((64, 36, 96), (3840, 2160))}.items():
+        with hvcf.Context(grid=grid, max_lights=16, device=local, mode=hvcf.MODE_BRUTE) as c:
+            c.set_ubo(0, hvcf.host_camera_ubo(grid, screen), sp)
+            us = []
+            for i in range(13):
+                flush.zero_()
+                c.mark_aabb_dirty()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                c.generate_aabbs(0, sp)
+                b.record(stream)
+                b.synchronize()
+                if i >= 3:
+                    us.append(a.elapsed_time(b) * 1e3)
+            C = grid[0] * grid[1] * grid[2]
+            out["aabb_generation"][name] = {"clusters": C, "us": float(np.median(us)), "us_min": float(min(us)), "bytes_out": 32 * C,
+                                            "note": "slice-plane table upload (4 B x (Z+1)) + one kernel, event pair around both"}
+    grid, screen, n = WORKLOADS["A1M"]
+    cap = 4096
+    C = grid[0] * grid[1] * grid[2]
+    with hvcf.Context(grid=grid, max_lights=n, max_lights_per_cluster=cap, device=local, mode=hvcf.MODE_BRUTE) as c:
+        c.set_lights(hvcf.host_init_lights(n), sp)
+        c.set_ubo(0, hvcf.host_camera_ubo(grid, screen), sp)
+        for _ in range(2):
+            c.cull(0, sp)
+        c.set_timing(True)
+        k_ms, t_ms = [], []
+        for _ in range(5):
+            flush.zero_()
+            c.cull(0, sp)
+            km, tm = c.timing(0)
+            k_ms.append(km), t_ms.append(tm)
+        st = c.stats(0, sp)
+        c.set_timing(False)
+    rate = hvcf.measure_fp32_issue_rate(local)
+    km = float(np.median(k_ms))
+    out["stress_no_early_exit"] = {"workload": "A1M, max_lights_per_cluster 4096, mode brute", "nominal_tests": C * n,
+                                   "executed_tests": st["executed_tests"], "executed_over_nominal": st["executed_tests"] / (C * n),
+                                   "total_indices": st["total_indices"], "overflow_clusters": st["overflow_clusters"],
+                                   "cull_kernel_ms": km, "step_ms": float(np.median(t_ms)),
+                                   "achieved_tlaneops": st["executed_tests"] * LANE_OPS_PER_TEST / (km * 1e-3) / 1e12,
+                                   "peak_tlaneops": rate / 1e12, "frac": st["executed_tests"] * LANE_OPS_PER_TEST / (km * 1e-3) / rate}
     return out
 
 
