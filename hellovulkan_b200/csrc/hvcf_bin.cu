@@ -235,6 +235,29 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	if (WRITE && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && p.frame_total)
 		*p.frame_total = index_base + *p.shard_total; // globalIndex after the frame (LightCulling.comp:21,79)
 
+	// ---- nothing to do for this (unit, segment)?  Most warp programs of the write pass own no output (clusters fill
+	// their quota in the early segments) and many of the count pass already know their clusters are full: leave before
+	// the union reductions and the tile walk.  (Measured on B200, B1M: 0.295 -> 0.283 ms/frame.  Staging the survivor
+	// slots up front with TMA bulk copies was also tried here and LOST -- 0.362 ms: most slots hold a handful of
+	// records, so speculative 1 KiB reads per (unit, tile) cost more L2 traffic than the round trips they hide.)
+	{
+		bool want = false;
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+			want = want || active[k];
+		if (!p.trace && !__any_sync(0xffffffffu, want))
+		{
+			if (!WRITE)
+			{
+#pragma unroll
+				for (int k = 0; k < K; ++k)
+					if (cidx[k] != kSkip)
+						p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = 0u;
+			}
+			return;
+		}
+	}
+
 	// ---- block union boxes (level 1) over the lanes that still want hits ------------------------------
 	float ulo[K][3], uhi[K][3];
 	uint32_t alive[K]; // lanes of the block that still want hits
