@@ -73,7 +73,7 @@ struct hvcf_ctx
 	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
-	uint32_t* d_hscratch = nullptr;          // cum[h_max_chunks][cluster_count]
+	uint32_t* d_hscratch = nullptr;          // cum[cluster_count][kHMaxChunks]
 	uint32_t* d_hoffsets = nullptr;
 	uint32_t* d_hlane_cluster = nullptr;
 	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
@@ -358,7 +358,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	{
 		HVCF_ALLOC(c->d_hseg_counts, sizeof(uint32_t) * Cs * c->h_max_segs);
 		HVCF_ALLOC(c->d_hseg_prefix, sizeof(uint32_t) * Cs * c->h_max_segs);
-		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * c->h_max_chunks);
+		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * kHMaxChunks);
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
 		if (!c->hier_v1)
@@ -685,10 +685,11 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		const uint32_t tiles_total = padded / kTileLights;
 		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
 		ctx->h_tiles_total = tiles_total;
-		const uint32_t chunks = hier_num_chunks(ctx->h_num_segs);
+		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
 		// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the transform kernel
 		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
-			ctx->cluster_count * chunks, stats, s, anim));
+			ctx->cluster_count * kHMaxChunks, stats, s, anim));
 		HierParams p = hier_params(ctx, frame);
 		if (!ctx->hier_v1)
 		{

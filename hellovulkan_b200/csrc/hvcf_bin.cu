@@ -14,7 +14,7 @@
 //
 // Exactness, ordering, early exit and the count -> finalize -> write scheme are those of hvcf_hier.cu (see its
 // header): union boxes are exactly conservative because they run the same uncontracted float sequence, light
-// order is never disturbed, and cum[chunk][cluster] lower bounds only remove work that cannot matter.
+// order is never disturbed, and cum[cluster][chunk] lower bounds only remove work that cannot matter.
 #include "hvcf_hier.cuh"
 
 namespace hvcf
@@ -214,11 +214,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			}
 			else
 			{
-				uint32_t prior = 0;
-#pragma unroll
-				for (uint32_t c = 0; c < kHMaxChunks; ++c)
-					if (c < chunk)
-						prior += __ldcg(&p.cum[static_cast<size_t>(c) * p.cluster_count + cidx[k]]);
+				const uint32_t prior = hier_prior_hits(p.cum, cidx[k], chunk);
 				if (prior < p.cap)
 				{
 					active[k] = true;
@@ -442,7 +438,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			{
 				p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = cnt[k];
 				if (cnt[k])
-					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
+					atomicAdd(&p.cum[static_cast<size_t>(cidx[k]) * kHMaxChunks + chunk], cnt[k]);
 			}
 	}
 	if (p.trace)

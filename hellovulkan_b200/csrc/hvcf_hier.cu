@@ -23,7 +23,7 @@
 //
 // Early exit (LightCulling.comp:71, `lightIter < MAX_LIGHTS_PER_CLUSTER`) across concurrently running
 // segments: segments are grouped into chunks of doubling size; a finishing CTA adds its counts to
-// cum[chunk][cluster]; a starting CTA sums cum over the EARLIER chunks and drops every cluster that already
+// cum[cluster][chunk]; a starting CTA sums cum over the EARLIER chunks and drops every cluster that already
 // holds `cap` hits.  Whatever it reads is a lower bound of the hits in earlier segments (counts only grow
 // towards the true value), and a lower bound >= cap proves that the first `cap` entries lie before this
 // segment -- so knowledge only ever removes work that cannot matter, and the result does not depend on
@@ -129,11 +129,7 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 			}
 			else
 			{
-				uint32_t prior = 0;
-#pragma unroll
-				for (uint32_t c = 0; c < kHMaxChunks; ++c)
-					if (c < chunk)
-						prior += __ldcg(&p.cum[static_cast<size_t>(c) * p.cluster_count + cidx[k]]);
+				const uint32_t prior = hier_prior_hits(p.cum, cidx[k], chunk);
 				if (prior < p.cap)
 				{
 					active[k] = true;
@@ -350,7 +346,7 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 			{
 				p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = cnt[k];
 				if (cnt[k])
-					atomicAdd(&p.cum[static_cast<size_t>(chunk) * p.cluster_count + cidx[k]], cnt[k]);
+					atomicAdd(&p.cum[static_cast<size_t>(cidx[k]) * kHMaxChunks + chunk], cnt[k]);
 			}
 	}
 	if (p.trace)

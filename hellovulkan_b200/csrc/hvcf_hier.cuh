@@ -8,7 +8,6 @@ namespace hvcf
 
 constexpr uint32_t kSkip = 0xffffffffu;
 constexpr uint32_t kCand = 4;       // level-2 candidates in flight per trip
-constexpr uint32_t kHMaxChunks = 8; // 256 segments at most (hier_num_chunks(256) == 7)
 
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p)
 {
@@ -63,6 +62,26 @@ __device__ __forceinline__ void sphere_box_hit2(const float4& a, const float4& b
 	unpack2(mul2(dz, dz), sz0, sz1);
 	h0 = __fadd_rn(__fadd_rn(sx0, sy0), sz0) < b.z;
 	h1 = __fadd_rn(__fadd_rn(sx1, sy1), sz1) < b.w;
+}
+
+// hits of the chunks before `chunk` for one cluster.  cum is laid out [cluster][kHMaxChunks] so that the whole row is two
+// 128-bit loads (it was [chunk][cluster] with one predicated 32-bit load per chunk: the hottest line of the count pass,
+// 10 % of its instructions and the most stall samples, profiles/r01b).  ld.global.cg: other SMs add to it while we read;
+// any value read is a lower bound of the true count, which is all the early exit needs (hvcf_hier.cu header).
+static_assert(kHMaxChunks == 8, "hier_prior_hits reads the row as two uint4");
+__device__ __forceinline__ uint32_t hier_prior_hits(const uint32_t* cum, uint32_t cluster, uint32_t chunk)
+{
+	if (chunk == 0)
+		return 0u;
+	const uint4* row = reinterpret_cast<const uint4*>(cum + static_cast<size_t>(cluster) * kHMaxChunks);
+	const uint4 a = __ldcg(row);
+	uint32_t prior = a.x + (chunk > 1 ? a.y : 0u) + (chunk > 2 ? a.z : 0u) + (chunk > 3 ? a.w : 0u);
+	if (chunk > 4)
+	{
+		const uint4 b = __ldcg(row + 1);
+		prior += b.x + (chunk > 5 ? b.y : 0u) + (chunk > 6 ? b.z : 0u) + (chunk > 7 ? b.w : 0u);
+	}
+	return prior;
 }
 
 // segment -> chunk: chunk 0 = segments [0,4), chunk c >= 1 = segments [2^(c+1), 2^(c+2))

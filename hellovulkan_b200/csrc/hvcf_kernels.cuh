@@ -76,6 +76,7 @@ cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream);
 cudaError_t launch_fp32_issue_rate(float* sink, uint32_t blocks, uint32_t iters, cudaStream_t stream);
 
 // ---- HVCF_MODE_HIERARCHICAL (hvcf_hier.cu) -------------------------------------------------------------
+constexpr uint32_t kHMaxChunks = 8; // early-exit chunks per cluster: 256 segments at most (hier_num_chunks(256) == 7)
 struct HierPlan
 {
 	uint32_t bx, by, bz;      // cluster block shape, bx * by * bz == 32 (one lane per cluster)
