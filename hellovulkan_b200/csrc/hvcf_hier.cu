@@ -377,7 +377,6 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 // warp-wide decoupled look-back; the state words carry the frame's epoch, so they never need clearing.
 // ======================================================================================================
 constexpr uint32_t kFinWarps = 8;
-constexpr uint32_t kFinMaxGroup = 256 / kFinWarps; // segments per warp at most (num_segs <= 256)
 
 __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const FinalizeParams p)
 {
@@ -388,15 +387,23 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 	grid_dep_launch();
 	grid_dep_wait();
 	const uint32_t group = (p.num_segs + kFinWarps - 1) / kFinWarps;
-	const uint32_t s0 = warp * group, s1 = min(s0 + group, p.num_segs);
-	uint32_t n[kFinMaxGroup];
+	const uint32_t s0 = min(warp * group, p.num_segs), s1 = min(s0 + group, p.num_segs);
+	// two sweeps over this warp's segments instead of holding all of them in registers (the 32-deep register array cost
+	// 120 registers = 2 CTAs per SM; the counts were written by the previous kernel and sit in L2, so the second read is
+	// cheap and the occupancy is what hides the latency): sweep 1 sums, sweep 2 turns counts into prefixes
+	const uint32_t* col = p.seg_counts + c;
 	uint32_t part = 0;
-#pragma unroll
-	for (uint32_t i = 0; i < kFinMaxGroup; ++i)
+	if (valid)
 	{
-		const uint32_t s = s0 + i;
-		n[i] = (valid && s < s1) ? p.seg_counts[static_cast<size_t>(s) * p.cluster_count + c] : 0u;
-		part += n[i];
+		uint32_t s = s0;
+		for (; s + 4 <= s1; s += 4)
+		{
+			const uint32_t a = col[static_cast<size_t>(s) * p.cluster_count], b = col[static_cast<size_t>(s + 1) * p.cluster_count];
+			const uint32_t d = col[static_cast<size_t>(s + 2) * p.cluster_count], e = col[static_cast<size_t>(s + 3) * p.cluster_count];
+			part += (a + b) + (d + e);
+		}
+		for (; s < s1; ++s)
+			part += col[static_cast<size_t>(s) * p.cluster_count];
 	}
 	s_part[warp][lane] = part;
 	__syncthreads();
@@ -408,13 +415,29 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 		run += w < warp ? v : 0u;
 		total += v;
 	}
-#pragma unroll
-	for (uint32_t i = 0; i < kFinMaxGroup; ++i)
+	if (valid)
 	{
-		const uint32_t s = s0 + i;
-		if (valid && s < s1)
-			p.seg_prefix[static_cast<size_t>(s) * p.cluster_count + c] = (n[i] == 0 || run >= p.cap) ? kSkip : run;
-		run += n[i];
+		uint32_t* pre = p.seg_prefix + c;
+		uint32_t s = s0;
+		for (; s + 4 <= s1; s += 4)
+		{
+			const uint32_t a = col[static_cast<size_t>(s) * p.cluster_count], b = col[static_cast<size_t>(s + 1) * p.cluster_count];
+			const uint32_t d = col[static_cast<size_t>(s + 2) * p.cluster_count], e = col[static_cast<size_t>(s + 3) * p.cluster_count];
+			pre[static_cast<size_t>(s) * p.cluster_count] = (a == 0 || run >= p.cap) ? kSkip : run;
+			run += a;
+			pre[static_cast<size_t>(s + 1) * p.cluster_count] = (b == 0 || run >= p.cap) ? kSkip : run;
+			run += b;
+			pre[static_cast<size_t>(s + 2) * p.cluster_count] = (d == 0 || run >= p.cap) ? kSkip : run;
+			run += d;
+			pre[static_cast<size_t>(s + 3) * p.cluster_count] = (e == 0 || run >= p.cap) ? kSkip : run;
+			run += e;
+		}
+		for (; s < s1; ++s)
+		{
+			const uint32_t a = col[static_cast<size_t>(s) * p.cluster_count];
+			pre[static_cast<size_t>(s) * p.cluster_count] = (a == 0 || run >= p.cap) ? kSkip : run;
+			run += a;
+		}
 	}
 	if (warp != 0)
 		return;
