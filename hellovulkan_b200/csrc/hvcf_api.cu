@@ -137,6 +137,8 @@ struct hvcf_ctx
 	uint32_t last_num_segs = 0;
 	uint32_t last_launches[8]{}; // per frame
 	bool timing = false;
+	bool ktimes = false;                 // HVCF_KERNEL_TIMES=1 (debug): an event after every kernel of the hierarchical frame
+	cudaEvent_t kev[8][8]{};             // [frame][begin, transform, bin, count, finalize, write]
 	cudaEvent_t ev[8][4]{}; // per frame: call begin, kernel begin, kernel end, call end
 	bool ev_valid[8]{};
 };
@@ -172,8 +174,13 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_scan_state);
 	cudaFree(c->d_trace);
 	for (int i = 0; i < 8; ++i)
+	{
 		if (c->ubo_events[i])
 			cudaEventDestroy(c->ubo_events[i]);
+		for (int j = 0; j < 8; ++j)
+			if (c->kev[i][j])
+				cudaEventDestroy(c->kev[i][j]);
+	}
 	cudaFree(c->d_slice_thr);
 	cudaFree(c->d_anim_table);
 	cudaFree(c->d_base_y);
@@ -331,6 +338,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
 		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));
 		c->hier_v1 = env_int("HVCF_HIER_V1", 0) != 0;
+		c->ktimes = env_int("HVCF_KERNEL_TIMES", 0) != 0;
 		c->tiles_cap = max_tiles;
 	}
 
@@ -687,9 +695,22 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		ctx->h_tiles_total = tiles_total;
 		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
 			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
+		auto kmark = [&](int i) -> cudaError_t {
+			if (!ctx->ktimes)
+				return cudaSuccess;
+			if (!ctx->kev[frame][i])
+			{
+				cudaError_t e = cudaEventCreate(&ctx->kev[frame][i]);
+				if (e != cudaSuccess)
+					return e;
+			}
+			return cudaEventRecord(ctx->kev[frame][i], s);
+		};
+		HVCF_CUDA(kmark(0));
 		// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the transform kernel
 		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
 			ctx->cluster_count * kHMaxChunks, stats, s, anim));
+		HVCF_CUDA(kmark(1));
 		HierParams p = hier_params(ctx, frame);
 		if (!ctx->hier_v1)
 		{
@@ -705,6 +726,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			HVCF_CUDA(launch_hier_bin(b, tiles_total, s));
 			++launches;
 		}
+		HVCF_CUDA(kmark(2));
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
 		// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
@@ -719,6 +741,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			++launches;
 		}
 		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
+		HVCF_CUDA(kmark(3));
 		if (ctx->timing)
 		{
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
@@ -738,6 +761,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		f.shard_total = ctx->d_shard_total;
 		f.stats = stats;
 		HVCF_CUDA(launch_hier_finalize(f, s));
+		HVCF_CUDA(kmark(4));
 		ctx->last_launches[frame] = launches + 3;
 		return HVCF_OK;
 	}
@@ -791,6 +815,12 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 		HierParams hp = hier_params(ctx, frame);
 		hp.index_base = d_index_base;
 		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+		if (ctx->ktimes && ctx->kev[frame][4])
+		{
+			if (!ctx->kev[frame][5])
+				HVCF_CUDA(cudaEventCreate(&ctx->kev[frame][5]));
+			HVCF_CUDA(cudaEventRecord(ctx->kev[frame][5], static_cast<cudaStream_t>(stream)));
+		}
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], static_cast<cudaStream_t>(stream)));
 		ctx->last_launches[frame] += 1;
@@ -920,6 +950,18 @@ int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_wo
 	HVCF_CUDA(cudaDeviceSynchronize());
 	HVCF_CUDA(cudaMemcpy(out_words, ctx->d_trace, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
 	*out_ctas_per_pass = ctas;
+	return HVCF_OK;
+}
+
+int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5])
+{
+	if (!ctx || !out_ms || frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_kernel_times: bad argument");
+	if (!ctx->ktimes || !ctx->kev[frame][5])
+		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_kernel_times: needs HVCF_KERNEL_TIMES=1 at hvcf_create and a hierarchical hvcf_cull on this frame");
+	HVCF_CUDA(cudaEventSynchronize(ctx->kev[frame][5]));
+	for (int i = 0; i < 5; ++i)
+		HVCF_CUDA(cudaEventElapsedTime(&out_ms[i], ctx->kev[frame][i], ctx->kev[frame][i + 1]));
 	return HVCF_OK;
 }
 

@@ -79,7 +79,7 @@ EXPORTS = [
     "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
-    "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
+    "hvcf_debug_kernel_times", "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -130,6 +130,7 @@ def load():
     lib.hvcf_debug_trace.argtypes = [vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
     lib.hvcf_get_timing.argtypes = [vp, u32, f3, f3]
     lib.hvcf_measure_fp32_issue_rate.argtypes = [i32, ctypes.POINTER(ctypes.c_double)]
+    lib.hvcf_debug_kernel_times.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float)]
     lib.hvcf_update_lights.argtypes = [vp, vp, vp, u32, vp]
     lib.hvcf_set_light_animation.argtypes = [vp, vp, u32, ctypes.c_float, vp]
     lib.hvcf_set_animation_step.argtypes = [vp, u32, u32]
@@ -459,6 +460,12 @@ class Context:
         _check(self.lib.hvcf_debug_trace(self.handle, _ptr(buf), buf.size, ctypes.byref(n)))
         n = n.value
         return buf[: 4 * n].reshape(n, 4).copy(), buf[4 * n: 8 * n].reshape(n, 4).copy()
+
+    def kernel_times(self, frame=0):
+        """ms of (transform, bin, count, finalize, write) of the last hierarchical cull; needs HVCF_KERNEL_TIMES=1."""
+        out = (ctypes.c_float * 5)()
+        _check(self.lib.hvcf_debug_kernel_times(self.handle, frame, out))
+        return [float(v) for v in out]
 
     def set_timing(self, enabled=True):
         _check(self.lib.hvcf_set_timing(self.handle, int(enabled)))

@@ -190,6 +190,9 @@ HVCF_API int hvcf_host_init_lights(uint32_t seed, uint32_t count, hvcf_light_dat
 /* debug: per-CTA {start ns, end ns, SM id, level-2 lane tests} of the last hierarchical frame, pass 1 then pass 2;
  * needs HVCF_HIER_TRACE=1 in the environment at hvcf_create. */
 HVCF_API int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_words, size_t* out_ctas_per_pass);
+/* debug: milliseconds of {transform, bin, count pass, finalize, write pass} of the last hierarchical hvcf_cull on `frame`
+ * (an event after every kernel, which also switches their programmatic overlap off); needs HVCF_KERNEL_TIMES=1 at hvcf_create. */
+HVCF_API int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5]);
 HVCF_API int hvcf_set_timing(hvcf_ctx* ctx, int enabled);
 HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms);
 /* Measured FP32 issue rate of the device (independent FADD/FMUL chains, no FMA), in lane-operations per

@@ -45,11 +45,20 @@ def main():
                             torch.cuda.synchronize()
                             times.append(e0.elapsed_time(e1))
                         st = ctx.stats(0)
+                        kt = None
+                        if os.environ.get("HVCF_KERNEL_TIMES") == "1":
+                            acc = np.zeros(5)
+                            for _ in range(10):
+                                flush.zero_()
+                                ctx.cull(0)
+                                acc += np.array(ctx.kernel_times(0))
+                            kt = [round(float(v) * 100, 1) for v in acc]  # us, mean of 10
                 except Exception as e:
                     print(json.dumps({"config": name, "K": k, "tps": tps, "error": str(e)[:100]}), flush=True)
                     continue
                 print(json.dumps({"config": name, "K": k, "tps": tps, "ms": round(float(np.median(times)), 4), "min_ms": round(min(times), 4),
-                                  "executed": st["executed_tests"], "prefilter": st["prefilter_tests"], "total": st["total_indices"]}), flush=True)
+                                  "executed": st["executed_tests"], "prefilter": st["prefilter_tests"], "total": st["total_indices"],
+                                  "kernel_us(transform,bin,count,finalize,write)": kt}), flush=True)
 
 
 if __name__ == "__main__":
