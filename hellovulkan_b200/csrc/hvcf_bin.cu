@@ -81,156 +81,75 @@ __global__ void __launch_bounds__(256) hier_unions_kernel(const uint32_t* __rest
 }
 
 // ======================================================================================================
-// level 0: grid = (ceil(ncb / 8), tiles), 8 warps = 8 groups = 2 super-groups of 4.  The tile is staged once per CTA by a
-// TMA bulk copy.
-//   phase 1  every light of the tile against the union box of each SUPER-group (lane = light pair, FADD2/FMUL2; warp w
-//            takes quarter w & 3 of the tile for super-group w >> 2); survivors are compacted in light order into a
-//            shared-memory id list per super-group (ballot/popc + a 4-warp prefix).
-//   phase 2  warp w walks the list of its super-group (lane = surviving light, gathered from the staged tile) against
-//            the union box of ITS group and appends the group's survivors to the (group, tile) slot in light order.
-// A light that passes a group union passes the super-group union (same float sequence, monotone rounding), so the slots
-// hold exactly what the one-level version wrote; measured on grid B the group filter passes 4.6 % of (group, light)
-// pairs and the super-group filter 8 %, i.e. 15 + 4.8 tests per light instead of 60.
+// level 0: grid = (ceil(ncb / 8), tiles).  The tile is staged once per CTA by a TMA bulk copy; warp w tests
+// all of it against group cbg * 8 + w and appends survivors to the (group, tile) slot in light order.
+// Measured and rejected on B200 (B1M, this kernel 57 us warm): a two-level variant (super-groups of 4 groups first:
+// 15 + 4.8 tests per light instead of 60, half the instructions) ran in the same 57 us (two more CTA barriers, shared-
+// memory gathers), and making its CTAs persistent over tiles with a two-deep TMA ring made it slower (65 us: 4 CTAs/SM).
 // ======================================================================================================
 __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParams p)
 {
-	// CTAs are persistent over tiles blockIdx.y, blockIdx.y + gridDim.y, ... with a two-deep TMA ring: the next tile
-	// lands while this one is tested (one tile per short-lived CTA was latency-bound: 7 waves of CTAs that mostly waited)
-	__shared__ __align__(128) unsigned char s_tile[2][kTileBytes];
-	__shared__ uint16_t s_list[2][kTileLights];
-	__shared__ uint32_t s_wcnt[kBinWarps];
-	__shared__ __align__(8) uint64_t bar[2];
+	__shared__ __align__(128) unsigned char s_tile[kTileBytes];
+	__shared__ __align__(8) uint64_t bar;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint32_t cb = blockIdx.x * kBinWarps + warp;
-	const uint32_t sg = warp >> 2, quarter = warp & 3;
+	const uint32_t tile_id = blockIdx.y, cb = blockIdx.x * kBinWarps + warp;
 	grid_dep_launch();
 	if (threadIdx.x == 0)
 	{
-		mbar_init(&bar[0], 1);
-		mbar_init(&bar[1], 1);
+		mbar_init(&bar, 1);
 		mbar_fence_init();
 	}
 	__syncthreads();
-	grid_dep_wait(); // the tiles are written by the transform kernel of this frame
-	const unsigned char* const src = reinterpret_cast<const unsigned char*>(p.lights_view);
-	if (threadIdx.x == 0 && blockIdx.y < p.tiles)
+	grid_dep_wait(); // the tile is written by the transform kernel of this frame
+	if (threadIdx.x == 0)
 	{
-		mbar_arrive_expect_tx(&bar[0], kTileBytes);
-		bulk_copy_g2s(s_tile[0], src + static_cast<size_t>(blockIdx.y) * kTileBytes, kTileBytes, &bar[0]);
+		mbar_arrive_expect_tx(&bar, kTileBytes);
+		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
 	}
-	// union boxes: this warp's group and its super-group (groups beyond ncb contribute an empty box)
-	const float kInf = __int_as_float(0x7f800000);
-	float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
-	float slo[3] = {kInf, kInf, kInf}, shi[3] = {-kInf, -kInf, -kInf};
-#pragma unroll
-	for (uint32_t g = 0; g < 4; ++g)
+	float lo[3] = {0.0f, 0.0f, 0.0f}, hi[3] = {0.0f, 0.0f, 0.0f};
+	if (cb < p.ncb)
 	{
-		const uint32_t c = blockIdx.x * kBinWarps + sg * 4 + g;
-		if (c < p.ncb)
-		{
-			const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(c) * 8);
-			const float4 a = __ldg(u), b = __ldg(u + 1);
-			slo[0] = fminf(slo[0], a.x), slo[1] = fminf(slo[1], a.y), slo[2] = fminf(slo[2], a.z);
-			shi[0] = fmaxf(shi[0], b.x), shi[1] = fmaxf(shi[1], b.y), shi[2] = fmaxf(shi[2], b.z);
-			if (g == quarter)
-			{
-				lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
-				hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
-			}
-		}
+		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
+		const float4 a = __ldg(u), b = __ldg(u + 1);
+		lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
+		hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
 	}
+	mbar_wait(&bar, 0);
+	if (cb >= p.ncb)
+		return;
+	const float4* tile = reinterpret_cast<const float4*>(s_tile);
+	const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+	float4* const rec = p.bin_rec + slot;
+	uint16_t* const idx = p.bin_idx + slot;
 	const uint32_t lt = lanemask_lt();
-	unsigned long long tests = 0;
-	uint32_t it = 0;
-	for (uint32_t tile_id = blockIdx.y; tile_id < p.tiles; tile_id += gridDim.y, ++it)
+	uint32_t cnt = 0;
+#pragma unroll 4
+	for (uint32_t g = 0; g < kTileGroups; ++g)
 	{
-		const uint32_t stage = it & 1u;
-		const uint32_t next = tile_id + gridDim.y;
-		if (threadIdx.x == 0 && next < p.tiles) // the other stage was released by the barrier that ended the last iteration
+		const float4 a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+		bool h0, h1;
+		sphere_box_hit2(a, b, lo, hi, h0, h1);
+		const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+		if ((m0 | m1) == 0)
+			continue;
+		const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+		if (h0 && d0 < kBinCap)
 		{
-			mbar_arrive_expect_tx(&bar[stage ^ 1u], kTileBytes);
-			bulk_copy_g2s(s_tile[stage ^ 1u], src + static_cast<size_t>(next) * kTileBytes, kTileBytes, &bar[stage ^ 1u]);
+			rec[d0] = make_float4(a.x, a.z, b.x, b.z);
+			idx[d0] = static_cast<uint16_t>(g * 64 + lane);
 		}
-		mbar_wait(&bar[stage], (it >> 1) & 1u);
-		const float4* tile = reinterpret_cast<const float4*>(s_tile[stage]);
-		const float* tile_f = reinterpret_cast<const float*>(s_tile[stage]);
-
-		// ---- phase 1: quarter `quarter` of the tile against super-group `sg` ------------------------------
-		constexpr uint32_t kIter = kTileGroups / 4;
-		uint32_t m0[kIter], m1[kIter];
-		uint32_t mine = 0;
-#pragma unroll
-		for (uint32_t i = 0; i < kIter; ++i)
+		if (h1 && d1 < kBinCap)
 		{
-			const uint32_t g = quarter * kIter + i;
-			const float4 a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
-			bool h0, h1;
-			sphere_box_hit2(a, b, slo, shi, h0, h1);
-			m0[i] = __ballot_sync(0xffffffffu, h0);
-			m1[i] = __ballot_sync(0xffffffffu, h1);
-			mine += __popc(m0[i]) + __popc(m1[i]);
+			rec[d1] = make_float4(a.y, a.w, b.y, b.w);
+			idx[d1] = static_cast<uint16_t>(g * 64 + 32 + lane);
 		}
-		if (lane == 0)
-			s_wcnt[warp] = mine;
-		__syncthreads();
-		uint32_t base = 0, n_sg = 0;
-#pragma unroll
-		for (uint32_t q = 0; q < 4; ++q)
-		{
-			const uint32_t v = s_wcnt[sg * 4 + q];
-			base += q < quarter ? v : 0u;
-			n_sg += v;
-		}
-#pragma unroll
-		for (uint32_t i = 0; i < kIter; ++i)
-		{
-			const uint32_t g = quarter * kIter + i;
-			if ((m0[i] >> lane) & 1u)
-				s_list[sg][base + __popc(m0[i] & lt)] = static_cast<uint16_t>(g * 64 + lane);
-			base += __popc(m0[i]);
-			if ((m1[i] >> lane) & 1u)
-				s_list[sg][base + __popc(m1[i] & lt)] = static_cast<uint16_t>(g * 64 + 32 + lane);
-			base += __popc(m1[i]);
-		}
-		__syncthreads();
-
-		// ---- phase 2: the super-group's survivors against this warp's group ------------------------------
-		if (cb < p.ncb)
-		{
-			const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
-			float4* const rec = p.bin_rec + slot;
-			uint16_t* const idx = p.bin_idx + slot;
-			uint32_t cnt = 0;
-			for (uint32_t b0 = 0; b0 < n_sg; b0 += 32)
-			{
-				bool hit = false;
-				float4 r = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
-				uint32_t i = 0;
-				if (b0 + lane < n_sg)
-				{
-					i = s_list[sg][b0 + lane];
-					// packed culling layout (hvcf_device.cuh): group of 64 lights, [l] = {x0,x1,y0,y1}, [32+l] = {z0,z1,r0,r1}
-					const uint32_t w = ((i >> 6) * 64 + (i & 31)) * 4 + ((i >> 5) & 1);
-					r = make_float4(tile_f[w], tile_f[w + 2], tile_f[w + 128], tile_f[w + 130]);
-					hit = sphere_box_hit(r.x, r.y, r.z, r.w, lo, hi);
-				}
-				const uint32_t m = __ballot_sync(0xffffffffu, hit);
-				const uint32_t d = cnt + __popc(m & lt);
-				if (hit && d < kBinCap)
-				{
-					rec[d] = r;
-					idx[d] = static_cast<uint16_t>(i);
-				}
-				cnt += __popc(m);
-			}
-			if (lane == 0)
-				p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
-			tests += kTileLights / 4 + n_sg;
-		}
-		__syncthreads(); // s_tile[stage], s_list and s_wcnt are free again
+		cnt += __popc(m0) + __popc(m1);
 	}
-	if (lane == 0 && tests)
-		atomicAdd(&p.stats->prefilter_tests, tests);
+	if (lane == 0)
+	{
+		p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
+		atomicAdd(&p.stats->prefilter_tests, static_cast<unsigned long long>(kTileLights));
+	}
 }
 
 // ======================================================================================================
@@ -572,32 +491,13 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	if (p.ncb == 0 || tiles == 0)
 		return cudaSuccess;
 	cudaLaunchConfig_t cfg{};
-	// exactly one resident wave; every CTA walks tiles y, y + gridDim.y, ...
-	static int resident = 0; // CTAs per device, queried once
-	if (resident == 0)
-	{
-		int per_sm = 0, dev = 0, sms = 0;
-		cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hier_bin_kernel, kBinWarps * 32, 0);
-		if (e == cudaSuccess)
-			e = cudaGetDevice(&dev);
-		if (e == cudaSuccess)
-			e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-		if (e != cudaSuccess)
-			return e;
-		resident = per_sm * sms > 0 ? per_sm * sms : 148;
-	}
-	const uint32_t gx = (p.ncb + kBinWarps - 1) / kBinWarps;
-	uint32_t gy = static_cast<uint32_t>(resident) / gx;
-	gy = gy < 1 ? 1 : (gy > tiles ? tiles : gy);
-	cfg.gridDim = dim3(gx, gy, 1);
+	cfg.gridDim = dim3((p.ncb + kBinWarps - 1) / kBinWarps, tiles, 1);
 	cfg.blockDim = dim3(kBinWarps * 32, 1, 1);
 	cfg.stream = stream;
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	BinParams q = p;
-	q.tiles = tiles;
-	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, q);
+	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
 template <int K, bool WRITE>

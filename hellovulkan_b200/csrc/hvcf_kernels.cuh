@@ -127,7 +127,6 @@ struct BinParams
 	const float* cb_union;         // [ncb][8]
 	uint32_t ncb;
 	uint32_t tiles_cap;
-	uint32_t tiles;                // tiles of this frame (set by launch_hier_bin)
 	uint32_t* bin_count;
 	float4* bin_rec;
 	uint16_t* bin_idx;
