@@ -98,25 +98,53 @@ class ShardedCuller:
         xy = grid[0] * grid[1]
         self.cluster_ranges = [(a * xy, b * xy) for a, b in self.slabs]
         self.equal = len({b - a for a, b in self.slabs}) == 1
+        self._marks = None          # [(phase, event)] of the frames run since enable_phase_timing()
+
+    # ---- optional per-phase device timing (CUDA events on the current stream; bench / profiling only) ----
+    def enable_phase_timing(self):
+        self._marks = []
+
+    def _mark(self, phase):
+        if self._marks is not None and self.engine.lights.is_cuda:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream())
+            self._marks.append((phase, ev))
+
+    def phase_ms(self):
+        """{phase: total ms} between consecutive marks; call after a synchronize."""
+        out = {}
+        m = self._marks or []
+        for (_, e0), (ph, e1) in zip(m[:-1], m[1:]):
+            if ph != "start":
+                out[ph] = out.get(ph, 0.0) + e0.elapsed_time(e1)
+        return out
 
     def broadcast_lights(self, n):
         """step 1: rank 0's first 48*n bytes of engine.lights reach every rank."""
+        self._mark("start")
         if self.world > 1:
             dist.broadcast(self.engine.lights[: 48 * n], src=0, group=self.group)
         self.engine.set_num_lights(n)
+        self._mark("broadcast_lights")
 
     def frame(self, frame, gather=True):
         e = self.engine
+        if self._marks is not None and (not self._marks or self._marks[-1][0] != "broadcast_lights"):
+            self._mark("start")
         e.cull_begin(frame)                                           # step 2
+        self._mark("cull_begin")
         totals = torch.zeros(self.world, dtype=torch.int32, device=e.shard_total.device)
         if self.world > 1:                                            # step 3
             dist.all_gather_into_tensor(totals, e.shard_total, group=self.group)
         else:
             totals.copy_(e.shard_total)
         bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
+        self._mark("totals")
         e.cull_finish(frame, bases[self.rank])                        # step 4
+        self._mark("cull_finish")
         if gather and self.world > 1:                                 # step 5
             self._gather(totals, bases)
+            self._mark("gather_grid")
         return totals, bases
 
     def _gather(self, totals, bases):
