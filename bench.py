@@ -427,7 +427,7 @@ def run_ours(args):
             fly = run_flythrough(args, hvcf, world, rank, local, dev, barrier)
         except Exception as e:
             fly = {"error": f"{type(e).__name__}: {e}"}
-    if world > 1 and not args.no_sharded:
+    if not args.no_sharded:
         try:
             sharded = run_sharded(args, hvcf, world, rank, local, dev, barrier)
         except Exception as e:  # the headline line must still be printed
@@ -663,51 +663,127 @@ def run_flythrough(args, hvcf, world, rank, local, dev, barrier):
 
 def run_sharded(args, hvcf, world, rank, local, dev, barrier):
     """configs[3]: the cluster grid split into z-slabs, one per rank; per step: NCCL broadcast of the light
-    buffer from rank 0, local culling, all-gather of totals, scatter at global offsets, all-gather of the grid."""
+    buffer from rank 0, local culling, exchange of totals, cells + indices written at global offsets, and the
+    grid gathered on every rank.  Headline variant: exchange over NVLink peer memory (hvcf_cull_sharded) on
+    load-balanced slabs; the torch.distributed/NCCL exchange on equal slabs is timed beside it.
+    At world 1 the same code runs without collectives: the N=1 point of the strong-scaling curve."""
     import torch
     import torch.distributed as dist
-    from hellovulkan_b200.sharded import HvcfEngine, ShardedCuller, z_slabs
+    from hellovulkan_b200.sharded import HvcfEngine, ShardedCuller, z_slabs, balance_slabs
 
     grid, screen, n = WORKLOADS[args.sharded_workload]
     C = grid[0] * grid[1] * grid[2]
-    slabs = z_slabs(grid[2], world)
-    eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
-    sc = ShardedCuller(eng, grid, world=world, rank=rank)
+    ubo = hvcf.host_camera_ubo(grid, screen)
+    stream = torch.cuda.current_stream()
+    steps = max(1, args.sharded_steps)
+    src = None
     if rank == 0:
         host = np.zeros(n, hvcf.LIGHT_DT)
         hvcf.host_init_lights(n, out=host)
-        eng.lights.copy_(torch.from_numpy(host.view(np.uint8).reshape(-1)))
+        src = torch.from_numpy(host.view(np.uint8).reshape(-1)).to(dev)
         del host
-    ubo = hvcf.host_camera_ubo(grid, screen)
-    for f in range(2):
-        eng.set_ubo(f, ubo)
-    stream = torch.cuda.current_stream()
-    steps = max(1, args.sharded_steps)
 
-    def step(f):
+    def allmax(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def make(slabs, exchange):
+        eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
+        sc = ShardedCuller(eng, grid, world=world, rank=rank, slabs=slabs, exchange=exchange)
+        if rank == 0:
+            eng.lights.copy_(src)
+        for f in range(2):
+            eng.set_ubo(f, ubo)
         sc.broadcast_lights(n)
-        return sc.frame(f, gather=True)
+        return eng, sc
 
-    step(0)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for i in range(steps):
-        totals, _ = step(i & 1)
-    e1.record(stream)
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item()) / steps
-    st = eng.ctx.stats((steps - 1) & 1)
-    ex = torch.tensor([float(st["executed_tests"])], device=dev, dtype=torch.float64)
-    dist.all_reduce(ex, op=dist.ReduceOp.SUM)
-    total = int(totals.sum().item())
-    eng.close()
-    return {"workload": args.sharded_workload, "grid": list(grid), "lights": n, "steps": steps, "ms_per_frame": ms,
-            "value": C * n / (ms * 1e-3), "unit": "tests/s (nominal)", "scaling": "strong",
-            "executed_tests_per_frame": float(ex.item()), "total_indices": total, "z_slabs": slabs,
-            "collectives": "ncclBroadcast 48 B x L lights; all-gather totals; all-gather light cells; per-owner broadcast of index segments"}
+    def drop(eng, sc):
+        torch.cuda.synchronize()
+        sc.close()
+        eng.close()
+
+    def timed(eng, sc, rebroadcast, k):
+        def step(f):
+            if rebroadcast:
+                sc.broadcast_lights(n)
+            return sc.frame(f, gather=True)
+        for i in range(2):
+            step(i & 1)
+        barrier()
+        sc.enable_phase_timing()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(k):
+            totals, _ = step(i & 1)
+        e1.record(stream)
+        barrier()
+        own = sc.phase_ms()
+        ms = allmax(e0.elapsed_time(e1)) / k
+        phases = {key: allmax(v) / k for key, v in own.items()}
+        local_ms = (own.get("cull_begin", 0.0) + own.get("cull_finish", 0.0)) / k   # this rank's own kernels
+        return ms, phases, totals.clone(), local_ms
+
+    def measure(slabs, exchange):
+        eng, sc = make(slabs, exchange)
+        ms, phases, totals, _ = timed(eng, sc, True, steps)
+        ms_res, phases_res, _, local_ms = timed(eng, sc, False, steps)
+        st = eng.ctx.stats((steps - 1) & 1)
+        ex = torch.tensor([float(st["executed_tests"])], device=dev, dtype=torch.float64)
+        lm = torch.zeros(world, device=dev, dtype=torch.float64)
+        lm[rank] = local_ms
+        if world > 1:
+            dist.all_reduce(ex, op=dist.ReduceOp.SUM)
+            dist.all_reduce(lm, op=dist.ReduceOp.SUM)
+        kernel_ms = None
+        if os.environ.get("HVCF_KERNEL_TIMES") == "1":   # debug: per-kernel events (they serialise the PDL chain)
+            try:
+                kernel_ms = dict(zip(("transform", "bin", "count", "finalize", "write"), eng.ctx.kernel_times((steps - 1) & 1)))
+            except Exception as e:
+                kernel_ms = {"error": str(e)}
+        if exchange == "peer":
+            eng.peer_status()
+        out = {"ms_per_frame": ms, "value": C * n / (ms * 1e-3), "unit": "tests/s (nominal)", "exchange": exchange,
+               "z_slabs": [list(x) for x in slabs], "phase_ms_max_over_ranks": phases,
+               "own_kernels_ms_per_rank": [float(x) for x in lm.tolist()],
+               "lights_resident": {"ms_per_frame": ms_res, "value": C * n / (ms_res * 1e-3), "phase_ms_max_over_ranks": phases_res,
+                                   "note": "same frame without re-broadcasting the light buffer (static lights, as in the reference app)"},
+               "executed_tests_per_frame": float(ex.item()), "total_indices": int(totals.sum().item()),
+               "kernel_ms_rank0_debug": kernel_ms}
+        drop(eng, sc)
+        return out
+
+    equal = z_slabs(grid[2], world)
+    slabs, history = equal, []
+    if world > 1:
+        # load balance: re-cut the z-range from each rank's measured kernel time until the cuts stop moving
+        for it in range(4):
+            eng, sc = make(slabs, "peer")
+            _, _, _, local_ms = timed(eng, sc, False, 3)
+            drop(eng, sc)
+            lm = torch.zeros(world, device=dev, dtype=torch.float64)
+            lm[rank] = local_ms
+            dist.all_reduce(lm, op=dist.ReduceOp.SUM)
+            times = [float(x) for x in lm.tolist()]
+            history.append({"z_slabs": [list(x) for x in slabs], "own_kernels_ms_per_rank": times})
+            new = balance_slabs(slabs, times)
+            if new == slabs or max(times) <= 1.03 * (sum(times) / world):
+                break
+            slabs = new
+    res = measure(slabs, "peer")
+    res.update({"workload": args.sharded_workload, "grid": list(grid), "lights": n, "steps": steps, "scaling": "strong",
+                "balance_iterations": history,
+                "collectives": "none (1 rank)" if world == 1 else
+                "ncclBroadcast 48 B x L lights; totals, light cells and index segments exchanged by hvcf_peer kernels over NVLink peer memory (CUDA IPC)"})
+    if world > 1:
+        try:
+            base = measure(equal, "nccl")
+            base["collectives"] = "ncclBroadcast 48 B x L lights; all-gather totals; all-gather light cells; per-owner broadcast of index segments"
+            res["nccl_equal_slabs"] = base
+        except Exception as e:
+            res["nccl_equal_slabs"] = {"error": f"{type(e).__name__}: {e}"}
+    return res
 
 
 def main():

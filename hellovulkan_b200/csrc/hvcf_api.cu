@@ -129,6 +129,15 @@ struct hvcf_ctx
 	float slice_key[8][2]{};                   // sliceScaling, sliceBias of the table in the slot
 	bool slice_valid[8]{};
 
+	// exchange step of the sharded grid over peer memory (hvcf_peer.cu)
+	PeerParams peer{};                         // world == 0: not attached
+	PeerMailbox* d_mail = nullptr;
+	uint32_t* d_index_base = nullptr;
+	uint32_t* d_peer_totals = nullptr;         // [kMaxPeers]
+	bool peer_ipc = false;                     // peers were mapped with cudaIpcOpenMemHandle
+	uint32_t peer_epoch = 0;
+	uint32_t peer_frame = 0;                   // frame slot of the last hvcf_cull_begin
+
 	cudaEvent_t ubo_events[8]{};               // per frame slot: the staged UBO has been consumed
 	bool* ubo_set = nullptr;
 	bool aabb_dirty = true;
@@ -143,10 +152,28 @@ struct hvcf_ctx
 	bool ev_valid[8]{};
 };
 
+static void peer_unmap(hvcf_ctx* c)
+{
+	if (c->peer_ipc)
+		for (uint32_t r = 0; r < c->peer.world; ++r)
+			if (r != c->peer.rank)
+			{
+				cudaIpcCloseMemHandle(c->peer.cells[r]);
+				cudaIpcCloseMemHandle(c->peer.indices[r]);
+				cudaIpcCloseMemHandle(c->peer.mail[r]);
+			}
+	c->peer = PeerParams{};
+	c->peer_ipc = false;
+}
+
 static void free_ctx(hvcf_ctx* c)
 {
 	if (!c)
 		return;
+	peer_unmap(c);
+	cudaFree(c->d_mail);
+	cudaFree(c->d_index_base);
+	cudaFree(c->d_peer_totals);
 	cudaFree(c->d_lights);
 	cudaFree(c->d_aabb);
 	cudaFree(c->d_cells);
@@ -843,6 +870,244 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	if (ctx->timing)
 		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], static_cast<cudaStream_t>(stream)));
 	ctx->last_launches[frame] += 1;
+	return HVCF_OK;
+}
+
+// ---- exchange step of the sharded grid over peer memory ---------------------------------------------------
+static int peer_alloc(hvcf_ctx* ctx)
+{
+	if (ctx->d_mail && ctx->d_index_base && ctx->d_peer_totals)
+		return HVCF_OK; // nothing to do -- and no synchronisation: getters may be called between stream-ordered peer calls
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	if (!ctx->d_mail)
+	{
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_mail), sizeof(PeerMailbox)));
+		HVCF_CUDA(cudaMemset(ctx->d_mail, 0, sizeof(PeerMailbox)));
+	}
+	if (!ctx->d_index_base)
+	{
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_index_base), sizeof(uint32_t)));
+		HVCF_CUDA(cudaMemset(ctx->d_index_base, 0, sizeof(uint32_t)));
+	}
+	if (!ctx->d_peer_totals)
+	{
+		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_peer_totals), sizeof(uint32_t) * kMaxPeers));
+		HVCF_CUDA(cudaMemset(ctx->d_peer_totals, 0, sizeof(uint32_t) * kMaxPeers));
+	}
+	HVCF_CUDA(cudaDeviceSynchronize());
+	return HVCF_OK;
+}
+
+int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out)
+{
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "hvcf_peer_handle holds three 64-byte IPC handles");
+	static_assert(HVCF_MAX_PEERS == kMaxPeers, "HVCF_MAX_PEERS");
+	if (!ctx || !out)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_export: null argument");
+	const int rc = peer_alloc(ctx);
+	if (rc != HVCF_OK)
+		return rc;
+	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->cells), ctx->d_cells));
+	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->indices), ctx->d_indices));
+	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->mailbox), ctx->d_mail));
+	return HVCF_OK;
+}
+
+static int peer_check_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const void* p, const char* who)
+{
+	if (!ctx || !p)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null argument", who);
+	if (world == 0 || world > kMaxPeers || rank >= world)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: rank %u of world %u (at most %u peers)", who, rank, world, kMaxPeers);
+	if (ctx->peer.world)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: already attached; call hvcf_peer_detach first", who);
+	return peer_alloc(ctx);
+}
+
+int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_peer_handle* handles)
+{
+	const int rc = peer_check_attach(ctx, rank, world, handles, "hvcf_peer_attach");
+	if (rc != HVCF_OK)
+		return rc;
+	PeerParams pp{};
+	pp.world = world;
+	pp.rank = rank;
+	for (uint32_t r = 0; r < world; ++r)
+	{
+		if (r == rank)
+		{
+			pp.cells[r] = ctx->d_cells;
+			pp.indices[r] = ctx->d_indices;
+			pp.mail[r] = ctx->d_mail;
+			continue;
+		}
+		void* ptr[3] = {nullptr, nullptr, nullptr};
+		const unsigned char* h[3] = {handles[r].cells, handles[r].indices, handles[r].mailbox};
+		for (int k = 0; k < 3; ++k)
+		{
+			cudaIpcMemHandle_t handle;
+			memcpy(&handle, h[k], sizeof(handle));
+			const cudaError_t e = cudaIpcOpenMemHandle(&ptr[k], handle, cudaIpcMemLazyEnablePeerAccess);
+			if (e != cudaSuccess)
+			{
+				for (int j = 0; j < k; ++j)
+					cudaIpcCloseMemHandle(ptr[j]);
+				for (uint32_t q = 0; q < r; ++q) // the ranks mapped so far
+					if (q != rank)
+					{
+						cudaIpcCloseMemHandle(pp.cells[q]);
+						cudaIpcCloseMemHandle(pp.indices[q]);
+						cudaIpcCloseMemHandle(pp.mail[q]);
+					}
+				return fail(HVCF_ERR_CUDA, "hvcf_peer_attach: cudaIpcOpenMemHandle(rank %u, buffer %d): %s", r, k, cudaGetErrorString(e));
+			}
+		}
+		pp.cells[r] = static_cast<hvcf_light_cell*>(ptr[0]);
+		pp.indices[r] = static_cast<uint32_t*>(ptr[1]);
+		pp.mail[r] = static_cast<PeerMailbox*>(ptr[2]);
+	}
+	ctx->peer = pp;
+	ctx->peer_ipc = true;
+	ctx->peer_epoch = 0;
+	return HVCF_OK;
+}
+
+int hvcf_peer_attach_local(hvcf_ctx* ctx, uint32_t rank, uint32_t world, hvcf_ctx* const* contexts)
+{
+	const int rc = peer_check_attach(ctx, rank, world, contexts, "hvcf_peer_attach_local");
+	if (rc != HVCF_OK)
+		return rc;
+	PeerParams pp{};
+	pp.world = world;
+	pp.rank = rank;
+	for (uint32_t r = 0; r < world; ++r)
+	{
+		hvcf_ctx* o = r == rank ? ctx : contexts[r];
+		if (!o)
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] is null", r);
+		if (o->cluster_total != ctx->cluster_total || o->cap != ctx->cap)
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] has a different grid or cap", r);
+		const int rc2 = peer_alloc(o);
+		if (rc2 != HVCF_OK)
+			return rc2;
+		if (o->device != ctx->device)
+		{
+			int can = 0;
+			HVCF_CUDA(cudaDeviceCanAccessPeer(&can, ctx->device, o->device));
+			if (!can)
+				return fail(HVCF_ERR_UNSUPPORTED, "hvcf_peer_attach_local: device %d cannot access device %d", ctx->device, o->device);
+			HVCF_CUDA(cudaSetDevice(ctx->device));
+			const cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+			if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+				return fail(HVCF_ERR_CUDA, "hvcf_peer_attach_local: cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+			(void)cudaGetLastError();
+		}
+		pp.cells[r] = o->d_cells;
+		pp.indices[r] = o->d_indices;
+		pp.mail[r] = o->d_mail;
+	}
+	ctx->peer = pp;
+	ctx->peer_ipc = false;
+	ctx->peer_epoch = 0;
+	return HVCF_OK;
+}
+
+int hvcf_peer_detach(hvcf_ctx* ctx)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_detach: null context");
+	cudaSetDevice(ctx->device);
+	cudaDeviceSynchronize();
+	peer_unmap(ctx);
+	if (ctx->d_mail)
+		cudaMemset(ctx->d_mail, 0, sizeof(PeerMailbox));
+	return HVCF_OK;
+}
+
+int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream)
+{
+	if (!ctx || !ctx->peer.world)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_exchange_totals: no peers attached");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	ctx->peer_epoch = ctx->peer_epoch >= 0x7fffffffu ? 1u : ctx->peer_epoch + 1u;
+	ctx->peer.epoch = ctx->peer_epoch;
+	HVCF_CUDA(launch_peer_totals(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->d_peer_totals, static_cast<cudaStream_t>(stream)));
+	return HVCF_OK;
+}
+
+int hvcf_peer_push_grid(hvcf_ctx* ctx, void* stream)
+{
+	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_push_grid: no peers attached or no totals exchanged");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	// enough CTAs to keep the NVLink ports busy without taking the whole GPU: 2 per SM
+	HVCF_CUDA(launch_peer_push(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->cluster_begin, ctx->cluster_count, 296u,
+		static_cast<cudaStream_t>(stream)));
+	return HVCF_OK;
+}
+
+int hvcf_peer_wait_grid(hvcf_ctx* ctx, void* stream)
+{
+	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_wait_grid: no peers attached or no totals exchanged");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(launch_peer_wait(ctx->peer, static_cast<cudaStream_t>(stream)));
+	return HVCF_OK;
+}
+
+int hvcf_cull_sharded(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	if (!ctx || !ctx->peer.world)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_sharded: no peers attached (hvcf_peer_attach)");
+	int rc = hvcf_cull_begin(ctx, frame, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_exchange_totals(ctx, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_cull_finish(ctx, frame, ctx->d_index_base, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_push_grid(ctx, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_wait_grid(ctx, stream);
+	return rc;
+}
+
+int hvcf_peer_totals_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
+{
+	if (!ctx || !out_device_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_totals_ptr: null argument");
+	const int rc = peer_alloc(ctx);
+	if (rc != HVCF_OK)
+		return rc;
+	*out_device_ptr = ctx->d_peer_totals;
+	return HVCF_OK;
+}
+
+int hvcf_peer_index_base_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
+{
+	if (!ctx || !out_device_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_index_base_ptr: null argument");
+	const int rc = peer_alloc(ctx);
+	if (rc != HVCF_OK)
+		return rc;
+	*out_device_ptr = ctx->d_index_base;
+	return HVCF_OK;
+}
+
+int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error)
+{
+	if (!ctx || !out_error)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_status: null argument");
+	*out_error = 0;
+	if (!ctx->d_mail)
+		return HVCF_OK;
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+	unsigned int err = 0;
+	HVCF_CUDA(cudaMemcpy(&err, &ctx->d_mail->error, sizeof(err), cudaMemcpyDeviceToHost));
+	*out_error = static_cast<int>(err);
+	if (err)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_status: rank %u waited in vain for the %s of rank %u in sharded frame %u (mod 2^20)", ctx->peer.rank,
+			(err >> 28) == 1 ? "index total" : "grid segment", (err >> 20) & 0xffu, err & 0xfffffu);
 	return HVCF_OK;
 }
 

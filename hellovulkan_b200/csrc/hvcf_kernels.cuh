@@ -160,4 +160,27 @@ cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aa
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
+// ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------
+constexpr uint32_t kMaxPeers = 16;
+struct PeerMailbox
+{
+	unsigned long long totals[2][kMaxPeers]; // [frame parity][rank] = epoch << 32 | index total of that rank's slab
+	unsigned long long arrived[kMaxPeers];   // [rank] = epoch << 32 once that rank's cells + indices are in OUR buffers
+	unsigned int done;                       // CTA counter of our own push kernel
+	unsigned int error;                      // 1 = a wait timed out
+};
+struct PeerParams
+{
+	hvcf_light_cell* cells[kMaxPeers];       // every rank's lightCells buffer (own pointer at [rank])
+	uint32_t* indices[kMaxPeers];            // every rank's lightIndices buffer
+	PeerMailbox* mail[kMaxPeers];
+	uint32_t world, rank;
+	uint32_t epoch;                          // sharded-frame serial, > 0, the same on every rank
+};
+cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total, uint32_t* index_base, uint32_t* totals_out,
+	cudaStream_t stream);
+cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, uint32_t cluster_begin,
+	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream);
+cudaError_t launch_peer_wait(const PeerParams& p, cudaStream_t stream);
+
 } // namespace hvcf

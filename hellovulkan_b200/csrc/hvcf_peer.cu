@@ -1,0 +1,197 @@
+// hvcf_peer.cu -- the exchange step of the z-slab sharded grid as kernels over NVLink peer memory.
+//
+// The reference has no multi-GPU path.  Sharded by z-slab, the only data that crosses GPUs after culling is
+//   (1) one uint32 per rank (its index total, to turn shard-local offsets into global ones), and
+//   (2) each rank's light cells and its segment of the light-index list, which every other rank needs to hold the
+//       full light grid (LightCulling.comp:81-87 output, consumed by Scene.frag:73-78).
+// Both are done here by the GPUs themselves: every rank maps its peers' cells / indices / mailbox allocations
+// (CUDA IPC across processes, plain pointers inside one process) and
+//   peer_totals_kernel   posts its total into every peer's mailbox, waits for the others', writes its index base;
+//   peer_push_kernel     streams its cells and index segment into every peer (one coalesced read, world-1 remote
+//                        stores over NVLink), then the last CTA raises its "arrived" flag on every peer;
+//   peer_wait_kernel     waits until every peer's segment has arrived.
+// No host round trip, no size exchange on the host (the segment length is read on the device), no NCCL call.
+//
+// Ordering.  Data stores to a peer are followed by __threadfence_system() and a release store of the flag; readers
+// spin with acquire loads at system scope.  Posting the total of frame e is stream-ordered after everything rank r did
+// for frame e-1 (including its consumers on the same stream), and nobody pushes frame e before it has seen every total
+// of frame e -- so the totals exchange is also the "your grid buffers may be overwritten" handshake.  Mailbox slots
+// are double-buffered on the frame parity.  Every spin has a time limit (kPeerTimeoutNs); on expiry the kernel sets
+// the mailbox error word and leaves, so a missing peer is an error code, never a hung GPU.
+#include "hvcf_kernels.cuh"
+
+namespace hvcf
+{
+
+constexpr unsigned long long kPeerTimeoutNs = 4000000000ull; // 4 s
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p)
+{
+	unsigned long long v;
+	asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v)
+{
+	asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+	unsigned long long t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	return t;
+}
+
+// wait until the word's upper half (the epoch) reaches `epoch`; returns the word, or 0 with the error flag set
+// error word: kind << 28 | rank waited for << 20 | epoch & 0xfffff  (kind 1 = total, 2 = grid segment)
+__device__ __forceinline__ unsigned long long spin_epoch(const unsigned long long* word, unsigned long long epoch, PeerMailbox* mail,
+	uint32_t kind, uint32_t who)
+{
+	const unsigned long long t0 = global_timer_ns();
+	for (;;)
+	{
+		const unsigned long long v = ld_acquire_sys_u64(word);
+		if ((v >> 32) >= epoch)
+			return v;
+		if (global_timer_ns() - t0 > kPeerTimeoutNs)
+		{
+			atomicCAS(&mail->error, 0u, (kind << 28) | (who << 20) | (static_cast<uint32_t>(epoch) & 0xfffffu));
+			return 0ull;
+		}
+		__nanosleep(200);
+	}
+}
+
+// one warp: lane r talks to rank r
+__global__ void __launch_bounds__(32) peer_totals_kernel(const PeerParams p, const uint32_t* __restrict__ shard_total,
+	uint32_t* __restrict__ index_base, uint32_t* __restrict__ totals_out)
+{
+	const uint32_t r = threadIdx.x;
+	const uint32_t parity = p.epoch & 1u;
+	const uint32_t mine = *shard_total;
+	uint32_t total_r = 0;
+	if (r < p.world)
+	{
+		st_release_sys_u64(&p.mail[r]->totals[parity][p.rank], (static_cast<unsigned long long>(p.epoch) << 32) | mine);
+		const unsigned long long v = spin_epoch(&p.mail[p.rank]->totals[parity][r], p.epoch, p.mail[p.rank], 1u, r);
+		total_r = static_cast<uint32_t>(v);
+		if (totals_out)
+			totals_out[r] = total_r;
+	}
+	// index base = totals of the ranks below (slabs are in rank order, so this is the scan in cluster order)
+	uint32_t below = r < p.rank ? total_r : 0u;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1)
+		below += __shfl_xor_sync(0xffffffffu, below, o);
+	if (r == 0)
+		*index_base = below;
+}
+
+// grid-stride copy of this rank's cells [cluster_begin, cluster_begin + cluster_count) and indices
+// [base, base + total) into the same positions of every peer's buffers.
+__global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, const uint32_t* __restrict__ shard_total,
+	const uint32_t* __restrict__ index_base, uint32_t cluster_begin, uint32_t cluster_count)
+{
+	const uint32_t base = *index_base, total = *shard_total;
+	const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+	const size_t nth = static_cast<size_t>(gridDim.x) * blockDim.x;
+
+	// ---- cells: 8 B records, copied as 16 B pairs where the range allows ----
+	{
+		const uint2* src = reinterpret_cast<const uint2*>(p.cells[p.rank]);
+		const size_t b = cluster_begin, e = static_cast<size_t>(cluster_begin) + cluster_count;
+		const size_t b2 = (b + 1) & ~static_cast<size_t>(1), e2 = e & ~static_cast<size_t>(1);
+		for (size_t i = b2 / 2 + tid; i < e2 / 2; i += nth)
+		{
+			const uint4 v = reinterpret_cast<const uint4*>(src)[i];
+			for (uint32_t r = 0; r < p.world; ++r)
+				if (r != p.rank)
+					reinterpret_cast<uint4*>(p.cells[r])[i] = v;
+		}
+		if (tid == 0 && b < b2 && b < e)
+			for (uint32_t r = 0; r < p.world; ++r)
+				if (r != p.rank)
+					reinterpret_cast<uint2*>(p.cells[r])[b] = src[b];
+		if (tid == 1 % nth && e2 < e && e2 >= b2)
+			for (uint32_t r = 0; r < p.world; ++r)
+				if (r != p.rank)
+					reinterpret_cast<uint2*>(p.cells[r])[e2] = src[e2];
+	}
+	// ---- indices: 4 B words; head up to a 16 B boundary, 16 B body, tail ----
+	{
+		const uint32_t* src = p.indices[p.rank];
+		const size_t b = base, e = static_cast<size_t>(base) + total;
+		size_t b4 = (b + 3) & ~static_cast<size_t>(3);
+		if (b4 > e)
+			b4 = e;
+		const size_t e4 = b4 + ((e - b4) & ~static_cast<size_t>(3));
+		for (size_t i = b4 / 4 + tid; i < e4 / 4; i += nth)
+		{
+			const uint4 v = reinterpret_cast<const uint4*>(src)[i];
+			for (uint32_t r = 0; r < p.world; ++r)
+				if (r != p.rank)
+					reinterpret_cast<uint4*>(p.indices[r])[i] = v;
+		}
+		if (tid < 8)
+		{
+			// lanes 0..3: head words, lanes 4..7: tail words
+			const size_t i = tid < 4 ? b + tid : e4 + (tid - 4);
+			const bool ok = tid < 4 ? i < b4 : i < e;
+			if (ok)
+			{
+				const uint32_t v = src[i];
+				for (uint32_t r = 0; r < p.world; ++r)
+					if (r != p.rank)
+						p.indices[r][i] = v;
+			}
+		}
+	}
+	// ---- last CTA out raises the flag on every peer ----
+	__shared__ bool last;
+	__threadfence_system();
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		PeerMailbox* mine = p.mail[p.rank];
+		const unsigned int done = atomicAdd(&mine->done, 1u);
+		last = done == gridDim.x - 1;
+		if (last)
+			mine->done = 0u;
+	}
+	__syncthreads();
+	if (last && threadIdx.x < p.world)
+	{
+		__threadfence_system();
+		st_release_sys_u64(&p.mail[threadIdx.x]->arrived[p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+	}
+}
+
+__global__ void __launch_bounds__(32) peer_wait_kernel(const PeerParams p)
+{
+	const uint32_t r = threadIdx.x;
+	if (r < p.world && r != p.rank)
+		spin_epoch(&p.mail[p.rank]->arrived[r], p.epoch, p.mail[p.rank], 2u, r);
+	__threadfence_system();
+}
+
+cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total, uint32_t* index_base, uint32_t* totals_out,
+	cudaStream_t stream)
+{
+	peer_totals_kernel<<<1, 32, 0, stream>>>(p, shard_total, index_base, totals_out);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, uint32_t cluster_begin,
+	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream)
+{
+	peer_push_kernel<<<blocks, 256, 0, stream>>>(p, shard_total, index_base, cluster_begin, cluster_count);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_peer_wait(const PeerParams& p, cudaStream_t stream)
+{
+	peer_wait_kernel<<<1, 32, 0, stream>>>(p);
+	return cudaGetLastError();
+}
+
+} // namespace hvcf

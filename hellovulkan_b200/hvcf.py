@@ -80,8 +80,13 @@ EXPORTS = [
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
     "hvcf_debug_kernel_times", "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
+    "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
+    "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
+    "hvcf_peer_status",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
+
+PEER_HANDLE_BYTES = 192
 
 _lib = None
 
@@ -139,6 +144,17 @@ def load():
     lib.hvcf_frustum_cull.argtypes = [i32, vp, vp, u32, vp, vp]
     lib.hvcf_host_frustum_ubo.argtypes = [f3, f3, ctypes.c_float, ctypes.c_float, vp]
     lib.hvcf_host_init_boxes.argtypes = [u32, u32, ctypes.c_float, vp]
+    lib.hvcf_peer_export.argtypes = [vp, vp]
+    lib.hvcf_peer_attach.argtypes = [vp, u32, u32, vp]
+    lib.hvcf_peer_attach_local.argtypes = [vp, u32, u32, ctypes.POINTER(vp)]
+    lib.hvcf_peer_detach.argtypes = [vp]
+    lib.hvcf_peer_exchange_totals.argtypes = [vp, vp]
+    lib.hvcf_peer_push_grid.argtypes = [vp, vp]
+    lib.hvcf_peer_wait_grid.argtypes = [vp, vp]
+    lib.hvcf_cull_sharded.argtypes = [vp, u32, vp]
+    lib.hvcf_peer_totals_ptr.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.hvcf_peer_index_base_ptr.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.hvcf_peer_status.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_int)]
     _lib = lib
     return lib
 
@@ -420,6 +436,56 @@ class Context:
         cam = (ctypes.c_float * 3)(*[float(v) for v in camera_position])
         _check(self.lib.hvcf_shade(self.handle, frame, ctypes.byref(dg.desc), ctypes.byref(pc), cam, dg.out_color.ptr,
                                    dg.out_cluster.ptr if dg.out_cluster is not None else None, stream))
+
+    # -- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ---------------------
+    def peer_export(self):
+        """192-byte handle (3 x cudaIpcMemHandle_t) to send to the other ranks."""
+        h = (ctypes.c_ubyte * PEER_HANDLE_BYTES)()
+        _check(self.lib.hvcf_peer_export(self.handle, h))
+        return bytes(h)
+
+    def peer_attach(self, rank, world, handles):
+        """handles: world x 192 bytes in rank order (own entry ignored)."""
+        blob = b"".join(bytes(h) for h in handles)
+        if len(blob) != world * PEER_HANDLE_BYTES:
+            raise ValueError("peer_attach: need one 192-byte handle per rank")
+        buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _check(self.lib.hvcf_peer_attach(self.handle, rank, world, buf))
+
+    def peer_attach_local(self, rank, contexts):
+        arr = (ctypes.c_void_p * len(contexts))(*[c.handle for c in contexts])
+        _check(self.lib.hvcf_peer_attach_local(self.handle, rank, len(contexts), arr))
+
+    def peer_detach(self):
+        _check(self.lib.hvcf_peer_detach(self.handle))
+
+    def peer_exchange_totals(self, stream=None):
+        _check(self.lib.hvcf_peer_exchange_totals(self.handle, stream))
+
+    def peer_push_grid(self, stream=None):
+        _check(self.lib.hvcf_peer_push_grid(self.handle, stream))
+
+    def peer_wait_grid(self, stream=None):
+        _check(self.lib.hvcf_peer_wait_grid(self.handle, stream))
+
+    def cull_sharded(self, frame=0, stream=None):
+        _check(self.lib.hvcf_cull_sharded(self.handle, frame, stream))
+
+    def peer_totals_ptr(self):
+        p = ctypes.c_void_p()
+        _check(self.lib.hvcf_peer_totals_ptr(self.handle, ctypes.byref(p)))
+        return p.value
+
+    def peer_index_base_ptr(self):
+        p = ctypes.c_void_p()
+        _check(self.lib.hvcf_peer_index_base_ptr(self.handle, ctypes.byref(p)))
+        return p.value
+
+    def peer_status(self, stream=None):
+        """synchronises `stream`; raises HvcfError if a peer wait timed out."""
+        e = ctypes.c_int()
+        _check(self.lib.hvcf_peer_status(self.handle, stream, ctypes.byref(e)))
+        return e.value
 
     def shard_total_ptr(self):
         p = ctypes.c_void_p()

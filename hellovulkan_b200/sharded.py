@@ -13,6 +13,14 @@ Per frame:
   5. all-gather the light cells (equal slabs) and the index segments        -- dist.all_gather / broadcast
 so that every GPU holds the full light grid, as BASELINE.json's north_star asks.
 
+Two implementations of steps 3-5:
+  exchange="nccl"  torch.distributed collectives (all-gather of totals, all-gather / per-owner broadcast of the grid);
+  exchange="peer"  the GPUs do it themselves over NVLink peer memory (hvcf_cull_sharded, csrc/hvcf_peer.cu): totals are
+                   posted into the peers' mailboxes, every rank pushes its cells + index segment into all peers with
+                   one kernel and waits for theirs -- no host round trip and no collective call inside the frame.
+Slabs need not be equal: far slices hold many more hits than near ones, so `balance_slabs` re-cuts the z-range from
+measured per-rank times (a few iterations converge; the contexts are re-created at the new cuts).
+
 torch.distributed is plumbing only.  `engine` is duck-typed (begin/finish/views) so the host logic can be
 exercised on CPU tensors under gloo with a stand-in engine (tests/test_sharded_gloo.py); the product
 engine is HvcfEngine below, which has no CPU path.
@@ -33,6 +41,41 @@ def z_slabs(Z: int, world: int):
         out.append((z, z + n))
         z += n
     return out
+
+
+def balance_slabs(slabs, times, min_slices=1):
+    """Re-cut contiguous z-slabs so that every rank gets the same share of the measured cost.
+
+    slabs: [(z0, z1)] in rank order covering [0, Z); times: measured cost of each rank's slab (any unit).
+    The cost is taken as uniform inside a slab (piecewise-constant density), cumulated over z and cut at k/N of the
+    total; every rank keeps at least `min_slices` slices when Z allows.  Pure function: unit-tested on the CPU."""
+    world = len(slabs)
+    Z = slabs[-1][1]
+    dens = np.zeros(Z, np.float64)
+    for (a, b), t in zip(slabs, times):
+        if b > a:
+            dens[a:b] = max(float(t), 1e-9) / (b - a)
+    if not dens.any():
+        return list(slabs)
+    cum = np.concatenate([[0.0], np.cumsum(dens)])
+    cuts = [0]
+    for k in range(1, world):
+        target = cum[-1] * k / world
+        z = int(np.searchsorted(cum, target, side="left"))
+        # the cut nearer to the target among z-1, z
+        if z > 0 and abs(cum[z - 1] - target) <= abs(cum[min(z, Z)] - target):
+            z -= 1
+        cuts.append(z)
+    cuts.append(Z)
+    if Z >= world * min_slices:
+        for k in range(1, world):                       # forward: at least min_slices each
+            cuts[k] = max(cuts[k], cuts[k - 1] + min_slices)
+        for k in range(world - 1, 0, -1):               # backward: leave room for the ranks above
+            cuts[k] = min(cuts[k], cuts[k + 1] - min_slices)
+    else:
+        for k in range(1, world):
+            cuts[k] = min(max(cuts[k], cuts[k - 1]), Z)
+    return [(cuts[k], cuts[k + 1]) for k in range(world)]
 
 
 class DevicePtrView:
@@ -81,6 +124,36 @@ class HvcfEngine:
         self.base.copy_(base.view(1))
         self.ctx.cull_finish(frame, self.base.data_ptr())
 
+    # -- exchange over peer memory (csrc/hvcf_peer.cu) --
+    def peer_export(self):
+        return self.ctx.peer_export()
+
+    def peer_attach(self, rank, world, handles):
+        self.ctx.peer_attach(rank, world, handles)
+        self.peer_totals = as_tensor(self.ctx.peer_totals_ptr(), 4 * world, self.device).view(torch.int32)
+        self._index_base_ptr = self.ctx.peer_index_base_ptr()
+
+    def peer_detach(self):
+        self.ctx.peer_detach()
+
+    def peer_exchange_totals(self):
+        self.ctx.peer_exchange_totals()
+
+    def cull_finish_peer(self, frame):
+        self.ctx.cull_finish(frame, self._index_base_ptr)
+
+    def peer_push_grid(self):
+        self.ctx.peer_push_grid()
+
+    def peer_wait_grid(self):
+        self.ctx.peer_wait_grid()
+
+    def cull_sharded(self, frame):
+        self.ctx.cull_sharded(frame)
+
+    def peer_status(self):
+        return self.ctx.peer_status()
+
     def close(self):
         self.ctx.close()
 
@@ -88,13 +161,18 @@ class HvcfEngine:
 class ShardedCuller:
     """Runs steps 1-5 above on `engine`; every tensor lives on engine's device."""
 
-    def __init__(self, engine, grid, world=None, rank=None, group=None):
+    def __init__(self, engine, grid, world=None, rank=None, group=None, slabs=None, exchange="nccl"):
         self.engine = engine
         self.group = group
         self.world = dist.get_world_size(group) if world is None else world
         self.rank = dist.get_rank(group) if rank is None else rank
         self.grid = tuple(grid)
-        self.slabs = z_slabs(grid[2], self.world)
+        self.slabs = list(slabs) if slabs is not None else z_slabs(grid[2], self.world)
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange
+        if exchange == "peer":
+            self._attach_peers()
         xy = grid[0] * grid[1]
         self.cluster_ranges = [(a * xy, b * xy) for a, b in self.slabs]
         self.equal = len({b - a for a, b in self.slabs}) == 1
@@ -119,6 +197,26 @@ class ShardedCuller:
                 out[ph] = out.get(ph, 0.0) + e0.elapsed_time(e1)
         return out
 
+    def _attach_peers(self):
+        """every rank's IPC handles to every rank (the only host-side exchange of the peer mode, once)."""
+        mine = self.engine.peer_export()
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, mine, group=self.group)
+        else:
+            handles = [mine]
+        self.engine.peer_attach(self.rank, self.world, handles)
+        if self.world > 1:
+            dist.barrier(group=self.group)   # nobody starts a frame before everybody has mapped everybody
+
+    def close(self):
+        if self.exchange == "peer":
+            if self.world > 1:
+                dist.barrier(group=self.group)   # nobody unmaps while a peer may still push
+            self.engine.peer_detach()
+            if self.world > 1:
+                dist.barrier(group=self.group)
+
     def broadcast_lights(self, n):
         """step 1: rank 0's first 48*n bytes of engine.lights reach every rank."""
         self._mark("start")
@@ -131,6 +229,8 @@ class ShardedCuller:
         e = self.engine
         if self._marks is not None and (not self._marks or self._marks[-1][0] != "broadcast_lights"):
             self._mark("start")
+        if self.exchange == "peer":
+            return self._frame_peer(frame)
         e.cull_begin(frame)                                           # step 2
         self._mark("cull_begin")
         totals = torch.zeros(self.world, dtype=torch.int32, device=e.shard_total.device)
@@ -145,6 +245,26 @@ class ShardedCuller:
         if gather and self.world > 1:                                 # step 5
             self._gather(totals, bases)
             self._mark("gather_grid")
+        return totals, bases
+
+    def _frame_peer(self, frame):
+        """steps 2-5 with the exchange done by the GPUs (hvcf_cull_sharded); with phase timing on, the same five
+        stream-ordered calls are issued one by one so that events can be recorded between them."""
+        e = self.engine
+        if self._marks is None:
+            e.cull_sharded(frame)
+        else:
+            e.cull_begin(frame)
+            self._mark("cull_begin")
+            e.peer_exchange_totals()
+            self._mark("totals")
+            e.cull_finish_peer(frame)
+            self._mark("cull_finish")
+            e.peer_push_grid()
+            e.peer_wait_grid()
+            self._mark("gather_grid")
+        totals = e.peer_totals[: self.world]
+        bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
         return totals, bases
 
     def _gather(self, totals, bases):

@@ -149,6 +149,42 @@ HVCF_API int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream);
 HVCF_API int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base, void* stream);
 HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 
+/* The exchange step of the z-slab sharded grid done by the GPUs themselves over NVLink peer memory (new: the
+ * reference is single-GPU).  Every rank exports three allocations (light cells, light indices,
+ * a small mailbox) and attaches every other rank's; after that one call per frame,
+ *   hvcf_cull_sharded = hvcf_cull_begin                       (local: transform, test, counts, scan)
+ *                     + hvcf_peer_exchange_totals             (kernel: post total to all peers, wait, index base)
+ *                     + hvcf_cull_finish(own index base)      (cells + indices at GLOBAL positions)
+ *                     + hvcf_peer_push_grid                   (kernel: own cells + index segment into every peer)
+ *                     + hvcf_peer_wait_grid                   (kernel: until every peer's segment has arrived)
+ * leaves the FULL light grid (lightCells[], lightIndices[] in the reference layouts) on every rank, with no host
+ * round trip and no collective-library call.  All ranks must call it the same number of times.  Waits are bounded:
+ * a missing peer raises the error that hvcf_peer_status reports (after synchronising `stream`).
+ *   hvcf_peer_export        handle = 3 x cudaIpcMemHandle_t (64 B each), to be sent to the other processes
+ *   hvcf_peer_attach        handles[world], own entry ignored; peers are mapped with cudaIpcOpenMemHandle
+ *   hvcf_peer_attach_local  the same for contexts living in THIS process (same or peer-accessible devices)
+ *   hvcf_peer_detach        unmaps; call on every rank (after a barrier) before hvcf_destroy */
+#define HVCF_MAX_PEERS 16
+typedef struct hvcf_peer_handle
+{
+	unsigned char cells[64];
+	unsigned char indices[64];
+	unsigned char mailbox[64];
+} hvcf_peer_handle;
+HVCF_API int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out);
+HVCF_API int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_peer_handle* handles);
+HVCF_API int hvcf_peer_attach_local(hvcf_ctx* ctx, uint32_t rank, uint32_t world, hvcf_ctx* const* contexts);
+HVCF_API int hvcf_peer_detach(hvcf_ctx* ctx);
+HVCF_API int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream);
+HVCF_API int hvcf_peer_push_grid(hvcf_ctx* ctx, void* stream);
+HVCF_API int hvcf_peer_wait_grid(hvcf_ctx* ctx, void* stream);
+HVCF_API int hvcf_cull_sharded(hvcf_ctx* ctx, uint32_t frame, void* stream);
+/* device uint32[world]: every rank's index total of the last exchange (valid after hvcf_peer_exchange_totals) */
+HVCF_API int hvcf_peer_totals_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
+/* device uint32: this rank's index base of the last exchange (what hvcf_cull_sharded passes to hvcf_cull_finish) */
+HVCF_API int hvcf_peer_index_base_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
+HVCF_API int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error);
+
 HVCF_API int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out);
 
 /* VulkanBuffer::DownloadBufferData (Source/Vulkan/VulkanBuffer.cpp:169-178): synchronous
