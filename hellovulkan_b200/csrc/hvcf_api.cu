@@ -137,6 +137,10 @@ struct hvcf_ctx
 	bool peer_ipc = false;                     // peers were mapped with cudaIpcOpenMemHandle
 	uint32_t peer_epoch = 0;
 	uint32_t peer_frame = 0;                   // frame slot of the last hvcf_cull_begin
+	// hvcf_cull_begin_range progress of the open frame
+	bool range_open = false, range_cleared = false;
+	uint32_t range_frame = 0, range_transformed = 0, range_binned = 0; // lights (padded at the end) done so far
+	uint32_t open_launches = 0;
 
 	cudaEvent_t ubo_events[8]{};               // per frame slot: the staged UBO has been consumed
 	bool* ubo_set = nullptr;
@@ -675,18 +679,35 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	return HVCF_OK;
 }
 
-int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
+// ---- hierarchical frame, in three steps so that the light exchange of the sharded grid can be pipelined with it:
+//   open   AABBs if dirty, light-segment plan
+//   range  transform + level-0 binning of the lights [begin, end) (whole tiles; the last range takes the padding)
+//   close  count pass + finalize (per-cluster counts, offsets, shard total)
+static cudaError_t hier_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s)
+{
+	if (!ctx->ktimes)
+		return cudaSuccess;
+	if (!ctx->kev[frame][i])
+	{
+		cudaError_t e = cudaEventCreate(&ctx->kev[frame][i]);
+		if (e != cudaSuccess)
+			return e;
+	}
+	return cudaEventRecord(ctx->kev[frame][i], s);
+}
+
+static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who)
 {
 	if (!ctx)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin: null context");
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null context", who);
 	if (frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin: frame %u >= frame_count %u", frame, ctx->frame_count);
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: frame %u >= frame_count %u", who, frame, ctx->frame_count);
 	if (!ctx->ubo_set[frame])
-		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_begin: hvcf_set_ubo(frame %u) has not been called", frame);
+		return fail(HVCF_ERR_NOT_READY, "%s: hvcf_set_ubo(frame %u) has not been called", who, frame);
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
-	uint32_t launches = 0;
 	ctx->ev_valid[frame] = false;
+	ctx->open_launches = 0;
 	if (ctx->timing)
 		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][0], s));
 	if (ctx->aabb_dirty)
@@ -694,12 +715,199 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		const int rc = hvcf_generate_aabbs(ctx, frame, stream);
 		if (rc != HVCF_OK)
 			return rc;
+		++ctx->open_launches;
+	}
+	if (ctx->hier)
+	{
+		// at least one (all-padding) tile, so that pass 2 always writes the light cells
+		const uint32_t n = ctx->num_lights;
+		const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
+		const uint32_t tiles_total = padded / kTileLights;
+		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
+		ctx->h_tiles_total = tiles_total;
+		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
+		HVCF_CUDA(hier_kmark(ctx, frame, 0, s));
+	}
+	ctx->range_frame = frame;
+	ctx->range_transformed = ctx->range_binned = 0;
+	ctx->range_cleared = false;
+	ctx->range_open = true;
+	return HVCF_OK;
+}
+
+static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t end, uint32_t flags, cudaStream_t s)
+{
+	const uint32_t n = ctx->num_lights;
+	const bool last = end >= n;
+	const uint32_t end_padded = last ? round_up_u32(n ? n : 1, kTileLights) : end;
+	DeviceStats* stats = &ctx->d_stats[frame];
+	// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the first transform launch
+	uint32_t* zero = ctx->range_cleared ? nullptr : ctx->d_hscratch;
+	const uint32_t zero_words = ctx->range_cleared ? 0u : ctx->cluster_count * kHMaxChunks;
+	DeviceStats* clear_stats = ctx->range_cleared ? nullptr : stats;
+	if (flags & HVCF_RANGE_TRANSFORM)
+	{
+		const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+		LightAnim anim_storage{};
+		const LightAnim* anim = nullptr;
+		if (ctx->anim_len && n)
+		{
+			anim_storage.base_y = ctx->d_base_y + begin;
+			anim_storage.table = ctx->d_anim_table;
+			anim_storage.mask = ctx->anim_len - 1;
+			anim_storage.step = ctx->anim_step[frame] + begin;
+			anim_storage.amplitude = ctx->anim_amplitude;
+			anim_storage.lights_rw = const_cast<hvcf_light_data*>(lights) + begin; // the moved position is written back, as UpdateLightPosition does
+			anim = &anim_storage;
+		}
+		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights + begin, n - begin, end_padded - begin, ctx->d_lights_view + begin, zero,
+			zero_words, clear_stats, s, anim));
+		ctx->range_cleared = true;
+		ctx->range_transformed = end_padded;
+		++ctx->open_launches;
+		HVCF_CUDA(hier_kmark(ctx, frame, 1, s));
+	}
+	if (flags & HVCF_RANGE_BIN)
+	{
+		if (!ctx->range_cleared) // the view records came from elsewhere: a clear-only launch
+		{
+			HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], nullptr, 0, 0, ctx->d_lights_view, zero, zero_words, clear_stats, s, nullptr));
+			ctx->range_cleared = true;
+			++ctx->open_launches;
+		}
+		if (!ctx->hier_v1)
+		{
+			BinParams b{};
+			b.lights_view = ctx->d_lights_view;
+			b.cb_union = ctx->d_cb_union;
+			b.ncb = ctx->hp.ncb;
+			b.tiles_cap = ctx->tiles_cap;
+			b.bin_count = ctx->d_bin_count;
+			b.bin_rec = ctx->d_bin_rec;
+			b.bin_idx = ctx->d_bin_idx;
+			b.stats = stats;
+			b.tile_begin = begin / kTileLights;
+			HVCF_CUDA(launch_hier_bin(b, (end_padded - begin) / kTileLights, s));
+			++ctx->open_launches;
+		}
+		ctx->range_binned = end_padded;
+		HVCF_CUDA(hier_kmark(ctx, frame, 2, s));
+	}
+	return HVCF_OK;
+}
+
+static int hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
+{
+	DeviceStats* stats = &ctx->d_stats[frame];
+	HierParams p = hier_params(ctx, frame);
+	if (ctx->timing)
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+	// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
+	// later segments then begin with the dense clusters already known to be full (PDL-chained, one extra launch)
+	const uint32_t head = ctx->h_split_head < ctx->h_num_segs ? ctx->h_split_head : 0u;
+	uint32_t launches = ctx->open_launches;
+	if (head)
+	{
+		p.seg_end = head;
+		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
+		p.seg_begin = head;
+		p.seg_end = ctx->h_num_segs;
 		++launches;
 	}
-	DeviceStats* stats = &ctx->d_stats[frame];
-	if (!ctx->hier)
-		HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
+	HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
+	HVCF_CUDA(hier_kmark(ctx, frame, 3, s));
+	if (ctx->timing)
+	{
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
+		ctx->ev_valid[frame] = true;
+	}
+	FinalizeParams f;
+	f.seg_counts = ctx->d_hseg_counts;
+	f.seg_prefix = ctx->d_hseg_prefix;
+	f.num_segs = ctx->h_num_segs;
+	f.cluster_count = ctx->cluster_count;
+	f.cap = ctx->cap;
+	ctx->epoch = ctx->epoch >= 0x3fffffffu ? 1u : ctx->epoch + 1u;
+	f.epoch = ctx->epoch;
+	f.scan_state = ctx->d_scan_state;
+	f.counts = ctx->d_counts;
+	f.offsets = ctx->d_hoffsets;
+	f.shard_total = ctx->d_shard_total;
+	f.stats = stats;
+	HVCF_CUDA(launch_hier_finalize(f, s));
+	HVCF_CUDA(hier_kmark(ctx, frame, 4, s));
+	ctx->last_launches[frame] = launches + 2;
+	ctx->range_open = false;
+	return HVCF_OK;
+}
+
+int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, uint32_t flags, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: null context");
+	if (!ctx->hier || ctx->hier_v1)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_begin_range: hierarchical mode only");
+	if (flags == 0)
+		flags = HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN;
+	if (flags & ~static_cast<uint32_t>(HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: unknown flags 0x%x", flags);
 	const uint32_t n = ctx->num_lights;
+	if (light_begin % kTileLights || light_begin > light_end || light_end > n || (light_end < n && light_end % kTileLights) ||
+		(light_begin == light_end && n != 0))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: [%u,%u) of %u lights: ranges are whole %u-light tiles, the last one ends at the light count",
+			light_begin, light_end, n, kTileLights);
+	const bool first = light_begin == 0 && (!ctx->range_open || ctx->range_frame != frame ||
+		((flags & HVCF_RANGE_TRANSFORM) ? ctx->range_transformed != 0 : ctx->range_binned != 0));
+	if (first)
+	{
+		const int rc = cull_open(ctx, frame, stream, "hvcf_cull_begin_range");
+		if (rc != HVCF_OK)
+			return rc;
+	}
+	if (!ctx->range_open || ctx->range_frame != frame)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_begin_range: the first range of a frame starts at light 0");
+	if ((flags & HVCF_RANGE_TRANSFORM) && light_begin != ctx->range_transformed)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: transform ranges must be consecutive (next light %u, got %u)", ctx->range_transformed, light_begin);
+	if ((flags & HVCF_RANGE_BIN) && light_begin != ctx->range_binned)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: bin ranges must be consecutive (next light %u, got %u)", ctx->range_binned, light_begin);
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	const int rc = hier_range(ctx, frame, light_begin, light_end, flags, s);
+	if (rc != HVCF_OK)
+		return rc;
+	if ((flags & HVCF_RANGE_BIN) && light_end >= n)
+		return hier_close(ctx, frame, s);
+	return HVCF_OK;
+}
+
+int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes)
+{
+	if (!ctx || !out_device_ptr)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_lights_view_ptr: null argument");
+	*out_device_ptr = ctx->d_lights_view;
+	if (out_bytes)
+		*out_bytes = static_cast<size_t>(ctx->padded_capacity) * 16;
+	return HVCF_OK;
+}
+
+int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	int rc = cull_open(ctx, frame, stream, "hvcf_cull_begin");
+	if (rc != HVCF_OK)
+		return rc;
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	uint32_t launches = ctx->open_launches;
+	DeviceStats* stats = &ctx->d_stats[frame];
+	const uint32_t n = ctx->num_lights;
+	if (ctx->hier)
+	{
+		rc = hier_range(ctx, frame, 0, n, ctx->hier_v1 ? HVCF_RANGE_TRANSFORM : (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN), s);
+		if (rc != HVCF_OK)
+			return rc;
+		return hier_close(ctx, frame, s);
+	}
+	ctx->range_open = false;
+	HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
 	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
 	LightAnim anim_storage{};
 	const LightAnim* anim = nullptr;
@@ -712,85 +920,6 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		anim_storage.amplitude = ctx->anim_amplitude;
 		anim_storage.lights_rw = const_cast<hvcf_light_data*>(lights); // the moved position is written back, as UpdateLightPosition does
 		anim = &anim_storage;
-	}
-	if (ctx->hier)
-	{
-		// at least one (all-padding) tile, so that pass 2 always writes the light cells
-		const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
-		const uint32_t tiles_total = padded / kTileLights;
-		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
-		ctx->h_tiles_total = tiles_total;
-		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
-			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
-		auto kmark = [&](int i) -> cudaError_t {
-			if (!ctx->ktimes)
-				return cudaSuccess;
-			if (!ctx->kev[frame][i])
-			{
-				cudaError_t e = cudaEventCreate(&ctx->kev[frame][i]);
-				if (e != cudaSuccess)
-					return e;
-			}
-			return cudaEventRecord(ctx->kev[frame][i], s);
-		};
-		HVCF_CUDA(kmark(0));
-		// ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit scratch are cleared by the transform kernel
-		HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights, n, padded, ctx->d_lights_view, ctx->d_hscratch,
-			ctx->cluster_count * kHMaxChunks, stats, s, anim));
-		HVCF_CUDA(kmark(1));
-		HierParams p = hier_params(ctx, frame);
-		if (!ctx->hier_v1)
-		{
-			BinParams b{};
-			b.lights_view = ctx->d_lights_view;
-			b.cb_union = ctx->d_cb_union;
-			b.ncb = ctx->hp.ncb;
-			b.tiles_cap = ctx->tiles_cap;
-			b.bin_count = ctx->d_bin_count;
-			b.bin_rec = ctx->d_bin_rec;
-			b.bin_idx = ctx->d_bin_idx;
-			b.stats = stats;
-			HVCF_CUDA(launch_hier_bin(b, tiles_total, s));
-			++launches;
-		}
-		HVCF_CUDA(kmark(2));
-		if (ctx->timing)
-			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
-		// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
-		// later segments then begin with the dense clusters already known to be full (PDL-chained, one extra launch)
-		const uint32_t head = ctx->h_split_head < ctx->h_num_segs ? ctx->h_split_head : 0u;
-		if (head)
-		{
-			p.seg_end = head;
-			HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
-			p.seg_begin = head;
-			p.seg_end = ctx->h_num_segs;
-			++launches;
-		}
-		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
-		HVCF_CUDA(kmark(3));
-		if (ctx->timing)
-		{
-			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
-			ctx->ev_valid[frame] = true;
-		}
-		FinalizeParams f;
-		f.seg_counts = ctx->d_hseg_counts;
-		f.seg_prefix = ctx->d_hseg_prefix;
-		f.num_segs = ctx->h_num_segs;
-		f.cluster_count = ctx->cluster_count;
-		f.cap = ctx->cap;
-		ctx->epoch = ctx->epoch >= 0x3fffffffu ? 1u : ctx->epoch + 1u;
-		f.epoch = ctx->epoch;
-		f.scan_state = ctx->d_scan_state;
-		f.counts = ctx->d_counts;
-		f.offsets = ctx->d_hoffsets;
-		f.shard_total = ctx->d_shard_total;
-		f.stats = stats;
-		HVCF_CUDA(launch_hier_finalize(f, s));
-		HVCF_CUDA(kmark(4));
-		ctx->last_launches[frame] = launches + 3;
-		return HVCF_OK;
 	}
 	const uint32_t padded = round_up_u32(n, kTileLights);
 	const uint32_t tiles_total = padded / kTileLights;
@@ -1040,8 +1169,9 @@ int hvcf_peer_push_grid(hvcf_ctx* ctx, void* stream)
 	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
 		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_push_grid: no peers attached or no totals exchanged");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
-	// enough CTAs to keep the NVLink ports busy without taking the whole GPU: 2 per SM
-	HVCF_CUDA(launch_peer_push(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->cluster_begin, ctx->cluster_count, 296u,
+	// enough CTAs to keep the NVLink ports busy: 4 per SM by default (HVCF_PEER_BLOCKS overrides, for sweeps)
+	static const uint32_t blocks = static_cast<uint32_t>(env_int("HVCF_PEER_BLOCKS", 592) > 0 ? env_int("HVCF_PEER_BLOCKS", 592) : 592);
+	HVCF_CUDA(launch_peer_push(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->cluster_begin, ctx->cluster_count, blocks,
 		static_cast<cudaStream_t>(stream)));
 	return HVCF_OK;
 }

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 	__shared__ __align__(128) unsigned char s_tile[kTileBytes];
 	__shared__ __align__(8) uint64_t bar;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint32_t tile_id = blockIdx.y, cb = blockIdx.x * kBinWarps + warp;
+	const uint32_t tile_id = p.tile_begin + blockIdx.y, cb = blockIdx.x * kBinWarps + warp;
 	grid_dep_launch();
 	if (threadIdx.x == 0)
 	{

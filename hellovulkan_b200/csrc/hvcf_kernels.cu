@@ -532,7 +532,10 @@ cudaError_t launch_light_transform(const hvcf_cluster_forward_ubo* ubo, const hv
 	const uint32_t pairs = padded_lights / 2;
 	if (pairs == 0 && zero_words == 0 && !stats)
 		return cudaSuccess;
-	const uint32_t blocks = pairs ? (pairs + 255) / 256 : 1;
+	uint32_t blocks = pairs ? (pairs + 255) / 256 : 1;
+	const uint32_t zero_blocks = (zero_words + 1023) / 1024 < 592u ? (zero_words + 1023) / 1024 : 592u; // a clear-only launch still spreads out
+	if (blocks < zero_blocks)
+		blocks = zero_blocks;
 	if (anim)
 		light_transform_kernel<true><<<blocks, 256, 0, stream>>>(ubo, lights, num_lights, pairs, out, zero, zero_words, stats, *anim);
 	else

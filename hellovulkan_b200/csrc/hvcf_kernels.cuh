@@ -131,6 +131,7 @@ struct BinParams
 	float4* bin_rec;
 	uint16_t* bin_idx;
 	DeviceStats* stats;
+	uint32_t tile_begin;           // first tile of this launch (grid.y counts from it)
 };
 
 struct FinalizeParams

@@ -125,7 +125,25 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 		if (b4 > e)
 			b4 = e;
 		const size_t e4 = b4 + ((e - b4) & ~static_cast<size_t>(3));
-		for (size_t i = b4 / 4 + tid; i < e4 / 4; i += nth)
+		// four independent 16 B loads per thread per trip, then the remote stores: enough bytes in flight per SM to
+		// keep the NVLink ports busy (one load per trip measured 150 GB/s at 2 GPUs, profiles/r01e)
+		size_t i = b4 / 4 + tid;
+		const size_t iend = e4 / 4;
+		for (; i + 3 * nth < iend; i += 4 * nth)
+		{
+			uint4 v[4];
+#pragma unroll
+			for (int u = 0; u < 4; ++u)
+				v[u] = __ldcs(reinterpret_cast<const uint4*>(src) + i + u * nth);
+			for (uint32_t r = 0; r < p.world; ++r)
+				if (r != p.rank)
+				{
+#pragma unroll
+					for (int u = 0; u < 4; ++u)
+						reinterpret_cast<uint4*>(p.indices[r])[i + u * nth] = v[u];
+				}
+		}
+		for (; i < iend; i += nth)
 		{
 			const uint4 v = reinterpret_cast<const uint4*>(src)[i];
 			for (uint32_t r = 0; r < p.world; ++r)

@@ -124,6 +124,16 @@ class HvcfEngine:
         self.base.copy_(base.view(1))
         self.ctx.cull_finish(frame, self.base.data_ptr())
 
+    # -- hvcf_cull_begin in pieces, for pipelining the light broadcast --
+    def cull_begin_range(self, frame, begin, end, flags=0):
+        self.ctx.cull_begin_range(frame, begin, end, flags)
+
+    def lights_view(self):
+        if not hasattr(self, "_lights_view"):
+            ptr, nbytes = self.ctx.lights_view_ptr()
+            self._lights_view = as_tensor(ptr, nbytes, self.device)
+        return self._lights_view
+
     # -- exchange over peer memory (csrc/hvcf_peer.cu) --
     def peer_export(self):
         return self.ctx.peer_export()
@@ -245,6 +255,74 @@ class ShardedCuller:
         if gather and self.world > 1:                                 # step 5
             self._gather(totals, bases)
             self._mark("gather_grid")
+        return totals, bases
+
+    # ---- light exchange pipelined with the first kernels of the frame -------------------------------------------
+    @staticmethod
+    def chunk_bounds(n, chunks, tile=1024):
+        """[(begin, end)] covering [0, n): whole tiles, the last chunk ends at n; at most `chunks` pieces."""
+        tiles = max(1, -(-n // tile))
+        chunks = max(1, min(chunks, tiles))
+        per = -(-tiles // chunks)
+        out, b = [], 0
+        while b < n or not out:
+            e = min(n, b + per * tile)
+            out.append((b, e))
+            if e >= n:
+                break
+            b = e
+        return out
+
+    def frame_pipelined(self, frame, n, chunks=8, wire="raw"):
+        """steps 1-5 with step 1 cut into chunks: while chunk q+1 is on the wire, chunk q is transformed and binned
+        (hvcf_cull_begin_range).  wire="raw": the 48 B LightData records travel and every rank transforms them
+        (every rank ends up with the reference light buffer); wire="view": rank 0 transforms each chunk once and the
+        16 B view-space culling records travel (a third of the bytes; the other ranks hold no LightData).
+        Peer exchange only."""
+        if self.exchange != "peer":
+            raise ValueError("frame_pipelined needs exchange='peer'")
+        if wire not in ("raw", "view"):
+            raise ValueError("wire must be 'raw' or 'view'")
+        e = self.engine
+        T, B = 1, 2
+        if e.num_lights != n:
+            e.set_num_lights(n)
+        bounds = self.chunk_bounds(n, chunks)
+        self._mark("start")
+        if self.world == 1:
+            for b, en in bounds:
+                e.cull_begin_range(frame, b, en, T | B)
+        elif wire == "raw":
+            works = [dist.broadcast(e.lights[48 * b: 48 * en], src=0, group=self.group, async_op=True) for b, en in bounds]
+            for (b, en), w in zip(bounds, works):
+                w.wait()                                   # the compute stream waits for this chunk only
+                e.cull_begin_range(frame, b, en, T | B)
+        else:
+            view = e.lights_view()
+            padded = -(-max(n, 1) // 1024) * 1024
+            works = []
+            for b, en in bounds:
+                if self.rank == 0:
+                    e.cull_begin_range(frame, b, en, T)
+                hi = padded if en >= n else en
+                works.append(dist.broadcast(view[16 * b: 16 * hi], src=0, group=self.group, async_op=True))
+            for (b, en), w in zip(bounds, works):
+                if self.rank != 0:
+                    w.wait()
+                e.cull_begin_range(frame, b, en, B)
+            if self.rank == 0:
+                for w in works:
+                    w.wait()
+        self._mark("lights+cull_begin")
+        e.peer_exchange_totals()
+        self._mark("totals")
+        e.cull_finish_peer(frame)
+        self._mark("cull_finish")
+        e.peer_push_grid()
+        e.peer_wait_grid()
+        self._mark("gather_grid")
+        totals = e.peer_totals[: self.world]
+        bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
         return totals, bases
 
     def _frame_peer(self, frame):

@@ -147,6 +147,17 @@ HVCF_API int hvcf_cull(hvcf_ctx* ctx, uint32_t frame, void* stream);
  *          positions, so shard segments concatenate without a fix-up pass. */
 HVCF_API int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream);
 HVCF_API int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base, void* stream);
+/* hvcf_cull_begin in pieces, so that the light exchange of the sharded grid (the ncclBroadcast of the light buffer)
+ * overlaps the first kernels of the frame: lights [light_begin, light_end) are transformed to view space and binned
+ * against the cluster-group boxes while later ranges are still in flight.  Ranges are whole 1,024-light tiles, issued
+ * in ascending order from 0; the call that reaches the light count also runs the count pass and the scan, i.e.
+ * completes hvcf_cull_begin.  flags = 0 means TRANSFORM | BIN.  With BIN alone the view-space records of the range
+ * (16 B per light, hvcf_lights_view_ptr) must already be in place -- e.g. broadcast from the one rank that ran
+ * TRANSFORM on them, 16 B per light on the wire instead of 48.  Hierarchical mode only. */
+#define HVCF_RANGE_TRANSFORM 1u
+#define HVCF_RANGE_BIN 2u
+HVCF_API int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, uint32_t flags, void* stream);
+HVCF_API int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes);
 HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 
 /* The exchange step of the z-slab sharded grid done by the GPUs themselves over NVLink peer memory (new: the

@@ -145,3 +145,79 @@ def test_calls_without_peers_fail(hv):
         for call in (ctx.peer_exchange_totals, ctx.peer_push_grid, ctx.peer_wait_grid, lambda: ctx.cull_sharded(0)):
             with pytest.raises(hv.HvcfError):
                 call()
+
+
+# ---- hvcf_cull_begin in pieces (the light exchange pipelined with the first kernels of the frame) ----------------
+def cull_in_ranges(hv, ctx, n, frame, chunks, flags=0):
+    from hellovulkan_b200.sharded import ShardedCuller
+    for b, e in ShardedCuller.chunk_bounds(n, chunks):
+        ctx.cull_begin_range(frame, b, e, flags)
+
+
+@pytest.mark.parametrize("chunks", [1, 3, 64])
+@pytest.mark.parametrize("n", [0, 1, 1024, 5000, 65536])
+def test_ranges_give_the_bytes_of_one_call(hv, oracle, n, chunks):
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    lights = oracle.init_lights(n)
+    want_cells, want_idx, want_total = run_single(hv, GRID_A, ubo, lights)
+    with hv.Context(grid=GRID_A, max_lights=max(n, 1)) as ctx:
+        ctx.set_lights(lights)
+        for f in range(2):
+            ctx.set_ubo(f, ubo)
+        for f in (0, 1, 0):                      # several frames: the per-frame scratch is cleared by the first range
+            cull_in_ranges(hv, ctx, n, f, chunks)
+            ctx.cull_finish(f, None)
+            cells = ctx.download_light_cells()
+            total = ctx.download_total(f)
+            assert total == want_total
+            assert cells.tobytes() == want_cells.tobytes()
+            assert ctx.download_light_indices(total).tobytes() == want_idx.tobytes()
+
+
+def test_view_records_transformed_elsewhere(hv, torch_mod, oracle):
+    """wire='view': one context transforms, the 16 B view records are copied, the other context only bins"""
+    from hellovulkan_b200.sharded import as_tensor
+    n = 20000
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    lights = oracle.init_lights(n)
+    want_cells, want_idx, want_total = run_single(hv, GRID_A, ubo, lights)
+    with hv.Context(grid=GRID_A, max_lights=n) as a, hv.Context(grid=GRID_A, max_lights=n) as b:
+        a.set_lights(lights)
+        b.set_lights(np.zeros(n, lights.dtype))     # b never sees the LightData; only the count matters
+        for c in (a, b):
+            c.set_ubo(0, ubo)
+        dev = torch_mod.device("cuda", 0)
+        va = as_tensor(*a.lights_view_ptr(), dev)
+        vb = as_tensor(*b.lights_view_ptr(), dev)
+        for frame_no in range(2):
+            cull_in_ranges(hv, a, n, 0, 4, hv.RANGE_TRANSFORM)
+            torch_mod.cuda.synchronize()
+            vb.copy_(va)
+            torch_mod.cuda.synchronize()
+            cull_in_ranges(hv, b, n, 0, 5, hv.RANGE_BIN)
+            b.cull_finish(0, None)
+            total = b.download_total(0)
+            assert total == want_total
+            assert b.download_light_cells().tobytes() == want_cells.tobytes()
+            assert b.download_light_indices(total).tobytes() == want_idx.tobytes()
+
+
+def test_range_argument_errors(hv, oracle):
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    lights = oracle.init_lights(5000)
+    with hv.Context(grid=GRID_A, max_lights=5000) as ctx:
+        ctx.set_lights(lights)
+        ctx.set_ubo(0, ubo)
+        for args in ((0, 100, 1000), (0, 0, 1000), (0, 1024, 2048), (0, 0, 6000), (0, 2048, 1024), (0, 0, 2048, 8)):
+            with pytest.raises(hv.HvcfError):
+                ctx.cull_begin_range(*args)
+        ctx.cull_begin_range(0, 0, 2048)
+        with pytest.raises(hv.HvcfError):
+            ctx.cull_begin_range(0, 3072, 5000)   # gap
+        ctx.cull_begin_range(0, 2048, 5000)
+        ctx.cull_finish(0, None)
+    with hv.Context(grid=GRID_A, max_lights=5000, mode=1) as brute:
+        brute.set_lights(lights)
+        brute.set_ubo(0, ubo)
+        with pytest.raises(hv.HvcfError):
+            brute.cull_begin_range(0, 0, 5000)
