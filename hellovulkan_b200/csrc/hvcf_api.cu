@@ -45,6 +45,8 @@ int env_int(const char* name, int dflt)
 }
 } // namespace
 
+constexpr uint32_t kBin2MinGroups = 48;
+
 struct hvcf_ctx
 {
 	hvcf_config cfg{};
@@ -78,6 +80,8 @@ struct hvcf_ctx
 	uint32_t* d_hlane_cluster = nullptr;
 	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
 	float* d_cb_union = nullptr;             // [ncb][8]
+	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
+	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel)
 	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
 	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
 	uint16_t* d_bin_idx = nullptr;
@@ -199,6 +203,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_hoffsets);
 	cudaFree(c->d_hlane_cluster);
 	cudaFree(c->d_cb_union);
+	cudaFree(c->d_sb_union);
 	cudaFree(c->d_bin_count);
 	cudaFree(c->d_bin_rec);
 	cudaFree(c->d_bin_idx);
@@ -371,6 +376,13 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->hier_v1 = env_int("HVCF_HIER_V1", 0) != 0;
 		c->ktimes = env_int("HVCF_KERNEL_TIMES", 0) != 0;
 		c->tiles_cap = max_tiles;
+		// two-level level-0 binning pays once a shard has many cluster groups (HVCF_BIN2=0/1 forces it off/on)
+		const int bin2 = env_int("HVCF_BIN2", -1);
+		if (!c->hier_v1 && (bin2 > 0 || (bin2 < 0 && c->hp.ncb >= kBin2MinGroups)))
+		{
+			c->bin_sg = (c->hp.ncb + 31) / 32 > 8 ? (c->hp.ncb + 31) / 32 : 8;
+			c->bin_ns = (c->hp.ncb + c->bin_sg - 1) / c->bin_sg;
+		}
 	}
 
 #define HVCF_ALLOC(ptr, bytes)                                                              \
@@ -404,6 +416,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		{
 			const size_t slots = static_cast<size_t>(c->hp.ncb) * c->tiles_cap;
 			HVCF_ALLOC(c->d_cb_union, sizeof(float) * 8 * c->hp.ncb);
+			HVCF_ALLOC(c->d_sb_union, sizeof(float) * 8 * (c->bin_ns ? c->bin_ns : 1));
 			HVCF_ALLOC(c->d_bin_count, sizeof(uint32_t) * slots);
 			HVCF_ALLOC(c->d_bin_rec, sizeof(float4) * slots * kBinCap);
 			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
@@ -670,7 +683,11 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	HVCF_CUDA(cudaMemcpyAsync(dz, hz, sizeof(float) * (ctx->Z + 1), cudaMemcpyHostToDevice, s));
 	HVCF_CUDA(launch_aabb_generate(&ctx->d_ubo[frame], dz, ctx->d_aabb, ctx->cluster_total, s));
 	if (ctx->hier && !ctx->hier_v1) // level-0 union boxes of the cluster groups follow the AABBs
+	{
 		HVCF_CUDA(launch_hier_unions(ctx->d_hlane_cluster, ctx->d_aabb, ctx->cluster_begin, ctx->hp.K, ctx->hp.ncb, ctx->d_cb_union, s));
+		if (ctx->bin_ns)
+			HVCF_CUDA(launch_hier_super_unions(ctx->d_cb_union, ctx->hp.ncb, ctx->bin_sg, ctx->bin_ns, ctx->d_sb_union, s));
+	}
 	memcpy(ctx->aabb_key, u.camera_inverse_projection, 64);
 	ctx->aabb_key[16] = u.camera_near;
 	ctx->aabb_key[17] = u.camera_far;
@@ -788,6 +805,9 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			b.bin_idx = ctx->d_bin_idx;
 			b.stats = stats;
 			b.tile_begin = begin / kTileLights;
+			b.sb_union = ctx->d_sb_union;
+			b.sg = ctx->bin_sg;
+			b.ns = ctx->bin_ns;
 			HVCF_CUDA(launch_hier_bin(b, (end_padded - begin) / kTileLights, s));
 			++ctx->open_launches;
 		}

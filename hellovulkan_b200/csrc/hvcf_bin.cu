@@ -477,6 +477,133 @@ static cudaLaunchAttribute pdl_attr()
 	return a;
 }
 
+// ======================================================================================================
+// Two-level level 0 ("bin2"), for shards with many cluster groups (grid C: 216 groups; one level costs groups x lights
+// tests and was 2.9 of the 5.4 ms of the 16M-light frame, profiles/r01d).  Groups are taken SG at a time into
+// super-groups (consecutive groups are spatial neighbours: blocks run x, then y, then z).  One CTA per light tile:
+//   phase A  warp w tests the whole tile against super-group w, w + 8, ... (lane = light pair, FADD2/FMUL2, ballot/popc)
+//            and compacts the survivors' tile indices, in light order, into a shared-memory list per super-group;
+//   phase B  warp w takes groups w, w + 8, ... (one of every super-group when SG == 8, so the warps stay balanced), walks
+//            its super-group's list (lane = surviving light, gathered from the staged tile) against the group's own
+//            union box and writes the (group, tile) slot exactly as hier_bin_kernel does.
+// The super box contains the group boxes and the test is the same monotone float sequence, so phase A can only pass
+// more lights than phase B needs: the slots are byte-identical to the one-level kernel's.  The tile is staged once
+// per tile instead of once per 8 groups.
+// ======================================================================================================
+__global__ void hier_super_unions_kernel(const float* __restrict__ cb_union, uint32_t ncb, uint32_t sg, float* __restrict__ sb_union)
+{
+	const uint32_t s = blockIdx.x, c = threadIdx.x; // c: 0..2 lo, 4..6 hi
+	if (c >= 8)
+		return;
+	const bool is_hi = c >= 4;
+	float v = is_hi ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
+	for (uint32_t g = s * sg; g < min(ncb, (s + 1) * sg); ++g)
+	{
+		const float u = cb_union[static_cast<size_t>(g) * 8 + c];
+		v = is_hi ? fmaxf(v, u) : fminf(v, u);
+	}
+	sb_union[static_cast<size_t>(s) * 8 + c] = (c & 3) == 3 ? 0.0f : v;
+}
+
+__global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinParams p)
+{
+	extern __shared__ __align__(128) unsigned char s_dyn[];
+	unsigned char* const s_tile = s_dyn;                                               // kTileBytes
+	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_dyn + kTileBytes);         // [ns][kTileLights]
+	uint32_t* const s_cnt = reinterpret_cast<uint32_t*>(s_list + static_cast<size_t>(p.ns) * kTileLights); // [ns]
+	__shared__ __align__(8) uint64_t bar;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t tile_id = p.tile_begin + blockIdx.x;
+	grid_dep_launch();
+	if (threadIdx.x == 0)
+	{
+		mbar_init(&bar, 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	grid_dep_wait(); // the tile is written by the transform kernel of this frame (or arrived from another rank)
+	if (threadIdx.x == 0)
+	{
+		mbar_arrive_expect_tx(&bar, kTileBytes);
+		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
+	}
+	mbar_wait(&bar, 0);
+	const float4* tile = reinterpret_cast<const float4*>(s_tile);
+	const uint32_t lt = lanemask_lt();
+	unsigned long long tests = 0;
+
+	// ---- phase A: super-group survivor lists ----
+	for (uint32_t s = warp; s < p.ns; s += kBinWarps)
+	{
+		const float4* u = reinterpret_cast<const float4*>(p.sb_union + static_cast<size_t>(s) * 8);
+		const float4 a4 = __ldg(u), b4 = __ldg(u + 1);
+		const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
+		uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
+		uint32_t cnt = 0;
+#pragma unroll 4
+		for (uint32_t g = 0; g < kTileGroups; ++g)
+		{
+			const float4 a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+			bool h0, h1;
+			sphere_box_hit2(a, b, lo, hi, h0, h1);
+			const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+			if (h0)
+				list[cnt + __popc(m0 & lt)] = static_cast<uint16_t>(g * 64 + lane);
+			if (h1)
+				list[cnt + __popc(m0) + __popc(m1 & lt)] = static_cast<uint16_t>(g * 64 + 32 + lane);
+			cnt += __popc(m0) + __popc(m1);
+		}
+		if (lane == 0)
+			s_cnt[s] = cnt;
+		tests += kTileLights;
+	}
+	__syncthreads();
+
+	// ---- phase B: every group against its super-group's survivors ----
+	const float* tile_f = reinterpret_cast<const float*>(s_tile);
+	for (uint32_t cb = warp; cb < p.ncb; cb += kBinWarps)
+	{
+		const uint32_t s = cb / p.sg;
+		const uint32_t ns = s_cnt[s];
+		const uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
+		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
+		const float4 a4 = __ldg(u), b4 = __ldg(u + 1);
+		const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
+		const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+		float4* const rec = p.bin_rec + slot;
+		uint16_t* const idx = p.bin_idx + slot;
+		uint32_t cnt = 0;
+		for (uint32_t i0 = 0; i0 < ns; i0 += 32)
+		{
+			const uint32_t i = i0 + lane;
+			bool hit = false;
+			uint32_t t = 0;
+			float x = 0.0f, y = 0.0f, z = 0.0f, r2 = -1.0f;
+			if (i < ns)
+			{
+				t = list[i];
+				// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
+				const uint32_t f = (((t >> 6) * 64 + (t & 31)) << 2) + ((t >> 5) & 1);
+				x = tile_f[f], y = tile_f[f + 2], z = tile_f[f + 128], r2 = tile_f[f + 130];
+				hit = sphere_box_hit(x, y, z, r2, lo, hi);
+			}
+			const uint32_t m = __ballot_sync(0xffffffffu, hit);
+			const uint32_t d = cnt + __popc(m & lt);
+			if (hit && d < kBinCap)
+			{
+				rec[d] = make_float4(x, y, z, r2);
+				idx[d] = static_cast<uint16_t>(t);
+			}
+			cnt += __popc(m);
+		}
+		if (lane == 0)
+			p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
+		tests += ns;
+	}
+	if (lane == 0 && tests)
+		atomicAdd(&p.stats->prefilter_tests, tests);
+}
+
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
 	float* cb_union, cudaStream_t stream)
 {
@@ -486,10 +613,44 @@ cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aa
 	return cudaGetLastError();
 }
 
+cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream)
+{
+	if (ns == 0)
+		return cudaSuccess;
+	hier_super_unions_kernel<<<ns, 32, 0, stream>>>(cb_union, ncb, sg, sb_union);
+	return cudaGetLastError();
+}
+
+size_t hier_bin2_smem_bytes(uint32_t ns) { return kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) + static_cast<size_t>(ns) * sizeof(uint32_t); }
+
+static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStream_t stream)
+{
+	const size_t smem = hier_bin2_smem_bytes(p.ns);
+	static size_t configured = 0;
+	if (smem > configured)
+	{
+		cudaError_t e = cudaFuncSetAttribute(hier_bin2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		if (e != cudaSuccess)
+			return e;
+		configured = smem;
+	}
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3(tiles, 1, 1);
+	cfg.blockDim = dim3(kBinWarps * 32, 1, 1);
+	cfg.dynamicSmemBytes = smem;
+	cfg.stream = stream;
+	cudaLaunchAttribute attr = pdl_attr();
+	cfg.attrs = &attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_bin2_kernel, p);
+}
+
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream)
 {
 	if (p.ncb == 0 || tiles == 0)
 		return cudaSuccess;
+	if (p.ns)
+		return launch_hier_bin2(p, tiles, stream);
 	cudaLaunchConfig_t cfg{};
 	cfg.gridDim = dim3((p.ncb + kBinWarps - 1) / kBinWarps, tiles, 1);
 	cfg.blockDim = dim3(kBinWarps * 32, 1, 1);

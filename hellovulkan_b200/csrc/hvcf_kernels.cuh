@@ -132,6 +132,10 @@ struct BinParams
 	uint16_t* bin_idx;
 	DeviceStats* stats;
 	uint32_t tile_begin;           // first tile of this launch (grid.y counts from it)
+	// two-level variant (hier_bin2_kernel): ns > 0 selects it
+	const float* sb_union;         // [ns][8] union boxes of the super-groups
+	uint32_t sg;                   // groups per super-group
+	uint32_t ns;                   // super-groups, at most 32
 };
 
 struct FinalizeParams
@@ -159,6 +163,8 @@ cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream);
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
 	float* cb_union, cudaStream_t stream);
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream);
+cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream);
+size_t hier_bin2_smem_bytes(uint32_t ns);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
 // ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------

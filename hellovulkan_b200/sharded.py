@@ -319,8 +319,9 @@ class ShardedCuller:
         e.cull_finish_peer(frame)
         self._mark("cull_finish")
         e.peer_push_grid()
+        self._mark("push_grid")
         e.peer_wait_grid()
-        self._mark("gather_grid")
+        self._mark("wait_grid")
         totals = e.peer_totals[: self.world]
         bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
         return totals, bases
@@ -339,8 +340,9 @@ class ShardedCuller:
             e.cull_finish_peer(frame)
             self._mark("cull_finish")
             e.peer_push_grid()
+            self._mark("push_grid")
             e.peer_wait_grid()
-            self._mark("gather_grid")
+            self._mark("wait_grid")
         totals = e.peer_totals[: self.world]
         bases = torch.cumsum(totals, 0, dtype=torch.int32) - totals
         return totals, bases

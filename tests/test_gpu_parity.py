@@ -280,3 +280,23 @@ def test_modes_give_identical_bytes(hv, oracle):
     a = run_cull(hv, grid, ubo, lights, mode=MODES["brute"])
     b = run_cull(hv, grid, ubo, lights, mode=MODES["hier"])
     assert a[2] == b[2] and a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+
+
+@pytest.mark.parametrize("name,n,z", [("A", 70_000, None), ("B", 300_000, None), ("C", 200_000, None), ("C", 150_000, (40, 52))])
+def test_one_and_two_level_binning_give_identical_bytes(hv, oracle, monkeypatch, name, n, z):
+    """level 0 of the hierarchy as one kernel per (8 groups, tile) or as the two-level kernel per tile (super-groups first):
+    the same survivor slots, hence the same light cells and index buffer, byte for byte; both equal brute force"""
+    grid, screen = GRIDS[name]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=11)
+    kw = {} if z is None else {"z_begin": z[0], "z_end": z[1]}
+    out = {}
+    for lvl in ("0", "1"):
+        monkeypatch.setenv("HVCF_BIN2", lvl)
+        out[lvl] = run_cull(hv, grid, ubo, lights, mode=MODES["hier"], **kw)
+    monkeypatch.delenv("HVCF_BIN2")
+    ref = run_cull(hv, grid, ubo, lights, mode=MODES["brute"], **kw)
+    for lvl in ("0", "1"):
+        assert out[lvl][2] == ref[2]
+        assert out[lvl][0].tobytes() == ref[0].tobytes() and out[lvl][1].tobytes() == ref[1].tobytes(), f"HVCF_BIN2={lvl}"
+    assert out["1"][3]["prefilter_tests"] != out["0"][3]["prefilter_tests"]   # the two kernels really ran
