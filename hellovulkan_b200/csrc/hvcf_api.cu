@@ -81,7 +81,8 @@ struct hvcf_ctx
 	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
 	float* d_cb_union = nullptr;             // [ncb][8]
 	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
-	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel)
+	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel only)
+	int bin2_mode = -1;                      // HVCF_BIN2: -1 = per frame by size, 0 = never, 1 = always
 	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
 	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
 	uint16_t* d_bin_idx = nullptr;
@@ -367,7 +368,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		uint32_t shape[3] = {0, 0, 0};
 		if (const char* sh = getenv("HVCF_HIER_SHAPE"))
 			sscanf(sh, "%u,%u,%u", &shape[0], &shape[1], &shape[2]);
-		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, &c->hp);
+		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, c->max_lights, &c->hp);
 		const uint32_t max_tiles = c->padded_capacity / kTileLights;
 		c->h_max_segs = max_tiles < 256 ? max_tiles : 256;
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
@@ -376,9 +377,9 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->hier_v1 = env_int("HVCF_HIER_V1", 0) != 0;
 		c->ktimes = env_int("HVCF_KERNEL_TIMES", 0) != 0;
 		c->tiles_cap = max_tiles;
-		// two-level level-0 binning pays once a shard has many cluster groups (HVCF_BIN2=0/1 forces it off/on)
-		const int bin2 = env_int("HVCF_BIN2", -1);
-		if (!c->hier_v1 && (bin2 > 0 || (bin2 < 0 && c->hp.ncb >= kBin2MinGroups)))
+		// two-level level-0 binning (HVCF_BIN2=0/1 forces it off/on; otherwise chosen per frame, see hier_range)
+		c->bin2_mode = env_int("HVCF_BIN2", -1);
+		if (!c->hier_v1 && c->bin2_mode != 0)
 		{
 			c->bin_sg = (c->hp.ncb + 31) / 32 > 8 ? (c->hp.ncb + 31) / 32 : 8;
 			c->bin_ns = (c->hp.ncb + c->bin_sg - 1) / c->bin_sg;
@@ -807,7 +808,11 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			b.tile_begin = begin / kTileLights;
 			b.sb_union = ctx->d_sb_union;
 			b.sg = ctx->bin_sg;
-			b.ns = ctx->bin_ns;
+			// the two-level kernel pays once there are many (group, light) pairs: >= 48 groups, or >= 2^28 pairs (measured:
+			// grid A with 18 groups loses with it up to 1M lights; every z-slab of grid C at 16M lights wins, slab_sweep.py)
+			const bool two_level = ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups ||
+				static_cast<uint64_t>(ctx->hp.ncb) * n >= (1ull << 28));
+			b.ns = two_level ? ctx->bin_ns : 0u;
 			HVCF_CUDA(launch_hier_bin(b, (end_padded - begin) / kTileLights, s));
 			++ctx->open_launches;
 		}

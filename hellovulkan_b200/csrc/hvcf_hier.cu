@@ -503,7 +503,7 @@ static uint32_t pow2_ceil(uint32_t v)
 	return r;
 }
 
-void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], HierPlan* out)
+void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], uint32_t max_lights, HierPlan* out)
 {
 	HierPlan& h = *out;
 	h.bx = pow2_ceil(X) < 8 ? pow2_ceil(X) : 8;
@@ -518,6 +518,11 @@ void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const u
 	h.nbz = (Zs + h.bz - 1) / h.bz;
 	h.nblocks = h.nbx * h.nby * h.nbz;
 	h.K = h.nblocks >= 2048 ? 4 : (h.nblocks >= 512 ? 2 : 1);
+	// with millions of lights the per-(group, light) binning cost outweighs the finer filtering of small groups: bigger
+	// groups earlier (measured on z-slabs of grid C with 16M lights, scripts/slab_sweep.py: 360 and 504 blocks K=2 best,
+	// 1,584 and 1,800 blocks K=4 best)
+	if (max_lights >= (1u << 22))
+		h.K = h.nblocks >= 1024 ? 4 : (h.nblocks >= 128 ? 2 : 1);
 	if (k_override == 1 || k_override == 2 || k_override == 4)
 		h.K = static_cast<uint32_t>(k_override);
 	h.ncb = (h.nblocks + kHWarps * h.K - 1) / (kHWarps * h.K);

@@ -153,7 +153,7 @@ struct FinalizeParams
 	DeviceStats* stats;
 };
 
-void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], HierPlan* out);
+void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], uint32_t max_lights, HierPlan* out);
 void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out);
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs);

@@ -165,11 +165,13 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 		}
 	}
 	// ---- last CTA out raises the flag on every peer ----
+	// (one system-scope fence per CTA, after the CTA barrier: the barrier orders every thread's stores before thread 0's
+	// fence, which is cumulative.  A fence in every thread cost ~0.3 ms per push -- each one waits for the NVLink acks.)
 	__shared__ bool last;
-	__threadfence_system();
 	__syncthreads();
 	if (threadIdx.x == 0)
 	{
+		__threadfence_system();
 		PeerMailbox* mine = p.mail[p.rank];
 		const unsigned int done = atomicAdd(&mine->done, 1u);
 		last = done == gridDim.x - 1;
