@@ -1352,6 +1352,8 @@ int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
 	out->nominal_tests = static_cast<uint64_t>(ctx->cluster_count) * ctx->num_lights;
 	out->executed_tests = ds.executed_tests;
 	out->prefilter_tests = ds.prefilter_tests;
+	out->bin_tests = ds.bin_tests;
+	out->write_pass_tests = ds.write_tests;
 	out->total_indices = ds.total_indices;
 	out->overflow_clusters = ds.overflow_clusters;
 	out->kernel_launches = ctx->last_launches[frame];

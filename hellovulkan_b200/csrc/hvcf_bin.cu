@@ -149,6 +149,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 	{
 		p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
 		atomicAdd(&p.stats->prefilter_tests, static_cast<unsigned long long>(kTileLights));
+		atomicAdd(&p.stats->bin_tests, static_cast<unsigned long long>(kTileLights));
 	}
 }
 
@@ -461,8 +462,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	}
 	if (lane == 0 && (n_l1 | n_l2))
 	{
-		atomicAdd(&p.stats->prefilter_tests, n_l1);
-		atomicAdd(&p.stats->executed_tests, n_l2);
+		if (WRITE) // the write pass repeats part of the count pass's tests: counted apart, so that per-kernel rates stay honest
+			atomicAdd(&p.stats->write_tests, n_l1 + n_l2);
+		else
+		{
+			atomicAdd(&p.stats->prefilter_tests, n_l1);
+			atomicAdd(&p.stats->executed_tests, n_l2);
+		}
 	}
 }
 
@@ -601,7 +607,10 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		tests += ns;
 	}
 	if (lane == 0 && tests)
+	{
 		atomicAdd(&p.stats->prefilter_tests, tests);
+		atomicAdd(&p.stats->bin_tests, tests);
+	}
 }
 
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,

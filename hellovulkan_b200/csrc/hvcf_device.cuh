@@ -139,6 +139,8 @@ struct DeviceStats
 	unsigned long long prefilter_tests;
 	uint32_t total_indices;
 	uint32_t overflow_clusters;
+	unsigned long long bin_tests;    // level-0 union tests (hier_bin_kernel / hier_bin2_kernel), also inside prefilter_tests
+	unsigned long long write_tests;  // union + exact tests the write pass repeats (not in the two counters above)
 };
 
 } // namespace hvcf

@@ -365,8 +365,13 @@ __global__ void __launch_bounds__(kHWarps * 32) hier_kernel(const HierParams p)
 	}
 	if (lane == 0 && (n_l0 | n_l1 | n_l2))
 	{
-		atomicAdd(&p.stats->prefilter_tests, n_l0 + n_l1);
-		atomicAdd(&p.stats->executed_tests, n_l2);
+		if (WRITE)
+			atomicAdd(&p.stats->write_tests, n_l0 + n_l1 + n_l2);
+		else
+		{
+			atomicAdd(&p.stats->prefilter_tests, n_l0 + n_l1);
+			atomicAdd(&p.stats->executed_tests, n_l2);
+		}
 	}
 }
 

@@ -90,6 +90,8 @@ __global__ void __launch_bounds__(256) light_transform_kernel(const hvcf_cluster
 		stats->prefilter_tests = 0ull;
 		stats->total_indices = 0u;
 		stats->overflow_clusters = 0u;
+		stats->bin_tests = 0ull;
+		stats->write_tests = 0ull;
 	}
 	if (p >= num_pairs)
 		return;

@@ -68,7 +68,7 @@ class PushConstPBR(ctypes.Structure):
 class Stats(ctypes.Structure):
     _fields_ = [("nominal_tests", ctypes.c_uint64), ("executed_tests", ctypes.c_uint64), ("prefilter_tests", ctypes.c_uint64),
                 ("total_indices", ctypes.c_uint32), ("overflow_clusters", ctypes.c_uint32), ("kernel_launches", ctypes.c_uint32),
-                ("reserved", ctypes.c_uint32)]
+                ("reserved", ctypes.c_uint32), ("bin_tests", ctypes.c_uint64), ("write_pass_tests", ctypes.c_uint64)]
 
 
 EXPORTS = [

@@ -97,12 +97,14 @@ typedef struct hvcf_buffers
 typedef struct hvcf_stats
 {
 	uint64_t nominal_tests;   /* clusters x lights of the shard */
-	uint64_t executed_tests;  /* exact sphere-vs-AABB lane tests the kernels actually ran */
-	uint64_t prefilter_tests; /* union-box tests of the hierarchical mode (levels 0 and 1), else 0 */
+	uint64_t executed_tests;  /* exact sphere-vs-AABB lane tests (brute: the cull kernel; hierarchical: the count pass) */
+	uint64_t prefilter_tests; /* union-box tests of the hierarchical mode (level 0 = binning, level 1 = count pass), else 0 */
 	uint32_t total_indices;   /* sum of counts */
 	uint32_t overflow_clusters; /* clusters whose count hit max_lights_per_cluster */
 	uint32_t kernel_launches; /* kernels launched by that hvcf_cull call */
 	uint32_t reserved;
+	uint64_t bin_tests;        /* the level-0 (binning kernel) part of prefilter_tests */
+	uint64_t write_pass_tests; /* union + exact tests the write pass repeats; in neither counter above */
 } hvcf_stats;
 
 HVCF_API const char* hvcf_last_error_string(void);

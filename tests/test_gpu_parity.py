@@ -300,3 +300,17 @@ def test_one_and_two_level_binning_give_identical_bytes(hv, oracle, monkeypatch,
         assert out[lvl][2] == ref[2]
         assert out[lvl][0].tobytes() == ref[0].tobytes() and out[lvl][1].tobytes() == ref[1].tobytes(), f"HVCF_BIN2={lvl}"
     assert out["1"][3]["prefilter_tests"] != out["0"][3]["prefilter_tests"]   # the two kernels really ran
+
+
+def test_stats_are_split_per_kernel(hv, oracle):
+    """hvcf_stats: the binning kernel's tests are a part of prefilter_tests, the write pass's repeats are counted apart, and the
+    count pass's exact tests equal the oracle's executed-test count rounded up to what a tile-granular early exit runs"""
+    grid, screen = GRIDS["B"]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(100_000, seed=3)
+    _, _, total, st = run_cull(hv, grid, ubo, lights, mode=MODES["hier"])
+    assert 0 < st["bin_tests"] < st["prefilter_tests"]
+    assert st["write_pass_tests"] > 0 and st["executed_tests"] > 0
+    assert st["executed_tests"] + st["prefilter_tests"] < st["nominal_tests"]
+    _, _, total_b, sb = run_cull(hv, grid, ubo, lights, mode=MODES["brute"])
+    assert total_b == total and sb["bin_tests"] == 0 and sb["write_pass_tests"] == 0 and sb["prefilter_tests"] == 0
