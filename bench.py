@@ -390,7 +390,64 @@ def run_ours(args):
     e2e_ms = float(t.item()) / Ke * 1e3
     e2e = {"value": world * nominal / (e2e_ms * 1e-3), "unit": "tests/s", "ms_per_step": e2e_ms, "steps": Ke,
            "h2d_bytes_per_step": 48 * n + hvcf.UBO_BYTES, "d2h_bytes_per_step": 4 + 8 * C + 4 * tot,
-           "timer": "host perf_counter around the loop, synchronised both sides (the downloads block)"}
+           "timer": "host perf_counter around the loop, synchronised both sides (the downloads block)",
+           "mode": "one frame at a time: upload, cull, three blocking downloads"}
+
+    # ---- e2e with two frames in flight (AppConfig::FrameCount = 2 in the reference, Configs.h:14): two contexts, each
+    # with its own stream and its own buffers; frame i+1 is issued (H2D + kernels, asynchronous) before the blocking
+    # downloads of frame i, so uploads, kernels and downloads of neighbouring frames overlap on PCIe's two directions.
+    # Same bytes per step, same public calls; reported beside the one-at-a-time figure, and used as the headline e2e.
+    try:
+        ctxs2 = [ctx, hvcf.Context(grid=grid, max_lights=n, device=local, mode=mode)]
+        streams2 = [torch.cuda.Stream(), torch.cuda.Stream()]
+        outs2 = [(cells_host, idx_host), (hvcf.PinnedBuffer(8 * C), hvcf.PinnedBuffer(4 * C * 150))]
+        totals2 = [np.zeros(1, np.uint32), np.zeros(1, np.uint32)]
+        torch.cuda.synchronize()
+
+        def issue(i):
+            c, st = ctxs2[i & 1], streams2[i & 1].cuda_stream
+            c.set_lights_ptr(pinned.ptr.value, n, False, st)
+            c.set_ubo_ptr(0, pinned_ubo.ptr.value + (i & 1) * hvcf.UBO_BYTES, st)
+            c.cull(0, st)
+
+        def collect(i):
+            c, st = ctxs2[i & 1], streams2[i & 1].cuda_stream
+            th, (ch, ih) = totals2[i & 1], outs2[i & 1]
+            hvcf._check(lib.hvcf_download_total(c.handle, 0, th.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), st))
+            hvcf._check(lib.hvcf_download_light_cells(c.handle, ch.ptr, 8 * C, st))
+            hvcf._check(lib.hvcf_download_light_indices(c.handle, ih.ptr, 4 * int(th[0]), st))
+            return int(th[0])
+
+        def run_pipelined(k):
+            issue(0)
+            last = 0
+            for i in range(k):
+                if i + 1 < k:
+                    issue(i + 1)
+                last = collect(i)
+            return last
+
+        run_pipelined(W + 1)
+        barrier()
+        t0 = time.perf_counter()
+        tot2 = run_pipelined(Ke)
+        torch.cuda.synchronize()
+        p_s = time.perf_counter() - t0
+        t = torch.tensor([p_s], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        p_ms = float(t.item()) / Ke * 1e3
+        ctxs2[1].close()
+        e2e["one_frame_at_a_time"] = {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"]}
+        if tot2 == tot and p_ms < e2e_ms:
+            e2e.update({"value": world * nominal / (p_ms * 1e-3), "ms_per_step": p_ms,
+                        "mode": "two frames in flight (two contexts on their own streams, as AppConfig::FrameCount = 2): frame i+1 is "
+                                "issued before the blocking downloads of frame i; every step still uploads all lights + UBO and "
+                                "downloads total + cells + indices"})
+        else:
+            e2e["two_frames_in_flight"] = {"ms_per_step": p_ms, "total_indices": tot2}
+    except Exception as ex:   # the one-at-a-time figure stands
+        e2e["two_frames_in_flight"] = {"error": f"{type(ex).__name__}: {ex}"}
 
     # ---- roofline of the dominant kernel (cull_kernel), live ------------------------------------------
     k_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
