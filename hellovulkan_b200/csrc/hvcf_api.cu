@@ -75,6 +75,7 @@ struct hvcf_ctx
 	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
+	uint32_t* d_hseg_lists = nullptr;        // [h_max_segs][cluster_count][cap] hits of the count pass, or NULL: write pass instead
 	uint32_t* d_hscratch = nullptr;          // cum[cluster_count][kHMaxChunks]
 	uint32_t* d_hoffsets = nullptr;
 	uint32_t* d_hlane_cluster = nullptr;
@@ -200,6 +201,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_stats);
 	cudaFree(c->d_hseg_counts);
 	cudaFree(c->d_hseg_prefix);
+	cudaFree(c->d_hseg_lists);
 	cudaFree(c->d_hscratch);
 	cudaFree(c->d_hoffsets);
 	cudaFree(c->d_hlane_cluster);
@@ -276,6 +278,7 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.bin_rec = ctx->d_bin_rec;
 	p.bin_idx = ctx->d_bin_idx;
 	p.tiles_cap = ctx->tiles_cap;
+	p.seg_lists = ctx->hier_v1 ? nullptr : ctx->d_hseg_lists;
 	return p;
 }
 
@@ -423,6 +426,26 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
 		}
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
+		// hit lists of the count pass + hier_copy_kernel instead of the write pass: OFF by default (HVCF_SEG_LISTS=1 enables it
+		// within HVCF_SEG_LISTS_MAX_GB).  Measured on B200 and rejected: segments run concurrently, so the count pass sees
+		// only a lower bound of the earlier hits and stores many hits that the cap later discards, each a 4 B store into
+		// its own 32 B sector -- count pass 0.102 -> 0.207 ms at B1M, frame 0.240 -> 0.385 ms; A65k 0.058 -> 0.104 ms; only
+		// grid C x 16M broke even (count 1.36 -> 2.04 ms, write 0.93 -> copy 0.24 ms).  Byte-identical either way
+		// (tests/test_gpu_parity.py::test_copy_pass_and_write_pass_give_identical_bytes).
+		if (!c->hier_v1 && env_int("HVCF_SEG_LISTS", 0) != 0)
+		{
+			const size_t bytes = sizeof(uint32_t) * Cs * c->h_max_segs * c->cap;
+			size_t free_b = 0, total_b = 0;
+			const size_t budget = static_cast<size_t>(env_int("HVCF_SEG_LISTS_MAX_GB", 40)) << 30;
+			if (bytes <= budget && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && bytes + (static_cast<size_t>(8) << 30) <= free_b)
+			{
+				if (cudaMalloc(reinterpret_cast<void**>(&c->d_hseg_lists), bytes ? bytes : 16) != cudaSuccess)
+				{
+					c->d_hseg_lists = nullptr;
+					(void)cudaGetLastError();
+				}
+			}
+		}
 		if (env_int("HVCF_HIER_TRACE", 0))
 			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 16 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
 	}
@@ -860,6 +883,7 @@ static int hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
 	f.offsets = ctx->d_hoffsets;
 	f.shard_total = ctx->d_shard_total;
 	f.stats = stats;
+	f.skip_prefix = p.seg_lists ? 1u : 0u;
 	HVCF_CUDA(launch_hier_finalize(f, s));
 	HVCF_CUDA(hier_kmark(ctx, frame, 4, s));
 	ctx->last_launches[frame] = launches + 2;
@@ -995,7 +1019,27 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	{
 		HierParams hp = hier_params(ctx, frame);
 		hp.index_base = d_index_base;
-		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+		if (hp.seg_lists)
+		{
+			// the count pass kept its hits: concatenate the (segment, cluster) lists instead of walking the hierarchy again
+			CopyParams cp{};
+			cp.seg_counts = ctx->d_hseg_counts;
+			cp.seg_lists = ctx->d_hseg_lists;
+			cp.num_segs = ctx->h_num_segs;
+			cp.cluster_count = ctx->cluster_count;
+			cp.cluster_begin = ctx->cluster_begin;
+			cp.cap = ctx->cap;
+			cp.counts = ctx->d_counts;
+			cp.offsets = ctx->d_hoffsets;
+			cp.index_base = d_index_base;
+			cp.shard_total = ctx->d_shard_total;
+			cp.cells = ctx->d_cells;
+			cp.indices = ctx->d_indices;
+			cp.frame_total = &ctx->d_global_index[frame];
+			HVCF_CUDA(launch_hier_copy(cp, static_cast<cudaStream_t>(stream)));
+		}
+		else
+			HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
 		if (ctx->ktimes && ctx->kev[frame][4])
 		{
 			if (!ctx->kev[frame][5])

@@ -158,7 +158,10 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // grid = segments x (ncb * 8 / kMainWarps) CTAs of kMainWarps independent warp programs; warp program
 // `unit` owns blocks unit * K .. unit * K + K - 1 (lane = cluster) and belongs to group unit / 8.
 // ======================================================================================================
-template <int K, bool WRITE>
+// LISTS (count pass only): every counted hit below the lane's limit is also stored, in light order, in the
+// (segment, cluster) list seg_lists[seg][cluster][cap]; hier_copy_kernel then concatenates the lists into the index buffer
+// and the write pass (the second walk of the hierarchy) is not needed.
+template <int K, bool WRITE, bool LISTS>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
 	__shared__ __align__(16) float4 s_rec[kMainWarps][64];
@@ -183,6 +186,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	uint32_t cnt[K];     // pass 1: hits counted in this segment; pass 2: entries written
 	uint32_t limit[K];   // pass 1: hits still missing before the cap; pass 2: entries this lane owns
 	uint32_t wbase[K];   // pass 2: first output slot
+	size_t lbase[K];     // LISTS: first word of this lane's (segment, cluster) list
 	bool active[K];
 	const uint32_t chunk = hier_chunk_of(seg);
 	const uint32_t index_base = (WRITE && p.index_base) ? *p.index_base : 0u;
@@ -194,6 +198,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		cnt[k] = 0;
 		limit[k] = 0;
 		wbase[k] = 0;
+		lbase[k] = valid ? (static_cast<size_t>(seg) * p.cluster_count + cidx[k]) * p.cap : 0;
 		active[k] = false;
 		lo[k][0] = lo[k][1] = lo[k][2] = kInf;
 		hi[k][0] = hi[k][1] = hi[k][2] = -kInf;
@@ -391,7 +396,11 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 									}
 								}
 								else
+								{
+									if (LISTS && hit && cnt[k] < limit[k])
+										p.seg_lists[lbase[k] + cnt[k]] = tile_base + my_idx[j[q]];
 									cnt[k] += hit ? 1u : 0u;
+								}
 							}
 						}
 						while (m)
@@ -409,7 +418,11 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 								}
 							}
 							else
+							{
+								if (LISTS && hit && cnt[k] < limit[k])
+									p.seg_lists[lbase[k] + cnt[k]] = tile_base + my_idx[j];
 								cnt[k] += hit ? 1u : 0u;
+							}
 						}
 					}
 					// early exit per lane: a cluster that holds its quota leaves the block's union box, so the remaining
@@ -670,7 +683,7 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
-template <int K, bool WRITE>
+template <int K, bool WRITE, bool LISTS>
 static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 {
 	cudaLaunchConfig_t cfg{};
@@ -680,21 +693,25 @@ static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE>, p);
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS>, p);
 }
 
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
 {
 	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
 		return cudaSuccess;
-	switch (K * 2 + (write ? 1 : 0))
+	const bool lists = !write && p.seg_lists != nullptr;
+	switch (K * 4 + (write ? 1 : 0) + (lists ? 2 : 0))
 	{
-	case 2: return launch_hier2_t<1, false>(p, stream);
-	case 3: return launch_hier2_t<1, true>(p, stream);
-	case 4: return launch_hier2_t<2, false>(p, stream);
-	case 5: return launch_hier2_t<2, true>(p, stream);
-	case 8: return launch_hier2_t<4, false>(p, stream);
-	case 9: return launch_hier2_t<4, true>(p, stream);
+	case 4: return launch_hier2_t<1, false, false>(p, stream);
+	case 5: return launch_hier2_t<1, true, false>(p, stream);
+	case 6: return launch_hier2_t<1, false, true>(p, stream);
+	case 8: return launch_hier2_t<2, false, false>(p, stream);
+	case 9: return launch_hier2_t<2, true, false>(p, stream);
+	case 10: return launch_hier2_t<2, false, true>(p, stream);
+	case 16: return launch_hier2_t<4, false, false>(p, stream);
+	case 17: return launch_hier2_t<4, true, false>(p, stream);
+	case 18: return launch_hier2_t<4, false, true>(p, stream);
 	default: return cudaErrorInvalidValue;
 	}
 }

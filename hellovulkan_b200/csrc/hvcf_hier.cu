@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 		run += w < warp ? v : 0u;
 		total += v;
 	}
-	if (valid)
+	if (valid && !p.skip_prefix)
 	{
 		uint32_t* pre = p.seg_prefix + c;
 		uint32_t s = s0;
@@ -623,6 +623,91 @@ cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t str
 	case 9: return launch_hier_t<4, true>(p, stream);
 	default: return cudaErrorInvalidValue;
 	}
+}
+
+// ======================================================================================================
+// copy pass (instead of the write pass when the count pass kept its hits in seg_lists): CTA = 32 clusters (lane) x 8
+// segment groups (warp), the shape of hier_finalize_kernel.  Sweep 1 sums this warp's segments, the warps exchange their
+// sums, sweep 2 walks the segments again with the running prefix and copies each (segment, cluster) list -- its first
+// min(count, cap - prefix) entries -- to indices[offset + prefix ...].  A count may exceed what the list holds (hits are
+// counted past the lane's limit inside a batch) but never the part that is needed: limit = cap - (a lower bound of the
+// earlier hits) >= cap - prefix.  Warp 0 also writes the light cells (LightCulling.comp:86-87).
+// ======================================================================================================
+__global__ void __launch_bounds__(kFinWarps * 32) hier_copy_kernel(const CopyParams p)
+{
+	__shared__ uint32_t s_part[kFinWarps][32];
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t c = blockIdx.x * 32 + lane;
+	const bool valid = c < p.cluster_count;
+	grid_dep_launch();
+	grid_dep_wait();
+	const uint32_t base = p.index_base ? *p.index_base : 0u;
+	const uint32_t group = (p.num_segs + kFinWarps - 1) / kFinWarps;
+	const uint32_t s0 = min(warp * group, p.num_segs), s1 = min(s0 + group, p.num_segs);
+	const uint32_t* col = p.seg_counts + c;
+	uint32_t part = 0;
+	if (valid)
+	{
+		uint32_t s = s0;
+		for (; s + 4 <= s1; s += 4)
+		{
+			const uint32_t a = col[static_cast<size_t>(s) * p.cluster_count], b = col[static_cast<size_t>(s + 1) * p.cluster_count];
+			const uint32_t d = col[static_cast<size_t>(s + 2) * p.cluster_count], e = col[static_cast<size_t>(s + 3) * p.cluster_count];
+			part += (a + b) + (d + e);
+		}
+		for (; s < s1; ++s)
+			part += col[static_cast<size_t>(s) * p.cluster_count];
+	}
+	s_part[warp][lane] = part;
+	__syncthreads();
+	uint32_t run = 0;
+#pragma unroll
+	for (uint32_t w = 0; w < kFinWarps; ++w)
+		run += w < warp ? s_part[w][lane] : 0u;
+	if (blockIdx.x == 0 && threadIdx.x == 0 && p.frame_total)
+		*p.frame_total = base + *p.shard_total; // globalIndex after the frame (LightCulling.comp:21,79)
+	if (!valid)
+		return;
+	const uint32_t off = p.offsets[c] + base;
+	if (warp == 0)
+		*reinterpret_cast<uint2*>(p.cells + p.cluster_begin + c) = make_uint2(off, p.counts[c]);
+	if (part == 0 || run >= p.cap)
+		return;
+	uint32_t* const dst0 = p.indices + off;
+	for (uint32_t s = s0; s < s1 && run < p.cap; ++s)
+	{
+		const uint32_t a = col[static_cast<size_t>(s) * p.cluster_count];
+		if (a == 0)
+			continue;
+		const uint32_t n = min(a, p.cap - run);
+		const uint32_t* src = p.seg_lists + (static_cast<size_t>(s) * p.cluster_count + c) * p.cap;
+		uint32_t* dst = dst0 + run;
+		uint32_t i = 0;
+		for (; i + 4 <= n; i += 4)
+		{
+			const uint32_t v0 = __ldcs(src + i), v1 = __ldcs(src + i + 1), v2 = __ldcs(src + i + 2), v3 = __ldcs(src + i + 3);
+			dst[i] = v0, dst[i + 1] = v1, dst[i + 2] = v2, dst[i + 3] = v3;
+		}
+		for (; i < n; ++i)
+			dst[i] = __ldcs(src + i);
+		run += a;
+	}
+}
+
+cudaError_t launch_hier_copy(const CopyParams& p, cudaStream_t stream)
+{
+	if (p.cluster_count == 0)
+		return cudaSuccess;
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3((p.cluster_count + 31) / 32, 1, 1);
+	cfg.blockDim = dim3(kFinWarps * 32, 1, 1);
+	cfg.stream = stream;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_copy_kernel, p);
 }
 
 cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream)

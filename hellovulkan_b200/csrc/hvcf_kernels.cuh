@@ -114,6 +114,7 @@ struct HierParams
 	const float4* bin_rec;         // [ncb][tiles_cap][kBinCap] {x, y, z, r*r} in light order
 	const uint16_t* bin_idx;       // [ncb][tiles_cap][kBinCap] light index inside the tile
 	uint32_t tiles_cap;
+	uint32_t* seg_lists;           // [num_segs][cluster_count][cap] hits of the count pass in light order, or NULL (write pass instead)
 };
 
 #ifndef HVCF_BIN_CAP
@@ -151,7 +152,24 @@ struct FinalizeParams
 	uint32_t* offsets;
 	uint32_t* shard_total;
 	DeviceStats* stats;
+	uint32_t skip_prefix;           // 1 = seg_prefix is not needed (hier_copy_kernel recomputes the prefixes)
 };
+
+// concatenates the (segment, cluster) hit lists of the count pass into the light-index buffer and writes the light cells
+struct CopyParams
+{
+	const uint32_t* seg_counts;    // [num_segs][cluster_count]
+	const uint32_t* seg_lists;     // [num_segs][cluster_count][cap]
+	uint32_t num_segs, cluster_count, cluster_begin, cap;
+	const uint32_t* counts;        // [cluster_count] capped
+	const uint32_t* offsets;       // [cluster_count] shard-local exclusive offsets
+	const uint32_t* index_base;    // device scalar or NULL
+	const uint32_t* shard_total;
+	hvcf_light_cell* cells;        // whole grid
+	uint32_t* indices;
+	uint32_t* frame_total;
+};
+cudaError_t launch_hier_copy(const CopyParams& p, cudaStream_t stream);
 
 void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], uint32_t max_lights, HierPlan* out);
 void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out);

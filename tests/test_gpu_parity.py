@@ -314,3 +314,25 @@ def test_stats_are_split_per_kernel(hv, oracle):
     assert st["executed_tests"] + st["prefilter_tests"] < st["nominal_tests"]
     _, _, total_b, sb = run_cull(hv, grid, ubo, lights, mode=MODES["brute"])
     assert total_b == total and sb["bin_tests"] == 0 and sb["write_pass_tests"] == 0 and sb["prefilter_tests"] == 0
+
+
+@pytest.mark.parametrize("name,n,cap,z", [("A", 70_000, 150, None), ("A", 3_000, 4, None), ("B", 300_000, 150, None), ("C", 150_000, 150, (40, 52)),
+                                         ("B", 0, 150, None), ("A", 65_536, 1, None)])
+def test_copy_pass_and_write_pass_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap, z):
+    """output stage of the hierarchical mode: a second walk of the hierarchy (write pass, the default) or hit lists kept by the
+    count pass + hier_copy_kernel (HVCF_SEG_LISTS=1; measured slower, kept as an option): same bytes, equal to brute force"""
+    grid, screen = GRIDS[name]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=17)
+    kw = {} if z is None else {"z_begin": z[0], "z_end": z[1]}
+    out = {}
+    for lists in ("0", "1"):
+        monkeypatch.setenv("HVCF_SEG_LISTS", lists)
+        out[lists] = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"], **kw)
+    monkeypatch.delenv("HVCF_SEG_LISTS")
+    ref = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["brute"], **kw)
+    for lists in ("0", "1"):
+        assert out[lists][2] == ref[2]
+        assert out[lists][0].tobytes() == ref[0].tobytes() and out[lists][1].tobytes() == ref[1].tobytes(), f"HVCF_SEG_LISTS={lists}"
+    assert out["0"][3]["write_pass_tests"] > 0 or n == 0
+    assert out["1"][3]["write_pass_tests"] == 0
