@@ -373,7 +373,13 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 			sscanf(sh, "%u,%u,%u", &shape[0], &shape[1], &shape[2]);
 		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, c->max_lights, &c->hp);
 		const uint32_t max_tiles = c->padded_capacity / kTileLights;
-		c->h_max_segs = max_tiles < 256 ? max_tiles : 256;
+		// most light segments a frame may be cut into (hier_plan_lights picks the actual number).  Measured on B200
+		// (scripts/sweep_hier.py): grid A x 1M lights 0.181 ms at 256 -> 0.131 ms at 512 (half the executed tests: shorter
+		// segments publish their counts sooner); grid B x 1M keeps 256 by the plan's own target, forcing 512 there costs
+		// 0.240 -> 0.339 ms (twice the warp-program prologues)
+		uint32_t seg_limit = static_cast<uint32_t>(env_int("HVCF_HIER_MAX_SEGS", 512));
+		seg_limit = seg_limit < 1 ? 1 : (seg_limit > 2048 ? 2048 : seg_limit);
+		c->h_max_segs = max_tiles < seg_limit ? max_tiles : seg_limit;
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
 		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));

@@ -581,7 +581,7 @@ uint32_t hier_num_chunks(uint32_t num_segs)
 		s >>= 1;
 		++c;
 	}
-	return c + 2; // chunk_of(num_segs - 1) + 1
+	return c + 2 < kHMaxChunks ? c + 2 : kHMaxChunks; // chunk_of(num_segs - 1) + 1
 }
 
 template <int K, bool WRITE>

@@ -85,5 +85,6 @@ __device__ __forceinline__ uint32_t hier_prior_hits(const uint32_t* cum, uint32_
 }
 
 // segment -> chunk: chunk 0 = segments [0,4), chunk c >= 1 = segments [2^(c+1), 2^(c+2))
-__device__ __forceinline__ uint32_t hier_chunk_of(uint32_t seg) { return seg < 4 ? 0u : (30u - __clz(seg)); }
+// (the last chunk, kHMaxChunks - 1, takes every segment from 256 on: any monotone map keeps the lower bounds valid)
+__device__ __forceinline__ uint32_t hier_chunk_of(uint32_t seg) { return seg < 4 ? 0u : min(30u - __clz(seg), kHMaxChunks - 1u); }
 } // namespace hvcf
