@@ -75,6 +75,7 @@ struct hvcf_ctx
 	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
+	uint32_t* d_hunit_any = nullptr;         // [h_max_segs][ncb * 8]
 	uint32_t* d_hseg_lists = nullptr;        // [h_max_segs][cluster_count][cap] hits of the count pass, or NULL: write pass instead
 	uint32_t* d_hscratch = nullptr;          // cum[cluster_count][kHMaxChunks]
 	uint32_t* d_hoffsets = nullptr;
@@ -202,6 +203,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_hseg_counts);
 	cudaFree(c->d_hseg_prefix);
 	cudaFree(c->d_hseg_lists);
+	cudaFree(c->d_hunit_any);
 	cudaFree(c->d_hscratch);
 	cudaFree(c->d_hoffsets);
 	cudaFree(c->d_hlane_cluster);
@@ -279,6 +281,7 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.bin_idx = ctx->d_bin_idx;
 	p.tiles_cap = ctx->tiles_cap;
 	p.seg_lists = ctx->hier_v1 ? nullptr : ctx->d_hseg_lists;
+	p.unit_any = ctx->d_hunit_any;
 	return p;
 }
 
@@ -421,6 +424,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hseg_prefix, sizeof(uint32_t) * Cs * c->h_max_segs);
 		HVCF_ALLOC(c->d_hscratch, sizeof(uint32_t) * Cs * kHMaxChunks);
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
+		HVCF_ALLOC(c->d_hunit_any, sizeof(uint32_t) * static_cast<size_t>(c->h_max_segs) * c->hp.ncb * 8);
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
 		if (!c->hier_v1)
 		{

@@ -178,6 +178,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	unsigned long long t_start = 0;
 	if (p.trace && threadIdx.x == 0)
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+	// the count pass left one word per (segment, warp program): nothing counted there means nothing to write.  One load
+	// instead of the whole prologue -- 63 % of the write pass's warp programs at B1M ran ~190 instructions of prologue only
+	// to find that they own no output (profiles/r01q).  Segment 0 stays: it writes the light cells.
+	// (the slot index is recomputed where it is needed: keeping it live cost the count pass two registers = one CTA per SM)
+#define HVCF_ANY_SLOT (static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit)
+	if (WRITE && seg != 0 && !p.trace && __ldg(&p.unit_any[HVCF_ANY_SLOT]) == 0u)
+		return;
 
 	// ---- this lane's K clusters (one per block) -------------------------------------------------------
 	const float kInf = __int_as_float(0x7f800000);
@@ -258,6 +265,8 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				for (int k = 0; k < K; ++k)
 					if (cidx[k] != kSkip)
 						p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = 0u;
+				if (lane == 0)
+					p.unit_any[HVCF_ANY_SLOT] = 0u;
 			}
 			return;
 		}
@@ -449,6 +458,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	}
 	if (!WRITE)
 	{
+		bool counted = false;
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+			counted = counted || cnt[k] != 0;
+		const bool any_counted = __any_sync(0xffffffffu, counted);
+		if (lane == 0)
+			p.unit_any[HVCF_ANY_SLOT] = any_counted ? 1u : 0u;
 #pragma unroll
 		for (int k = 0; k < K; ++k)
 			if (cidx[k] != kSkip)

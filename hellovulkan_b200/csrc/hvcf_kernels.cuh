@@ -115,6 +115,7 @@ struct HierParams
 	const uint16_t* bin_idx;       // [ncb][tiles_cap][kBinCap] light index inside the tile
 	uint32_t tiles_cap;
 	uint32_t* seg_lists;           // [num_segs][cluster_count][cap] hits of the count pass in light order, or NULL (write pass instead)
+	uint32_t* unit_any;            // [num_segs][ncb * 8] count pass: did this warp program count any hit?  The write pass leaves at once if not
 };
 
 #ifndef HVCF_BIN_CAP
