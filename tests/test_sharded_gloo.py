@@ -61,7 +61,10 @@ class OracleEngine:
         pass
 
 
-def _worker(rank, world, port, out_dir):
+UNEQUAL = {2: [(0, 17), (17, 24)], 3: [(0, 13), (13, 14), (14, 24)]}   # what balance_slabs produces: unequal slabs
+
+
+def _worker(rank, world, port, out_dir, unequal=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -69,9 +72,10 @@ def _worker(rank, world, port, out_dir):
         from cpu_checkers import Oracle
         from hellovulkan_b200.sharded import ShardedCuller, z_slabs
         O = Oracle()
-        slabs = z_slabs(GRID[2], world)
+        slabs = UNEQUAL[world] if unequal else z_slabs(GRID[2], world)
         eng = OracleEngine(O, GRID, N_LIGHTS, slabs[rank])
-        sc = ShardedCuller(eng, GRID, world=world, rank=rank)
+        sc = ShardedCuller(eng, GRID, world=world, rank=rank, slabs=slabs)
+        assert sc.equal == (not unequal)
         if rank == 0:  # only rank 0 holds the scene; the others receive it by broadcast
             eng.lights[: 48 * N_LIGHTS] = torch.from_numpy(O.init_lights(N_LIGHTS).view(np.uint8).reshape(-1).copy())
         eng.set_ubo(0, O.camera_ubo(GRID, SCREEN))
@@ -89,9 +93,9 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_sharded_frame_matches_single_process(world, oracle, tmp_path):
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+@pytest.mark.parametrize("world,unequal", [(2, False), (3, False), (2, True), (3, True)])
+def test_sharded_frame_matches_single_process(world, unequal, oracle, tmp_path):
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), unequal), nprocs=world, join=True)
     ubo = oracle.camera_ubo(GRID, SCREEN)
     lights = oracle.init_lights(N_LIGHTS)
     oc, oi, ototal, _ = oracle.cull(ubo, oracle.generate_aabbs(ubo), lights)
