@@ -185,6 +185,31 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 #define HVCF_ANY_SLOT (static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit)
 	if (WRITE && seg != 0 && !p.trace && __ldg(&p.unit_any[HVCF_ANY_SLOT]) == 0u)
 		return;
+	// count pass: a group whose level-0 slots are empty for every tile of this segment has nothing to test -- zero counts,
+	// no boxes, no early-exit counters, no union reductions (HVCF_EMPTY_SKIP=0 at build time switches the check off)
+#ifndef HVCF_EMPTY_SKIP
+#define HVCF_EMPTY_SKIP 1
+#endif
+	if (HVCF_EMPTY_SKIP && !WRITE && !p.trace)
+	{
+		const size_t d0 = static_cast<size_t>(cb) * p.tiles_cap + t_begin;
+		uint32_t some = 0;
+		for (uint32_t t = lane; t < ntiles; t += 32)
+			some |= __ldg(&p.bin_count[d0 + t]);
+		if (!__any_sync(0xffffffffu, some != 0))
+		{
+#pragma unroll
+			for (int k = 0; k < K; ++k)
+			{
+				const uint32_t c = __ldg(&p.lane_cluster[(static_cast<size_t>(unit * K + k) << 5) + lane]);
+				if (c != kSkip)
+					p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + c] = 0u;
+			}
+			if (lane == 0)
+				p.unit_any[HVCF_ANY_SLOT] = 0u;
+			return;
+		}
+	}
 
 	// ---- this lane's K clusters (one per block) -------------------------------------------------------
 	const float kInf = __int_as_float(0x7f800000);
