@@ -413,9 +413,8 @@ def run_ours(args):
         def collect(i):
             c, st = ctxs2[i & 1], streams2[i & 1].cuda_stream
             th, (ch, ih) = totals2[i & 1], outs2[i & 1]
-            hvcf._check(lib.hvcf_download_total(c.handle, 0, th.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), st))
-            hvcf._check(lib.hvcf_download_light_cells(c.handle, ch.ptr, 8 * C, st))
-            hvcf._check(lib.hvcf_download_light_indices(c.handle, ih.ptr, 4 * int(th[0]), st))
+            hvcf._check(lib.hvcf_download_grid(c.handle, 0, ch.ptr, 8 * C, ih.ptr, 4 * C * 150,
+                                               th.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), st))
             return int(th[0])
 
         def run_pipelined(k):

@@ -112,6 +112,7 @@ struct hvcf_ctx
 	// pinned staging
 	hvcf_cluster_forward_ubo* h_ubo = nullptr; // [frame]
 	float* h_zplanes = nullptr;                // [frame][Z+1]
+	uint32_t* h_total = nullptr;               // [8] pinned: hvcf_download_grid
 	hvcf_light_data* h_one_light = nullptr;    // hvcf_update_light staging ring
 	uint32_t one_light_cursor = 0;
 	cudaEvent_t one_light_events[16]{};
@@ -238,6 +239,7 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFreeHost(c->h_ubo);
 	cudaFreeHost(c->h_zplanes);
 	cudaFreeHost(c->h_one_light);
+	cudaFreeHost(c->h_total);
 	for (auto& e : c->one_light_events)
 		if (e)
 			cudaEventDestroy(e);
@@ -1390,6 +1392,36 @@ int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_total: frame %u >= frame_count %u", frame, ctx->frame_count);
 	return download(ctx, out_total, ctx ? &ctx->d_global_index[frame] : nullptr, sizeof(uint32_t), sizeof(uint32_t), stream,
 		"hvcf_download_total");
+}
+
+int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t cells_bytes, void* indices_dst,
+	size_t indices_capacity_bytes, uint32_t* out_total, void* stream)
+{
+	if (!ctx || !out_total || (cells_bytes && !cells_dst))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: null argument");
+	if (frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: frame %u >= frame_count %u", frame, ctx->frame_count);
+	if (cells_bytes > sizeof(hvcf_light_cell) * static_cast<size_t>(ctx->cluster_total))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: %zu bytes of cells > buffer size", cells_bytes);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (!ctx->h_total)
+		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 8));
+	HVCF_CUDA(cudaMemcpyAsync(&ctx->h_total[frame], &ctx->d_global_index[frame], sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	if (cells_bytes)
+		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells, cells_bytes, cudaMemcpyDeviceToHost, s));
+	HVCF_CUDA(cudaStreamSynchronize(s));
+	const uint32_t total = ctx->h_total[frame];
+	*out_total = total;
+	const size_t need = sizeof(uint32_t) * static_cast<size_t>(total);
+	if (need > indices_capacity_bytes || (need && !indices_dst))
+		return fail(HVCF_ERR_CAPACITY, "hvcf_download_grid: %u indices do not fit in %zu bytes", total, indices_capacity_bytes);
+	if (need)
+	{
+		HVCF_CUDA(cudaMemcpyAsync(indices_dst, ctx->d_indices, need, cudaMemcpyDeviceToHost, s));
+		HVCF_CUDA(cudaStreamSynchronize(s));
+	}
+	return HVCF_OK;
 }
 
 int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)

@@ -75,7 +75,7 @@ EXPORTS = [
     "hvcf_last_error_string", "hvcf_version", "hvcf_create", "hvcf_destroy", "hvcf_set_lights", "hvcf_update_light",
     "hvcf_set_ubo", "hvcf_mark_aabb_dirty", "hvcf_is_aabb_dirty", "hvcf_generate_aabbs", "hvcf_cull", "hvcf_cull_begin",
     "hvcf_cull_finish", "hvcf_shard_total_ptr", "hvcf_get_device_buffers", "hvcf_download_aabbs",
-    "hvcf_download_light_cells", "hvcf_download_light_indices", "hvcf_download_total", "hvcf_get_stats",
+    "hvcf_download_light_cells", "hvcf_download_light_indices", "hvcf_download_total", "hvcf_download_grid", "hvcf_get_stats",
     "hvcf_host_alloc", "hvcf_host_free", "hvcf_bind_lights", "hvcf_device_alloc", "hvcf_device_free",
     "hvcf_device_upload", "hvcf_device_download", "hvcf_stream_synchronize", "hvcf_host_camera_ubo",
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
@@ -121,6 +121,7 @@ def load():
     for name in ("hvcf_download_aabbs", "hvcf_download_light_cells", "hvcf_download_light_indices"):
         getattr(lib, name).argtypes = [vp, vp, ctypes.c_size_t, vp]
     lib.hvcf_download_total.argtypes = [vp, u32, ctypes.POINTER(u32), vp]
+    lib.hvcf_download_grid.argtypes = [vp, u32, vp, ctypes.c_size_t, vp, ctypes.c_size_t, ctypes.POINTER(u32), vp]
     lib.hvcf_get_stats.argtypes = [vp, u32, ctypes.POINTER(Stats), vp]
     lib.hvcf_host_alloc.argtypes = [ctypes.c_size_t, ctypes.POINTER(vp)]
     lib.hvcf_host_free.argtypes = [vp]
@@ -527,6 +528,16 @@ class Context:
         out = np.zeros(max(n, 1), np.uint32)
         _check(self.lib.hvcf_download_light_indices(self.handle, _ptr(out), n * 4, stream))
         return out[:n]
+
+    def download_grid(self, frame=0, stream=None):
+        """(cells, indices[:total], total) of the frame in one call (hvcf_download_grid)."""
+        b = self.buffers()
+        cells = np.empty(self.cluster_total, CELL_DT)
+        idx = np.empty(int(b.light_indices_capacity), np.uint32)
+        total = ctypes.c_uint32()
+        _check(self.lib.hvcf_download_grid(self.handle, frame, cells.ctypes.data, cells.nbytes, idx.ctypes.data, idx.nbytes,
+                                           ctypes.byref(total), stream))
+        return cells, idx[: total.value], int(total.value)
 
     def download_total(self, frame=0, stream=None):
         t = ctypes.c_uint32(0)

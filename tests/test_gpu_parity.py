@@ -336,3 +336,22 @@ def test_copy_pass_and_write_pass_give_identical_bytes(hv, oracle, monkeypatch, 
         assert out[lists][0].tobytes() == ref[0].tobytes() and out[lists][1].tobytes() == ref[1].tobytes(), f"HVCF_SEG_LISTS={lists}"
     assert out["0"][3]["write_pass_tests"] > 0 or n == 0
     assert out["1"][3]["write_pass_tests"] == 0
+
+
+def test_download_grid_in_one_call(hv, oracle):
+    grid, screen = GRIDS["A"]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(5000)
+    with hv.Context(grid=grid, max_lights=5000) as ctx:
+        ctx.set_lights(lights)
+        ctx.set_ubo(0, ubo)
+        ctx.cull(0)
+        cells, idx, total = ctx.download_grid(0)
+        assert total == ctx.download_total(0)
+        assert cells.tobytes() == ctx.download_light_cells().tobytes()
+        assert idx.tobytes() == ctx.download_light_indices(total).tobytes()
+        import ctypes
+        small = np.zeros(4, np.uint32)
+        t = ctypes.c_uint32()
+        rc = ctx.lib.hvcf_download_grid(ctx.handle, 0, cells.ctypes.data, cells.nbytes, small.ctypes.data, small.nbytes, ctypes.byref(t), None)
+        assert rc == -4 and t.value == total          # HVCF_ERR_CAPACITY, the total is still reported
