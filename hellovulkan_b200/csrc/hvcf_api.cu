@@ -1131,6 +1131,11 @@ static int peer_check_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: rank %u of world %u (at most %u peers)", who, rank, world, kMaxPeers);
 	if (ctx->peer.world)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: already attached; call hvcf_peer_detach first", who);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(preload_basic_kernels());
+	HVCF_CUDA(preload_hier_kernels());
+	HVCF_CUDA(preload_bin_kernels());
+	HVCF_CUDA(preload_peer_kernels());
 	return peer_alloc(ctx);
 }
 
@@ -1262,7 +1267,8 @@ int hvcf_peer_wait_grid(hvcf_ctx* ctx, void* stream)
 	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
 		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_wait_grid: no peers attached or no totals exchanged");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(launch_peer_wait(ctx->peer, static_cast<cudaStream_t>(stream)));
+	HVCF_CUDA(launch_peer_wait(ctx->peer, ctx->d_peer_totals, &ctx->d_global_index[ctx->range_frame < ctx->frame_count ? ctx->range_frame : 0],
+		static_cast<cudaStream_t>(stream)));
 	return HVCF_OK;
 }
 

@@ -757,4 +757,36 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 	}
 }
 
+
+// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
+// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
+// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
+// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
+#define HVCF_PRELOAD(k)                                                      \
+	do                                                                       \
+	{                                                                        \
+		cudaFuncAttributes a_;                                               \
+		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
+		if (e_ != cudaSuccess)                                               \
+			return e_;                                                       \
+	} while (0)
+
+cudaError_t preload_bin_kernels()
+{
+	HVCF_PRELOAD(hier_unions_kernel);
+	HVCF_PRELOAD(hier_super_unions_kernel);
+	HVCF_PRELOAD(hier_bin_kernel);
+	HVCF_PRELOAD(hier_bin2_kernel);
+	HVCF_PRELOAD((hier2_kernel<1, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, true>));
+	return cudaSuccess;
+}
+
 } // namespace hvcf

@@ -661,4 +661,37 @@ cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream)
 	return cudaGetLastError();
 }
 
+
+// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
+// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
+// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
+// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
+#define HVCF_PRELOAD(k)                                                      \
+	do                                                                       \
+	{                                                                        \
+		cudaFuncAttributes a_;                                               \
+		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
+		if (e_ != cudaSuccess)                                               \
+			return e_;                                                       \
+	} while (0)
+
+cudaError_t preload_basic_kernels()
+{
+	HVCF_PRELOAD(aabb_generate_kernel);
+	HVCF_PRELOAD(light_transform_kernel<false>);
+	HVCF_PRELOAD(light_transform_kernel<true>);
+	HVCF_PRELOAD((cull_kernel<1, true, 8>));
+	HVCF_PRELOAD((cull_kernel<2, true, 8>));
+	HVCF_PRELOAD((cull_kernel<4, true, 8>));
+	HVCF_PRELOAD((cull_kernel<1, false, 8>));
+	HVCF_PRELOAD((cull_kernel<2, false, 8>));
+	HVCF_PRELOAD((cull_kernel<4, false, 8>));
+	HVCF_PRELOAD(count_kernel);
+	HVCF_PRELOAD(scan_kernel);
+	HVCF_PRELOAD(scatter_kernel);
+	HVCF_PRELOAD(capture_base_y_kernel);
+	HVCF_PRELOAD(scatter_positions_kernel);
+	return cudaSuccess;
+}
+
 } // namespace hvcf

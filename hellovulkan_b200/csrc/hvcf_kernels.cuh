@@ -207,6 +207,11 @@ cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total,
 	cudaStream_t stream);
 cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, uint32_t cluster_begin,
 	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream);
-cudaError_t launch_peer_wait(const PeerParams& p, cudaStream_t stream);
+cudaError_t launch_peer_wait(const PeerParams& p, const uint32_t* totals, uint32_t* frame_total, cudaStream_t stream);
+// force-load every kernel a frame can launch (see hvcf_kernels.cu: lazy loading vs kernels that spin on another shard)
+cudaError_t preload_basic_kernels();
+cudaError_t preload_hier_kernels();
+cudaError_t preload_bin_kernels();
+cudaError_t preload_peer_kernels();
 
 } // namespace hvcf

@@ -187,11 +187,19 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 	}
 }
 
-__global__ void __launch_bounds__(32) peer_wait_kernel(const PeerParams p)
+// also leaves the total of the WHOLE grid in globalIndexCountBuffers_[frame] (the write pass stored this shard's running
+// total there), so that the counter too reads the same on every GPU as after an unsharded frame
+__global__ void __launch_bounds__(32) peer_wait_kernel(const PeerParams p, const uint32_t* __restrict__ totals, uint32_t* __restrict__ frame_total)
 {
 	const uint32_t r = threadIdx.x;
 	if (r < p.world && r != p.rank)
 		spin_epoch(&p.mail[p.rank]->arrived[r], p.epoch, p.mail[p.rank], 2u, r);
+	uint32_t sum = r < p.world ? totals[r] : 0u;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1)
+		sum += __shfl_xor_sync(0xffffffffu, sum, o);
+	if (r == 0 && frame_total)
+		*frame_total = sum;
 	__threadfence_system();
 }
 
@@ -209,10 +217,32 @@ cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, c
 	return cudaGetLastError();
 }
 
-cudaError_t launch_peer_wait(const PeerParams& p, cudaStream_t stream)
+cudaError_t launch_peer_wait(const PeerParams& p, const uint32_t* totals, uint32_t* frame_total, cudaStream_t stream)
 {
-	peer_wait_kernel<<<1, 32, 0, stream>>>(p);
+	peer_wait_kernel<<<1, 32, 0, stream>>>(p, totals, frame_total);
 	return cudaGetLastError();
+}
+
+
+// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
+// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
+// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
+// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
+#define HVCF_PRELOAD(k)                                                      \
+	do                                                                       \
+	{                                                                        \
+		cudaFuncAttributes a_;                                               \
+		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
+		if (e_ != cudaSuccess)                                               \
+			return e_;                                                       \
+	} while (0)
+
+cudaError_t preload_peer_kernels()
+{
+	HVCF_PRELOAD(peer_totals_kernel);
+	HVCF_PRELOAD(peer_push_kernel);
+	HVCF_PRELOAD(peer_wait_kernel);
+	return cudaSuccess;
 }
 
 } // namespace hvcf

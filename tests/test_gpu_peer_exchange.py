@@ -221,3 +221,53 @@ def test_range_argument_errors(hv, oracle):
         brute.set_ubo(0, ubo)
         with pytest.raises(hv.HvcfError):
             brute.cull_begin_range(0, 0, 5000)
+
+
+def test_config3_full_size_sharded_equals_unsharded(hv, torch_mod, oracle):
+    """BASELINE configs[3] at its full size, 64x36x96 clusters x 16,777,216 lights: invariants on everything, a seeded sample of
+    clusters checked in full by the oracle, and the z-slab sharded result (4 unequal slabs, peer exchange, light buffer fed in
+    chunks through hvcf_cull_begin_range) byte-identical to the unsharded one on every shard."""
+    grid, screen, n = (64, 36, 96), (3840, 2160), 1 << 24
+    ubo = oracle.camera_ubo(grid, screen)
+    aabb = oracle.generate_aabbs(ubo)
+    lights = oracle.init_lights(n)
+    want_cells, want_idx, want_total = run_single(hv, grid, ubo, lights)
+    cnt = want_cells["count"].astype(np.int64)
+    assert np.all(cnt <= 150) and int(cnt.sum()) == want_total
+    assert np.array_equal(want_cells["offset"].astype(np.int64), np.concatenate([[0], np.cumsum(cnt)[:-1]]))
+    rng = np.random.default_rng(7)
+    for c in rng.choice(len(aabb), size=12, replace=False):
+        want, _ = oracle.cull_one(ubo, aabb[c:c + 1], lights)
+        got = want_idx[want_cells["offset"][c]: want_cells["offset"][c] + want_cells["count"][c]]
+        assert np.array_equal(got, want), f"cluster {c}"
+    slabs = [(0, 40), (40, 61), (61, 70), (70, 96)]
+    ctxs = [hv.Context(grid=grid, max_lights=n, z_begin=a, z_end=b) for a, b in slabs]
+    streams = [torch_mod.cuda.Stream() for _ in slabs]
+    try:
+        for c in ctxs:
+            c.set_lights(lights)
+            c.set_ubo(0, ubo)
+        torch_mod.cuda.synchronize()
+        for r, c in enumerate(ctxs):
+            c.peer_attach_local(r, ctxs)
+        from hellovulkan_b200.sharded import ShardedCuller
+        for c, s in zip(ctxs, streams):
+            sp = s.cuda_stream
+            for b, e in ShardedCuller.chunk_bounds(n, 4):
+                c.cull_begin_range(0, b, e, 0, stream=sp)
+            c.peer_exchange_totals(stream=sp)
+            c.cull_finish(0, c.peer_index_base_ptr(), stream=sp)
+            c.peer_push_grid(stream=sp)
+            c.peer_wait_grid(stream=sp)
+        for c, s in zip(ctxs, streams):
+            assert c.peer_status(stream=s.cuda_stream) == 0
+        for r, c in enumerate(ctxs):
+            cells, idx, total = c.download_grid(0)
+            assert total == want_total, f"shard {r}"
+            assert cells.tobytes() == want_cells.tobytes(), f"shard {r}: light cells"
+            assert idx.tobytes() == want_idx.tobytes(), f"shard {r}: light indices"
+        for c in ctxs:
+            c.peer_detach()
+    finally:
+        for c in ctxs:
+            c.close()
