@@ -161,6 +161,8 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // LISTS (count pass only): every counted hit below the lane's limit is also stored, in light order, in the
 // (segment, cluster) list seg_lists[seg][cluster][cap]; hier_copy_kernel then concatenates the lists into the index buffer
 // and the write pass (the second walk of the hierarchy) is not needed.
+__device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
+
 template <int K, bool WRITE, bool LISTS>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
@@ -182,8 +184,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// instead of the whole prologue -- 63 % of the write pass's warp programs at B1M ran ~190 instructions of prologue only
 	// to find that they own no output (profiles/r01q).  Segment 0 stays: it writes the light cells.
 	// (the slot index is recomputed where it is needed: keeping it live cost the count pass two registers = one CTA per SM)
-#define HVCF_ANY_SLOT (static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit)
-	if (WRITE && seg != 0 && !p.trace && __ldg(&p.unit_any[HVCF_ANY_SLOT]) == 0u)
+	if (WRITE && seg != 0 && !p.trace && __ldg(&p.unit_any[any_slot(seg, unit)]) == 0u)
 		return;
 	// count pass: a group whose level-0 slots are empty for every tile of this segment has nothing to test -- zero counts,
 	// no boxes, no early-exit counters, no union reductions (HVCF_EMPTY_SKIP=0 at build time switches the check off)
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 					p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + c] = 0u;
 			}
 			if (lane == 0)
-				p.unit_any[HVCF_ANY_SLOT] = 0u;
+				p.unit_any[any_slot(seg, unit)] = 0u;
 			return;
 		}
 	}
@@ -291,7 +292,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 					if (cidx[k] != kSkip)
 						p.seg_counts[static_cast<size_t>(seg) * p.cluster_count + cidx[k]] = 0u;
 				if (lane == 0)
-					p.unit_any[HVCF_ANY_SLOT] = 0u;
+					p.unit_any[any_slot(seg, unit)] = 0u;
 			}
 			return;
 		}
@@ -489,7 +490,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			counted = counted || cnt[k] != 0;
 		const bool any_counted = __any_sync(0xffffffffu, counted);
 		if (lane == 0)
-			p.unit_any[HVCF_ANY_SLOT] = any_counted ? 1u : 0u;
+			p.unit_any[any_slot(seg, unit)] = any_counted ? 1u : 0u;
 #pragma unroll
 		for (int k = 0; k < K; ++k)
 			if (cidx[k] != kSkip)
@@ -633,28 +634,44 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		float4* const rec = p.bin_rec + slot;
 		uint16_t* const idx = p.bin_idx + slot;
 		uint32_t cnt = 0;
-		for (uint32_t i0 = 0; i0 < ns; i0 += 32)
+		// two list entries per lane per trip (i0 + lane, then i0 + 32 + lane: ascending), tested as a pair on FADD2/FMUL2 like the
+		// tile pairs of phase A; a missing entry is the never-hit record (r2 = -1)
+		for (uint32_t i0 = 0; i0 < ns; i0 += 64)
 		{
-			const uint32_t i = i0 + lane;
-			bool hit = false;
-			uint32_t t = 0;
-			float x = 0.0f, y = 0.0f, z = 0.0f, r2 = -1.0f;
-			if (i < ns)
+			const uint32_t ia = i0 + lane, ib = ia + 32;
+			uint32_t ta = 0, tb = 0;
+			float4 pa = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = make_float4(0.0f, 0.0f, -1.0f, -1.0f); // (x0,x1,y0,y1), (z0,z1,r0,r1)
+			if (ia < ns)
 			{
-				t = list[i];
+				ta = list[ia];
 				// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
-				const uint32_t f = (((t >> 6) * 64 + (t & 31)) << 2) + ((t >> 5) & 1);
-				x = tile_f[f], y = tile_f[f + 2], z = tile_f[f + 128], r2 = tile_f[f + 130];
-				hit = sphere_box_hit(x, y, z, r2, lo, hi);
+				const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
+				pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
 			}
-			const uint32_t m = __ballot_sync(0xffffffffu, hit);
-			const uint32_t d = cnt + __popc(m & lt);
-			if (hit && d < kBinCap)
+			if (ib < ns)
 			{
-				rec[d] = make_float4(x, y, z, r2);
-				idx[d] = static_cast<uint16_t>(t);
+				tb = list[ib];
+				const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
+				pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
 			}
-			cnt += __popc(m);
+			bool h0, h1;
+			sphere_box_hit2(pa, pb, lo, hi, h0, h1);
+			const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+			if ((m0 | m1) != 0)
+			{
+				const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+				if (h0 && d0 < kBinCap)
+				{
+					rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
+					idx[d0] = static_cast<uint16_t>(ta);
+				}
+				if (h1 && d1 < kBinCap)
+				{
+					rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
+					idx[d1] = static_cast<uint16_t>(tb);
+				}
+				cnt += __popc(m0) + __popc(m1);
+			}
 		}
 		if (lane == 0)
 			p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
@@ -758,18 +775,7 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 }
 
 
-// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
-// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
-// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
-// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
-#define HVCF_PRELOAD(k)                                                      \
-	do                                                                       \
-	{                                                                        \
-		cudaFuncAttributes a_;                                               \
-		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
-		if (e_ != cudaSuccess)                                               \
-			return e_;                                                       \
-	} while (0)
+// every kernel of this file that a frame can launch, force-loaded (HVCF_PRELOAD, hvcf_device.cuh)
 
 cudaError_t preload_bin_kernels()
 {

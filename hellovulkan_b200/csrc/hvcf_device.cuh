@@ -143,4 +143,17 @@ struct DeviceStats
 	unsigned long long write_tests;  // union + exact tests the write pass repeats (not in the two counters above)
 };
 
+// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
+// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
+// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
+// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
+#define HVCF_PRELOAD(k)                                                      \
+	do                                                                       \
+	{                                                                        \
+		cudaFuncAttributes a_;                                               \
+		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
+		if (e_ != cudaSuccess)                                               \
+			return e_;                                                       \
+	} while (0)
+
 } // namespace hvcf

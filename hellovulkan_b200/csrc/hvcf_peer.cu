@@ -224,18 +224,7 @@ cudaError_t launch_peer_wait(const PeerParams& p, const uint32_t* totals, uint32
 }
 
 
-// CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
-// that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next
-// kernel has never been launched before, the load waits for the spinning kernel and the spinning kernel waits for the load.
-// So every kernel a frame can launch is loaded up front, when peers are attached (cudaFuncGetAttributes forces the load).
-#define HVCF_PRELOAD(k)                                                      \
-	do                                                                       \
-	{                                                                        \
-		cudaFuncAttributes a_;                                               \
-		cudaError_t e_ = cudaFuncGetAttributes(&a_, reinterpret_cast<const void*>(k)); \
-		if (e_ != cudaSuccess)                                               \
-			return e_;                                                       \
-	} while (0)
+// every kernel of this file that a frame can launch, force-loaded (HVCF_PRELOAD, hvcf_device.cuh)
 
 cudaError_t preload_peer_kernels()
 {
