@@ -161,6 +161,10 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // LISTS (count pass only): every counted hit below the lane's limit is also stored, in light order, in the
 // (segment, cluster) list seg_lists[seg][cluster][cap]; hier_copy_kernel then concatenates the lists into the index buffer
 // and the write pass (the second walk of the hierarchy) is not needed.
+// Measured and rejected on B200 (r01y kernels, per-kernel events): one warp program serving 2 or 4 segments in a loop (stride
+// gridDim.y) with the lane's cluster indices and boxes loaded once.  The loop-carried state costs registers (write pass K=2
+// 64 -> 96, count pass K=2 spills 48 B) and the gain of the saved round trips does not pay for it: B1M count pass 97 -> 101 us,
+// write pass 57 -> 77 us with 2 segments per program; A65k and A1M within +-1 us.
 __device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
 
 template <int K, bool WRITE, bool LISTS>
