@@ -165,6 +165,8 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // gridDim.y) with the lane's cluster indices and boxes loaded once.  The loop-carried state costs registers (write pass K=2
 // 64 -> 96, count pass K=2 spills 48 B) and the gain of the saved round trips does not pay for it: B1M count pass 97 -> 101 us,
 // write pass 57 -> 77 us with 2 segments per program; A65k and A1M within +-1 us.
+// Also rejected: exact "owns output" flags per (segment, warp program) set by hier_finalize_kernel instead of the count pass's
+// "counted anything" word -- B1M write pass 57.3 -> 55.8 us but finalize 25.5 -> 28.6 us: almost every program that counted owns output.
 __device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
 
 template <int K, bool WRITE, bool LISTS>
