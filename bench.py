@@ -814,12 +814,13 @@ def run_sharded(args, hvcf, world, rank, local, dev, barrier):
                 kernel_ms = {"error": str(e)}
         pipelined = {}
         if exchange == "peer":
-            for wire in ("raw", "view"):
+            for wire in ("raw", "view", "gather"):
                 try:
                     pms, pph, ptot, _ = timed(eng, sc, True, steps, wire=wire)
                     pipelined[wire] = {"ms_per_frame": pms, "value": C * n / (pms * 1e-3), "phase_ms_max_over_ranks": pph,
                                        "chunks": args.sharded_chunks, "total_indices": int(ptot.sum().item()),
-                                       "wire_bytes_per_light": 48 if wire == "raw" else 16}
+                                       "wire_bytes_per_light": 48 if wire == "raw" else 16,
+                                       "lights_owned": "rank 0" if wire != "gather" else "in shards of L/N (all-gather of the 16 B view records)"}
                 except Exception as e:
                     pipelined[wire] = {"error": f"{type(e).__name__}: {e}"}
             sc.broadcast_lights(n)   # the view run leaves no LightData on the other ranks

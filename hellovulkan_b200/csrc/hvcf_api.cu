@@ -941,6 +941,38 @@ int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, u
 	return HVCF_OK;
 }
 
+int hvcf_transform_lights(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, void* stream)
+{
+	if (!ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_transform_lights: null context");
+	if (frame >= ctx->frame_count || !ctx->ubo_set[frame])
+		return fail(HVCF_ERR_NOT_READY, "hvcf_transform_lights: hvcf_set_ubo(frame %u) has not been called", frame);
+	const uint32_t n = ctx->num_lights;
+	const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
+	if (light_begin % kTileLights || light_begin > light_end || light_begin >= padded || (light_end < n && light_end % kTileLights) ||
+		light_end > padded)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_transform_lights: [%u,%u) of %u lights: whole %u-light tiles", light_begin, light_end, n,
+			kTileLights);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	const uint32_t end_padded = light_end >= n ? padded : light_end;
+	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+	LightAnim anim_storage{};
+	const LightAnim* anim = nullptr;
+	if (ctx->anim_len && n)
+	{
+		anim_storage.base_y = ctx->d_base_y + light_begin;
+		anim_storage.table = ctx->d_anim_table;
+		anim_storage.mask = ctx->anim_len - 1;
+		anim_storage.step = ctx->anim_step[frame] + light_begin;
+		anim_storage.amplitude = ctx->anim_amplitude;
+		anim_storage.lights_rw = const_cast<hvcf_light_data*>(lights) + light_begin;
+		anim = &anim_storage;
+	}
+	HVCF_CUDA(launch_light_transform(&ctx->d_ubo[frame], lights + light_begin, n > light_begin ? n - light_begin : 0u, end_padded - light_begin,
+		ctx->d_lights_view + light_begin, nullptr, 0, nullptr, static_cast<cudaStream_t>(stream), anim));
+	return HVCF_OK;
+}
+
 int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes)
 {
 	if (!ctx || !out_device_ptr)

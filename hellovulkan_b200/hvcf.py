@@ -81,7 +81,7 @@ EXPORTS = [
     "hvcf_host_init_lights", "hvcf_set_timing", "hvcf_get_timing", "hvcf_measure_fp32_issue_rate", "hvcf_debug_trace",
     "hvcf_debug_kernel_times", "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
-    "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
+    "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
     "hvcf_peer_status",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
@@ -148,6 +148,7 @@ def load():
     lib.hvcf_host_frustum_ubo.argtypes = [f3, f3, ctypes.c_float, ctypes.c_float, vp]
     lib.hvcf_host_init_boxes.argtypes = [u32, u32, ctypes.c_float, vp]
     lib.hvcf_cull_begin_range.argtypes = [vp, u32, u32, u32, u32, vp]
+    lib.hvcf_transform_lights.argtypes = [vp, u32, u32, u32, vp]
     lib.hvcf_lights_view_ptr.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
     lib.hvcf_peer_export.argtypes = [vp, vp]
     lib.hvcf_peer_attach.argtypes = [vp, u32, u32, vp]
@@ -445,6 +446,10 @@ class Context:
     def cull_begin_range(self, frame, light_begin, light_end, flags=0, stream=None):
         """hvcf_cull_begin in pieces (whole 1,024-light tiles, ascending); flags: RANGE_TRANSFORM | RANGE_BIN, 0 = both."""
         _check(self.lib.hvcf_cull_begin_range(self.handle, frame, light_begin, light_end, flags, stream))
+
+    def transform_lights(self, frame, light_begin, light_end, stream=None):
+        """view-space records of a whole-tile light range, in any order (hvcf_transform_lights)."""
+        _check(self.lib.hvcf_transform_lights(self.handle, frame, light_begin, light_end, stream))
 
     def lights_view_ptr(self):
         """(device pointer, bytes) of the view-space culling records, 16 B per light."""

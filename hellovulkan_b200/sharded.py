@@ -128,6 +128,9 @@ class HvcfEngine:
     def cull_begin_range(self, frame, begin, end, flags=0):
         self.ctx.cull_begin_range(frame, begin, end, flags)
 
+    def transform_lights(self, frame, begin, end):
+        self.ctx.transform_lights(frame, begin, end)
+
     def lights_view(self):
         if not hasattr(self, "_lights_view"):
             ptr, nbytes = self.ctx.lights_view_ptr()
@@ -277,12 +280,15 @@ class ShardedCuller:
         """steps 1-5 with step 1 cut into chunks: while chunk q+1 is on the wire, chunk q is transformed and binned
         (hvcf_cull_begin_range).  wire="raw": the 48 B LightData records travel and every rank transforms them
         (every rank ends up with the reference light buffer); wire="view": rank 0 transforms each chunk once and the
-        16 B view-space culling records travel (a third of the bytes; the other ranks hold no LightData).
+        16 B view-space culling records travel (a third of the bytes; the other ranks hold no LightData);
+        wire="gather": lights are OWNED in shards -- rank r holds (and moves) the LightData of light tiles
+        [r T/N, (r+1) T/N), transforms only those, and one in-place ncclAllGather of the 16 B records gives every rank
+        the whole view buffer: no rank sends more than its share, so the exchange scales with the ranks.
         Peer exchange only."""
         if self.exchange != "peer":
             raise ValueError("frame_pipelined needs exchange='peer'")
-        if wire not in ("raw", "view"):
-            raise ValueError("wire must be 'raw' or 'view'")
+        if wire not in ("raw", "view", "gather"):
+            raise ValueError("wire must be 'raw', 'view' or 'gather'")
         e = self.engine
         T, B = 1, 2
         if e.num_lights != n:
@@ -292,6 +298,19 @@ class ShardedCuller:
         if self.world == 1:
             for b, en in bounds:
                 e.cull_begin_range(frame, b, en, T | B)
+        elif wire == "gather":
+            view = e.lights_view()
+            tiles = -(-max(n, 1) // 1024)
+            per = -(-tiles // self.world)                     # tiles per rank; the buffer is padded to per * world tiles
+            lo, hi = self.rank * per * 1024, (self.rank + 1) * per * 1024
+            padded = tiles * 1024
+            if per * self.world * 1024 * 16 > view.numel():
+                raise ValueError("wire='gather' needs max_lights padded to world x whole tiles")
+            if lo < padded:
+                e.transform_lights(frame, lo, min(hi, max(n, lo)))   # the slice that reaches n also writes the padding records
+            dist.all_gather_into_tensor(view[: 16 * per * self.world * 1024], view[16 * lo: 16 * hi], group=self.group)
+            for b, en in bounds:
+                e.cull_begin_range(frame, b, en, B)
         elif wire == "raw":
             works = [dist.broadcast(e.lights[48 * b: 48 * en], src=0, group=self.group, async_op=True) for b, en in bounds]
             for (b, en), w in zip(bounds, works):

@@ -160,6 +160,12 @@ HVCF_API int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_i
 #define HVCF_RANGE_BIN 2u
 HVCF_API int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, uint32_t flags, void* stream);
 HVCF_API int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes);
+/* The TRANSFORM half alone, for any whole-tile range in any order and without touching the frame's progress: lights
+ * [light_begin, light_end) of the bound light buffer -> view-space records with the UBO of `frame` (LightCulling.comp:51-53
+ * hoisted).  For lights OWNED in shards: every rank transforms its own slice, the 16 B records are all-gathered, and
+ * hvcf_cull_begin_range(0, n, HVCF_RANGE_BIN) takes it from there.  The range that reaches the light count also writes the
+ * padding records of the last tile. */
+HVCF_API int hvcf_transform_lights(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, void* stream);
 HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 
 /* The exchange step of the z-slab sharded grid done by the GPUs themselves over NVLink peer memory (new: the

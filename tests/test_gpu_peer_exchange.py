@@ -271,3 +271,31 @@ def test_config3_full_size_sharded_equals_unsharded(hv, torch_mod, oracle):
     finally:
         for c in ctxs:
             c.close()
+
+
+@pytest.mark.parametrize("n", [0, 1, 1024, 5000, 70_000])
+def test_transform_slices_in_any_order_then_bin(hv, oracle, n):
+    """lights owned in shards (wire='gather'): the view records are produced slice by slice in any order by
+    hvcf_transform_lights, then hvcf_cull_begin_range(BIN) alone completes the frame: the bytes of one hvcf_cull call"""
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    lights = oracle.init_lights(n)
+    want_cells, want_idx, want_total = run_single(hv, GRID_A, ubo, lights)
+    tiles = max(1, -(-n // 1024))
+    with hv.Context(grid=GRID_A, max_lights=max(n, 1)) as ctx:
+        ctx.set_lights(lights)
+        ctx.set_ubo(0, ubo)
+        order = list(range(tiles))
+        np.random.default_rng(n).shuffle(order)
+        for frame_no in range(2):
+            for t in order:
+                b = t * 1024
+                ctx.transform_lights(0, b, min(b + 1024, max(n, b)))
+            ctx.cull_begin_range(0, 0, n, hv.RANGE_BIN)
+            ctx.cull_finish(0, None)
+            cells, idx, total = ctx.download_grid(0)
+            assert total == want_total
+            assert cells.tobytes() == want_cells.tobytes() and idx.tobytes() == want_idx.tobytes()
+        for args in ((0, 100, 2048), (0, 0, 99999999), (0, 2048, 1024)):
+            if n >= 5000:
+                with pytest.raises(hv.HvcfError):
+                    ctx.transform_lights(*args)
