@@ -420,6 +420,27 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 		run += w < warp ? v : 0u;
 		total += v;
 	}
+	// warp 0 publishes this CTA's aggregate BEFORE the second sweep: the CTAs behind it in the look-back chain need nothing else
+	// from us, so their wait shrinks by the length of our sweep (A65k: the chain is the kernel)
+	const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
+	uint32_t v = 0, inc = 0, agg = 0, over = 0;
+	if (warp == 0)
+	{
+		v = valid ? min(total, p.cap) : 0u;
+		inc = v;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1)
+		{
+			const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+			if (lane >= static_cast<uint32_t>(d))
+				inc += t;
+		}
+		agg = __shfl_sync(0xffffffffu, inc, 31);
+		over = __popc(__ballot_sync(0xffffffffu, valid && v >= p.cap));
+		// state word: [epoch:30 | flag:2 | value:32]; flag 1 = aggregate of this CTA, 2 = inclusive prefix
+		if (lane == 0)
+			st_release_u64(&p.scan_state[blockIdx.x], tag | ((blockIdx.x == 0 ? 2ull : 1ull) << 32) | agg);
+	}
 	if (valid && !p.skip_prefix)
 	{
 		uint32_t* pre = p.seg_prefix + c;
@@ -446,21 +467,6 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 	}
 	if (warp != 0)
 		return;
-	const uint32_t v = valid ? min(total, p.cap) : 0u;
-	uint32_t inc = v;
-#pragma unroll
-	for (int d = 1; d < 32; d <<= 1)
-	{
-		const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-		if (lane >= static_cast<uint32_t>(d))
-			inc += t;
-	}
-	const uint32_t agg = __shfl_sync(0xffffffffu, inc, 31);
-	const uint32_t over = __popc(__ballot_sync(0xffffffffu, valid && v >= p.cap));
-	// state word: [epoch:30 | flag:2 | value:32]; flag 1 = aggregate of this CTA, 2 = inclusive prefix
-	const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
-	if (lane == 0)
-		st_release_u64(&p.scan_state[blockIdx.x], tag | ((blockIdx.x == 0 ? 2ull : 1ull) << 32) | agg);
 	uint32_t prefix = 0;
 	for (int base = static_cast<int>(blockIdx.x); base > 0; base -= 32)
 	{
