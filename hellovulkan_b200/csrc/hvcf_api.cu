@@ -85,6 +85,7 @@ struct hvcf_ctx
 	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
 	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel only)
 	int bin2_mode = -1;                      // HVCF_BIN2: -1 = per frame by size, 0 = never, 1 = always
+	uint32_t xbin_max_lights = 0;            // HVCF_XBIN_MAX: frames with at most this many lights fuse transform + binning (0 = never)
 	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
 	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
 	uint16_t* d_bin_idx = nullptr;
@@ -393,6 +394,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->tiles_cap = max_tiles;
 		// two-level level-0 binning (HVCF_BIN2=0/1 forces it off/on; otherwise chosen per frame, see hier_range)
 		c->bin2_mode = env_int("HVCF_BIN2", -1);
+		c->xbin_max_lights = static_cast<uint32_t>(env_int("HVCF_XBIN_MAX", 262144));
 		if (!c->hier_v1 && c->bin2_mode != 0)
 		{
 			c->bin_sg = (c->hp.ncb + 31) / 32 > 8 ? (c->hp.ncb + 31) / 32 : 8;
@@ -799,6 +801,33 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 	uint32_t* zero = ctx->range_cleared ? nullptr : ctx->d_hscratch;
 	const uint32_t zero_words = ctx->range_cleared ? 0u : ctx->cluster_count * kHMaxChunks;
 	DeviceStats* clear_stats = ctx->range_cleared ? nullptr : stats;
+	// few lights, whole frame in one call, one-level binning, no animation: transform + binning as one kernel
+	if (flags == (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN) && begin == 0 && last && !ctx->range_cleared && !ctx->hier_v1 && !ctx->anim_len &&
+		ctx->xbin_max_lights && n <= ctx->xbin_max_lights &&
+		!(ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups || static_cast<uint64_t>(ctx->hp.ncb) * n >= (1ull << 28))))
+	{
+		XBinParams q{};
+		q.bin.lights_view = ctx->d_lights_view;
+		q.bin.cb_union = ctx->d_cb_union;
+		q.bin.ncb = ctx->hp.ncb;
+		q.bin.tiles_cap = ctx->tiles_cap;
+		q.bin.bin_count = ctx->d_bin_count;
+		q.bin.bin_rec = ctx->d_bin_rec;
+		q.bin.bin_idx = ctx->d_bin_idx;
+		q.bin.stats = stats;
+		q.ubo = &ctx->d_ubo[frame];
+		q.lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+		q.num_lights = n;
+		q.zero = zero;
+		q.zero_words = zero_words;
+		HVCF_CUDA(launch_hier_xbin(q, end_padded / kTileLights, s));
+		ctx->range_cleared = true;
+		ctx->range_transformed = ctx->range_binned = end_padded;
+		++ctx->open_launches;
+		HVCF_CUDA(hier_kmark(ctx, frame, 1, s));
+		HVCF_CUDA(hier_kmark(ctx, frame, 2, s));
+		return HVCF_OK;
+	}
 	if (flags & HVCF_RANGE_TRANSFORM)
 	{
 		const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;

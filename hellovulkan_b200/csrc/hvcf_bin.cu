@@ -699,6 +699,128 @@ cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aa
 	return cudaGetLastError();
 }
 
+// ======================================================================================================
+// transform + level 0 in ONE kernel, for frames with few lights (grid A x 65,536: the two kernels are 4 + 7 us of pure launch
+// and memory latency in a 57 us frame).  Every CTA of a tile transforms the tile's 1,024 lights itself (LightCulling.comp:51-53,
+// the arithmetic of light_transform_kernel, 28 flops per light -- cheaper than a round trip through HBM) straight into the
+// shared-memory tile; the CTA of the first group column also stores the tile to lights_view for the passes that follow.
+// It is the first kernel of the frame, so it also clears the early-exit counters and the work counters; its own test count
+// is a product (every light against every group), stored rather than accumulated.
+// ======================================================================================================
+constexpr uint32_t kXBinMinCtas = 32;
+__global__ void __launch_bounds__(kBinWarps * 32) hier_xbin_kernel(const XBinParams q)
+{
+	__shared__ __align__(128) float4 s_tile4[kTileBytes / 16];
+	const BinParams& p = q.bin;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t tile_id = blockIdx.y, cb = blockIdx.x * kBinWarps + warp;
+	grid_dep_launch();
+	{
+		const uint32_t nthreads = gridDim.x * gridDim.y * blockDim.x;
+		const uint32_t tid = (blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+		for (uint32_t i = tid; i < q.zero_words; i += nthreads)
+			q.zero[i] = 0u;
+		if (tid == 0)
+		{
+			DeviceStats* st = p.stats;
+			st->executed_tests = 0ull;
+			st->total_indices = 0u;
+			st->overflow_clusters = 0u;
+			st->write_tests = 0ull;
+			st->bin_tests = st->prefilter_tests = static_cast<unsigned long long>(p.ncb) * q.tiles * kTileLights;
+		}
+	}
+	if (tile_id >= q.tiles) // CTAs beyond the last tile only help with the clearing (frames of a few tiles)
+		return;
+	const float* view = q.ubo->camera_view;
+	// 512 lane pairs per tile, two per thread
+#pragma unroll
+	for (uint32_t r = 0; r < 2; ++r)
+	{
+		const uint32_t pr = r * 256 + threadIdx.x; // pair inside the tile
+		const uint32_t g = pr >> 5, l = pr & 31;
+		float x[2], y[2], z[2], r2[2];
+#pragma unroll
+		for (int h = 0; h < 2; ++h)
+		{
+			const uint32_t i = tile_id * kTileLights + g * kGroupLights + h * 32 + l;
+			if (i < q.num_lights)
+			{
+				const float4 pw = *reinterpret_cast<const float4*>(q.lights[i].position);
+				const float radius = q.lights[i].radius;
+				x[h] = mat_row_dot(view, 0, pw.x, pw.y, pw.z, pw.w);
+				y[h] = mat_row_dot(view, 1, pw.x, pw.y, pw.z, pw.w);
+				z[h] = mat_row_dot(view, 2, pw.x, pw.y, pw.z, pw.w);
+				r2[h] = __fmul_rn(radius, radius);
+			}
+			else
+			{
+				x[h] = y[h] = z[h] = 0.0f;
+				r2[h] = -1.0f; // pad lights cannot hit
+			}
+		}
+		s_tile4[g * 64 + l] = make_float4(x[0], x[1], y[0], y[1]);
+		s_tile4[g * 64 + 32 + l] = make_float4(z[0], z[1], r2[0], r2[1]);
+	}
+	__syncthreads();
+	if (blockIdx.x == 0)
+	{
+		float4* out = const_cast<float4*>(p.lights_view) + static_cast<size_t>(tile_id) * (kTileBytes / 16);
+		for (uint32_t i = threadIdx.x; i < kTileBytes / 16; i += blockDim.x)
+			out[i] = s_tile4[i];
+	}
+	if (cb >= p.ncb)
+		return;
+	float lo[3], hi[3];
+	{
+		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
+		const float4 a = __ldg(u), b = __ldg(u + 1);
+		lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
+		hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
+	}
+	const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+	float4* const rec = p.bin_rec + slot;
+	uint16_t* const idx = p.bin_idx + slot;
+	const uint32_t lt = lanemask_lt();
+	uint32_t cnt = 0;
+#pragma unroll 4
+	for (uint32_t g = 0; g < kTileGroups; ++g)
+	{
+		const float4 a = s_tile4[g * 64 + lane], b = s_tile4[g * 64 + 32 + lane];
+		bool h0, h1;
+		sphere_box_hit2(a, b, lo, hi, h0, h1);
+		const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+		if ((m0 | m1) == 0)
+			continue;
+		const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+		if (h0 && d0 < kBinCap)
+		{
+			rec[d0] = make_float4(a.x, a.z, b.x, b.z);
+			idx[d0] = static_cast<uint16_t>(g * 64 + lane);
+		}
+		if (h1 && d1 < kBinCap)
+		{
+			rec[d1] = make_float4(a.y, a.w, b.y, b.w);
+			idx[d1] = static_cast<uint16_t>(g * 64 + 32 + lane);
+		}
+		cnt += __popc(m0) + __popc(m1);
+	}
+	if (lane == 0)
+		p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
+}
+
+cudaError_t launch_hier_xbin(const XBinParams& q, uint32_t tiles, cudaStream_t stream)
+{
+	if (q.bin.ncb == 0 || tiles == 0)
+		return cudaSuccess;
+	XBinParams qq = q;
+	qq.tiles = tiles;
+	const uint32_t gx = (q.bin.ncb + kBinWarps - 1) / kBinWarps;
+	const uint32_t min_rows = q.zero_words ? (kXBinMinCtas + gx - 1) / gx : 0u;
+	hier_xbin_kernel<<<dim3(gx, tiles > min_rows ? tiles : min_rows, 1), kBinWarps * 32, 0, stream>>>(qq);
+	return cudaGetLastError();
+}
+
 cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream)
 {
 	if (ns == 0)
@@ -789,6 +911,7 @@ cudaError_t preload_bin_kernels()
 	HVCF_PRELOAD(hier_super_unions_kernel);
 	HVCF_PRELOAD(hier_bin_kernel);
 	HVCF_PRELOAD(hier_bin2_kernel);
+	HVCF_PRELOAD(hier_xbin_kernel);
 	HVCF_PRELOAD((hier2_kernel<1, false, false>));
 	HVCF_PRELOAD((hier2_kernel<1, true, false>));
 	HVCF_PRELOAD((hier2_kernel<1, false, true>));

@@ -182,6 +182,18 @@ cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream);
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
 	float* cb_union, cudaStream_t stream);
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream);
+// transform + one-level binning fused (hier_xbin_kernel): the first kernel of a frame with few lights
+struct XBinParams
+{
+	BinParams bin;
+	const hvcf_cluster_forward_ubo* ubo;
+	const hvcf_light_data* lights;
+	uint32_t num_lights;
+	uint32_t tiles;                // set by the launcher
+	uint32_t* zero;                // early-exit counters to clear
+	uint32_t zero_words;
+};
+cudaError_t launch_hier_xbin(const XBinParams& q, uint32_t tiles, cudaStream_t stream);
 cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream);
 size_t hier_bin2_smem_bytes(uint32_t ns);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);

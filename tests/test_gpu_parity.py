@@ -302,6 +302,30 @@ def test_one_and_two_level_binning_give_identical_bytes(hv, oracle, monkeypatch,
     assert out["1"][3]["prefilter_tests"] != out["0"][3]["prefilter_tests"]   # the two kernels really ran
 
 
+@pytest.mark.parametrize("name,n,cap", [("A", 70_000, 150), ("A", 65_536, 150), ("A", 1, 150), ("A", 0, 150), ("A", 3_000, 4), ("B", 20_000, 150),
+                                        ("A", 262_144, 150)])
+def test_fused_and_split_transform_binning_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap):
+    """frames with few lights run transform + level-0 binning as one kernel (hier_xbin_kernel, HVCF_XBIN_MAX lights at most);
+    with the fusion switched off the two kernels run: same light cells and index buffer, same binning test count, one launch more"""
+    grid, screen = GRIDS[name]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=23)
+    out = {}
+    for mx in ("0", "262144"):
+        monkeypatch.setenv("HVCF_XBIN_MAX", mx)
+        out[mx] = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"])
+    monkeypatch.delenv("HVCF_XBIN_MAX")
+    a, b = out["0"], out["262144"]
+    assert a[2] == b[2] and a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+    for k in ("bin_tests", "total_indices", "overflow_clusters"):   # the other counters depend on when early-exit knowledge arrives
+        assert a[3][k] == b[3][k], k
+    assert b[3]["prefilter_tests"] >= b[3]["bin_tests"]
+    fused = name == "A"   # grid B has enough cluster groups for the two-level binning kernel, which is not fused
+    assert a[3]["kernel_launches"] - b[3]["kernel_launches"] == (1 if fused else 0)
+    ref = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["brute"])
+    assert ref[2] == b[2] and ref[0].tobytes() == b[0].tobytes() and ref[1].tobytes() == b[1].tobytes()
+
+
 def test_stats_are_split_per_kernel(hv, oracle):
     """hvcf_stats: the binning kernel's tests are a part of prefilter_tests, the write pass's repeats are counted apart, and the
     count pass's exact tests equal the oracle's executed-test count rounded up to what a tile-granular early exit runs"""
