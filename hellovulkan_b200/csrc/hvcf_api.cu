@@ -85,6 +85,11 @@ struct hvcf_ctx
 	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
 	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel only)
 	int bin2_mode = -1;                      // HVCF_BIN2: -1 = per frame by size, 0 = never, 1 = always
+	bool download_kernel = true;             // HVCF_DOWNLOAD_KERNEL: hvcf_download_grid into pinned memory with one kernel
+	uint32_t download_blocks = 64;           // HVCF_DOWNLOAD_BLOCKS
+	uint32_t download_max_words = 1u << 20;  // HVCF_DOWNLOAD_KERNEL_MAX_MB (4): indices beyond this go through the copy engine
+	const void* dl_ptr[2] = {nullptr, nullptr};
+	bool dl_ok[2] = {false, false};
 	uint32_t xbin_max_lights = 0;            // HVCF_XBIN_MAX: frames with at most this many lights fuse transform + binning (0 = never)
 	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
 	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
@@ -360,6 +365,13 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	c->cluster_count = c->cluster_end - c->cluster_begin;
 	c->padded_capacity = round_up_u32(c->max_lights ? c->max_lights : 1, kTileLights);
 	c->variant = env_int("HVCF_CULL_VARIANT", 1);
+	c->download_kernel = env_int("HVCF_DOWNLOAD_KERNEL", 1) != 0;
+	{
+		const int db = env_int("HVCF_DOWNLOAD_BLOCKS", 64);
+		c->download_blocks = static_cast<uint32_t>(db < 1 ? 1 : (db > 4096 ? 4096 : db));
+		const int mb = env_int("HVCF_DOWNLOAD_KERNEL_MAX_MB", 4);
+		c->download_max_words = static_cast<uint32_t>(mb < 0 ? 0 : (mb > 2048 ? 2048 : mb)) << 18;
+	}
 	if (c->variant < 0 || c->variant >= kNumCullVariants)
 		c->variant = 1;
 	// light segments: enough CTAs to fill 148 SMs x 4 resident CTAs about twice
@@ -1461,6 +1473,22 @@ int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void
 		"hvcf_download_total");
 }
 
+// is p pinned host memory the device can store to at the same address?  (the last answer per destination is remembered:
+// a frame loop downloads into the same buffers)
+static bool mapped_host_ptr(hvcf_ctx* ctx, int which, const void* p)
+{
+	if (!p || (reinterpret_cast<uintptr_t>(p) & 15u))
+		return false;
+	if (ctx->dl_ptr[which] == p)
+		return ctx->dl_ok[which];
+	cudaPointerAttributes a{};
+	bool ok = cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer == p;
+	cudaGetLastError(); // unregistered memory is not an error here
+	ctx->dl_ptr[which] = p;
+	ctx->dl_ok[which] = ok;
+	return ok;
+}
+
 int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t cells_bytes, void* indices_dst,
 	size_t indices_capacity_bytes, uint32_t* out_total, void* stream)
 {
@@ -1474,6 +1502,28 @@ int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t ce
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	if (!ctx->h_total)
 		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 8));
+	// both destinations in pinned (mapped) host memory, 16 B aligned: one kernel stores count, cells and indices[0, count)
+	// across PCIe -- no host round trip between "how many" and "copy them" (HVCF_DOWNLOAD_KERNEL=0: the two-copy path)
+	if (ctx->download_kernel && cells_bytes % 4 == 0 && mapped_host_ptr(ctx, 0, cells_dst) && (indices_capacity_bytes == 0 || mapped_host_ptr(ctx, 1, indices_dst)))
+	{
+		const size_t cap_words = indices_capacity_bytes / sizeof(uint32_t);
+		HVCF_CUDA(launch_grid_download(ctx->d_cells, cells_bytes, ctx->d_indices, &ctx->d_global_index[frame],
+			static_cast<uint32_t>(cap_words < 0xffffffffull ? cap_words : 0xffffffffull), ctx->download_max_words, cells_dst, static_cast<uint32_t*>(indices_dst),
+			&ctx->h_total[frame], ctx->download_blocks, s));
+		HVCF_CUDA(cudaStreamSynchronize(s));
+		const uint32_t total = ctx->h_total[frame];
+		*out_total = total;
+		if (sizeof(uint32_t) * static_cast<size_t>(total) > indices_capacity_bytes)
+			return fail(HVCF_ERR_CAPACITY, "hvcf_download_grid: %u indices do not fit in %zu bytes", total, indices_capacity_bytes);
+		const uint32_t by_kernel = ctx->download_max_words & ~3u;
+		if (total > by_kernel) // a long list: the copy engine takes what the kernel left
+		{
+			HVCF_CUDA(cudaMemcpyAsync(static_cast<uint32_t*>(indices_dst) + by_kernel, ctx->d_indices + by_kernel,
+				sizeof(uint32_t) * static_cast<size_t>(total - by_kernel), cudaMemcpyDeviceToHost, s));
+			HVCF_CUDA(cudaStreamSynchronize(s));
+		}
+		return HVCF_OK;
+	}
 	HVCF_CUDA(cudaMemcpyAsync(&ctx->h_total[frame], &ctx->d_global_index[frame], sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 	if (cells_bytes)
 		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells, cells_bytes, cudaMemcpyDeviceToHost, s));

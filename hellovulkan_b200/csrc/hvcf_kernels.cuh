@@ -221,6 +221,8 @@ cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, c
 	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream);
 cudaError_t launch_peer_wait(const PeerParams& p, const uint32_t* totals, uint32_t* frame_total, cudaStream_t stream);
 // force-load every kernel a frame can launch (see hvcf_kernels.cu: lazy loading vs kernels that spin on another shard)
+cudaError_t launch_grid_download(const void* cells, size_t cells_bytes, const uint32_t* indices, const uint32_t* total_ptr,
+	uint32_t index_capacity, uint32_t max_words, void* cells_dst, uint32_t* indices_dst, uint32_t* total_dst, uint32_t blocks, cudaStream_t stream);
 cudaError_t preload_basic_kernels();
 cudaError_t preload_hier_kernels();
 cudaError_t preload_bin_kernels();

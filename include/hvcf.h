@@ -214,7 +214,10 @@ HVCF_API int hvcf_download_light_indices(hvcf_ctx* ctx, void* dst, size_t bytes,
 HVCF_API int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void* stream);
 /* The whole result of a frame in one call: total + light cells, one synchronisation, then exactly `total` light indices
  * (what a host-side consumer of lightCells / lightIndices reads back; two synchronisations instead of three calls' three).
- * cells_bytes <= 8 x clusters; at most indices_capacity_bytes of indices are copied (HVCF_ERR_CAPACITY if total does not fit). */
+ * cells_bytes <= 8 x clusters; at most indices_capacity_bytes of indices are copied (HVCF_ERR_CAPACITY if total does not fit).
+ * When both destinations are pinned host memory (hvcf_host_alloc, cudaMallocHost), 16-byte aligned, one kernel reads the count on
+ * the device and stores count, cells and the first 4 MB of indices across PCIe itself: ONE synchronisation, no host round trip
+ * between "how many" and "copy them" (longer lists: the copy engine takes the rest).  HVCF_DOWNLOAD_KERNEL=0 switches it off. */
 HVCF_API int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t cells_bytes, void* indices_dst,
 	size_t indices_capacity_bytes, uint32_t* out_total, void* stream);
 HVCF_API int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream);

@@ -379,3 +379,41 @@ def test_download_grid_in_one_call(hv, oracle):
         t = ctypes.c_uint32()
         rc = ctx.lib.hvcf_download_grid(ctx.handle, 0, cells.ctypes.data, cells.nbytes, small.ctypes.data, small.nbytes, ctypes.byref(t), None)
         assert rc == -4 and t.value == total          # HVCF_ERR_CAPACITY, the total is still reported
+
+
+@pytest.mark.parametrize("n", [0, 1, 5000, 70_000])
+def test_download_grid_into_pinned_memory_uses_one_kernel_and_gives_the_same_bytes(hv, oracle, monkeypatch, n):
+    """pinned destinations: count, cells and indices[0, count) are stored across PCIe by grid_download_kernel (no host round
+    trip for the count); pageable destinations and HVCF_DOWNLOAD_KERNEL=0 take the two-copy path.  Same bytes either way."""
+    import ctypes
+    grid, screen = GRIDS["A"]
+    C = grid[0] * grid[1] * grid[2]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=29)
+    got = {}
+    for sw in ("1:4", "1:1", "1:0", "0:4"):   # kernel on/off : MB of indices the kernel may store (the copy engine takes the rest)
+        monkeypatch.setenv("HVCF_DOWNLOAD_KERNEL", sw[0])
+        monkeypatch.setenv("HVCF_DOWNLOAD_KERNEL_MAX_MB", sw[2])
+        with hv.Context(grid=grid, max_lights=max(n, 1)) as ctx:
+            ctx.set_lights(lights)
+            ctx.set_ubo(0, ubo)
+            ctx.cull(0)
+            want_cells, want_idx, want_total = ctx.download_grid(0)     # pageable numpy destinations
+            ch, ih = hv.PinnedBuffer(8 * C), hv.PinnedBuffer(4 * C * 150)
+            ih.array[:] = 0xAB
+            t = ctypes.c_uint32(0xFFFFFFFF)
+            rc = ctx.lib.hvcf_download_grid(ctx.handle, 0, ch.ptr, 8 * C, ih.ptr, 4 * C * 150, ctypes.byref(t), None)
+            assert rc == 0 and t.value == want_total
+            assert ch.array.tobytes() == want_cells.tobytes()
+            assert ih.array[: 4 * want_total].tobytes() == want_idx.tobytes()
+            assert (ih.array[4 * want_total: 4 * want_total + 64] == 0xAB).all()     # nothing past the count is touched
+            if want_total > 8:
+                small = hv.PinnedBuffer(32)
+                small.array[:] = 0xCD
+                rc = ctx.lib.hvcf_download_grid(ctx.handle, 0, ch.ptr, 8 * C, small.ptr, 32, ctypes.byref(t), None)
+                assert rc == -4 and t.value == want_total and (small.array == 0xCD).all()
+                small.close()
+            got[sw] = (ch.array.tobytes(), ih.array[: 4 * want_total].tobytes(), want_total)
+            ch.close(), ih.close()
+    assert got["0:4"] == got["1:4"] == got["1:1"] == got["1:0"]
+    assert n < 70_000 or got["1:1"][2] > (1 << 18)   # the 1 MB case really splits the list
