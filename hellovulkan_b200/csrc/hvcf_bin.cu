@@ -167,6 +167,12 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // write pass 57 -> 77 us with 2 segments per program; A65k and A1M within +-1 us.
 // Also rejected: exact "owns output" flags per (segment, warp program) set by hier_finalize_kernel instead of the count pass's
 // "counted anything" word -- B1M write pass 57.3 -> 55.8 us but finalize 25.5 -> 28.6 us: almost every program that counted owns output.
+// Also rejected (profiles/r01zh_l2_pairs_rejected.txt, "default" = this variant): level 2 on candidate PAIRS -- the batch's level-1
+// survivors compacted in light order into (x0 x1 y0 y1)(z0 z1 r0 r1) records and tested two per trip with sphere_box_hit2
+// (12.5 instead of 24 instructions per candidate).  Byte-identical (205 GPU tests), but a batch of 64 survivor records holds
+// only ~5 level-2 candidates on average, so the compaction (scattered STS, per-block masks in compacted order) costs more than
+// the halved tests save, and the loop-invariant (lo, lo) / (hi, hi) register pairs cost occupancy: A65k 0.0521 -> 0.0541 ms,
+// A1M 0.130 -> 0.137, B1M 0.216 -> 0.237 (count pass 98 -> 115 us).
 __device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
 
 template <int K, bool WRITE, bool LISTS>
