@@ -173,6 +173,10 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // only ~5 level-2 candidates on average, so the compaction (scattered STS, per-block masks in compacted order) costs more than
 // the halved tests save, and the loop-invariant (lo, lo) / (hi, hi) register pairs cost occupancy: A65k 0.0521 -> 0.0541 ms,
 // A1M 0.130 -> 0.137, B1M 0.216 -> 0.237 (count pass 98 -> 115 us).
+// Also rejected (profiles/r01zi_early_loads_rejected.txt, "default" = this variant): the lane's cluster indices and boxes loaded
+// ABOVE griddepcontrol.wait (they are not written inside the frame's PDL chain; it takes ld.volatile to keep ptxas from sinking
+// the loads below ACQBULK).  No gain at A65k / A1M, B1M 0.215 -> 0.219 ms: the warp programs that leave right after the wait
+// (nothing counted, empty slots) now pay for loads they never use.
 __device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
 
 template <int K, bool WRITE, bool LISTS>
