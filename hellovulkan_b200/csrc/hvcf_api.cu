@@ -90,6 +90,8 @@ struct hvcf_ctx
 	uint32_t download_max_words = 1u << 20;  // HVCF_DOWNLOAD_KERNEL_MAX_MB (4): indices beyond this go through the copy engine
 	const void* dl_ptr[2] = {nullptr, nullptr};
 	bool dl_ok[2] = {false, false};
+	int pipe_mode = -1;                      // HVCF_BATCH_PIPE: -1 = by tiles per segment, 0 = never, 1 = always
+	uint32_t pipe_min_tps = 16;              // HVCF_PIPE_MIN_TPS
 	uint32_t xbin_max_lights = 0;            // HVCF_XBIN_MAX: frames with at most this many lights fuse transform + binning (0 = never)
 	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
 	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
@@ -269,6 +271,8 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.tiles_total = ctx->h_tiles_total;
 	p.tiles_per_seg = ctx->h_tiles_per_seg;
 	p.num_segs = ctx->h_num_segs;
+	// long segments walk many slots per warp program: pipelined variant (measured: wins at 32 tiles per segment, loses at 4)
+	p.pipe = ctx->pipe_mode >= 0 ? (ctx->pipe_mode ? 1u : 0u) : (ctx->h_tiles_per_seg >= ctx->pipe_min_tps ? 1u : 0u);
 	p.seg_begin = 0;
 	p.seg_end = ctx->h_num_segs;
 	p.cap = ctx->cap;
@@ -407,6 +411,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		// two-level level-0 binning (HVCF_BIN2=0/1 forces it off/on; otherwise chosen per frame, see hier_range)
 		c->bin2_mode = env_int("HVCF_BIN2", -1);
 		c->xbin_max_lights = static_cast<uint32_t>(env_int("HVCF_XBIN_MAX", 262144));
+		c->pipe_mode = env_int("HVCF_BATCH_PIPE", -1);
+		c->pipe_min_tps = static_cast<uint32_t>(env_int("HVCF_PIPE_MIN_TPS", 16));
 		if (!c->hier_v1 && c->bin2_mode != 0)
 		{
 			c->bin_sg = (c->hp.ncb + 31) / 32 > 8 ? (c->hp.ncb + 31) / 32 : 8;

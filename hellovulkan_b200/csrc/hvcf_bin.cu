@@ -179,11 +179,27 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // (nothing counted, empty slots) now pay for loads they never use.
 __device__ __forceinline__ size_t any_slot(uint32_t seg, uint32_t unit) { return static_cast<size_t>(seg) * (gridDim.x * kMainWarps) + unit; }
 
-template <int K, bool WRITE, bool LISTS>
+// 16-byte asynchronous copy global -> shared (SASS LDGSTS); src_bytes < 16 zero-fills the rest
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, uint32_t src_bytes)
+{
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src),
+		"r"(src_bytes)
+		: "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+	asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// PIPE: the walk over the survivor slots is software-pipelined (cp.async double buffer, see below); chosen by the host for frames
+// with many tiles per light segment
+template <int K, bool WRITE, bool LISTS, bool PIPE>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
-	__shared__ __align__(16) float4 s_rec[kMainWarps][64];
-	__shared__ uint16_t s_idx[kMainWarps][64];
+	__shared__ __align__(16) float4 s_rec2[kMainWarps][PIPE ? 2 : 1][64];
+	__shared__ __align__(16) uint16_t s_idx2[kMainWarps][PIPE ? 2 : 1][64];
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t seg = p.seg_begin + blockIdx.y;
 	const uint32_t unit = blockIdx.x * kMainWarps + warp;
@@ -338,8 +354,213 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 
 	unsigned long long n_l1 = 0, n_l2 = 0; // warp-uniform test counters (lane tests)
 	const size_t desc0 = static_cast<size_t>(cb) * p.tiles_cap + t_begin;
-	float4* const my_rec = s_rec[warp];
-	uint16_t* const my_idx = s_idx[warp];
+	float4* const my_rec = s_rec2[warp][0];
+	uint16_t* const my_idx = s_idx2[warp][0];
+	// one batch of up to 64 records in ascending light order: r0 = record of lane, r1 = record of 32 + lane.  `staged`: the
+	// records (and, where indices are needed, their tile indices) already sit in rec / idxs in exactly that order.
+	auto batch = [&](const float4& r0, const float4& r1, uint32_t id0, uint32_t id1, uint32_t tile_base, float4* rec, uint16_t* idxs,
+		bool staged) {
+		// ---- level 1: lane = light, against the union box of each block -----------------------------
+		uint32_t mlo[K], mhi[K];
+		uint32_t any = 0;
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+		{
+			mlo[k] = mhi[k] = 0;
+			if (alive[k])
+			{
+				mlo[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r0.x, r0.y, r0.z, r0.w, ulo[k], uhi[k]));
+				mhi[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r1.x, r1.y, r1.z, r1.w, ulo[k], uhi[k]));
+				n_l1 += 64;
+				any |= mlo[k] | mhi[k];
+			}
+		}
+		if (any == 0)
+			return;
+		if (!staged)
+		{
+			__syncwarp(); // the previous batch's broadcasts are done (and, for a raw batch, every lane has read its pair)
+			rec[lane] = r0;
+			rec[32 + lane] = r1;
+			idxs[lane] = static_cast<uint16_t>(id0);
+			idxs[32 + lane] = static_cast<uint16_t>(id1);
+			__syncwarp();
+		}
+		// ---- level 2: lane = cluster, candidates broadcast from the slab -----------------------------
+		warp_done = true;
+#pragma unroll
+		for (int k = 0; k < K; ++k)
+		{
+			if (alive[k] == 0)
+				continue;
+			n_l2 += 32u * (__popc(mlo[k]) + __popc(mhi[k]));
+#pragma unroll
+			for (uint32_t half = 0; half < 2; ++half)
+			{
+				uint32_t m = half ? mhi[k] : mlo[k];
+				// kCand candidates per trip while the mask holds that many: a trip is latency-bound (LDS -> 6-deep
+				// FP chain), so independent chains are free; the remainder goes one by one
+				while (__popc(m) >= static_cast<int>(kCand))
+				{
+					uint32_t j[kCand];
+					float4 c[kCand];
+#pragma unroll
+					for (uint32_t q = 0; q < kCand; ++q)
+					{
+						j[q] = half * 32 + __ffs(m) - 1;
+						m &= m - 1;
+						c[q] = rec[j[q]]; // broadcast
+					}
+#pragma unroll
+					for (uint32_t q = 0; q < kCand; ++q)
+					{
+						const bool hit = sphere_box_hit(c[q].x, c[q].y, c[q].z, c[q].w, lo[k], hi[k]) && active[k];
+						if (WRITE)
+						{
+							if (hit && cnt[k] < limit[k])
+							{
+								p.indices[wbase[k] + cnt[k]] = tile_base + idxs[j[q]];
+								++cnt[k];
+							}
+						}
+						else
+						{
+							if (LISTS && hit && cnt[k] < limit[k])
+								p.seg_lists[lbase[k] + cnt[k]] = tile_base + idxs[j[q]];
+							cnt[k] += hit ? 1u : 0u;
+						}
+					}
+				}
+				while (m)
+				{
+					const uint32_t j = half * 32 + __ffs(m) - 1;
+					m &= m - 1;
+					const float4 c = rec[j]; // broadcast
+					const bool hit = sphere_box_hit(c.x, c.y, c.z, c.w, lo[k], hi[k]) && active[k];
+					if (WRITE)
+					{
+						if (hit && cnt[k] < limit[k])
+						{
+							p.indices[wbase[k] + cnt[k]] = tile_base + idxs[j];
+							++cnt[k];
+						}
+					}
+					else
+					{
+						if (LISTS && hit && cnt[k] < limit[k])
+							p.seg_lists[lbase[k] + cnt[k]] = tile_base + idxs[j];
+						cnt[k] += hit ? 1u : 0u;
+					}
+				}
+			}
+			// early exit per lane: a cluster that holds its quota leaves the block's union box, so the remaining
+			// lanes see fewer candidates; a block with no lane left is finished
+			const uint32_t now_alive = __ballot_sync(0xffffffffu, active[k] && cnt[k] < limit[k]);
+			if (now_alive != alive[k])
+			{
+				alive[k] = now_alive;
+				active[k] = (now_alive >> lane) & 1u;
+				if (now_alive && !blk_nan[k])
+				{
+#pragma unroll
+					for (int a = 0; a < 3; ++a)
+					{
+						ulo[k][a] = warp_min_f(active[k] ? lo[k][a] : kInf);
+						uhi[k][a] = warp_max_f(active[k] ? hi[k][a] : -kInf);
+					}
+				}
+			}
+			warp_done = warp_done && alive[k] == 0;
+		}
+	};
+	// ---- the walk, software-pipelined: while batch i is tested, batch i + 1 (the next 64 records of the slot, or the first
+	// batch of the next non-empty tile) is already on its way into the other shared-memory buffer (cp.async, SASS LDGSTS: no
+	// registers held).  Measured on B200 (profiles/r01zj): grid C x 16M lights on one GPU, 32 tiles per segment, 3.63 -> 3.23 ms
+	// per frame; no change at 1-2 tiles per segment (A65k, A1M) and a loss at 4 (B1M 0.215 -> 0.223 ms: 12 registers more, and
+	// most slots there hold a single batch) -- hence a template parameter, set by the host from the tiles per segment.
+	if constexpr (PIPE)
+	{
+		uint32_t it_t = 0, it_b = 0, it_n0 = 0, it_nb = 0; // the batch to FETCH next: tile inside the segment, batch, slot count, batches
+		uint32_t cnt_chunk = 0xffffffffu, my_cnt = 0;
+		auto seek = [&]() -> bool { // first non-empty tile at or after it_t
+			for (; it_t < ntiles; ++it_t)
+			{
+				if ((it_t >> 5) != cnt_chunk)
+				{
+					cnt_chunk = it_t >> 5;
+					my_cnt = cnt_chunk * 32 + lane < ntiles ? __ldg(&p.bin_count[desc0 + cnt_chunk * 32 + lane]) : 0u;
+				}
+				it_n0 = __shfl_sync(0xffffffffu, my_cnt, it_t & 31u);
+				if (it_n0)
+				{
+					it_nb = it_n0 > kBinCap ? kTileGroups : (it_n0 + 63) / 64;
+					it_b = 0;
+					return true;
+				}
+			}
+			return false;
+		};
+		auto fetch = [&](uint32_t buf) { // batch (it_t, it_b) -> buffer buf
+			float4* const rec = s_rec2[warp][buf];
+			const uint32_t tile_id = t_begin + it_t;
+			if (it_n0 > kBinCap) // raw tile: the lane's packed pair, converted when it is consumed
+			{
+				const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16) + it_b * 64;
+				cp_async16(rec + lane, lv + lane, 16u);
+				cp_async16(rec + 32 + lane, lv + 32 + lane, 16u);
+			}
+			else
+			{
+				const size_t slot = (desc0 + it_t) * kBinCap;
+				const uint32_t i0 = it_b * 64 + lane, i1 = i0 + 32;
+				// beyond the slot's count: zero fill = (0, 0, 0, r2 = 0), and no squared distance is < 0
+				cp_async16(rec + lane, p.bin_rec + slot + (i0 < it_n0 ? i0 : 0u), i0 < it_n0 ? 16u : 0u);
+				cp_async16(rec + 32 + lane, p.bin_rec + slot + (i1 < it_n0 ? i1 : 0u), i1 < it_n0 ? 16u : 0u);
+				if ((WRITE || LISTS) && lane < 8) // 64 tile indices = 8 x 16 B (slots are whole: reading past the count is in bounds)
+					cp_async16(reinterpret_cast<uint4*>(s_idx2[warp][buf]) + lane, reinterpret_cast<const uint4*>(p.bin_idx + slot + it_b * 64) + lane, 16u);
+			}
+			cp_async_commit();
+		};
+		bool have = !warp_done && seek();
+		uint32_t cur = 0;
+		if (have)
+			fetch(0);
+		while (have && !warp_done)
+		{
+			const uint32_t c_t = it_t, c_b = it_b;
+			const bool c_raw = it_n0 > kBinCap;
+			bool have_next = true;
+			if (++it_b >= it_nb)
+			{
+				++it_t;
+				have_next = seek();
+			}
+			__syncwarp(); // everyone is done with the buffer the next batch goes into
+			if (have_next)
+			{
+				fetch(cur ^ 1u);
+				cp_async_wait<1>();
+			}
+			else
+				cp_async_wait<0>();
+			__syncwarp();
+			float4* const rec = s_rec2[warp][cur];
+			uint16_t* const idxs = s_idx2[warp][cur];
+			const uint32_t tile_base = (t_begin + c_t) * kTileLights;
+			if (c_raw)
+			{
+				const float4 a = rec[lane], b = rec[32 + lane];
+				batch(make_float4(a.x, a.z, b.x, b.z), make_float4(a.y, a.w, b.y, b.w), c_b * 64 + lane, c_b * 64 + 32 + lane, tile_base, rec, idxs, false);
+			}
+			else
+				batch(rec[lane], rec[32 + lane], 0u, 0u, tile_base, rec, idxs, true);
+			cur ^= 1u;
+			have = have_next;
+		}
+		cp_async_wait<0>();
+	}
+	else
+	{
 	for (uint32_t tb = 0; tb < ntiles && !warp_done; tb += 32)
 	{
 		// survivor counts of the next 32 tiles in one coalesced load
@@ -386,117 +607,10 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 						id1 = __ldg(p.bin_idx + slot + i1);
 					}
 				}
-				// ---- level 1: lane = light, against the union box of each block -----------------------------
-				uint32_t mlo[K], mhi[K];
-				uint32_t any = 0;
-#pragma unroll
-				for (int k = 0; k < K; ++k)
-				{
-					mlo[k] = mhi[k] = 0;
-					if (alive[k])
-					{
-						mlo[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r0.x, r0.y, r0.z, r0.w, ulo[k], uhi[k]));
-						mhi[k] = __ballot_sync(0xffffffffu, sphere_box_hit(r1.x, r1.y, r1.z, r1.w, ulo[k], uhi[k]));
-						n_l1 += 64;
-						any |= mlo[k] | mhi[k];
-					}
-				}
-				if (any == 0)
-					continue;
-				__syncwarp(); // the previous batch's broadcasts are done
-				my_rec[lane] = r0;
-				my_rec[32 + lane] = r1;
-				my_idx[lane] = static_cast<uint16_t>(id0);
-				my_idx[32 + lane] = static_cast<uint16_t>(id1);
-				__syncwarp();
-				// ---- level 2: lane = cluster, candidates broadcast from the slab -----------------------------
-				warp_done = true;
-#pragma unroll
-				for (int k = 0; k < K; ++k)
-				{
-					if (alive[k] == 0)
-						continue;
-					n_l2 += 32u * (__popc(mlo[k]) + __popc(mhi[k]));
-#pragma unroll
-					for (uint32_t half = 0; half < 2; ++half)
-					{
-						uint32_t m = half ? mhi[k] : mlo[k];
-						// kCand candidates per trip while the mask holds that many: a trip is latency-bound (LDS -> 6-deep
-						// FP chain), so independent chains are free; the remainder goes one by one
-						while (__popc(m) >= static_cast<int>(kCand))
-						{
-							uint32_t j[kCand];
-							float4 c[kCand];
-#pragma unroll
-							for (uint32_t q = 0; q < kCand; ++q)
-							{
-								j[q] = half * 32 + __ffs(m) - 1;
-								m &= m - 1;
-								c[q] = my_rec[j[q]]; // broadcast
-							}
-#pragma unroll
-							for (uint32_t q = 0; q < kCand; ++q)
-							{
-								const bool hit = sphere_box_hit(c[q].x, c[q].y, c[q].z, c[q].w, lo[k], hi[k]) && active[k];
-								if (WRITE)
-								{
-									if (hit && cnt[k] < limit[k])
-									{
-										p.indices[wbase[k] + cnt[k]] = tile_base + my_idx[j[q]];
-										++cnt[k];
-									}
-								}
-								else
-								{
-									if (LISTS && hit && cnt[k] < limit[k])
-										p.seg_lists[lbase[k] + cnt[k]] = tile_base + my_idx[j[q]];
-									cnt[k] += hit ? 1u : 0u;
-								}
-							}
-						}
-						while (m)
-						{
-							const uint32_t j = half * 32 + __ffs(m) - 1;
-							m &= m - 1;
-							const float4 c = my_rec[j]; // broadcast
-							const bool hit = sphere_box_hit(c.x, c.y, c.z, c.w, lo[k], hi[k]) && active[k];
-							if (WRITE)
-							{
-								if (hit && cnt[k] < limit[k])
-								{
-									p.indices[wbase[k] + cnt[k]] = tile_base + my_idx[j];
-									++cnt[k];
-								}
-							}
-							else
-							{
-								if (LISTS && hit && cnt[k] < limit[k])
-									p.seg_lists[lbase[k] + cnt[k]] = tile_base + my_idx[j];
-								cnt[k] += hit ? 1u : 0u;
-							}
-						}
-					}
-					// early exit per lane: a cluster that holds its quota leaves the block's union box, so the remaining
-					// lanes see fewer candidates; a block with no lane left is finished
-					const uint32_t now_alive = __ballot_sync(0xffffffffu, active[k] && cnt[k] < limit[k]);
-					if (now_alive != alive[k])
-					{
-						alive[k] = now_alive;
-						active[k] = (now_alive >> lane) & 1u;
-						if (now_alive && !blk_nan[k])
-						{
-#pragma unroll
-							for (int a = 0; a < 3; ++a)
-							{
-								ulo[k][a] = warp_min_f(active[k] ? lo[k][a] : kInf);
-								uhi[k][a] = warp_max_f(active[k] ? hi[k][a] : -kInf);
-							}
-						}
-					}
-					warp_done = warp_done && alive[k] == 0;
-				}
+				batch(r0, r1, id0, id1, tile_base, my_rec, my_idx, false);
 			}
 		}
+	}
 	}
 	if (!WRITE)
 	{
@@ -879,7 +993,7 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
-template <int K, bool WRITE, bool LISTS>
+template <int K, bool WRITE, bool LISTS, bool PIPE>
 static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 {
 	cudaLaunchConfig_t cfg{};
@@ -889,7 +1003,7 @@ static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS>, p);
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE>, p);
 }
 
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
@@ -897,17 +1011,24 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
 		return cudaSuccess;
 	const bool lists = !write && p.seg_lists != nullptr;
-	switch (K * 4 + (write ? 1 : 0) + (lists ? 2 : 0))
+	const bool pipe = p.pipe != 0 && !lists;
+	switch (K * 8 + (write ? 1 : 0) + (lists ? 2 : 0) + (pipe ? 4 : 0))
 	{
-	case 4: return launch_hier2_t<1, false, false>(p, stream);
-	case 5: return launch_hier2_t<1, true, false>(p, stream);
-	case 6: return launch_hier2_t<1, false, true>(p, stream);
-	case 8: return launch_hier2_t<2, false, false>(p, stream);
-	case 9: return launch_hier2_t<2, true, false>(p, stream);
-	case 10: return launch_hier2_t<2, false, true>(p, stream);
-	case 16: return launch_hier2_t<4, false, false>(p, stream);
-	case 17: return launch_hier2_t<4, true, false>(p, stream);
-	case 18: return launch_hier2_t<4, false, true>(p, stream);
+	case 8: return launch_hier2_t<1, false, false, false>(p, stream);
+	case 9: return launch_hier2_t<1, true, false, false>(p, stream);
+	case 10: return launch_hier2_t<1, false, true, false>(p, stream);
+	case 12: return launch_hier2_t<1, false, false, true>(p, stream);
+	case 13: return launch_hier2_t<1, true, false, true>(p, stream);
+	case 16: return launch_hier2_t<2, false, false, false>(p, stream);
+	case 17: return launch_hier2_t<2, true, false, false>(p, stream);
+	case 18: return launch_hier2_t<2, false, true, false>(p, stream);
+	case 20: return launch_hier2_t<2, false, false, true>(p, stream);
+	case 21: return launch_hier2_t<2, true, false, true>(p, stream);
+	case 32: return launch_hier2_t<4, false, false, false>(p, stream);
+	case 33: return launch_hier2_t<4, true, false, false>(p, stream);
+	case 34: return launch_hier2_t<4, false, true, false>(p, stream);
+	case 36: return launch_hier2_t<4, false, false, true>(p, stream);
+	case 37: return launch_hier2_t<4, true, false, true>(p, stream);
 	default: return cudaErrorInvalidValue;
 	}
 }
@@ -922,15 +1043,21 @@ cudaError_t preload_bin_kernels()
 	HVCF_PRELOAD(hier_bin_kernel);
 	HVCF_PRELOAD(hier_bin2_kernel);
 	HVCF_PRELOAD(hier_xbin_kernel);
-	HVCF_PRELOAD((hier2_kernel<1, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false>));
-	HVCF_PRELOAD((hier2_kernel<1, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false>));
-	HVCF_PRELOAD((hier2_kernel<2, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false>));
-	HVCF_PRELOAD((hier2_kernel<4, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, true, false>));
 	return cudaSuccess;
 }
 

@@ -88,6 +88,7 @@ struct HierPlan
 
 struct HierParams
 {
+	uint32_t pipe = 0;             // 1: software-pipelined slot walk (hier2_kernel<..., PIPE>)
 	const float4* lights_view;
 	const hvcf_aabb* aabbs;        // whole grid
 	const uint32_t* lane_cluster;  // [ncb * 8 * K][32] shard-local cluster index of each lane, 0xffffffff = none

@@ -326,6 +326,31 @@ def test_fused_and_split_transform_binning_give_identical_bytes(hv, oracle, monk
     assert ref[2] == b[2] and ref[0].tobytes() == b[0].tobytes() and ref[1].tobytes() == b[1].tobytes()
 
 
+@pytest.mark.parametrize("name,n,cap,z,tps", [("A", 70_000, 150, None, 0), ("A", 65_536, 150, None, 8), ("A", 3_000, 4, None, 0), ("B", 300_000, 150, None, 0),
+                                             ("B", 300_000, 150, None, 32), ("C", 150_000, 150, (40, 52), 16), ("A", 0, 150, None, 0),
+                                             ("A", 200_000, 4096, None, 16), ("A", 1, 150, None, 0)])
+def test_pipelined_and_plain_slot_walk_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap, z, tps):
+    """count / write pass with the survivor slots fetched one batch ahead by cp.async into a double buffer (hier2_kernel<..., PIPE>,
+    chosen by the host for long light segments; forced here) against the plain walk: same light cells and index buffer, equal to
+    brute force.  tps = tiles per light segment (0 = the plan's own); cap 4096 keeps dense slots (raw-tile batches) alive."""
+    grid, screen = GRIDS[name]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=31)
+    kw = {} if z is None else {"z_begin": z[0], "z_end": z[1]}
+    if tps:
+        monkeypatch.setenv("HVCF_HIER_TPS", str(tps))
+    out = {}
+    for sw in ("0", "1"):
+        monkeypatch.setenv("HVCF_BATCH_PIPE", sw)
+        out[sw] = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"], **kw)
+    monkeypatch.delenv("HVCF_BATCH_PIPE")
+    monkeypatch.delenv("HVCF_HIER_TPS", raising=False)
+    ref = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["brute"], **kw)
+    for sw in ("0", "1"):
+        assert out[sw][2] == ref[2], f"HVCF_BATCH_PIPE={sw}"
+        assert out[sw][0].tobytes() == ref[0].tobytes() and out[sw][1].tobytes() == ref[1].tobytes(), f"HVCF_BATCH_PIPE={sw}"
+
+
 def test_stats_are_split_per_kernel(hv, oracle):
     """hvcf_stats: the binning kernel's tests are a part of prefilter_tests, the write pass's repeats are counted apart, and the
     count pass's exact tests equal the oracle's executed-test count rounded up to what a tile-granular early exit runs"""
