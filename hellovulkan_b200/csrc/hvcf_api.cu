@@ -69,6 +69,9 @@ struct hvcf_ctx
 	bool hier = false;
 	HierPlan hp{};
 	uint32_t h_max_segs = 0, h_max_chunks = 0;
+	uint32_t h_plan_max_segs = 0;            // most whole-tile segments the plan may use
+	uint32_t h_parts_cfg = 0, h_parts = 1;   // HVCF_HIER_PARTS (0 = auto); parts per tile of this frame (1 unless every segment is one tile)
+	uint32_t h_pipe = 0;                     // this frame walks its slots with the pipelined kernels
 	int h_tps_override = 0;
 	uint32_t h_split_head = 0;
 	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
@@ -271,8 +274,9 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.tiles_total = ctx->h_tiles_total;
 	p.tiles_per_seg = ctx->h_tiles_per_seg;
 	p.num_segs = ctx->h_num_segs;
+	p.parts = ctx->h_parts;
 	// long segments walk many slots per warp program: pipelined variant (measured: wins at 32 tiles per segment, loses at 4)
-	p.pipe = ctx->pipe_mode >= 0 ? (ctx->pipe_mode ? 1u : 0u) : (ctx->h_tiles_per_seg >= ctx->pipe_min_tps ? 1u : 0u);
+	p.pipe = ctx->h_pipe;
 	p.seg_begin = 0;
 	p.seg_end = ctx->h_num_segs;
 	p.cap = ctx->cap;
@@ -401,7 +405,14 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		// 0.240 -> 0.339 ms (twice the warp-program prologues)
 		uint32_t seg_limit = static_cast<uint32_t>(env_int("HVCF_HIER_MAX_SEGS", 512));
 		seg_limit = seg_limit < 1 ? 1 : (seg_limit > 2048 ? 2048 : seg_limit);
-		c->h_max_segs = max_tiles < seg_limit ? max_tiles : seg_limit;
+		c->h_plan_max_segs = max_tiles < seg_limit ? max_tiles : seg_limit;
+		// frames of few tiles cut every tile into light segments of a part of its survivor slot (hier2_kernel): measured on B200,
+		// grid A x 65,536 lights
+		{
+			const int parts = env_int("HVCF_HIER_PARTS", 0); // 0 = by the number of tiles
+			c->h_parts_cfg = static_cast<uint32_t>(parts < 0 ? 0 : (parts > static_cast<int>(kHMaxParts) ? static_cast<int>(kHMaxParts) : parts));
+		}
+		c->h_max_segs = static_cast<uint64_t>(max_tiles) * kHMaxParts < seg_limit ? max_tiles * kHMaxParts : seg_limit;
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
 		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));
@@ -796,7 +807,23 @@ static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* wh
 		const uint32_t n = ctx->num_lights;
 		const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
 		const uint32_t tiles_total = padded / kTileLights;
-		hier_plan_lights(ctx->hp, tiles_total, ctx->h_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
+		hier_plan_lights(ctx->hp, tiles_total, ctx->h_plan_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
+		ctx->h_pipe = ctx->pipe_mode >= 0 ? (ctx->pipe_mode ? 1u : 0u) : (ctx->h_tiles_per_seg >= ctx->pipe_min_tps ? 1u : 0u);
+		// sub-tile segments: about 128 light segments per frame (measured: 64 tiles x 2 parts 0.0516 -> 0.0478 ms, x 4 0.0506;
+		// 1 tile x 8 parts 0.0347 -> 0.0252 ms), at most kHMaxParts per tile; HVCF_HIER_PARTS fixes the number (1 = off)
+		ctx->h_parts = 1;
+		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe)
+		{
+			uint32_t parts = ctx->h_parts_cfg ? ctx->h_parts_cfg : 128u / ctx->h_num_segs;
+			parts = parts > kHMaxParts ? kHMaxParts : parts;
+			while (parts > 1 && static_cast<uint64_t>(ctx->h_num_segs) * parts > ctx->h_max_segs)
+				--parts;
+			if (parts > 1)
+			{
+				ctx->h_parts = parts;
+				ctx->h_num_segs *= parts;
+			}
+		}
 		ctx->h_tiles_total = tiles_total;
 		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
 			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);

@@ -204,7 +204,16 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	const uint32_t seg = p.seg_begin + blockIdx.y;
 	const uint32_t unit = blockIdx.x * kMainWarps + warp;
 	const uint32_t cb = unit >> 3;
-	const uint32_t t_begin = seg * p.tiles_per_seg;
+	// sub-tile segments (frames of few tiles): segment = (tile, part); part q of P takes the batches [q nb / P, (q + 1) nb / P) of
+	// the tile's slot (nb = its batches of 64 records).  Slots are in light order, so segments still are; the dense slots'
+	// serial walks -- the tail of the count pass at grid A x 65,536 lights, profiles/r01zl -- are cut into P shorter ones.
+	const uint32_t parts = p.parts;
+	uint32_t part = 0, t_begin = seg * p.tiles_per_seg;
+	if (parts > 1)
+	{
+		part = seg % parts;
+		t_begin = seg / parts; // one tile per segment
+	}
 	const uint32_t t_end = min(t_begin + p.tiles_per_seg, p.tiles_total);
 	const uint32_t ntiles = t_end - t_begin;
 	grid_dep_launch();
@@ -227,8 +236,15 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	{
 		const size_t d0 = static_cast<size_t>(cb) * p.tiles_cap + t_begin;
 		uint32_t some = 0;
-		for (uint32_t t = lane; t < ntiles; t += 32)
-			some |= __ldg(&p.bin_count[d0 + t]);
+		if (parts > 1)
+		{
+			const uint32_t n0 = __ldg(&p.bin_count[d0]);
+			const uint32_t nb = n0 > kBinCap ? kTileGroups : (n0 + 63) / 64;
+			some = (part + 1) * nb / parts > part * nb / parts ? 1u : 0u;
+		}
+		else
+			for (uint32_t t = lane; t < ntiles; t += 32)
+				some |= __ldg(&p.bin_count[d0 + t]);
 		if (!__any_sync(0xffffffffu, some != 0))
 		{
 #pragma unroll
@@ -578,7 +594,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			const uint32_t nb = raw ? kTileGroups : (n0 + 63) / 64;
 			const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16);
 			const size_t slot = (desc0 + tb + ti) * kBinCap;
-			for (uint32_t bi = 0; bi < nb && !warp_done; ++bi)
+			uint32_t b_begin = 0, b_end = nb;
+			if (parts > 1) // (the division stays off the path of whole-tile segments)
+			{
+				b_begin = part * nb / parts;
+				b_end = (part + 1) * nb / parts;
+			}
+			for (uint32_t bi = b_begin; bi < b_end && !warp_done; ++bi)
 			{
 				// ---- a batch of up to 64 lights in ascending order: records r0 (lane) and r1 (32 + lane) ----
 				float4 r0, r1;

@@ -86,8 +86,10 @@ struct HierPlan
 	uint32_t ncb;             // CTAs per light segment
 };
 
+constexpr uint32_t kHMaxParts = 8;   // most sub-tile light segments per tile
 struct HierParams
 {
+	uint32_t parts = 1;            // > 1 (only with one tile per segment): a tile's survivor slot is cut into `parts` batch ranges, one light segment each
 	uint32_t pipe = 0;             // 1: software-pipelined slot walk (hier2_kernel<..., PIPE>)
 	const float4* lights_view;
 	const hvcf_aabb* aabbs;        // whole grid

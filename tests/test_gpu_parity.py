@@ -351,6 +351,23 @@ def test_pipelined_and_plain_slot_walk_give_identical_bytes(hv, oracle, monkeypa
         assert out[sw][0].tobytes() == ref[0].tobytes() and out[sw][1].tobytes() == ref[1].tobytes(), f"HVCF_BATCH_PIPE={sw}"
 
 
+@pytest.mark.parametrize("name,n,cap", [("A", 70_000, 150), ("A", 65_536, 150), ("A", 1, 150), ("A", 0, 150), ("A", 3_000, 4), ("B", 100_000, 150),
+                                        ("A", 40_000, 4096), ("A", 200_000, 150)])
+def test_sub_tile_light_segments_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap):
+    """frames of few tiles cut each tile's survivor slot into HVCF_HIER_PARTS batch ranges, one light segment each (shorter serial
+    walks in the dense cluster groups): same light cells and index buffer for 1, 2, 3, 4 and 8 parts, equal to brute force"""
+    grid, screen = GRIDS[name]
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=37)
+    ref = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["brute"])
+    for parts in ("1", "2", "3", "4", "8"):
+        monkeypatch.setenv("HVCF_HIER_PARTS", parts)
+        got = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"])
+        assert got[2] == ref[2], f"HVCF_HIER_PARTS={parts}"
+        assert got[0].tobytes() == ref[0].tobytes() and got[1].tobytes() == ref[1].tobytes(), f"HVCF_HIER_PARTS={parts}"
+    monkeypatch.delenv("HVCF_HIER_PARTS")
+
+
 def test_stats_are_split_per_kernel(hv, oracle):
     """hvcf_stats: the binning kernel's tests are a part of prefilter_tests, the write pass's repeats are counted apart, and the
     count pass's exact tests equal the oracle's executed-test count rounded up to what a tile-granular early exit runs"""
