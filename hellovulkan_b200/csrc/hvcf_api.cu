@@ -812,7 +812,7 @@ static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* wh
 		// sub-tile segments: about 128 light segments per frame (measured: 64 tiles x 2 parts 0.0516 -> 0.0478 ms, x 4 0.0506;
 		// 1 tile x 8 parts 0.0347 -> 0.0252 ms), at most kHMaxParts per tile; HVCF_HIER_PARTS fixes the number (1 = off)
 		ctx->h_parts = 1;
-		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe)
+		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe && !ctx->d_hseg_lists)
 		{
 			uint32_t parts = ctx->h_parts_cfg ? ctx->h_parts_cfg : 128u / ctx->h_num_segs;
 			parts = parts > kHMaxParts ? kHMaxParts : parts;

@@ -195,7 +195,8 @@ __device__ __forceinline__ void cp_async_wait()
 
 // PIPE: the walk over the survivor slots is software-pipelined (cp.async double buffer, see below); chosen by the host for frames
 // with many tiles per light segment
-template <int K, bool WRITE, bool LISTS, bool PIPE>
+// SUB: sub-tile light segments (p.parts > 1); a template parameter so that whole-tile frames run exactly the code they ran before
+template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
 	__shared__ __align__(16) float4 s_rec2[kMainWarps][PIPE ? 2 : 1][64];
@@ -207,7 +208,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// sub-tile segments (frames of few tiles): segment = (tile, part); part q of P takes the batches [q nb / P, (q + 1) nb / P) of
 	// the tile's slot (nb = its batches of 64 records).  Slots are in light order, so segments still are; the dense slots'
 	// serial walks -- the tail of the count pass at grid A x 65,536 lights, profiles/r01zl -- are cut into P shorter ones.
-	const uint32_t parts = p.parts;
+	const uint32_t parts = SUB ? p.parts : 1u;
 	uint32_t part = 0, t_begin = seg * p.tiles_per_seg;
 	if (parts > 1)
 	{
@@ -1015,7 +1016,7 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
-template <int K, bool WRITE, bool LISTS, bool PIPE>
+template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB>
 static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 {
 	cudaLaunchConfig_t cfg{};
@@ -1025,7 +1026,7 @@ static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE>, p);
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE, SUB>, p);
 }
 
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
@@ -1033,24 +1034,33 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
 		return cudaSuccess;
 	const bool lists = !write && p.seg_lists != nullptr;
+	const bool sub = p.parts > 1;
+	if (sub && (lists || p.pipe != 0))
+		return cudaErrorInvalidValue; // the host keeps sub-tile segments to the plain walk
 	const bool pipe = p.pipe != 0 && !lists;
-	switch (K * 8 + (write ? 1 : 0) + (lists ? 2 : 0) + (pipe ? 4 : 0))
+	switch (K * 16 + (write ? 1 : 0) + (lists ? 2 : 0) + (pipe ? 4 : 0) + (sub ? 8 : 0))
 	{
-	case 8: return launch_hier2_t<1, false, false, false>(p, stream);
-	case 9: return launch_hier2_t<1, true, false, false>(p, stream);
-	case 10: return launch_hier2_t<1, false, true, false>(p, stream);
-	case 12: return launch_hier2_t<1, false, false, true>(p, stream);
-	case 13: return launch_hier2_t<1, true, false, true>(p, stream);
-	case 16: return launch_hier2_t<2, false, false, false>(p, stream);
-	case 17: return launch_hier2_t<2, true, false, false>(p, stream);
-	case 18: return launch_hier2_t<2, false, true, false>(p, stream);
-	case 20: return launch_hier2_t<2, false, false, true>(p, stream);
-	case 21: return launch_hier2_t<2, true, false, true>(p, stream);
-	case 32: return launch_hier2_t<4, false, false, false>(p, stream);
-	case 33: return launch_hier2_t<4, true, false, false>(p, stream);
-	case 34: return launch_hier2_t<4, false, true, false>(p, stream);
-	case 36: return launch_hier2_t<4, false, false, true>(p, stream);
-	case 37: return launch_hier2_t<4, true, false, true>(p, stream);
+	case 16: return launch_hier2_t<1, false, false, false, false>(p, stream);
+	case 20: return launch_hier2_t<1, false, false, true, false>(p, stream);
+	case 24: return launch_hier2_t<1, false, false, false, true>(p, stream);
+	case 17: return launch_hier2_t<1, true, false, false, false>(p, stream);
+	case 21: return launch_hier2_t<1, true, false, true, false>(p, stream);
+	case 25: return launch_hier2_t<1, true, false, false, true>(p, stream);
+	case 18: return launch_hier2_t<1, false, true, false, false>(p, stream);
+	case 32: return launch_hier2_t<2, false, false, false, false>(p, stream);
+	case 36: return launch_hier2_t<2, false, false, true, false>(p, stream);
+	case 40: return launch_hier2_t<2, false, false, false, true>(p, stream);
+	case 33: return launch_hier2_t<2, true, false, false, false>(p, stream);
+	case 37: return launch_hier2_t<2, true, false, true, false>(p, stream);
+	case 41: return launch_hier2_t<2, true, false, false, true>(p, stream);
+	case 34: return launch_hier2_t<2, false, true, false, false>(p, stream);
+	case 64: return launch_hier2_t<4, false, false, false, false>(p, stream);
+	case 68: return launch_hier2_t<4, false, false, true, false>(p, stream);
+	case 72: return launch_hier2_t<4, false, false, false, true>(p, stream);
+	case 65: return launch_hier2_t<4, true, false, false, false>(p, stream);
+	case 69: return launch_hier2_t<4, true, false, true, false>(p, stream);
+	case 73: return launch_hier2_t<4, true, false, false, true>(p, stream);
+	case 66: return launch_hier2_t<4, false, true, false, false>(p, stream);
 	default: return cudaErrorInvalidValue;
 	}
 }
@@ -1065,21 +1075,27 @@ cudaError_t preload_bin_kernels()
 	HVCF_PRELOAD(hier_bin_kernel);
 	HVCF_PRELOAD(hier_bin2_kernel);
 	HVCF_PRELOAD(hier_xbin_kernel);
-	HVCF_PRELOAD((hier2_kernel<1, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, false, true, false>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, false, true, false>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, false, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, true, false, false>));
 	return cudaSuccess;
 }
 
