@@ -91,8 +91,6 @@ struct hvcf_ctx
 	bool download_kernel = true;             // HVCF_DOWNLOAD_KERNEL: hvcf_download_grid into pinned memory with one kernel
 	uint32_t download_blocks = 64;           // HVCF_DOWNLOAD_BLOCKS
 	uint32_t download_max_words = 1u << 20;  // HVCF_DOWNLOAD_KERNEL_MAX_MB (4): indices beyond this go through the copy engine
-	const void* dl_ptr[2] = {nullptr, nullptr};
-	bool dl_ok[2] = {false, false};
 	int pipe_mode = -1;                      // HVCF_BATCH_PIPE: -1 = by tiles per segment, 0 = never, 1 = always
 	uint32_t pipe_min_tps = 16;              // HVCF_PIPE_MIN_TPS
 	uint32_t xbin_max_lights = 0;            // HVCF_XBIN_MAX: frames with at most this many lights fuse transform + binning (0 = never)
@@ -1506,19 +1504,15 @@ int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void
 		"hvcf_download_total");
 }
 
-// is p pinned host memory the device can store to at the same address?  (the last answer per destination is remembered:
-// a frame loop downloads into the same buffers)
-static bool mapped_host_ptr(hvcf_ctx* ctx, int which, const void* p)
+// is p pinned host memory the device can store to at the same address?  Asked on every call (well under a microsecond): a
+// remembered answer would go stale when the caller frees a pinned buffer and pageable memory takes its address.
+static bool mapped_host_ptr(const void* p)
 {
 	if (!p || (reinterpret_cast<uintptr_t>(p) & 15u))
 		return false;
-	if (ctx->dl_ptr[which] == p)
-		return ctx->dl_ok[which];
 	cudaPointerAttributes a{};
-	bool ok = cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer == p;
+	const bool ok = cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer == p;
 	cudaGetLastError(); // unregistered memory is not an error here
-	ctx->dl_ptr[which] = p;
-	ctx->dl_ok[which] = ok;
 	return ok;
 }
 
@@ -1537,7 +1531,7 @@ int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t ce
 		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 8));
 	// both destinations in pinned (mapped) host memory, 16 B aligned: one kernel stores count, cells and indices[0, count)
 	// across PCIe -- no host round trip between "how many" and "copy them" (HVCF_DOWNLOAD_KERNEL=0: the two-copy path)
-	if (ctx->download_kernel && cells_bytes % 4 == 0 && mapped_host_ptr(ctx, 0, cells_dst) && (indices_capacity_bytes == 0 || mapped_host_ptr(ctx, 1, indices_dst)))
+	if (ctx->download_kernel && cells_bytes % 4 == 0 && mapped_host_ptr(cells_dst) && (indices_capacity_bytes == 0 || mapped_host_ptr(indices_dst)))
 	{
 		const size_t cap_words = indices_capacity_bytes / sizeof(uint32_t);
 		HVCF_CUDA(launch_grid_download(ctx->d_cells, cells_bytes, ctx->d_indices, &ctx->d_global_index[frame],
