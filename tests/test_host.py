@@ -115,5 +115,17 @@ def test_cull_kernels_have_no_contracted_fma():
             counts[fn] = 0
         elif fn and re.search(r"\bFFMA2?\b", line):
             counts[fn] += 1
-    cull = {k: v for k, v in counts.items() if "cull_kernel" in k or "light_transform" in k}
-    assert cull and all(v == 0 for v in cull.values()), cull
+    names = ("cull_kernel", "light_transform", "hier_xbin_kernel", "hier_bin_kernel", "hier_bin2_kernel", "hier2_kernel", "hier_kernel")
+    cull = {k: v for k, v in counts.items() if any(n in k for n in names)}
+    assert len(cull) >= 30 and all(v == 0 for v in cull.values()), {k: v for k, v in cull.items() if v}
+
+
+def test_sub_tile_segments_partition_every_slot_in_order():
+    """hier2_kernel<..., SUB>: part q of P takes the batches [q nb / P, (q + 1) nb / P) of a slot of nb batches -- the ranges of
+    q = 0 .. P-1 are disjoint, ascending and cover [0, nb) exactly (what keeps sub-tile light segments in light order)"""
+    for nb in range(0, 17):
+        for P in range(1, 9):
+            got = []
+            for q in range(P):
+                got += list(range(q * nb // P, (q + 1) * nb // P))
+            assert got == list(range(nb)), (nb, P)
