@@ -2,23 +2,21 @@
 // the reference's layouts, stages UBOs through pinned memory, and strings the kernels of
 // hvcf_kernels.cu together on the caller's stream.  No CPU fallback: every entry point fails with
 // HVCF_ERR_CUDA when no sm_100 device is usable.
-#include "../../include/hvcf.h"
+#include "hvcf_ctx.cuh"
 
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
-#include <cstdlib>
 #include <cstring>
 #include <new>
 
-#include "hvcf_kernels.cuh"
 #include "hvcf_shade.cuh"
 
 using namespace hvcf;
 
-namespace
+namespace hvcf
 {
-thread_local char g_last_error[512] = "";
+static thread_local char g_last_error[512] = "";
 
 int fail(int code, const char* fmt, ...)
 {
@@ -28,150 +26,7 @@ int fail(int code, const char* fmt, ...)
 	va_end(ap);
 	return code;
 }
-
-#define HVCF_CUDA(expr)                                                                                      \
-	do                                                                                                       \
-	{                                                                                                        \
-		cudaError_t e_ = (expr);                                                                             \
-		if (e_ != cudaSuccess)                                                                               \
-			return fail(e_ == cudaErrorMemoryAllocation ? HVCF_ERR_OUT_OF_MEMORY : HVCF_ERR_CUDA,            \
-				"%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_));                  \
-	} while (0)
-
-int env_int(const char* name, int dflt)
-{
-	const char* v = getenv(name);
-	return (v && *v) ? atoi(v) : dflt;
-}
-} // namespace
-
-constexpr uint32_t kBin2MinGroups = 48;
-
-struct hvcf_ctx
-{
-	hvcf_config cfg{};
-	int device = 0;
-	uint32_t X = 0, Y = 0, Z = 0;
-	uint32_t cluster_total = 0;  // whole grid
-	uint32_t cluster_begin = 0;  // shard [begin, end)
-	uint32_t cluster_end = 0;
-	uint32_t cluster_count = 0;  // shard size
-	uint32_t cap = 0;
-	uint32_t max_lights = 0;
-	uint32_t padded_capacity = 0; // max_lights rounded up to a tile
-	uint32_t frame_count = 0;
-	uint32_t num_lights = 0;
-	const hvcf_light_data* bound_lights = nullptr; // hvcf_bind_lights: external buffer, not owned
-	int variant = 1;
-	uint32_t max_segs = 1;
-	uint32_t count_blocks = 0;
-	// hierarchical mode
-	bool hier = false;
-	HierPlan hp{};
-	uint32_t h_max_segs = 0, h_max_chunks = 0;
-	uint32_t h_plan_max_segs = 0;            // most whole-tile segments the plan may use
-	uint32_t h_parts_cfg = 0, h_parts = 1;   // HVCF_HIER_PARTS (0 = auto); parts per tile of this frame (1 unless every segment is one tile)
-	uint32_t h_pipe = 0;                     // this frame walks its slots with the pipelined kernels
-	int h_tps_override = 0;
-	uint32_t h_split_head = 0;
-	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
-	uint32_t epoch = 0;
-	uint32_t* d_hseg_counts = nullptr;
-	uint32_t* d_hseg_prefix = nullptr;
-	uint32_t* d_hunit_any = nullptr;         // [h_max_segs][ncb * 8]
-	uint32_t* d_hseg_lists = nullptr;        // [h_max_segs][cluster_count][cap] hits of the count pass, or NULL: write pass instead
-	uint32_t* d_hscratch = nullptr;          // cum[cluster_count][kHMaxChunks]
-	uint32_t* d_hoffsets = nullptr;
-	uint32_t* d_hlane_cluster = nullptr;
-	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
-	float* d_cb_union = nullptr;             // [ncb][8]
-	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
-	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel only)
-	int bin2_mode = -1;                      // HVCF_BIN2: -1 = per frame by size, 0 = never, 1 = always
-	bool download_kernel = true;             // HVCF_DOWNLOAD_KERNEL: hvcf_download_grid into pinned memory with one kernel
-	uint32_t download_blocks = 64;           // HVCF_DOWNLOAD_BLOCKS
-	uint32_t download_max_words = 1u << 20;  // HVCF_DOWNLOAD_KERNEL_MAX_MB (4): indices beyond this go through the copy engine
-	int pipe_mode = -1;                      // HVCF_BATCH_PIPE: -1 = by tiles per segment, 0 = never, 1 = always
-	uint32_t pipe_min_tps = 16;              // HVCF_PIPE_MIN_TPS
-	uint32_t xbin_max_lights = 0;            // HVCF_XBIN_MAX: frames with at most this many lights fuse transform + binning (0 = never)
-	uint32_t* d_bin_count = nullptr;         // [ncb][tiles_cap]
-	float4* d_bin_rec = nullptr;             // [ncb][tiles_cap][kBinCap]
-	uint16_t* d_bin_idx = nullptr;
-	uint32_t tiles_cap = 0;
-	unsigned long long* d_scan_state = nullptr;
-	unsigned long long* d_trace = nullptr;   // HVCF_HIER_TRACE=1: per-CTA timestamps (debug)
-
-	// reference-layout buffers
-	hvcf_light_data* d_lights = nullptr;   // ResourcesLight::storageBuffer_
-	hvcf_aabb* d_aabb = nullptr;           // ResourcesClusterForward::aabbBuffer_
-	hvcf_light_cell* d_cells = nullptr;    // lightCellsBuffer_
-	uint32_t* d_indices = nullptr;         // lightIndicesBuffer_
-	uint32_t* d_global_index = nullptr;    // globalIndexCountBuffers_[frame]
-	hvcf_cluster_forward_ubo* d_ubo = nullptr; // cfUBOBuffers_[frame]
-	// library-internal
-	float4* d_lights_view = nullptr;
-	float* d_zplanes = nullptr;            // [frame][Z+1]
-	uint32_t* d_seg_counts = nullptr;
-	uint32_t* d_seg_lists = nullptr;
-	uint32_t* d_counts = nullptr;
-	uint32_t* d_block_sums = nullptr;
-	uint32_t* d_block_offsets = nullptr;
-	uint32_t* d_shard_total = nullptr;
-	DeviceStats* d_stats = nullptr;        // [frame]
-	// pinned staging
-	hvcf_cluster_forward_ubo* h_ubo = nullptr; // [frame]
-	float* h_zplanes = nullptr;                // [frame][Z+1]
-	uint32_t* h_total = nullptr;               // [8] pinned: hvcf_download_grid
-	hvcf_light_data* h_one_light = nullptr;    // hvcf_update_light staging ring
-	uint32_t one_light_cursor = 0;
-	cudaEvent_t one_light_events[16]{};
-
-	// device-side light animation (hvcf_set_light_animation) and batched position updates (hvcf_update_lights)
-	float* d_anim_table = nullptr;
-	float* d_base_y = nullptr;                 // [max_lights]
-	uint32_t anim_len = 0;                     // 0 = off
-	float anim_amplitude = 0.0f;
-	uint32_t anim_step[8]{};                   // per frame slot
-	uint32_t* d_upd_idx = nullptr;             // device staging of hvcf_update_lights
-	float* d_upd_xyz = nullptr;
-	uint32_t* h_upd_idx[2]{};                  // pinned, double-buffered
-	float* h_upd_xyz[2]{};
-	uint32_t upd_capacity = 0;
-	uint32_t upd_cursor = 0;
-	cudaEvent_t upd_events[2]{};
-
-	// consumer (hvcf_shade): z-slice thresholds in linear depth, per frame slot, built lazily
-	float* d_slice_thr = nullptr;              // [frame][Z+1]
-	float* h_slice_thr = nullptr;              // pinned
-	float slice_key[8][2]{};                   // sliceScaling, sliceBias of the table in the slot
-	bool slice_valid[8]{};
-
-	// exchange step of the sharded grid over peer memory (hvcf_peer.cu)
-	PeerParams peer{};                         // world == 0: not attached
-	PeerMailbox* d_mail = nullptr;
-	uint32_t* d_index_base = nullptr;
-	uint32_t* d_peer_totals = nullptr;         // [kMaxPeers]
-	bool peer_ipc = false;                     // peers were mapped with cudaIpcOpenMemHandle
-	uint32_t peer_epoch = 0;
-	uint32_t peer_frame = 0;                   // frame slot of the last hvcf_cull_begin
-	// hvcf_cull_begin_range progress of the open frame
-	bool range_open = false, range_cleared = false;
-	uint32_t range_frame = 0, range_transformed = 0, range_binned = 0; // lights (padded at the end) done so far
-	uint32_t open_launches = 0;
-
-	cudaEvent_t ubo_events[8]{};               // per frame slot: the staged UBO has been consumed
-	bool* ubo_set = nullptr;
-	bool aabb_dirty = true;
-	bool have_aabb_key = false;
-	float aabb_key[16 + 2]{}; // inverse projection + near/far of the last generated AABBs
-	uint32_t last_num_segs = 0;
-	uint32_t last_launches[8]{}; // per frame
-	bool timing = false;
-	bool ktimes = false;                 // HVCF_KERNEL_TIMES=1 (debug): an event after every kernel of the hierarchical frame
-	cudaEvent_t kev[8][8]{};             // [frame][begin, transform, bin, count, finalize, write]
-	cudaEvent_t ev[8][4]{}; // per frame: call begin, kernel begin, kernel end, call end
-	bool ev_valid[8]{};
-};
+} // namespace hvcf
 
 static void peer_unmap(hvcf_ctx* c)
 {
@@ -182,7 +37,11 @@ static void peer_unmap(hvcf_ctx* c)
 				cudaIpcCloseMemHandle(c->peer.cells[r]);
 				cudaIpcCloseMemHandle(c->peer.indices[r]);
 				cudaIpcCloseMemHandle(c->peer.mail[r]);
+				if (c->shard.inbox_peer[r])
+					cudaIpcCloseMemHandle(c->shard.inbox_peer[r]);
 			}
+	for (auto& q : c->shard.inbox_peer)
+		q = nullptr;
 	c->peer = PeerParams{};
 	c->peer_ipc = false;
 }
@@ -192,6 +51,7 @@ static void free_ctx(hvcf_ctx* c)
 	if (!c)
 		return;
 	peer_unmap(c);
+	hvcf_shard_free(c);
 	cudaFree(c->d_mail);
 	cudaFree(c->d_index_base);
 	cudaFree(c->d_peer_totals);
@@ -296,6 +156,15 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.tiles_cap = ctx->tiles_cap;
 	p.seg_lists = ctx->hier_v1 ? nullptr : ctx->d_hseg_lists;
 	p.unit_any = ctx->d_hunit_any;
+	if (ctx->routed_frame) // the tiles are this rank's inbox of the frame's parity
+	{
+		const ShardState& sh = ctx->shard;
+		unsigned char* box = sh.d_inbox + static_cast<size_t>(sh.epoch & 1u) * sh.parity_bytes;
+		p.lights_view = reinterpret_cast<const float4*>(box);
+		p.tile_ids = reinterpret_cast<const uint16_t*>(box + sh.off_idx);
+		p.tile_cnt = sh.d_tile_cnt;
+		p.tile_mask = ~(sh.block_tiles - 1u);
+	}
 	return p;
 }
 
@@ -753,6 +622,8 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		if (ctx->bin_ns)
 			HVCF_CUDA(launch_hier_super_unions(ctx->d_cb_union, ctx->hp.ncb, ctx->bin_sg, ctx->bin_ns, ctx->d_sb_union, s));
 	}
+	if (ctx->shard.on) // the level above the groups: union box of every rank's slab
+		HVCF_CUDA(launch_slab_unions(ctx->d_aabb, ctx->shard.d_ranges, ctx->shard.world, ctx->shard.d_slab_box, s));
 	memcpy(ctx->aabb_key, u.camera_inverse_projection, 64);
 	ctx->aabb_key[16] = u.camera_near;
 	ctx->aabb_key[17] = u.camera_far;
@@ -778,7 +649,7 @@ static cudaError_t hier_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t
 	return cudaEventRecord(ctx->kev[frame][i], s);
 }
 
-static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who)
+int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed)
 {
 	if (!ctx)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null context", who);
@@ -790,6 +661,7 @@ static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* wh
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	ctx->ev_valid[frame] = false;
 	ctx->open_launches = 0;
+	ctx->routed_frame = routed;
 	if (ctx->timing)
 		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][0], s));
 	if (ctx->aabb_dirty)
@@ -804,13 +676,13 @@ static int cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* wh
 		// at least one (all-padding) tile, so that pass 2 always writes the light cells
 		const uint32_t n = ctx->num_lights;
 		const uint32_t padded = round_up_u32(n ? n : 1, kTileLights);
-		const uint32_t tiles_total = padded / kTileLights;
+		const uint32_t tiles_total = routed ? ctx->shard.tiles_phys : padded / kTileLights; // routed: the tiles of the inbox
 		hier_plan_lights(ctx->hp, tiles_total, ctx->h_plan_max_segs, ctx->h_tps_override, &ctx->h_tiles_per_seg, &ctx->h_num_segs);
 		ctx->h_pipe = ctx->pipe_mode >= 0 ? (ctx->pipe_mode ? 1u : 0u) : (ctx->h_tiles_per_seg >= ctx->pipe_min_tps ? 1u : 0u);
 		// sub-tile segments: about 128 light segments per frame (measured: 64 tiles x 2 parts 0.0516 -> 0.0478 ms, x 4 0.0506;
 		// 1 tile x 8 parts 0.0347 -> 0.0252 ms), at most kHMaxParts per tile; HVCF_HIER_PARTS fixes the number (1 = off)
 		ctx->h_parts = 1;
-		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe && !ctx->d_hseg_lists)
+		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe && !ctx->d_hseg_lists && !routed)
 		{
 			uint32_t parts = ctx->h_parts_cfg ? ctx->h_parts_cfg : 128u / ctx->h_num_segs;
 			parts = parts > kHMaxParts ? kHMaxParts : parts;
@@ -929,7 +801,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 	return HVCF_OK;
 }
 
-static int hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
+int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
 {
 	DeviceStats* stats = &ctx->d_stats[frame];
 	HierParams p = hier_params(ctx, frame);
@@ -994,7 +866,7 @@ int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, u
 		((flags & HVCF_RANGE_TRANSFORM) ? ctx->range_transformed != 0 : ctx->range_binned != 0));
 	if (first)
 	{
-		const int rc = cull_open(ctx, frame, stream, "hvcf_cull_begin_range");
+		const int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin_range", false);
 		if (rc != HVCF_OK)
 			return rc;
 	}
@@ -1009,7 +881,7 @@ int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, u
 	if (rc != HVCF_OK)
 		return rc;
 	if ((flags & HVCF_RANGE_BIN) && light_end >= n)
-		return hier_close(ctx, frame, s);
+		return hvcf_hier_close(ctx, frame, s);
 	return HVCF_OK;
 }
 
@@ -1057,7 +929,7 @@ int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes
 
 int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 {
-	int rc = cull_open(ctx, frame, stream, "hvcf_cull_begin");
+	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin", false);
 	if (rc != HVCF_OK)
 		return rc;
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -1069,7 +941,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		rc = hier_range(ctx, frame, 0, n, ctx->hier_v1 ? HVCF_RANGE_TRANSFORM : (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN), s);
 		if (rc != HVCF_OK)
 			return rc;
-		return hier_close(ctx, frame, s);
+		return hvcf_hier_close(ctx, frame, s);
 	}
 	ctx->range_open = false;
 	HVCF_CUDA(cudaMemsetAsync(stats, 0, sizeof(DeviceStats), s)); // ResetGlobalIndex (PipelineLightCulling.cpp:38-43)
@@ -1214,7 +1086,7 @@ static int peer_alloc(hvcf_ctx* ctx)
 
 int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out)
 {
-	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "hvcf_peer_handle holds three 64-byte IPC handles");
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(hvcf_peer_handle) == 256, "hvcf_peer_handle holds four 64-byte IPC handles");
 	static_assert(HVCF_MAX_PEERS == kMaxPeers, "HVCF_MAX_PEERS");
 	if (!ctx || !out)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_export: null argument");
@@ -1224,6 +1096,9 @@ int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out)
 	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->cells), ctx->d_cells));
 	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->indices), ctx->d_indices));
 	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->mailbox), ctx->d_mail));
+	memset(out->inbox, 0, sizeof(out->inbox));
+	if (ctx->shard.on)
+		HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->inbox), ctx->shard.d_inbox));
 	return HVCF_OK;
 }
 
@@ -1240,6 +1115,10 @@ static int peer_check_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const
 	HVCF_CUDA(preload_hier_kernels());
 	HVCF_CUDA(preload_bin_kernels());
 	HVCF_CUDA(preload_peer_kernels());
+	HVCF_CUDA(preload_shard_kernels());
+	if (ctx->shard.on && (ctx->shard.world != world || ctx->shard.rank != rank))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: rank %u of %u, but the context was created as rank %u of %u", who, rank, world, ctx->shard.rank,
+			ctx->shard.world);
 	return peer_alloc(ctx);
 }
 
@@ -1260,9 +1139,10 @@ int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_pe
 			pp.mail[r] = ctx->d_mail;
 			continue;
 		}
-		void* ptr[3] = {nullptr, nullptr, nullptr};
-		const unsigned char* h[3] = {handles[r].cells, handles[r].indices, handles[r].mailbox};
-		for (int k = 0; k < 3; ++k)
+		void* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
+		const unsigned char* h[4] = {handles[r].cells, handles[r].indices, handles[r].mailbox, handles[r].inbox};
+		const int nh = ctx->shard.on ? 4 : 3;
+		for (int k = 0; k < nh; ++k)
 		{
 			cudaIpcMemHandle_t handle;
 			memcpy(&handle, h[k], sizeof(handle));
@@ -1277,6 +1157,9 @@ int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_pe
 						cudaIpcCloseMemHandle(pp.cells[q]);
 						cudaIpcCloseMemHandle(pp.indices[q]);
 						cudaIpcCloseMemHandle(pp.mail[q]);
+						if (ctx->shard.inbox_peer[q])
+							cudaIpcCloseMemHandle(ctx->shard.inbox_peer[q]);
+						ctx->shard.inbox_peer[q] = nullptr;
 					}
 				return fail(HVCF_ERR_CUDA, "hvcf_peer_attach: cudaIpcOpenMemHandle(rank %u, buffer %d): %s", r, k, cudaGetErrorString(e));
 			}
@@ -1284,10 +1167,14 @@ int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_pe
 		pp.cells[r] = static_cast<hvcf_light_cell*>(ptr[0]);
 		pp.indices[r] = static_cast<uint32_t*>(ptr[1]);
 		pp.mail[r] = static_cast<PeerMailbox*>(ptr[2]);
+		ctx->shard.inbox_peer[r] = static_cast<unsigned char*>(ptr[3]);
 	}
+	if (ctx->shard.on)
+		ctx->shard.inbox_peer[rank] = ctx->shard.d_inbox;
 	ctx->peer = pp;
 	ctx->peer_ipc = true;
 	ctx->peer_epoch = 0;
+	ctx->shard.epoch = 0;
 	return HVCF_OK;
 }
 
@@ -1324,10 +1211,17 @@ int hvcf_peer_attach_local(hvcf_ctx* ctx, uint32_t rank, uint32_t world, hvcf_ct
 		pp.cells[r] = o->d_cells;
 		pp.indices[r] = o->d_indices;
 		pp.mail[r] = o->d_mail;
+		if (ctx->shard.on)
+		{
+			if (!o->shard.on || o->shard.parity_bytes != ctx->shard.parity_bytes || o->shard.world != world)
+				return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] was not created with the same hvcf_shard_desc", r);
+			ctx->shard.inbox_peer[r] = o->shard.d_inbox;
+		}
 	}
 	ctx->peer = pp;
 	ctx->peer_ipc = false;
 	ctx->peer_epoch = 0;
+	ctx->shard.epoch = 0;
 	return HVCF_OK;
 }
 

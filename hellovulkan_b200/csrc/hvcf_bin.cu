@@ -196,7 +196,8 @@ __device__ __forceinline__ void cp_async_wait()
 // PIPE: the walk over the survivor slots is software-pipelined (cp.async double buffer, see below); chosen by the host for frames
 // with many tiles per light segment
 // SUB: sub-tile light segments (p.parts > 1); a template parameter so that whole-tile frames run exactly the code they ran before
-template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB>
+// INBOX: the tiles are inbox tiles of a routed frame (hvcf_shard.cu); a template parameter so that every other frame runs exactly the code it ran before
+template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB, bool INBOX = false>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
 	__shared__ __align__(16) float4 s_rec2[kMainWarps][PIPE ? 2 : 1][64];
@@ -240,7 +241,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		if (parts > 1)
 		{
 			const uint32_t n0 = __ldg(&p.bin_count[d0]);
-			const uint32_t nb = n0 > kBinCap ? kTileGroups : (n0 + 63) / 64;
+			const uint32_t nb = n0 > kBinCap ? (INBOX ? (__ldg(&p.tile_cnt[t_begin]) + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
 			some = (part + 1) * nb / parts > part * nb / parts ? 1u : 0u;
 		}
 		else
@@ -510,7 +511,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				it_n0 = __shfl_sync(0xffffffffu, my_cnt, it_t & 31u);
 				if (it_n0)
 				{
-					it_nb = it_n0 > kBinCap ? kTileGroups : (it_n0 + 63) / 64;
+					it_nb = it_n0 > kBinCap ? (INBOX ? (__ldg(&p.tile_cnt[t_begin + it_t]) + 63u) / 64u : kTileGroups) : (it_n0 + 63) / 64;
 					it_b = 0;
 					return true;
 				}
@@ -523,8 +524,20 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			if (it_n0 > kBinCap) // raw tile: the lane's packed pair, converted when it is consumed
 			{
 				const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16) + it_b * 64;
-				cp_async16(rec + lane, lv + lane, 16u);
-				cp_async16(rec + 32 + lane, lv + 32 + lane, 16u);
+				if constexpr (INBOX) // inbox tile: plain records, `valid` of them; zero fill = (0, 0, 0, r2 = 0) never hits
+				{
+					const uint32_t valid = __ldg(&p.tile_cnt[tile_id]), i0 = it_b * 64 + lane, i1 = i0 + 32;
+					cp_async16(rec + lane, lv + (i0 < valid ? lane : 0u), i0 < valid ? 16u : 0u);
+					cp_async16(rec + 32 + lane, lv + (i1 < valid ? 32 + lane : 0u), i1 < valid ? 16u : 0u);
+					if ((WRITE || LISTS) && lane < 8)
+						cp_async16(reinterpret_cast<uint4*>(s_idx2[warp][buf]) + lane,
+							reinterpret_cast<const uint4*>(p.tile_ids + static_cast<size_t>(tile_id) * kTileLights + it_b * 64) + lane, 16u);
+				}
+				else
+				{
+					cp_async16(rec + lane, lv + lane, 16u);
+					cp_async16(rec + 32 + lane, lv + 32 + lane, 16u);
+				}
 			}
 			else
 			{
@@ -563,8 +576,10 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			__syncwarp();
 			float4* const rec = s_rec2[warp][cur];
 			uint16_t* const idxs = s_idx2[warp][cur];
-			const uint32_t tile_base = (t_begin + c_t) * kTileLights;
-			if (c_raw)
+			const uint32_t tile_base = (INBOX ? ((t_begin + c_t) & p.tile_mask) : (t_begin + c_t)) * kTileLights;
+			if (INBOX && c_raw) // raw inbox tile: already plain records + their indices, as a slot batch
+				batch(rec[lane], rec[32 + lane], 0u, 0u, tile_base, rec, idxs, true);
+			else if (c_raw)
 			{
 				const float4 a = rec[lane], b = rec[32 + lane];
 				batch(make_float4(a.x, a.z, b.x, b.z), make_float4(a.y, a.w, b.y, b.w), c_b * 64 + lane, c_b * 64 + 32 + lane, tile_base, rec, idxs, false);
@@ -589,10 +604,11 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			if (n0 == 0)
 				continue;
 			const uint32_t tile_id = t_begin + tb + ti;
-			const uint32_t tile_base = tile_id * kTileLights;
+			const uint32_t tile_base = (INBOX ? (tile_id & p.tile_mask) : tile_id) * kTileLights;
 			// a slot that overflowed means the group's filter is not selective for this tile: read the raw tile
 			const bool raw = n0 > kBinCap;
-			const uint32_t nb = raw ? kTileGroups : (n0 + 63) / 64;
+			const uint32_t raw_valid = (INBOX && raw) ? __ldg(&p.tile_cnt[tile_id]) : kTileLights; // inbox tiles are partly filled
+			const uint32_t nb = raw ? (INBOX ? (raw_valid + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
 			const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16);
 			const size_t slot = (desc0 + tb + ti) * kBinCap;
 			uint32_t b_begin = 0, b_end = nb;
@@ -606,7 +622,24 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				// ---- a batch of up to 64 lights in ascending order: records r0 (lane) and r1 (32 + lane) ----
 				float4 r0, r1;
 				uint32_t id0, id1;
-				if (raw)
+				if (INBOX && raw) // inbox tile: plain records and their in-block indices
+				{
+					const uint32_t i0 = bi * 64 + lane, i1 = i0 + 32;
+					const uint16_t* const ids = p.tile_ids + static_cast<size_t>(tile_id) * kTileLights;
+					r0 = r1 = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+					id0 = id1 = 0;
+					if (i0 < raw_valid)
+					{
+						r0 = lv[i0];
+						id0 = ids[i0];
+					}
+					if (i1 < raw_valid)
+					{
+						r1 = lv[i1];
+						id1 = ids[i1];
+					}
+				}
+				else if (raw)
 				{
 					const float4 a = __ldg(lv + bi * 64 + lane), b = __ldg(lv + bi * 64 + 32 + lane);
 					r0 = make_float4(a.x, a.z, b.x, b.z);
@@ -719,12 +752,17 @@ __global__ void hier_super_unions_kernel(const float* __restrict__ cb_union, uin
 	sb_union[static_cast<size_t>(s) * 8 + c] = (c & 3) == 3 ? 0.0f : v;
 }
 
+// ROUTED (hvcf_shard.cu): the tile is a tile of this rank's INBOX -- up to 1,024 plain {x, y, z, r*r} records that the light
+// owners compacted in light order, `valid` of them in use -- and the slot's index of a record is the light's 16-bit index inside
+// its route block (in_idx), not its position.  Same two phases, same slots; an empty tile only zeroes its slot counts.
+template <bool ROUTED>
 __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinParams p)
 {
 	extern __shared__ __align__(128) unsigned char s_dyn[];
 	unsigned char* const s_tile = s_dyn;                                               // kTileBytes
 	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_dyn + kTileBytes);         // [ns][kTileLights]
 	uint32_t* const s_cnt = reinterpret_cast<uint32_t*>(s_list + static_cast<size_t>(p.ns) * kTileLights); // [ns]
+	uint16_t* const s_ids = reinterpret_cast<uint16_t*>(s_cnt + ((p.ns + 3u) & ~3u));  // ROUTED: [kTileLights]
 	__shared__ __align__(8) uint64_t bar;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t tile_id = p.tile_begin + blockIdx.x;
@@ -736,14 +774,40 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	}
 	__syncthreads();
 	grid_dep_wait(); // the tile is written by the transform kernel of this frame (or arrived from another rank)
+	uint32_t valid = kTileLights;
+	if constexpr (ROUTED)
+	{
+		const uint32_t in_block = (tile_id & (p.block_tiles - 1u)) * kTileLights;
+		const uint32_t c = p.in_cnt[tile_id / p.block_tiles];
+		valid = c > in_block ? min(c - in_block, kTileLights) : 0u;
+		if (threadIdx.x == 0)
+			p.tile_cnt[tile_id] = valid;
+		if (valid == 0u)
+		{
+			for (uint32_t cb = threadIdx.x; cb < p.ncb; cb += blockDim.x)
+				p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = 0u;
+			return;
+		}
+	}
 	if (threadIdx.x == 0)
 	{
-		mbar_arrive_expect_tx(&bar, kTileBytes);
-		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
+		if constexpr (ROUTED)
+		{
+			const uint32_t rec_bytes = valid * 16u, id_bytes = (valid * 2u + 15u) & ~15u;
+			mbar_arrive_expect_tx(&bar, rec_bytes + id_bytes);
+			bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, rec_bytes, &bar);
+			bulk_copy_g2s(s_ids, p.in_idx + static_cast<size_t>(tile_id) * kTileLights, id_bytes, &bar);
+		}
+		else
+		{
+			mbar_arrive_expect_tx(&bar, kTileBytes);
+			bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
+		}
 	}
 	mbar_wait(&bar, 0);
 	const float4* tile = reinterpret_cast<const float4*>(s_tile);
 	const uint32_t lt = lanemask_lt();
+	const uint32_t ngroups = ROUTED ? (valid + 63u) / 64u : kTileGroups;
 	unsigned long long tests = 0;
 
 	// ---- phase A: super-group survivor lists ----
@@ -755,11 +819,25 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
 		uint32_t cnt = 0;
 #pragma unroll 4
-		for (uint32_t g = 0; g < kTileGroups; ++g)
+		for (uint32_t g = 0; g < ngroups; ++g)
 		{
-			const float4 a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+			float4 a, b;
 			bool h0, h1;
-			sphere_box_hit2(a, b, lo, hi, h0, h1);
+			if constexpr (ROUTED)
+			{
+				// plain records of lights g * 64 + lane and g * 64 + 32 + lane, paired in registers into the packed operand shape
+				const float4 r0 = tile[g * 64 + lane], r1 = tile[g * 64 + 32 + lane];
+				a = make_float4(r0.x, r1.x, r0.y, r1.y);
+				b = make_float4(r0.z, r1.z, r0.w, r1.w);
+				sphere_box_hit2(a, b, lo, hi, h0, h1);
+				h0 = h0 && g * 64 + lane < valid;      // beyond the tile's records: whatever shared memory held
+				h1 = h1 && g * 64 + 32 + lane < valid;
+			}
+			else
+			{
+				a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+				sphere_box_hit2(a, b, lo, hi, h0, h1);
+			}
 			const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
 			if (h0)
 				list[cnt + __popc(m0 & lt)] = static_cast<uint16_t>(g * 64 + lane);
@@ -769,7 +847,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		}
 		if (lane == 0)
 			s_cnt[s] = cnt;
-		tests += kTileLights;
+		tests += ROUTED ? valid : kTileLights;
 	}
 	__syncthreads();
 
@@ -797,15 +875,31 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 			if (ia < ns)
 			{
 				ta = list[ia];
-				// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
-				const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
-				pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+				if constexpr (ROUTED)
+				{
+					const float4 r = tile[ta];
+					pa.x = r.x, pa.z = r.y, pb.x = r.z, pb.z = r.w;
+				}
+				else
+				{
+					// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
+					const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
+					pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+				}
 			}
 			if (ib < ns)
 			{
 				tb = list[ib];
-				const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
-				pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
+				if constexpr (ROUTED)
+				{
+					const float4 r = tile[tb];
+					pa.y = r.x, pa.w = r.y, pb.y = r.z, pb.w = r.w;
+				}
+				else
+				{
+					const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
+					pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
+				}
 			}
 			bool h0, h1;
 			sphere_box_hit2(pa, pb, lo, hi, h0, h1);
@@ -816,12 +910,12 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 				if (h0 && d0 < kBinCap)
 				{
 					rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
-					idx[d0] = static_cast<uint16_t>(ta);
+					idx[d0] = ROUTED ? s_ids[ta] : static_cast<uint16_t>(ta);
 				}
 				if (h1 && d1 < kBinCap)
 				{
 					rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
-					idx[d1] = static_cast<uint16_t>(tb);
+					idx[d1] = ROUTED ? s_ids[tb] : static_cast<uint16_t>(tb);
 				}
 				cnt += __popc(m0) + __popc(m1);
 			}
@@ -976,18 +1070,24 @@ cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32
 	return cudaGetLastError();
 }
 
-size_t hier_bin2_smem_bytes(uint32_t ns) { return kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) + static_cast<size_t>(ns) * sizeof(uint32_t); }
+size_t hier_bin2_smem_bytes(uint32_t ns, bool routed)
+{
+	return kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) + static_cast<size_t>((ns + 3u) & ~3u) * sizeof(uint32_t) +
+		(routed ? kTileLights * sizeof(uint16_t) : 0);
+}
 
 static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStream_t stream)
 {
-	const size_t smem = hier_bin2_smem_bytes(p.ns);
-	static size_t configured = 0;
-	if (smem > configured)
+	const bool routed = p.in_idx != nullptr;
+	const size_t smem = hier_bin2_smem_bytes(p.ns, routed);
+	static size_t configured[2] = {0, 0};
+	if (smem > configured[routed])
 	{
-		cudaError_t e = cudaFuncSetAttribute(hier_bin2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+		cudaError_t e = routed ? cudaFuncSetAttribute(hier_bin2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))
+			: cudaFuncSetAttribute(hier_bin2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 		if (e != cudaSuccess)
 			return e;
-		configured = smem;
+		configured[routed] = smem;
 	}
 	cudaLaunchConfig_t cfg{};
 	cfg.gridDim = dim3(tiles, 1, 1);
@@ -997,7 +1097,7 @@ static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStre
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier_bin2_kernel, p);
+	return routed ? cudaLaunchKernelEx(&cfg, hier_bin2_kernel<true>, p) : cudaLaunchKernelEx(&cfg, hier_bin2_kernel<false>, p);
 }
 
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream)
@@ -1016,7 +1116,7 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
-template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB>
+template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB, bool INBOX = false>
 static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 {
 	cudaLaunchConfig_t cfg{};
@@ -1026,7 +1126,7 @@ static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE, SUB>, p);
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE, SUB, INBOX>, p);
 }
 
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
@@ -1038,6 +1138,27 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 	if (sub && (lists || p.pipe != 0))
 		return cudaErrorInvalidValue; // the host keeps sub-tile segments to the plain walk
 	const bool pipe = p.pipe != 0 && !lists;
+	if (p.tile_ids) // routed frame: whole-tile segments, write pass
+	{
+		if (sub || lists)
+			return cudaErrorInvalidValue;
+		switch (K * 4 + (write ? 1 : 0) + (pipe ? 2 : 0))
+		{
+		case 4: return launch_hier2_t<1, false, false, false, false, true>(p, stream);
+		case 5: return launch_hier2_t<1, true, false, false, false, true>(p, stream);
+		case 6: return launch_hier2_t<1, false, false, true, false, true>(p, stream);
+		case 7: return launch_hier2_t<1, true, false, true, false, true>(p, stream);
+		case 8: return launch_hier2_t<2, false, false, false, false, true>(p, stream);
+		case 9: return launch_hier2_t<2, true, false, false, false, true>(p, stream);
+		case 10: return launch_hier2_t<2, false, false, true, false, true>(p, stream);
+		case 11: return launch_hier2_t<2, true, false, true, false, true>(p, stream);
+		case 16: return launch_hier2_t<4, false, false, false, false, true>(p, stream);
+		case 17: return launch_hier2_t<4, true, false, false, false, true>(p, stream);
+		case 18: return launch_hier2_t<4, false, false, true, false, true>(p, stream);
+		case 19: return launch_hier2_t<4, true, false, true, false, true>(p, stream);
+		default: return cudaErrorInvalidValue;
+		}
+	}
 	switch (K * 16 + (write ? 1 : 0) + (lists ? 2 : 0) + (pipe ? 4 : 0) + (sub ? 8 : 0))
 	{
 	case 16: return launch_hier2_t<1, false, false, false, false>(p, stream);
@@ -1073,7 +1194,8 @@ cudaError_t preload_bin_kernels()
 	HVCF_PRELOAD(hier_unions_kernel);
 	HVCF_PRELOAD(hier_super_unions_kernel);
 	HVCF_PRELOAD(hier_bin_kernel);
-	HVCF_PRELOAD(hier_bin2_kernel);
+	HVCF_PRELOAD(hier_bin2_kernel<false>);
+	HVCF_PRELOAD(hier_bin2_kernel<true>);
 	HVCF_PRELOAD(hier_xbin_kernel);
 	HVCF_PRELOAD((hier2_kernel<1, false, false, false, false>));
 	HVCF_PRELOAD((hier2_kernel<1, false, false, true, false>));
@@ -1096,6 +1218,18 @@ cudaError_t preload_bin_kernels()
 	HVCF_PRELOAD((hier2_kernel<4, true, false, true, false>));
 	HVCF_PRELOAD((hier2_kernel<4, true, false, false, true>));
 	HVCF_PRELOAD((hier2_kernel<4, false, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, false, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, true, false, true>));
 	return cudaSuccess;
 }
 

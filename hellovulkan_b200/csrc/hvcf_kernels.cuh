@@ -119,6 +119,12 @@ struct HierParams
 	uint32_t tiles_cap;
 	uint32_t* seg_lists;           // [num_segs][cluster_count][cap] hits of the count pass in light order, or NULL (write pass instead)
 	uint32_t* unit_any;            // [num_segs][ncb * 8] count pass: did this warp program count any hit?  The write pass leaves at once if not
+	// routed frames (hvcf_shard.cu): the tiles are this rank's INBOX -- plain {x, y, z, r*r} records that the light owners
+	// compacted block by block -- instead of the packed view cache of all lights.  A light's index is then
+	//   (tile & tile_mask) * 1024 + tile_ids[tile][position]      (first light of the owner's block + index inside the block).
+	uint32_t tile_mask = 0xffffffffu; // ~(tiles per route block - 1); all ones = every tile starts at tile * 1024
+	const uint16_t* tile_ids = nullptr; // [tiles][1024] or NULL: lights_view is the packed cache and position = index inside the tile
+	const uint32_t* tile_cnt = nullptr; // [tiles] valid records of an inbox tile (written by the routed binning kernel)
 };
 
 #ifndef HVCF_BIN_CAP
@@ -141,6 +147,11 @@ struct BinParams
 	const float* sb_union;         // [ns][8] union boxes of the super-groups
 	uint32_t sg;                   // groups per super-group
 	uint32_t ns;                   // super-groups, at most 32
+	// routed variant (hier_bin2_kernel<true>): the tile is an inbox tile of plain records, partly filled
+	const uint16_t* in_idx = nullptr; // [tiles][1024] index of the record's light inside its route block
+	const uint32_t* in_cnt = nullptr; // [tiles / block_tiles] records of each route block
+	uint32_t block_tiles = 1;         // tiles per route block (power of two)
+	uint32_t* tile_cnt = nullptr;     // [tiles] out: valid records of the tile
 };
 
 struct FinalizeParams
@@ -198,7 +209,7 @@ struct XBinParams
 };
 cudaError_t launch_hier_xbin(const XBinParams& q, uint32_t tiles, cudaStream_t stream);
 cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream);
-size_t hier_bin2_smem_bytes(uint32_t ns);
+size_t hier_bin2_smem_bytes(uint32_t ns, bool routed = false);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
 // ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------
@@ -209,6 +220,9 @@ struct PeerMailbox
 	unsigned long long arrived[kMaxPeers];   // [rank] = epoch << 32 once that rank's cells + indices are in OUR buffers
 	unsigned int done;                       // CTA counter of our own push kernel
 	unsigned int error;                      // 1 = a wait timed out
+	unsigned long long routed[2][kMaxPeers]; // [frame parity][rank] = epoch << 32 once that rank's share of the lights is in OUR inbox
+	unsigned int route_done;                 // CTA counter of our own route kernel
+	unsigned int pad_;
 };
 struct PeerParams
 {
@@ -218,6 +232,31 @@ struct PeerParams
 	uint32_t world, rank;
 	uint32_t epoch;                          // sharded-frame serial, > 0, the same on every rank
 };
+// ---- lights owned in shards: transform + slab test + route into the owning ranks' inboxes (hvcf_shard.cu) ----
+constexpr uint32_t kMaxRouteBlockTiles = 16;
+struct RouteParams
+{
+	const hvcf_cluster_forward_ubo* ubo;
+	const hvcf_light_data* lights;    // the rank's light buffer, indexed by GLOBAL light index
+	uint32_t light_end;               // owned lights end here (<= the total); they begin at block0 * block_tiles * 1024
+	uint32_t block_tiles;             // B: tiles per route block, power of two <= kMaxRouteBlockTiles
+	uint32_t block0, blocks;          // first route block of this rank (global numbering), own blocks
+	uint32_t world, rank, epoch, parity;
+	const float* slab_box;            // [world][8] union box of every rank's cluster slab { lo.xyz, 0, hi.xyz, 0 }
+	float4* rec[kMaxPeers];           // every rank's inbox of this frame parity: [tiles][1024] records,
+	uint16_t* idx[kMaxPeers];         //   [tiles][1024] in-block light indices,
+	uint32_t* cnt[kMaxPeers];         //   [blocks] records per route block
+	PeerMailbox* mail[kMaxPeers];
+	uint32_t* zero;                   // early-exit counters of the own frame to clear (the route kernel is the frame's first)
+	uint32_t zero_words;
+	DeviceStats* stats;
+};
+cudaError_t launch_shard_route(const RouteParams& p, cudaStream_t stream);
+cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream);
+// union box of each rank's cluster range [begin[r], end[r]) of the whole-grid AABB buffer
+cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges, uint32_t world, float* slab_box, cudaStream_t stream);
+cudaError_t preload_shard_kernels();
+
 cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total, uint32_t* index_base, uint32_t* totals_out,
 	cudaStream_t stream);
 cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, uint32_t cluster_begin,

@@ -1,0 +1,289 @@
+// hvcf_shard.cu -- the 2-D decomposition of the sharded grid: clusters sharded by z-slab AND lights owned in shards.
+//
+// The reference is single-GPU.  With clusters sharded by z-slab, a rank needs only the lights whose
+// sphere touches its slab (LightCulling.comp:49-57 against the union of the slab's boxes).  So instead of delivering every
+// light to every rank (a broadcast from one root, or an all-gather), rank r OWNS the LightData of a contiguous range of
+// lights, and per frame
+//   shard_route_kernel        transforms its own lights to view space ONCE (LightCulling.comp:51-53 hoisted), tests each
+//                             against the N slab union boxes (N tests per light -- the level above the cluster groups of the
+//                             hierarchy) and stores every survivor's 16 B view record + 16-bit index straight into the owning
+//                             rank's INBOX over NVLink peer memory.  Survivors are compacted in light order, one route block
+//                             (B tiles of 1,024 lights) per CTA, into a fixed-capacity region per (block, destination): no
+//                             size exchange, no atomics, and regions in block order = ascending light index.  The last CTA
+//                             raises the rank's "routed" flag on every peer (release, system scope).
+//   shard_wait_routed_kernel  waits until every rank's share has arrived (bounded; a missing peer is an error code).
+// The owner then runs level-0 binning on its inbox only (hier_bin2_kernel<true>), and the count / write passes walk the
+// survivor slots as before; a light's index is (first light of its route block) + (16-bit index inside the block).
+//
+// Exactness: the slab box contains every cluster box of the slab and the test is the same monotone uncontracted float sequence
+// (sphere_box_hit), so routing can only deliver more lights than a slab needs, never fewer (hvcf_hier.cu header).  Light order
+// is never disturbed, so each cluster still gets the first <= cap hits in ascending light index (LightCulling.comp:71-77).
+#include "hvcf_hier.cuh"
+
+namespace hvcf
+{
+
+constexpr uint32_t kRouteWarps = 8;
+constexpr unsigned long long kRouteTimeoutNs = 4000000000ull; // 4 s, as in hvcf_peer.cu
+
+__device__ __forceinline__ unsigned long long shard_ld_acquire_sys(const unsigned long long* p)
+{
+	unsigned long long v;
+	asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void shard_st_release_sys(unsigned long long* p, unsigned long long v)
+{
+	asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ======================================================================================================
+// union box of every rank's cluster range; runs when the AABBs change.  One CTA per rank.
+// layout as cb_union: { lo.xyz, 0, hi.xyz, 0 }; a range holding a NaN box passes everything.
+// ======================================================================================================
+__global__ void __launch_bounds__(256) slab_unions_kernel(const hvcf_aabb* __restrict__ aabbs, const uint32_t* __restrict__ ranges,
+	float* __restrict__ slab_box)
+{
+	__shared__ float s_u[8][6];
+	__shared__ int s_nan;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const float kInf = __int_as_float(0x7f800000);
+	const uint32_t begin = ranges[2 * blockIdx.x], end = ranges[2 * blockIdx.x + 1];
+	if (threadIdx.x == 0)
+		s_nan = 0;
+	__syncthreads();
+	float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+	bool nan = false;
+	for (uint32_t c = begin + threadIdx.x; c < end; c += blockDim.x)
+	{
+		const float4* a = reinterpret_cast<const float4*>(aabbs + c);
+		const float4 mn = a[0], mx = a[1];
+		nan = nan || !(mn.x == mn.x && mn.y == mn.y && mn.z == mn.z && mx.x == mx.x && mx.y == mx.y && mx.z == mx.z);
+		lo[0] = fminf(lo[0], mn.x), lo[1] = fminf(lo[1], mn.y), lo[2] = fminf(lo[2], mn.z);
+		hi[0] = fmaxf(hi[0], mx.x), hi[1] = fmaxf(hi[1], mx.y), hi[2] = fmaxf(hi[2], mx.z);
+	}
+	if (__any_sync(0xffffffffu, nan) && lane == 0)
+		s_nan = 1;
+#pragma unroll
+	for (int i = 0; i < 3; ++i)
+	{
+		lo[i] = warp_min_f(lo[i]);
+		hi[i] = warp_max_f(hi[i]);
+	}
+	if (lane == 0)
+	{
+		s_u[warp][0] = lo[0], s_u[warp][1] = lo[1], s_u[warp][2] = lo[2];
+		s_u[warp][3] = hi[0], s_u[warp][4] = hi[1], s_u[warp][5] = hi[2];
+	}
+	__syncthreads();
+	if (threadIdx.x < 3)
+	{
+		float l = kInf, h = -kInf;
+		for (int w = 0; w < 8; ++w)
+		{
+			l = fminf(l, s_u[w][threadIdx.x]);
+			h = fmaxf(h, s_u[w][3 + threadIdx.x]);
+		}
+		float* u = slab_box + static_cast<size_t>(blockIdx.x) * 8;
+		u[threadIdx.x] = s_nan ? -kInf : l;
+		u[4 + threadIdx.x] = s_nan ? kInf : h;
+		if (threadIdx.x == 0)
+			u[3] = u[7] = 0.0f;
+	}
+}
+
+// ======================================================================================================
+// transform + slab test + route.  One CTA of 8 warps per route block of B tiles; per tile, warp w owns the 128 consecutive
+// lights [w * 128, w * 128 + 128) as four rounds of 32 (lane = light), so (warp, round, lane) order = light order.
+// Per tile and destination: warp totals -> shared memory -> each warp's first position = running count of the block
+// + totals of the warps before it; survivors are stored at consecutive positions (16 B records: full 32 B sectors on the
+// wire wherever two neighbours survive).
+// ======================================================================================================
+__global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const RouteParams p)
+{
+	__shared__ float s_box[kMaxPeers][6];
+	__shared__ uint32_t s_wt[2][kRouteWarps][kMaxPeers];
+	__shared__ uint32_t s_run[kMaxPeers];
+	__shared__ bool s_last;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	// the first kernel of the frame also clears the early-exit counters and the work counters (ResetGlobalIndex,
+	// PipelineLightCulling.cpp:38-43, is part of that); its own test count is a product, stored rather than accumulated
+	{
+		const uint32_t nthreads = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
+		for (uint32_t i = tid; i < p.zero_words; i += nthreads)
+			p.zero[i] = 0u;
+		if (tid == 0 && p.stats)
+		{
+			DeviceStats* st = p.stats;
+			const uint32_t first = p.block0 * p.block_tiles * kTileLights;
+			st->executed_tests = 0ull;
+			st->total_indices = 0u;
+			st->overflow_clusters = 0u;
+			st->write_tests = 0ull;
+			st->bin_tests = st->prefilter_tests = static_cast<unsigned long long>(p.light_end > first ? p.light_end - first : 0u) * p.world;
+		}
+	}
+	if (threadIdx.x < p.world * 6)
+	{
+		const uint32_t d = threadIdx.x / 6, c = threadIdx.x % 6;
+		s_box[d][c] = p.slab_box[d * 8 + (c < 3 ? c : c + 1)];
+	}
+	if (threadIdx.x < kMaxPeers)
+		s_run[threadIdx.x] = 0u;
+	__syncthreads();
+	const float* view = p.ubo->camera_view;
+	const uint32_t blk = p.block0 + blockIdx.x;
+	const size_t slot = static_cast<size_t>(blk) * p.block_tiles * kTileLights;
+	const uint32_t lt = lanemask_lt();
+	for (uint32_t k = 0; k < p.block_tiles; ++k)
+	{
+		const uint32_t in_block = k * kTileLights + warp * 128u;
+		const uint32_t light0 = blk * p.block_tiles * kTileLights + in_block;
+		float4 v[4];
+		uint32_t hm[4];
+#pragma unroll
+		for (int it = 0; it < 4; ++it)
+		{
+			const uint32_t i = light0 + it * 32 + lane;
+			hm[it] = 0u;
+			v[it] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+			if (i < p.light_end)
+			{
+				const float4 pw = *reinterpret_cast<const float4*>(p.lights[i].position);
+				const float radius = p.lights[i].radius;
+				v[it].x = mat_row_dot(view, 0, pw.x, pw.y, pw.z, pw.w); // LightCulling.comp:53
+				v[it].y = mat_row_dot(view, 1, pw.x, pw.y, pw.z, pw.w);
+				v[it].z = mat_row_dot(view, 2, pw.x, pw.y, pw.z, pw.w);
+				v[it].w = __fmul_rn(radius, radius);                    // LightCulling.comp:56
+				for (uint32_t d = 0; d < p.world; ++d)
+					hm[it] |= sphere_box_hit(v[it].x, v[it].y, v[it].z, v[it].w, &s_box[d][0], &s_box[d][3]) ? (1u << d) : 0u;
+			}
+		}
+		uint32_t my_tot = 0u; // lane d: survivors of this warp for destination d
+		for (uint32_t d = 0; d < p.world; ++d)
+		{
+			uint32_t t = 0u;
+#pragma unroll
+			for (int it = 0; it < 4; ++it)
+				t += __popc(__ballot_sync(0xffffffffu, (hm[it] >> d) & 1u));
+			if (lane == d)
+				my_tot = t;
+		}
+		if (lane < p.world)
+			s_wt[k & 1u][warp][lane] = my_tot;
+		__syncthreads();
+		uint32_t base = 0u; // lane d: next position of this warp in destination d's region of the block
+		if (lane < p.world)
+		{
+			base = s_run[lane];
+			for (uint32_t w = 0; w < warp; ++w)
+				base += s_wt[k & 1u][w][lane];
+		}
+#pragma unroll
+		for (int it = 0; it < 4; ++it)
+			for (uint32_t d = 0; d < p.world; ++d)
+			{
+				const bool bit = (hm[it] >> d) & 1u;
+				const uint32_t b = __ballot_sync(0xffffffffu, bit);
+				if (b == 0u)
+					continue;
+				const uint32_t bd = __shfl_sync(0xffffffffu, base, d);
+				if (bit)
+				{
+					const size_t q = slot + bd + __popc(b & lt);
+					p.rec[d][q] = v[it];
+					p.idx[d][q] = static_cast<uint16_t>(in_block + it * 32 + lane);
+				}
+				if (lane == d)
+					base += __popc(b);
+			}
+		__syncthreads();
+		if (threadIdx.x < p.world)
+		{
+			uint32_t t = 0u;
+			for (uint32_t w = 0; w < kRouteWarps; ++w)
+				t += s_wt[k & 1u][w][threadIdx.x];
+			s_run[threadIdx.x] += t;
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x < p.world)
+		p.cnt[threadIdx.x][blk] = s_run[threadIdx.x];
+	// ---- last CTA out raises the flag on every rank (the pattern of peer_push_kernel: CTA barrier, one cumulative system
+	// fence, a device-scope counter, release stores of the flags) ----
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		__threadfence_system();
+		PeerMailbox* mine = p.mail[p.rank];
+		const unsigned int done = atomicAdd(&mine->route_done, 1u);
+		s_last = done == gridDim.x - 1;
+		if (s_last)
+			mine->route_done = 0u;
+	}
+	__syncthreads();
+	if (s_last && threadIdx.x < p.world)
+	{
+		__threadfence_system();
+		shard_st_release_sys(&p.mail[threadIdx.x]->routed[p.parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+	}
+}
+
+// one warp: lane r waits for rank r's share of the lights (its own included: the flag is raised by its own route kernel)
+__global__ void __launch_bounds__(32) shard_wait_routed_kernel(const PeerParams p, uint32_t parity)
+{
+	const uint32_t r = threadIdx.x;
+	if (r < p.world)
+	{
+		PeerMailbox* mine = p.mail[p.rank];
+		unsigned long long t0;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+		for (;;)
+		{
+			const unsigned long long v = shard_ld_acquire_sys(&mine->routed[parity][r]);
+			if ((v >> 32) == p.epoch)
+				break;
+			unsigned long long t1;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+			if (t1 - t0 > kRouteTimeoutNs)
+			{
+				atomicCAS(&mine->error, 0u, (3u << 28) | (r << 20) | (p.epoch & 0xfffffu)); // kind 3 = routed lights
+				break;
+			}
+			__nanosleep(200);
+		}
+	}
+	__threadfence_system();
+}
+
+cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges, uint32_t world, float* slab_box, cudaStream_t stream)
+{
+	if (world == 0)
+		return cudaSuccess;
+	slab_unions_kernel<<<world, 256, 0, stream>>>(aabbs, d_ranges, slab_box);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_shard_route(const RouteParams& p, cudaStream_t stream)
+{
+	if (p.blocks == 0 || p.world == 0 || p.world > kMaxPeers || p.block_tiles == 0 || p.block_tiles > kMaxRouteBlockTiles)
+		return cudaErrorInvalidValue;
+	shard_route_kernel<<<p.blocks, kRouteWarps * 32, 0, stream>>>(p);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream)
+{
+	shard_wait_routed_kernel<<<1, 32, 0, stream>>>(p, parity);
+	return cudaGetLastError();
+}
+
+cudaError_t preload_shard_kernels()
+{
+	HVCF_PRELOAD(slab_unions_kernel);
+	HVCF_PRELOAD(shard_route_kernel);
+	HVCF_PRELOAD(shard_wait_routed_kernel);
+	return cudaSuccess;
+}
+
+} // namespace hvcf

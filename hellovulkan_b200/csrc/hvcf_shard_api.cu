@@ -1,0 +1,266 @@
+// hvcf_shard_api.cu -- C ABI of the sharded frame with the lights sharded too (include/hvcf.h, "hvcf_cull_routed";
+// kernels in hvcf_shard.cu).  The reference is single-GPU: what this replaces, at scale, is the one dispatch of
+// PipelineLightCulling::Execute (Source/Pipelines/PipelineLightCulling.cpp:58-119).
+#include "hvcf_ctx.cuh"
+
+#include <cstring>
+
+using namespace hvcf;
+
+namespace
+{
+uint32_t default_block_tiles(uint32_t world)
+{
+	// a route block is compacted by one CTA per destination, so a block of B tiles arrives as about B x (share of the lights that
+	// touch the slab) dense inbox tiles: B = world keeps that near two tiles for the reference's light distribution
+	uint32_t b = 1;
+	while (b < world && b < 8u)
+		b <<= 1;
+	return b;
+}
+} // namespace
+
+extern "C" {
+
+void hvcf_shard_free(hvcf_ctx* c)
+{
+	cudaFree(c->shard.d_inbox);
+	cudaFree(c->shard.d_ranges);
+	cudaFree(c->shard.d_slab_box);
+	cudaFree(c->shard.d_tile_cnt);
+	c->shard = ShardState{};
+}
+
+int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, hvcf_ctx** out_ctx)
+{
+	if (!config || !desc || !out_ctx)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: null argument");
+	if (desc->struct_size != sizeof(hvcf_shard_desc))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: struct_size %u != %zu", desc->struct_size, sizeof(hvcf_shard_desc));
+	*out_ctx = nullptr;
+	const uint32_t world = desc->world, rank = desc->rank;
+	if (world == 0 || world > HVCF_MAX_PEERS || rank >= world)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: rank %u of world %u (at most %u ranks)", rank, world, HVCF_MAX_PEERS);
+	const uint32_t B = desc->block_tiles ? desc->block_tiles : default_block_tiles(world);
+	if (B > kMaxRouteBlockTiles || (B & (B - 1u)))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: block_tiles %u is not a power of two <= %u", B, kMaxRouteBlockTiles);
+	const uint32_t Z = config->slice_count_z ? config->slice_count_z : HVCF_DEFAULT_SLICE_COUNT_Z;
+	if (desc->z_cuts[0] != 0 || desc->z_cuts[world] != Z)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: z_cuts must run from 0 to slice_count_z = %u", Z);
+	for (uint32_t r = 0; r < world; ++r)
+		if (desc->z_cuts[r] > desc->z_cuts[r + 1])
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: z_cuts must ascend");
+	if (desc->z_cuts[rank] == desc->z_cuts[rank + 1])
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: rank %u owns no slice", rank);
+	if (config->mode == HVCF_MODE_BRUTE)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create_sharded: hierarchical mode only");
+
+	// ownership plan: whole route blocks, the same number on every rank (the last ranks may own fewer lights, or none)
+	const uint64_t n = desc->total_lights;
+	const uint64_t tiles = (n + kTileLights - 1) / kTileLights;
+	const uint64_t blocks_total = tiles ? (tiles + B - 1) / B : 1;
+	const uint64_t bpr = (blocks_total + world - 1) / world;
+	const uint64_t blocks_phys = bpr * world, tiles_phys = blocks_phys * B;
+	if (tiles_phys * kTileLights > 0xffff0000ull)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: %u lights are too many", desc->total_lights);
+
+	hvcf_config cfg = *config;
+	cfg.z_begin = desc->z_cuts[rank];
+	cfg.z_end = desc->z_cuts[rank + 1];
+	cfg.mode = HVCF_MODE_HIERARCHICAL;
+	const uint32_t need = static_cast<uint32_t>(tiles_phys * kTileLights);
+	if (cfg.max_lights < need)
+		cfg.max_lights = need; // the survivor slots are indexed by inbox tile
+	hvcf_ctx* c = nullptr;
+	int rc = hvcf_create(&cfg, &c);
+	if (rc != HVCF_OK)
+		return rc;
+	if (!c->bin_ns)
+	{
+		hvcf_destroy(c);
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create_sharded: routed frames bin with the two-level kernel (HVCF_BIN2=0 / HVCF_HIER_V1 switch it off)");
+	}
+	ShardState& sh = c->shard;
+	sh.rank = rank, sh.world = world, sh.total_lights = desc->total_lights;
+	sh.block_tiles = B;
+	sh.blocks_per_rank = static_cast<uint32_t>(bpr);
+	sh.blocks_phys = static_cast<uint32_t>(blocks_phys);
+	sh.tiles_phys = static_cast<uint32_t>(tiles_phys);
+	memcpy(sh.z_cuts, desc->z_cuts, sizeof(uint32_t) * (world + 1));
+	sh.off_idx = static_cast<size_t>(tiles_phys) * kTileBytes;
+	sh.off_cnt = sh.off_idx + static_cast<size_t>(tiles_phys) * kTileLights * sizeof(uint16_t);
+	sh.parity_bytes = (sh.off_cnt + static_cast<size_t>(blocks_phys) * sizeof(uint32_t) + 255u) & ~static_cast<size_t>(255u);
+	uint32_t ranges[2 * HVCF_MAX_PEERS];
+	for (uint32_t r = 0; r < world; ++r)
+	{
+		ranges[2 * r] = desc->z_cuts[r] * c->X * c->Y;
+		ranges[2 * r + 1] = desc->z_cuts[r + 1] * c->X * c->Y;
+	}
+	cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&sh.d_inbox), 2 * sh.parity_bytes);
+	if (e == cudaSuccess)
+		e = cudaMemset(sh.d_inbox, 0, 2 * sh.parity_bytes);
+	if (e == cudaSuccess)
+		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_ranges), sizeof(ranges));
+	if (e == cudaSuccess)
+		e = cudaMemcpy(sh.d_ranges, ranges, sizeof(uint32_t) * 2 * world, cudaMemcpyHostToDevice);
+	if (e == cudaSuccess)
+		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_slab_box), sizeof(float) * 8 * world);
+	if (e == cudaSuccess)
+		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_tile_cnt), sizeof(uint32_t) * tiles_phys);
+	if (e == cudaSuccess)
+		e = cudaMemset(sh.d_tile_cnt, 0, sizeof(uint32_t) * tiles_phys);
+	if (e != cudaSuccess)
+	{
+		hvcf_destroy(c);
+		return fail(e == cudaErrorMemoryAllocation ? HVCF_ERR_OUT_OF_MEMORY : HVCF_ERR_CUDA, "hvcf_create_sharded: inbox of %zu bytes: %s",
+			2 * sh.parity_bytes, cudaGetErrorString(e));
+	}
+	sh.on = true;
+	c->num_lights = desc->total_lights; // the frame is over all the lights of the scene; this rank holds its own range of them
+	c->aabb_dirty = true;
+	*out_ctx = c;
+	return HVCF_OK;
+}
+
+int hvcf_shard_light_range(hvcf_ctx* ctx, uint32_t* out_begin, uint32_t* out_end)
+{
+	if (!ctx || !out_begin || !out_end)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shard_light_range: null argument");
+	if (!ctx->shard.on)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_shard_light_range: not a context of hvcf_create_sharded");
+	const ShardState& sh = ctx->shard;
+	const uint64_t per = static_cast<uint64_t>(sh.blocks_per_rank) * sh.block_tiles * kTileLights;
+	const uint64_t b = per * sh.rank, e = per * (sh.rank + 1);
+	*out_begin = static_cast<uint32_t>(b < sh.total_lights ? b : sh.total_lights);
+	*out_end = static_cast<uint32_t>(e < sh.total_lights ? e : sh.total_lights);
+	return HVCF_OK;
+}
+
+int hvcf_set_lights_range(hvcf_ctx* ctx, const void* lights, uint32_t begin, uint32_t count, int src_is_device, void* stream)
+{
+	if (!ctx || (count && !lights))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_lights_range: null argument");
+	if (static_cast<uint64_t>(begin) + count > ctx->max_lights)
+		return fail(HVCF_ERR_CAPACITY, "hvcf_set_lights_range: [%u, %u + %u) beyond max_lights %u", begin, begin, count, ctx->max_lights);
+	if (ctx->bound_lights)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_lights_range: an external light buffer is bound (hvcf_bind_lights); write to it directly");
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	if (count)
+		HVCF_CUDA(cudaMemcpyAsync(ctx->d_lights + begin, lights, sizeof(hvcf_light_data) * static_cast<size_t>(count),
+			src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+	if (!ctx->shard.on && begin + count > ctx->num_lights)
+		ctx->num_lights = begin + count;
+	return HVCF_OK;
+}
+
+int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	if (!ctx || !ctx->shard.on)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_routed: not a context of hvcf_create_sharded");
+	ShardState& sh = ctx->shard;
+	if (ctx->anim_len)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_routed: device-side light animation is not routed (frame-partitioned replicas animate)");
+	if (ctx->bound_lights)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_routed: the owned lights live in the context's own buffer (hvcf_set_lights_range)");
+	if (!ctx->peer.world)
+	{
+		if (sh.world != 1)
+			return fail(HVCF_ERR_NOT_READY, "hvcf_cull_routed: no peers attached (hvcf_peer_attach)");
+		hvcf_ctx* self[1] = {ctx};
+		const int rc = hvcf_peer_attach_local(ctx, 0, 1, self);
+		if (rc != HVCF_OK)
+			return rc;
+	}
+	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true);
+	if (rc != HVCF_OK)
+		return rc;
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	sh.epoch = sh.epoch >= 0x7fffffffu ? 1u : sh.epoch + 1u;
+	const uint32_t parity = sh.epoch & 1u;
+	DeviceStats* stats = &ctx->d_stats[frame];
+
+	// ---- route: own lights -> view space -> every slab that they touch ----
+	RouteParams rp{};
+	rp.ubo = &ctx->d_ubo[frame];
+	rp.lights = ctx->d_lights;
+	uint32_t lb = 0, le = 0;
+	hvcf_shard_light_range(ctx, &lb, &le);
+	rp.light_end = le;
+	rp.block_tiles = sh.block_tiles;
+	rp.block0 = sh.rank * sh.blocks_per_rank;
+	rp.blocks = sh.blocks_per_rank;
+	rp.world = sh.world, rp.rank = sh.rank, rp.epoch = sh.epoch, rp.parity = parity;
+	rp.slab_box = sh.d_slab_box;
+	for (uint32_t r = 0; r < sh.world; ++r)
+	{
+		unsigned char* box = sh.inbox_peer[r] + static_cast<size_t>(parity) * sh.parity_bytes;
+		rp.rec[r] = reinterpret_cast<float4*>(box);
+		rp.idx[r] = reinterpret_cast<uint16_t*>(box + sh.off_idx);
+		rp.cnt[r] = reinterpret_cast<uint32_t*>(box + sh.off_cnt);
+		rp.mail[r] = ctx->peer.mail[r];
+	}
+	rp.zero = ctx->d_hscratch; // ResetGlobalIndex (PipelineLightCulling.cpp:38-43) and the early-exit counters
+	rp.zero_words = ctx->cluster_count * kHMaxChunks;
+	rp.stats = stats;
+	HVCF_CUDA(launch_shard_route(rp, s));
+	ctx->range_cleared = true;
+	PeerParams pp = ctx->peer;
+	pp.epoch = sh.epoch;
+	HVCF_CUDA(launch_shard_wait_routed(pp, parity, s));
+
+	// ---- level 0 on the inbox: every tile against the cluster groups of this slab ----
+	unsigned char* box = sh.d_inbox + static_cast<size_t>(parity) * sh.parity_bytes;
+	BinParams b{};
+	b.lights_view = reinterpret_cast<const float4*>(box);
+	b.cb_union = ctx->d_cb_union;
+	b.ncb = ctx->hp.ncb;
+	b.tiles_cap = ctx->tiles_cap;
+	b.bin_count = ctx->d_bin_count;
+	b.bin_rec = ctx->d_bin_rec;
+	b.bin_idx = ctx->d_bin_idx;
+	b.stats = stats;
+	b.tile_begin = 0;
+	b.sb_union = ctx->d_sb_union;
+	b.sg = ctx->bin_sg;
+	b.ns = ctx->bin_ns;
+	b.in_idx = reinterpret_cast<const uint16_t*>(box + sh.off_idx);
+	b.in_cnt = reinterpret_cast<const uint32_t*>(box + sh.off_cnt);
+	b.block_tiles = sh.block_tiles;
+	b.tile_cnt = sh.d_tile_cnt;
+	HVCF_CUDA(launch_hier_bin(b, sh.tiles_phys, s));
+	ctx->open_launches += 3;
+	ctx->range_transformed = ctx->range_binned = sh.tiles_phys * kTileLights;
+
+	// ---- count pass + scan, then the exchange of hvcf_cull_sharded ----
+	rc = hvcf_hier_close(ctx, frame, s);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_exchange_totals(ctx, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_cull_finish(ctx, frame, ctx->d_index_base, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_push_grid(ctx, stream);
+	if (rc == HVCF_OK)
+		rc = hvcf_peer_wait_grid(ctx, stream);
+	return rc;
+}
+
+int hvcf_shard_inbox_records(hvcf_ctx* ctx, void* stream, uint64_t* out_records)
+{
+	if (!ctx || !out_records)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shard_inbox_records: null argument");
+	if (!ctx->shard.on)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_shard_inbox_records: not a context of hvcf_create_sharded");
+	const ShardState& sh = ctx->shard;
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+	std::vector<uint32_t> cnt(sh.blocks_phys);
+	HVCF_CUDA(cudaMemcpy(cnt.data(), sh.d_inbox + static_cast<size_t>(sh.epoch & 1u) * sh.parity_bytes + sh.off_cnt, sizeof(uint32_t) * sh.blocks_phys,
+		cudaMemcpyDeviceToHost));
+	uint64_t sum = 0;
+	for (uint32_t v : cnt)
+		sum += v;
+	*out_records = sum;
+	return HVCF_OK;
+}
+
+} // extern "C"

@@ -40,6 +40,13 @@ class Config(ctypes.Structure):
                 ("reserved", ctypes.c_uint32 * 5)]
 
 
+class ShardDesc(ctypes.Structure):
+    """hvcf_shard_desc: this rank's place in the 2-D decomposition (z-slabs of clusters x owned ranges of lights)."""
+    _fields_ = [("struct_size", ctypes.c_uint32), ("rank", ctypes.c_uint32), ("world", ctypes.c_uint32),
+                ("total_lights", ctypes.c_uint32), ("block_tiles", ctypes.c_uint32), ("z_cuts", ctypes.c_uint32 * 17),
+                ("reserved", ctypes.c_uint32 * 4)]
+
+
 class Buffers(ctypes.Structure):
     _fields_ = [("aabb", ctypes.c_void_p), ("light_cells", ctypes.c_void_p), ("light_indices", ctypes.c_void_p),
                 ("global_index_count", ctypes.c_void_p), ("lights", ctypes.c_void_p), ("lights_view", ctypes.c_void_p),
@@ -82,11 +89,12 @@ EXPORTS = [
     "hvcf_debug_kernel_times", "hvcf_update_lights", "hvcf_set_light_animation", "hvcf_set_animation_step",
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
     "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
-    "hvcf_peer_status",
+    "hvcf_peer_status", "hvcf_create_sharded", "hvcf_shard_light_range", "hvcf_set_lights_range", "hvcf_cull_routed",
+    "hvcf_shard_inbox_records",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
-PEER_HANDLE_BYTES = 192
+PEER_HANDLE_BYTES = 256
 RANGE_TRANSFORM, RANGE_BIN = 1, 2
 TILE_LIGHTS = 1024
 
@@ -107,6 +115,11 @@ def load():
     vp, u32, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int
     lib.hvcf_create.argtypes = [ctypes.POINTER(Config), ctypes.POINTER(vp)]
     lib.hvcf_destroy.argtypes = [vp]
+    lib.hvcf_create_sharded.argtypes = [ctypes.POINTER(Config), ctypes.POINTER(ShardDesc), ctypes.POINTER(vp)]
+    lib.hvcf_shard_light_range.argtypes = [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]
+    lib.hvcf_set_lights_range.argtypes = [vp, vp, u32, u32, i32, vp]
+    lib.hvcf_cull_routed.argtypes = [vp, u32, vp]
+    lib.hvcf_shard_inbox_records.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_uint64)]
     lib.hvcf_set_lights.argtypes = [vp, vp, u32, i32, vp]
     lib.hvcf_update_light.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float), vp]
     lib.hvcf_set_ubo.argtypes = [vp, u32, vp, vp]
@@ -331,7 +344,9 @@ class Context:
     """One hvcf_ctx: the device buffers of ResourcesClusterForward + ResourcesLight and the two passes."""
 
     def __init__(self, grid=(16, 9, 24), max_lights=1024, max_lights_per_cluster=150, frame_count=2, device=-1,
-                 mode=MODE_AUTO, z_begin=0, z_end=0):
+                 mode=MODE_AUTO, z_begin=0, z_end=0, shard=None):
+        """shard = (rank, world, total_lights, z_cuts[, block_tiles]): hvcf_create_sharded -- this rank's z-slab of the grid
+        and its own range of the lights (hvcf_cull_routed); z_begin / z_end are then taken from z_cuts."""
         self.lib = load()
         cfg = Config()
         cfg.struct_size = ctypes.sizeof(Config)
@@ -343,7 +358,17 @@ class Context:
         cfg.mode = mode
         cfg.z_begin, cfg.z_end = z_begin, z_end
         self.handle = ctypes.c_void_p()
-        _check(self.lib.hvcf_create(ctypes.byref(cfg), ctypes.byref(self.handle)))
+        if shard is not None:
+            rank, world, total, cuts = shard[:4]
+            d = ShardDesc()
+            d.struct_size = ctypes.sizeof(ShardDesc)
+            d.rank, d.world, d.total_lights = rank, world, total
+            d.block_tiles = shard[4] if len(shard) > 4 else 0
+            for i, z in enumerate(cuts):
+                d.z_cuts[i] = z
+            _check(self.lib.hvcf_create_sharded(ctypes.byref(cfg), ctypes.byref(d), ctypes.byref(self.handle)))
+        else:
+            _check(self.lib.hvcf_create(ctypes.byref(cfg), ctypes.byref(self.handle)))
         self.grid = tuple(grid)
         self.cap = max_lights_per_cluster
         self.cluster_total = grid[0] * grid[1] * grid[2]
@@ -459,16 +484,16 @@ class Context:
 
     # -- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ---------------------
     def peer_export(self):
-        """192-byte handle (3 x cudaIpcMemHandle_t) to send to the other ranks."""
+        """256-byte handle (4 x cudaIpcMemHandle_t) to send to the other ranks."""
         h = (ctypes.c_ubyte * PEER_HANDLE_BYTES)()
         _check(self.lib.hvcf_peer_export(self.handle, h))
         return bytes(h)
 
     def peer_attach(self, rank, world, handles):
-        """handles: world x 192 bytes in rank order (own entry ignored)."""
+        """handles: world x 256 bytes in rank order (own entry ignored)."""
         blob = b"".join(bytes(h) for h in handles)
         if len(blob) != world * PEER_HANDLE_BYTES:
-            raise ValueError("peer_attach: need one 192-byte handle per rank")
+            raise ValueError("peer_attach: need one 256-byte handle per rank")
         buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
         _check(self.lib.hvcf_peer_attach(self.handle, rank, world, buf))
 
@@ -487,6 +512,30 @@ class Context:
 
     def peer_wait_grid(self, stream=None):
         _check(self.lib.hvcf_peer_wait_grid(self.handle, stream))
+
+    # -- lights owned in shards: the routed frame (hvcf_shard.cu) ---------------------------------------
+    def shard_light_range(self):
+        """[begin, end) of the lights this rank owns, in global light indices."""
+        b, e = ctypes.c_uint32(), ctypes.c_uint32()
+        _check(self.lib.hvcf_shard_light_range(self.handle, ctypes.byref(b), ctypes.byref(e)))
+        return int(b.value), int(e.value)
+
+    def set_lights_range(self, lights, begin, stream=None):
+        """lights: numpy LIGHT_DT (host) -> lights [begin, begin + len) of the context's light buffer."""
+        lights = np.ascontiguousarray(lights)
+        assert lights.dtype == LIGHT_DT
+        _check(self.lib.hvcf_set_lights_range(self.handle, _ptr(lights) if len(lights) else None, begin, len(lights), 0, stream))
+
+    def set_lights_range_ptr(self, ptr, begin, count, is_device, stream=None):
+        _check(self.lib.hvcf_set_lights_range(self.handle, ptr, begin, count, 1 if is_device else 0, stream))
+
+    def cull_routed(self, frame=0, stream=None):
+        _check(self.lib.hvcf_cull_routed(self.handle, frame, stream))
+
+    def shard_inbox_records(self, stream=None):
+        v = ctypes.c_uint64()
+        _check(self.lib.hvcf_shard_inbox_records(self.handle, stream, ctypes.byref(v)))
+        return int(v.value)
 
     def cull_sharded(self, frame=0, stream=None):
         _check(self.lib.hvcf_cull_sharded(self.handle, frame, stream))

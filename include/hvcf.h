@@ -179,7 +179,7 @@ HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
  * leaves the FULL light grid (lightCells[], lightIndices[] in the reference layouts) on every rank, with no host
  * round trip and no collective-library call.  All ranks must call it the same number of times.  Waits are bounded:
  * a missing peer raises the error that hvcf_peer_status reports (after synchronising `stream`).
- *   hvcf_peer_export        handle = 3 x cudaIpcMemHandle_t (64 B each), to be sent to the other processes
+ *   hvcf_peer_export        handle = 4 x cudaIpcMemHandle_t (64 B each), to be sent to the other processes
  *   hvcf_peer_attach        handles[world], own entry ignored; peers are mapped with cudaIpcOpenMemHandle
  *   hvcf_peer_attach_local  the same for contexts living in THIS process (same or peer-accessible devices)
  *   hvcf_peer_detach        unmaps; call on every rank (after a barrier) before hvcf_destroy */
@@ -189,6 +189,7 @@ typedef struct hvcf_peer_handle
 	unsigned char cells[64];
 	unsigned char indices[64];
 	unsigned char mailbox[64];
+	unsigned char inbox[64];   /* routed frames (hvcf_create_sharded); zero otherwise */
 } hvcf_peer_handle;
 HVCF_API int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out);
 HVCF_API int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_peer_handle* handles);
@@ -203,6 +204,44 @@ HVCF_API int hvcf_peer_totals_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 /* device uint32: this rank's index base of the last exchange (what hvcf_cull_sharded passes to hvcf_cull_finish) */
 HVCF_API int hvcf_peer_index_base_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 HVCF_API int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error);
+
+/* ---------------------------------------------------------------------------------------------------
+ * The sharded frame with the LIGHTS sharded too (new: the reference is single-GPU).
+ * Rank r owns the z-slab [z_cuts[r], z_cuts[r + 1]) of the cluster grid AND the LightData of a contiguous range
+ * of lights (hvcf_shard_light_range; whole route blocks of block_tiles x 1,024 lights).  One call per frame,
+ *   hvcf_cull_routed = route    own lights -> view space, tested against every rank's slab box, survivors stored
+ *                               straight into the owning rank's inbox over NVLink peer memory (in light order)
+ *                    + wait     until every rank's share has arrived
+ *                    + level-0 binning of the inbox, count pass, scan          (local)
+ *                    + totals exchange, write pass at GLOBAL offsets, grid push, wait   (as hvcf_cull_sharded)
+ * leaves the FULL light grid on every rank, byte-identical to the single-GPU frame over all the lights.  No rank ever
+ * holds, transforms or bins all the lights; there is no collective-library call and no host round trip in the frame.
+ * Setup: hvcf_create_sharded on every rank, hvcf_peer_export / exchange the handles / hvcf_peer_attach (or
+ * hvcf_peer_attach_local for contexts of one process), hvcf_set_lights_range for the owned lights, hvcf_set_ubo.
+ * world = 1 needs no attach.  Replaces, at scale, the single dispatch of PipelineLightCulling::Execute
+ * (Source/Pipelines/PipelineLightCulling.cpp:58-119) over LightCulling.comp:59-88.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct hvcf_shard_desc
+{
+	uint32_t struct_size;                  /* = sizeof(hvcf_shard_desc) */
+	uint32_t rank, world;                  /* world <= HVCF_MAX_PEERS */
+	uint32_t total_lights;                 /* lights of the whole scene, the same on every rank */
+	uint32_t block_tiles;                  /* tiles per route block, a power of two <= 16; 0 = library default */
+	uint32_t z_cuts[HVCF_MAX_PEERS + 1];   /* ascending, z_cuts[0] = 0, z_cuts[world] = slice_count_z */
+	uint32_t reserved[4];
+} hvcf_shard_desc;
+/* hvcf_create with z_begin / z_end = this rank's slab and max_lights raised to the padded light count of the
+ * decomposition, plus the inbox, the slab boxes and the ownership plan. */
+HVCF_API int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, hvcf_ctx** out_ctx);
+/* the lights this rank owns: [*out_begin, *out_end) in GLOBAL light indices (may be empty) */
+HVCF_API int hvcf_shard_light_range(hvcf_ctx* ctx, uint32_t* out_begin, uint32_t* out_end);
+/* ResourcesLight::AddLights for a part of the light buffer (VulkanBuffer::UploadOffsetBufferData,
+ * Source/Vulkan/VulkanBuffer.cpp:158-167): lights [begin, begin + count) <- `lights` (count x 48 B). */
+HVCF_API int hvcf_set_lights_range(hvcf_ctx* ctx, const void* lights, uint32_t begin, uint32_t count, int src_is_device, void* stream);
+HVCF_API int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream);
+/* records that arrived in this rank's inbox in the last routed frame (synchronises `stream`); the wire carried
+ * 18 B per record that came from another rank */
+HVCF_API int hvcf_shard_inbox_records(hvcf_ctx* ctx, void* stream, uint64_t* out_records);
 
 HVCF_API int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out);
 
