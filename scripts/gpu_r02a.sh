@@ -4,6 +4,9 @@ TAG=${1:-r02a}; O=gpurun_out/$TAG; mkdir -p $O
 export PYTHONPATH=$PWD
 nvidia-smi --query-gpu=index,name,clocks.sm,clocks.max.sm,clocks.mem,power.draw,power.limit --format=csv > $O/smi.txt 2>&1
 nproc > $O/nproc.txt
+timeout 900 python -m pytest tests/test_gpu_routed.py -x -q --durations=5 > $O/pytest_routed.txt 2>&1
+echo "routed rc=$?" >> $O/pytest_routed.txt
+tail -25 $O/pytest_routed.txt
 timeout 1500 python -m pytest tests/test_gpu_full_size.py -x -q --durations=10 > $O/pytest_full_size.txt 2>&1
 echo "full-size rc=$?" >> $O/pytest_full_size.txt
 tail -15 $O/pytest_full_size.txt
