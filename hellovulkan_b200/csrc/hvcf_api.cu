@@ -606,6 +606,7 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_generate_aabbs: frame %u >= frame_count %u", frame, ctx->frame_count);
 	if (!ctx->ubo_set[frame])
 		return fail(HVCF_ERR_NOT_READY, "hvcf_generate_aabbs: hvcf_set_ubo(frame %u) has not been called", frame);
+	NvtxZone zone("AABB_Generator");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	const hvcf_cluster_forward_ubo& u = ctx->h_ubo[frame];
@@ -929,6 +930,7 @@ int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes
 
 int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 {
+	NvtxZone zone("Light_Culling");
 	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin", false);
 	if (rc != HVCF_OK)
 		return rc;
@@ -1002,6 +1004,7 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_finish: null context");
 	if (frame >= ctx->frame_count)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_finish: frame %u >= frame_count %u", frame, ctx->frame_count);
+	NvtxZone zone("Light_Culling");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	if (ctx->hier)
 	{

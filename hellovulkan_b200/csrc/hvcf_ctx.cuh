@@ -6,6 +6,8 @@
 
 #include <cstdlib>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "hvcf_kernels.cuh"
 
 namespace hvcf
@@ -18,6 +20,15 @@ inline int env_int(const char* name, int dflt)
 	const char* v = getenv(name);
 	return (v && *v) ? atoi(v) : dflt;
 }
+// profiler zone of the calling thread for the duration of a scope: the reference wraps the pass in TracyVkZoneC(..., "Light_Culling", ...)
+// (Source/Pipelines/PipelineLightCulling.cpp:53); here the same names as NVTX ranges (nsys / ncu --nvtx pick them up; a no-op otherwise)
+struct NvtxZone
+{
+	explicit NvtxZone(const char* name) { nvtxRangePushA(name); }
+	~NvtxZone() { nvtxRangePop(); }
+	NvtxZone(const NvtxZone&) = delete;
+	NvtxZone& operator=(const NvtxZone&) = delete;
+};
 } // namespace hvcf
 
 struct hvcf_ctx;

@@ -171,6 +171,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		if (rc != HVCF_OK)
 			return rc;
 	}
+	NvtxZone zone("Light_Culling");
 	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true);
 	if (rc != HVCF_OK)
 		return rc;
