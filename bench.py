@@ -3,21 +3,27 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
-One "step" = one frame of the hot path (AABB generation if dirty + light transform + culling +
-offsets + scatter) over one synthetic scene (hvcf_host_init_lights, seed 12345; reference camera).
+ONE headline workload at every N: C16M = BASELINE.json configs[3], 64x36x96 clusters x 16,777,216 lights at 3840x2160
+(the only config the metric's "at 1/2/4/8 B200" applies to; it fits one GPU), "scaling": "strong".
+One "step" = one frame of the hot path over the whole scene: AABB generation if dirty + light transform + culling +
+offsets + scatter, the full light grid (lightCells + lightIndices in the reference layouts) left on EVERY GPU.
+  N = 1   hvcf_cull on one context, all lights resident on the GPU.
+  N > 1   hvcf_cull_routed: clusters sharded by z-slab AND lights owned in shards; every light is transformed every frame by
+          its owner, tested against the slab boxes and routed into the owning ranks' inboxes over NVLink peer memory; totals,
+          cells and index segments exchanged by kernels over peer memory.  No collective-library call inside the frame.
+          Every rank hashes its full grid on the device and compares it with the UNSHARDED frame of rank 0
+          ("sharded_bytes_equal"); a mismatch fails the run.
 
-  N = 1   workload A65k = BASELINE.json configs[1]: 16x9x24 clusters x 65,536 lights, 2560x1600.
-  N > 1   every rank culls its own frames of the same workload (the frame-partitioned mode of
-          configs[4]; no data-path collective) -> "scaling": "weak"; the line additionally carries
-          "sharded": the z-slab sharded grid of configs[3] (NCCL light broadcast + grid all-gather).
-
-Keys of the JSON line (rank 0 prints exactly one line on stdout):
+Keys of the JSON line (rank 0 prints exactly one line on stdout; it ENDS with a compact "summary"):
   value          nominal cluster x light tests per second, whole job, inputs resident in HBM
-  e2e            same metric through the C ABI with HOST buffers: pinned H2D of the light buffer and
-                 the UBO, the frame, D2H of light cells + index list, every step
-  roofline       the culling kernel: executed tests x 16 FP32-pipe lane-ops / kernel time (CUDA events
-                 inside libhvcf, live) against the FP32 issue rate measured on this GPU
-  cpu_baseline   the reference's own shader source compiled as C++ (oracle/_ref), all host threads
+  e2e            same metric through the C ABI with HOST buffers: per step every rank uploads its own share of the LightData
+                 (pinned H2D; N = 1: all of it) and the UBO, runs the frame, and downloads its own slab's cells + index
+                 segment, so the whole job moves every light in and the whole grid out exactly once per step
+  roofline       the dominant kernel of the step: its own tests x 16 FP32-pipe lane-ops / its duration (CUDA events inside
+                 libhvcf, live) against the FP32 issue rate measured on this GPU
+  cpu_baseline   the reference's own shader source compiled as C++ (oracle/_ref), all host threads, on a cluster sample
+  summary        N = 1: ms / frac / e2e_ms of A1k, A65k, A1M, B1M and the fly-through, boundary-disagreement counts;
+                 N > 1: phase split, per-rank kernel times, NVLink bytes, the NCCL-broadcast formulation beside the routed one
 
 --impl reference times that CPU build alone (rank 0 only under torchrun).
 Nothing here reads /root/reference at run time.
@@ -41,10 +47,10 @@ sys.path.insert(0, ROOT)
 # name -> (grid, screen, lights)     
 WORKLOADS = {
     "A1k": ((16, 9, 24), (2560, 1600), 1000),            # configs[0]
-    "A65k": ((16, 9, 24), (2560, 1600), 65536),          # configs[1]  <- default at N=1
+    "A65k": ((16, 9, 24), (2560, 1600), 65536),          # configs[1]
     "A1M": ((16, 9, 24), (2560, 1600), 1 << 20),         # north_star "1M lights x 16x9x24"
     "B1M": ((32, 18, 48), (3840, 2160), 1 << 20),        # configs[2]
-    "C16M": ((64, 36, 96), (3840, 2160), 1 << 24),       # configs[3] (sharded)
+    "C16M": ((64, 36, 96), (3840, 2160), 1 << 24),       # configs[3]  <- headline at every N
 }
 LANE_OPS_PER_TEST = 16  # 6 min/max + 3 sub + 3 mul + 3 add + 1 compare
 L2_FLUSH_BYTES = 256 << 20
@@ -57,22 +63,30 @@ def log(*a):
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="A65k", choices=sorted(WORKLOADS))
-    ap.add_argument("--sharded-workload", default="C16M", choices=sorted(WORKLOADS))
-    ap.add_argument("--sharded-steps", type=int, default=3)
-    ap.add_argument("--sharded-balance-iters", type=int, default=8, help="slab re-cuts from measured per-rank times")
-    ap.add_argument("--sharded-chunks", type=int, default=4, help="pieces of the pipelined light broadcast")
-    ap.add_argument("--mode", default="auto", choices=["auto", "brute", "hier"], help="hvcf_mode of the culling context")
-    ap.add_argument("--no-sharded", action="store_true")
+    ap.add_argument("--workload", default="C16M", choices=sorted(WORKLOADS))
+    ap.add_argument("--balance-iters", type=int, default=4, help="N > 1: slab re-cuts from measured per-rank kernel times")
+    ap.add_argument("--block-tiles", type=int, default=0, help="tiles per route block (0 = library default)")
+    ap.add_argument("--z-cuts", default="", help="N > 1: comma-separated z cuts (N + 1 numbers) instead of balancing")
+    ap.add_argument("--no-summary", action="store_true", help="N = 1: skip the legs on the other workloads")
+    ap.add_argument("--no-compare", action="store_true", help="N > 1: skip the NCCL-broadcast formulation")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flythrough", action="store_true", help="skip the 1,024-frame animated fly-through leg (configs[4])")
     ap.add_argument("--fly-frames", type=int, default=0, help="frames of the fly-through (0 = 1,024)")
     ap.add_argument("--no-next-rows", action="store_true", help="skip the consumer / frustum-culling legs")
-    ap.add_argument("--cpu-seconds", type=float, default=4.0, help="wall-clock budget of the cpu_baseline sample")
+    ap.add_argument("--cpu-seconds", type=float, default=8.0, help="wall-clock budget of the cpu_baseline sample")
     return ap.parse_args()
+
+
+def host_threads():
+    """Threads for the CPU legs: the cores this process may run on.  torch.distributed.run exports OMP_NUM_THREADS=1 to its
+    workers; the reference arm must not inherit that (it would time ONE thread and call it the box)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -143,42 +157,34 @@ def cpu_checker():
     import cpu_checkers as cc
     if cc.Reference.available():
         ref = cc.Reference()
-        return "reference", ref, ref.max_threads()
+        return "reference", ref, host_threads()
     orc = cc.Oracle()
-    return "port", orc, orc.max_threads()
+    return "port", orc, host_threads()
 
 
 def cpu_frame_fn(kind, impl, grid, screen, n):
-    """Returns (fn, tests_per_call, sample_description): fn() culls one bounded sample on the host cores."""
+    """Returns (fn, tests_per_call, sample_description, threads): fn() culls one bounded sample on the host cores."""
     ubo = impl.camera_ubo(grid, screen)
     aabbs = impl.generate_aabbs(ubo)
     lights = impl.init_lights(n)
     C = len(aabbs)
-    threads = impl.max_threads()
+    threads = host_threads()   # explicit: never OMP_NUM_THREADS
     full = C * n
-    # bound one call to ~3e8 nominal tests (a second or two on 8 cores): whole frame for A65k,
-    # an evenly strided cluster subset (every slab represented) for the larger grids
-    stride = max(1, int(np.ceil(full / 3.0e8)))
+    # bound one call to ~1e9 nominal tests (about a second on 16 cores): the whole frame for A1k / A65k, an evenly strided
+    # cluster subset (every z-slice region represented) for the larger configs -- the figure is then an extrapolation
+    stride = max(1, int(np.ceil(full / 1.0e9)))
     if stride == 1:
         sub, desc = aabbs, f"whole frame: {C} clusters x {n} lights"
     else:
         sub = np.ascontiguousarray(aabbs[::stride])
-        desc = f"every {stride}th cluster ({len(sub)} of {C}) x {n} lights"
+        desc = f"every {stride}th cluster ({len(sub)} of {C}) x all {n} lights; whole-frame figure extrapolated from the sample"
     if kind == "reference":
-        # hvref_cull dispatches one workgroup per cluster of the grid in the UBO; a subset is run by
-        # shrinking the Z count of a copy of the UBO to cover len(sub) clusters (the shader only uses the
-        # counts to form the tile index)
+        # hvref_cull dispatches one workgroup per cluster of the grid in the UBO (gl_NumWorkGroups = the UBO's slice counts,
+        # tile index = x + y X + z X Y, LightCulling.comp:61-64); a subset is run as a (len(sub), 1, 1) dispatch over the
+        # gathered boxes -- the shader uses the counts only to form the tile index
         u = ubo.copy()
         if stride > 1:
-            X, Y = grid[0], grid[1]
-            # whole XY layers only: re-stride so that at least one layer of X*Y sampled clusters remains
-            layers = max(1, len(sub) // (X * Y))
-            m = layers * X * Y
-            stride = max(1, C // m)
-            sub = np.ascontiguousarray(aabbs[::stride][:m])
-            assert len(sub) == m, (len(sub), m)
-            u.view(np.uint32)[40] = m // (X * Y)
-            desc = f"every {stride}th cluster ({m} of {C}) x {n} lights"
+            u.view(np.uint32)[38:41] = (len(sub), 1, 1)
 
         def fn():
             impl.cull(u, sub, lights, threads=threads)
@@ -226,7 +232,7 @@ def run_reference_arm(args):
     line = {
         "impl": "reference", "metric": "cluster-light tests/s", "value": value, "unit": "tests/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "ms_per_frame_equiv": full_frame_tests / value * 1e3,
-        "higher_is_better": True, "scaling": "weak",
+        "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
                    "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)", "device": "host cpu"},
@@ -253,7 +259,7 @@ def hbm_peak():
 
 
 def ncu_traffic(workload):
-    """dram bytes per launch of the culling kernel from the committed ncu --set full capture, or None."""
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture, or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         with open(p) as f:
@@ -261,281 +267,363 @@ def ncu_traffic(workload):
     return None
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    from hellovulkan_b200 import hvcf
+KERNEL_NAMES = ("transform", "bin", "count", "finalize", "write")
+KERNEL_SYMBOL = {"transform": "light_transform_kernel / shard_route_kernel (+ wait for the other ranks' shares)",
+                 "bin": "hier_bin2_kernel / hier_bin_kernel / hier_xbin_kernel (level-0 binning)",
+                 "count": "hier2_kernel<K,0> (count pass)", "finalize": "hier_finalize_kernel", "write": "hier2_kernel<K,1> (write pass)"}
 
-    hvcf.load()  # raises if libhvcf.so is missing: there is no fallback
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py --impl ours needs a CUDA device (libhvcf has no CPU path)")
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        log(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}; using WORLD_SIZE")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL on a high-priority stream: its few CTAs must get SM slots while the binning kernel has thousands queued,
-        # otherwise the chunked light broadcast cannot overlap the compute it is pipelined with
-        opts = dist.ProcessGroupNCCL.Options()
-        opts.is_high_priority_stream = os.environ.get("HVCF_NCCL_LOW_PRIORITY") != "1"
-        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
 
-    def barrier():
-        if world > 1:
-            dist.barrier(device_ids=[local])
-        torch.cuda.synchronize()
+def instrumented_kernels(hvcf, make_ctx, run_frame, sp, frames=6):
+    """Per-kernel milliseconds of the hierarchical frame from CUDA events recorded inside libhvcf on the launching stream
+    (HVCF_KERNEL_TIMES=1 at hvcf_create: an event after every kernel, which also switches their programmatic overlap off),
+    and the work counters of the same frames.  make_ctx() -> context (created with the env switch on); run_frame(ctx, f).
+    The caller closes the returned context."""
+    os.environ["HVCF_KERNEL_TIMES"] = "1"
+    try:
+        ctx = make_ctx()
+    finally:
+        os.environ.pop("HVCF_KERNEL_TIMES", None)
+    try:
+        for f in range(2):
+            run_frame(ctx, f & 1)
+        rows = []
+        for f in range(frames):
+            run_frame(ctx, f & 1)
+            rows.append(ctx.kernel_times(f & 1))
+        st = ctx.stats((frames - 1) & 1, sp)
+    except Exception:
+        ctx.close()
+        raise
+    ms = dict(zip(KERNEL_NAMES, [float(x) for x in np.median(np.array(rows), axis=0)]))
+    return ms, st, ctx
 
-    grid, screen, n = WORKLOADS[args.workload]
+
+def kernel_roofline(ms, st, issue_rate, step_ms):
+    """roofline object of the dominant kernel: ITS OWN tests x 16 lane-ops / ITS duration against the measured issue rate.
+    bin kernel: the level-0 union tests (hvcf_stats.bin_tests); count pass: exact tests + level-1 union tests; the write
+    pass: the tests it repeats (hvcf_stats.write_pass_tests); transform / finalize are HBM-side and carry no test count."""
+    tests = {"bin": st["bin_tests"], "count": st["executed_tests"] + st["prefilter_tests"] - st["bin_tests"], "write": st["write_pass_tests"]}
+    top = max(("bin", "count", "write"), key=lambda k: ms[k])
+    total = sum(ms.values())
+    ach = tests[top] * LANE_OPS_PER_TEST / (ms[top] * 1e-3)
+    per_kernel = {k: {"ms": ms[k], "tests": int(tests[k]) if k in tests else None,
+                      "frac": (tests[k] * LANE_OPS_PER_TEST / (ms[k] * 1e-3) / issue_rate) if k in tests and ms[k] > 0 else None}
+                  for k in KERNEL_NAMES}
+    return {"bound": "fp32", "kernel": KERNEL_SYMBOL[top], "achieved": ach / 1e12, "peak": issue_rate / 1e12, "unit": "TFLOP/s",
+            "frac": ach / issue_rate, "traffic": None, "kernel_ms": ms[top], "kernel_share_of_step": ms[top] / total if total else None,
+            "tests_per_launch": int(tests[top]), "flop_per_test": LANE_OPS_PER_TEST,
+            "peak_source": "hvcf_measure_fp32_issue_rate on this GPU, this run (non-FMA FADD/FMUL issue rate; MEASURED_PEAKS.json has no "
+                           "FP32 figure); nominal 148 SM x 128 lanes x 1.965 GHz = 37.2",
+            "kernel_share_note": "share of the instrumented frame (an event after every kernel serialises the PDL chain); the ncu launch "
+                                 "list under profiles/ must agree on the share, not on the absolute time",
+            "per_kernel": per_kernel, "instrumented_step_ms": total, "step_ms": step_ms}
+
+
+def timed_frames(torch, stream, run_frame, K, W, flush, barrier):
+    """W warm-up frames, then K frames each bracketed by CUDA events on the launching stream (L2 flushed before each when
+    `flush` is given); returns per-step ms."""
+    for i in range(W):
+        run_frame(i & 1)
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for i in range(K):
+        if flush is not None:
+            flush.zero_()
+        ev[i][0].record(stream)
+        run_frame(i & 1)
+        ev[i][1].record(stream)
+    barrier()
+    return np.array([a.elapsed_time(b) for a, b in ev])
+
+
+def measure_single(hvcf, torch, name, K, W, local, flush_all, barrier=lambda: None, e2e_steps=50, graph=False):
+    """One workload on ONE GPU through the C ABI: device-timed frame, per-kernel times + roofline of the dominant kernel,
+    e2e with host buffers (everything uploaded every step) and with the lights resident (what the reference app does per
+    frame: UBO up, AppPBRClusterForward.cpp:120-136; here plus the grid down)."""
+    import ctypes
+    grid, screen, n = WORKLOADS[name]
     C = grid[0] * grid[1] * grid[2]
-    K, W = args.steps, max(args.warmup, 3)
     stream = torch.cuda.current_stream()
-    sp = stream.cuda_stream  # libhvcf launches on torch's current stream, so torch events bracket its kernels
-
-    # ---- inputs (host side of the reference interface: Camera -> UBO, InitLights) -----------------
+    sp = stream.cuda_stream
+    lib = hvcf.load()
     pinned = hvcf.PinnedBuffer(48 * n)
     lights = pinned.array.view(hvcf.LIGHT_DT)
     hvcf.host_init_lights(n, out=lights)
-    pos_a, pos_b = hvcf.REF_CAMERA_POS, (0.5, 1.0, 6.0)  # two views, same projection: AABBs stay valid
-    ubos = [hvcf.host_camera_ubo(grid, screen, pos=pos_a), hvcf.host_camera_ubo(grid, screen, pos=pos_b)]
+    ubos = [hvcf.host_camera_ubo(grid, screen, pos=hvcf.REF_CAMERA_POS), hvcf.host_camera_ubo(grid, screen, pos=(0.5, 1.0, 6.0))]
+    pinned_ubo = hvcf.PinnedBuffer(2 * hvcf.UBO_BYTES)
+    for f in range(2):
+        pinned_ubo.array[f * hvcf.UBO_BYTES:(f + 1) * hvcf.UBO_BYTES] = ubos[f]
+    big = 48 * n > (256 << 20)          # inputs larger than L2 (126 MB) by themselves: no flush needed
+    flush = None if big else flush_all
+
+    def make_ctx():
+        c = hvcf.Context(grid=grid, max_lights=n, device=local)
+        c.set_lights_ptr(pinned.ptr.value, n, False, sp)
+        for f in range(2):
+            c.set_ubo(f, ubos[f], sp)
+        return c
+
+    ctx = make_ctx()
+    out = {"workload": name, "grid": list(grid), "lights": n}
+    try:
+        step_ms = timed_frames(torch, stream, lambda f: ctx.cull(f, sp), K, W, flush, barrier)
+        st = ctx.stats((K - 1) & 1, sp)
+        out.update({"ms": float(step_ms.mean()), "ms_min": float(step_ms.min()), "ms_median": float(np.median(step_ms)),
+                    "launches_per_step": st["kernel_launches"], "total_indices": st["total_indices"],
+                    "l2": "inputs larger than L2" if big else f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)"})
+        if graph:   # config 1 is launch-bound: the same frame captured once into a CUDA graph and replayed
+            out["graph"] = measure_graph(hvcf, torch, ctx, K, W, flush)
+        # ---- e2e through the C ABI with host buffers ----
+        cells_host, idx_host = hvcf.PinnedBuffer(8 * C), hvcf.PinnedBuffer(4 * C * 150)
+        total_host = np.zeros(1, np.uint32)
+        tp = total_host.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32))
+
+        def e2e_step(f, upload_lights):
+            if upload_lights:
+                ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)                  # H2D 48*n
+            ctx.set_ubo_ptr(f, pinned_ubo.ptr.value + f * hvcf.UBO_BYTES, sp)        # H2D 176
+            ctx.cull(f, sp)
+            hvcf._check(lib.hvcf_download_grid(ctx.handle, f, cells_host.ptr, 8 * C, idx_host.ptr, 4 * C * 150, tp, sp))
+            return int(total_host[0])
+
+        Ke = max(3, min(K, e2e_steps))
+        for upload, key in ((True, "e2e"), (False, "e2e_resident")):
+            for i in range(min(W, 3)):
+                e2e_step(i & 1, upload)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(Ke):
+                tot = e2e_step(i & 1, upload)
+            torch.cuda.synchronize()
+            ms = (time.perf_counter() - t0) / Ke * 1e3
+            out[key] = {"ms_per_step": ms, "steps": Ke, "h2d_bytes_per_step": (48 * n if upload else 0) + hvcf.UBO_BYTES,
+                        "d2h_bytes_per_step": 4 + 8 * C + 4 * tot}
+        out["e2e"]["mode"] = "one frame at a time: upload lights + UBO, cull, hvcf_download_grid (blocking)"
+        out["e2e_resident"]["mode"] = "lights resident (static lights, as ResourcesLight::AddLights once at init): upload UBO, cull, hvcf_download_grid"
+    finally:
+        ctx.close()
+    # ---- per-kernel times and the dominant kernel's roofline (a second, instrumented context) ----
+    ms, st2, ictx = instrumented_kernels(hvcf, make_ctx, lambda c, f: ((flush.zero_() if flush is not None else None), c.cull(f, sp)), sp)
+    ictx.close()
+    issue_rate = hvcf.measure_fp32_issue_rate(local)
+    out["roofline"] = kernel_roofline(ms, st2, issue_rate, out["ms"])
+    out["stats"] = {k: int(v) for k, v in st2.items()}
+    out["nominal_tests"] = C * n
+    return out
+
+
+def measure_graph(hvcf, torch, ctx, K, W, flush):
+    """The frame captured into a CUDA graph (torch.cuda.graphs on a side stream; libhvcf's launches are stream-ordered and
+    capture-safe once the AABBs are clean) and replayed: launch-inclusive time per frame, against the kernel-only time
+    (sum of the kernels' own durations would need ncu; reported is the graph replay bracketed by events)."""
+    s = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    try:
+        with torch.cuda.stream(s):
+            ctx.cull(0, s.cuda_stream)     # warm: AABBs clean, kernels loaded
+            s.synchronize()
+            g.capture_begin()
+            ctx.cull(0, s.cuda_stream)
+            g.capture_end()
+        for _ in range(W):
+            g.replay()
+        torch.cuda.synchronize()
+        ms = []
+        cur = torch.cuda.current_stream()
+        for _ in range(K):
+            if flush is not None:
+                flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(cur)
+            g.replay()
+            b.record(cur)
+            b.synchronize()
+            ms.append(a.elapsed_time(b))
+        return {"ms": float(np.mean(ms)), "ms_min": float(min(ms)), "note": "one cudaGraphLaunch per frame, event pair around it"}
+    except Exception as e:   # capture is best effort: the stream-launched figure stands
+        return {"error": f"{type(e).__name__}: {e}"}
+
+
+def grid_hash(torch, cells_t, idx_t):
+    """64-bit position-dependent hash of the full light grid, computed on the device: lightCells (offset, count) and
+    lightIndices[0, total) as int32 words.  Equal hashes on two GPUs <=> (to 2^-64) equal bytes."""
+    def h(t, salt):
+        x = t.reshape(-1).to(torch.int64)
+        i = torch.arange(x.numel(), device=x.device, dtype=torch.int64)
+        return ((x ^ salt) * (2 * i + 1)).sum()
+    return int((h(cells_t, -7046029254386353131) * 31 + h(idx_t, 0x2545F4914F6CDD1D)).item())
+
+
+def full_grid_hash(torch, hvcf, ctx, frame, dev, sp):
+    from hellovulkan_b200.sharded import as_tensor
+    b = ctx.buffers()
+    total = ctx.download_total(frame, sp)
+    cells = as_tensor(b.light_cells, 8 * b.cluster_count, dev).view(torch.int32)
+    idx = as_tensor(b.light_indices, 4 * max(total, 1), dev).view(torch.int32)[:total]
+    return grid_hash(torch, cells, idx), total
+
+
+def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, flush):
+    """The headline at N > 1: hvcf_cull_routed (clusters sharded by z-slab, lights owned in shards)."""
+    import ctypes
+    from hellovulkan_b200.sharded import slice_touch_counts, cuts_from_cost, balance_slabs
+    grid, screen, n = WORKLOADS[args.workload]
+    C = grid[0] * grid[1] * grid[2]
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+    all_lights = hvcf.host_init_lights(n)
+    ubos = [hvcf.host_camera_ubo(grid, screen, pos=hvcf.REF_CAMERA_POS), hvcf.host_camera_ubo(grid, screen, pos=(0.5, 1.0, 6.0))]
     pinned_ubo = hvcf.PinnedBuffer(2 * hvcf.UBO_BYTES)
     for f in range(2):
         pinned_ubo.array[f * hvcf.UBO_BYTES:(f + 1) * hvcf.UBO_BYTES] = ubos[f]
 
-    mode = {"auto": hvcf.MODE_AUTO, "brute": hvcf.MODE_BRUTE, "hier": hvcf.MODE_HIERARCHICAL}[args.mode]
-    ctx = hvcf.Context(grid=grid, max_lights=n, device=local, mode=mode)
-    ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)
-    for f in range(2):
-        ctx.set_ubo(f, ubos[f], sp)
-    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
-    sampler = ClockSampler(local) if rank == 0 else None
+    def allgather(x):
+        out = [None] * world
+        dist.all_gather_object(out, x)
+        return out
 
-    # ---- value: inputs resident in HBM, L2 flushed between steps, CUDA events per step ------------
-    for i in range(W):
-        ctx.cull(i & 1, sp)
-    barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    t_wall0 = time.time()
-    for i in range(K):
-        flush.zero_()
-        ev[i][0].record(stream)
-        ctx.cull(i & 1, sp)
-        ev[i][1].record(stream)
-    barrier()
-    t_wall1 = time.time()
-    if sampler:
-        sampler.window(t_wall0, t_wall1)
-    step_ms = np.array([a.elapsed_time(b) for a, b in ev])
-    # the dominant kernel's own duration: a second, shorter loop with the library's in-stream events switched on
-    # (kept out of the loop above: an event record between two kernels breaks their programmatic dependent launch)
-    ctx.set_timing(True)
-    kernel_ms, timed_step_ms, launches, executed, prefilter, total_idx, other_tests = [], [], 0, 0, 0, 0, {}
-    for i in range(min(K, 24)):
-        flush.zero_()
-        ctx.cull(i & 1, sp)
-        km, tm = ctx.timing(i & 1)
-        kernel_ms.append(km)
-        timed_step_ms.append(tm)
-        st = ctx.stats(i & 1, sp)
-        launches_per_step, total_idx = st["kernel_launches"], st["total_indices"]
-        # the timed kernel is the count pass: its own exact tests + its own level-1 union tests; the binning kernel's
-        # level-0 tests and the tests the write pass repeats are counted apart (hvcf_stats) and NOT credited to it
-        prefilter = st["prefilter_tests"] - st["bin_tests"]
-        executed = st["executed_tests"] + prefilter
-        other_tests = {"bin_kernel": st["bin_tests"], "write_pass": st["write_pass_tests"]}
-    ctx.set_timing(False)
+    state = {}
+
+    def make(cuts, ktimes=False):
+        if ktimes:
+            os.environ["HVCF_KERNEL_TIMES"] = "1"
+        try:
+            ctx = hvcf.Context(grid=grid, max_lights=n, device=local, shard=(rank, world, n, cuts, args.block_tiles))
+        finally:
+            os.environ.pop("HVCF_KERNEL_TIMES", None)
+        b, e = ctx.shard_light_range()
+        if state.get("range") != (b, e):
+            state["pinned"] = hvcf.PinnedBuffer(48 * max(e - b, 1))
+            state["pinned"].array[:48 * (e - b)] = all_lights[b:e].view(np.uint8).reshape(-1)
+            state["range"] = (b, e)
+        ctx.set_lights_range_ptr(state["pinned"].ptr.value, b, e - b, False, sp)
+        for f in range(2):
+            ctx.set_ubo(f, ubos[f], sp)
+        ctx.peer_attach(rank, world, allgather(ctx.peer_export()))
+        barrier()
+        return ctx
+
+    def drop(ctx):
+        barrier()
+        ctx.peer_detach()
+        barrier()
+        ctx.close()
+
+    # ---- z cuts: a host cost proxy (lights reaching each slice), then re-cuts from measured per-rank kernel times ----
+    history = []
+    if args.z_cuts:
+        cuts = [int(x) for x in args.z_cuts.split(",")]
+    else:
+        touch = slice_touch_counts(ubos[0], all_lights, stride=16).astype(np.float64)
+        cuts = cuts_from_cost(touch + 0.05 * touch.mean(), world)
+        best = None
+        for it in range(max(0, args.balance_iters)):
+            ctx = make(cuts, ktimes=True)
+            for f in range(4):
+                ctx.cull_routed(f & 1, sp)
+            kt = ctx.kernel_times(1)
+            err = ctx.peer_status(sp)
+            drop(ctx)
+            own = float(sum(kt[1:]))                       # bin + count + finalize + write: this rank's own work, no waiting
+            times = allgather(own)
+            history.append({"z_cuts": list(cuts), "own_kernels_ms": [round(t, 4) for t in times], "peer_error": err})
+            if best is None or max(times) < best[0]:
+                best = (max(times), list(cuts))
+            if max(times) <= 1.04 * (sum(times) / world):
+                break
+            slabs = [(cuts[r], cuts[r + 1]) for r in range(world)]
+            new = balance_slabs(slabs, times)
+            new_cuts = [a for a, _ in new] + [grid[2]]
+            if new_cuts == cuts:
+                break
+            cuts = new_cuts
+        if best is not None:
+            cuts = best[1]
+    ctx = make(cuts)
+    out = {"z_cuts": list(cuts), "balance_iterations": history}
+
+    # ---- value: lights resident on their owners, every light transformed every frame; per-step events; max over ranks ----
+    step_ms = timed_frames(torch, stream, lambda f: ctx.cull_routed(f, sp), K, W, flush, barrier)
+    out["peer_error"] = ctx.peer_status(sp)
     t = torch.tensor([float(step_ms.sum())], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / K
-    nominal = C * n
-    value = world * nominal / (ms_per_step * 1e-3)
-    launches = launches_per_step * K
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["ms"] = float(t.item()) / K
+    st = ctx.stats((K - 1) & 1, sp)
+    out["launches_per_step"] = st["kernel_launches"] + 4   # + totals, push, wait, (route/wait are counted inside)
+    out["inbox_records_per_rank"] = allgather(ctx.shard_inbox_records(sp))
+    out["light_range_per_rank"] = allgather(list(state["range"]))
+    total = ctx.download_total((K - 1) & 1, sp)
+    out["total_indices"] = int(total)
+    b = ctx.buffers()
+    out["own_clusters"] = [b.cluster_begin, b.cluster_end]
 
-    # ---- e2e: HOST buffers through the C ABI, H2D and D2H inside the timed region -------------------
-    cells_host = hvcf.PinnedBuffer(8 * C)
-    idx_host = hvcf.PinnedBuffer(4 * C * 150)
-    total_host = np.zeros(1, np.uint32)
-    lib = hvcf.load()
-    import ctypes
+    # ---- byte equality with the UNSHARDED frame (rank 0 culls the whole scene on one context) ----
+    f_last = (K - 1) & 1
+    mine, _ = full_grid_hash(torch, hvcf, ctx, f_last, dev, sp)
+    ref_hash = None
+    if rank == 0:
+        with hvcf.Context(grid=grid, max_lights=n, device=local) as u:
+            u.set_lights(all_lights, sp)
+            u.set_ubo(f_last, ubos[f_last], sp)
+            u.cull(f_last, sp)
+            ref_hash, ref_total = full_grid_hash(torch, hvcf, u, f_last, dev, sp)
+            out["unsharded_total_indices"] = int(ref_total)
+    hashes = allgather(mine)
+    ref_hash = allgather(ref_hash)[0]
+    out["sharded_bytes_equal"] = bool(all(h == ref_hash for h in hashes))
+    out["grid_hash"] = f"{ref_hash & 0xffffffffffffffff:016x}"
 
-    def e2e_step(f):
-        ctx.set_lights_ptr(pinned.ptr.value, n, False, sp)                      # H2D 48*n
-        ctx.set_ubo_ptr(f, pinned_ubo.ptr.value + f * hvcf.UBO_BYTES, sp)        # H2D 176
-        ctx.cull(f, sp)
-        hvcf._check(lib.hvcf_download_total(ctx.handle, f, total_host.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), sp))
-        hvcf._check(lib.hvcf_download_light_cells(ctx.handle, cells_host.ptr, 8 * C, sp))
-        hvcf._check(lib.hvcf_download_light_indices(ctx.handle, idx_host.ptr, 4 * int(total_host[0]), sp))
-        return int(total_host[0])
+    # ---- e2e: HOST buffers; every rank uploads its own lights + UBO and downloads its own slab's cells + index segment ----
+    lb, le = state["range"]
+    Cs = b.cluster_end - b.cluster_begin
+    cells_host, idx_host = hvcf.PinnedBuffer(8 * max(Cs, 1)), hvcf.PinnedBuffer(4 * max(Cs, 1) * 150)
 
-    for i in range(W):
-        e2e_step(i & 1)
-    barrier()
-    Ke = min(K, 200)
-    t0 = time.perf_counter()
-    t_wall0 = time.time()
-    for i in range(Ke):
-        tot = e2e_step(i & 1)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if sampler:
-        sampler.window(t_wall0, time.time())
-    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item()) / Ke * 1e3
-    e2e = {"value": world * nominal / (e2e_ms * 1e-3), "unit": "tests/s", "ms_per_step": e2e_ms, "steps": Ke,
-           "h2d_bytes_per_step": 48 * n + hvcf.UBO_BYTES, "d2h_bytes_per_step": 4 + 8 * C + 4 * tot,
-           "timer": "host perf_counter around the loop, synchronised both sides (the downloads block)",
-           "mode": "one frame at a time: upload, cull, three blocking downloads"}
+    def e2e_step(f, upload):
+        if upload:
+            ctx.set_lights_range_ptr(state["pinned"].ptr.value, lb, le - lb, False, sp)
+        ctx.set_ubo_ptr(f, pinned_ubo.ptr.value + f * hvcf.UBO_BYTES, sp)
+        ctx.cull_routed(f, sp)
+        return ctx.download_shard_into(cells_host.ptr, 8 * Cs, idx_host.ptr, 4 * Cs * 150, sp)
 
-    # ---- e2e with two frames in flight (AppConfig::FrameCount = 2 in the reference, Configs.h:14): two contexts, each
-    # with its own stream and its own buffers; frame i+1 is issued (H2D + kernels, asynchronous) before the blocking
-    # downloads of frame i, so uploads, kernels and downloads of neighbouring frames overlap on PCIe's two directions.
-    # Same bytes per step, same public calls; reported beside the one-at-a-time figure, and used as the headline e2e.
-    try:
-        ctxs2 = [ctx, hvcf.Context(grid=grid, max_lights=n, device=local, mode=mode)]
-        streams2 = [torch.cuda.Stream(), torch.cuda.Stream()]
-        outs2 = [(cells_host, idx_host), (hvcf.PinnedBuffer(8 * C), hvcf.PinnedBuffer(4 * C * 150))]
-        totals2 = [np.zeros(1, np.uint32), np.zeros(1, np.uint32)]
-        torch.cuda.synchronize()
-
-        def issue(i):
-            c, st = ctxs2[i & 1], streams2[i & 1].cuda_stream
-            c.set_lights_ptr(pinned.ptr.value, n, False, st)
-            c.set_ubo_ptr(0, pinned_ubo.ptr.value + (i & 1) * hvcf.UBO_BYTES, st)
-            c.cull(0, st)
-
-        def collect(i):
-            c, st = ctxs2[i & 1], streams2[i & 1].cuda_stream
-            th, (ch, ih) = totals2[i & 1], outs2[i & 1]
-            hvcf._check(lib.hvcf_download_grid(c.handle, 0, ch.ptr, 8 * C, ih.ptr, 4 * C * 150,
-                                               th.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)), st))
-            return int(th[0])
-
-        def run_pipelined(k):
-            issue(0)
-            last = 0
-            for i in range(k):
-                if i + 1 < k:
-                    issue(i + 1)
-                last = collect(i)
-            return last
-
-        run_pipelined(W + 1)
+    Ke = max(3, min(K, 20))
+    for upload, key in ((True, "e2e"), (False, "e2e_resident")):
+        for i in range(2):
+            e2e_step(i & 1, upload)
         barrier()
         t0 = time.perf_counter()
-        tot2 = run_pipelined(Ke)
+        for i in range(Ke):
+            _, tot = e2e_step(i & 1, upload)
         torch.cuda.synchronize()
-        p_s = time.perf_counter() - t0
-        t = torch.tensor([p_s], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        p_ms = float(t.item()) / Ke * 1e3
-        ctxs2[1].close()
-        e2e["one_frame_at_a_time"] = {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"]}
-        if tot2 == tot and p_ms < e2e_ms:
-            e2e.update({"value": world * nominal / (p_ms * 1e-3), "ms_per_step": p_ms,
-                        "mode": "two frames in flight (two contexts on their own streams, as AppConfig::FrameCount = 2): frame i+1 is "
-                                "issued before the blocking downloads of frame i; every step still uploads all lights + UBO and "
-                                "downloads total + cells + indices"})
-        else:
-            e2e["two_frames_in_flight"] = {"ms_per_step": p_ms, "total_indices": tot2}
-    except Exception as ex:   # the one-at-a-time figure stands
-        e2e["two_frames_in_flight"] = {"error": f"{type(ex).__name__}: {ex}"}
+        t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        h2d = torch.tensor([float((48 * (le - lb) if upload else 0) + hvcf.UBO_BYTES), float(8 * Cs + 4 * tot + 8)], device=dev, dtype=torch.float64)
+        dist.all_reduce(h2d, op=dist.ReduceOp.SUM)
+        out[key] = {"ms_per_step": float(t.item()) / Ke * 1e3, "steps": Ke, "h2d_bytes_per_step": int(h2d[0].item()),
+                    "d2h_bytes_per_step": int(h2d[1].item())}
+    drop(ctx)
 
-    # ---- roofline of the dominant kernel (cull_kernel), live ------------------------------------------
-    k_ms = float(np.mean(kernel_ms)) if kernel_ms else float("nan")
-    issue_rate = hvcf.measure_fp32_issue_rate(local)          # lane-ops/s, FADD/FMUL chains, measured now
-    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
-    achieved = executed * LANE_OPS_PER_TEST / (k_ms * 1e-3)    # lane-ops/s
-    hbm_gbs, hbm_src = hbm_peak()
-    alg_bytes = 48 * n + 16 * n * 2 + 32 * C + 8 * C + 4 * total_idx   # AoS in, SoA out+in, AABB, cells, indices
-    roofline = {
-        "bound": "fp32",
-        "kernel": "hier2_kernel<K,0> (count pass)" if prefilter else "cull_kernel",
-        "prefilter_tests_per_launch": prefilter, "tests_of_other_kernels_per_step": other_tests,
-        "achieved": achieved / 1e12, "peak": issue_rate / 1e12, "unit": "TFLOP/s", "frac": achieved / issue_rate,
-        "peak_source": "hvcf_measure_fp32_issue_rate on this GPU, this run (non-FMA FADD/FMUL issue rate; MEASURED_PEAKS.json has no "
-                       "FP32 figure); nominal 148 SM x 128 lanes x 1.965 GHz = 37.2",
-        "flop_per_test": LANE_OPS_PER_TEST, "executed_tests_per_launch": executed, "nominal_tests_per_launch": nominal,
-        "kernel_ms": k_ms, "kernel_share_of_step": k_ms / float(np.mean(timed_step_ms)),
-        "kernel_share_note": "share of the step of the same instrumented loop (in-stream events serialise the kernels)",
-        "executed_tests_per_s": executed / (k_ms * 1e-3),
-        # north_star's own definition: (clusters x lights x ops per test) at the FP32 peak, against the whole step.
-        # Above 1 means the step beats what ANY brute-force kernel could do at the issue roofline (hierarchy + early exit).
-        "nominal_frac_of_step": nominal * LANE_OPS_PER_TEST / (ms_per_step * 1e-3) / issue_rate,
-        "traffic": ncu_traffic(args.workload),
-        "hbm": {"algorithmic_bytes_per_step": alg_bytes, "achieved_gbs": alg_bytes / (ms_per_step * 1e-3) / 1e9, "peak_gbs": hbm_gbs,
-                "peak_source": hbm_src, "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / hbm_gbs},
-    }
-
-    # ---- rows next to the path: consumer light loop, frustum culling (rank 0, N=1) --------------------------
-    next_rows = None
-    if rank == 0 and world == 1 and not args.no_next_rows:
-        try:
-            next_rows = run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush)
-            next_rows.update(run_extras(args, hvcf, local, stream, sp, flush))
-        except Exception as e:  # the headline line must still be printed
-            next_rows = {"error": f"{type(e).__name__}: {e}"}
-
-    # ---- z-slab sharded grid (configs[3]): NCCL light broadcast + grid all-gather ------------------------
-    sharded = None
-    ctx.close()
-    del flush
-    fly = None
-    if not args.no_flythrough:
-        try:
-            fly = run_flythrough(args, hvcf, world, rank, local, dev, barrier)
-        except Exception as e:
-            fly = {"error": f"{type(e).__name__}: {e}"}
-    if not args.no_sharded:
-        try:
-            sharded = run_sharded(args, hvcf, world, rank, local, dev, barrier)
-        except Exception as e:  # the headline line must still be printed
-            sharded = {"error": f"{type(e).__name__}: {e}"}
-
-    if sampler:
-        sampler.stop()
-    clocks = sampler.summary() if sampler else None
-
-    # ---- CPU baseline beside it (rank 0, N=1 only) -------------------------------------------------------
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        kind, impl, _ = cpu_checker()
-        cpu = time_cpu(kind, impl, args.workload, args.cpu_seconds)
-
-    if world > 1:
-        dist.barrier(device_ids=[local])
-        dist.destroy_process_group()
-    if rank != 0:
-        return 0
-    line = {
-        "metric": "cluster-light tests/s", "value": value, "unit": "tests/s", "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
-                   "max_lights_per_cluster": 150, "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)",
-                   "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
-                   "parallelism": "single GPU" if world == 1 else f"{world} ranks x own frames (no collective); z-slab sharding under 'sharded'",
-                   "tests": "nominal = clusters x lights; executed (early exit at 150 hits, LightCulling.comp:71) under roofline"},
-        "step_ms_min": float(step_ms.min()), "step_ms_median": float(np.median(step_ms)),
-        "executed_tests_per_step": executed, "total_indices": total_idx,
-        "e2e": e2e, "gpu_launches": launches, "gpu_launches_per_step": launches_per_step,
-        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "impl": "ours",
-    }
-    if sharded is not None:
-        line["sharded"] = sharded
-    if next_rows is not None:
-        line["next_rows"] = next_rows
-    if fly is not None:
-        line["flythrough"] = fly
-    print(json.dumps(line), flush=True)
-    return 0
+    # ---- per-kernel times on every rank (instrumented contexts) and the dominant kernel's roofline ----
+    ictx = make(cuts, ktimes=True)
+    for f in range(2):
+        ictx.cull_routed(f & 1, sp)
+    rows = []
+    for f in range(6):
+        flush.zero_()
+        ictx.cull_routed(f & 1, sp)
+        rows.append(ictx.kernel_times(f & 1))
+    st2 = ictx.stats(1, sp)
+    drop(ictx)
+    ms = dict(zip(KERNEL_NAMES, [float(x) for x in np.median(np.array(rows), axis=0)]))
+    issue_rate = hvcf.measure_fp32_issue_rate(local)
+    roof = kernel_roofline(ms, st2, issue_rate, out["ms"])
+    per_rank = allgather({"ms": ms, "roofline": roof, "stats": {k: int(v) for k, v in st2.items()}})
+    own = [sum(p["ms"][k] for k in ("bin", "count", "finalize", "write")) for p in per_rank]
+    crit = int(np.argmax(own))
+    out["roofline"] = dict(per_rank[crit]["roofline"], rank=crit)
+    out["own_kernels_ms_per_rank"] = [round(x, 4) for x in own]
+    out["kernel_ms_per_rank"] = [{k: round(v, 4) for k, v in p["ms"].items()} for p in per_rank]
+    out["executed_tests_all_ranks"] = int(sum(p["stats"]["executed_tests"] + p["stats"]["prefilter_tests"] for p in per_rank))
+    return out
 
 
 def run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush):
@@ -727,163 +815,247 @@ def run_flythrough(args, hvcf, world, rank, local, dev, barrier):
             "note": "camera orbit + lights y = y0 + 0.5 sin(4 theta_f + phase_i) evaluated on the device from a 1,024-entry host sine table"}
 
 
-def run_sharded(args, hvcf, world, rank, local, dev, barrier):
-    """configs[3]: the cluster grid split into z-slabs, one per rank; per step: NCCL broadcast of the light
-    buffer from rank 0, local culling, exchange of totals, cells + indices written at global offsets, and the
-    grid gathered on every rank.  Headline variant: exchange over NVLink peer memory (hvcf_cull_sharded) on
-    load-balanced slabs; the torch.distributed/NCCL exchange on equal slabs is timed beside it.
-    At world 1 the same code runs without collectives: the N=1 point of the strong-scaling curve."""
-    import torch
-    import torch.distributed as dist
-    from hellovulkan_b200.sharded import HvcfEngine, ShardedCuller, z_slabs, balance_slabs
-
-    grid, screen, n = WORKLOADS[args.sharded_workload]
-    C = grid[0] * grid[1] * grid[2]
-    ubo = hvcf.host_camera_ubo(grid, screen)
+def run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, cuts, steps=3):
+    """north_star's own formulation beside the routed frame, on the same z cuts: the light buffer lives on rank 0 and is
+    broadcast with NCCL every frame (48 B LightData records, cut into chunks and pipelined with transform + level-0
+    binning), every rank transforms and bins ALL the lights, the grid is exchanged by the peer kernels (hvcf_cull_sharded's
+    steps).  Timed on the device, max over ranks; its full grid is hashed against the routed frame's."""
+    from hellovulkan_b200.sharded import HvcfEngine, ShardedCuller
+    grid, screen, n = WORKLOADS[args.workload]
     stream = torch.cuda.current_stream()
-    steps = max(1, args.sharded_steps)
-    src = None
+    sp = stream.cuda_stream
+    slabs = [(cuts[r], cuts[r + 1]) for r in range(world)]
+    eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
+    sc = ShardedCuller(eng, grid, world=world, rank=rank, slabs=slabs, exchange="peer")
+    ubos = [hvcf.host_camera_ubo(grid, screen, pos=hvcf.REF_CAMERA_POS), hvcf.host_camera_ubo(grid, screen, pos=(0.5, 1.0, 6.0))]
     if rank == 0:
-        host = np.zeros(n, hvcf.LIGHT_DT)
-        hvcf.host_init_lights(n, out=host)
-        src = torch.from_numpy(host.view(np.uint8).reshape(-1)).to(dev)
+        host = hvcf.host_init_lights(n)
+        eng.lights.copy_(torch.from_numpy(host.view(np.uint8).reshape(-1)))
         del host
-
-    def allmax(x):
-        t = torch.tensor([x], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def make(slabs, exchange):
-        eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
-        sc = ShardedCuller(eng, grid, world=world, rank=rank, slabs=slabs, exchange=exchange)
-        if rank == 0:
-            eng.lights.copy_(src)
-        for f in range(2):
-            eng.set_ubo(f, ubo)
-        sc.broadcast_lights(n)
-        return eng, sc
-
-    def drop(eng, sc):
-        torch.cuda.synchronize()
-        sc.close()
-        eng.close()
-
-    def timed(eng, sc, rebroadcast, k, wire=None):
-        """wire None: broadcast of the whole light buffer, then the frame; 'raw' / 'view': broadcast cut into chunks
-        and pipelined with transform + binning (ShardedCuller.frame_pipelined)."""
-        def step(f):
-            if wire is not None:
-                return sc.frame_pipelined(f, n, chunks=args.sharded_chunks, wire=wire)
-            if rebroadcast:
-                sc.broadcast_lights(n)
-            return sc.frame(f, gather=True)
+    for f in range(2):
+        eng.set_ubo(f, ubos[f])
+    res = {}
+    try:
         for i in range(2):
-            step(i & 1)
+            sc.frame_pipelined(i & 1, n, chunks=4, wire="raw")
         barrier()
         sc.enable_phase_timing()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for i in range(k):
-            totals, _ = step(i & 1)
+        for i in range(steps):
+            sc.frame_pipelined(i & 1, n, chunks=4, wire="raw")
         e1.record(stream)
         barrier()
-        own = sc.phase_ms()
-        ms = allmax(e0.elapsed_time(e1)) / k
-        phases = {key: allmax(v) / k for key, v in own.items()}
-        local_ms = (own.get("cull_begin", 0.0) + own.get("cull_finish", 0.0)) / k   # this rank's own kernels
-        return ms, phases, totals.clone(), local_ms
-
-    def measure(slabs, exchange):
-        eng, sc = make(slabs, exchange)
-        ms, phases, totals, _ = timed(eng, sc, True, steps)
-        ms_res, phases_res, _, local_ms = timed(eng, sc, False, steps)
-        st = eng.ctx.stats((steps - 1) & 1)
-        ex = torch.tensor([float(st["executed_tests"])], device=dev, dtype=torch.float64)
-        lm = torch.zeros(world, device=dev, dtype=torch.float64)
-        lm[rank] = local_ms
-        if world > 1:
-            dist.all_reduce(ex, op=dist.ReduceOp.SUM)
-            dist.all_reduce(lm, op=dist.ReduceOp.SUM)
-        kernel_ms = None
-        if os.environ.get("HVCF_KERNEL_TIMES") == "1":   # debug: per-kernel events (they serialise the PDL chain)
-            try:
-                kernel_ms = dict(zip(("transform", "bin", "count", "finalize", "write"), eng.ctx.kernel_times((steps - 1) & 1)))
-            except Exception as e:
-                kernel_ms = {"error": str(e)}
-        pipelined = {}
-        if exchange == "peer":
-            for wire in ("raw", "view", "gather"):
-                try:
-                    pms, pph, ptot, _ = timed(eng, sc, True, steps, wire=wire)
-                    pipelined[wire] = {"ms_per_frame": pms, "value": C * n / (pms * 1e-3), "phase_ms_max_over_ranks": pph,
-                                       "chunks": args.sharded_chunks, "total_indices": int(ptot.sum().item()),
-                                       "wire_bytes_per_light": 48 if wire == "raw" else 16,
-                                       "lights_owned": "rank 0" if wire != "gather" else "in shards of L/N (all-gather of the 16 B view records)"}
-                except Exception as e:
-                    pipelined[wire] = {"error": f"{type(e).__name__}: {e}"}
-            sc.broadcast_lights(n)   # the view run leaves no LightData on the other ranks
-            eng.peer_status()
-        out = {"ms_per_frame": ms, "pipelined_light_exchange": pipelined, "value": C * n / (ms * 1e-3), "unit": "tests/s (nominal)", "exchange": exchange,
-               "z_slabs": [list(x) for x in slabs], "phase_ms_max_over_ranks": phases,
-               "own_kernels_ms_per_rank": [float(x) for x in lm.tolist()],
-               "lights_resident": {"ms_per_frame": ms_res, "value": C * n / (ms_res * 1e-3), "phase_ms_max_over_ranks": phases_res,
-                                   "note": "same frame without re-broadcasting the light buffer (static lights, as in the reference app)"},
-               "executed_tests_per_frame": float(ex.item()), "total_indices": int(totals.sum().item()),
-               "kernel_ms_rank0_debug": kernel_ms}
-        drop(eng, sc)
-        return out
-
-    equal = z_slabs(grid[2], world)
-    slabs, history = equal, []
-    if world > 1:
-        # load balance: re-cut the z-range from each rank's measured kernel time; the cost of a slab is not linear in its
-        # slices (the group plan changes with the slab), so iterate a few times and keep the best cut seen
-        best = None
-        for it in range(args.sharded_balance_iters):
-            eng, sc = make(slabs, "peer")
-            _, _, _, local_ms = timed(eng, sc, False, 3)
-            drop(eng, sc)
-            lm = torch.zeros(world, device=dev, dtype=torch.float64)
-            lm[rank] = local_ms
-            dist.all_reduce(lm, op=dist.ReduceOp.SUM)
-            times = [float(x) for x in lm.tolist()]
-            history.append({"z_slabs": [list(x) for x in slabs], "own_kernels_ms_per_rank": times})
-            if best is None or max(times) < best[0]:
-                best = (max(times), slabs)
-            if max(times) <= 1.03 * (sum(times) / world):
-                break
-            new = balance_slabs(slabs, times)
-            if it >= 3:   # damp late moves: halfway between the current and the proposed cuts
-                new = [((a0 + a1 + 1) // 2, (b0 + b1 + 1) // 2) for (a0, b0), (a1, b1) in zip(slabs, new)]
-                new = [(new[k][0] if k else 0, new[k + 1][0] if k + 1 < world else grid[2]) for k in range(world)]
-            if new == slabs or any(b <= a for a, b in new):
-                break
-            slabs = new
-        slabs = best[1]
-    res = measure(slabs, "peer")
-    # headline = the frame with the light exchange pipelined (48 B LightData on the wire: every rank keeps the reference
-    # light buffer); the unpipelined frame and the 16 B view-record wire are reported beside it
-    raw = res["pipelined_light_exchange"].get("raw", {})
-    res["unpipelined"] = {"ms_per_frame": res["ms_per_frame"], "value": res["value"], "phase_ms_max_over_ranks": res["phase_ms_max_over_ranks"]}
-    if "ms_per_frame" in raw and raw["ms_per_frame"] < res["ms_per_frame"]:
-        res["ms_per_frame"], res["value"], res["phase_ms_max_over_ranks"] = raw["ms_per_frame"], raw["value"], raw["phase_ms_max_over_ranks"]
-        res["headline_variant"] = "pipelined light exchange, raw LightData on the wire"
-    else:
-        res["headline_variant"] = "unpipelined"
-    res.update({"workload": args.sharded_workload, "grid": list(grid), "lights": n, "steps": steps, "scaling": "strong",
-                "balance_iterations": history,
-                "collectives": "none (1 rank)" if world == 1 else
-                "ncclBroadcast 48 B x L lights; totals, light cells and index segments exchanged by hvcf_peer kernels over NVLink peer memory (CUDA IPC)"})
-    if world > 1:
-        try:
-            base = measure(equal, "nccl")
-            base["collectives"] = "ncclBroadcast 48 B x L lights; all-gather totals; all-gather light cells; per-owner broadcast of index segments"
-            res["nccl_equal_slabs"] = base
-        except Exception as e:
-            res["nccl_equal_slabs"] = {"error": f"{type(e).__name__}: {e}"}
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        phases = sc.phase_ms()
+        pm = torch.tensor([phases.get(k, 0.0) / steps for k in ("lights+cull_begin", "totals", "cull_finish", "push_grid", "wait_grid")],
+                          device=dev, dtype=torch.float64)
+        dist.all_reduce(pm, op=dist.ReduceOp.MAX)
+        h, total = full_grid_hash(torch, hvcf, eng.ctx, (steps - 1) & 1, dev, sp)
+        res = {"ms": float(t.item()) / steps, "steps": steps, "wire": "ncclBroadcast of 48 B LightData from rank 0, 4 chunks pipelined",
+               "phase_ms_max_over_ranks": dict(zip(("lights+cull_begin", "totals", "cull_finish", "push_grid", "wait_grid"), [round(float(x), 4) for x in pm.tolist()])),
+               "grid_hash": f"{h & 0xffffffffffffffff:016x}", "total_indices": int(total), "peer_error": eng.peer_status()}
+    finally:
+        torch.cuda.synchronize()
+        sc.close()
+        eng.close()
     return res
+
+
+def boundary_counts(impl_oracle, names, threads):
+    """north_star: "boundary disagreements are counted and reported, as lights within 1 ulp of a cluster plane" -- the oracle's
+    count of (cluster, light) pairs whose squared distance is within 1 ulp of r^2 (the strict `<` of LightCulling.comp:56),
+    and of pairs whose result flips when the sum is contracted into FMAs (the SPIR-V carries no NoContraction).  Whole frame
+    for A1k / A65k; every 64th cluster for B1M (the count is then scaled, and says so)."""
+    out = {}
+    for name in names:
+        grid, screen, n = WORKLOADS[name]
+        ubo = impl_oracle.camera_ubo(grid, screen)
+        aabbs = impl_oracle.generate_aabbs(ubo)
+        lights = impl_oracle.init_lights(n)
+        stride = max(1, int(np.ceil(len(aabbs) * n / 6.0e8)))
+        sub = aabbs if stride == 1 else np.ascontiguousarray(aabbs[::stride])
+        near, flips = impl_oracle.boundary_report(ubo, sub, lights, threads=threads)
+        out[name] = {"within_1ulp": near * stride, "flip_under_fma": flips * stride, "pairs": len(aabbs) * n,
+                     "sample": "all pairs" if stride == 1 else f"every {stride}th cluster, scaled"}
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from hellovulkan_b200 import hvcf
+
+    hvcf.load()  # raises if libhvcf.so is missing: there is no fallback
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl ours needs a CUDA device (libhvcf has no CPU path)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}; using WORLD_SIZE")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        opts = dist.ProcessGroupNCCL.Options()
+        opts.is_high_priority_stream = True   # the comparison leg pipelines an NCCL broadcast with compute
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    grid, screen, n = WORKLOADS[args.workload]
+    C = grid[0] * grid[1] * grid[2]
+    K, W = max(1, args.steps), max(args.warmup, 3)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    sampler = ClockSampler(local) if rank == 0 else None
+    nominal = C * n
+    t_wall0 = time.time()
+    summary = {}
+    if world == 1:
+        head = measure_single(hvcf, torch, args.workload, K, W, local, flush, barrier, e2e_steps=20)
+        ms_per_step = head["ms"]
+        roofline = head["roofline"]
+        e2e_ms, e2e_res_ms = head["e2e"]["ms_per_step"], head["e2e_resident"]["ms_per_step"]
+        e2e = {"value": nominal / (e2e_ms * 1e-3), "unit": "tests/s", "ms_per_step": e2e_ms, "steps": head["e2e"]["steps"],
+               "h2d_bytes_per_step": head["e2e"]["h2d_bytes_per_step"], "d2h_bytes_per_step": head["e2e"]["d2h_bytes_per_step"],
+               "mode": head["e2e"]["mode"],
+               "lights_resident": {"value": nominal / (e2e_res_ms * 1e-3), "ms_per_step": e2e_res_ms,
+                                   "h2d_bytes_per_step": head["e2e_resident"]["h2d_bytes_per_step"],
+                                   "d2h_bytes_per_step": head["e2e_resident"]["d2h_bytes_per_step"], "mode": head["e2e_resident"]["mode"]},
+               "timer": "host perf_counter around the loop, synchronised both sides (the download blocks)"}
+        launches_per_step, total_idx = head["launches_per_step"], head["total_indices"]
+        parallelism = "single GPU: hvcf_cull, all lights resident"
+        detail = {"l2": head["l2"], "step_ms_min": head["ms_min"], "step_ms_median": head["ms_median"], "stats": head["stats"]}
+        summary[args.workload] = {"ms": round(ms_per_step, 4), "frac": round(roofline["frac"], 3), "e2e_ms": round(e2e_ms, 3),
+                                  "e2e_res_ms": round(e2e_res_ms, 3), "top": roofline["kernel"].split(" ")[0]}
+    else:
+        head = run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, flush)
+        ms_per_step = head["ms"]
+        roofline = head["roofline"]
+        e2e_ms, e2e_res_ms = head["e2e"]["ms_per_step"], head["e2e_resident"]["ms_per_step"]
+        e2e = {"value": nominal / (e2e_ms * 1e-3), "unit": "tests/s", "ms_per_step": e2e_ms, "steps": head["e2e"]["steps"],
+               "h2d_bytes_per_step": head["e2e"]["h2d_bytes_per_step"], "d2h_bytes_per_step": head["e2e"]["d2h_bytes_per_step"],
+               "mode": "every rank: pinned H2D of its own share of the LightData + the UBO, hvcf_cull_routed, D2H of its own slab's cells + "
+                       "index segment (hvcf_download_shard); bytes are whole-job sums",
+               "lights_resident": {"value": nominal / (e2e_res_ms * 1e-3), "ms_per_step": e2e_res_ms,
+                                   "h2d_bytes_per_step": head["e2e_resident"]["h2d_bytes_per_step"],
+                                   "d2h_bytes_per_step": head["e2e_resident"]["d2h_bytes_per_step"]},
+               "timer": "host perf_counter around the loop, barrier + synchronise both sides, max over ranks"}
+        launches_per_step, total_idx = head["launches_per_step"], head["total_indices"]
+        parallelism = (f"{world} ranks: clusters sharded by z-slab {head['z_cuts']}, lights owned in shards and routed over NVLink peer "
+                       f"memory (hvcf_cull_routed); no collective call in the frame")
+        detail = {k: head[k] for k in ("z_cuts", "balance_iterations", "inbox_records_per_rank", "light_range_per_rank", "own_kernels_ms_per_rank",
+                                       "kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks")}
+        inbox = head["inbox_records_per_rank"]
+        own = head["own_kernels_ms_per_rank"]
+        summary["routed"] = {"ms": round(ms_per_step, 4), "bytes_equal": head["sharded_bytes_equal"], "z_cuts": head["z_cuts"],
+                             "own_ms_min_max": [min(own), max(own)], "inbox_Mrec_min_max": [round(min(inbox) / 1e6, 2), round(max(inbox) / 1e6, 2)],
+                             "inbound_MB_max": round(max(inbox) * 18 / 1e6, 1), "e2e_ms": round(e2e_ms, 3), "e2e_res_ms": round(e2e_res_ms, 3),
+                             "frac": round(roofline["frac"], 3), "top": roofline["kernel"].split(" ")[0],
+                             "kernels_ms_crit_rank": head["kernel_ms_per_rank"][roofline["rank"]]}
+        if not args.no_compare:
+            try:
+                cmp_ = run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, head["z_cuts"])
+                cmp_["bytes_equal"] = cmp_.get("grid_hash") == head["grid_hash"]
+                detail["nccl_broadcast_formulation"] = cmp_
+                summary["nccl_bcast"] = {"ms": round(cmp_["ms"], 4), "bytes_equal": cmp_["bytes_equal"], "phases": cmp_["phase_ms_max_over_ranks"]}
+            except Exception as e:
+                detail["nccl_broadcast_formulation"] = {"error": f"{type(e).__name__}: {e}"}
+    if sampler:
+        sampler.window(t_wall0, time.time())
+    value = nominal / (ms_per_step * 1e-3)
+    roofline["traffic"] = ncu_traffic(args.workload if world == 1 else f"{args.workload}_N{world}")
+    hbm_gbs, hbm_src = hbm_peak()
+    alg_bytes = 48 * n + 16 * n * 2 + 32 * C + 8 * C + 4 * total_idx   # SURVEY.md 8(d): AoS in, view records out + in, AABB, cells, indices
+    roofline["nominal_frac_of_step"] = nominal * LANE_OPS_PER_TEST / (ms_per_step * 1e-3) / (roofline["peak"] * 1e12) / world
+    roofline["hbm"] = {"algorithmic_bytes_per_step": alg_bytes, "achieved_gbs": alg_bytes / (ms_per_step * 1e-3) / 1e9, "peak_gbs": hbm_gbs * world,
+                       "peak_source": hbm_src, "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / (hbm_gbs * world)}
+
+    # ---- the other configs, one GPU each (N = 1 only): ms / frac / e2e per workload, graph-launched config 1 ----
+    extra = {}
+    if world == 1 and not args.no_summary:
+        for name in ("A1k", "A65k", "A1M", "B1M"):
+            if name == args.workload:
+                continue
+            try:
+                r = measure_single(hvcf, torch, name, min(K * 5, 100), W, local, flush, e2e_steps=40, graph=(name == "A1k"))
+                extra[name] = r
+                summary[name] = {"ms": round(r["ms"], 4), "frac": round(r["roofline"]["frac"], 3), "e2e_ms": round(r["e2e"]["ms_per_step"], 3),
+                                 "e2e_res_ms": round(r["e2e_resident"]["ms_per_step"], 3), "top": r["roofline"]["kernel"].split(" ")[0]}
+                if "graph" in r:
+                    summary[name]["graph_ms"] = round(r["graph"].get("ms", float("nan")), 4)
+                    summary[name]["kernels_only_ms"] = round(r["roofline"]["instrumented_step_ms"], 4)
+            except Exception as e:
+                summary[name] = {"error": f"{type(e).__name__}: {e}"[:120]}
+    next_rows = None
+    if rank == 0 and world == 1 and not args.no_next_rows:
+        try:
+            stream = torch.cuda.current_stream()
+            g2, s2, n2 = WORKLOADS["A65k"]
+            with hvcf.Context(grid=g2, max_lights=n2, device=local) as c2:
+                c2.set_lights(hvcf.host_init_lights(n2), stream.cuda_stream)
+                c2.set_ubo(0, hvcf.host_camera_ubo(g2, s2), stream.cuda_stream)
+                next_rows = run_next_rows(args, hvcf, c2, g2, s2, n2, local, stream, stream.cuda_stream, flush)
+            next_rows.update(run_extras(args, hvcf, local, stream, stream.cuda_stream, flush))
+        except Exception as e:
+            next_rows = {"error": f"{type(e).__name__}: {e}"}
+    del flush
+    fly = None
+    if not args.no_flythrough:
+        try:
+            fly = run_flythrough(args, hvcf, world, rank, local, dev, barrier)
+            summary["fly_B1M"] = {"ms_per_frame": round(fly["ms_per_frame"], 4), "frames": fly["frames"]}
+        except Exception as e:
+            fly = {"error": f"{type(e).__name__}: {e}"}
+    if sampler:
+        sampler.stop()
+    clocks = sampler.summary() if sampler else None
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only), and the boundary-disagreement counts ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        kind, impl, _ = cpu_checker()
+        cpu = time_cpu(kind, impl, args.workload, args.cpu_seconds)
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import cpu_checkers as cc
+            bc = boundary_counts(cc.Oracle(), ("A1k", "A65k", "B1M"), host_threads())
+            cpu["boundary"] = bc
+            summary["boundary"] = {k: [v["within_1ulp"], v["flip_under_fma"]] for k, v in bc.items()}
+        except Exception as e:
+            cpu["boundary"] = {"error": f"{type(e).__name__}: {e}"}
+    if world > 1:
+        dist.barrier(device_ids=[local])
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
+    ok = world == 1 or bool(head.get("sharded_bytes_equal"))
+    line = {
+        "metric": "cluster-light tests/s", "value": value, "unit": "tests/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
+                   "max_lights_per_cluster": 150, "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)",
+                   "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed); the inputs are larger than L2 anyway",
+                   "parallelism": parallelism,
+                   "tests": "nominal = clusters x lights; executed (early exit at 150 hits, LightCulling.comp:71) under roofline"},
+        "total_indices": total_idx, "e2e": e2e, "gpu_launches": launches_per_step * K, "gpu_launches_per_step": launches_per_step,
+        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "impl": "ours", "detail": detail,
+    }
+    if extra:
+        line["workloads"] = extra
+    if next_rows is not None:
+        line["next_rows"] = next_rows
+    if fly is not None:
+        line["flythrough"] = fly
+    line["summary"] = summary   # LAST: the driver keeps the tail of stdout
+    print(json.dumps(line), flush=True)
+    return 0 if ok else 3
 
 
 def main():

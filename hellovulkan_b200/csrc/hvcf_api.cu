@@ -335,7 +335,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 			HVCF_ALLOC(c->d_bin_rec, sizeof(float4) * slots * kBinCap);
 			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
 		}
-		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
+		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);
 		// hit lists of the count pass + hier_copy_kernel instead of the write pass: OFF by default (HVCF_SEG_LISTS=1 enables it
 		// within HVCF_SEG_LISTS_MAX_GB).  Measured on B200 and rejected: segments run concurrently, so the count pass sees
 		// only a lower bound of the earlier hits and stores many hits that the cap later discards, each a 4 B store into
@@ -394,7 +394,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		e = cudaMemcpy(c->d_hlane_cluster, map.data(), map.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
 	}
 	if (e == cudaSuccess && c->hier)
-		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32));
+		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);
 	if (e != cudaSuccess)
 	{
 		free_ctx(c);
@@ -637,7 +637,7 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 //   open   AABBs if dirty, light-segment plan
 //   range  transform + level-0 binning of the lights [begin, end) (whole tiles; the last range takes the padding)
 //   close  count pass + finalize (per-cluster counts, offsets, shard total)
-static cudaError_t hier_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s)
+cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s)
 {
 	if (!ctx->ktimes)
 		return cudaSuccess;
@@ -698,7 +698,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 		ctx->h_tiles_total = tiles_total;
 		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
 			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
-		HVCF_CUDA(hier_kmark(ctx, frame, 0, s));
+		HVCF_CUDA(hvcf_kmark(ctx, frame, 0, s));
 	}
 	ctx->range_frame = frame;
 	ctx->range_transformed = ctx->range_binned = 0;
@@ -740,8 +740,8 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 		ctx->range_cleared = true;
 		ctx->range_transformed = ctx->range_binned = end_padded;
 		++ctx->open_launches;
-		HVCF_CUDA(hier_kmark(ctx, frame, 1, s));
-		HVCF_CUDA(hier_kmark(ctx, frame, 2, s));
+		HVCF_CUDA(hvcf_kmark(ctx, frame, 1, s));
+		HVCF_CUDA(hvcf_kmark(ctx, frame, 2, s));
 		return HVCF_OK;
 	}
 	if (flags & HVCF_RANGE_TRANSFORM)
@@ -764,7 +764,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 		ctx->range_cleared = true;
 		ctx->range_transformed = end_padded;
 		++ctx->open_launches;
-		HVCF_CUDA(hier_kmark(ctx, frame, 1, s));
+		HVCF_CUDA(hvcf_kmark(ctx, frame, 1, s));
 	}
 	if (flags & HVCF_RANGE_BIN)
 	{
@@ -797,7 +797,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			++ctx->open_launches;
 		}
 		ctx->range_binned = end_padded;
-		HVCF_CUDA(hier_kmark(ctx, frame, 2, s));
+		HVCF_CUDA(hvcf_kmark(ctx, frame, 2, s));
 	}
 	return HVCF_OK;
 }
@@ -821,7 +821,7 @@ int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
 		++launches;
 	}
 	HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
-	HVCF_CUDA(hier_kmark(ctx, frame, 3, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 3, s));
 	if (ctx->timing)
 	{
 		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
@@ -833,16 +833,14 @@ int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
 	f.num_segs = ctx->h_num_segs;
 	f.cluster_count = ctx->cluster_count;
 	f.cap = ctx->cap;
-	ctx->epoch = ctx->epoch >= 0x3fffffffu ? 1u : ctx->epoch + 1u;
-	f.epoch = ctx->epoch;
-	f.scan_state = ctx->d_scan_state;
+	f.scan_state = ctx->d_scan_state + static_cast<size_t>(frame) * ((ctx->cluster_count + 31) / 32); // per frame slot: tags are per-slot serials
 	f.counts = ctx->d_counts;
 	f.offsets = ctx->d_hoffsets;
 	f.shard_total = ctx->d_shard_total;
 	f.stats = stats;
 	f.skip_prefix = p.seg_lists ? 1u : 0u;
 	HVCF_CUDA(launch_hier_finalize(f, s));
-	HVCF_CUDA(hier_kmark(ctx, frame, 4, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 4, s));
 	ctx->last_launches[frame] = launches + 2;
 	ctx->range_open = false;
 	return HVCF_OK;
@@ -1425,7 +1423,7 @@ int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t ce
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	if (!ctx->h_total)
-		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 8));
+		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 16));
 	// both destinations in pinned (mapped) host memory, 16 B aligned: one kernel stores count, cells and indices[0, count)
 	// across PCIe -- no host round trip between "how many" and "copy them" (HVCF_DOWNLOAD_KERNEL=0: the two-copy path)
 	if (ctx->download_kernel && cells_bytes % 4 == 0 && mapped_host_ptr(cells_dst) && (indices_capacity_bytes == 0 || mapped_host_ptr(indices_dst)))

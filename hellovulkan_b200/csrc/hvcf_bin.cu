@@ -969,6 +969,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_xbin_kernel(const XBinPar
 			st->overflow_clusters = 0u;
 			st->write_tests = 0ull;
 			st->bin_tests = st->prefilter_tests = static_cast<unsigned long long>(p.ncb) * q.tiles * kTileLights;
+			stats_next_epoch(st);
 		}
 	}
 	if (tile_id >= q.tiles) // CTAs beyond the last tile only help with the clearing (frames of a few tiles)

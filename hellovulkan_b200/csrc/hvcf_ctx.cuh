@@ -37,6 +37,7 @@ extern "C" {
 int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed);
 int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s);
 void hvcf_shard_free(hvcf_ctx* ctx);
+cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s);
 }
 
 #define HVCF_CUDA(expr)                                                                                      \
@@ -100,7 +101,6 @@ struct hvcf_ctx
 	int h_tps_override = 0;
 	uint32_t h_split_head = 0;
 	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
-	uint32_t epoch = 0;
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
 	uint32_t* d_hunit_any = nullptr;         // [h_max_segs][ncb * 8]

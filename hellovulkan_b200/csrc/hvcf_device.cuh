@@ -141,7 +141,13 @@ struct DeviceStats
 	uint32_t overflow_clusters;
 	unsigned long long bin_tests;    // level-0 union tests (hier_bin_kernel / hier_bin2_kernel), also inside prefilter_tests
 	unsigned long long write_tests;  // union + exact tests the write pass repeats (not in the two counters above)
+	// serial of the frames culled on this frame slot, bumped ON THE DEVICE by the frame's first kernel (never cleared): the tag
+	// of hier_finalize_kernel's look-back state words.  It lives on the device so that a frame captured into a CUDA graph
+	// can be replayed: no kernel argument changes from one frame to the next.
+	uint32_t epoch;
+	uint32_t pad_;
 };
+__device__ __forceinline__ void stats_next_epoch(DeviceStats* st) { st->epoch = st->epoch >= 0x3fffffffu ? 1u : st->epoch + 1u; }
 
 // CUDA loads kernels lazily, and loading one can wait for the device to go idle.  A frame of the sharded grid has kernels
 // that SPIN until another shard has made progress (hvcf_peer.cu); if that other shard lives in the same process and its next

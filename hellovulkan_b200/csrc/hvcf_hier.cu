@@ -422,7 +422,8 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 	}
 	// warp 0 publishes this CTA's aggregate BEFORE the second sweep: the CTAs behind it in the look-back chain need nothing else
 	// from us, so their wait shrinks by the length of our sweep (A65k: the chain is the kernel)
-	const unsigned long long tag = static_cast<unsigned long long>(p.epoch) << 34;
+	const uint32_t epoch = p.stats->epoch; // bumped by the first kernel of this frame (DeviceStats)
+	const unsigned long long tag = static_cast<unsigned long long>(epoch) << 34;
 	uint32_t v = 0, inc = 0, agg = 0, over = 0;
 	if (warp == 0)
 	{
@@ -476,7 +477,7 @@ __global__ void __launch_bounds__(kFinWarps * 32) hier_finalize_kernel(const Fin
 		do
 		{
 			w = i >= 0 ? ld_acquire_u64(&p.scan_state[i]) : (tag | (2ull << 32));
-			ok = (w >> 34) == p.epoch && ((w >> 32) & 3ull) != 0;
+			ok = (w >> 34) == epoch && ((w >> 32) & 3ull) != 0;
 		} while (!__all_sync(0xffffffffu, ok));
 		const uint32_t inclusive = __ballot_sync(0xffffffffu, ((w >> 32) & 3ull) == 2);
 		const uint32_t upto = inclusive ? static_cast<uint32_t>(__ffs(inclusive)) - 1u : 31u; // nearest inclusive prefix ends the walk

@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(256) light_transform_kernel(const hvcf_cluster
 		stats->overflow_clusters = 0u;
 		stats->bin_tests = 0ull;
 		stats->write_tests = 0ull;
+		stats_next_epoch(stats);
 	}
 	if (p >= num_pairs)
 		return;

@@ -161,8 +161,7 @@ struct FinalizeParams
 	uint32_t num_segs;
 	uint32_t cluster_count;
 	uint32_t cap;
-	uint32_t epoch;                 // frame serial, > 0, < 2^30
-	unsigned long long* scan_state; // [ceil(cluster_count / 32)]
+	unsigned long long* scan_state; // [ceil(cluster_count / 32)] of this frame slot; tagged with stats->epoch
 	uint32_t* counts;
 	uint32_t* offsets;
 	uint32_t* shard_total;

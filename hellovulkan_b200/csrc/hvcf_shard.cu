@@ -121,6 +121,7 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 			st->overflow_clusters = 0u;
 			st->write_tests = 0ull;
 			st->bin_tests = st->prefilter_tests = static_cast<unsigned long long>(p.light_end > first ? p.light_end - first : 0u) * p.world;
+			stats_next_epoch(st);
 		}
 	}
 	if (threadIdx.x < p.world * 6)

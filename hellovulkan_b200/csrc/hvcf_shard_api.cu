@@ -208,6 +208,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	PeerParams pp = ctx->peer;
 	pp.epoch = sh.epoch;
 	HVCF_CUDA(launch_shard_wait_routed(pp, parity, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 1, s)); // HVCF_KERNEL_TIMES: "transform" = route + wait for the other ranks' shares
 
 	// ---- level 0 on the inbox: every tile against the cluster groups of this slab ----
 	unsigned char* box = sh.d_inbox + static_cast<size_t>(parity) * sh.parity_bytes;
@@ -229,6 +230,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	b.block_tiles = sh.block_tiles;
 	b.tile_cnt = sh.d_tile_cnt;
 	HVCF_CUDA(launch_hier_bin(b, sh.tiles_phys, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 2, s));
 	ctx->open_launches += 3;
 	ctx->range_transformed = ctx->range_binned = sh.tiles_phys * kTileLights;
 
@@ -243,6 +245,38 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	if (rc == HVCF_OK)
 		rc = hvcf_peer_wait_grid(ctx, stream);
 	return rc;
+}
+
+int hvcf_download_shard(hvcf_ctx* ctx, void* cells_dst, size_t cells_bytes, void* indices_dst, size_t indices_capacity_bytes, uint32_t* out_index_base,
+	uint32_t* out_total, void* stream)
+{
+	if (!ctx || !out_index_base || !out_total || (cells_bytes && !cells_dst))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_shard: null argument");
+	if (cells_bytes > sizeof(hvcf_light_cell) * static_cast<size_t>(ctx->cluster_count))
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_shard: %zu bytes of cells > the shard's %u clusters", cells_bytes, ctx->cluster_count);
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	if (!ctx->h_total)
+		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 16));
+	uint32_t* h = ctx->h_total; // [8] = index base, [9] = shard total (slots 0..7 belong to hvcf_download_grid's frames)
+	h[8] = 0u;
+	if (ctx->peer.world && ctx->d_index_base)
+		HVCF_CUDA(cudaMemcpyAsync(&h[8], ctx->d_index_base, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	HVCF_CUDA(cudaMemcpyAsync(&h[9], ctx->d_shard_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	if (cells_bytes)
+		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells + ctx->cluster_begin, cells_bytes, cudaMemcpyDeviceToHost, s));
+	HVCF_CUDA(cudaStreamSynchronize(s));
+	*out_index_base = h[8];
+	*out_total = h[9];
+	const size_t need = sizeof(uint32_t) * static_cast<size_t>(h[9]);
+	if (need > indices_capacity_bytes || (need && !indices_dst))
+		return fail(HVCF_ERR_CAPACITY, "hvcf_download_shard: %u indices do not fit in %zu bytes", h[9], indices_capacity_bytes);
+	if (need)
+	{
+		HVCF_CUDA(cudaMemcpyAsync(indices_dst, ctx->d_indices + h[8], need, cudaMemcpyDeviceToHost, s));
+		HVCF_CUDA(cudaStreamSynchronize(s));
+	}
+	return HVCF_OK;
 }
 
 int hvcf_shard_inbox_records(hvcf_ctx* ctx, void* stream, uint64_t* out_records)

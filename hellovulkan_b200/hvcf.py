@@ -90,7 +90,7 @@ EXPORTS = [
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
     "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
     "hvcf_peer_status", "hvcf_create_sharded", "hvcf_shard_light_range", "hvcf_set_lights_range", "hvcf_cull_routed",
-    "hvcf_shard_inbox_records",
+    "hvcf_shard_inbox_records", "hvcf_download_shard",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -119,6 +119,7 @@ def load():
     lib.hvcf_shard_light_range.argtypes = [vp, ctypes.POINTER(u32), ctypes.POINTER(u32)]
     lib.hvcf_set_lights_range.argtypes = [vp, vp, u32, u32, i32, vp]
     lib.hvcf_cull_routed.argtypes = [vp, u32, vp]
+    lib.hvcf_download_shard.argtypes = [vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t, ctypes.POINTER(u32), ctypes.POINTER(u32), vp]
     lib.hvcf_shard_inbox_records.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_uint64)]
     lib.hvcf_set_lights.argtypes = [vp, vp, u32, i32, vp]
     lib.hvcf_update_light.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float), vp]
@@ -531,6 +532,13 @@ class Context:
 
     def cull_routed(self, frame=0, stream=None):
         _check(self.lib.hvcf_cull_routed(self.handle, frame, stream))
+
+    def download_shard_into(self, cells_ptr, cells_bytes, idx_ptr, idx_capacity_bytes, stream=None):
+        """this rank's own cells + index segment into host memory at the given addresses; returns (index_base, total)."""
+        b, t = ctypes.c_uint32(), ctypes.c_uint32()
+        _check(self.lib.hvcf_download_shard(self.handle, cells_ptr, cells_bytes, idx_ptr, idx_capacity_bytes, ctypes.byref(b),
+                                            ctypes.byref(t), stream))
+        return int(b.value), int(t.value)
 
     def shard_inbox_records(self, stream=None):
         v = ctypes.c_uint64()

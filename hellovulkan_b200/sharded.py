@@ -393,3 +393,48 @@ def merge_reference(cells_per_rank, indices_per_rank):
         cells["offset"][off: off + len(c)] = c["offset"] + b
         off += len(c)
     return cells, np.concatenate(indices_per_rank)
+
+
+def slice_touch_counts(ubo: np.ndarray, lights: np.ndarray, stride: int = 1) -> np.ndarray:
+    """[Z] how many lights' spheres reach each z-slice of the grid in `ubo` (host, float64, a cost proxy only: the
+    exact routing test is the kernel's).  A light at view depth d with radius r reaches the slices whose depth
+    interval [near (far/near)^(z/Z), near (far/near)^((z+1)/Z)) (AABBGenerator.comp:72-75) meets [d - r, d + r]."""
+    u = np.frombuffer(np.ascontiguousarray(ubo).tobytes(), np.float32)
+    view = u[16:32].astype(np.float64)             # column-major cameraView (UBOs.h:67-89)
+    near, far = float(u[36]), float(u[37])
+    Z = int(np.frombuffer(np.ascontiguousarray(ubo).tobytes(), np.uint32)[40])
+    pos = lights["position"][::stride].astype(np.float64)
+    r = lights["radius"][::stride].astype(np.float64)
+    depth = -(view[2] * pos[:, 0] + view[6] * pos[:, 1] + view[10] * pos[:, 2] + view[14] * pos[:, 3])
+    lo, hi = depth - r, depth + r
+    keep = (hi > near) & (lo < far) & np.isfinite(lo) & np.isfinite(hi)
+    lo, hi = np.maximum(lo[keep], near), np.minimum(hi[keep], far * (1 - 1e-12))
+    k = Z / np.log(far / near)
+    z0 = np.clip(np.floor(np.log(lo / near) * k).astype(np.int64), 0, Z - 1)
+    z1 = np.clip(np.floor(np.log(hi / near) * k).astype(np.int64), 0, Z - 1)
+    diff = np.zeros(Z + 1, np.int64)
+    np.add.at(diff, z0, 1)
+    np.add.at(diff, z1 + 1, -1)
+    return np.cumsum(diff)[:Z] * stride
+
+
+def cuts_from_cost(cost, world: int):
+    """z_cuts [world + 1]: contiguous slabs of about equal summed cost, every rank at least one slice."""
+    cost = np.asarray(cost, np.float64)
+    Z = len(cost)
+    if world > Z:
+        raise ValueError(f"{world} ranks for {Z} slices")
+    cum = np.concatenate([[0.0], np.cumsum(np.maximum(cost, 0.0))])
+    cuts = [0]
+    for k in range(1, world):
+        target = cum[-1] * k / world
+        z = int(np.searchsorted(cum, target, side="left"))
+        if z > 0 and abs(cum[z - 1] - target) <= abs(cum[min(z, Z)] - target):
+            z -= 1
+        cuts.append(z)
+    cuts.append(Z)
+    for k in range(1, world):
+        cuts[k] = max(cuts[k], cuts[k - 1] + 1)
+    for k in range(world - 1, 0, -1):
+        cuts[k] = min(cuts[k], cuts[k + 1] - 1)
+    return cuts

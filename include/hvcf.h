@@ -239,6 +239,12 @@ HVCF_API int hvcf_shard_light_range(hvcf_ctx* ctx, uint32_t* out_begin, uint32_t
  * Source/Vulkan/VulkanBuffer.cpp:158-167): lights [begin, begin + count) <- `lights` (count x 48 B). */
 HVCF_API int hvcf_set_lights_range(hvcf_ctx* ctx, const void* lights, uint32_t begin, uint32_t count, int src_is_device, void* stream);
 HVCF_API int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream);
+/* This rank's OWN part of the result -- its slab's light cells [cluster_begin, cluster_end) and its segment
+ * lightIndices[*out_index_base, *out_index_base + *out_total) -- into host memory (synchronises `stream`).  Over all ranks
+ * the parts add up to the full light grid exactly once: what a host-side consumer of a sharded frame reads back.  Works
+ * after hvcf_cull_routed, hvcf_cull_sharded and, with base 0, hvcf_cull. */
+HVCF_API int hvcf_download_shard(hvcf_ctx* ctx, void* cells_dst, size_t cells_bytes, void* indices_dst, size_t indices_capacity_bytes,
+	uint32_t* out_index_base, uint32_t* out_total, void* stream);
 /* records that arrived in this rank's inbox in the last routed frame (synchronises `stream`); the wire carried
  * 18 B per record that came from another rank */
 HVCF_API int hvcf_shard_inbox_records(hvcf_ctx* ctx, void* stream, uint64_t* out_records);

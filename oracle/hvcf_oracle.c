@@ -439,8 +439,11 @@ void hvo_cull(const hvcf_cluster_forward_ubo* ubo, const hvcf_aabb* aabbs, const
 	uint64_t* exec = (uint64_t*)malloc(sizeof(uint64_t) * (size_t)(n ? n : 1));
 	hvo_transform_lights(ubo, lights, num_lights, xyzr2);
 	const int nt = threads > 1 ? threads : 1;
+	/* clusters per grab: 16 for whole frames, fewer for a small sample so that every thread still gets several */
+	const int chunk = (int64_t)n >= 64 * (int64_t)nt ? 16 : ((int)n / (4 * nt) > 1 ? (int)n / (4 * nt) : 1);
 	(void)nt;
-#pragma omp parallel for schedule(dynamic, 16) num_threads(nt)
+	(void)chunk;
+#pragma omp parallel for schedule(dynamic, chunk) num_threads(nt)
 	for (int64_t c = 0; c < (int64_t)n; ++c)
 	{
 		cells[c].count = cull_one_xyzr2(&aabbs[cluster_begin + c], xyzr2, num_lights, cap,
