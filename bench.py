@@ -336,11 +336,13 @@ def timed_frames(torch, stream, run_frame, K, W, flush, barrier):
     return np.array([a.elapsed_time(b) for a, b in ev])
 
 
-def measure_single(hvcf, torch, name, K, W, local, flush_all, barrier=lambda: None, e2e_steps=50, graph=False):
+def measure_single(hvcf, torch, name, K, W, local, flush_all, barrier=None, e2e_steps=50, graph=False):
     """One workload on ONE GPU through the C ABI: device-timed frame, per-kernel times + roofline of the dominant kernel,
     e2e with host buffers (everything uploaded every step) and with the lights resident (what the reference app does per
     frame: UBO up, AppPBRClusterForward.cpp:120-136; here plus the grid down)."""
     import ctypes
+    if barrier is None:
+        barrier = torch.cuda.synchronize
     grid, screen, n = WORKLOADS[name]
     C = grid[0] * grid[1] * grid[2]
     stream = torch.cuda.current_stream()
