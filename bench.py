@@ -817,7 +817,7 @@ def run_flythrough(args, hvcf, world, rank, local, dev, barrier):
             "note": "camera orbit + lights y = y0 + 0.5 sin(4 theta_f + phase_i) evaluated on the device from a 1,024-entry host sine table"}
 
 
-def run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, cuts, steps=3):
+def run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, cuts, f_last, steps=3):
     """north_star's own formulation beside the routed frame, on the same z cuts: the light buffer lives on rank 0 and is
     broadcast with NCCL every frame (48 B LightData records, cut into chunks and pipelined with transform + level-0
     binning), every rank transforms and bins ALL the lights, the grid is exchanged by the peer kernels (hvcf_cull_sharded's
@@ -854,7 +854,10 @@ def run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, 
         pm = torch.tensor([phases.get(k, 0.0) / steps for k in ("lights+cull_begin", "totals", "cull_finish", "push_grid", "wait_grid")],
                           device=dev, dtype=torch.float64)
         dist.all_reduce(pm, op=dist.ReduceOp.MAX)
-        h, total = full_grid_hash(torch, hvcf, eng.ctx, (steps - 1) & 1, dev, sp)
+        sc._marks = None
+        sc.frame_pipelined(f_last, n, chunks=4, wire="raw")   # the frame slot (camera) whose grid the routed frame hashed
+        barrier()
+        h, total = full_grid_hash(torch, hvcf, eng.ctx, f_last, dev, sp)
         res = {"ms": float(t.item()) / steps, "steps": steps, "wire": "ncclBroadcast of 48 B LightData from rank 0, 4 chunks pipelined",
                "phase_ms_max_over_ranks": dict(zip(("lights+cull_begin", "totals", "cull_finish", "push_grid", "wait_grid"), [round(float(x), 4) for x in pm.tolist()])),
                "grid_hash": f"{h & 0xffffffffffffffff:016x}", "total_indices": int(total), "peer_error": eng.peer_status()}
@@ -962,7 +965,7 @@ def run_ours(args):
                              "kernels_ms_crit_rank": head["kernel_ms_per_rank"][roofline["rank"]]}
         if not args.no_compare:
             try:
-                cmp_ = run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, head["z_cuts"])
+                cmp_ = run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, head["z_cuts"], (K - 1) & 1)
                 cmp_["bytes_equal"] = cmp_.get("grid_hash") == head["grid_hash"]
                 detail["nccl_broadcast_formulation"] = cmp_
                 summary["nccl_bcast"] = {"ms": round(cmp_["ms"], 4), "bytes_equal": cmp_["bytes_equal"], "phases": cmp_["phase_ms_max_over_ranks"]}

@@ -663,6 +663,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 	ctx->ev_valid[frame] = false;
 	ctx->open_launches = 0;
 	ctx->routed_frame = routed;
+	ctx->kev_exchange[frame] = false;
 	if (ctx->timing)
 		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][0], s));
 	if (ctx->aabb_dirty)
@@ -1246,6 +1247,11 @@ int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream)
 	ctx->peer_epoch = ctx->peer_epoch >= 0x7fffffffu ? 1u : ctx->peer_epoch + 1u;
 	ctx->peer.epoch = ctx->peer_epoch;
 	HVCF_CUDA(launch_peer_totals(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->d_peer_totals, static_cast<cudaStream_t>(stream)));
+	if (ctx->ktimes && ctx->range_frame < ctx->frame_count)
+	{
+		HVCF_CUDA(hvcf_kmark(ctx, ctx->range_frame, 6, static_cast<cudaStream_t>(stream)));
+		ctx->kev_exchange[ctx->range_frame] = true;
+	}
 	return HVCF_OK;
 }
 
@@ -1509,6 +1515,8 @@ int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5])
 	HVCF_CUDA(cudaEventSynchronize(ctx->kev[frame][5]));
 	for (int i = 0; i < 5; ++i)
 		HVCF_CUDA(cudaEventElapsedTime(&out_ms[i], ctx->kev[frame][i], ctx->kev[frame][i + 1]));
+	if (ctx->kev_exchange[frame]) // sharded frames: the wait for the other ranks' totals sits between finalize and the write pass
+		HVCF_CUDA(cudaEventElapsedTime(&out_ms[4], ctx->kev[frame][6], ctx->kev[frame][5]));
 	return HVCF_OK;
 }
 

@@ -193,6 +193,7 @@ struct hvcf_ctx
 	uint32_t last_launches[8]{}; // per frame
 	bool timing = false;
 	bool ktimes = false;                 // HVCF_KERNEL_TIMES=1 (debug): an event after every kernel of the hierarchical frame
+	bool kev_exchange[8]{};              // kev[frame][6] (after the totals exchange of a sharded frame) was recorded in this frame
 	cudaEvent_t kev[8][8]{};             // [frame][begin, transform, bin, count, finalize, write]
 	cudaEvent_t ev[8][4]{}; // per frame: call begin, kernel begin, kernel end, call end
 	bool ev_valid[8]{};
