@@ -613,6 +613,7 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
         flush.zero_()
         ictx.cull_routed(f & 1, sp)
         rows.append(ictx.kernel_times(f & 1))
+    route_ms = ictx.route_ms(1)
     st2 = ictx.stats(1, sp)
     drop(ictx)
     ms = dict(zip(KERNEL_NAMES, [float(x) for x in np.median(np.array(rows), axis=0)]))
@@ -623,6 +624,7 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
     crit = int(np.argmax(own))
     out["roofline"] = dict(per_rank[crit]["roofline"], rank=crit)
     out["own_kernels_ms_per_rank"] = [round(x, 4) for x in own]
+    out["route_kernel_ms_per_rank"] = [round(x, 4) for x in allgather(route_ms)]
     out["kernel_ms_per_rank"] = [{k: round(v, 4) for k, v in p["ms"].items()} for p in per_rank]
     out["executed_tests_all_ranks"] = int(sum(p["stats"]["executed_tests"] + p["stats"]["prefilter_tests"] for p in per_rank))
     return out
@@ -955,12 +957,12 @@ def run_ours(args):
         parallelism = (f"{world} ranks: clusters sharded by z-slab {head['z_cuts']}, lights owned in shards and routed over NVLink peer "
                        f"memory (hvcf_cull_routed); no collective call in the frame")
         detail = {k: head[k] for k in ("z_cuts", "balance_iterations", "inbox_records_per_rank", "light_range_per_rank", "own_kernels_ms_per_rank",
-                                       "kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks")}
+                                       "kernel_ms_per_rank", "route_kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks")}
         inbox = head["inbox_records_per_rank"]
         own = head["own_kernels_ms_per_rank"]
         summary["routed"] = {"ms": round(ms_per_step, 4), "bytes_equal": head["sharded_bytes_equal"], "z_cuts": head["z_cuts"],
                              "own_ms_min_max": [min(own), max(own)], "inbox_Mrec_min_max": [round(min(inbox) / 1e6, 2), round(max(inbox) / 1e6, 2)],
-                             "inbound_MB_max": round(max(inbox) * 18 / 1e6, 1), "e2e_ms": round(e2e_ms, 3), "e2e_res_ms": round(e2e_res_ms, 3),
+                             "inbound_MB_max": round(max(inbox) * 16 / 1e6, 1), "e2e_ms": round(e2e_ms, 3), "e2e_res_ms": round(e2e_res_ms, 3),
                              "frac": round(roofline["frac"], 3), "top": roofline["kernel"].split(" ")[0],
                              "kernels_ms_crit_rank": head["kernel_ms_per_rank"][roofline["rank"]]}
         if not args.no_compare:

@@ -161,7 +161,7 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 		const ShardState& sh = ctx->shard;
 		unsigned char* box = sh.d_inbox + static_cast<size_t>(sh.epoch & 1u) * sh.parity_bytes;
 		p.lights_view = reinterpret_cast<const float4*>(box);
-		p.tile_ids = reinterpret_cast<const uint16_t*>(box + sh.off_idx);
+		p.tile_ids = sh.d_tile_ids;
 		p.tile_cnt = sh.d_tile_cnt;
 		p.tile_mask = ~(sh.block_tiles - 1u);
 	}

@@ -754,7 +754,7 @@ __global__ void hier_super_unions_kernel(const float* __restrict__ cb_union, uin
 
 // ROUTED (hvcf_shard.cu): the tile is a tile of this rank's INBOX -- up to 1,024 plain {x, y, z, r*r} records that the light
 // owners compacted in light order, `valid` of them in use -- and the slot's index of a record is the light's 16-bit index inside
-// its route block (in_idx), not its position.  Same two phases, same slots; an empty tile only zeroes its slot counts.
+// its route block (rebuilt from the block's survivor bitmask, in_mask), not its position.  Same two phases, same slots; an empty tile only zeroes its slot counts.
 template <bool ROUTED>
 __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinParams p)
 {
@@ -791,18 +791,60 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	}
 	if (threadIdx.x == 0)
 	{
-		if constexpr (ROUTED)
+		mbar_arrive_expect_tx(&bar, ROUTED ? valid * 16u : kTileBytes);
+		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, ROUTED ? valid * 16u : kTileBytes, &bar);
+	}
+	if constexpr (ROUTED)
+	{
+		// the in-block light index of this tile's records: the j-th record of the block's region is the j-th set bit of the block's
+		// survivor bitmask (block_tiles x 32 words, one bit per light of the block in light order).  Each thread takes the words
+		// t, t + 256, ...: an exclusive prefix of the popcounts gives the rank of a word's first set bit.
+		__shared__ uint32_t s_wsum[kBinWarps];
+		__shared__ uint32_t s_carry;
+		const uint32_t lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
+		const uint32_t words = p.block_tiles * 32u;
+		const uint32_t* mask = p.in_mask + static_cast<size_t>(tile_id & ~(p.block_tiles - 1u)) * 32u;
+		const uint32_t r_begin = (tile_id & (p.block_tiles - 1u)) * kTileLights, r_end = r_begin + valid;
+		if (threadIdx.x == 0)
+			s_carry = 0u;
+		__syncthreads();
+		for (uint32_t w0 = 0; w0 < words; w0 += blockDim.x)
 		{
-			const uint32_t rec_bytes = valid * 16u, id_bytes = (valid * 2u + 15u) & ~15u;
-			mbar_arrive_expect_tx(&bar, rec_bytes + id_bytes);
-			bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, rec_bytes, &bar);
-			bulk_copy_g2s(s_ids, p.in_idx + static_cast<size_t>(tile_id) * kTileLights, id_bytes, &bar);
+			const uint32_t wi = w0 + threadIdx.x;
+			uint32_t word = wi < words ? mask[wi] : 0u;
+			const uint32_t c = __popc(word);
+			uint32_t inc = c;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1)
+			{
+				const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+				if (lane_ >= static_cast<uint32_t>(o))
+					inc += t;
+			}
+			if (lane_ == 31)
+				s_wsum[warp_] = inc;
+			__syncthreads();
+			uint32_t before = s_carry;
+			for (uint32_t w = 0; w < warp_; ++w)
+				before += s_wsum[w];
+			uint32_t rank = before + inc - c; // rank of this word's first set bit inside the block's region
+			if (rank < r_end && rank + c > r_begin)
+				while (word)
+				{
+					const uint32_t bit = __ffs(word) - 1;
+					word &= word - 1;
+					if (rank >= r_begin && rank < r_end)
+						s_ids[rank - r_begin] = static_cast<uint16_t>(wi * 32u + bit);
+					++rank;
+				}
+			__syncthreads();
+			if (threadIdx.x == blockDim.x - 1)
+				s_carry = before + inc;
+			__syncthreads();
 		}
-		else
-		{
-			mbar_arrive_expect_tx(&bar, kTileBytes);
-			bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, kTileBytes, &bar);
-		}
+		// kept for the raw-tile path of the count / write passes (a slot that overflowed reads the inbox tile itself)
+		for (uint32_t i = threadIdx.x; i < valid; i += blockDim.x)
+			p.tile_ids[static_cast<size_t>(tile_id) * kTileLights + i] = s_ids[i];
 	}
 	mbar_wait(&bar, 0);
 	const float4* tile = reinterpret_cast<const float4*>(s_tile);
@@ -1079,7 +1121,7 @@ size_t hier_bin2_smem_bytes(uint32_t ns, bool routed)
 
 static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStream_t stream)
 {
-	const bool routed = p.in_idx != nullptr;
+	const bool routed = p.in_mask != nullptr;
 	const size_t smem = hier_bin2_smem_bytes(p.ns, routed);
 	static size_t configured[2] = {0, 0};
 	if (smem > configured[routed])

@@ -61,13 +61,14 @@ struct ShardState
 	uint32_t block_tiles = 0;                  // B: tiles per route block
 	uint32_t blocks_per_rank = 0, blocks_phys = 0, tiles_phys = 0; // blocks_phys = blocks_per_rank * world, tiles_phys = blocks_phys * B
 	uint32_t z_cuts[HVCF_MAX_PEERS + 1]{};     // rank r owns slices [z_cuts[r], z_cuts[r + 1])
-	// inbox: ONE allocation (one IPC handle), per frame parity { rec[tiles_phys][1024] float4, idx[tiles_phys][1024] u16, cnt[blocks_phys] u32 }
+	// inbox: ONE allocation (one IPC handle), per frame parity { rec[tiles_phys][1024] float4, mask[tiles_phys][32] u32, cnt[blocks_phys] u32 }
 	unsigned char* d_inbox = nullptr;
-	size_t parity_bytes = 0, off_idx = 0, off_cnt = 0;
+	size_t parity_bytes = 0, off_mask = 0, off_cnt = 0;
 	unsigned char* inbox_peer[HVCF_MAX_PEERS]{}; // every rank's inbox (own pointer at [rank]); valid while peers are attached
 	uint32_t* d_ranges = nullptr;              // [world][2] cluster range of every rank
 	float* d_slab_box = nullptr;               // [world][8]
 	uint32_t* d_tile_cnt = nullptr;            // [tiles_phys] valid records of every inbox tile of the open frame
+	uint16_t* d_tile_ids = nullptr;            // [tiles_phys][1024] in-block light index of every inbox record of the open frame (rebuilt by the binning kernel)
 	uint32_t epoch = 0;                        // routed-frame serial, the same on every rank
 };
 

@@ -148,10 +148,11 @@ struct BinParams
 	uint32_t sg;                   // groups per super-group
 	uint32_t ns;                   // super-groups, at most 32
 	// routed variant (hier_bin2_kernel<true>): the tile is an inbox tile of plain records, partly filled
-	const uint16_t* in_idx = nullptr; // [tiles][1024] index of the record's light inside its route block
+	const uint32_t* in_mask = nullptr; // [tiles][32] survivor bitmasks of the SOURCE tiles of each route block (the j-th record of the block's region is its j-th set bit)
 	const uint32_t* in_cnt = nullptr; // [tiles / block_tiles] records of each route block
 	uint32_t block_tiles = 1;         // tiles per route block (power of two)
 	uint32_t* tile_cnt = nullptr;     // [tiles] out: valid records of the tile
+	uint16_t* tile_ids = nullptr;     // [tiles][1024] out: index of every record's light inside its route block (for the raw-tile path of the passes)
 };
 
 struct FinalizeParams
@@ -242,8 +243,8 @@ struct RouteParams
 	uint32_t block0, blocks;          // first route block of this rank (global numbering), own blocks
 	uint32_t world, rank, epoch, parity;
 	const float* slab_box;            // [world][8] union box of every rank's cluster slab { lo.xyz, 0, hi.xyz, 0 }
-	float4* rec[kMaxPeers];           // every rank's inbox of this frame parity: [tiles][1024] records,
-	uint16_t* idx[kMaxPeers];         //   [tiles][1024] in-block light indices,
+	float4* rec[kMaxPeers];           // every rank's inbox of this frame parity: [tiles][1024] records (a route block's region is dense from its start),
+	uint32_t* mask[kMaxPeers];        //   [tiles][32] survivor bitmask of every source tile: the j-th record of a block's region is its j-th set bit,
 	uint32_t* cnt[kMaxPeers];         //   [blocks] records per route block
 	PeerMailbox* mail[kMaxPeers];
 	uint32_t* zero;                   // early-exit counters of the own frame to clear (the route kernel is the frame's first)

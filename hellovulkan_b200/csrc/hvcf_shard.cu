@@ -94,21 +94,43 @@ __global__ void __launch_bounds__(256) slab_unions_kernel(const hvcf_aabb* __res
 	}
 }
 
+// ---- TMA bulk store shared -> (peer) global, bulk-group completion (SASS UBLKCP / UTMASTG family) -----------------------
+__device__ __forceinline__ void bulk_store_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes)
+{
+	asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() // at most N of the most recent groups may still be READING shared memory
+{
+	asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 // ======================================================================================================
 // transform + slab test + route.  A route block of B tiles is a THREAD-BLOCK CLUSTER of B CTAs, one tile of 1,024 lights
-// each, so every tile of the rank's share is in flight at once (a first version walked the B tiles of a block one after
-// the other in one CTA: 0.23 ms for 2 M lights at 8 GPUs, latency-bound).  Inside a CTA, warp w owns the 128 consecutive
-// lights [w * 128, w * 128 + 128) as four rounds of 32 (lane = light), so (CTA rank, warp, round, lane) order = light order.
-// Per destination: warp totals -> CTA totals in shared memory -> cluster barrier -> every CTA reads the totals of the CTAs
-// before it through distributed shared memory -> each warp's first position in the (block, destination) region.
-// Survivors are stored at consecutive positions (16 B records: full 32 B sectors on the wire wherever two neighbours survive).
+// each, so every tile of the rank's share is in flight at once.  Inside a CTA, warp w owns the 128 consecutive lights
+// [w * 128, w * 128 + 128) as four rounds of 32 (lane = light), so (CTA rank, warp, round, lane) order = light order.
+// Per destination: the ballots ARE the survivor bitmask of the tile (32 words); warp totals -> CTA totals in shared memory
+// -> cluster barrier -> every CTA reads the totals of the CTAs before it through distributed shared memory = its first
+// position in the (block, destination) region.  The CTA's survivors for one destination are compacted into a shared-memory
+// staging buffer and leave as ONE TMA bulk store (cp.async.bulk shared -> peer global) of count x 16 B, plus one of 128 B for
+// the bitmask: the copy engine cuts them into full-size NVLink writes.  (A first version stored the records and a 16-bit
+// index per record straight from registers, 16 + 2 B per lane: 0.25 ms per frame for 2 M lights at 8 GPUs whatever the
+// parallelism -- NVLink packet-bound, profiles/r02g.)  The destination rebuilds a record's in-block light index from the
+// bitmask: the j-th record of the region is the j-th set bit.
 // ======================================================================================================
 __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const RouteParams p)
 {
 	namespace cg = cooperative_groups;
+	__shared__ __align__(128) float4 s_stage[2][kTileLights];
+	__shared__ __align__(128) uint32_t s_mask[kMaxPeers][32];
 	__shared__ float s_box[kMaxPeers][6];
 	__shared__ uint32_t s_wt[kRouteWarps][kMaxPeers];
 	__shared__ uint32_t s_tot[kMaxPeers];   // this CTA's survivors per destination; read by the CTAs after it in the cluster
+	__shared__ uint32_t s_cbase[kMaxPeers]; // this CTA's first position in the (block, destination) region
 	__shared__ bool s_last;
 	cg::cluster_group cluster = cg::this_cluster();
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -141,8 +163,7 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 	const float* view = p.ubo->camera_view;
 	const size_t slot = static_cast<size_t>(blk) * p.block_tiles * kTileLights;
 	const uint32_t lt = lanemask_lt();
-	const uint32_t in_block = k * kTileLights + warp * 128u;
-	const uint32_t light0 = blk * p.block_tiles * kTileLights + in_block;
+	const uint32_t light0 = (blk * p.block_tiles + k) * kTileLights + warp * 128u;
 	float4 v[4];
 	uint32_t hm[4];
 #pragma unroll
@@ -169,7 +190,12 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 		uint32_t t = 0u;
 #pragma unroll
 		for (int it = 0; it < 4; ++it)
-			t += __popc(__ballot_sync(0xffffffffu, (hm[it] >> d) & 1u));
+		{
+			const uint32_t b = __ballot_sync(0xffffffffu, (hm[it] >> d) & 1u);
+			if (lane == 0)
+				s_mask[d][warp * 4 + it] = b; // bit l of word (w * 4 + it) = light w * 128 + it * 32 + l of the tile
+			t += __popc(b);
+		}
 		if (lane == d)
 			my_tot = t;
 	}
@@ -184,39 +210,62 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 		s_tot[threadIdx.x] = t;
 	}
 	cluster.sync(); // every CTA's totals are in its shared memory
-	uint32_t base = 0u; // lane d: next position of this warp in destination d's region of the block
+	uint32_t wbase = 0u; // lane d: first position of this warp inside the CTA's run for destination d
 	if (lane < p.world)
 	{
-		for (uint32_t r = 0; r < k; ++r)
-			base += *cluster.map_shared_rank(&s_tot[lane], r);
 		for (uint32_t w = 0; w < warp; ++w)
-			base += s_wt[w][lane];
-	}
-	if (k + 1 == p.block_tiles && warp == kRouteWarps - 1 && lane < p.world)
-		p.cnt[lane][blk] = base + s_wt[warp][lane]; // the block's last warp: everything before it + its own = the region's count
-#pragma unroll
-	for (int it = 0; it < 4; ++it)
-		for (uint32_t d = 0; d < p.world; ++d)
+			wbase += s_wt[w][lane];
+		if (warp == 0)
 		{
-			const bool bit = (hm[it] >> d) & 1u;
-			const uint32_t b = __ballot_sync(0xffffffffu, bit);
-			if (b == 0u)
-				continue;
-			const uint32_t bd = __shfl_sync(0xffffffffu, base, d);
-			if (bit)
-			{
-				const size_t q = slot + bd + __popc(b & lt);
-				p.rec[d][q] = v[it];
-				p.idx[d][q] = static_cast<uint16_t>(in_block + it * 32 + lane);
-			}
-			if (lane == d)
-				base += __popc(b);
+			uint32_t cb = 0u;
+			for (uint32_t r = 0; r < k; ++r)
+				cb += *cluster.map_shared_rank(&s_tot[lane], r);
+			s_cbase[lane] = cb;
+			if (k + 1 == p.block_tiles)
+				p.cnt[lane][blk] = cb + s_tot[lane]; // the block's last tile: everything before it + its own = the region's count
 		}
-	// ---- last CTA out raises the flag on every rank (the pattern of peer_push_kernel: CTA barrier, one cumulative system
-	// fence, a device-scope counter, release stores of the flags) ----
+	}
 	__syncthreads();
+	uint32_t used = 0u; // staging buffers handed to the copy engine so far (CTA-uniform)
+	for (uint32_t d = 0; d < p.world; ++d)
+	{
+		const uint32_t tot = s_tot[d];
+		const uint32_t buf = used & 1u;
+		if (tot != 0u)
+		{
+			if (used >= 2u) // the group that read this buffer is two record groups back: at most the latest group may be pending
+			{
+				if (threadIdx.x == 0)
+					bulk_wait_read<1>();
+				__syncthreads();
+			}
+			uint32_t wb = __shfl_sync(0xffffffffu, wbase, d);
+#pragma unroll
+			for (int it = 0; it < 4; ++it)
+			{
+				const uint32_t b = s_mask[d][warp * 4 + it];
+				if ((b >> lane) & 1u)
+					s_stage[buf][wb + __popc(b & lt)] = v[it];
+				wb += __popc(b);
+			}
+			fence_proxy_async_smem(); // generic-proxy writes to shared memory -> visible to the copy engine
+		}
+		__syncthreads();
+		if (threadIdx.x == 0)
+		{
+			if (tot != 0u)
+				bulk_store_s2g(p.rec[d] + slot + s_cbase[d], s_stage[buf], tot * 16u);
+			bulk_store_s2g(p.mask[d] + (static_cast<size_t>(blk) * p.block_tiles + k) * 32u, s_mask[d], 128u);
+			bulk_commit();
+		}
+		used += tot != 0u ? 1u : 0u;
+	}
+	// ---- last CTA out raises the flag on every rank: the bulk stores have completed (wait_group), one cumulative system fence,
+	// a device-scope counter, release stores of the flags ----
 	if (threadIdx.x == 0)
 	{
+		bulk_wait_all();
+		fence_proxy_async_all();
 		__threadfence_system();
 		PeerMailbox* mine = p.mail[p.rank];
 		const unsigned int done = atomicAdd(&mine->route_done, 1u);

@@ -28,6 +28,7 @@ void hvcf_shard_free(hvcf_ctx* c)
 	cudaFree(c->shard.d_ranges);
 	cudaFree(c->shard.d_slab_box);
 	cudaFree(c->shard.d_tile_cnt);
+	cudaFree(c->shard.d_tile_ids);
 	c->shard = ShardState{};
 }
 
@@ -87,8 +88,8 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 	sh.blocks_phys = static_cast<uint32_t>(blocks_phys);
 	sh.tiles_phys = static_cast<uint32_t>(tiles_phys);
 	memcpy(sh.z_cuts, desc->z_cuts, sizeof(uint32_t) * (world + 1));
-	sh.off_idx = static_cast<size_t>(tiles_phys) * kTileBytes;
-	sh.off_cnt = sh.off_idx + static_cast<size_t>(tiles_phys) * kTileLights * sizeof(uint16_t);
+	sh.off_mask = static_cast<size_t>(tiles_phys) * kTileBytes;
+	sh.off_cnt = sh.off_mask + static_cast<size_t>(tiles_phys) * 32 * sizeof(uint32_t);
 	sh.parity_bytes = (sh.off_cnt + static_cast<size_t>(blocks_phys) * sizeof(uint32_t) + 255u) & ~static_cast<size_t>(255u);
 	uint32_t ranges[2 * HVCF_MAX_PEERS];
 	for (uint32_t r = 0; r < world; ++r)
@@ -109,6 +110,8 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_tile_cnt), sizeof(uint32_t) * tiles_phys);
 	if (e == cudaSuccess)
 		e = cudaMemset(sh.d_tile_cnt, 0, sizeof(uint32_t) * tiles_phys);
+	if (e == cudaSuccess)
+		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_tile_ids), sizeof(uint16_t) * tiles_phys * kTileLights);
 	if (e != cudaSuccess)
 	{
 		hvcf_destroy(c);
@@ -196,7 +199,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	{
 		unsigned char* box = sh.inbox_peer[r] + static_cast<size_t>(parity) * sh.parity_bytes;
 		rp.rec[r] = reinterpret_cast<float4*>(box);
-		rp.idx[r] = reinterpret_cast<uint16_t*>(box + sh.off_idx);
+		rp.mask[r] = reinterpret_cast<uint32_t*>(box + sh.off_mask);
 		rp.cnt[r] = reinterpret_cast<uint32_t*>(box + sh.off_cnt);
 		rp.mail[r] = ctx->peer.mail[r];
 	}
@@ -204,6 +207,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	rp.zero_words = ctx->cluster_count * kHMaxChunks;
 	rp.stats = stats;
 	HVCF_CUDA(launch_shard_route(rp, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 7, s)); // HVCF_KERNEL_TIMES: the route kernel alone (hvcf_debug_route_ms)
 	ctx->range_cleared = true;
 	PeerParams pp = ctx->peer;
 	pp.epoch = sh.epoch;
@@ -225,7 +229,8 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	b.sb_union = ctx->d_sb_union;
 	b.sg = ctx->bin_sg;
 	b.ns = ctx->bin_ns;
-	b.in_idx = reinterpret_cast<const uint16_t*>(box + sh.off_idx);
+	b.in_mask = reinterpret_cast<const uint32_t*>(box + sh.off_mask);
+	b.tile_ids = sh.d_tile_ids;
 	b.in_cnt = reinterpret_cast<const uint32_t*>(box + sh.off_cnt);
 	b.block_tiles = sh.block_tiles;
 	b.tile_cnt = sh.d_tile_cnt;
@@ -276,6 +281,17 @@ int hvcf_download_shard(hvcf_ctx* ctx, void* cells_dst, size_t cells_bytes, void
 		HVCF_CUDA(cudaMemcpyAsync(indices_dst, ctx->d_indices + h[8], need, cudaMemcpyDeviceToHost, s));
 		HVCF_CUDA(cudaStreamSynchronize(s));
 	}
+	return HVCF_OK;
+}
+
+int hvcf_debug_route_ms(hvcf_ctx* ctx, uint32_t frame, float* out_route_ms)
+{
+	if (!ctx || !out_route_ms || frame >= ctx->frame_count)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_route_ms: bad argument");
+	if (!ctx->ktimes || !ctx->kev[frame][7] || !ctx->kev[frame][0])
+		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_route_ms: needs HVCF_KERNEL_TIMES=1 at hvcf_create and a routed frame on this slot");
+	HVCF_CUDA(cudaEventSynchronize(ctx->kev[frame][7]));
+	HVCF_CUDA(cudaEventElapsedTime(out_route_ms, ctx->kev[frame][0], ctx->kev[frame][7]));
 	return HVCF_OK;
 }
 

@@ -90,7 +90,7 @@ EXPORTS = [
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
     "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
     "hvcf_peer_status", "hvcf_create_sharded", "hvcf_shard_light_range", "hvcf_set_lights_range", "hvcf_cull_routed",
-    "hvcf_shard_inbox_records", "hvcf_download_shard",
+    "hvcf_shard_inbox_records", "hvcf_download_shard", "hvcf_debug_route_ms",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -120,6 +120,7 @@ def load():
     lib.hvcf_set_lights_range.argtypes = [vp, vp, u32, u32, i32, vp]
     lib.hvcf_cull_routed.argtypes = [vp, u32, vp]
     lib.hvcf_download_shard.argtypes = [vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t, ctypes.POINTER(u32), ctypes.POINTER(u32), vp]
+    lib.hvcf_debug_route_ms.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float)]
     lib.hvcf_shard_inbox_records.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_uint64)]
     lib.hvcf_set_lights.argtypes = [vp, vp, u32, i32, vp]
     lib.hvcf_update_light.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float), vp]
@@ -539,6 +540,11 @@ class Context:
         _check(self.lib.hvcf_download_shard(self.handle, cells_ptr, cells_bytes, idx_ptr, idx_capacity_bytes, ctypes.byref(b),
                                             ctypes.byref(t), stream))
         return int(b.value), int(t.value)
+
+    def route_ms(self, frame=0):
+        v = ctypes.c_float()
+        _check(self.lib.hvcf_debug_route_ms(self.handle, frame, ctypes.byref(v)))
+        return float(v.value)
 
     def shard_inbox_records(self, stream=None):
         v = ctypes.c_uint64()

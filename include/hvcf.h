@@ -246,7 +246,7 @@ HVCF_API int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream);
 HVCF_API int hvcf_download_shard(hvcf_ctx* ctx, void* cells_dst, size_t cells_bytes, void* indices_dst, size_t indices_capacity_bytes,
 	uint32_t* out_index_base, uint32_t* out_total, void* stream);
 /* records that arrived in this rank's inbox in the last routed frame (synchronises `stream`); the wire carried
- * 18 B per record that came from another rank */
+ * 16 B per record that came from another rank, plus one bit per (light, destination) */
 HVCF_API int hvcf_shard_inbox_records(hvcf_ctx* ctx, void* stream, uint64_t* out_records);
 
 HVCF_API int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out);
@@ -301,6 +301,9 @@ HVCF_API int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size
 /* debug: milliseconds of {transform, bin, count pass, finalize, write pass} of the last hierarchical hvcf_cull on `frame`
  * (an event after every kernel, which also switches their programmatic overlap off); needs HVCF_KERNEL_TIMES=1 at hvcf_create. */
 HVCF_API int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5]);
+/* debug: milliseconds of the route kernel alone in the last hvcf_cull_routed on `frame` (out_ms[0] of hvcf_debug_kernel_times is
+ * route + the wait for the other ranks' shares); needs HVCF_KERNEL_TIMES=1 at hvcf_create. */
+HVCF_API int hvcf_debug_route_ms(hvcf_ctx* ctx, uint32_t frame, float* out_route_ms);
 HVCF_API int hvcf_set_timing(hvcf_ctx* ctx, int enabled);
 HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms);
 /* Measured FP32 issue rate of the device (independent FADD/FMUL chains, no FMA), in lane-operations per
