@@ -131,7 +131,6 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 	__shared__ uint32_t s_wt[kRouteWarps][kMaxPeers];
 	__shared__ uint32_t s_tot[kMaxPeers];   // this CTA's survivors per destination; read by the CTAs after it in the cluster
 	__shared__ uint32_t s_cbase[kMaxPeers]; // this CTA's first position in the (block, destination) region
-	__shared__ bool s_last;
 	cg::cluster_group cluster = cg::this_cluster();
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t k = cluster.block_rank();            // tile inside the route block
@@ -225,61 +224,76 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 				p.cnt[lane][blk] = cb + s_tot[lane]; // the block's last tile: everything before it + its own = the region's count
 		}
 	}
-	__syncthreads();
-	uint32_t used = 0u; // staging buffers handed to the copy engine so far (CTA-uniform)
-	for (uint32_t d = 0; d < p.world; ++d)
+	cluster.sync(); // every CTA has read what it needs from the others (and s_cbase is in place): from here on the CTAs are independent
+	// ---- staging rounds: consecutive destinations are packed into the staging buffer while they fit (2,048 records; a tile's
+	// survivors over ALL destinations usually do), one proxy fence + one barrier per round, then thread d hands destination d's
+	// run to the copy engine.  Every destination also gets the tile's 128-byte bitmask (zeros included: the owner sums all of them). ----
+	float4* const stage = &s_stage[0][0];
+	constexpr uint32_t kStageCap = 2u * kTileLights;
+	uint32_t d0 = 0u;
+	bool first_round = true;
+	while (d0 < p.world)
 	{
-		const uint32_t tot = s_tot[d];
-		const uint32_t buf = used & 1u;
-		if (tot != 0u)
+		uint32_t d1 = d0, fill = 0u;
+		while (d1 < p.world && (d1 == d0 || fill + s_tot[d1] <= kStageCap))
+			fill += s_tot[d1++];
+		if (!first_round) // the copy engine must have read the previous round out of the staging buffer
 		{
-			if (used >= 2u) // the group that read this buffer is two record groups back: at most the latest group may be pending
-			{
-				if (threadIdx.x == 0)
-					bulk_wait_read<1>();
-				__syncthreads();
-			}
-			uint32_t wb = __shfl_sync(0xffffffffu, wbase, d);
-#pragma unroll
-			for (int it = 0; it < 4; ++it)
-			{
-				const uint32_t b = s_mask[d][warp * 4 + it];
-				if ((b >> lane) & 1u)
-					s_stage[buf][wb + __popc(b & lt)] = v[it];
-				wb += __popc(b);
-			}
-			fence_proxy_async_smem(); // generic-proxy writes to shared memory -> visible to the copy engine
+			if (threadIdx.x < p.world)
+				bulk_wait_read<0>();
+			__syncthreads();
 		}
-		__syncthreads();
-		if (threadIdx.x == 0)
+		first_round = false;
+		uint32_t off = 0u; // first staging slot of destination d (CTA-uniform)
+		for (uint32_t d = d0; d < d1; ++d)
 		{
+			const uint32_t tot = s_tot[d];
 			if (tot != 0u)
-				bulk_store_s2g(p.rec[d] + slot + s_cbase[d], s_stage[buf], tot * 16u);
+			{
+				uint32_t wb = off + __shfl_sync(0xffffffffu, wbase, d);
+#pragma unroll
+				for (int it = 0; it < 4; ++it)
+				{
+					const uint32_t b = s_mask[d][warp * 4 + it];
+					if ((b >> lane) & 1u)
+						stage[wb + __popc(b & lt)] = v[it];
+					wb += __popc(b);
+				}
+			}
+			off += tot;
+		}
+		fence_proxy_async_smem(); // generic-proxy writes to shared memory -> visible to the copy engine
+		__syncthreads();
+		if (threadIdx.x >= d0 && threadIdx.x < d1)
+		{
+			const uint32_t d = threadIdx.x;
+			uint32_t o = 0u;
+			for (uint32_t e = d0; e < d; ++e)
+				o += s_tot[e];
+			if (s_tot[d] != 0u)
+				bulk_store_s2g(p.rec[d] + slot + s_cbase[d], stage + o, s_tot[d] * 16u);
 			bulk_store_s2g(p.mask[d] + (static_cast<size_t>(blk) * p.block_tiles + k) * 32u, s_mask[d], 128u);
 			bulk_commit();
 		}
-		used += tot != 0u ? 1u : 0u;
+		d0 = d1;
 	}
-	// ---- last CTA out raises the flag on every rank: the bulk stores have completed (wait_group), one cumulative system fence,
-	// a device-scope counter, release stores of the flags ----
-	if (threadIdx.x == 0)
+	// ---- the threads that issued bulk stores wait for their completion, fence at system scope and count themselves off;
+	// the last one of the whole grid raises the rank's flag on every rank.  Everybody else has left: no trailing barrier. ----
+	if (threadIdx.x < p.world)
 	{
 		bulk_wait_all();
 		fence_proxy_async_all();
 		__threadfence_system();
 		PeerMailbox* mine = p.mail[p.rank];
 		const unsigned int done = atomicAdd(&mine->route_done, 1u);
-		s_last = done == gridDim.x - 1;
-		if (s_last)
+		if (done == gridDim.x * p.world - 1u)
+		{
 			mine->route_done = 0u;
+			__threadfence_system();
+			for (uint32_t r = 0; r < p.world; ++r)
+				shard_st_release_sys(&p.mail[r]->routed[p.parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+		}
 	}
-	__syncthreads();
-	if (s_last && threadIdx.x < p.world)
-	{
-		__threadfence_system();
-		shard_st_release_sys(&p.mail[threadIdx.x]->routed[p.parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
-	}
-	cluster.sync(); // nobody leaves while a later CTA of the cluster may still read its totals
 }
 
 // one warp: lane r waits for rank r's share of the lights (its own included: the flag is raised by its own route kernel)
