@@ -156,6 +156,8 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.tiles_cap = ctx->tiles_cap;
 	p.seg_lists = ctx->hier_v1 ? nullptr : ctx->d_hseg_lists;
 	p.unit_any = ctx->d_hunit_any;
+	if (ctx->shard.seg_local) // the write pass runs before the totals exchange: local positions, relocated by the push
+		p.indices = ctx->shard.d_seg;
 	if (ctx->routed_frame) // the tiles are this rank's inbox of the frame's parity
 	{
 		const ShardState& sh = ctx->shard;
@@ -1239,21 +1241,26 @@ int hvcf_peer_detach(hvcf_ctx* ctx)
 	return HVCF_OK;
 }
 
-int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream)
+int hvcf_peer_totals_step(hvcf_ctx* ctx, void* stream, uint32_t what)
 {
 	if (!ctx || !ctx->peer.world)
 		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_exchange_totals: no peers attached");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
-	ctx->peer_epoch = ctx->peer_epoch >= 0x7fffffffu ? 1u : ctx->peer_epoch + 1u;
-	ctx->peer.epoch = ctx->peer_epoch;
-	HVCF_CUDA(launch_peer_totals(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->d_peer_totals, static_cast<cudaStream_t>(stream)));
-	if (ctx->ktimes && ctx->range_frame < ctx->frame_count)
+	if (what & 1u) // a new exchange starts with the post
+	{
+		ctx->peer_epoch = ctx->peer_epoch >= 0x7fffffffu ? 1u : ctx->peer_epoch + 1u;
+		ctx->peer.epoch = ctx->peer_epoch;
+	}
+	HVCF_CUDA(launch_peer_totals(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->d_peer_totals, static_cast<cudaStream_t>(stream), what));
+	if (what == 3u && ctx->ktimes && ctx->range_frame < ctx->frame_count) // (posted early / waited late: the write pass does not wait)
 	{
 		HVCF_CUDA(hvcf_kmark(ctx, ctx->range_frame, 6, static_cast<cudaStream_t>(stream)));
 		ctx->kev_exchange[ctx->range_frame] = true;
 	}
 	return HVCF_OK;
 }
+
+int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream) { return hvcf_peer_totals_step(ctx, stream, 3u); }
 
 int hvcf_peer_push_grid(hvcf_ctx* ctx, void* stream)
 {

@@ -38,6 +38,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s);
 void hvcf_shard_free(hvcf_ctx* ctx);
 cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s);
+int hvcf_peer_totals_step(hvcf_ctx* ctx, void* stream, uint32_t what); // 1 = post, 2 = wait + index base, 3 = both
 }
 
 #define HVCF_CUDA(expr)                                                                                      \
@@ -70,6 +71,8 @@ struct ShardState
 	uint32_t* d_tile_cnt = nullptr;            // [tiles_phys] valid records of every inbox tile of the open frame
 	uint16_t* d_tile_ids = nullptr;            // [tiles_phys][1024] in-block light index of every inbox record of the open frame (rebuilt by the binning kernel)
 	uint32_t epoch = 0;                        // routed-frame serial, the same on every rank
+	uint32_t* d_seg = nullptr;                 // [cluster_count * cap] this rank's index segment at LOCAL positions (the write pass runs before the totals are known)
+	bool seg_local = false;                    // the write pass of the open frame writes d_seg / local offsets (hvcf_cull_routed)
 };
 
 struct hvcf_ctx

@@ -258,7 +258,9 @@ cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges,
 cudaError_t preload_shard_kernels();
 
 cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total, uint32_t* index_base, uint32_t* totals_out,
-	cudaStream_t stream);
+	cudaStream_t stream, uint32_t what = 3u);
+cudaError_t launch_peer_push_relocate(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, const uint32_t* seg,
+	uint32_t cluster_begin, uint32_t cluster_count, uint32_t blocks, cudaStream_t stream);
 cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, uint32_t cluster_begin,
 	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream);
 cudaError_t launch_peer_wait(const PeerParams& p, const uint32_t* totals, uint32_t* frame_total, cudaStream_t stream);

@@ -63,16 +63,21 @@ __device__ __forceinline__ unsigned long long spin_epoch(const unsigned long lon
 }
 
 // one warp: lane r talks to rank r
+// what: 1 = post this rank's total, 2 = wait for everybody's and compute the index base, 3 = both.  Posting early and
+// waiting late (hvcf_cull_routed) lets the write pass run while the other ranks are still counting.
 __global__ void __launch_bounds__(32) peer_totals_kernel(const PeerParams p, const uint32_t* __restrict__ shard_total,
-	uint32_t* __restrict__ index_base, uint32_t* __restrict__ totals_out)
+	uint32_t* __restrict__ index_base, uint32_t* __restrict__ totals_out, uint32_t what)
 {
 	const uint32_t r = threadIdx.x;
 	const uint32_t parity = p.epoch & 1u;
 	const uint32_t mine = *shard_total;
 	uint32_t total_r = 0;
+	if (r < p.world && (what & 1u))
+		st_release_sys_u64(&p.mail[r]->totals[parity][p.rank], (static_cast<unsigned long long>(p.epoch) << 32) | mine);
+	if (!(what & 2u))
+		return;
 	if (r < p.world)
 	{
-		st_release_sys_u64(&p.mail[r]->totals[parity][p.rank], (static_cast<unsigned long long>(p.epoch) << 32) | mine);
 		const unsigned long long v = spin_epoch(&p.mail[p.rank]->totals[parity][r], p.epoch, p.mail[p.rank], 1u, r);
 		total_r = static_cast<uint32_t>(v);
 		if (totals_out)
@@ -187,6 +192,91 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 	}
 }
 
+// The same push for a frame whose write pass ran BEFORE the totals were known (hvcf_cull_routed): the rank's cells carry
+// shard-local offsets and its index segment sits at seg[0, total); this kernel adds the index base to the offsets and
+// places the segment at [base, base + total) on EVERY rank, its own included.  Destination-aligned 16 B stores; the source
+// is read with 4 B loads (local memory, coalesced), because base is not a multiple of 4 in general.
+__global__ void __launch_bounds__(256) peer_push_relocate_kernel(const PeerParams p, const uint32_t* __restrict__ shard_total,
+	const uint32_t* __restrict__ index_base, const uint32_t* __restrict__ seg, uint32_t cluster_begin, uint32_t cluster_count)
+{
+	const uint32_t base = *index_base, total = *shard_total;
+	const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+	const size_t nth = static_cast<size_t>(gridDim.x) * blockDim.x;
+	// ---- cells: {offset + base, count}; own cells are rewritten in place (same element, same thread) ----
+	{
+		const uint2* src = reinterpret_cast<const uint2*>(p.cells[p.rank]);
+		for (size_t i = cluster_begin + tid; i < static_cast<size_t>(cluster_begin) + cluster_count; i += nth)
+		{
+			uint2 v = src[i];
+			v.x += base;
+			for (uint32_t r = 0; r < p.world; ++r)
+				reinterpret_cast<uint2*>(p.cells[r])[i] = v;
+		}
+	}
+	// ---- indices: destination words [base, base + total); head up to a 16 B boundary, 16 B body, tail ----
+	{
+		const size_t b = base, e = static_cast<size_t>(base) + total;
+		size_t b4 = (b + 3) & ~static_cast<size_t>(3);
+		if (b4 > e)
+			b4 = e;
+		const size_t e4 = b4 + ((e - b4) & ~static_cast<size_t>(3));
+		size_t i = b4 / 4 + tid;
+		const size_t iend = e4 / 4;
+		for (; i + nth < iend; i += 2 * nth)
+		{
+			uint4 v[2];
+#pragma unroll
+			for (int u = 0; u < 2; ++u)
+			{
+				const uint32_t* s4 = seg + ((i + u * nth) * 4 - b);
+				v[u] = make_uint4(__ldcs(s4), __ldcs(s4 + 1), __ldcs(s4 + 2), __ldcs(s4 + 3));
+			}
+			for (uint32_t r = 0; r < p.world; ++r)
+			{
+#pragma unroll
+				for (int u = 0; u < 2; ++u)
+					reinterpret_cast<uint4*>(p.indices[r])[i + u * nth] = v[u];
+			}
+		}
+		for (; i < iend; i += nth)
+		{
+			const uint32_t* s4 = seg + (i * 4 - b);
+			const uint4 v = make_uint4(s4[0], s4[1], s4[2], s4[3]);
+			for (uint32_t r = 0; r < p.world; ++r)
+				reinterpret_cast<uint4*>(p.indices[r])[i] = v;
+		}
+		if (tid < 8)
+		{
+			// lanes 0..3: head words, lanes 4..7: tail words
+			const size_t j = tid < 4 ? b + tid : e4 + (tid - 4);
+			const bool ok = tid < 4 ? j < b4 : j < e;
+			if (ok)
+			{
+				const uint32_t v = seg[j - b];
+				for (uint32_t r = 0; r < p.world; ++r)
+					p.indices[r][j] = v;
+			}
+		}
+	}
+	__shared__ bool last;
+	__syncthreads();
+	if (threadIdx.x == 0)
+	{
+		__threadfence_system();
+		PeerMailbox* mine = p.mail[p.rank];
+		const unsigned int done = atomicAdd(&mine->done, 1u);
+		last = done == gridDim.x - 1;
+		if (last)
+			mine->done = 0u;
+	}
+	__syncthreads();
+	if (last && threadIdx.x < p.world)
+	{
+		__threadfence_system();
+		st_release_sys_u64(&p.mail[threadIdx.x]->arrived[p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+	}
+}
+
 // also leaves the total of the WHOLE grid in globalIndexCountBuffers_[frame] (the write pass stored this shard's running
 // total there), so that the counter too reads the same on every GPU as after an unsharded frame
 __global__ void __launch_bounds__(32) peer_wait_kernel(const PeerParams p, const uint32_t* __restrict__ totals, uint32_t* __restrict__ frame_total)
@@ -204,9 +294,9 @@ __global__ void __launch_bounds__(32) peer_wait_kernel(const PeerParams p, const
 }
 
 cudaError_t launch_peer_totals(const PeerParams& p, const uint32_t* shard_total, uint32_t* index_base, uint32_t* totals_out,
-	cudaStream_t stream)
+	cudaStream_t stream, uint32_t what)
 {
-	peer_totals_kernel<<<1, 32, 0, stream>>>(p, shard_total, index_base, totals_out);
+	peer_totals_kernel<<<1, 32, 0, stream>>>(p, shard_total, index_base, totals_out, what);
 	return cudaGetLastError();
 }
 
@@ -214,6 +304,13 @@ cudaError_t launch_peer_push(const PeerParams& p, const uint32_t* shard_total, c
 	uint32_t cluster_count, uint32_t blocks, cudaStream_t stream)
 {
 	peer_push_kernel<<<blocks, 256, 0, stream>>>(p, shard_total, index_base, cluster_begin, cluster_count);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_peer_push_relocate(const PeerParams& p, const uint32_t* shard_total, const uint32_t* index_base, const uint32_t* seg,
+	uint32_t cluster_begin, uint32_t cluster_count, uint32_t blocks, cudaStream_t stream)
+{
+	peer_push_relocate_kernel<<<blocks, 256, 0, stream>>>(p, shard_total, index_base, seg, cluster_begin, cluster_count);
 	return cudaGetLastError();
 }
 
@@ -230,6 +327,7 @@ cudaError_t preload_peer_kernels()
 {
 	HVCF_PRELOAD(peer_totals_kernel);
 	HVCF_PRELOAD(peer_push_kernel);
+	HVCF_PRELOAD(peer_push_relocate_kernel);
 	HVCF_PRELOAD(peer_wait_kernel);
 	return cudaSuccess;
 }

@@ -29,6 +29,7 @@ void hvcf_shard_free(hvcf_ctx* c)
 	cudaFree(c->shard.d_slab_box);
 	cudaFree(c->shard.d_tile_cnt);
 	cudaFree(c->shard.d_tile_ids);
+	cudaFree(c->shard.d_seg);
 	c->shard = ShardState{};
 }
 
@@ -110,6 +111,8 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_tile_cnt), sizeof(uint32_t) * tiles_phys);
 	if (e == cudaSuccess)
 		e = cudaMemset(sh.d_tile_cnt, 0, sizeof(uint32_t) * tiles_phys);
+	if (e == cudaSuccess)
+		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_seg), sizeof(uint32_t) * static_cast<size_t>(c->cluster_count) * c->cap + 64);
 	if (e == cudaSuccess)
 		e = cudaMalloc(reinterpret_cast<void**>(&sh.d_tile_ids), sizeof(uint16_t) * tiles_phys * kTileLights);
 	if (e != cudaSuccess)
@@ -239,14 +242,25 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	ctx->open_launches += 3;
 	ctx->range_transformed = ctx->range_binned = sh.tiles_phys * kTileLights;
 
-	// ---- count pass + scan, then the exchange of hvcf_cull_sharded ----
+	// ---- count pass + scan; this rank's total is POSTED at once, but nobody waits yet: the write pass runs on local positions
+	// (own segment buffer, shard-local offsets) while the other ranks finish counting; the push then adds the index base and
+	// places cells + segment on every rank, this one included ----
 	rc = hvcf_hier_close(ctx, frame, s);
 	if (rc == HVCF_OK)
-		rc = hvcf_peer_exchange_totals(ctx, stream);
+		rc = hvcf_peer_totals_step(ctx, stream, 1u);
 	if (rc == HVCF_OK)
-		rc = hvcf_cull_finish(ctx, frame, ctx->d_index_base, stream);
+	{
+		sh.seg_local = true;
+		rc = hvcf_cull_finish(ctx, frame, nullptr, stream);
+		sh.seg_local = false;
+	}
 	if (rc == HVCF_OK)
-		rc = hvcf_peer_push_grid(ctx, stream);
+		rc = hvcf_peer_totals_step(ctx, stream, 2u);
+	if (rc == HVCF_OK)
+	{
+		static const uint32_t blocks = static_cast<uint32_t>(env_int("HVCF_PEER_BLOCKS", 592) > 0 ? env_int("HVCF_PEER_BLOCKS", 592) : 592);
+		HVCF_CUDA(launch_peer_push_relocate(ctx->peer, ctx->d_shard_total, ctx->d_index_base, sh.d_seg, ctx->cluster_begin, ctx->cluster_count, blocks, s));
+	}
 	if (rc == HVCF_OK)
 		rc = hvcf_peer_wait_grid(ctx, stream);
 	return rc;
