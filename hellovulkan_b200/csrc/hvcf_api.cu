@@ -225,6 +225,18 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		delete c;
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: z shard [%u,%u) outside [0,%u)", zb, ze, c->Z);
 	}
+	uint32_t rb = zb * c->Y, re = ze * c->Y; // the shard in cluster rows
+	if (config->row_end)
+	{
+		rb = config->row_begin, re = config->row_end;
+		if (rb >= re || re > c->Y * c->Z)
+		{
+			delete c;
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create: row shard [%u,%u) outside [0,%u)", rb, re, c->Y * c->Z);
+		}
+		zb = rb / c->Y;                  // the slices that cover the rows: the plan's box
+		ze = (re + c->Y - 1) / c->Y;
+	}
 	uint32_t mode = config->mode;
 	if (mode > HVCF_MODE_HIERARCHICAL)
 	{
@@ -237,8 +249,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		mode = (m && !strcmp(m, "brute")) ? HVCF_MODE_BRUTE : HVCF_MODE_HIERARCHICAL;
 	}
 	c->hier = mode == HVCF_MODE_HIERARCHICAL;
-	c->cluster_begin = zb * c->X * c->Y;
-	c->cluster_end = ze * c->X * c->Y;
+	c->cluster_begin = rb * c->X;
+	c->cluster_end = re * c->X;
 	c->cluster_count = c->cluster_end - c->cluster_begin;
 	c->padded_capacity = round_up_u32(c->max_lights ? c->max_lights : 1, kTileLights);
 	c->variant = env_int("HVCF_CULL_VARIANT", 1);
@@ -267,6 +279,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		if (const char* sh = getenv("HVCF_HIER_SHAPE"))
 			sscanf(sh, "%u,%u,%u", &shape[0], &shape[1], &shape[2]);
 		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, c->max_lights, &c->hp);
+		// blocks of the covering box that hold none of the shard's clusters are dropped here, before anything is sized by the plan
+		hier_build_lane_map(&c->hp, c->X, c->Y, ze - zb, c->cluster_begin - zb * c->X * c->Y, c->cluster_end - zb * c->X * c->Y, &c->lane_map);
 		const uint32_t max_tiles = c->padded_capacity / kTileLights;
 		// most light segments a frame may be cut into (hier_plan_lights picks the actual number).  Measured on B200
 		// (scripts/sweep_hier.py): grid A x 1M lights 0.181 ms at 256 -> 0.131 ms at 512 (half the executed tests: shorter
@@ -391,9 +405,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		e = cudaMemset(c->d_shard_total, 0, sizeof(uint32_t));
 	if (e == cudaSuccess && c->hier)
 	{
-		std::vector<uint32_t> map;
-		hier_build_lane_map(c->hp, c->X, c->Y, ze - zb, &map);
-		e = cudaMemcpy(c->d_hlane_cluster, map.data(), map.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+		e = cudaMemcpy(c->d_hlane_cluster, c->lane_map.data(), c->lane_map.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+		std::vector<uint32_t>().swap(c->lane_map);
 	}
 	if (e == cudaSuccess && c->hier)
 		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);

@@ -61,7 +61,7 @@ struct ShardState
 	uint32_t rank = 0, world = 0, total_lights = 0;
 	uint32_t block_tiles = 0;                  // B: tiles per route block
 	uint32_t blocks_per_rank = 0, blocks_phys = 0, tiles_phys = 0; // blocks_phys = blocks_per_rank * world, tiles_phys = blocks_phys * B
-	uint32_t z_cuts[HVCF_MAX_PEERS + 1]{};     // rank r owns slices [z_cuts[r], z_cuts[r + 1])
+	uint32_t row_cuts[HVCF_MAX_PEERS + 1]{};   // rank r owns the cluster rows [row_cuts[r], row_cuts[r + 1]), row = y + z * Y
 	// inbox: ONE allocation (one IPC handle), per frame parity { rec[tiles_phys][1024] float4, mask[tiles_phys][32] u32, cnt[blocks_phys] u32 }
 	unsigned char* d_inbox = nullptr;
 	size_t parity_bytes = 0, off_mask = 0, off_cnt = 0;
@@ -98,6 +98,7 @@ struct hvcf_ctx
 	// hierarchical mode
 	bool hier = false;
 	HierPlan hp{};
+	std::vector<uint32_t> lane_map;          // host copy between planning and upload (hvcf_create)
 	uint32_t h_max_segs = 0, h_max_chunks = 0;
 	uint32_t h_plan_max_segs = 0;            // most whole-tile segments the plan may use
 	uint32_t h_parts_cfg = 0, h_parts = 1;   // HVCF_HIER_PARTS (0 = auto); parts per tile of this frame (1 unless every segment is one tile)

@@ -30,6 +30,8 @@
 // scheduling.  No flags, no fences.
 #include "hvcf_hier.cuh"
 
+#include <algorithm>
+
 #include <vector>
 
 namespace hvcf
@@ -540,22 +542,47 @@ void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const u
 	h.ncb = (h.nblocks + kHWarps * h.K - 1) / (kHWarps * h.K);
 }
 
-// cluster index (inside the shard) of every lane of every block, kSkip where the block sticks out of the grid;
+// cluster index (inside the shard) of every lane of every block, kSkip where the block sticks out of the grid or the cluster
+// is not the shard's (row-granular shards: the box covers whole slices, the shard may start and end inside one); blocks
+// that keep no lane are dropped, the rest keep their order (x, then y, then z: neighbours stay neighbours in a group);
 // padded to whole CTAs so the kernel needs no bounds check
-void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out)
+void hier_build_lane_map(HierPlan* hp, uint32_t X, uint32_t Y, uint32_t Zs, uint32_t cluster_lo, uint32_t cluster_hi, std::vector<uint32_t>* out)
 {
-	const size_t blocks = static_cast<size_t>(h.ncb) * kHWarps * h.K;
-	out->assign(blocks * 32, kSkip);
+	HierPlan& h = *hp;
+	std::vector<uint32_t> kept;
+	kept.reserve(static_cast<size_t>(h.nblocks) * 32);
+	uint32_t nkept = 0;
 	for (uint32_t b = 0; b < h.nblocks; ++b)
 	{
 		const uint32_t bxi = b % h.nbx, byi = (b / h.nbx) % h.nby, bzi = b / (h.nbx * h.nby);
+		uint32_t lanes[32];
+		bool any = false;
 		for (uint32_t lane = 0; lane < 32; ++lane)
 		{
 			const uint32_t x = bxi * h.bx + lane % h.bx, y = byi * h.by + (lane / h.bx) % h.by, z = bzi * h.bz + lane / (h.bx * h.by);
+			lanes[lane] = kSkip;
 			if (x < X && y < Y && z < Zs)
-				(*out)[static_cast<size_t>(b) * 32 + lane] = x + y * X + z * X * Y;
+			{
+				const uint32_t c = x + y * X + z * X * Y;
+				if (c >= cluster_lo && c < cluster_hi)
+				{
+					lanes[lane] = c - cluster_lo;
+					any = true;
+				}
+			}
+		}
+		if (any)
+		{
+			kept.insert(kept.end(), lanes, lanes + 32);
+			++nkept;
 		}
 	}
+	h.nblocks = nkept;
+	h.ncb = (nkept + kHWarps * h.K - 1) / (kHWarps * h.K);
+	if (h.ncb == 0)
+		h.ncb = 1;
+	out->assign(static_cast<size_t>(h.ncb) * kHWarps * h.K * 32, kSkip);
+	std::copy(kept.begin(), kept.end(), out->begin());
 }
 
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,

@@ -187,7 +187,9 @@ struct CopyParams
 cudaError_t launch_hier_copy(const CopyParams& p, cudaStream_t stream);
 
 void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], uint32_t max_lights, HierPlan* out);
-void hier_build_lane_map(const HierPlan& h, uint32_t X, uint32_t Y, uint32_t Zs, std::vector<uint32_t>* out);
+// cluster_lo / cluster_hi: the shard's clusters inside the X x Y x Zs box (box-local indices); clusters outside are masked, blocks
+// without any cluster of the shard are dropped and h->nblocks / h->ncb shrink accordingly
+void hier_build_lane_map(HierPlan* h, uint32_t X, uint32_t Y, uint32_t Zs, uint32_t cluster_lo, uint32_t cluster_hi, std::vector<uint32_t>* out);
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs);
 uint32_t hier_num_chunks(uint32_t num_segs);

@@ -47,13 +47,20 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 	if (B > kMaxRouteBlockTiles || (B & (B - 1u)))
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: block_tiles %u is not a power of two <= %u", B, kMaxRouteBlockTiles);
 	const uint32_t Z = config->slice_count_z ? config->slice_count_z : HVCF_DEFAULT_SLICE_COUNT_Z;
-	if (desc->z_cuts[0] != 0 || desc->z_cuts[world] != Z)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: z_cuts must run from 0 to slice_count_z = %u", Z);
+	const uint32_t Yc = config->slice_count_y ? config->slice_count_y : HVCF_DEFAULT_SLICE_COUNT_Y;
+	// the cuts in cluster rows (row = y + z * Y): row_cuts if given, else the z cuts
+	uint32_t rows[HVCF_MAX_PEERS + 1];
+	const bool by_rows = desc->row_cuts[world] != 0;
+	for (uint32_t r = 0; r <= world; ++r)
+		rows[r] = by_rows ? desc->row_cuts[r] : desc->z_cuts[r] * Yc;
+	if (rows[0] != 0 || rows[world] != Yc * Z)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: the cuts must run from 0 to %s = %u", by_rows ? "slice_count_y x slice_count_z" : "slice_count_z",
+			by_rows ? Yc * Z : Z);
 	for (uint32_t r = 0; r < world; ++r)
-		if (desc->z_cuts[r] > desc->z_cuts[r + 1])
-			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: z_cuts must ascend");
-	if (desc->z_cuts[rank] == desc->z_cuts[rank + 1])
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: rank %u owns no slice", rank);
+		if (rows[r] > rows[r + 1])
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: the cuts must ascend");
+	if (rows[rank] == rows[rank + 1])
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: rank %u owns no cluster", rank);
 	if (config->mode == HVCF_MODE_BRUTE)
 		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_create_sharded: hierarchical mode only");
 
@@ -67,8 +74,9 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_create_sharded: %u lights are too many", desc->total_lights);
 
 	hvcf_config cfg = *config;
-	cfg.z_begin = desc->z_cuts[rank];
-	cfg.z_end = desc->z_cuts[rank + 1];
+	cfg.z_begin = cfg.z_end = 0;
+	cfg.row_begin = rows[rank];
+	cfg.row_end = rows[rank + 1];
 	cfg.mode = HVCF_MODE_HIERARCHICAL;
 	const uint32_t need = static_cast<uint32_t>(tiles_phys * kTileLights);
 	if (cfg.max_lights < need)
@@ -88,15 +96,15 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 	sh.blocks_per_rank = static_cast<uint32_t>(bpr);
 	sh.blocks_phys = static_cast<uint32_t>(blocks_phys);
 	sh.tiles_phys = static_cast<uint32_t>(tiles_phys);
-	memcpy(sh.z_cuts, desc->z_cuts, sizeof(uint32_t) * (world + 1));
+	memcpy(sh.row_cuts, rows, sizeof(uint32_t) * (world + 1));
 	sh.off_mask = static_cast<size_t>(tiles_phys) * kTileBytes;
 	sh.off_cnt = sh.off_mask + static_cast<size_t>(tiles_phys) * 32 * sizeof(uint32_t);
 	sh.parity_bytes = (sh.off_cnt + static_cast<size_t>(blocks_phys) * sizeof(uint32_t) + 255u) & ~static_cast<size_t>(255u);
 	uint32_t ranges[2 * HVCF_MAX_PEERS];
 	for (uint32_t r = 0; r < world; ++r)
 	{
-		ranges[2 * r] = desc->z_cuts[r] * c->X * c->Y;
-		ranges[2 * r + 1] = desc->z_cuts[r + 1] * c->X * c->Y;
+		ranges[2 * r] = rows[r] * c->X;
+		ranges[2 * r + 1] = rows[r + 1] * c->X;
 	}
 	cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&sh.d_inbox), 2 * sh.parity_bytes);
 	if (e == cudaSuccess)

@@ -37,14 +37,14 @@ class Config(ctypes.Structure):
                 ("slice_count_x", ctypes.c_uint32), ("slice_count_y", ctypes.c_uint32), ("slice_count_z", ctypes.c_uint32),
                 ("max_lights_per_cluster", ctypes.c_uint32), ("max_lights", ctypes.c_uint32), ("frame_count", ctypes.c_uint32),
                 ("mode", ctypes.c_uint32), ("z_begin", ctypes.c_uint32), ("z_end", ctypes.c_uint32),
-                ("reserved", ctypes.c_uint32 * 5)]
+                ("row_begin", ctypes.c_uint32), ("row_end", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 3)]
 
 
 class ShardDesc(ctypes.Structure):
     """hvcf_shard_desc: this rank's place in the 2-D decomposition (z-slabs of clusters x owned ranges of lights)."""
     _fields_ = [("struct_size", ctypes.c_uint32), ("rank", ctypes.c_uint32), ("world", ctypes.c_uint32),
                 ("total_lights", ctypes.c_uint32), ("block_tiles", ctypes.c_uint32), ("z_cuts", ctypes.c_uint32 * 17),
-                ("reserved", ctypes.c_uint32 * 4)]
+                ("row_cuts", ctypes.c_uint32 * 17), ("reserved", ctypes.c_uint32 * 3)]
 
 
 class Buffers(ctypes.Structure):
@@ -346,9 +346,10 @@ class Context:
     """One hvcf_ctx: the device buffers of ResourcesClusterForward + ResourcesLight and the two passes."""
 
     def __init__(self, grid=(16, 9, 24), max_lights=1024, max_lights_per_cluster=150, frame_count=2, device=-1,
-                 mode=MODE_AUTO, z_begin=0, z_end=0, shard=None):
-        """shard = (rank, world, total_lights, z_cuts[, block_tiles]): hvcf_create_sharded -- this rank's z-slab of the grid
-        and its own range of the lights (hvcf_cull_routed); z_begin / z_end are then taken from z_cuts."""
+                 mode=MODE_AUTO, z_begin=0, z_end=0, shard=None, rows=None):
+        """shard = (rank, world, total_lights, cuts[, block_tiles]): hvcf_create_sharded -- this rank's slab of the grid and its
+        own range of the lights (hvcf_cull_routed).  cuts are z cuts (cuts[-1] == Z) or, finer, cuts in cluster rows
+        (cuts[-1] == Y * Z; row = y + z * Y).  rows = (row_begin, row_end): a row-granular shard of a plain context."""
         self.lib = load()
         cfg = Config()
         cfg.struct_size = ctypes.sizeof(Config)
@@ -359,6 +360,8 @@ class Context:
         cfg.frame_count = frame_count
         cfg.mode = mode
         cfg.z_begin, cfg.z_end = z_begin, z_end
+        if rows is not None:
+            cfg.row_begin, cfg.row_end = rows
         self.handle = ctypes.c_void_p()
         if shard is not None:
             rank, world, total, cuts = shard[:4]
@@ -366,8 +369,12 @@ class Context:
             d.struct_size = ctypes.sizeof(ShardDesc)
             d.rank, d.world, d.total_lights = rank, world, total
             d.block_tiles = shard[4] if len(shard) > 4 else 0
+            by_rows = len(cuts) > 1 and cuts[-1] == grid[1] * grid[2] and grid[1] > 1
             for i, z in enumerate(cuts):
-                d.z_cuts[i] = z
+                if by_rows:
+                    d.row_cuts[i] = z
+                else:
+                    d.z_cuts[i] = z
             _check(self.lib.hvcf_create_sharded(ctypes.byref(cfg), ctypes.byref(d), ctypes.byref(self.handle)))
         else:
             _check(self.lib.hvcf_create(ctypes.byref(cfg), ctypes.byref(self.handle)))

@@ -74,7 +74,13 @@ typedef struct hvcf_config
 	/* z-slab shard owned by this context: slices [z_begin, z_end); 0,0 = whole grid. */
 	uint32_t z_begin;
 	uint32_t z_end;
-	uint32_t reserved[5];
+	/* or, finer, a range of cluster ROWS: row = y + z * slice_count_y, clusters [row_begin * X, row_end * X) -- still a contiguous
+	 * cluster-index range (tileIndex = x + y*X + z*X*Y, LightCulling.comp:61-64), so shard segments concatenate exactly as z-slabs
+	 * do.  row_end != 0 overrides z_begin / z_end.  Cuts on multiples of the cluster-block height (4 rows for X >= 8) keep every
+	 * 32-cluster block whole. */
+	uint32_t row_begin;
+	uint32_t row_end;
+	uint32_t reserved[3];
 } hvcf_config;
 
 /* Device pointers in the reference's exact layouts (ResourcesClusterForward.h:24-30). */
@@ -228,7 +234,10 @@ typedef struct hvcf_shard_desc
 	uint32_t total_lights;                 /* lights of the whole scene, the same on every rank */
 	uint32_t block_tiles;                  /* tiles per route block, a power of two <= 16; 0 = library default */
 	uint32_t z_cuts[HVCF_MAX_PEERS + 1];   /* ascending, z_cuts[0] = 0, z_cuts[world] = slice_count_z */
-	uint32_t reserved[4];
+	/* or, finer (used when row_cuts[world] != 0): cuts in cluster rows (row = y + z * slice_count_y), row_cuts[0] = 0,
+	 * row_cuts[world] = slice_count_y * slice_count_z */
+	uint32_t row_cuts[HVCF_MAX_PEERS + 1];
+	uint32_t reserved[3];
 } hvcf_shard_desc;
 /* hvcf_create with z_begin / z_end = this rank's slab and max_lights raised to the padded light count of the
  * decomposition, plus the inbox, the slab boxes and the ownership plan. */

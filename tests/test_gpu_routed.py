@@ -188,3 +188,40 @@ def test_routed_argument_errors(hv, oracle):
             c.cull_routed(0)
         with pytest.raises(hv.HvcfError):
             c.shard_light_range()
+
+
+# ---- row-granular shards: cuts inside a z-slice (row = y + z * Y), for load balance finer than whole slices ----
+@pytest.mark.parametrize("cuts", [(0, 216), (0, 100, 216), (0, 37, 101, 130, 216), (0, 8, 16, 24, 32, 40, 48, 150, 216), (0, 1, 2, 216)])
+@pytest.mark.parametrize("n", [1000, 70_000])
+def test_routed_row_cuts(hv, torch_mod, oracle, cuts, n):
+    """grid A has 9 x 24 = 216 cluster rows; cuts that are not multiples of the block height (4) leave partly masked blocks"""
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    lights = oracle.init_lights(n, seed=21)
+    want = run_single(hv, GRID_A, ubo, lights)
+    out, _ = run_routed(hv, torch_mod, GRID_A, [ubo], lights, cuts, frames=2)
+    assert_all_equal(out, want, f"rows {cuts}")
+
+
+def test_row_shards_of_plain_contexts_concatenate(hv, oracle):
+    """hvcf_config.row_begin / row_end on plain contexts (no peers): each writes its own cells and its own index segment at
+    shard-local offsets; concatenated in row order they are the whole grid"""
+    ubo = oracle.camera_ubo(GRID_B, SCREEN_B)
+    lights = oracle.init_lights(120_000, seed=4)
+    want_cells, want_idx, want_total = run_single(hv, GRID_B, ubo, lights)
+    X, Y, Z = GRID_B
+    cuts = [0, 5, 300, 301, 555, Y * Z]
+    got_counts, got_idx = [], []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        with hv.Context(grid=GRID_B, max_lights=len(lights), rows=(a, b)) as ctx:
+            ctx.set_lights(lights)
+            ctx.set_ubo(0, ubo)
+            ctx.cull(0)
+            cells = ctx.download_light_cells()[a * X: b * X]
+            total = ctx.download_total(0)
+            idx = ctx.download_light_indices(total)
+            assert int(cells["count"].sum()) == total
+            assert np.array_equal(cells["offset"].astype(np.int64), np.concatenate([[0], np.cumsum(cells["count"].astype(np.int64))[:-1]]))
+            got_counts.append(cells["count"].copy())
+            got_idx.append(idx.copy())
+    assert np.array_equal(np.concatenate(got_counts), want_cells["count"])
+    assert np.array_equal(np.concatenate(got_idx), want_idx)
