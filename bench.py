@@ -67,9 +67,10 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C16M", choices=sorted(WORKLOADS))
-    ap.add_argument("--balance-iters", type=int, default=4, help="N > 1: slab re-cuts from measured per-rank kernel times")
+    ap.add_argument("--balance-iters", type=int, default=6, help="N > 1: slab re-cuts from measured per-rank kernel times")
     ap.add_argument("--block-tiles", type=int, default=0, help="tiles per route block (0 = library default)")
     ap.add_argument("--z-cuts", default="", help="N > 1: comma-separated z cuts (N + 1 numbers) instead of balancing")
+    ap.add_argument("--row-cuts", default="", help="N > 1: comma-separated cuts in cluster rows (row = y + z * Y) instead of balancing")
     ap.add_argument("--no-summary", action="store_true", help="N = 1: skip the legs on the other workloads")
     ap.add_argument("--no-compare", action="store_true", help="N > 1: skip the NCCL-broadcast formulation")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -511,16 +512,23 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
         barrier()
         ctx.close()
 
-    # ---- z cuts: a host cost proxy (lights reaching each slice), then re-cuts from measured per-rank kernel times ----
+    # ---- cuts: in units of 4 cluster rows (the height of a 32-cluster block; row = y + z * Y), i.e. finer than whole z-slices.
+    # A host cost proxy first (lights reaching each slice), then re-cuts from measured per-rank kernel times ----
     history = []
+    X, Y, Z = grid
+    unit = 4 if Y % 4 == 0 else Y                  # rows per unit
+    upz = Y // unit                                # units per slice
     if args.z_cuts:
-        cuts = [int(x) for x in args.z_cuts.split(",")]
+        cuts_u = [int(x) * upz for x in args.z_cuts.split(",")]
+    elif args.row_cuts:
+        cuts_u = [int(x) // unit for x in args.row_cuts.split(",")]
     else:
         touch = slice_touch_counts(ubos[0], all_lights, stride=16).astype(np.float64)
-        cuts = cuts_from_cost(touch + 0.05 * touch.mean(), world)
+        cost_u = np.repeat((touch + 0.05 * touch.mean()) / upz, upz)
+        cuts_u = cuts_from_cost(cost_u, world)
         best = None
         for it in range(max(0, args.balance_iters)):
-            ctx = make(cuts, ktimes=True)
+            ctx = make([c * unit for c in cuts_u], ktimes=True)
             for f in range(4):
                 ctx.cull_routed(f & 1, sp)
             kt = ctx.kernel_times(1)
@@ -528,21 +536,28 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
             drop(ctx)
             own = float(sum(kt[1:]))                       # bin + count + finalize + write: this rank's own work, no waiting
             times = allgather(own)
-            history.append({"z_cuts": list(cuts), "own_kernels_ms": [round(t, 4) for t in times], "peer_error": err})
+            history.append({"row_cuts": [c * unit for c in cuts_u], "own_kernels_ms": [round(t, 4) for t in times], "peer_error": err})
             if best is None or max(times) < best[0]:
-                best = (max(times), list(cuts))
+                best = (max(times), list(cuts_u))
             if max(times) <= 1.04 * (sum(times) / world):
                 break
-            slabs = [(cuts[r], cuts[r + 1]) for r in range(world)]
+            slabs = [(cuts_u[r], cuts_u[r + 1]) for r in range(world)]
             new = balance_slabs(slabs, times)
-            new_cuts = [a for a, _ in new] + [grid[2]]
-            if new_cuts == cuts:
+            if it >= 2:   # damp late moves: halfway between the current and the proposed cuts
+                new = [((a0 + a1 + 1) // 2, (b0 + b1 + 1) // 2) for (a0, b0), (a1, b1) in zip(slabs, new)]
+            new_cuts = [0] + [max(a, 1) for a, _ in new[1:]] + [Z * upz]
+            for k in range(1, world):
+                new_cuts[k] = max(new_cuts[k], new_cuts[k - 1] + 1)
+            for k in range(world - 1, 0, -1):
+                new_cuts[k] = min(new_cuts[k], new_cuts[k + 1] - 1)
+            if new_cuts == cuts_u:
                 break
-            cuts = new_cuts
+            cuts_u = new_cuts
         if best is not None:
-            cuts = best[1]
+            cuts_u = best[1]
+    cuts = [c * unit for c in cuts_u]              # in cluster rows
     ctx = make(cuts)
-    out = {"z_cuts": list(cuts), "balance_iterations": history}
+    out = {"row_cuts": list(cuts), "rows_per_slice": Y, "balance_iterations": history}
 
     # ---- value: lights resident on their owners, every light transformed every frame; per-step events; max over ranks ----
     step_ms = timed_frames(torch, stream, lambda f: ctx.cull_routed(f, sp), K, W, flush, barrier)
@@ -828,9 +843,9 @@ def run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, 
     grid, screen, n = WORKLOADS[args.workload]
     stream = torch.cuda.current_stream()
     sp = stream.cuda_stream
-    slabs = [(cuts[r], cuts[r + 1]) for r in range(world)]
-    eng = HvcfEngine(hvcf, grid, n, slabs[rank], local)
-    sc = ShardedCuller(eng, grid, world=world, rank=rank, slabs=slabs, exchange="peer")
+    slabs = [(cuts[r], cuts[r + 1]) for r in range(world)]          # in cluster rows
+    eng = HvcfEngine(hvcf, grid, n, None, local, rows=slabs[rank])
+    sc = ShardedCuller(eng, grid, world=world, rank=rank, slabs=[(0, grid[2])] * world, exchange="peer")
     ubos = [hvcf.host_camera_ubo(grid, screen, pos=hvcf.REF_CAMERA_POS), hvcf.host_camera_ubo(grid, screen, pos=(0.5, 1.0, 6.0))]
     if rank == 0:
         host = hvcf.host_init_lights(n)
@@ -954,20 +969,20 @@ def run_ours(args):
                                    "d2h_bytes_per_step": head["e2e_resident"]["d2h_bytes_per_step"]},
                "timer": "host perf_counter around the loop, barrier + synchronise both sides, max over ranks"}
         launches_per_step, total_idx = head["launches_per_step"], head["total_indices"]
-        parallelism = (f"{world} ranks: clusters sharded by z-slab {head['z_cuts']}, lights owned in shards and routed over NVLink peer "
+        parallelism = (f"{world} ranks: clusters sharded into row slabs {head['row_cuts']} (row = y + z * {grid[1]}), lights owned in shards and routed over NVLink peer "
                        f"memory (hvcf_cull_routed); no collective call in the frame")
-        detail = {k: head[k] for k in ("z_cuts", "balance_iterations", "inbox_records_per_rank", "light_range_per_rank", "own_kernels_ms_per_rank",
+        detail = {k: head[k] for k in ("row_cuts", "rows_per_slice", "balance_iterations", "inbox_records_per_rank", "light_range_per_rank", "own_kernels_ms_per_rank",
                                        "kernel_ms_per_rank", "route_kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks")}
         inbox = head["inbox_records_per_rank"]
         own = head["own_kernels_ms_per_rank"]
-        summary["routed"] = {"ms": round(ms_per_step, 4), "bytes_equal": head["sharded_bytes_equal"], "z_cuts": head["z_cuts"],
+        summary["routed"] = {"ms": round(ms_per_step, 4), "bytes_equal": head["sharded_bytes_equal"], "row_cuts": head["row_cuts"],
                              "own_ms_min_max": [min(own), max(own)], "inbox_Mrec_min_max": [round(min(inbox) / 1e6, 2), round(max(inbox) / 1e6, 2)],
                              "inbound_MB_max": round(max(inbox) * 16 / 1e6, 1), "e2e_ms": round(e2e_ms, 3), "e2e_res_ms": round(e2e_res_ms, 3),
                              "frac": round(roofline["frac"], 3), "top": roofline["kernel"].split(" ")[0],
                              "kernels_ms_crit_rank": head["kernel_ms_per_rank"][roofline["rank"]]}
         if not args.no_compare:
             try:
-                cmp_ = run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, head["z_cuts"], (K - 1) & 1)
+                cmp_ = run_broadcast_formulation(args, hvcf, torch, dist, world, rank, local, dev, barrier, head["row_cuts"], (K - 1) & 1)
                 cmp_["bytes_equal"] = cmp_.get("grid_hash") == head["grid_hash"]
                 detail["nccl_broadcast_formulation"] = cmp_
                 summary["nccl_bcast"] = {"ms": round(cmp_["ms"], 4), "bytes_equal": cmp_["bytes_equal"], "phases": cmp_["phase_ms_max_over_ranks"]}

@@ -93,11 +93,14 @@ def as_tensor(ptr: int, nbytes: int, device) -> torch.Tensor:
 class HvcfEngine:
     """One hvcf context restricted to this rank's z-slab; exposes its device buffers as torch tensors."""
 
-    def __init__(self, hvcf, grid, max_lights, z_range, device_index, cap=150):
+    def __init__(self, hvcf, grid, max_lights, z_range, device_index, cap=150, rows=None):
         self.hvcf = hvcf
         self.device = torch.device("cuda", device_index)
-        self.ctx = hvcf.Context(grid=grid, max_lights=max_lights, max_lights_per_cluster=cap, device=device_index,
-                                z_begin=z_range[0], z_end=z_range[1])
+        if rows is not None:   # a row-granular shard (row = y + z * Y)
+            self.ctx = hvcf.Context(grid=grid, max_lights=max_lights, max_lights_per_cluster=cap, device=device_index, rows=rows)
+        else:
+            self.ctx = hvcf.Context(grid=grid, max_lights=max_lights, max_lights_per_cluster=cap, device=device_index,
+                                    z_begin=z_range[0], z_end=z_range[1])
         b = self.ctx.buffers()
         C = b.cluster_count
         self.cluster_begin, self.cluster_end = b.cluster_begin, b.cluster_end
