@@ -1348,8 +1348,12 @@ int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error)
 	HVCF_CUDA(cudaMemcpy(&err, &ctx->d_mail->error, sizeof(err), cudaMemcpyDeviceToHost));
 	*out_error = static_cast<int>(err);
 	if (err)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_status: rank %u waited in vain for the %s of rank %u in sharded frame %u (mod 2^20)", ctx->peer.rank,
-			(err >> 28) == 1 ? "index total" : "grid segment", (err >> 20) & 0xffu, err & 0xfffffu);
+	{
+		static const char* const kinds[] = {"?", "index total", "grid segment", "routed lights", "error report"};
+		const unsigned int kind = err >> 28;
+		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_status: rank %u %s the %s of rank %u in sharded frame %u (mod 2^20)", ctx->peer.rank,
+			kind == 4 ? "received" : "waited in vain for", kinds[kind < 5 ? kind : 0], (err >> 20) & 0xffu, err & 0xfffffu);
+	}
 	return HVCF_OK;
 }
 
@@ -1388,6 +1392,21 @@ int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out)
 	return HVCF_OK;
 }
 
+// Sharded contexts: a download is the caller's next synchronisation point after a frame, so a wait that timed out inside
+// the frame (hvcf_peer.cu; the push kernels then skipped their stores) is reported here instead of handing out a stale grid.
+// Called after the stream has been synchronised.  One 4-byte read, only when peers are attached.
+int hvcf_peer_error_after_sync(hvcf_ctx* ctx, const char* what)
+{
+	if (!ctx->d_mail || ctx->peer.world < 2)
+		return HVCF_OK;
+	unsigned int err = 0;
+	HVCF_CUDA(cudaMemcpy(&err, &ctx->d_mail->error, sizeof(err), cudaMemcpyDeviceToHost));
+	if (err)
+		return fail(HVCF_ERR_NOT_READY, "%s: the sharded frame failed on rank %u (peer error 0x%08x: kind %u, rank %u, frame %u mod 2^20); hvcf_peer_status has the details",
+			what, ctx->peer.rank, err, err >> 28, (err >> 20) & 0xffu, err & 0xfffffu);
+	return HVCF_OK;
+}
+
 static int download(hvcf_ctx* ctx, void* dst, const void* src, size_t bytes, size_t limit, void* stream, const char* what)
 {
 	if (!ctx || (bytes && !dst))
@@ -1399,7 +1418,7 @@ static int download(hvcf_ctx* ctx, void* dst, const void* src, size_t bytes, siz
 	if (bytes)
 		HVCF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
 	HVCF_CUDA(cudaStreamSynchronize(s));
-	return HVCF_OK;
+	return hvcf_peer_error_after_sync(ctx, what);
 }
 
 int hvcf_download_aabbs(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
@@ -1459,6 +1478,8 @@ int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t ce
 			static_cast<uint32_t>(cap_words < 0xffffffffull ? cap_words : 0xffffffffull), ctx->download_max_words, cells_dst, static_cast<uint32_t*>(indices_dst),
 			&ctx->h_total[frame], ctx->download_blocks, s));
 		HVCF_CUDA(cudaStreamSynchronize(s));
+		if (const int prc = hvcf_peer_error_after_sync(ctx, "hvcf_download_grid"))
+			return prc;
 		const uint32_t total = ctx->h_total[frame];
 		*out_total = total;
 		if (sizeof(uint32_t) * static_cast<size_t>(total) > indices_capacity_bytes)
@@ -1476,6 +1497,8 @@ int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t ce
 	if (cells_bytes)
 		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells, cells_bytes, cudaMemcpyDeviceToHost, s));
 	HVCF_CUDA(cudaStreamSynchronize(s));
+	if (const int prc = hvcf_peer_error_after_sync(ctx, "hvcf_download_grid"))
+		return prc;
 	const uint32_t total = ctx->h_total[frame];
 	*out_total = total;
 	const size_t need = sizeof(uint32_t) * static_cast<size_t>(total);

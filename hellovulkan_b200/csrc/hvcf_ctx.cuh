@@ -38,6 +38,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s);
 void hvcf_shard_free(hvcf_ctx* ctx);
 cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s);
+int hvcf_peer_error_after_sync(hvcf_ctx* ctx, const char* what);
 int hvcf_peer_totals_step(hvcf_ctx* ctx, void* stream, uint32_t what); // 1 = post, 2 = wait + index base, 3 = both
 }
 

@@ -35,6 +35,16 @@ __device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsign
 {
 	asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// A frame whose wait timed out must not scatter cells and indices computed from a wrong index base into the peers' grids:
+// the push kernels read their own error word first, skip every data store when it is set and tell the peers instead (their
+// error word becomes kind 4), but still raise the "arrived" flags so that nobody spins for 4 s on a frame that is lost anyway.
+__device__ __forceinline__ bool peer_frame_failed(const PeerParams& p)
+{
+	const unsigned int err = *reinterpret_cast<volatile unsigned int*>(&p.mail[p.rank]->error);
+	if (err != 0u && blockIdx.x == 0 && threadIdx.x < p.world && threadIdx.x != p.rank)
+		atomicCAS_system(&p.mail[threadIdx.x]->error, 0u, (4u << 28) | (p.rank << 20) | (p.epoch & 0xfffffu));
+	return err != 0u;
+}
 __device__ __forceinline__ unsigned long long global_timer_ns()
 {
 	unsigned long long t;
@@ -42,8 +52,12 @@ __device__ __forceinline__ unsigned long long global_timer_ns()
 	return t;
 }
 
-// wait until the word's upper half (the epoch) reaches `epoch`; returns the word, or 0 with the error flag set
-// error word: kind << 28 | rank waited for << 20 | epoch & 0xfffff  (kind 1 = total, 2 = grid segment)
+// wait until the word's upper half (the epoch) EQUALS `epoch`; returns the word, or 0 with the error flag set.
+// Equality, not >=: nobody can run ahead of a frame we still wait for (a peer needs our total of frame e + 1 before it
+// pushes e + 1, and we post that after our own frame e), and after the epoch wraps from 0x7fffffff to 1 a stale word of a
+// high epoch must not satisfy the wait.
+// error word: kind << 28 | rank waited for << 20 | epoch & 0xfffff  (kind 1 = total, 2 = grid segment, 3 = routed lights,
+// 4 = a peer reported an error of its own)
 __device__ __forceinline__ unsigned long long spin_epoch(const unsigned long long* word, unsigned long long epoch, PeerMailbox* mail,
 	uint32_t kind, uint32_t who)
 {
@@ -51,7 +65,7 @@ __device__ __forceinline__ unsigned long long spin_epoch(const unsigned long lon
 	for (;;)
 	{
 		const unsigned long long v = ld_acquire_sys_u64(word);
-		if ((v >> 32) >= epoch)
+		if ((v >> 32) == epoch)
 			return v;
 		if (global_timer_ns() - t0 > kPeerTimeoutNs)
 		{
@@ -100,8 +114,10 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 	const uint32_t base = *index_base, total = *shard_total;
 	const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
 	const size_t nth = static_cast<size_t>(gridDim.x) * blockDim.x;
+	const bool failed = peer_frame_failed(p);
 
 	// ---- cells: 8 B records, copied as 16 B pairs where the range allows ----
+	if (!failed)
 	{
 		const uint2* src = reinterpret_cast<const uint2*>(p.cells[p.rank]);
 		const size_t b = cluster_begin, e = static_cast<size_t>(cluster_begin) + cluster_count;
@@ -123,6 +139,7 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const PeerParams p, cons
 					reinterpret_cast<uint2*>(p.cells[r])[e2] = src[e2];
 	}
 	// ---- indices: 4 B words; head up to a 16 B boundary, 16 B body, tail ----
+	if (!failed)
 	{
 		const uint32_t* src = p.indices[p.rank];
 		const size_t b = base, e = static_cast<size_t>(base) + total;
@@ -202,7 +219,9 @@ __global__ void __launch_bounds__(256) peer_push_relocate_kernel(const PeerParam
 	const uint32_t base = *index_base, total = *shard_total;
 	const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
 	const size_t nth = static_cast<size_t>(gridDim.x) * blockDim.x;
+	const bool failed = peer_frame_failed(p);
 	// ---- cells: {offset + base, count}; own cells are rewritten in place (same element, same thread) ----
+	if (!failed)
 	{
 		const uint2* src = reinterpret_cast<const uint2*>(p.cells[p.rank]);
 		for (size_t i = cluster_begin + tid; i < static_cast<size_t>(cluster_begin) + cluster_count; i += nth)
@@ -214,6 +233,7 @@ __global__ void __launch_bounds__(256) peer_push_relocate_kernel(const PeerParam
 		}
 	}
 	// ---- indices: destination words [base, base + total); head up to a 16 B boundary, 16 B body, tail ----
+	if (!failed)
 	{
 		const size_t b = base, e = static_cast<size_t>(base) + total;
 		size_t b4 = (b + 3) & ~static_cast<size_t>(3);

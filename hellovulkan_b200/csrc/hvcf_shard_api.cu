@@ -293,6 +293,8 @@ int hvcf_download_shard(hvcf_ctx* ctx, void* cells_dst, size_t cells_bytes, void
 	if (cells_bytes)
 		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells + ctx->cluster_begin, cells_bytes, cudaMemcpyDeviceToHost, s));
 	HVCF_CUDA(cudaStreamSynchronize(s));
+	if (const int prc = hvcf_peer_error_after_sync(ctx, "hvcf_download_shard"))
+		return prc;
 	*out_index_base = h[8];
 	*out_total = h[9];
 	const size_t need = sizeof(uint32_t) * static_cast<size_t>(h[9]);

@@ -109,8 +109,9 @@ public:
 		{
 			if (f > 0)
 			{
-				float p[3] = { 0.25f * static_cast<float>(f), 2.0f, 1.0f };
-				resourcesLight_->UpdateLightPosition(vulkanContext_, 0, std::span<float>(p, 3));
+				// AppBase hands the UI state to every resource each frame; ResourcesLight moves light 0 to the shadow-caster position
+				uiData_.shadowCasterPosition_ = { 0.25f * static_cast<float>(f), 2.0f, 1.0f };
+				static_cast<ResourcesBase*>(resourcesLight_.get())->UpdateFromUIData(vulkanContext_, uiData_);
 				camera_->SetPositionAndTarget({ 0.5f * static_cast<float>(f), 1.0f, 6.0f }, { 0.0f, 2.5f, 0.0f });
 			}
 			lastFrameIndex_ = vulkanContext_.GetFrameIndex();
@@ -190,6 +191,7 @@ private:
 	float width_, height_;
 	uint32_t lightCount_, seed_;
 	uint32_t lastFrameIndex_ = 0;
+	UIData uiData_{};
 };
 
 int main(int argc, char** argv)

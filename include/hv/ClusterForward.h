@@ -70,6 +70,12 @@ public:
 	VulkanBuffer* GetVulkanBufferPtr() { return &storageBuffer_; }
 	uint32_t GetLightCount() const { return lightCount_; }
 
+	// Header/Resources/ResourcesLight.h:68-72: light 0 is the shadow caster and follows the UI every frame
+	void UpdateFromUIData(VulkanContext& ctx, UIData& uiData) override
+	{
+		UpdateLightPosition(ctx, 0, uiData.shadowCasterPosition_);
+	}
+
 public:
 	std::vector<LightData> lights_{};
 

@@ -9,6 +9,7 @@
 #define HV_TYPES_H
 
 #include <cstddef>
+#include <array>
 #include <cstdint>
 
 #include "../hvcf_types.h"
@@ -127,7 +128,23 @@ struct DrawIndirectCommand
 	uint32_t firstInstance;
 };
 
-struct UIData; // opaque here: no UI on this path
+// The members of the UI state that this path reads (HelloVulkan/Header/UIData.h:19-36): the PBR push constants consumed by
+// PipelinePBRClusterForward and the shadow-caster position that ResourcesLight::UpdateFromUIData writes into light 0.
+// Mouse / gizmo / ImGui state is out of scope (no window on this path).
+struct UIData
+{
+public:
+	PushConstPBR pbrPC_ =
+	{
+		.lightIntensity = 1.75f,
+		.baseReflectivity = 0.01f,
+		.maxReflectionLod = 1.f,
+		.lightFalloff = 0.1f,
+		.albedoMultipler = 0.1f
+	};
+
+	std::array<float, 3> shadowCasterPosition_ = { 0.f, 0.f, 0.f };
+};
 
 static_assert(sizeof(LightData) == sizeof(hvcf_light_data) && offsetof(LightData, radius_) == offsetof(hvcf_light_data, radius));
 static_assert(sizeof(AABB) == sizeof(hvcf_aabb) && sizeof(LightCell) == sizeof(hvcf_light_cell));

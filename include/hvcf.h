@@ -184,7 +184,9 @@ HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
  *                     + hvcf_peer_wait_grid                   (kernel: until every peer's segment has arrived)
  * leaves the FULL light grid (lightCells[], lightIndices[] in the reference layouts) on every rank, with no host
  * round trip and no collective-library call.  All ranks must call it the same number of times.  Waits are bounded:
- * a missing peer raises the error that hvcf_peer_status reports (after synchronising `stream`).
+ * a missing peer raises the error that hvcf_peer_status reports (after synchronising `stream`).  A rank whose wait timed
+ * out skips its remote stores for that frame and marks every peer's error word, and every hvcf_download_* of a context
+ * with peers attached returns HVCF_ERR_NOT_READY while the error stands (cleared by hvcf_peer_detach / re-attach).
  *   hvcf_peer_export        handle = 4 x cudaIpcMemHandle_t (64 B each), to be sent to the other processes
  *   hvcf_peer_attach        handles[world], own entry ignored; peers are mapped with cudaIpcOpenMemHandle
  *   hvcf_peer_attach_local  the same for contexts living in THIS process (same or peer-accessible devices)
