@@ -8,6 +8,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <new>
 
 #include "hvcf_shade.cuh"
@@ -72,7 +73,6 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_stats);
 	cudaFree(c->d_hseg_counts);
 	cudaFree(c->d_hseg_prefix);
-	cudaFree(c->d_hseg_lists);
 	cudaFree(c->d_hunit_any);
 	cudaFree(c->d_hscratch);
 	cudaFree(c->d_hoffsets);
@@ -81,6 +81,8 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_sb_union);
 	cudaFree(c->d_bin_count);
 	cudaFree(c->d_bin_rec);
+	cudaFree(c->d_group_alive);
+	cudaFree(c->d_alive_union);
 	cudaFree(c->d_bin_idx);
 	cudaFree(c->d_scan_state);
 	cudaFree(c->d_trace);
@@ -116,6 +118,11 @@ static void free_ctx(hvcf_ctx* c)
 		for (auto& e : fe)
 			if (e)
 				cudaEventDestroy(e);
+	for (auto& fe : c->kev_round)
+		for (auto& re : fe)
+			for (auto& e : re)
+				if (e)
+					cudaEventDestroy(e);
 	delete[] c->ubo_set;
 	delete c;
 }
@@ -154,7 +161,6 @@ static HierParams hier_params(hvcf_ctx* ctx, uint32_t frame)
 	p.bin_rec = ctx->d_bin_rec;
 	p.bin_idx = ctx->d_bin_idx;
 	p.tiles_cap = ctx->tiles_cap;
-	p.seg_lists = ctx->hier_v1 ? nullptr : ctx->d_hseg_lists;
 	p.unit_any = ctx->d_hunit_any;
 	if (ctx->shard.seg_local) // the write pass runs before the totals exchange: local positions, relocated by the push
 		p.indices = ctx->shard.d_seg;
@@ -253,7 +259,6 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	c->cluster_end = re * c->X;
 	c->cluster_count = c->cluster_end - c->cluster_begin;
 	c->padded_capacity = round_up_u32(c->max_lights ? c->max_lights : 1, kTileLights);
-	c->variant = env_int("HVCF_CULL_VARIANT", 1);
 	c->download_kernel = env_int("HVCF_DOWNLOAD_KERNEL", 1) != 0;
 	{
 		const int db = env_int("HVCF_DOWNLOAD_BLOCKS", 64);
@@ -261,10 +266,8 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		const int mb = env_int("HVCF_DOWNLOAD_KERNEL_MAX_MB", 4);
 		c->download_max_words = static_cast<uint32_t>(mb < 0 ? 0 : (mb > 2048 ? 2048 : mb)) << 18;
 	}
-	if (c->variant < 0 || c->variant >= kNumCullVariants)
-		c->variant = 1;
 	// light segments: enough CTAs to fill 148 SMs x 4 resident CTAs about twice
-	const uint32_t per_cta = cull_variant_clusters_per_cta(c->variant);
+	const uint32_t per_cta = kCullClustersPerCta;
 	const uint32_t groups = (c->cluster_count + per_cta - 1) / per_cta;
 	uint32_t segs = (2 * 148 * 4 + groups - 1) / groups;
 	segs = segs < 1 ? 1 : (segs > 32 ? 32 : segs);
@@ -279,6 +282,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		if (const char* sh = getenv("HVCF_HIER_SHAPE"))
 			sscanf(sh, "%u,%u,%u", &shape[0], &shape[1], &shape[2]);
 		hier_plan_grid(c->X, c->Y, ze - zb, env_int("HVCF_HIER_K", 0), shape, c->max_lights, &c->hp);
+		c->hp.brick = env_int("HVCF_HIER_BRICK", 1) != 0 ? 1u : 0u;
 		// blocks of the covering box that hold none of the shard's clusters are dropped here, before anything is sized by the plan
 		hier_build_lane_map(&c->hp, c->X, c->Y, ze - zb, c->cluster_begin - zb * c->X * c->Y, c->cluster_end - zb * c->X * c->Y, &c->lane_map);
 		const uint32_t max_tiles = c->padded_capacity / kTileLights;
@@ -299,15 +303,22 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->h_max_chunks = hier_num_chunks(c->h_max_segs);
 		c->h_tps_override = env_int("HVCF_HIER_TPS", 0);
 		c->h_split_head = static_cast<uint32_t>(env_int("HVCF_HIER_SPLIT", 0));
-		c->hier_v1 = env_int("HVCF_HIER_V1", 0) != 0;
 		c->ktimes = env_int("HVCF_KERNEL_TIMES", 0) != 0;
 		c->tiles_cap = max_tiles;
 		// two-level level-0 binning (HVCF_BIN2=0/1 forces it off/on; otherwise chosen per frame, see hier_range)
 		c->bin2_mode = env_int("HVCF_BIN2", -1);
 		c->xbin_max_lights = static_cast<uint32_t>(env_int("HVCF_XBIN_MAX", 262144));
+		c->rounds_mode = env_int("HVCF_ROUNDS", -1);
+		c->rounds_min_tiles = static_cast<uint32_t>(env_int("HVCF_ROUNDS_MIN_TILES", 2048));
+		c->rounds_head = static_cast<uint32_t>(env_int("HVCF_ROUNDS_HEAD", 64));
+		c->rounds_growth = static_cast<uint32_t>(env_int("HVCF_ROUNDS_GROWTH", 4));
+		c->rounds_macro = env_int("HVCF_ROUNDS_MACRO", -1);
+		c->rounds_late_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_LATE_SEGS", 32));
+		if (c->rounds_late_segs == 0)
+			c->rounds_late_segs = 1;
 		c->pipe_mode = env_int("HVCF_BATCH_PIPE", -1);
 		c->pipe_min_tps = static_cast<uint32_t>(env_int("HVCF_PIPE_MIN_TPS", 16));
-		if (!c->hier_v1 && c->bin2_mode != 0)
+		if (c->bin2_mode != 0)
 		{
 			c->bin_sg = (c->hp.ncb + 31) / 32 > 8 ? (c->hp.ncb + 31) / 32 : 8;
 			c->bin_ns = (c->hp.ncb + c->bin_sg - 1) / c->bin_sg;
@@ -342,36 +353,17 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hoffsets, sizeof(uint32_t) * Cs);
 		HVCF_ALLOC(c->d_hunit_any, sizeof(uint32_t) * static_cast<size_t>(c->h_max_segs) * c->hp.ncb * 8);
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
-		if (!c->hier_v1)
 		{
 			const size_t slots = static_cast<size_t>(c->hp.ncb) * c->tiles_cap;
 			HVCF_ALLOC(c->d_cb_union, sizeof(float) * 8 * c->hp.ncb);
 			HVCF_ALLOC(c->d_sb_union, sizeof(float) * 8 * (c->bin_ns ? c->bin_ns : 1));
 			HVCF_ALLOC(c->d_bin_count, sizeof(uint32_t) * slots);
+			HVCF_ALLOC(c->d_group_alive, sizeof(uint32_t) * c->hp.ncb * kHMaxChunks);
+			HVCF_ALLOC(c->d_alive_union, sizeof(float) * 8 * c->hp.ncb);
 			HVCF_ALLOC(c->d_bin_rec, sizeof(float4) * slots * kBinCap);
 			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
 		}
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);
-		// hit lists of the count pass + hier_copy_kernel instead of the write pass: OFF by default (HVCF_SEG_LISTS=1 enables it
-		// within HVCF_SEG_LISTS_MAX_GB).  Measured on B200 and rejected: segments run concurrently, so the count pass sees
-		// only a lower bound of the earlier hits and stores many hits that the cap later discards, each a 4 B store into
-		// its own 32 B sector -- count pass 0.102 -> 0.207 ms at B1M, frame 0.240 -> 0.385 ms; A65k 0.058 -> 0.104 ms; only
-		// grid C x 16M broke even (count 1.36 -> 2.04 ms, write 0.93 -> copy 0.24 ms).  Byte-identical either way
-		// (tests/test_gpu_parity.py::test_copy_pass_and_write_pass_give_identical_bytes).
-		if (!c->hier_v1 && env_int("HVCF_SEG_LISTS", 0) != 0)
-		{
-			const size_t bytes = sizeof(uint32_t) * Cs * c->h_max_segs * c->cap;
-			size_t free_b = 0, total_b = 0;
-			const size_t budget = static_cast<size_t>(env_int("HVCF_SEG_LISTS_MAX_GB", 40)) << 30;
-			if (bytes <= budget && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && bytes + (static_cast<size_t>(8) << 30) <= free_b)
-			{
-				if (cudaMalloc(reinterpret_cast<void**>(&c->d_hseg_lists), bytes ? bytes : 16) != cudaSuccess)
-				{
-					c->d_hseg_lists = nullptr;
-					(void)cudaGetLastError();
-				}
-			}
-		}
 		if (env_int("HVCF_HIER_TRACE", 0))
 			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 16 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
 	}
@@ -632,7 +624,7 @@ int hvcf_generate_aabbs(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	float* dz = ctx->d_zplanes + static_cast<size_t>(frame) * (ctx->Z + 1);
 	HVCF_CUDA(cudaMemcpyAsync(dz, hz, sizeof(float) * (ctx->Z + 1), cudaMemcpyHostToDevice, s));
 	HVCF_CUDA(launch_aabb_generate(&ctx->d_ubo[frame], dz, ctx->d_aabb, ctx->cluster_total, s));
-	if (ctx->hier && !ctx->hier_v1) // level-0 union boxes of the cluster groups follow the AABBs
+	if (ctx->hier) // level-0 union boxes of the cluster groups follow the AABBs
 	{
 		HVCF_CUDA(launch_hier_unions(ctx->d_hlane_cluster, ctx->d_aabb, ctx->cluster_begin, ctx->hp.K, ctx->hp.ncb, ctx->d_cb_union, s));
 		if (ctx->bin_ns)
@@ -665,7 +657,7 @@ cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s)
 	return cudaEventRecord(ctx->kev[frame][i], s);
 }
 
-int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed)
+int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed, bool allow_rounds)
 {
 	if (!ctx)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null context", who);
@@ -699,7 +691,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 		// sub-tile segments: about 128 light segments per frame (measured: 64 tiles x 2 parts 0.0516 -> 0.0478 ms, x 4 0.0506;
 		// 1 tile x 8 parts 0.0347 -> 0.0252 ms), at most kHMaxParts per tile; HVCF_HIER_PARTS fixes the number (1 = off)
 		ctx->h_parts = 1;
-		if (ctx->h_tiles_per_seg == 1 && !ctx->hier_v1 && !ctx->h_pipe && !ctx->d_hseg_lists && !routed)
+		if (ctx->h_tiles_per_seg == 1 && !ctx->h_pipe && !routed)
 		{
 			uint32_t parts = ctx->h_parts_cfg ? ctx->h_parts_cfg : 128u / ctx->h_num_segs;
 			parts = parts > kHMaxParts ? kHMaxParts : parts;
@@ -712,7 +704,54 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 			}
 		}
 		ctx->h_tiles_total = tiles_total;
-		if (hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
+		ctx->h_num_rounds = 0;
+		if (allow_rounds && ctx->h_parts == 1 && ctx->rounds_mode != 0 && tiles_total >= 2 &&
+			(ctx->rounds_mode > 0 || tiles_total >= ctx->rounds_min_tiles))
+		{
+			// rounds of growing length: head, head * growth, ...; the last one takes the rest.  Early rounds are cut into short
+			// segments (that is where clusters fill up: most of the frame's hits, spread over many warp programs), late ones into
+			// few long segments (sparse: only the groups that are still alive are walked at all).
+			const uint32_t max_rounds = ctx->rounds_mode > 0 ? (static_cast<uint32_t>(ctx->rounds_mode) < kHMaxChunks ? static_cast<uint32_t>(ctx->rounds_mode) : kHMaxChunks) : kHMaxChunks;
+			const uint32_t growth = ctx->rounds_growth < 2 ? 2 : ctx->rounds_growth;
+			uint32_t t = 0, size = ctx->rounds_head ? ctx->rounds_head : 1, nr = 0, seg = 0;
+			while (t < tiles_total && nr < max_rounds)
+			{
+				uint32_t end = static_cast<uint64_t>(t) + size < tiles_total ? t + size : tiles_total;
+				if (nr + 1 == max_rounds || tiles_total - end < size) // the last round takes the rest (no tiny tail round)
+					end = tiles_total;
+				const uint32_t target = nr < 2 ? 128u : ctx->rounds_late_segs;
+				uint32_t tps = (end - t + target - 1) / target;
+				// macro tiles (two-level binning only, pipelined walk only): late rounds are sparse, so M consecutive tiles share one
+				// slot per group.  M by what keeps about four binning CTAs per SM, at most 64, and segments are whole macro tiles.
+				uint32_t mshift = 0;
+				const bool two_level = ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups ||
+					static_cast<uint64_t>(ctx->hp.ncb) * ctx->num_lights >= (1ull << 28));
+				if (nr >= 2 && two_level && !routed && ctx->pipe_mode != 0)
+				{
+					uint32_t want = ctx->rounds_macro >= 0 ? static_cast<uint32_t>(ctx->rounds_macro) : (end - t) / 592u;
+					want = want > 64u ? 64u : want;
+					while ((2u << mshift) <= want)
+						++mshift;
+					tps = ((tps + (1u << mshift) - 1u) >> mshift) << mshift;
+				}
+				hvcf_ctx::Round& r = ctx->h_rounds[nr];
+				r.macro_shift = mshift;
+				r.tile_begin = t, r.tile_end = end, r.tiles_per_seg = tps;
+				r.seg_begin = seg;
+				seg += (end - t + tps - 1) / tps;
+				r.seg_end = seg;
+				r.pipe = mshift ? 1u : (ctx->pipe_mode >= 0 ? (ctx->pipe_mode ? 1u : 0u) : (tps >= ctx->pipe_min_tps ? 1u : 0u));
+				t = end;
+				size = static_cast<uint64_t>(size) * growth > 0x7fffffffu ? 0x7fffffffu : size * growth;
+				++nr;
+			}
+			if (nr >= 2 && seg <= ctx->h_max_segs)
+			{
+				ctx->h_num_rounds = nr;
+				ctx->h_num_segs = seg;
+			}
+		}
+		if (ctx->h_num_rounds < 2 && hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
 			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull: %u light segments need more than %u early-exit chunks", ctx->h_num_segs, kHMaxChunks);
 		HVCF_CUDA(hvcf_kmark(ctx, frame, 0, s));
 	}
@@ -734,7 +773,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 	const uint32_t zero_words = ctx->range_cleared ? 0u : ctx->cluster_count * kHMaxChunks;
 	DeviceStats* clear_stats = ctx->range_cleared ? nullptr : stats;
 	// few lights, whole frame in one call, one-level binning, no animation: transform + binning as one kernel
-	if (flags == (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN) && begin == 0 && last && !ctx->range_cleared && !ctx->hier_v1 && !ctx->anim_len &&
+	if (flags == (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN) && begin == 0 && last && !ctx->range_cleared && !ctx->anim_len &&
 		ctx->xbin_max_lights && n <= ctx->xbin_max_lights &&
 		!(ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups || static_cast<uint64_t>(ctx->hp.ncb) * n >= (1ull << 28))))
 	{
@@ -790,11 +829,10 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			ctx->range_cleared = true;
 			++ctx->open_launches;
 		}
-		if (!ctx->hier_v1)
 		{
 			BinParams b{};
 			b.lights_view = ctx->d_lights_view;
-			b.cb_union = ctx->d_cb_union;
+			b.cb_union = ctx->bin_alive ? ctx->d_alive_union : ctx->d_cb_union; // rounds: the boxes of the clusters that are still alive
 			b.ncb = ctx->hp.ncb;
 			b.tiles_cap = ctx->tiles_cap;
 			b.bin_count = ctx->d_bin_count;
@@ -802,6 +840,8 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			b.bin_idx = ctx->d_bin_idx;
 			b.stats = stats;
 			b.tile_begin = begin / kTileLights;
+			b.group_alive = ctx->bin_alive;
+			b.macro = ctx->bin_macro;
 			b.sb_union = ctx->d_sb_union;
 			b.sg = ctx->bin_sg;
 			// the two-level kernel pays once there are many (group, light) pairs: >= 48 groups, or >= 2^28 pairs (measured:
@@ -818,32 +858,43 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 	return HVCF_OK;
 }
 
-int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
+// count pass of one round (round < 0: the whole frame in one launch, or head + rest with HVCF_HIER_SPLIT)
+static int hier_count(hvcf_ctx* ctx, uint32_t frame, int round, cudaStream_t s, uint32_t* launches)
 {
-	DeviceStats* stats = &ctx->d_stats[frame];
 	HierParams p = hier_params(ctx, frame);
-	if (ctx->timing)
-		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+	if (round >= 0)
+	{
+		const hvcf_ctx::Round& r = ctx->h_rounds[round];
+		p.seg_begin = r.seg_begin, p.seg_end = r.seg_end;
+		p.tile_begin = r.tile_begin, p.tiles_total = r.tile_end;
+		p.tiles_per_seg = r.tiles_per_seg, p.pipe = r.pipe;
+		p.macro_shift = r.macro_shift;
+		p.round_chunk = static_cast<uint32_t>(round);
+		p.round_alive = round > 0 ? ctx->d_group_alive + static_cast<size_t>(round) * ctx->hp.ncb : nullptr;
+		HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), false, p, s));
+		++*launches;
+		return HVCF_OK;
+	}
 	// the first segments run as a launch of their own when the whole grid would otherwise start at once: the
 	// later segments then begin with the dense clusters already known to be full (PDL-chained, one extra launch)
 	const uint32_t head = ctx->h_split_head < ctx->h_num_segs ? ctx->h_split_head : 0u;
-	uint32_t launches = ctx->open_launches;
 	if (head)
 	{
 		p.seg_end = head;
-		HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
+		HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), false, p, s));
 		p.seg_begin = head;
+		p.tile_begin = head * p.tiles_per_seg;
 		p.seg_end = ctx->h_num_segs;
-		++launches;
+		++*launches;
 	}
-	HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), false, p, s));
-	HVCF_CUDA(hvcf_kmark(ctx, frame, 3, s));
-	if (ctx->timing)
-	{
-		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
-		ctx->ev_valid[frame] = true;
-	}
-	FinalizeParams f;
+	HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), false, p, s));
+	++*launches;
+	return HVCF_OK;
+}
+
+static int hier_finalize(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
+{
+	FinalizeParams f{};
 	f.seg_counts = ctx->d_hseg_counts;
 	f.seg_prefix = ctx->d_hseg_prefix;
 	f.num_segs = ctx->h_num_segs;
@@ -853,11 +904,87 @@ int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
 	f.counts = ctx->d_counts;
 	f.offsets = ctx->d_hoffsets;
 	f.shard_total = ctx->d_shard_total;
-	f.stats = stats;
-	f.skip_prefix = p.seg_lists ? 1u : 0u;
+	f.stats = &ctx->d_stats[frame];
+	if (ctx->h_num_rounds >= 2)
+	{
+		f.cum = ctx->d_hscratch;
+		f.num_rounds = ctx->h_num_rounds;
+		for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
+			f.round_seg_begin[r] = ctx->h_rounds[r].seg_begin;
+		f.round_seg_begin[ctx->h_num_rounds] = ctx->h_num_segs;
+	}
 	HVCF_CUDA(launch_hier_finalize(f, s));
 	HVCF_CUDA(hvcf_kmark(ctx, frame, 4, s));
-	ctx->last_launches[frame] = launches + 2;
+	return HVCF_OK;
+}
+
+static cudaError_t round_mark(hvcf_ctx* ctx, uint32_t frame, uint32_t round, int i, cudaStream_t s)
+{
+	if (!ctx->ktimes)
+		return cudaSuccess;
+	cudaEvent_t& e = ctx->kev_round[frame][round][i];
+	if (!e)
+	{
+		const cudaError_t rc = cudaEventCreate(&e);
+		if (rc != cudaSuccess)
+			return rc;
+	}
+	return cudaEventRecord(e, s);
+}
+
+// rounds: level-0 binning (against the groups that the earlier rounds left alive) + count pass, round by round, over the tiles
+// that have been transformed (or, routed frames, have arrived in the inbox) already.  bin_round(round) launches the round's binning.
+static int hier_rounds(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s, uint32_t* launches, const std::function<int(uint32_t)>& bin_round)
+{
+	for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
+	{
+		HVCF_CUDA(round_mark(ctx, frame, r, 0, s));
+		ctx->bin_alive = nullptr;
+		if (r > 0)
+		{
+			uint32_t* flags = ctx->d_group_alive + static_cast<size_t>(r) * ctx->hp.ncb; // kept per round: the write pass asks again
+			HVCF_CUDA(launch_hier_alive(ctx->d_hlane_cluster, ctx->d_aabb, ctx->cluster_begin, ctx->d_hscratch, ctx->hp.K, ctx->hp.ncb, ctx->cap, flags,
+				ctx->d_alive_union, s));
+			ctx->bin_alive = flags;
+			++*launches;
+		}
+		ctx->bin_macro = 1u << ctx->h_rounds[r].macro_shift;
+		const int rc = bin_round(r);
+		ctx->bin_alive = nullptr;
+		ctx->bin_macro = 1;
+		if (rc != HVCF_OK)
+			return rc;
+		++*launches;
+		HVCF_CUDA(round_mark(ctx, frame, r, 1, s));
+		const int rc2 = hier_count(ctx, frame, static_cast<int>(r), s, launches);
+		if (rc2 != HVCF_OK)
+			return rc2;
+		HVCF_CUDA(round_mark(ctx, frame, r, 2, s));
+	}
+	return HVCF_OK;
+}
+
+int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s)
+{
+	if (ctx->timing)
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+	uint32_t launches = ctx->open_launches;
+	if (ctx->h_num_rounds < 2)
+	{
+		const int rc = hier_count(ctx, frame, -1, s, &launches);
+		if (rc != HVCF_OK)
+			return rc;
+	}
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 3, s));
+	if (ctx->timing)
+	{
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
+		ctx->ev_valid[frame] = true;
+	}
+	const int rc = hier_finalize(ctx, frame, s);
+	if (rc != HVCF_OK)
+		return rc;
+	ctx->last_launches[frame] = launches + 1;
 	ctx->range_open = false;
 	return HVCF_OK;
 }
@@ -866,7 +993,7 @@ int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, u
 {
 	if (!ctx)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_cull_begin_range: null context");
-	if (!ctx->hier || ctx->hier_v1)
+	if (!ctx->hier)
 		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_begin_range: hierarchical mode only");
 	if (flags == 0)
 		flags = HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN;
@@ -881,7 +1008,7 @@ int hvcf_cull_begin_range(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, u
 		((flags & HVCF_RANGE_TRANSFORM) ? ctx->range_transformed != 0 : ctx->range_binned != 0));
 	if (first)
 	{
-		const int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin_range", false);
+		const int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin_range", false, false);
 		if (rc != HVCF_OK)
 			return rc;
 	}
@@ -945,7 +1072,7 @@ int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* out_bytes
 int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 {
 	NvtxZone zone("Light_Culling");
-	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin", false);
+	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_begin", false, true);
 	if (rc != HVCF_OK)
 		return rc;
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -954,7 +1081,22 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	const uint32_t n = ctx->num_lights;
 	if (ctx->hier)
 	{
-		rc = hier_range(ctx, frame, 0, n, ctx->hier_v1 ? HVCF_RANGE_TRANSFORM : (HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN), s);
+		if (ctx->h_num_rounds >= 2)
+		{
+			rc = hier_range(ctx, frame, 0, n, HVCF_RANGE_TRANSFORM, s); // every light to view space (and the frame's counters cleared)
+			if (rc != HVCF_OK)
+				return rc;
+			rc = hier_rounds(ctx, frame, s, &ctx->open_launches, [&](uint32_t r) {
+				const hvcf_ctx::Round& rd = ctx->h_rounds[r];
+				const uint64_t le = static_cast<uint64_t>(rd.tile_end) * kTileLights;
+				--ctx->open_launches; // hier_range counts the launch itself
+				return hier_range(ctx, frame, rd.tile_begin * kTileLights, le < n ? static_cast<uint32_t>(le) : n, HVCF_RANGE_BIN, s);
+			});
+			if (rc != HVCF_OK)
+				return rc;
+			return hvcf_hier_close(ctx, frame, s);
+		}
+		rc = hier_range(ctx, frame, 0, n, HVCF_RANGE_TRANSFORM | HVCF_RANGE_BIN, s);
 		if (rc != HVCF_OK)
 			return rc;
 		return hvcf_hier_close(ctx, frame, s);
@@ -996,7 +1138,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 		p.stats = stats;
 		if (ctx->timing)
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
-		HVCF_CUDA(launch_cull(ctx->variant, p, num_segs, s));
+		HVCF_CUDA(launch_cull(p, num_segs, s));
 		if (ctx->timing)
 		{
 			HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
@@ -1024,27 +1166,23 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	{
 		HierParams hp = hier_params(ctx, frame);
 		hp.index_base = d_index_base;
-		if (hp.seg_lists)
+		if (ctx->h_num_rounds >= 2)
 		{
-			// the count pass kept its hits: concatenate the (segment, cluster) lists instead of walking the hierarchy again
-			CopyParams cp{};
-			cp.seg_counts = ctx->d_hseg_counts;
-			cp.seg_lists = ctx->d_hseg_lists;
-			cp.num_segs = ctx->h_num_segs;
-			cp.cluster_count = ctx->cluster_count;
-			cp.cluster_begin = ctx->cluster_begin;
-			cp.cap = ctx->cap;
-			cp.counts = ctx->d_counts;
-			cp.offsets = ctx->d_hoffsets;
-			cp.index_base = d_index_base;
-			cp.shard_total = ctx->d_shard_total;
-			cp.cells = ctx->d_cells;
-			cp.indices = ctx->d_indices;
-			cp.frame_total = &ctx->d_global_index[frame];
-			HVCF_CUDA(launch_hier_copy(cp, static_cast<cudaStream_t>(stream)));
+			// one launch per round (their segments differ in length, and long ones take the pipelined walk); independent of each other
+			for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
+			{
+				const hvcf_ctx::Round& rd = ctx->h_rounds[r];
+				hp.seg_begin = rd.seg_begin, hp.seg_end = rd.seg_end;
+				hp.tile_begin = rd.tile_begin, hp.tiles_total = rd.tile_end;
+				hp.tiles_per_seg = rd.tiles_per_seg, hp.pipe = rd.pipe;
+				hp.macro_shift = rd.macro_shift;
+				hp.round_alive = r > 0 ? ctx->d_group_alive + static_cast<size_t>(r) * ctx->hp.ncb : nullptr;
+				HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+			}
+			ctx->last_launches[frame] += ctx->h_num_rounds - 1;
 		}
 		else
-			HVCF_CUDA((ctx->hier_v1 ? launch_hier : launch_hier2)(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+			HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
 		if (ctx->ktimes && ctx->kev[frame][4])
 		{
 			if (!ctx->kev[frame][5])
@@ -1540,7 +1678,7 @@ int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_wo
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_trace: null argument");
 	if (!ctx->d_trace)
 		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_trace: create the context with HVCF_HIER_TRACE=1 (hierarchical mode)");
-	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * (ctx->hier_v1 ? 1 : 2) * ctx->h_num_segs;
+	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * 2 * ctx->h_num_segs;
 	const size_t words = ctas * 8 < max_words ? ctas * 8 : max_words;
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	HVCF_CUDA(cudaDeviceSynchronize());
@@ -1558,8 +1696,53 @@ int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5])
 	HVCF_CUDA(cudaEventSynchronize(ctx->kev[frame][5]));
 	for (int i = 0; i < 5; ++i)
 		HVCF_CUDA(cudaEventElapsedTime(&out_ms[i], ctx->kev[frame][i], ctx->kev[frame][i + 1]));
+	if (ctx->h_num_rounds >= 2 && ctx->kev_round[frame][0][2]) // rounds: bin = the rounds' alive + binning launches, count = their count passes
+	{
+		out_ms[1] = out_ms[2] = 0.0f;
+		for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
+		{
+			float a = 0.0f, b = 0.0f;
+			HVCF_CUDA(cudaEventElapsedTime(&a, ctx->kev_round[frame][r][0], ctx->kev_round[frame][r][1]));
+			HVCF_CUDA(cudaEventElapsedTime(&b, ctx->kev_round[frame][r][1], ctx->kev_round[frame][r][2]));
+			out_ms[1] += a, out_ms[2] += b;
+		}
+		HVCF_CUDA(cudaEventElapsedTime(&out_ms[3], ctx->kev_round[frame][ctx->h_num_rounds - 1][2], ctx->kev[frame][4]));
+	}
 	if (ctx->kev_exchange[frame]) // sharded frames: the wait for the other ranks' totals sits between finalize and the write pass
 		HVCF_CUDA(cudaEventElapsedTime(&out_ms[4], ctx->kev[frame][6], ctx->kev[frame][5]));
+	return HVCF_OK;
+}
+
+int hvcf_debug_rounds(hvcf_ctx* ctx, uint32_t plan[68], uint32_t what, void* dst, size_t bytes)
+{
+	if (!ctx || !plan)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: null argument");
+	if (!ctx->hier)
+		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_rounds: hierarchical mode only");
+	memset(plan, 0, sizeof(uint32_t) * 68);
+	plan[0] = ctx->hp.ncb, plan[1] = ctx->hp.K, plan[2] = ctx->tiles_cap, plan[3] = ctx->h_num_rounds;
+	for (uint32_t r = 0; r < ctx->h_num_rounds && r < kHMaxChunks; ++r)
+	{
+		const hvcf_ctx::Round& rd = ctx->h_rounds[r];
+		uint32_t* o = plan + 4 + 8 * r;
+		o[0] = rd.seg_begin, o[1] = rd.seg_end, o[2] = rd.tile_begin, o[3] = rd.tile_end, o[4] = rd.tiles_per_seg, o[5] = rd.pipe, o[6] = rd.macro_shift;
+	}
+	if (!dst)
+		return HVCF_OK;
+	HVCF_CUDA(cudaSetDevice(ctx->device));
+	HVCF_CUDA(cudaDeviceSynchronize());
+	const void* src = nullptr;
+	size_t have = 0;
+	switch (what)
+	{
+	case 0: src = ctx->d_group_alive, have = sizeof(uint32_t) * ctx->hp.ncb * kHMaxChunks; break;
+	case 1: src = ctx->d_bin_count, have = sizeof(uint32_t) * static_cast<size_t>(ctx->hp.ncb) * ctx->tiles_cap; break;
+	case 2: src = ctx->d_alive_union, have = sizeof(float) * 8 * ctx->hp.ncb; break;
+	default: return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: what = %u", what);
+	}
+	if (bytes > have)
+		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: %zu bytes > %zu", bytes, have);
+	HVCF_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
 	return HVCF_OK;
 }
 

@@ -81,6 +81,81 @@ __global__ void __launch_bounds__(256) hier_unions_kernel(const uint32_t* __rest
 }
 
 // ======================================================================================================
+// Rounds (frames of many tiles; hvcf_api.cu plans them): the light stream is cut into a few rounds of growing length, and each
+// round is binned and counted by launches of its own.  BETWEEN launches cum[cluster][*] is exact -- every count of the earlier
+// rounds has been added -- so a cluster whose row sums to >= cap provably has its first `cap` hits among the lights of those
+// rounds (LightCulling.comp:71-77), and a GROUP without any cluster below its cap needs no light of any later round.  This
+// kernel publishes that per group, together with the union box of the group's LIVE clusters; the binning kernels of the next
+// round leave the dead groups' slots empty and test the others against that tighter box.  It is the count pass's per-cluster early exit lifted to level 0:
+// on the reference scene at 16M lights every cluster in front of slice 64 is full after the first 70,000 lights.
+// One CTA per group (8 warp programs x K blocks x 32 lanes).
+// ======================================================================================================
+__global__ void __launch_bounds__(256) hier_alive_kernel(const uint32_t* __restrict__ lane_cluster, const hvcf_aabb* __restrict__ aabbs,
+	uint32_t cluster_begin, const uint32_t* cum, uint32_t K, uint32_t cap, uint32_t* __restrict__ group_alive, float* __restrict__ alive_union)
+{
+	__shared__ float s_u[8][6];
+	__shared__ int s_nan;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const float kInf = __int_as_float(0x7f800000);
+	grid_dep_launch();
+	if (threadIdx.x == 0)
+		s_nan = 0;
+	grid_dep_wait(); // cum: the count pass of the previous round
+	float lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+	bool alive = false, nan = false;
+	for (uint32_t k = 0; k < K; ++k)
+	{
+		const uint32_t c = lane_cluster[(static_cast<size_t>((blockIdx.x * 8 + warp) * K + k) << 5) + lane];
+		if (c == kSkip)
+			continue;
+		const uint4* row = reinterpret_cast<const uint4*>(cum + static_cast<size_t>(c) * kHMaxChunks);
+		const uint4 a = __ldcg(row), b = __ldcg(row + 1);
+		if ((a.x + a.y) + (a.z + a.w) + (b.x + b.y) + (b.z + b.w) >= cap)
+			continue; // full: no later light can enter its list
+		alive = true;
+		const float4* bx = reinterpret_cast<const float4*>(aabbs + cluster_begin + c);
+		const float4 mn = bx[0], mx = bx[1];
+		nan = nan || !(mn.x == mn.x && mn.y == mn.y && mn.z == mn.z && mx.x == mx.x && mx.y == mx.y && mx.z == mx.z);
+		lo[0] = fminf(lo[0], mn.x), lo[1] = fminf(lo[1], mn.y), lo[2] = fminf(lo[2], mn.z);
+		hi[0] = fmaxf(hi[0], mx.x), hi[1] = fmaxf(hi[1], mx.y), hi[2] = fmaxf(hi[2], mx.z);
+	}
+	const int any = __syncthreads_or(alive ? 1 : 0);
+	if (__any_sync(0xffffffffu, nan) && lane == 0)
+		s_nan = 1;
+#pragma unroll
+	for (int i = 0; i < 3; ++i)
+	{
+		lo[i] = warp_min_f(lo[i]);
+		hi[i] = warp_max_f(hi[i]);
+	}
+	if (lane == 0)
+	{
+		s_u[warp][0] = lo[0], s_u[warp][1] = lo[1], s_u[warp][2] = lo[2];
+		s_u[warp][3] = hi[0], s_u[warp][4] = hi[1], s_u[warp][5] = hi[2];
+	}
+	__syncthreads();
+	if (threadIdx.x == 0)
+		group_alive[blockIdx.x] = any ? 1u : 0u;
+	if (threadIdx.x < 3)
+	{
+		// the union box of the LIVE clusters only (layout and NaN rule of hier_unions_kernel): it contains every box that can still
+		// take a light, so the level-0 test against it stays exactly conservative -- and it is much tighter than the group's box
+		// where a group straddles the edge of the lit region (its full clusters are the ones inside)
+		float l = kInf, h = -kInf;
+		for (int w = 0; w < 8; ++w)
+		{
+			l = fminf(l, s_u[w][threadIdx.x]);
+			h = fmaxf(h, s_u[w][3 + threadIdx.x]);
+		}
+		float* u = alive_union + static_cast<size_t>(blockIdx.x) * 8;
+		u[threadIdx.x] = s_nan ? -kInf : l;
+		u[4 + threadIdx.x] = s_nan ? kInf : h;
+		if (threadIdx.x == 0)
+			u[3] = u[7] = 0.0f;
+	}
+}
+
+// ======================================================================================================
 // level 0: grid = (ceil(ncb / 8), tiles).  The tile is staged once per CTA by a TMA bulk copy; warp w tests
 // all of it against group cbg * 8 + w and appends survivors to the (group, tile) slot in light order.
 // Measured and rejected on B200 (B1M, this kernel 57 us warm): a two-level variant (super-groups of 4 groups first:
@@ -101,6 +176,17 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 	}
 	__syncthreads();
 	grid_dep_wait(); // the tile is written by the transform kernel of this frame
+	// rounds: groups without a cluster below its cap keep an empty slot; a CTA whose groups are all dead does not stage the tile
+	uint32_t alive_mask = 0xffu;
+	if (p.group_alive)
+	{
+		const uint32_t g = blockIdx.x * kBinWarps + (lane & 7u);
+		alive_mask = __ballot_sync(0xffffffffu, g < p.ncb && __ldcg(&p.group_alive[g]) != 0u) & 0xffu;
+		if (((alive_mask >> warp) & 1u) == 0u && cb < p.ncb && lane == 0)
+			p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = 0u;
+		if (alive_mask == 0u)
+			return;
+	}
 	if (threadIdx.x == 0)
 	{
 		mbar_arrive_expect_tx(&bar, kTileBytes);
@@ -109,13 +195,13 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 	float lo[3] = {0.0f, 0.0f, 0.0f}, hi[3] = {0.0f, 0.0f, 0.0f};
 	if (cb < p.ncb)
 	{
-		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
-		const float4 a = __ldg(u), b = __ldg(u + 1);
+		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8); // (rounds: written by hier_alive_kernel just before)
+		const float4 a = __ldcg(u), b = __ldcg(u + 1);
 		lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
 		hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
 	}
 	mbar_wait(&bar, 0);
-	if (cb >= p.ncb)
+	if (cb >= p.ncb || ((alive_mask >> warp) & 1u) == 0u)
 		return;
 	const float4* tile = reinterpret_cast<const float4*>(s_tile);
 	const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
@@ -158,9 +244,6 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 // grid = segments x (ncb * 8 / kMainWarps) CTAs of kMainWarps independent warp programs; warp program
 // `unit` owns blocks unit * K .. unit * K + K - 1 (lane = cluster) and belongs to group unit / 8.
 // ======================================================================================================
-// LISTS (count pass only): every counted hit below the lane's limit is also stored, in light order, in the
-// (segment, cluster) list seg_lists[seg][cluster][cap]; hier_copy_kernel then concatenates the lists into the index buffer
-// and the write pass (the second walk of the hierarchy) is not needed.
 // Measured and rejected on B200 (r01y kernels, per-kernel events): one warp program serving 2 or 4 segments in a loop (stride
 // gridDim.y) with the lane's cluster indices and boxes loaded once.  The loop-carried state costs registers (write pass K=2
 // 64 -> 96, count pass K=2 spills 48 B) and the gain of the saved round trips does not pay for it: B1M count pass 97 -> 101 us,
@@ -197,7 +280,7 @@ __device__ __forceinline__ void cp_async_wait()
 // with many tiles per light segment
 // SUB: sub-tile light segments (p.parts > 1); a template parameter so that whole-tile frames run exactly the code they ran before
 // INBOX: the tiles are inbox tiles of a routed frame (hvcf_shard.cu); a template parameter so that every other frame runs exactly the code it ran before
-template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB, bool INBOX = false>
+template <int K, bool WRITE, bool PIPE, bool SUB, bool INBOX = false>
 __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams p)
 {
 	__shared__ __align__(16) float4 s_rec2[kMainWarps][PIPE ? 2 : 1][64];
@@ -210,7 +293,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// the tile's slot (nb = its batches of 64 records).  Slots are in light order, so segments still are; the dense slots'
 	// serial walks -- the tail of the count pass at grid A x 65,536 lights, profiles/r01zl -- are cut into P shorter ones.
 	const uint32_t parts = SUB ? p.parts : 1u;
-	uint32_t part = 0, t_begin = seg * p.tiles_per_seg;
+	uint32_t part = 0, t_begin = p.tile_begin + (seg - p.seg_begin) * p.tiles_per_seg;
 	if (parts > 1)
 	{
 		part = seg % parts;
@@ -227,7 +310,11 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// instead of the whole prologue -- 63 % of the write pass's warp programs at B1M ran ~190 instructions of prologue only
 	// to find that they own no output (profiles/r01q).  Segment 0 stays: it writes the light cells.
 	// (the slot index is recomputed where it is needed: keeping it live cost the count pass two registers = one CTA per SM)
-	if (WRITE && seg != 0 && !p.trace && __ldg(&p.unit_any[any_slot(seg, unit)]) == 0u)
+	// rounds: the group held its cap everywhere before this round -- nothing to count, nothing to write, and nobody reads this
+	// program's counts (hier_finalize_kernel stops at the round before which a cluster was full)
+	if (p.round_alive && !p.trace && __ldcg(&p.round_alive[cb]) == 0u)
+		return;
+	if (WRITE && seg != 0 && !p.trace && __ldcg(&p.unit_any[any_slot(seg, unit)]) == 0u)
 		return;
 	// count pass: a group whose level-0 slots are empty for every tile of this segment has nothing to test -- zero counts,
 	// no boxes, no early-exit counters, no union reductions (HVCF_EMPTY_SKIP=0 at build time switches the check off)
@@ -240,13 +327,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		uint32_t some = 0;
 		if (parts > 1)
 		{
-			const uint32_t n0 = __ldg(&p.bin_count[d0]);
-			const uint32_t nb = n0 > kBinCap ? (INBOX ? (__ldg(&p.tile_cnt[t_begin]) + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
+			const uint32_t n0 = __ldcg(&p.bin_count[d0]);
+			const uint32_t nb = n0 > kBinCap ? (INBOX ? (__ldcg(&p.tile_cnt[t_begin]) + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
 			some = (part + 1) * nb / parts > part * nb / parts ? 1u : 0u;
 		}
-		else
-			for (uint32_t t = lane; t < ntiles; t += 32)
-				some |= __ldg(&p.bin_count[d0 + t]);
+		else // (macro tiles: only the count of a macro tile's first tile means anything)
+			for (uint32_t t = lane << p.macro_shift; t < ntiles; t += 32u << p.macro_shift)
+				some |= __ldcg(&p.bin_count[d0 + t]);
 		if (!__any_sync(0xffffffffu, some != 0))
 		{
 #pragma unroll
@@ -269,9 +356,8 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	uint32_t cnt[K];     // pass 1: hits counted in this segment; pass 2: entries written
 	uint32_t limit[K];   // pass 1: hits still missing before the cap; pass 2: entries this lane owns
 	uint32_t wbase[K];   // pass 2: first output slot
-	size_t lbase[K];     // LISTS: first word of this lane's (segment, cluster) list
 	bool active[K];
-	const uint32_t chunk = hier_chunk_of(seg);
+	const uint32_t chunk = p.round_chunk != 0xffffffffu ? p.round_chunk : hier_chunk_of(seg);
 	const uint32_t index_base = (WRITE && p.index_base) ? *p.index_base : 0u;
 #pragma unroll
 	for (int k = 0; k < K; ++k)
@@ -281,7 +367,6 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		cnt[k] = 0;
 		limit[k] = 0;
 		wbase[k] = 0;
-		lbase[k] = valid ? (static_cast<size_t>(seg) * p.cluster_count + cidx[k]) * p.cap : 0;
 		active[k] = false;
 		lo[k][0] = lo[k][1] = lo[k][2] = kInf;
 		hi[k][0] = hi[k][1] = hi[k][2] = -kInf;
@@ -443,8 +528,6 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 						}
 						else
 						{
-							if (LISTS && hit && cnt[k] < limit[k])
-								p.seg_lists[lbase[k] + cnt[k]] = tile_base + idxs[j[q]];
 							cnt[k] += hit ? 1u : 0u;
 						}
 					}
@@ -465,8 +548,6 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 					}
 					else
 					{
-						if (LISTS && hit && cnt[k] < limit[k])
-							p.seg_lists[lbase[k] + cnt[k]] = tile_base + idxs[j];
 						cnt[k] += hit ? 1u : 0u;
 					}
 				}
@@ -498,20 +579,28 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// most slots there hold a single batch) -- hence a template parameter, set by the host from the tiles per segment.
 	if constexpr (PIPE)
 	{
-		uint32_t it_t = 0, it_b = 0, it_n0 = 0, it_nb = 0; // the batch to FETCH next: tile inside the segment, batch, slot count, batches
+		// macro tiles (p.macro_shift = log2 M; hier_bin2_kernel): a slot belongs to M consecutive tiles, its count sits at the first
+		// of them, it holds M x kBinCap records and its 16-bit indices run over the M tiles.  M = 1: a slot per tile, as ever.
+		const uint32_t ms = INBOX ? 0u : p.macro_shift, mstep = 1u << ms;
+		uint32_t it_t = 0, it_b = 0, it_n0 = 0, it_nb = 0; // the batch to FETCH next: (first) tile inside the segment, batch, slot count, batches
+		bool it_raw = false;                                // the slot overflowed: its tiles are read raw
 		uint32_t cnt_chunk = 0xffffffffu, my_cnt = 0;
-		auto seek = [&]() -> bool { // first non-empty tile at or after it_t
-			for (; it_t < ntiles; ++it_t)
+		auto seek = [&]() -> bool { // first non-empty slot at or after it_t
+			for (; it_t < ntiles; it_t += mstep)
 			{
-				if ((it_t >> 5) != cnt_chunk)
+				const uint32_t mi = it_t >> ms;
+				if ((mi >> 5) != cnt_chunk)
 				{
-					cnt_chunk = it_t >> 5;
-					my_cnt = cnt_chunk * 32 + lane < ntiles ? __ldg(&p.bin_count[desc0 + cnt_chunk * 32 + lane]) : 0u;
+					cnt_chunk = mi >> 5;
+					const uint32_t tt = (cnt_chunk * 32 + lane) << ms;
+					my_cnt = tt < ntiles ? __ldcg(&p.bin_count[desc0 + tt]) : 0u;
 				}
-				it_n0 = __shfl_sync(0xffffffffu, my_cnt, it_t & 31u);
+				it_n0 = __shfl_sync(0xffffffffu, my_cnt, mi & 31u);
 				if (it_n0)
 				{
-					it_nb = it_n0 > kBinCap ? (INBOX ? (__ldg(&p.tile_cnt[t_begin + it_t]) + 63u) / 64u : kTileGroups) : (it_n0 + 63) / 64;
+					const uint32_t meff = min(mstep, ntiles - it_t);
+					it_raw = it_n0 > meff * kBinCap;
+					it_nb = it_raw ? (INBOX ? (__ldcg(&p.tile_cnt[t_begin + it_t]) + 63u) / 64u : meff * kTileGroups) : (it_n0 + 63) / 64;
 					it_b = 0;
 					return true;
 				}
@@ -521,15 +610,15 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		auto fetch = [&](uint32_t buf) { // batch (it_t, it_b) -> buffer buf
 			float4* const rec = s_rec2[warp][buf];
 			const uint32_t tile_id = t_begin + it_t;
-			if (it_n0 > kBinCap) // raw tile: the lane's packed pair, converted when it is consumed
+			if (it_raw) // raw tile(s): the lane's packed pair, converted when it is consumed
 			{
 				const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16) + it_b * 64;
 				if constexpr (INBOX) // inbox tile: plain records, `valid` of them; zero fill = (0, 0, 0, r2 = 0) never hits
 				{
-					const uint32_t valid = __ldg(&p.tile_cnt[tile_id]), i0 = it_b * 64 + lane, i1 = i0 + 32;
+					const uint32_t valid = __ldcg(&p.tile_cnt[tile_id]), i0 = it_b * 64 + lane, i1 = i0 + 32;
 					cp_async16(rec + lane, lv + (i0 < valid ? lane : 0u), i0 < valid ? 16u : 0u);
 					cp_async16(rec + 32 + lane, lv + (i1 < valid ? 32 + lane : 0u), i1 < valid ? 16u : 0u);
-					if ((WRITE || LISTS) && lane < 8)
+					if (WRITE && lane < 8)
 						cp_async16(reinterpret_cast<uint4*>(s_idx2[warp][buf]) + lane,
 							reinterpret_cast<const uint4*>(p.tile_ids + static_cast<size_t>(tile_id) * kTileLights + it_b * 64) + lane, 16u);
 				}
@@ -546,7 +635,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				// beyond the slot's count: zero fill = (0, 0, 0, r2 = 0), and no squared distance is < 0
 				cp_async16(rec + lane, p.bin_rec + slot + (i0 < it_n0 ? i0 : 0u), i0 < it_n0 ? 16u : 0u);
 				cp_async16(rec + 32 + lane, p.bin_rec + slot + (i1 < it_n0 ? i1 : 0u), i1 < it_n0 ? 16u : 0u);
-				if ((WRITE || LISTS) && lane < 8) // 64 tile indices = 8 x 16 B (slots are whole: reading past the count is in bounds)
+				if (WRITE && lane < 8) // 64 tile indices = 8 x 16 B (slots are whole: reading past the count is in bounds)
 					cp_async16(reinterpret_cast<uint4*>(s_idx2[warp][buf]) + lane, reinterpret_cast<const uint4*>(p.bin_idx + slot + it_b * 64) + lane, 16u);
 			}
 			cp_async_commit();
@@ -558,11 +647,11 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		while (have && !warp_done)
 		{
 			const uint32_t c_t = it_t, c_b = it_b;
-			const bool c_raw = it_n0 > kBinCap;
+			const bool c_raw = it_raw;
 			bool have_next = true;
 			if (++it_b >= it_nb)
 			{
-				++it_t;
+				it_t += mstep;
 				have_next = seek();
 			}
 			__syncwarp(); // everyone is done with the buffer the next batch goes into
@@ -596,7 +685,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	for (uint32_t tb = 0; tb < ntiles && !warp_done; tb += 32)
 	{
 		// survivor counts of the next 32 tiles in one coalesced load
-		const uint32_t my_cnt = tb + lane < ntiles ? __ldg(&p.bin_count[desc0 + tb + lane]) : 0u;
+		const uint32_t my_cnt = tb + lane < ntiles ? __ldcg(&p.bin_count[desc0 + tb + lane]) : 0u;
 		const uint32_t tn = min(32u, ntiles - tb);
 		for (uint32_t ti = 0; ti < tn && !warp_done; ++ti)
 		{
@@ -607,7 +696,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 			const uint32_t tile_base = (INBOX ? (tile_id & p.tile_mask) : tile_id) * kTileLights;
 			// a slot that overflowed means the group's filter is not selective for this tile: read the raw tile
 			const bool raw = n0 > kBinCap;
-			const uint32_t raw_valid = (INBOX && raw) ? __ldg(&p.tile_cnt[tile_id]) : kTileLights; // inbox tiles are partly filled
+			const uint32_t raw_valid = (INBOX && raw) ? __ldcg(&p.tile_cnt[tile_id]) : kTileLights; // inbox tiles are partly filled
 			const uint32_t nb = raw ? (INBOX ? (raw_valid + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
 			const float4* const lv = p.lights_view + static_cast<size_t>(tile_id) * (kTileBytes / 16);
 			const size_t slot = (desc0 + tb + ti) * kBinCap;
@@ -641,7 +730,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				}
 				else if (raw)
 				{
-					const float4 a = __ldg(lv + bi * 64 + lane), b = __ldg(lv + bi * 64 + 32 + lane);
+					const float4 a = __ldcg(lv + bi * 64 + lane), b = __ldcg(lv + bi * 64 + 32 + lane);
 					r0 = make_float4(a.x, a.z, b.x, b.z);
 					r1 = make_float4(a.y, a.w, b.y, b.w);
 					id0 = bi * 64 + lane;
@@ -654,13 +743,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 					id0 = id1 = 0;
 					if (i0 < n0)
 					{
-						r0 = __ldg(p.bin_rec + slot + i0);
-						id0 = __ldg(p.bin_idx + slot + i0);
+						r0 = __ldcg(p.bin_rec + slot + i0);
+						id0 = __ldcg(p.bin_idx + slot + i0);
 					}
 					if (i1 < n0)
 					{
-						r1 = __ldg(p.bin_rec + slot + i1);
-						id1 = __ldg(p.bin_idx + slot + i1);
+						r1 = __ldcg(p.bin_rec + slot + i1);
+						id1 = __ldcg(p.bin_idx + slot + i1);
 					}
 				}
 				batch(r0, r1, id0, id1, tile_base, my_rec, my_idx, false);
@@ -755,22 +844,42 @@ __global__ void hier_super_unions_kernel(const float* __restrict__ cb_union, uin
 // ROUTED (hvcf_shard.cu): the tile is a tile of this rank's INBOX -- up to 1,024 plain {x, y, z, r*r} records that the light
 // owners compacted in light order, `valid` of them in use -- and the slot's index of a record is the light's 16-bit index inside
 // its route block (rebuilt from the block's survivor bitmask, in_mask), not its position.  Same two phases, same slots; an empty tile only zeroes its slot counts.
+//
+// MACRO TILES (p.macro = M > 1; late rounds of a frame cut into rounds): one CTA takes M consecutive tiles, one after the other
+// (TMA double buffer), and APPENDS every group's survivors to ONE slot per (group, macro tile) -- the M tiles' slots are
+// contiguous in memory, so the macro slot starts at the first tile's slot and holds M x kBinCap records; a record's 16-bit index
+// is (tile inside the macro tile) << 10 | (light inside the tile).  Where few lights survive (the far field of the reference
+// scene: 98 % of the lights produce 0.1 % of the hits) the count / write passes then visit one dense slot instead of M nearly
+// empty ones; the per-visit latency was their whole cost there (profiles/r02m).  Only the slot count of the macro tile's FIRST
+// tile is written and read.
+//
+// Rounds (p.group_alive): only the super-groups that still hold a live group are tested, dead groups keep an empty slot, and a
+// tile whose groups are all dead is not even staged.
 template <bool ROUTED>
 __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinParams p)
 {
 	extern __shared__ __align__(128) unsigned char s_dyn[];
-	unsigned char* const s_tile = s_dyn;                                               // kTileBytes
-	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_dyn + kTileBytes);         // [ns][kTileLights]
+	const uint32_t M = ROUTED ? 1u : p.macro;
+	const uint32_t nbuf = M > 1u ? 2u : 1u;
+	unsigned char* const s_tiles = s_dyn;                                                          // nbuf x kTileBytes
+	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_dyn + nbuf * kTileBytes);               // [ns][kTileLights]
 	uint32_t* const s_cnt = reinterpret_cast<uint32_t*>(s_list + static_cast<size_t>(p.ns) * kTileLights); // [ns]
-	uint16_t* const s_ids = reinterpret_cast<uint16_t*>(s_cnt + ((p.ns + 3u) & ~3u));  // ROUTED: [kTileLights]
-	__shared__ __align__(8) uint64_t bar;
+	uint32_t* const s_gcnt = s_cnt + ((p.ns + 3u) & ~3u);                                          // [ncb] running slot counts
+	uint32_t* const s_galive = s_gcnt + ((p.ncb + 3u) & ~3u);                                      // [ceil(ncb / 32)] live-group bits
+	float4* const s_sbox = reinterpret_cast<float4*>(s_galive + (((p.ncb + 31u) / 32u + 3u) & ~3u)); // [ns][2] super-group boxes {lo, hi}
+	uint16_t* const s_ids = reinterpret_cast<uint16_t*>(s_sbox + 2u * p.ns);                       // ROUTED: [kTileLights]
+	__shared__ __align__(8) uint64_t bar[2];
+	__shared__ uint32_t s_smask;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint32_t tile_id = p.tile_begin + blockIdx.x;
+	const uint32_t tile_id = p.tile_begin + blockIdx.x * M;                 // first tile of this CTA
+	const uint32_t tM = min(M, p.tile_end - tile_id);                       // its tiles
 	grid_dep_launch();
 	if (threadIdx.x == 0)
 	{
-		mbar_init(&bar, 1);
+		mbar_init(&bar[0], 1);
+		mbar_init(&bar[1], 1);
 		mbar_fence_init();
+		s_smask = 0u;
 	}
 	__syncthreads();
 	grid_dep_wait(); // the tile is written by the transform kernel of this frame (or arrived from another rank)
@@ -789,10 +898,63 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 			return;
 		}
 	}
+	// ---- which groups are alive: bits in shared memory (the phases must not wait for a global load per group), live
+	// super-groups as a mask; dead groups get their empty slot here ----
+	{
+		uint32_t mine = 0u;
+		for (uint32_t cb0 = 0; cb0 < p.ncb; cb0 += blockDim.x)
+		{
+			const uint32_t cb = cb0 + threadIdx.x;
+			const bool a = cb < p.ncb && (!p.group_alive || __ldcg(&p.group_alive[cb]) != 0u);
+			const uint32_t bits = __ballot_sync(0xffffffffu, a);
+			if (cb < p.ncb)
+			{
+				if (lane == 0)
+					s_galive[cb >> 5] = bits;
+				s_gcnt[cb] = 0u;
+				if (a)
+					mine |= 1u << (cb / p.sg);
+				else
+					p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = 0u;
+			}
+		}
+		mine = __reduce_or_sync(0xffffffffu, mine);
+		if (lane == 0 && mine)
+			atomicOr(&s_smask, mine);
+	}
+	__syncthreads();
+	const uint32_t smask = s_smask;
+	if (smask == 0u)
+		return;
+	// super-group boxes: the static ones, or -- rounds, where the group boxes have shrunk to their live clusters -- the union of
+	// the live groups' boxes (fminf / fmaxf ignore nothing here: the boxes hold no NaN, a NaN group is (-inf, +inf))
+	for (uint32_t sidx = threadIdx.x; sidx < p.ns * 8u; sidx += blockDim.x)
+	{
+		const uint32_t sgi = sidx >> 3, c = sidx & 7u;
+		float v;
+		if (!p.group_alive)
+			v = __ldg(p.sb_union + static_cast<size_t>(sgi) * 8 + c);
+		else
+		{
+			const bool is_hi = c >= 4;
+			v = is_hi ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
+			for (uint32_t g = sgi * p.sg; g < min(p.ncb, (sgi + 1u) * p.sg); ++g)
+				if ((s_galive[g >> 5] >> (g & 31u)) & 1u)
+				{
+					const float x = __ldcg(p.cb_union + static_cast<size_t>(g) * 8 + c);
+					v = is_hi ? fmaxf(v, x) : fminf(v, x);
+				}
+			if ((c & 3u) == 3u)
+				v = 0.0f;
+		}
+		reinterpret_cast<float*>(s_sbox + 2 * sgi)[c] = v;
+	}
+	__syncthreads();
+	const unsigned char* const src = reinterpret_cast<const unsigned char*>(p.lights_view);
 	if (threadIdx.x == 0)
 	{
-		mbar_arrive_expect_tx(&bar, ROUTED ? valid * 16u : kTileBytes);
-		bulk_copy_g2s(s_tile, reinterpret_cast<const unsigned char*>(p.lights_view) + static_cast<size_t>(tile_id) * kTileBytes, ROUTED ? valid * 16u : kTileBytes, &bar);
+		mbar_arrive_expect_tx(&bar[0], ROUTED ? valid * 16u : kTileBytes);
+		bulk_copy_g2s(s_tiles, src + static_cast<size_t>(tile_id) * kTileBytes, ROUTED ? valid * 16u : kTileBytes, &bar[0]);
 	}
 	if constexpr (ROUTED)
 	{
@@ -801,7 +963,6 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		// t, t + 256, ...: an exclusive prefix of the popcounts gives the rank of a word's first set bit.
 		__shared__ uint32_t s_wsum[kBinWarps];
 		__shared__ uint32_t s_carry;
-		const uint32_t lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
 		const uint32_t words = p.block_tiles * 32u;
 		const uint32_t* mask = p.in_mask + static_cast<size_t>(tile_id & ~(p.block_tiles - 1u)) * 32u;
 		const uint32_t r_begin = (tile_id & (p.block_tiles - 1u)) * kTileLights, r_end = r_begin + valid;
@@ -818,14 +979,14 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 			for (int o = 1; o < 32; o <<= 1)
 			{
 				const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-				if (lane_ >= static_cast<uint32_t>(o))
+				if (lane >= static_cast<uint32_t>(o))
 					inc += t;
 			}
-			if (lane_ == 31)
-				s_wsum[warp_] = inc;
+			if (lane == 31)
+				s_wsum[warp] = inc;
 			__syncthreads();
 			uint32_t before = s_carry;
-			for (uint32_t w = 0; w < warp_; ++w)
+			for (uint32_t w = 0; w < warp; ++w)
 				before += s_wsum[w];
 			uint32_t rank = before + inc - c; // rank of this word's first set bit inside the block's region
 			if (rank < r_end && rank + c > r_begin)
@@ -846,131 +1007,182 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		for (uint32_t i = threadIdx.x; i < valid; i += blockDim.x)
 			p.tile_ids[static_cast<size_t>(tile_id) * kTileLights + i] = s_ids[i];
 	}
-	mbar_wait(&bar, 0);
-	const float4* tile = reinterpret_cast<const float4*>(s_tile);
 	const uint32_t lt = lanemask_lt();
 	const uint32_t ngroups = ROUTED ? (valid + 63u) / 64u : kTileGroups;
+	const uint32_t ns_alive = __popc(smask);
+	const uint32_t slot_cap = tM * kBinCap; // records of a (group, macro tile) slot
 	unsigned long long tests = 0;
-
-	// ---- phase A: super-group survivor lists ----
-	for (uint32_t s = warp; s < p.ns; s += kBinWarps)
+	float4 gb_lo = make_float4(0.0f, 0.0f, 0.0f, 0.0f), gb_hi = gb_lo; // phase B: the box of one of this warp's groups
+	for (uint32_t m = 0; m < tM; ++m)
 	{
-		const float4* u = reinterpret_cast<const float4*>(p.sb_union + static_cast<size_t>(s) * 8);
-		const float4 a4 = __ldg(u), b4 = __ldg(u + 1);
-		const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
-		uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
-		uint32_t cnt = 0;
-#pragma unroll 4
-		for (uint32_t g = 0; g < ngroups; ++g)
+		const uint32_t buf = nbuf == 2u ? (m & 1u) : 0u;
+		// the next tile goes into the other buffer: every warp left it at the barrier that ended tile m - 1
+		if (m + 1u < tM && threadIdx.x == 0)
 		{
-			float4 a, b;
-			bool h0, h1;
-			if constexpr (ROUTED)
-			{
-				// plain records of lights g * 64 + lane and g * 64 + 32 + lane, paired in registers into the packed operand shape
-				const float4 r0 = tile[g * 64 + lane], r1 = tile[g * 64 + 32 + lane];
-				a = make_float4(r0.x, r1.x, r0.y, r1.y);
-				b = make_float4(r0.z, r1.z, r0.w, r1.w);
-				sphere_box_hit2(a, b, lo, hi, h0, h1);
-				h0 = h0 && g * 64 + lane < valid;      // beyond the tile's records: whatever shared memory held
-				h1 = h1 && g * 64 + 32 + lane < valid;
-			}
-			else
-			{
-				a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
-				sphere_box_hit2(a, b, lo, hi, h0, h1);
-			}
-			const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
-			if (h0)
-				list[cnt + __popc(m0 & lt)] = static_cast<uint16_t>(g * 64 + lane);
-			if (h1)
-				list[cnt + __popc(m0) + __popc(m1 & lt)] = static_cast<uint16_t>(g * 64 + 32 + lane);
-			cnt += __popc(m0) + __popc(m1);
+			mbar_arrive_expect_tx(&bar[buf ^ 1u], kTileBytes);
+			bulk_copy_g2s(s_tiles + (buf ^ 1u) * kTileBytes, src + static_cast<size_t>(tile_id + m + 1u) * kTileBytes, kTileBytes, &bar[buf ^ 1u]);
 		}
-		if (lane == 0)
-			s_cnt[s] = cnt;
-		tests += ROUTED ? valid : kTileLights;
-	}
-	__syncthreads();
+		mbar_wait(&bar[buf], (m >> 1) & 1u);
+		const float4* tile = reinterpret_cast<const float4*>(s_tiles + buf * kTileBytes);
 
-	// ---- phase B: every group against its super-group's survivors ----
-	const float* tile_f = reinterpret_cast<const float*>(s_tile);
-	for (uint32_t cb = warp; cb < p.ncb; cb += kBinWarps)
-	{
-		const uint32_t s = cb / p.sg;
-		const uint32_t ns = s_cnt[s];
-		const uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
-		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
-		const float4 a4 = __ldg(u), b4 = __ldg(u + 1);
-		const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
-		const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
-		float4* const rec = p.bin_rec + slot;
-		uint16_t* const idx = p.bin_idx + slot;
-		uint32_t cnt = 0;
-		// two list entries per lane per trip (i0 + lane, then i0 + 32 + lane: ascending), tested as a pair on FADD2/FMUL2 like the
-		// tile pairs of phase A; a missing entry is the never-hit record (r2 = -1)
-		for (uint32_t i0 = 0; i0 < ns; i0 += 64)
+		// ---- phase A: super-group survivor lists ----
+		for (uint32_t si = warp; si < ns_alive; si += kBinWarps)
 		{
-			const uint32_t ia = i0 + lane, ib = ia + 32;
-			uint32_t ta = 0, tb = 0;
-			float4 pa = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = make_float4(0.0f, 0.0f, -1.0f, -1.0f); // (x0,x1,y0,y1), (z0,z1,r0,r1)
-			if (ia < ns)
+			const uint32_t s = __fns(smask, 0u, static_cast<int>(si) + 1); // the si-th live super-group
+			const float4 a4 = s_sbox[2 * s], b4 = s_sbox[2 * s + 1];
+			const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
+			uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
+			uint32_t cnt = 0;
+#pragma unroll 4
+			for (uint32_t g = 0; g < ngroups; ++g)
 			{
-				ta = list[ia];
+				float4 a, b;
+				bool h0, h1;
 				if constexpr (ROUTED)
 				{
-					const float4 r = tile[ta];
-					pa.x = r.x, pa.z = r.y, pb.x = r.z, pb.z = r.w;
+					// plain records of lights g * 64 + lane and g * 64 + 32 + lane, paired in registers into the packed operand shape
+					const float4 r0 = tile[g * 64 + lane], r1 = tile[g * 64 + 32 + lane];
+					a = make_float4(r0.x, r1.x, r0.y, r1.y);
+					b = make_float4(r0.z, r1.z, r0.w, r1.w);
+					sphere_box_hit2(a, b, lo, hi, h0, h1);
+					h0 = h0 && g * 64 + lane < valid;      // beyond the tile's records: whatever shared memory held
+					h1 = h1 && g * 64 + 32 + lane < valid;
 				}
 				else
 				{
-					// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
-					const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
-					pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+					a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+					sphere_box_hit2(a, b, lo, hi, h0, h1);
 				}
-			}
-			if (ib < ns)
-			{
-				tb = list[ib];
-				if constexpr (ROUTED)
-				{
-					const float4 r = tile[tb];
-					pa.y = r.x, pa.w = r.y, pb.y = r.z, pb.w = r.w;
-				}
-				else
-				{
-					const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
-					pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
-				}
-			}
-			bool h0, h1;
-			sphere_box_hit2(pa, pb, lo, hi, h0, h1);
-			const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
-			if ((m0 | m1) != 0)
-			{
-				const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
-				if (h0 && d0 < kBinCap)
-				{
-					rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
-					idx[d0] = ROUTED ? s_ids[ta] : static_cast<uint16_t>(ta);
-				}
-				if (h1 && d1 < kBinCap)
-				{
-					rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
-					idx[d1] = ROUTED ? s_ids[tb] : static_cast<uint16_t>(tb);
-				}
+				const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+				if (h0)
+					list[cnt + __popc(m0 & lt)] = static_cast<uint16_t>(g * 64 + lane);
+				if (h1)
+					list[cnt + __popc(m0) + __popc(m1 & lt)] = static_cast<uint16_t>(g * 64 + 32 + lane);
 				cnt += __popc(m0) + __popc(m1);
 			}
+			if (lane == 0)
+				s_cnt[s] = cnt;
+			tests += ROUTED ? valid : kTileLights;
 		}
-		if (lane == 0)
-			p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = cnt;
-		tests += ns;
+		__syncthreads();
+
+		// ---- phase B: every live group against its super-group's survivors ----
+		const float* tile_f = reinterpret_cast<const float*>(tile);
+		for (uint32_t cb = warp; cb < p.ncb; cb += kBinWarps)
+		{
+			// the warp's groups are cb = warp + 8 i: lane i holds the box of group i of the current batch of 32 (one load per lane
+			// instead of a dependent global load per group -- that chain was the latency of this phase -- and no shared memory, which
+			// would cost the third CTA per SM); loaded once per CTA unless the warp has more than 32 groups
+			const uint32_t gi = (cb - warp) / kBinWarps;
+			if ((gi & 31u) == 0u && (m == 0u || p.ncb > kBinWarps * 32u))
+			{
+				const uint32_t mine = cb + kBinWarps * lane;
+				if (mine < p.ncb)
+				{
+					const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(mine) * 8);
+					gb_lo = __ldcg(u), gb_hi = __ldcg(u + 1);
+				}
+			}
+			const float lo[3] = {__shfl_sync(0xffffffffu, gb_lo.x, gi & 31u), __shfl_sync(0xffffffffu, gb_lo.y, gi & 31u), __shfl_sync(0xffffffffu, gb_lo.z, gi & 31u)};
+			const float hi[3] = {__shfl_sync(0xffffffffu, gb_hi.x, gi & 31u), __shfl_sync(0xffffffffu, gb_hi.y, gi & 31u), __shfl_sync(0xffffffffu, gb_hi.z, gi & 31u)};
+			if (((s_galive[cb >> 5] >> (cb & 31u)) & 1u) == 0u)
+				continue; // dead: its slot count was zeroed above
+			const uint32_t s = cb / p.sg;
+			const uint32_t ns = s_cnt[s];
+			if (ns == 0u)
+				continue;
+			const uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
+			const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+			float4* const rec = p.bin_rec + slot;
+			uint16_t* const idx = p.bin_idx + slot;
+			uint32_t cnt = s_gcnt[cb];
+			const uint32_t cnt_in = cnt;
+			// two list entries per lane per trip (i0 + lane, then i0 + 32 + lane: ascending), tested as a pair on FADD2/FMUL2 like the
+			// tile pairs of phase A; a missing entry is the never-hit record (r2 = -1)
+			for (uint32_t i0 = 0; i0 < ns; i0 += 64)
+			{
+				const uint32_t ia = i0 + lane, ib = ia + 32;
+				uint32_t ta = 0, tb = 0;
+				float4 pa = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = make_float4(0.0f, 0.0f, -1.0f, -1.0f); // (x0,x1,y0,y1), (z0,z1,r0,r1)
+				if (ia < ns)
+				{
+					ta = list[ia];
+					if constexpr (ROUTED)
+					{
+						const float4 r = tile[ta];
+						pa.x = r.x, pa.z = r.y, pb.x = r.z, pb.z = r.w;
+					}
+					else
+					{
+						// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
+						const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
+						pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+					}
+				}
+				if (ib < ns)
+				{
+					tb = list[ib];
+					if constexpr (ROUTED)
+					{
+						const float4 r = tile[tb];
+						pa.y = r.x, pa.w = r.y, pb.y = r.z, pb.w = r.w;
+					}
+					else
+					{
+						const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
+						pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
+					}
+				}
+				bool h0, h1;
+				sphere_box_hit2(pa, pb, lo, hi, h0, h1);
+				const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+				if ((m0 | m1) != 0)
+				{
+					const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+					if (h0 && d0 < slot_cap)
+					{
+						rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
+						idx[d0] = ROUTED ? s_ids[ta] : static_cast<uint16_t>((m << 10) | ta);
+					}
+					if (h1 && d1 < slot_cap)
+					{
+						rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
+						idx[d1] = ROUTED ? s_ids[tb] : static_cast<uint16_t>((m << 10) | tb);
+					}
+					cnt += __popc(m0) + __popc(m1);
+				}
+			}
+			if (lane == 0 && cnt != cnt_in)
+				s_gcnt[cb] = cnt;
+			tests += ns;
+		}
+		__syncthreads(); // the lists and (two tiles on) the tile buffer are free again; the running counts are in place
 	}
+	for (uint32_t cb = threadIdx.x; cb < p.ncb; cb += blockDim.x)
+		if ((s_galive[cb >> 5] >> (cb & 31u)) & 1u)
+			p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = s_gcnt[cb];
 	if (lane == 0 && tests)
 	{
 		atomicAdd(&p.stats->prefilter_tests, tests);
 		atomicAdd(&p.stats->bin_tests, tests);
 	}
+}
+
+cudaError_t launch_hier_alive(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, const uint32_t* cum, uint32_t K, uint32_t ncb,
+	uint32_t cap, uint32_t* group_alive, float* alive_union, cudaStream_t stream)
+{
+	if (ncb == 0)
+		return cudaSuccess;
+	cudaLaunchConfig_t cfg{};
+	cfg.gridDim = dim3(ncb, 1, 1);
+	cfg.blockDim = dim3(256, 1, 1);
+	cfg.stream = stream;
+	cudaLaunchAttribute attr{};
+	attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr.val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = &attr;
+	cfg.numAttrs = 1;
+	return cudaLaunchKernelEx(&cfg, hier_alive_kernel, lane_cluster, aabbs, cluster_begin, cum, K, cap, group_alive, alive_union);
 }
 
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
@@ -1113,16 +1325,24 @@ cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32
 	return cudaGetLastError();
 }
 
-size_t hier_bin2_smem_bytes(uint32_t ns, bool routed)
+size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro)
 {
-	return kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) + static_cast<size_t>((ns + 3u) & ~3u) * sizeof(uint32_t) +
+	return static_cast<size_t>(macro > 1 ? 2 : 1) * kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) +
+		static_cast<size_t>((ns + 3u) & ~3u) * sizeof(uint32_t) + static_cast<size_t>((ncb + 3u) & ~3u) * sizeof(uint32_t) +
+		static_cast<size_t>(((ncb + 31u) / 32u + 3u) & ~3u) * sizeof(uint32_t) + static_cast<size_t>(ns) * 32u +
 		(routed ? kTileLights * sizeof(uint16_t) : 0);
 }
 
-static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStream_t stream)
+static cudaError_t launch_hier_bin2(const BinParams& p0, uint32_t tiles, cudaStream_t stream)
 {
+	BinParams p = p0;
 	const bool routed = p.in_mask != nullptr;
-	const size_t smem = hier_bin2_smem_bytes(p.ns, routed);
+	if (p.macro == 0 || routed)
+		p.macro = 1;
+	if (p.macro > 64 || (p.macro & (p.macro - 1u)))
+		return cudaErrorInvalidValue; // a record's 16-bit index holds 6 + 10 bits
+	p.tile_end = p.tile_begin + tiles;
+	const size_t smem = hier_bin2_smem_bytes(p.ns, p.ncb, routed, p.macro);
 	static size_t configured[2] = {0, 0};
 	if (smem > configured[routed])
 	{
@@ -1133,7 +1353,7 @@ static cudaError_t launch_hier_bin2(const BinParams& p, uint32_t tiles, cudaStre
 		configured[routed] = smem;
 	}
 	cudaLaunchConfig_t cfg{};
-	cfg.gridDim = dim3(tiles, 1, 1);
+	cfg.gridDim = dim3((tiles + p.macro - 1u) / p.macro, 1, 1);
 	cfg.blockDim = dim3(kBinWarps * 32, 1, 1);
 	cfg.dynamicSmemBytes = smem;
 	cfg.stream = stream;
@@ -1159,7 +1379,7 @@ cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t str
 	return cudaLaunchKernelEx(&cfg, hier_bin_kernel, p);
 }
 
-template <int K, bool WRITE, bool LISTS, bool PIPE, bool SUB, bool INBOX = false>
+template <int K, bool WRITE, bool PIPE, bool SUB, bool INBOX = false>
 static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 {
 	cudaLaunchConfig_t cfg{};
@@ -1169,62 +1389,58 @@ static cudaError_t launch_hier2_t(const HierParams& p, cudaStream_t stream)
 	cudaLaunchAttribute attr = pdl_attr();
 	cfg.attrs = &attr;
 	cfg.numAttrs = 1;
-	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, LISTS, PIPE, SUB, INBOX>, p);
+	return cudaLaunchKernelEx(&cfg, hier2_kernel<K, WRITE, PIPE, SUB, INBOX>, p);
 }
 
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream)
 {
 	if (p.ncb == 0 || p.seg_end <= p.seg_begin)
 		return cudaSuccess;
-	const bool lists = !write && p.seg_lists != nullptr;
 	const bool sub = p.parts > 1;
-	if (sub && (lists || p.pipe != 0))
+	if (sub && p.pipe != 0)
 		return cudaErrorInvalidValue; // the host keeps sub-tile segments to the plain walk
-	const bool pipe = p.pipe != 0 && !lists;
-	if (p.tile_ids) // routed frame: whole-tile segments, write pass
+	const bool pipe = p.pipe != 0;
+	if (p.tile_ids) // routed frame: whole-tile segments
 	{
-		if (sub || lists)
+		if (sub)
 			return cudaErrorInvalidValue;
 		switch (K * 4 + (write ? 1 : 0) + (pipe ? 2 : 0))
 		{
-		case 4: return launch_hier2_t<1, false, false, false, false, true>(p, stream);
-		case 5: return launch_hier2_t<1, true, false, false, false, true>(p, stream);
-		case 6: return launch_hier2_t<1, false, false, true, false, true>(p, stream);
-		case 7: return launch_hier2_t<1, true, false, true, false, true>(p, stream);
-		case 8: return launch_hier2_t<2, false, false, false, false, true>(p, stream);
-		case 9: return launch_hier2_t<2, true, false, false, false, true>(p, stream);
-		case 10: return launch_hier2_t<2, false, false, true, false, true>(p, stream);
-		case 11: return launch_hier2_t<2, true, false, true, false, true>(p, stream);
-		case 16: return launch_hier2_t<4, false, false, false, false, true>(p, stream);
-		case 17: return launch_hier2_t<4, true, false, false, false, true>(p, stream);
-		case 18: return launch_hier2_t<4, false, false, true, false, true>(p, stream);
-		case 19: return launch_hier2_t<4, true, false, true, false, true>(p, stream);
+		case 4: return launch_hier2_t<1, false, false, false, true>(p, stream);
+		case 5: return launch_hier2_t<1, true, false, false, true>(p, stream);
+		case 6: return launch_hier2_t<1, false, true, false, true>(p, stream);
+		case 7: return launch_hier2_t<1, true, true, false, true>(p, stream);
+		case 8: return launch_hier2_t<2, false, false, false, true>(p, stream);
+		case 9: return launch_hier2_t<2, true, false, false, true>(p, stream);
+		case 10: return launch_hier2_t<2, false, true, false, true>(p, stream);
+		case 11: return launch_hier2_t<2, true, true, false, true>(p, stream);
+		case 16: return launch_hier2_t<4, false, false, false, true>(p, stream);
+		case 17: return launch_hier2_t<4, true, false, false, true>(p, stream);
+		case 18: return launch_hier2_t<4, false, true, false, true>(p, stream);
+		case 19: return launch_hier2_t<4, true, true, false, true>(p, stream);
 		default: return cudaErrorInvalidValue;
 		}
 	}
-	switch (K * 16 + (write ? 1 : 0) + (lists ? 2 : 0) + (pipe ? 4 : 0) + (sub ? 8 : 0))
+	switch (K * 8 + (write ? 1 : 0) + (pipe ? 2 : 0) + (sub ? 4 : 0))
 	{
-	case 16: return launch_hier2_t<1, false, false, false, false>(p, stream);
-	case 20: return launch_hier2_t<1, false, false, true, false>(p, stream);
-	case 24: return launch_hier2_t<1, false, false, false, true>(p, stream);
-	case 17: return launch_hier2_t<1, true, false, false, false>(p, stream);
-	case 21: return launch_hier2_t<1, true, false, true, false>(p, stream);
-	case 25: return launch_hier2_t<1, true, false, false, true>(p, stream);
-	case 18: return launch_hier2_t<1, false, true, false, false>(p, stream);
-	case 32: return launch_hier2_t<2, false, false, false, false>(p, stream);
-	case 36: return launch_hier2_t<2, false, false, true, false>(p, stream);
-	case 40: return launch_hier2_t<2, false, false, false, true>(p, stream);
-	case 33: return launch_hier2_t<2, true, false, false, false>(p, stream);
-	case 37: return launch_hier2_t<2, true, false, true, false>(p, stream);
-	case 41: return launch_hier2_t<2, true, false, false, true>(p, stream);
-	case 34: return launch_hier2_t<2, false, true, false, false>(p, stream);
-	case 64: return launch_hier2_t<4, false, false, false, false>(p, stream);
-	case 68: return launch_hier2_t<4, false, false, true, false>(p, stream);
-	case 72: return launch_hier2_t<4, false, false, false, true>(p, stream);
-	case 65: return launch_hier2_t<4, true, false, false, false>(p, stream);
-	case 69: return launch_hier2_t<4, true, false, true, false>(p, stream);
-	case 73: return launch_hier2_t<4, true, false, false, true>(p, stream);
-	case 66: return launch_hier2_t<4, false, true, false, false>(p, stream);
+	case 8: return launch_hier2_t<1, false, false, false>(p, stream);
+	case 9: return launch_hier2_t<1, true, false, false>(p, stream);
+	case 10: return launch_hier2_t<1, false, true, false>(p, stream);
+	case 11: return launch_hier2_t<1, true, true, false>(p, stream);
+	case 12: return launch_hier2_t<1, false, false, true>(p, stream);
+	case 13: return launch_hier2_t<1, true, false, true>(p, stream);
+	case 16: return launch_hier2_t<2, false, false, false>(p, stream);
+	case 17: return launch_hier2_t<2, true, false, false>(p, stream);
+	case 18: return launch_hier2_t<2, false, true, false>(p, stream);
+	case 19: return launch_hier2_t<2, true, true, false>(p, stream);
+	case 20: return launch_hier2_t<2, false, false, true>(p, stream);
+	case 21: return launch_hier2_t<2, true, false, true>(p, stream);
+	case 32: return launch_hier2_t<4, false, false, false>(p, stream);
+	case 33: return launch_hier2_t<4, true, false, false>(p, stream);
+	case 34: return launch_hier2_t<4, false, true, false>(p, stream);
+	case 35: return launch_hier2_t<4, true, true, false>(p, stream);
+	case 36: return launch_hier2_t<4, false, false, true>(p, stream);
+	case 37: return launch_hier2_t<4, true, false, true>(p, stream);
 	default: return cudaErrorInvalidValue;
 	}
 }
@@ -1235,44 +1451,42 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 cudaError_t preload_bin_kernels()
 {
 	HVCF_PRELOAD(hier_unions_kernel);
+	HVCF_PRELOAD(hier_alive_kernel);
 	HVCF_PRELOAD(hier_super_unions_kernel);
 	HVCF_PRELOAD(hier_bin_kernel);
 	HVCF_PRELOAD(hier_bin2_kernel<false>);
 	HVCF_PRELOAD(hier_bin2_kernel<true>);
 	HVCF_PRELOAD(hier_xbin_kernel);
-	HVCF_PRELOAD((hier2_kernel<1, false, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, false, true>));
 	HVCF_PRELOAD((hier2_kernel<1, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, false, true>));
 	HVCF_PRELOAD((hier2_kernel<1, true, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, false, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<1, true, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, false, true>));
 	HVCF_PRELOAD((hier2_kernel<2, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, false, true>));
 	HVCF_PRELOAD((hier2_kernel<2, true, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, false, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<2, true, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, false, true>));
 	HVCF_PRELOAD((hier2_kernel<4, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, false, false>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, true, false>));
+	HVCF_PRELOAD((hier2_kernel<4, true, false, true>));
 	HVCF_PRELOAD((hier2_kernel<4, true, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, false, true, false, false>));
-	HVCF_PRELOAD((hier2_kernel<1, false, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, false, false, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<1, true, false, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, false, false, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<2, true, false, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, false, false, true, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, false, false, true>));
-	HVCF_PRELOAD((hier2_kernel<4, true, false, true, false, true>));
+	HVCF_PRELOAD((hier2_kernel<4, true, true, false, true>));
 	return cudaSuccess;
 }
 

@@ -34,7 +34,7 @@ struct NvtxZone
 struct hvcf_ctx;
 // pieces of the frame shared by hvcf_api.cu (hvcf_cull*) and hvcf_shard_api.cu (hvcf_cull_routed)
 extern "C" {
-int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed);
+int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed, bool allow_rounds);
 int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s);
 void hvcf_shard_free(hvcf_ctx* ctx);
 cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s);
@@ -93,7 +93,6 @@ struct hvcf_ctx
 	uint32_t frame_count = 0;
 	uint32_t num_lights = 0;
 	const hvcf_light_data* bound_lights = nullptr; // hvcf_bind_lights: external buffer, not owned
-	int variant = 1;
 	uint32_t max_segs = 1;
 	uint32_t count_blocks = 0;
 	// hierarchical mode
@@ -107,14 +106,29 @@ struct hvcf_ctx
 	int h_tps_override = 0;
 	uint32_t h_split_head = 0;
 	uint32_t h_tiles_total = 0, h_tiles_per_seg = 0, h_num_segs = 0; // of the frame between cull_begin and cull_finish
+	// rounds (hier_alive_kernel, hvcf_bin.cu): a frame of many tiles is binned and counted in a few rounds of growing length, each
+	// knowing exactly which cluster groups the earlier rounds have filled.  h_num_rounds <= 1: one launch over all segments.
+	struct Round
+	{
+		uint32_t seg_begin, seg_end, tile_begin, tile_end, tiles_per_seg, pipe, macro_shift;
+	};
+	Round h_rounds[kHMaxChunks]{};
+	uint32_t h_num_rounds = 0;
+	int rounds_mode = -1;                    // HVCF_ROUNDS: -1 = by the number of tiles, 0 = never, n > 0 = at most n rounds whenever the frame has two tiles or more
+	uint32_t rounds_min_tiles = 2048, rounds_head = 64, rounds_growth = 4; // HVCF_ROUNDS_MIN_TILES / _HEAD / _GROWTH
+	uint32_t* d_group_alive = nullptr;       // [kHMaxChunks][ncb]: per round, which groups still had a cluster below its cap when it began
+	float* d_alive_union = nullptr;          // [ncb][8] union box of each group's live clusters (rounds after the first)
+	const uint32_t* bin_alive = nullptr;     // what the next binning launch takes as BinParams::group_alive
+	uint32_t rounds_late_segs = 32;          // HVCF_ROUNDS_LATE_SEGS: light segments of every round after the first two
+	uint32_t bin_macro = 1;                  // ... and as BinParams::macro
+	int rounds_macro = -1;                   // HVCF_ROUNDS_MACRO: -1 = by the round's size, else tiles per macro tile of the rounds after the first two (power of two <= 64)
+	cudaEvent_t kev_round[8][kHMaxChunks][3]{}; // HVCF_KERNEL_TIMES with rounds: [frame][round][before, after alive + bin, after count]
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;
 	uint32_t* d_hunit_any = nullptr;         // [h_max_segs][ncb * 8]
-	uint32_t* d_hseg_lists = nullptr;        // [h_max_segs][cluster_count][cap] hits of the count pass, or NULL: write pass instead
 	uint32_t* d_hscratch = nullptr;          // cum[cluster_count][kHMaxChunks]
 	uint32_t* d_hoffsets = nullptr;
 	uint32_t* d_hlane_cluster = nullptr;
-	bool hier_v1 = false;                    // HVCF_HIER_V1=1: first-generation kernels (hvcf_hier.cu)
 	float* d_cb_union = nullptr;             // [ncb][8]
 	float* d_sb_union = nullptr;             // [bin_ns][8] super-group boxes of the two-level bin kernel
 	uint32_t bin_sg = 0, bin_ns = 0;         // groups per super-group, super-groups (0 = one-level bin kernel only)

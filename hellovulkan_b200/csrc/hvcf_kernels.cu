@@ -607,34 +607,13 @@ static cudaError_t launch_cull_t(const CullParams& p, uint32_t num_segs, cudaStr
 	return cudaGetLastError();
 }
 
-uint32_t cull_variant_clusters_per_cta(int variant)
-{
-	switch (variant)
-	{
-	case 0: return 8 * 1;
-	case 1: return 8 * 2;
-	case 2: return 8 * 4;
-	case 3: return 8 * 1;
-	case 4: return 8 * 2;
-	case 5: return 8 * 4;
-	default: return 0;
-	}
-}
-
-cudaError_t launch_cull(int variant, const CullParams& p, uint32_t num_segs, cudaStream_t stream)
+cudaError_t launch_cull(const CullParams& p, uint32_t num_segs, cudaStream_t stream)
 {
 	if (p.cluster_count == 0 || p.tiles_total == 0 || num_segs == 0)
 		return cudaSuccess;
-	switch (variant)
-	{
-	case 0: return launch_cull_t<1, true, 8>(p, num_segs, stream);
-	case 1: return launch_cull_t<2, true, 8>(p, num_segs, stream);
-	case 2: return launch_cull_t<4, true, 8>(p, num_segs, stream);
-	case 3: return launch_cull_t<1, false, 8>(p, num_segs, stream);
-	case 4: return launch_cull_t<2, false, 8>(p, num_segs, stream);
-	case 5: return launch_cull_t<4, false, 8>(p, num_segs, stream);
-	default: return cudaErrorInvalidValue;
-	}
+	// K = 2 clusters per warp on packed light pairs: the fastest of the six (K x packed / plain) shapes measured in round 1
+	// (profiles/r01b); the others are gone from the build
+	return launch_cull_t<2, true, 8>(p, num_segs, stream);
 }
 
 cudaError_t launch_count(const uint32_t* seg_counts, uint32_t num_segs, uint32_t cluster_count, uint32_t cap,
@@ -722,12 +701,7 @@ cudaError_t preload_basic_kernels()
 	HVCF_PRELOAD(aabb_generate_kernel);
 	HVCF_PRELOAD(light_transform_kernel<false>);
 	HVCF_PRELOAD(light_transform_kernel<true>);
-	HVCF_PRELOAD((cull_kernel<1, true, 8>));
 	HVCF_PRELOAD((cull_kernel<2, true, 8>));
-	HVCF_PRELOAD((cull_kernel<4, true, 8>));
-	HVCF_PRELOAD((cull_kernel<1, false, 8>));
-	HVCF_PRELOAD((cull_kernel<2, false, 8>));
-	HVCF_PRELOAD((cull_kernel<4, false, 8>));
 	HVCF_PRELOAD(count_kernel);
 	HVCF_PRELOAD(scan_kernel);
 	HVCF_PRELOAD(scatter_kernel);

@@ -64,9 +64,8 @@ cudaError_t launch_capture_base_y(const hvcf_light_data* lights, uint32_t num_li
 cudaError_t launch_scatter_positions(hvcf_light_data* lights, uint32_t num_lights, const uint32_t* indices, const float* xyz,
 	uint32_t count, float* base_y, cudaStream_t stream);
 // variant: 0..2 = packed FP32x2 with 1/2/4 clusters per warp, 3..5 = scalar FP32 with 1/2/4
-constexpr int kNumCullVariants = 6;
-uint32_t cull_variant_clusters_per_cta(int variant);
-cudaError_t launch_cull(int variant, const CullParams& p, uint32_t num_segs, cudaStream_t stream);
+constexpr uint32_t kCullClustersPerCta = 16; // cull_kernel<2, true, 8>: 8 warps x 2 clusters
+cudaError_t launch_cull(const CullParams& p, uint32_t num_segs, cudaStream_t stream);
 cudaError_t launch_count(const uint32_t* seg_counts, uint32_t num_segs, uint32_t cluster_count, uint32_t cap,
 	uint32_t* counts, uint32_t* block_sums, DeviceStats* stats, cudaStream_t stream);
 cudaError_t launch_scan(const uint32_t* block_sums, uint32_t num_blocks, uint32_t* block_offsets,
@@ -84,6 +83,7 @@ struct HierPlan
 	uint32_t nblocks;
 	uint32_t K;               // blocks per warp (1, 2 or 4)
 	uint32_t ncb;             // CTAs per light segment
+	uint32_t brick = 1;       // wide grids: blocks ordered brick by brick inside a slice (hier_build_lane_map); 0 = plain x-then-y order
 };
 
 constexpr uint32_t kHMaxParts = 8;   // most sub-tile light segments per tile
@@ -97,8 +97,12 @@ struct HierParams
 	uint32_t cluster_begin;        // shard, global cluster ids
 	uint32_t cluster_count;
 	uint32_t ncb;
-	uint32_t tiles_total, tiles_per_seg, num_segs;
+	uint32_t tiles_total, tiles_per_seg, num_segs; // tiles_total: one past the last tile of this launch's segments
 	uint32_t seg_begin, seg_end;   // segments of this launch
+	uint32_t tile_begin = 0;       // first tile of segment seg_begin: segment s covers tiles tile_begin + (s - seg_begin) * tiles_per_seg ...
+	uint32_t macro_shift = 0;      // log2 of the tiles per macro tile of this launch's slots (pipelined walk only)
+	const uint32_t* round_alive = nullptr; // [ncb] rounds after the first: 0 = the group was full before this launch's round; its warp programs leave at once and write nothing
+	uint32_t round_chunk = 0xffffffffu; // frames cut into rounds: the early-exit chunk of this launch = its round; all ones = hier_chunk_of(segment)
 	uint32_t cap;
 	uint32_t* seg_counts;          // [num_segs][cluster_count]   pass 1 out, pass 2 in
 	uint32_t* seg_prefix;          // [num_segs][cluster_count]   finalize out, pass 2 in
@@ -117,7 +121,6 @@ struct HierParams
 	const float4* bin_rec;         // [ncb][tiles_cap][kBinCap] {x, y, z, r*r} in light order
 	const uint16_t* bin_idx;       // [ncb][tiles_cap][kBinCap] light index inside the tile
 	uint32_t tiles_cap;
-	uint32_t* seg_lists;           // [num_segs][cluster_count][cap] hits of the count pass in light order, or NULL (write pass instead)
 	uint32_t* unit_any;            // [num_segs][ncb * 8] count pass: did this warp program count any hit?  The write pass leaves at once if not
 	// routed frames (hvcf_shard.cu): the tiles are this rank's INBOX -- plain {x, y, z, r*r} records that the light owners
 	// compacted block by block -- instead of the packed view cache of all lights.  A light's index is then
@@ -143,6 +146,9 @@ struct BinParams
 	uint16_t* bin_idx;
 	DeviceStats* stats;
 	uint32_t tile_begin;           // first tile of this launch (grid.y counts from it)
+	uint32_t tile_end = 0;         // set by the launcher: one past the last tile of this launch
+	uint32_t macro = 1;            // two-level kernel: tiles per macro tile (power of two <= 64; hvcf_bin.cu), 1 = every tile has its own slots
+	const uint32_t* group_alive = nullptr; // [ncb] or NULL: 0 = every cluster of the group already holds its cap (rounds, hier_alive_kernel): its slots stay empty
 	// two-level variant (hier_bin2_kernel): ns > 0 selects it
 	const float* sb_union;         // [ns][8] union boxes of the super-groups
 	uint32_t sg;                   // groups per super-group
@@ -167,24 +173,14 @@ struct FinalizeParams
 	uint32_t* offsets;
 	uint32_t* shard_total;
 	DeviceStats* stats;
-	uint32_t skip_prefix;           // 1 = seg_prefix is not needed (hier_copy_kernel recomputes the prefixes)
+	// rounds: the warp programs of a group that was full before a round write nothing, so a cluster's counts are read only up to
+	// the round before which it held its cap (cum[cluster][round] = its hits of that round, exact once the count passes are done)
+	const uint32_t* cum = nullptr;            // [cluster_count][kHMaxChunks]
+	uint32_t num_rounds = 0;                  // < 2: every (segment, cluster) count is valid
+	uint32_t round_seg_begin[kHMaxChunks + 1]{};
 };
 
 // concatenates the (segment, cluster) hit lists of the count pass into the light-index buffer and writes the light cells
-struct CopyParams
-{
-	const uint32_t* seg_counts;    // [num_segs][cluster_count]
-	const uint32_t* seg_lists;     // [num_segs][cluster_count][cap]
-	uint32_t num_segs, cluster_count, cluster_begin, cap;
-	const uint32_t* counts;        // [cluster_count] capped
-	const uint32_t* offsets;       // [cluster_count] shard-local exclusive offsets
-	const uint32_t* index_base;    // device scalar or NULL
-	const uint32_t* shard_total;
-	hvcf_light_cell* cells;        // whole grid
-	uint32_t* indices;
-	uint32_t* frame_total;
-};
-cudaError_t launch_hier_copy(const CopyParams& p, cudaStream_t stream);
 
 void hier_plan_grid(uint32_t X, uint32_t Y, uint32_t Zs, int k_override, const uint32_t shape_override[3], uint32_t max_lights, HierPlan* out);
 // cluster_lo / cluster_hi: the shard's clusters inside the X x Y x Zs box (box-local indices); clusters outside are masked, blocks
@@ -193,11 +189,13 @@ void hier_build_lane_map(HierPlan* h, uint32_t X, uint32_t Y, uint32_t Zs, uint3
 void hier_plan_lights(const HierPlan& h, uint32_t tiles_total, uint32_t max_segs, int tps_override, uint32_t* tiles_per_seg,
 	uint32_t* num_segs);
 uint32_t hier_num_chunks(uint32_t num_segs);
-cudaError_t launch_hier(int K, bool write, const HierParams& p, cudaStream_t stream);
 cudaError_t launch_hier_finalize(const FinalizeParams& p, cudaStream_t stream);
 cudaError_t launch_hier_unions(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, uint32_t K, uint32_t ncb,
 	float* cb_union, cudaStream_t stream);
 cudaError_t launch_hier_bin(const BinParams& p, uint32_t tiles, cudaStream_t stream);
+// rounds: which cluster groups still have a cluster below its cap after the rounds counted so far (cum is exact between launches)
+cudaError_t launch_hier_alive(const uint32_t* lane_cluster, const hvcf_aabb* aabbs, uint32_t cluster_begin, const uint32_t* cum, uint32_t K, uint32_t ncb,
+	uint32_t cap, uint32_t* group_alive, float* alive_union, cudaStream_t stream);
 // transform + one-level binning fused (hier_xbin_kernel): the first kernel of a frame with few lights
 struct XBinParams
 {
@@ -211,7 +209,7 @@ struct XBinParams
 };
 cudaError_t launch_hier_xbin(const XBinParams& q, uint32_t tiles, cudaStream_t stream);
 cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream);
-size_t hier_bin2_smem_bytes(uint32_t ns, bool routed = false);
+size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
 // ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------

@@ -186,7 +186,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			return rc;
 	}
 	NvtxZone zone("Light_Culling");
-	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true);
+	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true, false);
 	if (rc != HVCF_OK)
 		return rc;
 	cudaStream_t s = static_cast<cudaStream_t>(stream);

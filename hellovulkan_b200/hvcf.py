@@ -90,7 +90,7 @@ EXPORTS = [
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
     "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
     "hvcf_peer_status", "hvcf_create_sharded", "hvcf_shard_light_range", "hvcf_set_lights_range", "hvcf_cull_routed",
-    "hvcf_shard_inbox_records", "hvcf_download_shard", "hvcf_debug_route_ms",
+    "hvcf_shard_inbox_records", "hvcf_download_shard", "hvcf_debug_route_ms", "hvcf_debug_rounds",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -121,6 +121,7 @@ def load():
     lib.hvcf_cull_routed.argtypes = [vp, u32, vp]
     lib.hvcf_download_shard.argtypes = [vp, vp, ctypes.c_size_t, vp, ctypes.c_size_t, ctypes.POINTER(u32), ctypes.POINTER(u32), vp]
     lib.hvcf_debug_route_ms.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float)]
+    lib.hvcf_debug_rounds.argtypes = [vp, ctypes.POINTER(ctypes.c_uint32), u32, vp, ctypes.c_size_t]
     lib.hvcf_shard_inbox_records.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_uint64)]
     lib.hvcf_set_lights.argtypes = [vp, vp, u32, i32, vp]
     lib.hvcf_update_light.argtypes = [vp, u32, ctypes.POINTER(ctypes.c_float), vp]
@@ -626,6 +627,29 @@ class Context:
         _check(self.lib.hvcf_debug_trace(self.handle, _ptr(buf), buf.size, ctypes.byref(n)))
         n = n.value
         return buf[: 4 * n].reshape(n, 4).copy(), buf[4 * n: 8 * n].reshape(n, 4).copy()
+
+    def rounds_plan(self):
+        """(ncb, K, tiles_cap, [round dicts]) of the last hierarchical frame (hvcf_debug_rounds)."""
+        plan = (ctypes.c_uint32 * 68)()
+        _check(self.lib.hvcf_debug_rounds(self.handle, plan, 0, None, 0))
+        keys = ("seg_begin", "seg_end", "tile_begin", "tile_end", "tiles_per_seg", "pipe", "macro_shift")
+        return plan[0], plan[1], plan[2], [dict(zip(keys, plan[4 + 8 * r: 4 + 8 * r + 7])) for r in range(plan[3])]
+
+    def rounds_state(self, what):
+        """what = 'alive' -> uint32[rounds][ncb], 'bin_count' -> uint32[ncb][tiles_cap], 'alive_union' -> float32[ncb][8]."""
+        ncb, _, tiles_cap, rounds = self.rounds_plan()
+        plan = (ctypes.c_uint32 * 68)()
+        if what == "alive":
+            out = np.zeros((max(len(rounds), 1), ncb), np.uint32)
+            code = 0
+        elif what == "bin_count":
+            out = np.zeros((ncb, tiles_cap), np.uint32)
+            code = 1
+        else:
+            out = np.zeros((ncb, 8), np.float32)
+            code = 2
+        _check(self.lib.hvcf_debug_rounds(self.handle, plan, code, _ptr(out), out.nbytes))
+        return out
 
     def kernel_times(self, frame=0):
         """ms of (transform, bin, count, finalize, write) of the last hierarchical cull; needs HVCF_KERNEL_TIMES=1."""

@@ -315,6 +315,12 @@ HVCF_API int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms
 /* debug: milliseconds of the route kernel alone in the last hvcf_cull_routed on `frame` (out_ms[0] of hvcf_debug_kernel_times is
  * route + the wait for the other ranks' shares); needs HVCF_KERNEL_TIMES=1 at hvcf_create. */
 HVCF_API int hvcf_debug_route_ms(hvcf_ctx* ctx, uint32_t frame, float* out_route_ms);
+/* debug: the rounds plan of the last hierarchical frame and the level-0 state it left behind.
+ *   plan[0..3] = groups (ncb), blocks per warp program (K), slot rows per group (tiles_cap), rounds (0 or 1 = a single launch);
+ *   plan[4 + 8 r ..] = round r: seg_begin, seg_end, tile_begin, tile_end, tiles_per_seg, pipe, log2(tiles per macro tile), 0
+ *   what = 0: uint32 alive[rounds][ncb] (row 0 is not used);  1: uint32 bin_count[ncb][tiles_cap];  2: float alive_union[ncb][8]
+ * Synchronises the device.  plan holds 4 + 8 * 8 words; dst may be NULL to fetch the plan only. */
+HVCF_API int hvcf_debug_rounds(hvcf_ctx* ctx, uint32_t plan[68], uint32_t what, void* dst, size_t bytes);
 HVCF_API int hvcf_set_timing(hvcf_ctx* ctx, int enabled);
 HVCF_API int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms);
 /* Measured FP32 issue rate of the device (independent FADD/FMUL chains, no FMA), in lane-operations per

@@ -101,10 +101,8 @@ def test_cull_matches_golden_reference_lists(hv, oracle, golden, mode):
     assert np.array_equal(idx, arrs["cull_A_1000_gathered"])
 
 
-@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "4", "5"])
 @pytest.mark.parametrize("segs", ["1", "3", "0"])
-def test_cull_variants_agree(hv, oracle, variant, segs, monkeypatch):
-    monkeypatch.setenv("HVCF_CULL_VARIANT", variant)
+def test_brute_force_segment_counts_agree(hv, oracle, segs, monkeypatch):
     monkeypatch.setenv("HVCF_SEGMENTS", segs)
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen, pos=(4, 3, -5), target=(-1, 0.5, 2))
@@ -383,25 +381,36 @@ def test_stats_are_split_per_kernel(hv, oracle):
 
 
 @pytest.mark.parametrize("name,n,cap,z", [("A", 70_000, 150, None), ("A", 3_000, 4, None), ("B", 300_000, 150, None), ("C", 150_000, 150, (40, 52)),
-                                         ("B", 0, 150, None), ("A", 65_536, 1, None)])
-def test_copy_pass_and_write_pass_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap, z):
-    """output stage of the hierarchical mode: a second walk of the hierarchy (write pass, the default) or hit lists kept by the
-    count pass + hier_copy_kernel (HVCF_SEG_LISTS=1; measured slower, kept as an option): same bytes, equal to brute force"""
+                                         ("B", 0, 150, None), ("A", 65_536, 1, None), ("A", 1_025, 150, None), ("B", 40_000, 7, None)])
+@pytest.mark.parametrize("plan", ["8:1:2", "2:3:2", "3:16:4", "8:64:4", "8:1:2:2", "4:2:2:64", "3:1:4:8"])
+def test_rounds_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap, z, plan):
+    """Frames of many tiles are binned and counted in rounds; between rounds hier_alive_kernel marks the cluster groups whose clusters
+    all hold their cap already, and the next round's binning skips them.  Forced here on small frames with several round plans
+    (rounds : head tiles : growth [: tiles per macro tile of the rounds after the first two, with the two-level binning kernel]):
+    the bytes equal the single-launch frame's and brute force's, and no round does more level-0 work."""
     grid, screen = GRIDS[name]
     ubo = oracle.camera_ubo(grid, screen)
     lights = oracle.init_lights(n, seed=17)
     kw = {} if z is None else {"z_begin": z[0], "z_end": z[1]}
-    out = {}
-    for lists in ("0", "1"):
-        monkeypatch.setenv("HVCF_SEG_LISTS", lists)
-        out[lists] = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"], **kw)
-    monkeypatch.delenv("HVCF_SEG_LISTS")
+    monkeypatch.setenv("HVCF_ROUNDS", "0")
+    monkeypatch.setenv("HVCF_HIER_PARTS", "1")
+    one = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"], **kw)
+    rounds, head, growth, macro = (plan.split(":") + [None])[:4]
+    if macro:
+        monkeypatch.setenv("HVCF_ROUNDS_MACRO", macro)
+        monkeypatch.setenv("HVCF_BIN2", "1")
+    monkeypatch.setenv("HVCF_ROUNDS", rounds)
+    monkeypatch.setenv("HVCF_ROUNDS_HEAD", head)
+    monkeypatch.setenv("HVCF_ROUNDS_GROWTH", growth)
+    got = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["hier"], **kw)
     ref = run_cull(hv, grid, ubo, lights, cap=cap, mode=MODES["brute"], **kw)
-    for lists in ("0", "1"):
-        assert out[lists][2] == ref[2]
-        assert out[lists][0].tobytes() == ref[0].tobytes() and out[lists][1].tobytes() == ref[1].tobytes(), f"HVCF_SEG_LISTS={lists}"
-    assert out["0"][3]["write_pass_tests"] > 0 or n == 0
-    assert out["1"][3]["write_pass_tests"] == 0
+    for out in (one, got):
+        assert out[2] == ref[2]
+        assert out[0].tobytes() == ref[0].tobytes() and out[1].tobytes() == ref[1].tobytes()
+    tiles = (n + 1023) // 1024
+    if tiles >= 2 * int(head):
+        assert got[3]["kernel_launches"] > one[3]["kernel_launches"]          # the rounds really ran
+        assert macro or got[3]["bin_tests"] <= one[3]["bin_tests"]
 
 
 def test_download_grid_in_one_call(hv, oracle):
