@@ -311,9 +311,12 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->rounds_mode = env_int("HVCF_ROUNDS", -1);
 		c->rounds_min_tiles = static_cast<uint32_t>(env_int("HVCF_ROUNDS_MIN_TILES", 2048));
 		c->rounds_head = static_cast<uint32_t>(env_int("HVCF_ROUNDS_HEAD", 64));
-		c->rounds_growth = static_cast<uint32_t>(env_int("HVCF_ROUNDS_GROWTH", 4));
+		c->rounds_growth = static_cast<uint32_t>(env_int("HVCF_ROUNDS_GROWTH", 8));
 		c->rounds_macro = env_int("HVCF_ROUNDS_MACRO", -1);
 		c->rounds_late_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_LATE_SEGS", 32));
+		c->rounds_early_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_EARLY_SEGS", 16));
+		if (c->rounds_early_segs == 0)
+			c->rounds_early_segs = 1;
 		if (c->rounds_late_segs == 0)
 			c->rounds_late_segs = 1;
 		c->pipe_mode = env_int("HVCF_BATCH_PIPE", -1);
@@ -719,7 +722,7 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 				uint32_t end = static_cast<uint64_t>(t) + size < tiles_total ? t + size : tiles_total;
 				if (nr + 1 == max_rounds || tiles_total - end < size) // the last round takes the rest (no tiny tail round)
 					end = tiles_total;
-				const uint32_t target = nr < 2 ? 128u : ctx->rounds_late_segs;
+				const uint32_t target = nr < 2 ? ctx->rounds_early_segs : ctx->rounds_late_segs;
 				uint32_t tps = (end - t + target - 1) / target;
 				// macro tiles (two-level binning only, pipelined walk only): late rounds are sparse, so M consecutive tiles share one
 				// slot per group.  M by what keeps about four binning CTAs per SM, at most 64, and segments are whole macro tiles.
@@ -934,7 +937,7 @@ static cudaError_t round_mark(hvcf_ctx* ctx, uint32_t frame, uint32_t round, int
 
 // rounds: level-0 binning (against the groups that the earlier rounds left alive) + count pass, round by round, over the tiles
 // that have been transformed (or, routed frames, have arrived in the inbox) already.  bin_round(round) launches the round's binning.
-static int hier_rounds(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s, uint32_t* launches, const std::function<int(uint32_t)>& bin_round)
+int hvcf_hier_rounds(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s, uint32_t* launches, const std::function<int(uint32_t)>& bin_round)
 {
 	for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
 	{
@@ -1086,7 +1089,7 @@ int hvcf_cull_begin(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			rc = hier_range(ctx, frame, 0, n, HVCF_RANGE_TRANSFORM, s); // every light to view space (and the frame's counters cleared)
 			if (rc != HVCF_OK)
 				return rc;
-			rc = hier_rounds(ctx, frame, s, &ctx->open_launches, [&](uint32_t r) {
+			rc = hvcf_hier_rounds(ctx, frame, s, &ctx->open_launches, [&](uint32_t r) {
 				const hvcf_ctx::Round& rd = ctx->h_rounds[r];
 				const uint64_t le = static_cast<uint64_t>(rd.tile_end) * kTileLights;
 				--ctx->open_launches; // hier_range counts the launch itself

@@ -861,15 +861,20 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	extern __shared__ __align__(128) unsigned char s_dyn[];
 	const uint32_t M = ROUTED ? 1u : p.macro;
 	const uint32_t nbuf = M > 1u ? 2u : 1u;
+	const uint32_t LS = p.list_supers; // super-group survivor lists held at a time
 	unsigned char* const s_tiles = s_dyn;                                                          // nbuf x kTileBytes
-	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_dyn + nbuf * kTileBytes);               // [ns][kTileLights]
-	uint32_t* const s_cnt = reinterpret_cast<uint32_t*>(s_list + static_cast<size_t>(p.ns) * kTileLights); // [ns]
-	uint32_t* const s_gcnt = s_cnt + ((p.ns + 3u) & ~3u);                                          // [ncb] running slot counts
+	uint32_t* const s_mask = reinterpret_cast<uint32_t*>(s_dyn + nbuf * kTileBytes);               // [ns][32] survivor bits of the tile per live super-group
+	uint16_t* const s_list = reinterpret_cast<uint16_t*>(s_mask + static_cast<size_t>(p.ns) * 32); // [LS][kTileLights]
+	uint32_t* const s_cnt = reinterpret_cast<uint32_t*>(s_list + static_cast<size_t>(LS) * kTileLights); // [LS]
+	uint32_t* const s_gcnt = s_cnt + ((LS + 3u) & ~3u);                                            // [ncb] running slot counts
 	uint32_t* const s_galive = s_gcnt + ((p.ncb + 3u) & ~3u);                                      // [ceil(ncb / 32)] live-group bits
-	float4* const s_sbox = reinterpret_cast<float4*>(s_galive + (((p.ncb + 31u) / 32u + 3u) & ~3u)); // [ns][2] super-group boxes {lo, hi}
-	uint16_t* const s_ids = reinterpret_cast<uint16_t*>(s_sbox + 2u * p.ns);                       // ROUTED: [kTileLights]
+	float4* const s_sbox = reinterpret_cast<float4*>(s_galive + (((p.ncb + 31u) / 32u + 3u) & ~3u)); // [ns][2] super-group boxes {lo, hi}, live ones first
+	float4* const s_gbox = s_sbox + 2u * p.ns;                                                     // [live groups][2] group boxes, in group order
+	uint16_t* const s_glist = reinterpret_cast<uint16_t*>(s_gbox + 2u * p.ncb);                    // [live groups] group ids
+	uint16_t* const s_ids = s_glist + ((p.ncb + 7u) & ~7u);                                        // ROUTED: [kTileLights]
 	__shared__ __align__(8) uint64_t bar[2];
 	__shared__ uint32_t s_smask;
+	__shared__ uint32_t s_super[32]; // the i-th live super-group
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t tile_id = p.tile_begin + blockIdx.x * M;                 // first tile of this CTA
 	const uint32_t tM = min(M, p.tile_end - tile_id);                       // its tiles
@@ -898,8 +903,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 			return;
 		}
 	}
-	// ---- which groups are alive: bits in shared memory (the phases must not wait for a global load per group), live
-	// super-groups as a mask; dead groups get their empty slot here ----
+	// ---- which groups are alive: bits in shared memory, live super-groups as a mask; dead groups get their empty slot here ----
 	{
 		uint32_t mine = 0u;
 		for (uint32_t cb0 = 0; cb0 < p.ncb; cb0 += blockDim.x)
@@ -926,35 +930,56 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	const uint32_t smask = s_smask;
 	if (smask == 0u)
 		return;
-	// super-group boxes: the static ones, or -- rounds, where the group boxes have shrunk to their live clusters -- the union of
-	// the live groups' boxes (fminf / fmaxf ignore nothing here: the boxes hold no NaN, a NaN group is (-inf, +inf))
-	for (uint32_t sidx = threadIdx.x; sidx < p.ns * 8u; sidx += blockDim.x)
-	{
-		const uint32_t sgi = sidx >> 3, c = sidx & 7u;
-		float v;
-		if (!p.group_alive)
-			v = __ldg(p.sb_union + static_cast<size_t>(sgi) * 8 + c);
-		else
-		{
-			const bool is_hi = c >= 4;
-			v = is_hi ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
-			for (uint32_t g = sgi * p.sg; g < min(p.ncb, (sgi + 1u) * p.sg); ++g)
-				if ((s_galive[g >> 5] >> (g & 31u)) & 1u)
-				{
-					const float x = __ldcg(p.cb_union + static_cast<size_t>(g) * 8 + c);
-					v = is_hi ? fmaxf(v, x) : fminf(v, x);
-				}
-			if ((c & 3u) == 3u)
-				v = 0.0f;
-		}
-		reinterpret_cast<float*>(s_sbox + 2 * sgi)[c] = v;
-	}
-	__syncthreads();
 	const unsigned char* const src = reinterpret_cast<const unsigned char*>(p.lights_view);
 	if (threadIdx.x == 0)
 	{
 		mbar_arrive_expect_tx(&bar[0], ROUTED ? valid * 16u : kTileBytes);
 		bulk_copy_g2s(s_tiles, src + static_cast<size_t>(tile_id) * kTileBytes, ROUTED ? valid * 16u : kTileBytes, &bar[0]);
+	}
+	const uint32_t n_as = __popc(smask); // live super-groups
+	// ---- the live groups, compacted in group order, with their boxes (one global load per group and CTA: a load per group and
+	// tile inside phase B was that phase's latency chain), and the live super-groups' boxes: the static ones, or -- rounds, where
+	// the group boxes have shrunk to their live clusters -- the union of their live groups' boxes ----
+	uint32_t n_ag = 0;
+	{
+		const uint32_t words = (p.ncb + 31u) / 32u;
+		for (uint32_t w = 0; w < words; ++w)
+			n_ag += __popc(s_galive[w]);
+		for (uint32_t cb = threadIdx.x; cb < p.ncb; cb += blockDim.x)
+			if ((s_galive[cb >> 5] >> (cb & 31u)) & 1u)
+			{
+				uint32_t pos = __popc(s_galive[cb >> 5] & ((1u << (cb & 31u)) - 1u));
+				for (uint32_t w = 0; w < (cb >> 5); ++w)
+					pos += __popc(s_galive[w]);
+				const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8);
+				s_glist[pos] = static_cast<uint16_t>(cb);
+				s_gbox[2 * pos] = __ldcg(u);
+				s_gbox[2 * pos + 1] = __ldcg(u + 1);
+			}
+		if (threadIdx.x < n_as)
+			s_super[threadIdx.x] = __fns(smask, 0u, static_cast<int>(threadIdx.x) + 1);
+		for (uint32_t sidx = threadIdx.x; sidx < n_as * 8u; sidx += blockDim.x)
+		{
+			const uint32_t si = sidx >> 3, c = sidx & 7u;
+			const uint32_t sgi = __fns(smask, 0u, static_cast<int>(si) + 1);
+			float v;
+			if (!p.group_alive)
+				v = __ldg(p.sb_union + static_cast<size_t>(sgi) * 8 + c);
+			else
+			{
+				const bool is_hi = c >= 4;
+				v = is_hi ? -__int_as_float(0x7f800000) : __int_as_float(0x7f800000);
+				for (uint32_t g = sgi * p.sg; g < min(p.ncb, (sgi + 1u) * p.sg); ++g)
+					if ((s_galive[g >> 5] >> (g & 31u)) & 1u)
+					{
+						const float x = __ldcg(p.cb_union + static_cast<size_t>(g) * 8 + c);
+						v = is_hi ? fmaxf(v, x) : fminf(v, x);
+					}
+				if ((c & 3u) == 3u)
+					v = 0.0f;
+			}
+			reinterpret_cast<float*>(s_sbox + 2 * si)[c] = v;
+		}
 	}
 	if constexpr (ROUTED)
 	{
@@ -1007,12 +1032,11 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		for (uint32_t i = threadIdx.x; i < valid; i += blockDim.x)
 			p.tile_ids[static_cast<size_t>(tile_id) * kTileLights + i] = s_ids[i];
 	}
+	__syncthreads(); // the compacted groups, the boxes (and the in-block indices) are in place
 	const uint32_t lt = lanemask_lt();
 	const uint32_t ngroups = ROUTED ? (valid + 63u) / 64u : kTileGroups;
-	const uint32_t ns_alive = __popc(smask);
 	const uint32_t slot_cap = tM * kBinCap; // records of a (group, macro tile) slot
 	unsigned long long tests = 0;
-	float4 gb_lo = make_float4(0.0f, 0.0f, 0.0f, 0.0f), gb_hi = gb_lo; // phase B: the box of one of this warp's groups
 	for (uint32_t m = 0; m < tM; ++m)
 	{
 		const uint32_t buf = nbuf == 2u ? (m & 1u) : 0u;
@@ -1025,138 +1049,156 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 		mbar_wait(&bar[buf], (m >> 1) & 1u);
 		const float4* tile = reinterpret_cast<const float4*>(s_tiles + buf * kTileBytes);
 
-		// ---- phase A: super-group survivor lists ----
-		for (uint32_t si = warp; si < ns_alive; si += kBinWarps)
+		// ---- phase A1: warp w takes the 128 lights of pair rounds 2 w and 2 w + 1 against EVERY live super-group (the same
+		// work for every warp, whatever the number of live super-groups); the ballots are the tile's survivor bits per super-group ----
+#pragma unroll
+		for (uint32_t gg = 0; gg < 2; ++gg)
 		{
-			const uint32_t s = __fns(smask, 0u, static_cast<int>(si) + 1); // the si-th live super-group
-			const float4 a4 = s_sbox[2 * s], b4 = s_sbox[2 * s + 1];
-			const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
-			uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
-			uint32_t cnt = 0;
-#pragma unroll 4
-			for (uint32_t g = 0; g < ngroups; ++g)
+			const uint32_t g = warp * 2u + gg;
+			if (g >= ngroups)
 			{
-				float4 a, b;
-				bool h0, h1;
-				if constexpr (ROUTED)
-				{
-					// plain records of lights g * 64 + lane and g * 64 + 32 + lane, paired in registers into the packed operand shape
-					const float4 r0 = tile[g * 64 + lane], r1 = tile[g * 64 + 32 + lane];
-					a = make_float4(r0.x, r1.x, r0.y, r1.y);
-					b = make_float4(r0.z, r1.z, r0.w, r1.w);
-					sphere_box_hit2(a, b, lo, hi, h0, h1);
-					h0 = h0 && g * 64 + lane < valid;      // beyond the tile's records: whatever shared memory held
-					h1 = h1 && g * 64 + 32 + lane < valid;
-				}
-				else
-				{
-					a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
-					sphere_box_hit2(a, b, lo, hi, h0, h1);
-				}
-				const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
-				if (h0)
-					list[cnt + __popc(m0 & lt)] = static_cast<uint16_t>(g * 64 + lane);
-				if (h1)
-					list[cnt + __popc(m0) + __popc(m1 & lt)] = static_cast<uint16_t>(g * 64 + 32 + lane);
-				cnt += __popc(m0) + __popc(m1);
+				for (uint32_t si = lane; si < n_as; si += 32)
+					s_mask[si * 32 + 2 * g] = s_mask[si * 32 + 2 * g + 1] = 0u;
+				continue;
 			}
-			if (lane == 0)
-				s_cnt[s] = cnt;
-			tests += ROUTED ? valid : kTileLights;
+			float4 a, b;
+			bool v0 = true, v1 = true;
+			if constexpr (ROUTED)
+			{
+				// plain records of lights g * 64 + lane and g * 64 + 32 + lane, paired in registers into the packed operand shape
+				const float4 r0 = tile[g * 64 + lane], r1 = tile[g * 64 + 32 + lane];
+				a = make_float4(r0.x, r1.x, r0.y, r1.y);
+				b = make_float4(r0.z, r1.z, r0.w, r1.w);
+				v0 = g * 64 + lane < valid; // beyond the tile's records: whatever shared memory held
+				v1 = g * 64 + 32 + lane < valid;
+			}
+			else
+				a = tile[g * 64 + lane], b = tile[g * 64 + 32 + lane];
+			for (uint32_t si = 0; si < n_as; ++si)
+			{
+				const float4 a4 = s_sbox[2 * si], b4 = s_sbox[2 * si + 1];
+				const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
+				bool h0, h1;
+				sphere_box_hit2(a, b, lo, hi, h0, h1);
+				const uint32_t m0 = __ballot_sync(0xffffffffu, h0 && v0), m1 = __ballot_sync(0xffffffffu, h1 && v1);
+				if (lane == 0)
+				{
+					s_mask[si * 32 + 2 * g] = m0;
+					s_mask[si * 32 + 2 * g + 1] = m1;
+				}
+			}
+			tests += static_cast<unsigned long long>(n_as) * (ROUTED ? min(64u, valid - g * 64u) : 64u);
 		}
 		__syncthreads();
-
-		// ---- phase B: every live group against its super-group's survivors ----
 		const float* tile_f = reinterpret_cast<const float*>(tile);
-		for (uint32_t cb = warp; cb < p.ncb; cb += kBinWarps)
+		for (uint32_t c0 = 0; c0 < n_as; c0 += LS)
 		{
-			// the warp's groups are cb = warp + 8 i: lane i holds the box of group i of the current batch of 32 (one load per lane
-			// instead of a dependent global load per group -- that chain was the latency of this phase -- and no shared memory, which
-			// would cost the third CTA per SM); loaded once per CTA unless the warp has more than 32 groups
-			const uint32_t gi = (cb - warp) / kBinWarps;
-			if ((gi & 31u) == 0u && (m == 0u || p.ncb > kBinWarps * 32u))
+			// ---- phase A2: the bits of up to LS live super-groups become index lists in light order (lane = word: words 2 g and
+			// 2 g + 1 hold lights g * 64 .. g * 64 + 63) ----
+			for (uint32_t si = c0 + warp; si < min(c0 + LS, n_as); si += kBinWarps)
 			{
-				const uint32_t mine = cb + kBinWarps * lane;
-				if (mine < p.ncb)
+				uint32_t word = s_mask[si * 32 + lane];
+				const uint32_t c = __popc(word);
+				uint32_t inc = c;
+#pragma unroll
+				for (int o = 1; o < 32; o <<= 1)
 				{
-					const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(mine) * 8);
-					gb_lo = __ldcg(u), gb_hi = __ldcg(u + 1);
+					const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+					if (lane >= static_cast<uint32_t>(o))
+						inc += t;
 				}
+				uint16_t* out = s_list + static_cast<size_t>(si - c0) * kTileLights + (inc - c);
+				while (word)
+				{
+					const uint32_t bit = __ffs(word) - 1;
+					word &= word - 1;
+					*out++ = static_cast<uint16_t>(lane * 32u + bit);
+				}
+				if (lane == 31)
+					s_cnt[si - c0] = inc;
 			}
-			const float lo[3] = {__shfl_sync(0xffffffffu, gb_lo.x, gi & 31u), __shfl_sync(0xffffffffu, gb_lo.y, gi & 31u), __shfl_sync(0xffffffffu, gb_lo.z, gi & 31u)};
-			const float hi[3] = {__shfl_sync(0xffffffffu, gb_hi.x, gi & 31u), __shfl_sync(0xffffffffu, gb_hi.y, gi & 31u), __shfl_sync(0xffffffffu, gb_hi.z, gi & 31u)};
-			if (((s_galive[cb >> 5] >> (cb & 31u)) & 1u) == 0u)
-				continue; // dead: its slot count was zeroed above
-			const uint32_t s = cb / p.sg;
-			const uint32_t ns = s_cnt[s];
-			if (ns == 0u)
-				continue;
-			const uint16_t* const list = s_list + static_cast<size_t>(s) * kTileLights;
-			const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
-			float4* const rec = p.bin_rec + slot;
-			uint16_t* const idx = p.bin_idx + slot;
-			uint32_t cnt = s_gcnt[cb];
-			const uint32_t cnt_in = cnt;
-			// two list entries per lane per trip (i0 + lane, then i0 + 32 + lane: ascending), tested as a pair on FADD2/FMUL2 like the
-			// tile pairs of phase A; a missing entry is the never-hit record (r2 = -1)
-			for (uint32_t i0 = 0; i0 < ns; i0 += 64)
+			__syncthreads();
+
+			// ---- phase B: every live group of these super-groups against its super-group's survivors ----
+			for (uint32_t gi = warp; gi < n_ag; gi += kBinWarps)
 			{
-				const uint32_t ia = i0 + lane, ib = ia + 32;
-				uint32_t ta = 0, tb = 0;
-				float4 pa = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = make_float4(0.0f, 0.0f, -1.0f, -1.0f); // (x0,x1,y0,y1), (z0,z1,r0,r1)
-				if (ia < ns)
+				const uint32_t cb = s_glist[gi];
+				const uint32_t sgi = cb / p.sg;
+				const uint32_t si = __popc(smask & ((1u << sgi) - 1u));
+				if (si < c0 || si >= c0 + LS)
+					continue;
+				const uint32_t ns = s_cnt[si - c0];
+				if (ns == 0u)
+					continue;
+				const uint16_t* const list = s_list + static_cast<size_t>(si - c0) * kTileLights;
+				const float4 a4 = s_gbox[2 * gi], b4 = s_gbox[2 * gi + 1];
+				const float lo[3] = {a4.x, a4.y, a4.z}, hi[3] = {b4.x, b4.y, b4.z};
+				const size_t slot = (static_cast<size_t>(cb) * p.tiles_cap + tile_id) * kBinCap;
+				float4* const rec = p.bin_rec + slot;
+				uint16_t* const idx = p.bin_idx + slot;
+				uint32_t cnt = s_gcnt[cb];
+				const uint32_t cnt_in = cnt;
+				// two list entries per lane per trip (i0 + lane, then i0 + 32 + lane: ascending), tested as a pair on FADD2/FMUL2 like the
+				// tile pairs of phase A; a missing entry is the never-hit record (r2 = -1)
+				for (uint32_t i0 = 0; i0 < ns; i0 += 64)
 				{
-					ta = list[ia];
-					if constexpr (ROUTED)
+					const uint32_t ia = i0 + lane, ib = ia + 32;
+					uint32_t ta = 0, tb = 0;
+					float4 pa = make_float4(0.0f, 0.0f, 0.0f, 0.0f), pb = make_float4(0.0f, 0.0f, -1.0f, -1.0f); // (x0,x1,y0,y1), (z0,z1,r0,r1)
+					if (ia < ns)
 					{
-						const float4 r = tile[ta];
-						pa.x = r.x, pa.z = r.y, pb.x = r.z, pb.z = r.w;
+						ta = list[ia];
+						if constexpr (ROUTED)
+						{
+							const float4 r = tile[ta];
+							pa.x = r.x, pa.z = r.y, pb.x = r.z, pb.z = r.w;
+						}
+						else
+						{
+							// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
+							const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
+							pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+						}
 					}
-					else
+					if (ib < ns)
 					{
-						// packed culling layout: light t sits in pair (t & 31) of group t >> 6, half (t >> 5) & 1
-						const uint32_t f = (((ta >> 6) * 64 + (ta & 31)) << 2) + ((ta >> 5) & 1);
-						pa.x = tile_f[f], pa.z = tile_f[f + 2], pb.x = tile_f[f + 128], pb.z = tile_f[f + 130];
+						tb = list[ib];
+						if constexpr (ROUTED)
+						{
+							const float4 r = tile[tb];
+							pa.y = r.x, pa.w = r.y, pb.y = r.z, pb.w = r.w;
+						}
+						else
+						{
+							const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
+							pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
+						}
+					}
+					bool h0, h1;
+					sphere_box_hit2(pa, pb, lo, hi, h0, h1);
+					const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
+					if ((m0 | m1) != 0)
+					{
+						const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
+						if (h0 && d0 < slot_cap)
+						{
+							rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
+							idx[d0] = ROUTED ? s_ids[ta] : static_cast<uint16_t>((m << 10) | ta);
+						}
+						if (h1 && d1 < slot_cap)
+						{
+							rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
+							idx[d1] = ROUTED ? s_ids[tb] : static_cast<uint16_t>((m << 10) | tb);
+						}
+						cnt += __popc(m0) + __popc(m1);
 					}
 				}
-				if (ib < ns)
-				{
-					tb = list[ib];
-					if constexpr (ROUTED)
-					{
-						const float4 r = tile[tb];
-						pa.y = r.x, pa.w = r.y, pb.y = r.z, pb.w = r.w;
-					}
-					else
-					{
-						const uint32_t f = (((tb >> 6) * 64 + (tb & 31)) << 2) + ((tb >> 5) & 1);
-						pa.y = tile_f[f], pa.w = tile_f[f + 2], pb.y = tile_f[f + 128], pb.w = tile_f[f + 130];
-					}
-				}
-				bool h0, h1;
-				sphere_box_hit2(pa, pb, lo, hi, h0, h1);
-				const uint32_t m0 = __ballot_sync(0xffffffffu, h0), m1 = __ballot_sync(0xffffffffu, h1);
-				if ((m0 | m1) != 0)
-				{
-					const uint32_t d0 = cnt + __popc(m0 & lt), d1 = cnt + __popc(m0) + __popc(m1 & lt);
-					if (h0 && d0 < slot_cap)
-					{
-						rec[d0] = make_float4(pa.x, pa.z, pb.x, pb.z);
-						idx[d0] = ROUTED ? s_ids[ta] : static_cast<uint16_t>((m << 10) | ta);
-					}
-					if (h1 && d1 < slot_cap)
-					{
-						rec[d1] = make_float4(pa.y, pa.w, pb.y, pb.w);
-						idx[d1] = ROUTED ? s_ids[tb] : static_cast<uint16_t>((m << 10) | tb);
-					}
-					cnt += __popc(m0) + __popc(m1);
-				}
+				if (lane == 0 && cnt != cnt_in)
+					s_gcnt[cb] = cnt;
+				tests += ns;
 			}
-			if (lane == 0 && cnt != cnt_in)
-				s_gcnt[cb] = cnt;
-			tests += ns;
+			__syncthreads(); // the lists (and, after the last chunk, the masks and two tiles on the tile buffer) are free again
 		}
-		__syncthreads(); // the lists and (two tiles on) the tile buffer are free again; the running counts are in place
 	}
 	for (uint32_t cb = threadIdx.x; cb < p.ncb; cb += blockDim.x)
 		if ((s_galive[cb >> 5] >> (cb & 31u)) & 1u)
@@ -1325,12 +1367,12 @@ cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32
 	return cudaGetLastError();
 }
 
-size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro)
+size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro, uint32_t list_supers)
 {
-	return static_cast<size_t>(macro > 1 ? 2 : 1) * kTileBytes + static_cast<size_t>(ns) * kTileLights * sizeof(uint16_t) +
-		static_cast<size_t>((ns + 3u) & ~3u) * sizeof(uint32_t) + static_cast<size_t>((ncb + 3u) & ~3u) * sizeof(uint32_t) +
-		static_cast<size_t>(((ncb + 31u) / 32u + 3u) & ~3u) * sizeof(uint32_t) + static_cast<size_t>(ns) * 32u +
-		(routed ? kTileLights * sizeof(uint16_t) : 0);
+	return static_cast<size_t>(macro > 1 ? 2 : 1) * kTileBytes + static_cast<size_t>(ns) * 32 * sizeof(uint32_t) +
+		static_cast<size_t>(list_supers) * kTileLights * sizeof(uint16_t) + static_cast<size_t>((list_supers + 3u) & ~3u) * sizeof(uint32_t) +
+		static_cast<size_t>((ncb + 3u) & ~3u) * sizeof(uint32_t) + static_cast<size_t>(((ncb + 31u) / 32u + 3u) & ~3u) * sizeof(uint32_t) +
+		(static_cast<size_t>(ns) + ncb) * 32u + static_cast<size_t>((ncb + 7u) & ~7u) * sizeof(uint16_t) + (routed ? kTileLights * sizeof(uint16_t) : 0);
 }
 
 static cudaError_t launch_hier_bin2(const BinParams& p0, uint32_t tiles, cudaStream_t stream)
@@ -1342,7 +1384,12 @@ static cudaError_t launch_hier_bin2(const BinParams& p0, uint32_t tiles, cudaStr
 	if (p.macro > 64 || (p.macro & (p.macro - 1u)))
 		return cudaErrorInvalidValue; // a record's 16-bit index holds 6 + 10 bits
 	p.tile_end = p.tile_begin + tiles;
-	const size_t smem = hier_bin2_smem_bytes(p.ns, p.ncb, routed, p.macro);
+	// survivor lists of at most 16 super-groups at a time (8 with the second tile buffer of macro tiles): 3 CTAs per SM.  Late
+	// rounds rarely have more live super-groups than that; the first round takes two or three passes over its lists.
+	p.list_supers = p.ns < (p.macro > 1 ? 8u : 16u) ? p.ns : (p.macro > 1 ? 8u : 16u);
+	const size_t smem = hier_bin2_smem_bytes(p.ns, p.ncb, routed, p.macro, p.list_supers);
+	if (smem > 227u * 1024u || p.ncb > 0xffffu)
+		return cudaErrorInvalidValue; // (a grid of more than ~5,000 cluster groups: the group tables no longer fit)
 	static size_t configured[2] = {0, 0};
 	if (smem > configured[routed])
 	{

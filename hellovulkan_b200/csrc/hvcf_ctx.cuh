@@ -5,6 +5,7 @@
 #include "../../include/hvcf.h"
 
 #include <cstdlib>
+#include <functional>
 
 #include <nvtx3/nvToolsExt.h>
 
@@ -39,6 +40,8 @@ int hvcf_hier_close(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s);
 void hvcf_shard_free(hvcf_ctx* ctx);
 cudaError_t hvcf_kmark(hvcf_ctx* ctx, uint32_t frame, int i, cudaStream_t s);
 int hvcf_peer_error_after_sync(hvcf_ctx* ctx, const char* what);
+// rounds: level-0 binning (bin_round(r) launches round r's, against what hier_alive_kernel left alive) + count pass, round by round
+int hvcf_hier_rounds(hvcf_ctx* ctx, uint32_t frame, cudaStream_t s, uint32_t* launches, const std::function<int(uint32_t)>& bin_round);
 int hvcf_peer_totals_step(hvcf_ctx* ctx, void* stream, uint32_t what); // 1 = post, 2 = wait + index base, 3 = both
 }
 
@@ -115,10 +118,11 @@ struct hvcf_ctx
 	Round h_rounds[kHMaxChunks]{};
 	uint32_t h_num_rounds = 0;
 	int rounds_mode = -1;                    // HVCF_ROUNDS: -1 = by the number of tiles, 0 = never, n > 0 = at most n rounds whenever the frame has two tiles or more
-	uint32_t rounds_min_tiles = 2048, rounds_head = 64, rounds_growth = 4; // HVCF_ROUNDS_MIN_TILES / _HEAD / _GROWTH
+	uint32_t rounds_min_tiles = 2048, rounds_head = 64, rounds_growth = 8; // HVCF_ROUNDS_MIN_TILES / _HEAD / _GROWTH
 	uint32_t* d_group_alive = nullptr;       // [kHMaxChunks][ncb]: per round, which groups still had a cluster below its cap when it began
 	float* d_alive_union = nullptr;          // [ncb][8] union box of each group's live clusters (rounds after the first)
 	const uint32_t* bin_alive = nullptr;     // what the next binning launch takes as BinParams::group_alive
+	uint32_t rounds_early_segs = 16;         // HVCF_ROUNDS_EARLY_SEGS: light segments of each of the first two rounds (at most one per tile)
 	uint32_t rounds_late_segs = 32;          // HVCF_ROUNDS_LATE_SEGS: light segments of every round after the first two
 	uint32_t bin_macro = 1;                  // ... and as BinParams::macro
 	int rounds_macro = -1;                   // HVCF_ROUNDS_MACRO: -1 = by the round's size, else tiles per macro tile of the rounds after the first two (power of two <= 64)

@@ -243,7 +243,10 @@ void hier_build_lane_map(HierPlan* hp, uint32_t X, uint32_t Y, uint32_t Zs, uint
 	const uint32_t ux = h.K >= 2 ? 2 : 1, uy = h.K >= 4 ? 2 : 1;          // blocks of one warp program
 	auto brick_of = [&](uint32_t b) {
 		const uint64_t bxi = b % h.nbx, byi = (b / h.nbx) % h.nby, bzi = b / (h.nbx * h.nby);
-		return (bzi * 4096 + byi / gy) * 4096 + bxi / gx;
+		return ((byi / gy) * 4096 + bxi / gx) * 65536 + bzi; // brick position first, slice last: consecutive groups -- and with them
+		                                                     // the super-groups of the two-level binning -- are the same brick in
+		                                                     // consecutive slices, so a super-group at the edge of the lit region
+		                                                     // stays at the edge (its box rejects most lights in phase A)
 	};
 	if (brick)
 	{

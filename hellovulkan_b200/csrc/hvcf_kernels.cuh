@@ -147,6 +147,7 @@ struct BinParams
 	DeviceStats* stats;
 	uint32_t tile_begin;           // first tile of this launch (grid.y counts from it)
 	uint32_t tile_end = 0;         // set by the launcher: one past the last tile of this launch
+	uint32_t list_supers = 0;      // set by the launcher: super-group survivor lists held in shared memory at a time
 	uint32_t macro = 1;            // two-level kernel: tiles per macro tile (power of two <= 64; hvcf_bin.cu), 1 = every tile has its own slots
 	const uint32_t* group_alive = nullptr; // [ncb] or NULL: 0 = every cluster of the group already holds its cap (rounds, hier_alive_kernel): its slots stay empty
 	// two-level variant (hier_bin2_kernel): ns > 0 selects it
@@ -209,7 +210,7 @@ struct XBinParams
 };
 cudaError_t launch_hier_xbin(const XBinParams& q, uint32_t tiles, cudaStream_t stream);
 cudaError_t launch_hier_super_unions(const float* cb_union, uint32_t ncb, uint32_t sg, uint32_t ns, float* sb_union, cudaStream_t stream);
-size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro);
+size_t hier_bin2_smem_bytes(uint32_t ns, uint32_t ncb, bool routed, uint32_t macro, uint32_t list_supers);
 cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t stream);
 
 // ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------

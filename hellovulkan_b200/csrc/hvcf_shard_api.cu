@@ -186,7 +186,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			return rc;
 	}
 	NvtxZone zone("Light_Culling");
-	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true, false);
+	int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull_routed", true, true);
 	if (rc != HVCF_OK)
 		return rc;
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -245,9 +245,31 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	b.in_cnt = reinterpret_cast<const uint32_t*>(box + sh.off_cnt);
 	b.block_tiles = sh.block_tiles;
 	b.tile_cnt = sh.d_tile_cnt;
-	HVCF_CUDA(launch_hier_bin(b, sh.tiles_phys, s));
+	ctx->open_launches += 2;
+	if (ctx->h_num_rounds >= 2)
+	{
+		// the inbox is in light order, so it takes rounds like any other frame: each round's binning skips the groups of this
+		// slab that the earlier rounds have filled (hier_alive_kernel, hvcf_bin.cu)
+		const int rrc = hvcf_hier_rounds(ctx, frame, s, &ctx->open_launches, [&](uint32_t r) {
+			const hvcf_ctx::Round& rd = ctx->h_rounds[r];
+			BinParams br = b;
+			br.tile_begin = rd.tile_begin;
+			br.group_alive = ctx->bin_alive;
+			br.cb_union = ctx->bin_alive ? ctx->d_alive_union : ctx->d_cb_union;
+			const cudaError_t e = launch_hier_bin(br, rd.tile_end - rd.tile_begin, s);
+			if (e != cudaSuccess)
+				return fail(HVCF_ERR_CUDA, "hvcf_cull_routed: binning of round %u: %s", r, cudaGetErrorString(e));
+			return static_cast<int>(HVCF_OK);
+		});
+		if (rrc != HVCF_OK)
+			return rrc;
+	}
+	else
+	{
+		HVCF_CUDA(launch_hier_bin(b, sh.tiles_phys, s));
+		++ctx->open_launches;
+	}
 	HVCF_CUDA(hvcf_kmark(ctx, frame, 2, s));
-	ctx->open_launches += 3;
 	ctx->range_transformed = ctx->range_binned = sh.tiles_phys * kTileLights;
 
 	// ---- count pass + scan; this rank's total is POSTED at once, but nobody waits yet: the write pass runs on local positions

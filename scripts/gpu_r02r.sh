@@ -15,12 +15,13 @@ for l in open("$O/bench_${w}_$name.json"):
         print("$w $name", "ms", round(d["ms_per_step"], 4), {k: round(v["ms"], 4) for k, v in r["per_kernel"].items()}, "launches", d["gpu_launches_per_step"], "bin_tests", d["detail"]["stats"]["bin_tests"], "exec", d["detail"]["stats"]["executed_tests"], "pre", d["detail"]["stats"]["prefilter_tests"], "write", d["detail"]["stats"]["write_pass_tests"])
 PY
 }
-run brick C16M HVCF_ROUNDS=-1
-run strip C16M HVCF_HIER_BRICK=0
-run brick_r0 C16M HVCF_ROUNDS=0
-run strip_r0 C16M HVCF_ROUNDS=0 HVCF_HIER_BRICK=0
-run brick_ls64 C16M HVCF_ROUNDS_LATE_SEGS=64
-run brick_g8 C16M HVCF_ROUNDS_GROWTH=8
+run default C16M HVCF_ROUNDS=-1
+run g8 C16M HVCF_ROUNDS_GROWTH=8
+run es64 C16M HVCF_ROUNDS_EARLY_SEGS=64
+run es32 C16M HVCF_ROUNDS_EARLY_SEGS=32
+run h32 C16M HVCF_ROUNDS_HEAD=32
+run h128g8 C16M HVCF_ROUNDS_HEAD=128 HVCF_ROUNDS_GROWTH=8
+run h32g2x C16M HVCF_ROUNDS_HEAD=32 HVCF_ROUNDS_GROWTH=2 HVCF_ROUNDS=4
 tail -5 $O/err.txt
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 260 --csv --log-file $O/launches_C16M.csv $B --steps 2 > $O/ncu.log 2>&1
 echo "== C16M"; python scripts/launch_seq.py $O/launches_C16M.csv

@@ -225,3 +225,21 @@ def test_row_shards_of_plain_contexts_concatenate(hv, oracle):
             got_idx.append(idx.copy())
     assert np.array_equal(np.concatenate(got_counts), want_cells["count"])
     assert np.array_equal(np.concatenate(got_idx), want_idx)
+
+
+@pytest.mark.parametrize("plan", ["8:1:2", "3:4:4", "4:16:8"])
+@pytest.mark.parametrize("grid,screen,n,cuts,cap", [(GRID_A, SCREEN_A, 70_000, (0, 15, 19, 24), 150), (GRID_B, SCREEN_B, 120_000, (0, 30, 40, 48), 150),
+                                                   (GRID_A, SCREEN_A, 30_000, (0, 12, 24), 5)])
+def test_routed_frames_in_rounds(hv, torch_mod, oracle, monkeypatch, plan, grid, screen, n, cuts, cap):
+    """the inbox of a routed frame is in light order, so it takes rounds like any other frame (hier_alive_kernel between the rounds'
+    binning launches); forced here on small frames: rounds : head tiles : growth.  Every rank's full grid equals the single context's."""
+    ubo = oracle.camera_ubo(grid, screen)
+    lights = oracle.init_lights(n, seed=21)
+    monkeypatch.setenv("HVCF_ROUNDS", "0")
+    want = run_single(hv, grid, ubo, lights, cap=cap)
+    rounds, head, growth = plan.split(":")
+    monkeypatch.setenv("HVCF_ROUNDS", rounds)
+    monkeypatch.setenv("HVCF_ROUNDS_HEAD", head)
+    monkeypatch.setenv("HVCF_ROUNDS_GROWTH", growth)
+    out, _ = run_routed(hv, torch_mod, grid, [ubo], lights, cuts, frames=2, cap=cap)
+    assert_all_equal(out, want, f"rounds {plan}")
