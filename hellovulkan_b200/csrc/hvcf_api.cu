@@ -118,6 +118,10 @@ static void free_ctx(hvcf_ctx* c)
 		for (auto& e : fe)
 			if (e)
 				cudaEventDestroy(e);
+	for (auto& fe : c->kev_phase2)
+		for (auto& e : fe)
+			if (e)
+				cudaEventDestroy(e);
 	for (auto& fe : c->kev_round)
 		for (auto& re : fe)
 			for (auto& e : re)
@@ -729,10 +733,12 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 				uint32_t mshift = 0;
 				const bool two_level = ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups ||
 					static_cast<uint64_t>(ctx->hp.ncb) * ctx->num_lights >= (1ull << 28));
-				if (nr >= 2 && two_level && !routed && ctx->pipe_mode != 0)
+				if (nr >= 2 && two_level && ctx->pipe_mode != 0)
 				{
 					uint32_t want = ctx->rounds_macro >= 0 ? static_cast<uint32_t>(ctx->rounds_macro) : (end - t) / 592u;
 					want = want > 64u ? 64u : want;
+					if (routed) // a routed frame's macro tile is a route block: its records are dense from the block's first inbox tile
+						want = ctx->rounds_macro == 0 || t % ctx->shard.block_tiles ? 1u : ctx->shard.block_tiles;
 					while ((2u << mshift) <= want)
 						++mshift;
 					tps = ((tps + (1u << mshift) - 1u) >> mshift) << mshift;
@@ -1710,6 +1716,13 @@ int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5])
 			out_ms[1] += a, out_ms[2] += b;
 		}
 		HVCF_CUDA(cudaEventElapsedTime(&out_ms[3], ctx->kev_round[frame][ctx->h_num_rounds - 1][2], ctx->kev[frame][4]));
+		if (ctx->routed_frame && ctx->kev_phase2[frame][1]) // the second route of a two-phase frame sits inside a round's binning interval
+		{
+			float ph = 0.0f;
+			if (cudaEventElapsedTime(&ph, ctx->kev_phase2[frame][0], ctx->kev_phase2[frame][1]) == cudaSuccess && ph > 0.0f && ph < out_ms[1])
+				out_ms[0] += ph, out_ms[1] -= ph;
+			(void)cudaGetLastError();
+		}
 	}
 	if (ctx->kev_exchange[frame]) // sharded frames: the wait for the other ranks' totals sits between finalize and the write pass
 		HVCF_CUDA(cudaEventElapsedTime(&out_ms[4], ctx->kev[frame][6], ctx->kev[frame][5]));

@@ -581,7 +581,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	{
 		// macro tiles (p.macro_shift = log2 M; hier_bin2_kernel): a slot belongs to M consecutive tiles, its count sits at the first
 		// of them, it holds M x kBinCap records and its 16-bit indices run over the M tiles.  M = 1: a slot per tile, as ever.
-		const uint32_t ms = INBOX ? 0u : p.macro_shift, mstep = 1u << ms;
+		const uint32_t ms = p.macro_shift, mstep = 1u << ms; // (routed frames: a route block's tiles, one slot per group and block)
 		uint32_t it_t = 0, it_b = 0, it_n0 = 0, it_nb = 0; // the batch to FETCH next: (first) tile inside the segment, batch, slot count, batches
 		bool it_raw = false;                                // the slot overflowed: its tiles are read raw
 		uint32_t cnt_chunk = 0xffffffffu, my_cnt = 0;
@@ -859,7 +859,7 @@ template <bool ROUTED>
 __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinParams p)
 {
 	extern __shared__ __align__(128) unsigned char s_dyn[];
-	const uint32_t M = ROUTED ? 1u : p.macro;
+	const uint32_t M = p.macro; // (routed frames: 1, or the tiles of a route block -- one slot per group and BLOCK)
 	const uint32_t nbuf = M > 1u ? 2u : 1u;
 	const uint32_t LS = p.list_supers; // super-group survivor lists held at a time
 	unsigned char* const s_tiles = s_dyn;                                                          // nbuf x kTileBytes
@@ -877,7 +877,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	__shared__ uint32_t s_super[32]; // the i-th live super-group
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t tile_id = p.tile_begin + blockIdx.x * M;                 // first tile of this CTA
-	const uint32_t tM = min(M, p.tile_end - tile_id);                       // its tiles
+	uint32_t tM = min(M, p.tile_end - tile_id);                             // its tiles
 	grid_dep_launch();
 	if (threadIdx.x == 0)
 	{
@@ -888,15 +888,20 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 	}
 	__syncthreads();
 	grid_dep_wait(); // the tile is written by the transform kernel of this frame (or arrived from another rank)
-	uint32_t valid = kTileLights;
+	uint32_t valid = kTileLights; // records of the current tile
+	uint32_t left = 0;            // ROUTED: records of the route block from this CTA's first tile on
 	if constexpr (ROUTED)
 	{
 		const uint32_t in_block = (tile_id & (p.block_tiles - 1u)) * kTileLights;
 		const uint32_t c = p.in_cnt[tile_id / p.block_tiles];
-		valid = c > in_block ? min(c - in_block, kTileLights) : 0u;
+		left = c > in_block ? c - in_block : 0u;
+		if (M == 1u)
+			left = min(left, kTileLights);
+		valid = min(left, kTileLights);
+		tM = min(tM, (left + kTileLights - 1u) / kTileLights); // only the tiles of the block's region that hold records
 		if (threadIdx.x == 0)
-			p.tile_cnt[tile_id] = valid;
-		if (valid == 0u)
+			p.tile_cnt[tile_id] = left; // (a macro tile's raw walk runs over all of its records)
+		if (left == 0u)
 		{
 			for (uint32_t cb = threadIdx.x; cb < p.ncb; cb += blockDim.x)
 				p.bin_count[static_cast<size_t>(cb) * p.tiles_cap + tile_id] = 0u;
@@ -981,16 +986,16 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 			reinterpret_cast<float*>(s_sbox + 2 * si)[c] = v;
 		}
 	}
-	if constexpr (ROUTED)
-	{
-		// the in-block light index of this tile's records: the j-th record of the block's region is the j-th set bit of the block's
-		// survivor bitmask (block_tiles x 32 words, one bit per light of the block in light order).  Each thread takes the words
-		// t, t + 256, ...: an exclusive prefix of the popcounts gives the rank of a word's first set bit.
-		__shared__ uint32_t s_wsum[kBinWarps];
-		__shared__ uint32_t s_carry;
+	__shared__ uint32_t s_wsum[kBinWarps];
+	__shared__ uint32_t s_carry;
+	// ROUTED: the in-block light index of tile t's records.  The j-th record of the block's region is the j-th set bit of the
+	// block's survivor bitmask (block_tiles x 32 words, one bit per light of the block in light order).  Each thread takes the
+	// words t, t + 256, ...: an exclusive prefix of the popcounts gives the rank of a word's first set bit.  Also kept in
+	// tile_ids for the raw walk of the count / write passes (a slot that overflowed reads the inbox records themselves).
+	auto rebuild_ids = [&](uint32_t t, uint32_t t_valid) {
 		const uint32_t words = p.block_tiles * 32u;
-		const uint32_t* mask = p.in_mask + static_cast<size_t>(tile_id & ~(p.block_tiles - 1u)) * 32u;
-		const uint32_t r_begin = (tile_id & (p.block_tiles - 1u)) * kTileLights, r_end = r_begin + valid;
+		const uint32_t* mask = p.in_mask + static_cast<size_t>(t & ~(p.block_tiles - 1u)) * 32u;
+		const uint32_t r_begin = (t & (p.block_tiles - 1u)) * kTileLights, r_end = r_begin + t_valid;
 		if (threadIdx.x == 0)
 			s_carry = 0u;
 		__syncthreads();
@@ -1003,9 +1008,9 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 #pragma unroll
 			for (int o = 1; o < 32; o <<= 1)
 			{
-				const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+				const uint32_t tt = __shfl_up_sync(0xffffffffu, inc, o);
 				if (lane >= static_cast<uint32_t>(o))
-					inc += t;
+					inc += tt;
 			}
 			if (lane == 31)
 				s_wsum[warp] = inc;
@@ -1028,23 +1033,31 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin2_kernel(const BinPara
 				s_carry = before + inc;
 			__syncthreads();
 		}
-		// kept for the raw-tile path of the count / write passes (a slot that overflowed reads the inbox tile itself)
-		for (uint32_t i = threadIdx.x; i < valid; i += blockDim.x)
-			p.tile_ids[static_cast<size_t>(tile_id) * kTileLights + i] = s_ids[i];
-	}
+		for (uint32_t i = threadIdx.x; i < t_valid; i += blockDim.x)
+			p.tile_ids[static_cast<size_t>(t) * kTileLights + i] = s_ids[i];
+	};
+	if constexpr (ROUTED)
+		rebuild_ids(tile_id, valid);
 	__syncthreads(); // the compacted groups, the boxes (and the in-block indices) are in place
 	const uint32_t lt = lanemask_lt();
-	const uint32_t ngroups = ROUTED ? (valid + 63u) / 64u : kTileGroups;
-	const uint32_t slot_cap = tM * kBinCap; // records of a (group, macro tile) slot
+	const uint32_t slot_cap = (ROUTED ? M : tM) * kBinCap; // records of a (group, macro tile) slot
 	unsigned long long tests = 0;
 	for (uint32_t m = 0; m < tM; ++m)
 	{
 		const uint32_t buf = nbuf == 2u ? (m & 1u) : 0u;
+		if constexpr (ROUTED)
+		{
+			valid = min(left - m * kTileLights, kTileLights);
+			if (m != 0u)
+				rebuild_ids(tile_id + m, valid); // (ends with a barrier-free store loop; the barrier below the next phase A1 orders s_ids)
+		}
+		const uint32_t ngroups = ROUTED ? (valid + 63u) / 64u : kTileGroups;
 		// the next tile goes into the other buffer: every warp left it at the barrier that ended tile m - 1
 		if (m + 1u < tM && threadIdx.x == 0)
 		{
-			mbar_arrive_expect_tx(&bar[buf ^ 1u], kTileBytes);
-			bulk_copy_g2s(s_tiles + (buf ^ 1u) * kTileBytes, src + static_cast<size_t>(tile_id + m + 1u) * kTileBytes, kTileBytes, &bar[buf ^ 1u]);
+			const uint32_t bytes = ROUTED ? min(left - (m + 1u) * kTileLights, kTileLights) * 16u : kTileBytes;
+			mbar_arrive_expect_tx(&bar[buf ^ 1u], bytes);
+			bulk_copy_g2s(s_tiles + (buf ^ 1u) * kTileBytes, src + static_cast<size_t>(tile_id + m + 1u) * kTileBytes, bytes, &bar[buf ^ 1u]);
 		}
 		mbar_wait(&bar[buf], (m >> 1) & 1u);
 		const float4* tile = reinterpret_cast<const float4*>(s_tiles + buf * kTileBytes);
@@ -1379,8 +1392,10 @@ static cudaError_t launch_hier_bin2(const BinParams& p0, uint32_t tiles, cudaStr
 {
 	BinParams p = p0;
 	const bool routed = p.in_mask != nullptr;
-	if (p.macro == 0 || routed)
+	if (p.macro == 0)
 		p.macro = 1;
+	if (routed && p.macro != 1 && p.macro != p.block_tiles)
+		return cudaErrorInvalidValue; // a routed frame's macro tile is a route block
 	if (p.macro > 64 || (p.macro & (p.macro - 1u)))
 		return cudaErrorInvalidValue; // a record's 16-bit index holds 6 + 10 bits
 	p.tile_end = p.tile_begin + tiles;

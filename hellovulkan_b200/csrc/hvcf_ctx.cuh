@@ -75,7 +75,9 @@ struct ShardState
 	uint32_t* d_tile_cnt = nullptr;            // [tiles_phys] valid records of every inbox tile of the open frame
 	uint16_t* d_tile_ids = nullptr;            // [tiles_phys][1024] in-block light index of every inbox record of the open frame (rebuilt by the binning kernel)
 	uint32_t epoch = 0;                        // routed-frame serial, the same on every rank
+	uint32_t* d_cnt_last = nullptr;            // [blocks_phys] the last routed frame's records per route block (the inbox's own counts are cleared after use)
 	uint32_t* d_seg = nullptr;                 // [cluster_count * cap] this rank's index segment at LOCAL positions (the write pass runs before the totals are known)
+	bool two_phase = true;                     // HVCF_ROUTE_TWO_PHASE=0: every light is routed against the slabs' union boxes, in one launch
 	bool seg_local = false;                    // the write pass of the open frame writes d_seg / local offsets (hvcf_cull_routed)
 };
 
@@ -126,6 +128,7 @@ struct hvcf_ctx
 	uint32_t rounds_late_segs = 32;          // HVCF_ROUNDS_LATE_SEGS: light segments of every round after the first two
 	uint32_t bin_macro = 1;                  // ... and as BinParams::macro
 	int rounds_macro = -1;                   // HVCF_ROUNDS_MACRO: -1 = by the round's size, else tiles per macro tile of the rounds after the first two (power of two <= 64)
+	cudaEvent_t kev_phase2[8][2]{};          // HVCF_KERNEL_TIMES, two-phase routed frames: around live boxes + second route + waits (counted as "transform")
 	cudaEvent_t kev_round[8][kHMaxChunks][3]{}; // HVCF_KERNEL_TIMES with rounds: [frame][round][before, after alive + bin, after count]
 	uint32_t* d_hseg_counts = nullptr;
 	uint32_t* d_hseg_prefix = nullptr;

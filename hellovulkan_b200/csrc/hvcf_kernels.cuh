@@ -215,6 +215,7 @@ cudaError_t launch_hier2(int K, bool write, const HierParams& p, cudaStream_t st
 
 // ---- exchange step of the z-slab sharded grid over peer memory (hvcf_peer.cu) ----------------------------
 constexpr uint32_t kMaxPeers = 16;
+constexpr uint32_t kSlabBoxes = 2;  // live boxes per slab in the second phase of a routed frame: view-space x < 0 and x >= 0
 struct PeerMailbox
 {
 	unsigned long long totals[2][kMaxPeers]; // [frame parity][rank] = epoch << 32 | index total of that rank's slab
@@ -222,8 +223,13 @@ struct PeerMailbox
 	unsigned int done;                       // CTA counter of our own push kernel
 	unsigned int error;                      // 1 = a wait timed out
 	unsigned long long routed[2][kMaxPeers]; // [frame parity][rank] = epoch << 32 once that rank's share of the lights is in OUR inbox
-	unsigned int route_done;                 // CTA counter of our own route kernel
+	unsigned int route_done;                 // (unused)
 	unsigned int pad_;
+	// two-phase routed frames (hvcf_shard.cu): the frame's first lights are routed and counted, every rank then publishes the
+	// boxes of its clusters that are still below their cap, and the rest of the lights is routed against THOSE
+	unsigned long long routed2[2][kMaxPeers];    // [frame parity][rank] = epoch << 32 once that rank's second share is in OUR inbox
+	unsigned long long alive_flag[2][kMaxPeers]; // [frame parity][rank] = epoch << 32 once that rank's live boxes are in alive_box
+	float alive_box[2][kMaxPeers][kSlabBoxes][8]; // [frame parity][rank][box] { lo.xyz, 0, hi.xyz, 0 }; (+inf, -inf) = nothing alive there
 };
 struct PeerParams
 {
@@ -243,7 +249,9 @@ struct RouteParams
 	uint32_t block_tiles;             // B: tiles per route block, power of two <= kMaxRouteBlockTiles
 	uint32_t block0, blocks;          // first route block of this rank (global numbering), own blocks
 	uint32_t world, rank, epoch, parity;
-	const float* slab_box;            // [world][8] union box of every rank's cluster slab { lo.xyz, 0, hi.xyz, 0 }
+	const float* slab_box;            // [world][boxes][8] boxes of every rank's cluster slab { lo.xyz, 0, hi.xyz, 0 }: a light goes where it hits any
+	uint32_t boxes;                   // 1 = the slabs' union boxes; kSlabBoxes = their live boxes (second phase)
+	uint32_t phase;                   // 0 = first (or only) route launch of the frame: clears the counters, raises `routed`; 1 = second: adds, raises `routed2`
 	float4* rec[kMaxPeers];           // every rank's inbox of this frame parity: [tiles][1024] records (a route block's region is dense from its start),
 	uint32_t* mask[kMaxPeers];        //   [tiles][32] survivor bitmask of every source tile: the j-th record of a block's region is its j-th set bit,
 	uint32_t* cnt[kMaxPeers];         //   [blocks] records per route block
@@ -253,7 +261,10 @@ struct RouteParams
 	DeviceStats* stats;
 };
 cudaError_t launch_shard_route(const RouteParams& p, cudaStream_t stream);
-cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream);
+// what: 0 / 2 = raise this rank's flag of the first / second share on every rank, then wait for everybody's; 1 = wait for the live boxes
+cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream, uint32_t what = 0);
+// reduces the live boxes of this rank's groups (hier_alive_kernel) to kSlabBoxes boxes and publishes them on every rank
+cudaError_t launch_slab_alive(const PeerParams& p, uint32_t parity, const uint32_t* group_alive, const float* alive_union, uint32_t ncb, cudaStream_t stream);
 // union box of each rank's cluster range [begin[r], end[r]) of the whole-grid AABB buffer
 cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges, uint32_t world, float* slab_box, cudaStream_t stream);
 cudaError_t preload_shard_kernels();

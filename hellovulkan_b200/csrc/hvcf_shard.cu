@@ -127,10 +127,11 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 	namespace cg = cooperative_groups;
 	__shared__ __align__(128) float4 s_stage[2][kTileLights];
 	__shared__ __align__(128) uint32_t s_mask[kMaxPeers][32];
-	__shared__ float s_box[kMaxPeers][6];
+	__shared__ float s_box[kMaxPeers * kSlabBoxes][6];
 	__shared__ uint32_t s_wt[kRouteWarps][kMaxPeers];
 	__shared__ uint32_t s_tot[kMaxPeers];   // this CTA's survivors per destination; read by the CTAs after it in the cluster
 	__shared__ uint32_t s_cbase[kMaxPeers]; // this CTA's first position in the (block, destination) region
+	__shared__ uint32_t s_btot[kMaxPeers];  // the whole block's survivors per destination
 	cg::cluster_group cluster = cg::this_cluster();
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t k = cluster.block_rank();            // tile inside the route block
@@ -145,18 +146,28 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 		{
 			DeviceStats* st = p.stats;
 			const uint32_t first = p.block0 * p.block_tiles * kTileLights;
-			st->executed_tests = 0ull;
-			st->total_indices = 0u;
-			st->overflow_clusters = 0u;
-			st->write_tests = 0ull;
-			st->bin_tests = st->prefilter_tests = static_cast<unsigned long long>(p.light_end > first ? p.light_end - first : 0u) * p.world;
-			stats_next_epoch(st);
+			const unsigned long long mine = static_cast<unsigned long long>(p.light_end > first ? p.light_end - first : 0u) * p.world * p.boxes;
+			if (p.phase == 0)
+			{
+				st->executed_tests = 0ull;
+				st->total_indices = 0u;
+				st->overflow_clusters = 0u;
+				st->write_tests = 0ull;
+				st->bin_tests = st->prefilter_tests = mine;
+				stats_next_epoch(st);
+			}
+			else
+			{
+				atomicAdd(&st->bin_tests, mine);
+				atomicAdd(&st->prefilter_tests, mine);
+			}
 		}
 	}
-	if (threadIdx.x < p.world * 6)
+	const uint32_t nbox = p.world * p.boxes;
+	if (threadIdx.x < nbox * 6)
 	{
 		const uint32_t d = threadIdx.x / 6, c = threadIdx.x % 6;
-		s_box[d][c] = p.slab_box[d * 8 + (c < 3 ? c : c + 1)];
+		s_box[d][c] = __ldcg(&p.slab_box[d * 8 + (c < 3 ? c : c + 1)]); // (second phase: written into this rank's mailbox by the peers)
 	}
 	__syncthreads();
 	const float* view = p.ubo->camera_view;
@@ -180,7 +191,12 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 			v[it].z = mat_row_dot(view, 2, pw.x, pw.y, pw.z, pw.w);
 			v[it].w = __fmul_rn(radius, radius);                    // LightCulling.comp:56
 			for (uint32_t d = 0; d < p.world; ++d)
-				hm[it] |= sphere_box_hit(v[it].x, v[it].y, v[it].z, v[it].w, &s_box[d][0], &s_box[d][3]) ? (1u << d) : 0u;
+			{
+				bool hit = sphere_box_hit(v[it].x, v[it].y, v[it].z, v[it].w, &s_box[d * p.boxes][0], &s_box[d * p.boxes][3]);
+				for (uint32_t bx = 1; bx < p.boxes; ++bx)
+					hit = hit || sphere_box_hit(v[it].x, v[it].y, v[it].z, v[it].w, &s_box[d * p.boxes + bx][0], &s_box[d * p.boxes + bx][3]);
+				hm[it] |= hit ? (1u << d) : 0u;
+			}
 		}
 	}
 	uint32_t my_tot = 0u; // lane d: survivors of this warp for destination d
@@ -216,18 +232,24 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 			wbase += s_wt[w][lane];
 		if (warp == 0)
 		{
-			uint32_t cb = 0u;
-			for (uint32_t r = 0; r < k; ++r)
-				cb += *cluster.map_shared_rank(&s_tot[lane], r);
+			uint32_t cb = 0u, all = 0u;
+			for (uint32_t r = 0; r < p.block_tiles; ++r)
+			{
+				const uint32_t t = *cluster.map_shared_rank(&s_tot[lane], r);
+				cb += r < k ? t : 0u;
+				all += t;
+			}
 			s_cbase[lane] = cb;
-			if (k + 1 == p.block_tiles)
-				p.cnt[lane][blk] = cb + s_tot[lane]; // the block's last tile: everything before it + its own = the region's count
+			s_btot[lane] = all; // the block's records for this destination: none -> the owner never looks at the block's bitmasks
+			if (k + 1 == p.block_tiles && all != 0u)
+				p.cnt[lane][blk] = all; // the region's count (the owner cleared its counts after the last frame of this parity: zero is not sent)
 		}
 	}
 	cluster.sync(); // every CTA has read what it needs from the others (and s_cbase is in place): from here on the CTAs are independent
 	// ---- staging rounds: consecutive destinations are packed into the staging buffer while they fit (2,048 records; a tile's
 	// survivors over ALL destinations usually do), one proxy fence + one barrier per round, then thread d hands destination d's
-	// run to the copy engine.  Every destination also gets the tile's 128-byte bitmask (zeros included: the owner sums all of them). ----
+	// run to the copy engine.  Every destination that gets any record of the BLOCK also gets the tile's 128-byte bitmask (zeros
+	// included: the owner sums the block's masks). ----
 	float4* const stage = &s_stage[0][0];
 	constexpr uint32_t kStageCap = 2u * kTileLights;
 	uint32_t d0 = 0u;
@@ -272,55 +294,119 @@ __global__ void __launch_bounds__(kRouteWarps * 32) shard_route_kernel(const Rou
 				o += s_tot[e];
 			if (s_tot[d] != 0u)
 				bulk_store_s2g(p.rec[d] + slot + s_cbase[d], stage + o, s_tot[d] * 16u);
-			bulk_store_s2g(p.mask[d] + (static_cast<size_t>(blk) * p.block_tiles + k) * 32u, s_mask[d], 128u);
+			if (s_btot[d] != 0u) // (the second phase of a two-phase frame sends nothing at all to the slabs that are full)
+				bulk_store_s2g(p.mask[d] + (static_cast<size_t>(blk) * p.block_tiles + k) * 32u, s_mask[d], 128u);
 			bulk_commit();
 		}
 		d0 = d1;
 	}
-	// ---- the threads that issued bulk stores wait for their completion, fence at system scope and count themselves off;
-	// the last one of the whole grid raises the rank's flag on every rank.  Everybody else has left: no trailing barrier. ----
+	// ---- the threads that issued bulk stores only wait until the copy engine has READ the staging buffer (the CTA may then
+	// leave).  Nobody fences or counts here: the rank's flag is raised by the NEXT kernel of the stream (shard_wait_routed_kernel),
+	// and a kernel boundary orders every store of this grid -- the bulk copies included -- before it.  (A first version waited for
+	// the completion of its remote stores, fenced at system scope and counted itself off in every CTA: that tail, not the routing,
+	// was most of the kernel's 0.3 ms for 8M lights, profiles/r02z.) ----
 	if (threadIdx.x < p.world)
-	{
-		bulk_wait_all();
-		fence_proxy_async_all();
-		__threadfence_system();
-		PeerMailbox* mine = p.mail[p.rank];
-		const unsigned int done = atomicAdd(&mine->route_done, 1u);
-		if (done == gridDim.x * p.world - 1u)
-		{
-			mine->route_done = 0u;
-			__threadfence_system();
-			for (uint32_t r = 0; r < p.world; ++r)
-				shard_st_release_sys(&p.mail[r]->routed[p.parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
-		}
-	}
+		bulk_wait_read<0>();
 }
 
-// one warp: lane r waits for rank r's share of the lights (its own included: the flag is raised by its own route kernel)
-__global__ void __launch_bounds__(32) shard_wait_routed_kernel(const PeerParams p, uint32_t parity)
+// one warp: lane r raises this rank's flag of the phase on rank r (what = 0 / 2: the route kernel of the phase, if the rank had
+// anything to route, is the previous kernel of the stream) and waits for rank r's share of the lights, or (what = 1) only waits
+// for rank r's live boxes
+__global__ void __launch_bounds__(32) shard_wait_routed_kernel(const PeerParams p, uint32_t parity, uint32_t what)
 {
 	const uint32_t r = threadIdx.x;
 	if (r < p.world)
 	{
 		PeerMailbox* mine = p.mail[p.rank];
+		// the route kernel before this one in the stream has completed, and with it every store into the peers' inboxes: fence at
+		// system scope, then tell rank r (release) that this rank's share of the phase has arrived
+		if (what != 1u)
+		{
+			__threadfence_system();
+			shard_st_release_sys(what == 0 ? &p.mail[r]->routed[parity][p.rank] : &p.mail[r]->routed2[parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+		}
+		const unsigned long long* word = what == 0 ? &mine->routed[parity][r] : (what == 1 ? &mine->alive_flag[parity][r] : &mine->routed2[parity][r]);
 		unsigned long long t0;
 		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
 		for (;;)
 		{
-			const unsigned long long v = shard_ld_acquire_sys(&mine->routed[parity][r]);
+			const unsigned long long v = shard_ld_acquire_sys(word);
 			if ((v >> 32) == p.epoch)
 				break;
 			unsigned long long t1;
 			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
 			if (t1 - t0 > kRouteTimeoutNs)
 			{
-				atomicCAS(&mine->error, 0u, (3u << 28) | (r << 20) | (p.epoch & 0xfffffu)); // kind 3 = routed lights
+				atomicCAS(&mine->error, 0u, (3u << 28) | (r << 20) | (p.epoch & 0xfffffu)); // kind 3 = routed lights (or the live boxes between its two shares)
 				break;
 			}
 			__nanosleep(200);
 		}
 	}
 	__threadfence_system();
+}
+
+// ======================================================================================================
+// Between the two phases of a routed frame: the rounds counted so far have filled most clusters (on the reference scene at 16M
+// lights every cluster in front of slice 64 after 70,000 lights), and hier_alive_kernel has left, per group of this slab, whether
+// any cluster is still below its cap and the union box of those that are.  This kernel folds the live groups' boxes into
+// kSlabBoxes boxes -- by the side of the view axis their centre lies on: the clusters that stay alive longest sit at the left
+// and right edge of the lit region, and one box around both would span everything between them -- and stores them into every
+// rank's mailbox, followed by a release flag.  The rest of the frame's lights is routed against these boxes: a slab that is full
+// receives nothing any more, and the others only the lights that can still matter (exactly conservative, as every box test here).
+// One CTA.
+// ======================================================================================================
+__global__ void __launch_bounds__(256) slab_alive_kernel(const PeerParams p, uint32_t parity, const uint32_t* group_alive, const float* alive_union, uint32_t ncb)
+{
+	__shared__ float s_u[8][kSlabBoxes][6];
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const float kInf = __int_as_float(0x7f800000);
+	float lo[kSlabBoxes][3], hi[kSlabBoxes][3];
+#pragma unroll
+	for (uint32_t b = 0; b < kSlabBoxes; ++b)
+		for (int i = 0; i < 3; ++i)
+			lo[b][i] = kInf, hi[b][i] = -kInf;
+	for (uint32_t g = threadIdx.x; g < ncb; g += blockDim.x)
+	{
+		if (__ldcg(&group_alive[g]) == 0u)
+			continue;
+		const float4* u = reinterpret_cast<const float4*>(alive_union + static_cast<size_t>(g) * 8);
+		const float4 a = __ldcg(u), b4 = __ldcg(u + 1);
+		// a group holding a NaN box is (-inf, +inf): its centre is NaN, the comparison false, it lands in box 1 and makes that box pass everything
+		const uint32_t side = (a.x + b4.x) < 0.0f ? 0u : 1u;
+#pragma unroll
+		for (uint32_t b = 0; b < kSlabBoxes; ++b)
+			if (b == side)
+			{
+				lo[b][0] = fminf(lo[b][0], a.x), lo[b][1] = fminf(lo[b][1], a.y), lo[b][2] = fminf(lo[b][2], a.z);
+				hi[b][0] = fmaxf(hi[b][0], b4.x), hi[b][1] = fmaxf(hi[b][1], b4.y), hi[b][2] = fmaxf(hi[b][2], b4.z);
+			}
+	}
+#pragma unroll
+	for (uint32_t b = 0; b < kSlabBoxes; ++b)
+		for (int i = 0; i < 3; ++i)
+		{
+			const float l = warp_min_f(lo[b][i]), h = warp_max_f(hi[b][i]);
+			if (lane == 0)
+				s_u[warp][b][i] = l, s_u[warp][b][3 + i] = h;
+		}
+	__syncthreads();
+	if (threadIdx.x < p.world)
+	{
+		float* dst = &p.mail[threadIdx.x]->alive_box[parity][p.rank][0][0];
+		for (uint32_t b = 0; b < kSlabBoxes; ++b)
+		{
+			float l[3] = {kInf, kInf, kInf}, h[3] = {-kInf, -kInf, -kInf};
+			for (int w = 0; w < 8; ++w)
+				for (int i = 0; i < 3; ++i)
+					l[i] = fminf(l[i], s_u[w][b][i]), h[i] = fmaxf(h[i], s_u[w][b][3 + i]);
+			float* o = dst + b * 8;
+			o[0] = l[0], o[1] = l[1], o[2] = l[2], o[3] = 0.0f;
+			o[4] = h[0], o[5] = h[1], o[6] = h[2], o[7] = 0.0f;
+		}
+		__threadfence_system();
+		shard_st_release_sys(&p.mail[threadIdx.x]->alive_flag[parity][p.rank], static_cast<unsigned long long>(p.epoch) << 32);
+	}
 }
 
 cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges, uint32_t world, float* slab_box, cudaStream_t stream)
@@ -333,7 +419,7 @@ cudaError_t launch_slab_unions(const hvcf_aabb* aabbs, const uint32_t* d_ranges,
 
 cudaError_t launch_shard_route(const RouteParams& p, cudaStream_t stream)
 {
-	if (p.blocks == 0 || p.world == 0 || p.world > kMaxPeers || p.block_tiles == 0 || p.block_tiles > kMaxRouteBlockTiles ||
+	if (p.blocks == 0 || p.world == 0 || p.boxes == 0 || p.boxes > kSlabBoxes || p.world > kMaxPeers || p.block_tiles == 0 || p.block_tiles > kMaxRouteBlockTiles ||
 		(p.block_tiles & (p.block_tiles - 1u)))
 		return cudaErrorInvalidValue;
 	if (p.block_tiles > 8) // clusters of more than 8 CTAs are a per-kernel opt-in
@@ -361,9 +447,15 @@ cudaError_t launch_shard_route(const RouteParams& p, cudaStream_t stream)
 	return cudaLaunchKernelEx(&cfg, shard_route_kernel, p);
 }
 
-cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream)
+cudaError_t launch_shard_wait_routed(const PeerParams& p, uint32_t parity, cudaStream_t stream, uint32_t what)
 {
-	shard_wait_routed_kernel<<<1, 32, 0, stream>>>(p, parity);
+	shard_wait_routed_kernel<<<1, 32, 0, stream>>>(p, parity, what);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_slab_alive(const PeerParams& p, uint32_t parity, const uint32_t* group_alive, const float* alive_union, uint32_t ncb, cudaStream_t stream)
+{
+	slab_alive_kernel<<<1, 256, 0, stream>>>(p, parity, group_alive, alive_union, ncb);
 	return cudaGetLastError();
 }
 
@@ -372,6 +464,7 @@ cudaError_t preload_shard_kernels()
 	HVCF_PRELOAD(slab_unions_kernel);
 	HVCF_PRELOAD(shard_route_kernel);
 	HVCF_PRELOAD(shard_wait_routed_kernel);
+	HVCF_PRELOAD(slab_alive_kernel);
 	return cudaSuccess;
 }
 

@@ -16,6 +16,7 @@ pytestmark = pytest.mark.gpu
 
 GRID_A, SCREEN_A = (16, 9, 24), (2560, 1600)
 GRID_B, SCREEN_B = (32, 18, 48), (3840, 2160)
+INBOX_SEEN = {}
 
 
 @pytest.fixture(scope="module")
@@ -227,19 +228,31 @@ def test_row_shards_of_plain_contexts_concatenate(hv, oracle):
     assert np.array_equal(np.concatenate(got_idx), want_idx)
 
 
-@pytest.mark.parametrize("plan", ["8:1:2", "3:4:4", "4:16:8"])
+@pytest.mark.parametrize("two_phase", ["1", "0"])
+@pytest.mark.parametrize("plan", ["8:1:2", "3:4:4", "4:16:8", "5:8:2", "4:4:4:m0", "3:8:2:b8", "4:16:4:b16", "3:2:2:b1"])
 @pytest.mark.parametrize("grid,screen,n,cuts,cap", [(GRID_A, SCREEN_A, 70_000, (0, 15, 19, 24), 150), (GRID_B, SCREEN_B, 120_000, (0, 30, 40, 48), 150),
                                                    (GRID_A, SCREEN_A, 30_000, (0, 12, 24), 5)])
-def test_routed_frames_in_rounds(hv, torch_mod, oracle, monkeypatch, plan, grid, screen, n, cuts, cap):
+def test_routed_frames_in_rounds(hv, torch_mod, oracle, monkeypatch, plan, grid, screen, n, cuts, cap, two_phase):
     """the inbox of a routed frame is in light order, so it takes rounds like any other frame (hier_alive_kernel between the rounds'
-    binning launches); forced here on small frames: rounds : head tiles : growth.  Every rank's full grid equals the single context's."""
+    binning launches); forced here on small frames: rounds : head tiles : growth.  With three rounds or more (and the third one
+    starting at a whole route block) the frame is routed in two phases: the lights of the first two rounds against the slabs' union
+    boxes, the rest against the boxes of the clusters still below their cap, which every rank publishes in between
+    (slab_alive_kernel).  Every rank's full grid equals the single context's, two frames in a row (both mailbox parities)."""
+    monkeypatch.setenv("HVCF_ROUTE_TWO_PHASE", two_phase)
     ubo = oracle.camera_ubo(grid, screen)
     lights = oracle.init_lights(n, seed=21)
     monkeypatch.setenv("HVCF_ROUNDS", "0")
     want = run_single(hv, grid, ubo, lights, cap=cap)
-    rounds, head, growth = plan.split(":")
+    rounds, head, growth, opt = (plan.split(":") + [""])[:4]
     monkeypatch.setenv("HVCF_ROUNDS", rounds)
     monkeypatch.setenv("HVCF_ROUNDS_HEAD", head)
     monkeypatch.setenv("HVCF_ROUNDS_GROWTH", growth)
-    out, _ = run_routed(hv, torch_mod, grid, [ubo], lights, cuts, frames=2, cap=cap)
-    assert_all_equal(out, want, f"rounds {plan}")
+    if opt == "m0":     # one slot per inbox tile in every round (otherwise the late rounds keep one slot per route block)
+        monkeypatch.setenv("HVCF_ROUNDS_MACRO", "0")
+    block_tiles = int(opt[1:]) if opt.startswith("b") else 0
+    out, inbox = run_routed(hv, torch_mod, grid, [ubo], lights, cuts, frames=3, cap=cap, block_tiles=block_tiles)
+    assert_all_equal(out, want, f"rounds {plan} two_phase {two_phase}")
+    INBOX_SEEN.setdefault((plan, grid, n, cuts, cap), {})[two_phase] = sum(inbox)
+    seen = INBOX_SEEN[(plan, grid, n, cuts, cap)]
+    if len(seen) == 2:
+        assert seen["1"] <= seen["0"]   # live boxes never route more than the union boxes
