@@ -336,6 +336,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	do                                                                                      \
 	{                                                                                       \
 		cudaError_t e_ = cudaMalloc(reinterpret_cast<void**>(&(ptr)), (bytes) ? (bytes) : 16); \
+		c->device_bytes += (bytes) ? (bytes) : 16;                                           \
 		if (e_ != cudaSuccess)                                                              \
 		{                                                                                   \
 			free_ctx(c);                                                                    \
@@ -362,6 +363,18 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		HVCF_ALLOC(c->d_hlane_cluster, sizeof(uint32_t) * 32 * static_cast<size_t>(c->hp.ncb) * 8 * c->hp.K);
 		{
 			const size_t slots = static_cast<size_t>(c->hp.ncb) * c->tiles_cap;
+			{
+				// the survivor slots are DENSE -- groups x tiles x kBinCap records, whatever the filter lets through (64x36x96 clusters
+				// x 16M lights: 3.5 M slots, 32 GB) -- so say what is missing before cudaMalloc fails with a bare "out of memory"
+				const size_t need = slots * kBinCap * (sizeof(float4) + sizeof(uint16_t)) + slots * sizeof(uint32_t);
+				size_t free_b = 0, total_b = 0;
+				if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && need + (static_cast<size_t>(1) << 30) > free_b)
+				{
+					free_ctx(c);
+					return fail(HVCF_ERR_OUT_OF_MEMORY, "hvcf_create: the level-0 survivor slots of %u cluster groups x %u light tiles need %.1f GB, %.1f GB are free: "
+						"lower max_lights, or shard the grid (hvcf_create_sharded: a rank's slots shrink with its slab)", c->hp.ncb, c->tiles_cap, need / 1e9, free_b / 1e9);
+				}
+			}
 			HVCF_ALLOC(c->d_cb_union, sizeof(float) * 8 * c->hp.ncb);
 			HVCF_ALLOC(c->d_sb_union, sizeof(float) * 8 * (c->bin_ns ? c->bin_ns : 1));
 			HVCF_ALLOC(c->d_bin_count, sizeof(uint32_t) * slots);
@@ -712,6 +725,8 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 		}
 		ctx->h_tiles_total = tiles_total;
 		ctx->h_num_rounds = 0;
+		ctx->last_plan_flags = (ctx->h_pipe ? HVCF_PLAN_PIPELINED_WALK : 0u) | (ctx->h_parts > 1 ? HVCF_PLAN_SUBTILE_SEGMENTS : 0u) |
+			(routed ? HVCF_PLAN_TWO_LEVEL_BIN : 0u);
 		if (allow_rounds && ctx->h_parts == 1 && ctx->rounds_mode != 0 && tiles_total >= 2 &&
 			(ctx->rounds_mode > 0 || tiles_total >= ctx->rounds_min_tiles))
 		{
@@ -758,6 +773,9 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 			{
 				ctx->h_num_rounds = nr;
 				ctx->h_num_segs = seg;
+				ctx->last_plan_flags &= ~HVCF_PLAN_PIPELINED_WALK;
+				for (uint32_t r = 0; r < nr; ++r)
+					ctx->last_plan_flags |= (ctx->h_rounds[r].pipe ? HVCF_PLAN_PIPELINED_WALK : 0u) | (ctx->h_rounds[r].macro_shift ? HVCF_PLAN_MACRO_TILES : 0u);
 			}
 		}
 		if (ctx->h_num_rounds < 2 && hier_num_chunks(ctx->h_num_segs) > kHMaxChunks)
@@ -801,6 +819,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 		q.zero = zero;
 		q.zero_words = zero_words;
 		HVCF_CUDA(launch_hier_xbin(q, end_padded / kTileLights, s));
+		ctx->last_plan_flags |= HVCF_PLAN_FUSED_BIN;
 		ctx->range_cleared = true;
 		ctx->range_transformed = ctx->range_binned = end_padded;
 		++ctx->open_launches;
@@ -858,6 +877,7 @@ static int hier_range(hvcf_ctx* ctx, uint32_t frame, uint32_t begin, uint32_t en
 			const bool two_level = ctx->bin_ns && (ctx->bin2_mode > 0 || ctx->hp.ncb >= kBin2MinGroups ||
 				static_cast<uint64_t>(ctx->hp.ncb) * n >= (1ull << 28));
 			b.ns = two_level ? ctx->bin_ns : 0u;
+			ctx->last_plan_flags |= two_level ? HVCF_PLAN_TWO_LEVEL_BIN : 0u;
 			HVCF_CUDA(launch_hier_bin(b, (end_padded - begin) / kTileLights, s));
 			++ctx->open_launches;
 		}
@@ -1675,6 +1695,21 @@ int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
 	out->prefilter_tests = ds.prefilter_tests;
 	out->bin_tests = ds.bin_tests;
 	out->write_pass_tests = ds.write_tests;
+	{
+		const size_t C = ctx->cluster_total;
+		const uint64_t ref_bytes = sizeof(hvcf_light_data) * static_cast<uint64_t>(ctx->max_lights) + (sizeof(hvcf_aabb) + sizeof(hvcf_light_cell)) * C +
+			sizeof(uint32_t) * C * ctx->cap + (sizeof(uint32_t) + sizeof(hvcf_cluster_forward_ubo)) * ctx->frame_count;
+		out->device_bytes = ctx->device_bytes;
+		out->scratch_bytes = ctx->device_bytes > ref_bytes ? ctx->device_bytes - ref_bytes : 0;
+	}
+	if (ctx->hier)
+	{
+		out->plan_groups = ctx->hp.ncb;
+		out->plan_blocks_per_program = ctx->hp.K;
+		out->plan_segments = ctx->h_num_segs;
+		out->plan_rounds = ctx->h_num_rounds >= 2 ? ctx->h_num_rounds : 1;
+		out->plan_flags = ctx->last_plan_flags;
+	}
 	out->total_indices = ds.total_indices;
 	out->overflow_clusters = ds.overflow_clusters;
 	out->kernel_launches = ctx->last_launches[frame];

@@ -216,6 +216,8 @@ struct hvcf_ctx
 	bool aabb_dirty = true;
 	bool have_aabb_key = false;
 	float aabb_key[16 + 2]{}; // inverse projection + near/far of the last generated AABBs
+	uint64_t device_bytes = 0;           // every cudaMalloc of the context (hvcf_stats)
+	uint32_t last_plan_flags = 0;        // HVCF_PLAN_* of the last frame
 	uint32_t last_num_segs = 0;
 	uint32_t last_launches[8]{}; // per frame
 	bool timing = false;

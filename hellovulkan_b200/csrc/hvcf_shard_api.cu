@@ -140,6 +140,8 @@ int hvcf_create_sharded(const hvcf_config* config, const hvcf_shard_desc* desc, 
 		return fail(e == cudaErrorMemoryAllocation ? HVCF_ERR_OUT_OF_MEMORY : HVCF_ERR_CUDA, "hvcf_create_sharded: inbox of %zu bytes: %s",
 			2 * sh.parity_bytes, cudaGetErrorString(e));
 	}
+	c->device_bytes += 2 * sh.parity_bytes + sizeof(ranges) + sizeof(float) * 8 * world + sizeof(uint32_t) * tiles_phys +
+		sizeof(uint32_t) * static_cast<size_t>(c->cluster_count) * c->cap + 64 + sizeof(uint16_t) * tiles_phys * kTileLights + sizeof(uint32_t) * blocks_phys;
 	sh.on = true;
 	c->num_lights = desc->total_lights; // the frame is over all the lights of the scene; this rank holds its own range of them
 	c->aabb_dirty = true;
@@ -301,6 +303,7 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 							HVCF_CUDA(cudaEventCreate(&e));
 					HVCF_CUDA(cudaEventRecord(ctx->kev_phase2[frame][0], s));
 				}
+				ctx->last_plan_flags |= HVCF_PLAN_TWO_PHASE_ROUTE;
 				HVCF_CUDA(launch_slab_alive(pp, parity, ctx->bin_alive, ctx->d_alive_union, ctx->hp.ncb, s));
 				HVCF_CUDA(launch_shard_wait_routed(pp, parity, s, 1u));
 				const int prc = route(head_end, own1, 1u);

@@ -75,7 +75,10 @@ class PushConstPBR(ctypes.Structure):
 class Stats(ctypes.Structure):
     _fields_ = [("nominal_tests", ctypes.c_uint64), ("executed_tests", ctypes.c_uint64), ("prefilter_tests", ctypes.c_uint64),
                 ("total_indices", ctypes.c_uint32), ("overflow_clusters", ctypes.c_uint32), ("kernel_launches", ctypes.c_uint32),
-                ("reserved", ctypes.c_uint32), ("bin_tests", ctypes.c_uint64), ("write_pass_tests", ctypes.c_uint64)]
+                ("reserved", ctypes.c_uint32), ("bin_tests", ctypes.c_uint64), ("write_pass_tests", ctypes.c_uint64),
+                ("device_bytes", ctypes.c_uint64), ("scratch_bytes", ctypes.c_uint64), ("plan_groups", ctypes.c_uint32),
+                ("plan_blocks_per_program", ctypes.c_uint32), ("plan_segments", ctypes.c_uint32), ("plan_rounds", ctypes.c_uint32),
+                ("plan_flags", ctypes.c_uint32), ("reserved2", ctypes.c_uint32)]
 
 
 EXPORTS = [
@@ -669,7 +672,7 @@ class Context:
     def stats(self, frame=0, stream=None):
         s = Stats()
         _check(self.lib.hvcf_get_stats(self.handle, frame, ctypes.byref(s), stream))
-        return {k: int(getattr(s, k)) for k, _ in Stats._fields_ if k != "reserved"}
+        return {k: int(getattr(s, k)) for k, _ in Stats._fields_ if not k.startswith("reserved")}
 
 
 class PinnedBuffer:

@@ -111,7 +111,23 @@ typedef struct hvcf_stats
 	uint32_t reserved;
 	uint64_t bin_tests;        /* the level-0 (binning kernel) part of prefilter_tests */
 	uint64_t write_pass_tests; /* union + exact tests the write pass repeats; in neither counter above */
+	/* what the context holds on the device, and the plan the frame ran with (nothing here depends on the frame's lights) */
+	uint64_t device_bytes;     /* every cudaMalloc of the context */
+	uint64_t scratch_bytes;    /* the library-internal part: everything but lights, AABBs, cells, indices, counters and UBOs.  Mostly the
+	                              level-0 survivor slots: groups x light tiles x 512 records x 18 B, committed whatever the filter lets through */
+	uint32_t plan_groups;      /* cluster groups (level 0) of the shard */
+	uint32_t plan_blocks_per_program; /* K: 32-cluster blocks per warp program */
+	uint32_t plan_segments;    /* light segments of the frame */
+	uint32_t plan_rounds;      /* rounds the frame was binned and counted in (1 = a single launch each) */
+	uint32_t plan_flags;       /* HVCF_PLAN_* */
+	uint32_t reserved2;
 } hvcf_stats;
+#define HVCF_PLAN_TWO_LEVEL_BIN 1u  /* level 0 through super-groups (hier_bin2_kernel) */
+#define HVCF_PLAN_FUSED_BIN 2u      /* transform + level 0 in one kernel (hier_xbin_kernel) */
+#define HVCF_PLAN_PIPELINED_WALK 4u /* some segment walks its slots with the cp.async double buffer */
+#define HVCF_PLAN_SUBTILE_SEGMENTS 8u /* a tile's slot is cut into several light segments */
+#define HVCF_PLAN_MACRO_TILES 16u   /* late rounds keep one slot per group and several tiles (or route block) */
+#define HVCF_PLAN_TWO_PHASE_ROUTE 32u /* routed frame: second share routed against the slabs' live boxes */
 
 HVCF_API const char* hvcf_last_error_string(void);
 HVCF_API const char* hvcf_version(void);

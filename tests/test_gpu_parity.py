@@ -408,7 +408,9 @@ def test_rounds_give_identical_bytes(hv, oracle, monkeypatch, name, n, cap, z, p
         assert out[2] == ref[2]
         assert out[0].tobytes() == ref[0].tobytes() and out[1].tobytes() == ref[1].tobytes()
     tiles = (n + 1023) // 1024
+    assert one[3]["plan_rounds"] == 1 and one[3]["device_bytes"] > one[3]["scratch_bytes"] > 0
     if tiles >= 2 * int(head):
+        assert got[3]["plan_rounds"] >= 2 and got[3]["plan_segments"] >= got[3]["plan_rounds"]
         assert got[3]["kernel_launches"] > one[3]["kernel_launches"]          # the rounds really ran
         assert macro or got[3]["bin_tests"] <= one[3]["bin_tests"]
 

@@ -33,7 +33,7 @@ def test_every_declared_symbol_is_exported(hv):
 
 def test_struct_sizes_match_header(hv):
     assert ctypes.sizeof(hv.Config) == 64
-    assert ctypes.sizeof(hv.Stats) == 56
+    assert ctypes.sizeof(hv.Stats) == 56 + 16 + 6 * 4
     assert ctypes.sizeof(hv.Buffers) == 6 * 8 + 8 + 4 * 4
     assert hv.LIGHT_DT.itemsize == 48 and hv.AABB_DT.itemsize == 32 and hv.CELL_DT.itemsize == 8
 
