@@ -67,7 +67,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C16M", choices=sorted(WORKLOADS))
-    ap.add_argument("--balance-iters", type=int, default=6, help="N > 1: slab re-cuts from measured per-rank kernel times")
+    ap.add_argument("--balance-iters", type=int, default=10, help="N > 1: slab re-cuts from measured per-rank kernel times")
     ap.add_argument("--block-tiles", type=int, default=0, help="tiles per route block (0 = library default)")
     ap.add_argument("--z-cuts", default="", help="N > 1: comma-separated z cuts (N + 1 numbers) instead of balancing")
     ap.add_argument("--row-cuts", default="", help="N > 1: comma-separated cuts in cluster rows (row = y + z * Y) instead of balancing")
@@ -88,6 +88,25 @@ def host_threads():
         return max(1, len(os.sched_getaffinity(0)))
     except AttributeError:
         return max(1, os.cpu_count() or 1)
+
+
+def pin_to_gpu_node(local):
+    """N > 1: keep this rank's host thread (and with it the pinned buffers it first touches) on the CPU cores NVML reports as
+    local to its GPU, so that eight ranks' H2D / D2H copies do not all cross the socket link.  Returns the number of cores kept,
+    or None when NVML has nothing to say (then the affinity stays as it was)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 64) + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        want = cpus & os.sched_getaffinity(0)
+        if want:
+            os.sched_setaffinity(0, want)
+            return len(want)
+    except Exception:
+        pass
+    return None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -469,7 +488,7 @@ def full_grid_hash(torch, hvcf, ctx, frame, dev, sp):
 def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, flush):
     """The headline at N > 1: hvcf_cull_routed (clusters sharded by z-slab, lights owned in shards)."""
     import ctypes
-    from hellovulkan_b200.sharded import slice_touch_counts, cuts_from_cost, balance_slabs
+    from hellovulkan_b200.sharded import slice_touch_counts, cuts_from_cost, CutSearch
     grid, screen, n = WORKLOADS[args.workload]
     C = grid[0] * grid[1] * grid[2]
     stream = torch.cuda.current_stream()
@@ -526,7 +545,7 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
         touch = slice_touch_counts(ubos[0], all_lights, stride=16).astype(np.float64)
         cost_u = np.repeat((touch + 0.05 * touch.mean()) / upz, upz)
         cuts_u = cuts_from_cost(cost_u, world)
-        best = None
+        search = CutSearch(Z * upz, world)
         for it in range(max(0, args.balance_iters)):
             ctx = make([c * unit for c in cuts_u], ktimes=True)
             for f in range(4):
@@ -537,24 +556,15 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
             own = float(sum(kt[1:]))                       # bin + count + finalize + write: this rank's own work, no waiting
             times = allgather(own)
             history.append({"row_cuts": [c * unit for c in cuts_u], "own_kernels_ms": [round(t, 4) for t in times], "peer_error": err})
-            if best is None or max(times) < best[0]:
-                best = (max(times), list(cuts_u))
+            search.add(cuts_u, times)
             if max(times) <= 1.04 * (sum(times) / world):
                 break
-            slabs = [(cuts_u[r], cuts_u[r + 1]) for r in range(world)]
-            new = balance_slabs(slabs, times)
-            if it >= 2:   # damp late moves: halfway between the current and the proposed cuts
-                new = [((a0 + a1 + 1) // 2, (b0 + b1 + 1) // 2) for (a0, b0), (a1, b1) in zip(slabs, new)]
-            new_cuts = [0] + [max(a, 1) for a, _ in new[1:]] + [Z * upz]
-            for k in range(1, world):
-                new_cuts[k] = max(new_cuts[k], new_cuts[k - 1] + 1)
-            for k in range(world - 1, 0, -1):
-                new_cuts[k] = min(new_cuts[k], new_cuts[k + 1] - 1)
+            new_cuts = search.next_cuts()
             if new_cuts == cuts_u:
                 break
             cuts_u = new_cuts
-        if best is not None:
-            cuts_u = best[1]
+        if search.best is not None:
+            cuts_u = search.best[1]
     cuts = [c * unit for c in cuts_u]              # in cluster rows
     ctx = make(cuts)
     out = {"row_cuts": list(cuts), "rows_per_slice": Y, "balance_iterations": history}
@@ -919,6 +929,7 @@ def run_ours(args):
         log(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}; using WORLD_SIZE")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_cores = pin_to_gpu_node(local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         opts = dist.ProcessGroupNCCL.Options()
@@ -1064,7 +1075,7 @@ def run_ours(args):
         "config": {"workload": args.workload, "grid": list(grid), "screen": list(screen), "lights": n,
                    "max_lights_per_cluster": 150, "light_distribution": "AppPBRClusterForward::InitLights, mt19937(12345)",
                    "l2": f"flushed between steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed); the inputs are larger than L2 anyway",
-                   "parallelism": parallelism,
+                   "parallelism": parallelism, "host_cores_per_rank": numa_cores,
                    "tests": "nominal = clusters x lights; executed (early exit at 150 hits, LightCulling.comp:71) under roofline"},
         "total_indices": total_idx, "e2e": e2e, "gpu_launches": launches_per_step * K, "gpu_launches_per_step": launches_per_step,
         "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "impl": "ours", "detail": detail,

@@ -78,6 +78,49 @@ def balance_slabs(slabs, times, min_slices=1):
     return [(cuts[k], cuts[k + 1]) for k in range(world)]
 
 
+class CutSearch:
+    """Iterative slab balancing from measured per-rank costs, without assuming anything about the cost inside a slab.
+
+    Every measurement (cuts, times) gives the cumulative share of the cost at each of its cuts.  The shares of ALL measurements so
+    far are kept as knots of one piecewise-linear, monotone estimate of the cumulative cost over the rows, and the next cuts are its
+    k/N quantiles.  New cuts land where the cost is dense, so the estimate refines itself exactly where a piecewise-constant
+    density (balance_slabs) overshoots -- a frame counted in rounds has nearly all of its late cost in the few slices at the edge
+    of the lit region.  Pure host logic: unit-tested on the CPU (tests/test_sharded_host_logic.py)."""
+
+    def __init__(self, total_units: int, world: int):
+        self.total, self.world = int(total_units), int(world)
+        self.samples = {}     # unit position -> [cumulative share]
+        self.best = None      # (max time, cuts)
+
+    def add(self, cuts, times):
+        times = [max(float(t), 1e-9) for t in times]
+        if self.best is None or max(times) < self.best[0]:
+            self.best = (max(times), list(cuts))
+        cum = np.cumsum(times) / sum(times)
+        for k in range(1, self.world):
+            self.samples.setdefault(int(cuts[k]), []).append(float(cum[k - 1]))
+
+    def next_cuts(self):
+        pos = sorted(self.samples)
+        xs = np.array([0] + pos + [self.total], np.float64)
+        ys = np.array([0.0] + [float(np.mean(self.samples[p])) for p in pos] + [1.0])
+        ys = np.maximum.accumulate(ys)                      # measurements of different cuts may disagree slightly
+        cuts = [0]
+        for k in range(1, self.world):
+            t = k / self.world
+            i = int(np.searchsorted(ys, t, side="left"))
+            i = min(max(i, 1), len(xs) - 1)
+            x0, x1, y0, y1 = xs[i - 1], xs[i], ys[i - 1], ys[i]
+            x = x1 if y1 <= y0 else x0 + (x1 - x0) * (t - y0) / (y1 - y0)
+            cuts.append(int(round(x)))
+        cuts.append(self.total)
+        for k in range(1, self.world):
+            cuts[k] = max(cuts[k], cuts[k - 1] + 1)
+        for k in range(self.world - 1, 0, -1):
+            cuts[k] = min(cuts[k], cuts[k + 1] - 1)
+        return cuts
+
+
 class DevicePtrView:
     """Zero-copy torch view of a raw device pointer (via __cuda_array_interface__)."""
 

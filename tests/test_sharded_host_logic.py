@@ -74,3 +74,26 @@ def test_culler_rejects_unknown_modes():
     with pytest.raises(ValueError):
         sc.frame_pipelined(0, 10)                            # needs the peer exchange
     assert sc.phase_ms() == {}
+
+
+def test_cut_search_converges_on_a_peaked_cost():
+    """CutSearch (bench.py's slab balancing): the cost of a frame counted in rounds sits in a few rows; quantiles of the accumulated
+    cumulative-share knots find balanced cuts where one piecewise-constant re-cut per iteration keeps overshooting."""
+    from hellovulkan_b200.sharded import CutSearch
+    rows = 864
+    dens = np.full(rows, 0.2)
+    dens[560:600] = 30.0            # the edge of the lit region
+    dens[600:640] = 6.0
+    cum = np.concatenate([[0.0], np.cumsum(dens)])
+    world = 8
+    cuts = [rows * k // world for k in range(world + 1)]
+    search = CutSearch(rows, world)
+    worst = []
+    for _ in range(10):
+        times = [cum[cuts[k + 1]] - cum[cuts[k]] for k in range(world)]
+        worst.append(max(times) / (sum(times) / world))
+        search.add(cuts, times)
+        cuts = search.next_cuts()
+        assert cuts[0] == 0 and cuts[-1] == rows and all(b > a for a, b in zip(cuts, cuts[1:]))
+    assert worst[0] > 4.0 and min(worst) < 1.25, worst
+    assert search.best[0] == min(max(cum[c[k + 1]] - cum[c[k]] for k in range(world)) for c in [search.best[1]])
