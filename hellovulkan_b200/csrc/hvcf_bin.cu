@@ -20,6 +20,18 @@
 namespace hvcf
 {
 
+// Loads of the level-0 slots (bin_count / bin_rec / bin_idx, unit_any) in the count / write passes.  They were written by an
+// EARLIER kernel of the same programmatic-dependent-launch chain and are read only after griddepcontrol.wait, i.e. after that
+// kernel has completed and its stores are visible; a grid's L1 starts invalidated and no line of these buffers can be filled before
+// the wait, so the read-only path (ld.global.nc, L1-cached) cannot return a stale line.  It matters: the four warp programs of a
+// CTA belong to one group and read the same slot records (A65k 0.0446 ms per frame against 0.0511 with ld.global.cg).  The PTX
+// wording ("read-only for the lifetime of the kernel") is stricter than that argument; -DHVCF_CHAIN_LDCG builds the L2-only loads.
+#ifdef HVCF_CHAIN_LDCG
+#define HVCF_CHAIN_LD(p) __ldcg(p)
+#else
+#define HVCF_CHAIN_LD(p) __ldg(p)
+#endif
+
 constexpr uint32_t kBinWarps = 8;  // hier_bin_kernel: groups per CTA (one per warp)
 constexpr uint32_t kMainWarps = 4; // hier2_kernel: warp programs per CTA
 
@@ -314,7 +326,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	// program's counts (hier_finalize_kernel stops at the round before which a cluster was full)
 	if (p.round_alive && !p.trace && __ldcg(&p.round_alive[cb]) == 0u)
 		return;
-	if (WRITE && seg != 0 && !p.trace && __ldcg(&p.unit_any[any_slot(seg, unit)]) == 0u)
+	if (WRITE && seg != 0 && !p.trace && HVCF_CHAIN_LD(&p.unit_any[any_slot(seg, unit)]) == 0u)
 		return;
 	// count pass: a group whose level-0 slots are empty for every tile of this segment has nothing to test -- zero counts,
 	// no boxes, no early-exit counters, no union reductions (HVCF_EMPTY_SKIP=0 at build time switches the check off)
@@ -327,13 +339,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 		uint32_t some = 0;
 		if (parts > 1)
 		{
-			const uint32_t n0 = __ldcg(&p.bin_count[d0]);
+			const uint32_t n0 = HVCF_CHAIN_LD(&p.bin_count[d0]);
 			const uint32_t nb = n0 > kBinCap ? (INBOX ? (__ldcg(&p.tile_cnt[t_begin]) + 63u) / 64u : kTileGroups) : (n0 + 63) / 64;
 			some = (part + 1) * nb / parts > part * nb / parts ? 1u : 0u;
 		}
 		else // (macro tiles: only the count of a macro tile's first tile means anything)
 			for (uint32_t t = lane << p.macro_shift; t < ntiles; t += 32u << p.macro_shift)
-				some |= __ldcg(&p.bin_count[d0 + t]);
+				some |= HVCF_CHAIN_LD(&p.bin_count[d0 + t]);
 		if (!__any_sync(0xffffffffu, some != 0))
 		{
 #pragma unroll
@@ -593,7 +605,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				{
 					cnt_chunk = mi >> 5;
 					const uint32_t tt = (cnt_chunk * 32 + lane) << ms;
-					my_cnt = tt < ntiles ? __ldcg(&p.bin_count[desc0 + tt]) : 0u;
+					my_cnt = tt < ntiles ? HVCF_CHAIN_LD(&p.bin_count[desc0 + tt]) : 0u;
 				}
 				it_n0 = __shfl_sync(0xffffffffu, my_cnt, mi & 31u);
 				if (it_n0)
@@ -685,7 +697,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 	for (uint32_t tb = 0; tb < ntiles && !warp_done; tb += 32)
 	{
 		// survivor counts of the next 32 tiles in one coalesced load
-		const uint32_t my_cnt = tb + lane < ntiles ? __ldcg(&p.bin_count[desc0 + tb + lane]) : 0u;
+		const uint32_t my_cnt = tb + lane < ntiles ? HVCF_CHAIN_LD(&p.bin_count[desc0 + tb + lane]) : 0u;
 		const uint32_t tn = min(32u, ntiles - tb);
 		for (uint32_t ti = 0; ti < tn && !warp_done; ++ti)
 		{
@@ -730,7 +742,7 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 				}
 				else if (raw)
 				{
-					const float4 a = __ldcg(lv + bi * 64 + lane), b = __ldcg(lv + bi * 64 + 32 + lane);
+					const float4 a = HVCF_CHAIN_LD(lv + bi * 64 + lane), b = HVCF_CHAIN_LD(lv + bi * 64 + 32 + lane);
 					r0 = make_float4(a.x, a.z, b.x, b.z);
 					r1 = make_float4(a.y, a.w, b.y, b.w);
 					id0 = bi * 64 + lane;
@@ -743,13 +755,13 @@ __global__ void __launch_bounds__(kMainWarps * 32) hier2_kernel(const HierParams
 					id0 = id1 = 0;
 					if (i0 < n0)
 					{
-						r0 = __ldcg(p.bin_rec + slot + i0);
-						id0 = __ldcg(p.bin_idx + slot + i0);
+						r0 = HVCF_CHAIN_LD(p.bin_rec + slot + i0);
+						id0 = HVCF_CHAIN_LD(p.bin_idx + slot + i0);
 					}
 					if (i1 < n0)
 					{
-						r1 = __ldcg(p.bin_rec + slot + i1);
-						id1 = __ldcg(p.bin_idx + slot + i1);
+						r1 = HVCF_CHAIN_LD(p.bin_rec + slot + i1);
+						id1 = HVCF_CHAIN_LD(p.bin_idx + slot + i1);
 					}
 				}
 				batch(r0, r1, id0, id1, tile_base, my_rec, my_idx, false);
