@@ -455,7 +455,10 @@ int hvcf_set_lights(hvcf_ctx* ctx, const void* lights, uint32_t n, int src_is_de
 	ctx->num_lights = n;
 	ctx->bound_lights = nullptr;
 	if (ctx->anim_len) // new lights, new rest positions
+	{
 		HVCF_CUDA(launch_capture_base_y(ctx->d_lights, n, ctx->d_base_y, static_cast<cudaStream_t>(stream)));
+		ctx->base_y_count = n;
+	}
 	return HVCF_OK;
 }
 
@@ -465,8 +468,18 @@ int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_bind_lights: null context");
 	if (n > ctx->max_lights)
 		return fail(HVCF_ERR_CAPACITY, "hvcf_bind_lights: %u lights > max_lights %u", n, ctx->max_lights);
+	const bool changed = ctx->bound_lights != static_cast<const hvcf_light_data*>(device_lights) || n > ctx->base_y_count;
 	ctx->bound_lights = static_cast<const hvcf_light_data*>(device_lights);
 	ctx->num_lights = device_lights ? n : 0;
+	// device-side animation moves the lights about their REST height: a new buffer, or more lights than were captured, needs a new
+	// capture (on the legacy default stream, which orders itself against every blocking stream).  The moved
+	// positions are written back into the bound buffer, as UpdateLightPosition writes them into the SSBO.
+	if (ctx->anim_len && device_lights && n && changed)
+	{
+		HVCF_CUDA(cudaSetDevice(ctx->device));
+		HVCF_CUDA(launch_capture_base_y(ctx->bound_lights, n, ctx->d_base_y, nullptr));
+		ctx->base_y_count = n;
+	}
 	return HVCF_OK;
 }
 
@@ -563,6 +576,7 @@ int hvcf_set_light_animation(hvcf_ctx* ctx, const float* table, uint32_t table_l
 	HVCF_CUDA(cudaStreamSynchronize(s)); // `table` may be pageable and go away
 	const hvcf_light_data* lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
 	HVCF_CUDA(launch_capture_base_y(lights, ctx->num_lights, ctx->d_base_y, s));
+	ctx->base_y_count = ctx->num_lights;
 	ctx->anim_len = table_len;
 	ctx->anim_amplitude = amplitude;
 	return HVCF_OK;

@@ -181,6 +181,7 @@ struct hvcf_ctx
 	// device-side light animation (hvcf_set_light_animation) and batched position updates (hvcf_update_lights)
 	float* d_anim_table = nullptr;
 	float* d_base_y = nullptr;                 // [max_lights]
+	uint32_t base_y_count = 0;                 // lights whose rest height is in d_base_y
 	uint32_t anim_len = 0;                     // 0 = off
 	float anim_amplitude = 0.0f;
 	uint32_t anim_step[8]{};                   // per frame slot

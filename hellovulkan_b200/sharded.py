@@ -154,6 +154,11 @@ class HvcfEngine:
         self.base = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.num_lights = 0
 
+    def _s(self):
+        """torch's CURRENT stream: every hvcf call of the engine goes where the surrounding torch work goes (copies into the
+        light buffer, NCCL waits, phase-timing events), also under torch.cuda.stream(...)."""
+        return torch.cuda.current_stream(self.device).cuda_stream
+
     def set_num_lights(self, n):
         # the light bytes already sit in self.lights (broadcast target); just tell the context how many
         b = self.ctx.buffers()
@@ -161,21 +166,21 @@ class HvcfEngine:
         self.num_lights = n
 
     def set_ubo(self, frame, ubo):
-        self.ctx.set_ubo(frame, ubo)
+        self.ctx.set_ubo(frame, ubo, self._s())
 
     def cull_begin(self, frame):
-        self.ctx.cull_begin(frame)
+        self.ctx.cull_begin(frame, self._s())
 
     def cull_finish(self, frame, base: torch.Tensor):
         self.base.copy_(base.view(1))
-        self.ctx.cull_finish(frame, self.base.data_ptr())
+        self.ctx.cull_finish(frame, self.base.data_ptr(), self._s())
 
     # -- hvcf_cull_begin in pieces, for pipelining the light broadcast --
     def cull_begin_range(self, frame, begin, end, flags=0):
-        self.ctx.cull_begin_range(frame, begin, end, flags)
+        self.ctx.cull_begin_range(frame, begin, end, flags, self._s())
 
     def transform_lights(self, frame, begin, end):
-        self.ctx.transform_lights(frame, begin, end)
+        self.ctx.transform_lights(frame, begin, end, self._s())
 
     def lights_view(self):
         if not hasattr(self, "_lights_view"):
@@ -196,19 +201,19 @@ class HvcfEngine:
         self.ctx.peer_detach()
 
     def peer_exchange_totals(self):
-        self.ctx.peer_exchange_totals()
+        self.ctx.peer_exchange_totals(self._s())
 
     def cull_finish_peer(self, frame):
-        self.ctx.cull_finish(frame, self._index_base_ptr)
+        self.ctx.cull_finish(frame, self._index_base_ptr, self._s())
 
     def peer_push_grid(self):
-        self.ctx.peer_push_grid()
+        self.ctx.peer_push_grid(self._s())
 
     def peer_wait_grid(self):
-        self.ctx.peer_wait_grid()
+        self.ctx.peer_wait_grid(self._s())
 
     def cull_sharded(self, frame):
-        self.ctx.cull_sharded(frame)
+        self.ctx.cull_sharded(frame, self._s())
 
     def peer_status(self):
         return self.ctx.peer_status()

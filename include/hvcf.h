@@ -298,7 +298,9 @@ HVCF_API int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void
  * the descriptor write of binding 1 in PipelineLightCulling::CreateDescriptor
  * (PipelineLightCulling.cpp:121-141).  The caller keeps ownership; hvcf_cull reads it in place,
  * so ResourcesLight::UpdateLightPosition writes are seen by the next frame without a copy.
- * NULL rebinds the context's own buffer. */
+ * NULL rebinds the context's own buffer.  The buffer is read-only to the library EXCEPT with device-side light animation on
+ * (hvcf_set_light_animation): the moved positions are then written back into it, as UpdateLightPosition writes them into the
+ * SSBO, and binding a new buffer (or more lights) re-captures the rest heights on the default stream. */
 HVCF_API int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n);
 
 /* Raw device buffers for the C++ mirror of VulkanBuffer (include/hv/Context.h):
