@@ -118,6 +118,12 @@ static void free_ctx(hvcf_ctx* c)
 		for (auto& e : fe)
 			if (e)
 				cudaEventDestroy(e);
+	for (auto& st : c->write_streams)
+		if (st)
+			cudaStreamDestroy(st);
+	for (auto& e : c->write_ev)
+		if (e)
+			cudaEventDestroy(e);
 	for (auto& fe : c->kev_phase2)
 		for (auto& e : fe)
 			if (e)
@@ -317,6 +323,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->rounds_head = static_cast<uint32_t>(env_int("HVCF_ROUNDS_HEAD", 64));
 		c->rounds_growth = static_cast<uint32_t>(env_int("HVCF_ROUNDS_GROWTH", 8));
 		c->rounds_macro = env_int("HVCF_ROUNDS_MACRO", -1);
+		c->write_fork = env_int("HVCF_WRITE_FORK", 1) != 0;
 		c->rounds_late_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_LATE_SEGS", 32));
 		c->rounds_early_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_EARLY_SEGS", 16));
 		if (c->rounds_early_segs == 0)
@@ -1211,7 +1218,26 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 		hp.index_base = d_index_base;
 		if (ctx->h_num_rounds >= 2)
 		{
-			// one launch per round (their segments differ in length, and long ones take the pipelined walk); independent of each other
+			// one launch per round (their segments differ in length, and long ones take the pipelined walk).  They are independent of
+			// each other and the late ones are latency-bound (few live groups, long walks), so the rounds after the first go to side
+			// streams and run UNDER the first round's launch, which writes most of the frame's indices: fork after finalize, join
+			// before the call returns to the caller's stream (grid C x 16M: 198 + 69 + 74 + 75 us in a row -> about the first alone)
+			cudaStream_t s0 = static_cast<cudaStream_t>(stream);
+			// (not for shard contexts that share this process with their peers -- the test harness of hvcf_peer_attach_local: four
+			// streams per context exceed the device's hardware queues, and a write pass queued behind another shard's spinning wait
+			// kernel is a false dependency that only the 4 s bound breaks)
+			const bool fork = ctx->write_fork && ctx->h_num_rounds >= 2 && !(ctx->peer.world > 1 && !ctx->peer_ipc);
+			if (fork)
+			{
+				if (!ctx->write_ev[0])
+				{
+					for (auto& st : ctx->write_streams)
+						HVCF_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+					for (auto& e : ctx->write_ev)
+						HVCF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+				}
+				HVCF_CUDA(cudaEventRecord(ctx->write_ev[0], s0));
+			}
 			for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
 			{
 				const hvcf_ctx::Round& rd = ctx->h_rounds[r];
@@ -1220,8 +1246,21 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 				hp.tiles_per_seg = rd.tiles_per_seg, hp.pipe = rd.pipe;
 				hp.macro_shift = rd.macro_shift;
 				hp.round_alive = r > 0 ? ctx->d_group_alive + static_cast<size_t>(r) * ctx->hp.ncb : nullptr;
-				HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), true, hp, static_cast<cudaStream_t>(stream)));
+				cudaStream_t sr = s0;
+				if (fork && r > 0)
+				{
+					sr = ctx->write_streams[(r - 1) % 3];
+					if (r <= 3)
+						HVCF_CUDA(cudaStreamWaitEvent(sr, ctx->write_ev[0], 0));
+				}
+				HVCF_CUDA(launch_hier2(static_cast<int>(ctx->hp.K), true, hp, sr));
 			}
+			if (fork)
+				for (uint32_t i = 0; i < 3 && i + 1 < ctx->h_num_rounds; ++i)
+				{
+					HVCF_CUDA(cudaEventRecord(ctx->write_ev[1 + i], ctx->write_streams[i]));
+					HVCF_CUDA(cudaStreamWaitEvent(s0, ctx->write_ev[1 + i], 0));
+				}
 			ctx->last_launches[frame] += ctx->h_num_rounds - 1;
 		}
 		else

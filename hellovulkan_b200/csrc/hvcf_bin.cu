@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kBinWarps * 32) hier_bin_kernel(const BinParam
 	if (cb < p.ncb)
 	{
 		const float4* u = reinterpret_cast<const float4*>(p.cb_union + static_cast<size_t>(cb) * 8); // (rounds: written by hier_alive_kernel just before)
-		const float4 a = __ldcg(u), b = __ldcg(u + 1);
+		const float4 a = p.group_alive ? __ldcg(u) : __ldg(u), b = p.group_alive ? __ldcg(u + 1) : __ldg(u + 1);
 		lo[0] = a.x, lo[1] = a.y, lo[2] = a.z;
 		hi[0] = b.x, hi[1] = b.y, hi[2] = b.z;
 	}

@@ -121,6 +121,9 @@ struct hvcf_ctx
 	uint32_t h_num_rounds = 0;
 	int rounds_mode = -1;                    // HVCF_ROUNDS: -1 = by the number of tiles, 0 = never, n > 0 = at most n rounds whenever the frame has two tiles or more
 	uint32_t rounds_min_tiles = 2048, rounds_head = 64, rounds_growth = 8; // HVCF_ROUNDS_MIN_TILES / _HEAD / _GROWTH
+	bool write_fork = true;                  // HVCF_WRITE_FORK: the write passes of the rounds after the first run on side streams
+	cudaStream_t write_streams[3]{};
+	cudaEvent_t write_ev[4]{};               // [0] fork (after finalize), [1..3] join
 	uint32_t* d_group_alive = nullptr;       // [kHMaxChunks][ncb]: per round, which groups still had a cluster below its cap when it began
 	float* d_alive_union = nullptr;          // [ncb][8] union box of each group's live clusters (rounds after the first)
 	const uint32_t* bin_alive = nullptr;     // what the next binning launch takes as BinParams::group_alive
