@@ -548,17 +548,26 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
         search = CutSearch(Z * upz, world)
         for it in range(max(0, args.balance_iters)):
             ctx = make([c * unit for c in cuts_u], ktimes=True)
+            for f in range(2):
+                ctx.cull_routed(f & 1, sp)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
             for f in range(4):
                 ctx.cull_routed(f & 1, sp)
+            e1.record(stream)
+            torch.cuda.synchronize()
             kt = ctx.kernel_times(1)
             err = ctx.peer_status(sp)
             drop(ctx)
             own = float(sum(kt[1:]))                       # bin + count + finalize + write: this rank's own work, no waiting
-            times = allgather(own)
-            history.append({"row_cuts": [c * unit for c in cuts_u], "own_kernels_ms": [round(t, 4) for t in times], "peer_error": err})
-            search.add(cuts_u, times)
-            if max(times) <= 1.04 * (sum(times) / world):
-                break
+            got = allgather((own, e0.elapsed_time(e1) / 4))
+            times, frame_ms = [g[0] for g in got], max(g[1] for g in got)
+            history.append({"row_cuts": [c * unit for c in cuts_u], "own_kernels_ms": [round(t, 4) for t in times], "frame_ms": round(frame_ms, 4),
+                            "peer_error": err})
+            # the estimate of the cost over the rows comes from the per-rank kernel times; the cuts that are KEPT are the ones with the
+            # shortest measured frame (ranks also wait for each other at the two phase boundaries of a frame)
+            search.add(cuts_u, times, score=frame_ms)
             new_cuts = search.next_cuts()
             if new_cuts == cuts_u:
                 break

@@ -92,10 +92,14 @@ class CutSearch:
         self.samples = {}     # unit position -> [cumulative share]
         self.best = None      # (max time, cuts)
 
-    def add(self, cuts, times):
+    def add(self, cuts, times, score=None):
+        """times: per-rank cost of the slabs cut at `cuts` (what the estimate is built from); score: what `best` minimises
+        (the measured frame time, when the caller has it: ranks also wait for each other inside a frame, so equal costs
+        are not always the shortest frame), default max(times)."""
         times = [max(float(t), 1e-9) for t in times]
-        if self.best is None or max(times) < self.best[0]:
-            self.best = (max(times), list(cuts))
+        score = max(times) if score is None else float(score)
+        if self.best is None or score < self.best[0]:
+            self.best = (score, list(cuts))
         cum = np.cumsum(times) / sum(times)
         for k in range(1, self.world):
             self.samples.setdefault(int(cuts[k]), []).append(float(cum[k - 1]))
