@@ -81,6 +81,9 @@ static void free_ctx(hvcf_ctx* c)
 	cudaFree(c->d_sb_union);
 	cudaFree(c->d_bin_count);
 	cudaFree(c->d_bin_rec);
+	cudaFree(c->d_small_state);
+	cudaFree(c->d_small_over);
+	cudaFree(c->d_small_ctl);
 	cudaFree(c->d_group_alive);
 	cudaFree(c->d_alive_union);
 	cudaFree(c->d_bin_idx);
@@ -324,6 +327,7 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 		c->rounds_growth = static_cast<uint32_t>(env_int("HVCF_ROUNDS_GROWTH", 8));
 		c->rounds_macro = env_int("HVCF_ROUNDS_MACRO", -1);
 		c->write_fork = env_int("HVCF_WRITE_FORK", 1) != 0;
+		c->small_mode = env_int("HVCF_SMALL", 1) != 0;
 		c->rounds_late_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_LATE_SEGS", 32));
 		c->rounds_early_segs = static_cast<uint32_t>(env_int("HVCF_ROUNDS_EARLY_SEGS", 16));
 		if (c->rounds_early_segs == 0)
@@ -391,6 +395,9 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 			HVCF_ALLOC(c->d_bin_idx, sizeof(uint16_t) * slots * kBinCap);
 		}
 		HVCF_ALLOC(c->d_scan_state, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);
+		HVCF_ALLOC(c->d_small_state, sizeof(unsigned long long) * ((Cs + 31) / 32));
+		HVCF_ALLOC(c->d_small_over, sizeof(uint32_t) * ((Cs + 31) / 32));
+		HVCF_ALLOC(c->d_small_ctl, sizeof(uint32_t) * 4);
 		if (env_int("HVCF_HIER_TRACE", 0))
 			HVCF_ALLOC(c->d_trace, sizeof(unsigned long long) * 16 * static_cast<size_t>(c->hp.ncb) * c->h_max_segs);
 	}
@@ -429,6 +436,13 @@ int hvcf_create(const hvcf_config* config, hvcf_ctx** out_ctx)
 	}
 	if (e == cudaSuccess && c->hier)
 		e = cudaMemset(c->d_scan_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32) * c->frame_count);
+	if (e == cudaSuccess && c->hier)
+		e = cudaMemset(c->d_small_state, 0, sizeof(unsigned long long) * ((Cs + 31) / 32));
+	if (e == cudaSuccess && c->hier)
+	{
+		const uint32_t ctl[4] = {1u, 0u, 0u, 0u}; // serial (never 0: the zeroed state words carry tag 0), ticket counter
+		e = cudaMemcpy(c->d_small_ctl, ctl, sizeof(ctl), cudaMemcpyHostToDevice);
+	}
 	if (e != cudaSuccess)
 	{
 		free_ctx(c);
@@ -1351,6 +1365,7 @@ static int peer_check_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const
 	HVCF_CUDA(preload_basic_kernels());
 	HVCF_CUDA(preload_hier_kernels());
 	HVCF_CUDA(preload_bin_kernels());
+	HVCF_CUDA(preload_small_kernels());
 	HVCF_CUDA(preload_peer_kernels());
 	HVCF_CUDA(preload_shard_kernels());
 	if (ctx->shard.on && (ctx->shard.world != world || ctx->shard.rank != rank))
@@ -1577,8 +1592,68 @@ int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error)
 	return HVCF_OK;
 }
 
+// frames of a few thousand lights on an unsharded context: the whole frame as one kernel (hvcf_small.cu)
+static bool small_frame_ok(const hvcf_ctx* ctx)
+{
+	return ctx && ctx->hier && ctx->small_mode && !ctx->anim_len && !ctx->shard.on && !ctx->peer.world && ctx->cluster_count == ctx->cluster_total &&
+		ctx->num_lights <= small_frame_max_lights() && ctx->d_small_state;
+}
+
+static int cull_small(hvcf_ctx* ctx, uint32_t frame, void* stream)
+{
+	NvtxZone zone("Light_Culling");
+	const int rc = hvcf_cull_open(ctx, frame, stream, "hvcf_cull", false, false); // AABBs if dirty; frame / UBO checks
+	if (rc != HVCF_OK)
+		return rc;
+	cudaStream_t s = static_cast<cudaStream_t>(stream);
+	SmallParams p{};
+	p.ubo = &ctx->d_ubo[frame];
+	p.lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
+	p.num_lights = ctx->num_lights;
+	p.aabbs = ctx->d_aabb;
+	p.cluster_count = ctx->cluster_count;
+	p.cap = ctx->cap;
+	p.cells = ctx->d_cells;
+	p.indices = ctx->d_indices;
+	p.frame_total = &ctx->d_global_index[frame];
+	p.shard_total = ctx->d_shard_total;
+	p.stats = &ctx->d_stats[frame];
+	p.scan_state = ctx->d_small_state;
+	p.over_part = ctx->d_small_over;
+	p.serial = ctx->d_small_ctl;
+	p.done = ctx->d_small_ctl + 1;
+	p.trace = ctx->d_trace;
+	for (int i = 1; i <= 2; ++i)
+		HVCF_CUDA(hvcf_kmark(ctx, frame, i, s));
+	if (ctx->timing)
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][1], s));
+	HVCF_CUDA(launch_small_frame(p, s));
+	if (ctx->timing)
+	{
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][2], s));
+		HVCF_CUDA(cudaEventRecord(ctx->ev[frame][3], s));
+		ctx->ev_valid[frame] = true;
+	}
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 3, s));
+	HVCF_CUDA(hvcf_kmark(ctx, frame, 4, s));
+	if (ctx->ktimes)
+	{
+		if (!ctx->kev[frame][5])
+			HVCF_CUDA(cudaEventCreate(&ctx->kev[frame][5]));
+		HVCF_CUDA(cudaEventRecord(ctx->kev[frame][5], s));
+	}
+	ctx->h_num_rounds = 0;
+	ctx->h_num_segs = 1;
+	ctx->last_plan_flags = HVCF_PLAN_SINGLE_KERNEL;
+	ctx->last_launches[frame] = ctx->open_launches + 1;
+	ctx->range_open = false;
+	return HVCF_OK;
+}
+
 int hvcf_cull(hvcf_ctx* ctx, uint32_t frame, void* stream)
 {
+	if (small_frame_ok(ctx))
+		return cull_small(ctx, frame, stream);
 	const int rc = hvcf_cull_begin(ctx, frame, stream);
 	if (rc != HVCF_OK)
 		return rc;

@@ -121,6 +121,10 @@ struct hvcf_ctx
 	uint32_t h_num_rounds = 0;
 	int rounds_mode = -1;                    // HVCF_ROUNDS: -1 = by the number of tiles, 0 = never, n > 0 = at most n rounds whenever the frame has two tiles or more
 	uint32_t rounds_min_tiles = 2048, rounds_head = 64, rounds_growth = 8; // HVCF_ROUNDS_MIN_TILES / _HEAD / _GROWTH
+	bool small_mode = true;                  // HVCF_SMALL: frames of at most 2,048 lights on an unsharded context run as one kernel (hvcf_small.cu)
+	unsigned long long* d_small_state = nullptr; // its look-back words, per-CTA overflow counts, {serial, ticket}
+	uint32_t* d_small_over = nullptr;
+	uint32_t* d_small_ctl = nullptr;
 	bool write_fork = true;                  // HVCF_WRITE_FORK: the write passes of the rounds after the first run on side streams
 	cudaStream_t write_streams[3]{};
 	cudaEvent_t write_ev[4]{};               // [0] fork (after finalize), [1..3] join

@@ -74,6 +74,30 @@ cudaError_t launch_scatter(const ScatterParams& p, cudaStream_t stream);
 // 16 lane-ops per thread per iteration (8 FMUL + 8 FADD)
 cudaError_t launch_fp32_issue_rate(float* sink, uint32_t blocks, uint32_t iters, cudaStream_t stream);
 
+// ---- the whole frame as one kernel, for frames of at most small_frame_max_lights() lights (hvcf_small.cu) ----
+struct SmallParams
+{
+	const hvcf_cluster_forward_ubo* ubo;
+	const hvcf_light_data* lights;
+	uint32_t num_lights;
+	const hvcf_aabb* aabbs;         // the context's clusters (whole grid: unsharded contexts only)
+	uint32_t cluster_count;
+	uint32_t cap;
+	hvcf_light_cell* cells;
+	uint32_t* indices;
+	uint32_t* frame_total;          // globalIndexCountBuffers_[frame]
+	uint32_t* shard_total;
+	DeviceStats* stats;
+	unsigned long long* scan_state; // [ceil(cluster_count / 32)] look-back words, tagged with *serial
+	uint32_t* over_part;            // [ceil(cluster_count / 32)] clusters at the cap, per CTA
+	uint32_t* serial;               // device-resident frame serial of this kernel (never 0), bumped by the last CTA
+	uint32_t* done;                 // ticket counter
+	unsigned long long* trace = nullptr; // debug: phase timestamps of the first CTAs
+};
+uint32_t small_frame_max_lights();
+cudaError_t launch_small_frame(const SmallParams& p, cudaStream_t stream);
+cudaError_t preload_small_kernels();
+
 // ---- HVCF_MODE_HIERARCHICAL (hvcf_hier.cu) -------------------------------------------------------------
 constexpr uint32_t kHMaxChunks = 8; // early-exit chunks per cluster: 256 segments at most (hier_num_chunks(256) == 7)
 struct HierPlan

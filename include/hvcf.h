@@ -128,6 +128,7 @@ typedef struct hvcf_stats
 #define HVCF_PLAN_SUBTILE_SEGMENTS 8u /* a tile's slot is cut into several light segments */
 #define HVCF_PLAN_MACRO_TILES 16u   /* late rounds keep one slot per group and several tiles (or route block) */
 #define HVCF_PLAN_TWO_PHASE_ROUTE 32u /* routed frame: second share routed against the slabs' live boxes */
+#define HVCF_PLAN_SINGLE_KERNEL 64u   /* at most 2,048 lights, unsharded: transform + test + scan + write in one kernel (hvcf_small.cu) */
 
 HVCF_API const char* hvcf_last_error_string(void);
 HVCF_API const char* hvcf_version(void);

@@ -9,7 +9,8 @@ from cpu_checkers import AABB_DT, LIGHT_DT, Oracle, same_light_sets
 
 pytestmark = pytest.mark.gpu
 
-MODES = {"brute": 1, "hier": 2}  # hvcf_mode: HVCF_MODE_BRUTE, HVCF_MODE_HIERARCHICAL
+MODES = {"brute": 1, "hier": 2, "small": 2}  # hvcf_mode: HVCF_MODE_BRUTE, HVCF_MODE_HIERARCHICAL; "small" = hierarchical with the
+# single-kernel path for frames of <= 2,048 lights switched on (conftest.py), as it is by default outside the tests
 GRIDS = {"A": ((16, 9, 24), (2560, 1600)), "B": ((32, 18, 48), (3840, 2160)), "C": ((64, 36, 96), (3840, 2160))}
 
 
@@ -66,7 +67,7 @@ def run_cull(hv, grid, ubo, lights, cap=150, frame=0, **kw):
 
 
 @pytest.mark.parametrize("mode", list(MODES))
-@pytest.mark.parametrize("n", [0, 1, 31, 64, 1000, 1025, 65536])
+@pytest.mark.parametrize("n", [0, 1, 31, 64, 255, 256, 257, 1000, 1025, 2047, 2048, 2049, 65536])
 def test_cull_config_A(hv, oracle, n, mode):
     grid, screen = GRIDS["A"]
     ubo = oracle.camera_ubo(grid, screen)
@@ -84,6 +85,9 @@ def test_cull_config_A(hv, oracle, n, mode):
     if mode == "brute":
         assert stats["executed_tests"] >= oexec or n == 0  # tile-granular early exit never does less than the exact bound
         assert stats["prefilter_tests"] == 0
+    elif mode == "small" and n <= 2048:
+        assert stats["plan_flags"] == 64 and stats["kernel_launches"] <= 2      # HVCF_PLAN_SINGLE_KERNEL (+ AABB generation)
+        assert stats["executed_tests"] == stats["nominal_tests"] and stats["prefilter_tests"] == 0
     elif n:
         assert stats["prefilter_tests"] > 0
         assert stats["executed_tests"] + stats["prefilter_tests"] < stats["nominal_tests"] or n < 4096
@@ -470,3 +474,38 @@ def test_download_grid_into_pinned_memory_uses_one_kernel_and_gives_the_same_byt
             ch.close(), ih.close()
     assert got["0:4"] == got["1:4"] == got["1:1"] == got["1:0"]
     assert n < 70_000 or got["1:1"][2] > (1 << 18)   # the 1 MB case really splits the list
+
+
+@pytest.mark.parametrize("mode", ["small"])
+@pytest.mark.parametrize("cap", [1, 150, 4096])
+@pytest.mark.parametrize("grid,screen,n", [((16, 9, 24), (2560, 1600), 1000), ((16, 9, 24), (2560, 1600), 2048), ((1, 1, 1), (640, 480), 300), ((33, 2, 2), (1280, 720), 777),
+                                           ((5, 7, 3), (1280, 720), 1), ((32, 18, 48), (3840, 2160), 1500), ((64, 36, 96), (3840, 2160), 2048)])
+def test_small_frames_run_as_one_kernel(hv, oracle, grid, screen, n, cap, mode):
+    """csrc/hvcf_small.cu: transform + test + capped counts + scan over the clusters + index lists in ONE kernel for frames of at
+    most 2,048 lights (the reference's own scene is 1,000 lights in one dispatch, PipelineLightCulling.cpp:74-77).  Four frames in a
+    row on both frame slots with a moving camera and a moved light (the look-back serial lives on the device), a scene with NaN /
+    Inf / zero-radius lights, bytes against the oracle every time."""
+    ubos = [oracle.camera_ubo(grid, screen), oracle.camera_ubo(grid, screen, pos=(1.5, 2.0, 5.0), target=(0, 2, -1))]
+    lights = oracle.init_lights(n, seed=5)
+    if n >= 300:
+        lights["position"][7] = (np.nan, 1, 1, 1)
+        lights["position"][8] = (np.inf, 0, 0, 1)
+        lights["radius"][9] = 0.0
+        lights["radius"][10] = np.inf
+    aabb = oracle.generate_aabbs(ubos[0])
+    with hv.Context(grid=grid, max_lights=n, max_lights_per_cluster=cap, mode=MODES[mode]) as ctx:
+        ctx.set_lights(lights)
+        for f in range(4):
+            if f == 2:
+                lights["position"][0] = (0.25, 2.0, 1.0, 1.0)
+                ctx.update_light(0, (0.25, 2.0, 1.0))
+            ctx.set_ubo(f & 1, ubos[f & 1])
+            ctx.cull(f & 1)
+            cells, idx, total = ctx.download_grid(f & 1)
+            st = ctx.stats(f & 1)
+            oc, oi, ototal, _ = oracle.cull(ubos[f & 1], aabb, lights, cap=cap)
+            assert total == ototal and st["total_indices"] == ototal, f
+            assert cells.tobytes() == oc.tobytes() and idx.tobytes() == oi.tobytes(), f
+            assert st["plan_flags"] == 64 and st["kernel_launches"] == (2 if f == 0 else 1)
+            assert st["overflow_clusters"] == int((oc["count"] == cap).sum())
+            check_invariants(cells, idx, total, n, cap)

@@ -115,7 +115,7 @@ def test_cull_kernels_have_no_contracted_fma():
             counts[fn] = 0
         elif fn and re.search(r"\bFFMA2?\b", line):
             counts[fn] += 1
-    names = ("cull_kernel", "light_transform", "hier_xbin_kernel", "hier_bin_kernel", "hier_bin2_kernel", "hier2_kernel", "hier_kernel")
+    names = ("cull_kernel", "light_transform", "hier_xbin_kernel", "hier_bin_kernel", "hier_bin2_kernel", "hier2_kernel", "small_frame_kernel", "shard_route_kernel")
     cull = {k: v for k, v in counts.items() if any(n in k for n in names)}
     assert len(cull) >= 30 and all(v == 0 for v in cull.values()), {k: v for k, v in cull.items() if v}
 
