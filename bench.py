@@ -429,6 +429,8 @@ def measure_single(hvcf, torch, name, K, W, local, flush_all, barrier=None, e2e_
     ictx.close()
     issue_rate = hvcf.measure_fp32_issue_rate(local)
     out["roofline"] = kernel_roofline(ms, st2, issue_rate, out["ms"])
+    if st2.get("plan_flags", 0) & 64:   # HVCF_PLAN_SINGLE_KERNEL: the frame was one launch; its time sits in the "count" slot
+        out["roofline"]["kernel"] = "small_frame_kernel (hvcf_small.cu: the whole frame in one launch)"
     out["stats"] = {k: int(v) for k, v in st2.items()}
     out["nominal_tests"] = C * n
     return out

@@ -11,7 +11,7 @@ timeout 900 python bench.py > $O/bench_N1.json 2> $O/bench_N1.err; echo "bench r
 tail -3 $O/bench_N1.err
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_reference.json 2> $O/bench_reference.err; echo "ref rc=$?" | tee -a $O/rc.txt
 ARGS="--steps 2 --warmup 3 --no-summary --no-flythrough --no-next-rows --no-cpu-baseline"
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_C16M.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file $O/launches_C16M.csv \
   python bench.py $ARGS > $O/ncu_launch.log 2>&1; echo "launches rc=$?" | tee -a $O/rc.txt
 python scripts/launch_seq.py $O/launches_C16M.csv | tee $O/launch_seq_C16M.txt
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"hier|light_transform" --launch-skip 34 -c 17 -o $O/full_C16M -f \
@@ -20,8 +20,6 @@ ncu -i $O/full_C16M.ncu-rep --page raw --csv > $O/full_C16M_raw.csv 2>/dev/null
 python scripts/ncu_summary.py $O/full_C16M_raw.csv > $O/full_C16M_summary.txt 2>&1
 cut -c1-260 $O/full_C16M_summary.txt
 rm -f $O/full_C16M.ncu-rep
-bash scripts/gpu_sweep.sh $TAG B1M "off:HVCF_ROUNDS=0" "r2:HVCF_ROUNDS=2" "r3:HVCF_ROUNDS=3" "r2h128:HVCF_ROUNDS=2 HVCF_ROUNDS_HEAD=128"
-bash scripts/gpu_sweep.sh $TAG A1M "off:HVCF_ROUNDS=0" "r2:HVCF_ROUNDS=2" "r3:HVCF_ROUNDS=3"
 python - <<PY
 import json
 for l in open("$O/bench_N1.json"):
