@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(WARPS * 32) cull_kernel(const CullParams p)
 						const f32x2 dz = pack2(d0, d1);
 						// products packed (FMUL2), sums scalar: ptxas contracts mul.rn.f32x2 + add.rn.f32x2
 						// into FFMA2 even under --fmad=false, which would break bit-exactness; a scalar
-						// add.rn.f32 is never contracted (tests/test_build.py checks the SASS for FFMA)
+						// add.rn.f32 is never contracted (tests/test_host.py::test_cull_kernels_have_no_contracted_fma checks the SASS for FFMA)
 						float sx0, sx1, sy0, sy1, sz0, sz1;
 						unpack2(mul2(dx, dx), sx0, sx1);
 						unpack2(mul2(dy, dy), sy0, sy1);
