@@ -705,7 +705,7 @@ def run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush):
         dg.close()
     fr = {}
     frustum = hvcf.host_frustum_ubo(screen)
-    for count in (10000, 1 << 20):
+    for count in (10000, 1 << 20, 1 << 24):   # 2^24 boxes = 604 MB: larger than L2, the asymptotic bandwidth of the kernel
         boxes = hvcf.host_init_boxes(count, 60.0)
         db = hvcf.DeviceBuffer.from_array(boxes, device=local)
         dc = hvcf.DeviceBuffer(16 * count, device=local)
@@ -726,7 +726,8 @@ def run_next_rows(args, hvcf, ctx, grid, screen, n, local, stream, sp, flush):
             t = float(np.median(us))
             bytes_ = (32 + 4) * count
             fr[str(count)] = {"us": t, "us_min": float(min(us)), "visible": vis, "boxes_per_s": count / (t * 1e-6),
-                              "algorithmic_bytes": bytes_, "gbs": bytes_ / (t * 1e-6) / 1e9}
+                              "algorithmic_bytes": bytes_, "gbs": bytes_ / (t * 1e-6) / 1e9,
+                              "hbm_frac": bytes_ / (t * 1e-6) / 1e9 / hbm_peak()[0]}
         finally:
             db.close(), dc.close()
     fr["reference_published_us_10000"] = 25.0
