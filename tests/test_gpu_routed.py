@@ -256,3 +256,19 @@ def test_routed_frames_in_rounds(hv, torch_mod, oracle, monkeypatch, plan, grid,
     seen = INBOX_SEEN[(plan, grid, n, cuts, cap)]
     if len(seen) == 2:
         assert seen["1"] <= seen["0"]   # live boxes never route more than the union boxes
+
+
+@pytest.mark.parametrize("args", [("16", "9", "24", "2560", "1600", "30000", "12345", "3", "3"),
+                                  ("32", "18", "48", "3840", "2160", "1500", "7", "2", "2"),      # unsharded side: the single-kernel frame
+                                  ("16", "9", "24", "2560", "1600", "5000", "3", "1", "2")])      # world 1: no attach
+def test_routed_frame_driven_from_cpp_alone(args):
+    """hellovulkan_b200/lib/hv_routed_shards_app (host/app_routed_shards.cpp): `world` shard contexts in one C++ process, nothing but
+    the C ABI and one CUDA stream per shard; it compares every shard's full light grid with the unsharded hvcf_cull frame by frame
+    (camera orbiting, light 0 moving) and prints OK."""
+    import os
+    import subprocess
+    app = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "hellovulkan_b200", "lib", "hv_routed_shards_app")
+    assert os.path.exists(app), "build() did not produce the routed-shards driver"
+    env = {k: v for k, v in os.environ.items() if not k.startswith("HVCF_")}    # the library's defaults, as a C++ caller gets them
+    r = subprocess.run([app, *args], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and r.stdout.startswith("OK "), r.stdout + r.stderr
