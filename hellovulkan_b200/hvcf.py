@@ -21,6 +21,7 @@ UBO_BYTES = 176
 FRUSTUM_BYTES = 224
 
 HVCF_OK = 0
+HVCF_ERR_INVALID_ARGUMENT, HVCF_ERR_CUDA, HVCF_ERR_OUT_OF_MEMORY, HVCF_ERR_CAPACITY, HVCF_ERR_NOT_READY, HVCF_ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 MODE_AUTO = 0
 MODE_BRUTE = 1
 MODE_HIERARCHICAL = 2
@@ -93,7 +94,7 @@ EXPORTS = [
     "hvcf_peer_export", "hvcf_peer_attach", "hvcf_peer_attach_local", "hvcf_peer_detach", "hvcf_peer_exchange_totals",
     "hvcf_peer_push_grid", "hvcf_peer_wait_grid", "hvcf_cull_begin_range", "hvcf_lights_view_ptr", "hvcf_transform_lights", "hvcf_cull_sharded", "hvcf_peer_totals_ptr", "hvcf_peer_index_base_ptr",
     "hvcf_peer_status", "hvcf_create_sharded", "hvcf_shard_light_range", "hvcf_set_lights_range", "hvcf_cull_routed",
-    "hvcf_shard_inbox_records", "hvcf_download_shard", "hvcf_debug_route_ms", "hvcf_debug_rounds",
+    "hvcf_shard_inbox_records", "hvcf_download_shard", "hvcf_debug_route_ms", "hvcf_debug_rounds", "hvcf_cull_small_noalloc",
     "hvcf_shade", "hvcf_host_init_gbuffer", "hvcf_frustum_cull", "hvcf_host_frustum_ubo", "hvcf_host_init_boxes",
 ]
 
@@ -180,6 +181,7 @@ def load():
     lib.hvcf_peer_totals_ptr.argtypes = [vp, ctypes.POINTER(vp)]
     lib.hvcf_peer_index_base_ptr.argtypes = [vp, ctypes.POINTER(vp)]
     lib.hvcf_peer_status.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_int)]
+    lib.hvcf_cull_small_noalloc.argtypes = [vp, vp, u32, vp, u32, u32, vp, vp, ctypes.c_uint64, vp, vp]
     _lib = lib
     return lib
 
@@ -308,6 +310,14 @@ def frustum_cull(frustum, boxes_ptr, count, commands_ptr, device=-1, stream=None
     frustum = np.ascontiguousarray(frustum).view(np.uint8)
     assert frustum.nbytes == FRUSTUM_BYTES
     _check(load().hvcf_frustum_cull(device, _ptr(frustum), boxes_ptr, count, commands_ptr, stream))
+
+
+def cull_small_noalloc(ubo_ptr, lights_ptr, num_lights, aabbs_ptr, cluster_count, cap, cells_ptr, indices_ptr, indices_capacity,
+                       total_ptr, stream=None):
+    """hvcf_cull_small_noalloc: the single-kernel frame over caller-owned DEVICE buffers, scratch in the library's static array
+    (nothing is allocated; <= 2,048 lights, <= 131,072 clusters; overlapping calls race on the scratch)."""
+    _check(load().hvcf_cull_small_noalloc(ubo_ptr, lights_ptr, num_lights, aabbs_ptr, cluster_count, cap, cells_ptr, indices_ptr,
+                                          indices_capacity, total_ptr, stream))
 
 
 # ---- fly-through of BASELINE.json configs[4] (SURVEY.md 8(d) config 5): camera orbit + animated lights --------------

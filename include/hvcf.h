@@ -191,6 +191,23 @@ HVCF_API int hvcf_lights_view_ptr(hvcf_ctx* ctx, void** out_device_ptr, size_t* 
 HVCF_API int hvcf_transform_lights(hvcf_ctx* ctx, uint32_t frame, uint32_t light_begin, uint32_t light_end, void* stream);
 HVCF_API int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr);
 
+/* hvcf_cull for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  It runs the single-kernel frame (the kernel
+ * hvcf_cull picks for at most 2,048 lights: LightCulling.comp:49-88 for the whole grid in one launch) with the kernel's scratch --
+ * scan state words, overflow counts, ticket counter, work counters -- in a file-scope __device__ array of the library instead of
+ * a context's cudaMalloc'ed buffers: 49,664 B, held by every GPU that loads the library until the process exits.  There is no
+ * context: every pointer is a DEVICE pointer of the current device, inputs and outputs in the reference's layouts
+ * (UBO 176 B, lights n x 48 B, AABBs clusters x 32 B as hvcf_generate_aabbs writes them, light cells clusters x 8 B, light indices,
+ * *d_total = globalIndex after the frame); UBO, lights and AABBs 16-byte aligned, light cells 8.  Results are byte-identical to
+ * hvcf_cull's.  The call allocates nothing: one cudaMemsetAsync of the scratch in use and one kernel launch on `stream` (the first
+ * call on a device also asks for the array's device address, cudaGetSymbolAddress -- make that call outside a capture).
+ * Limits: cluster_count <= 131,072, num_lights <= 2,048, light_indices_capacity (elements) >= cluster_count x min(num_lights,
+ * max_lights_per_cluster); beyond them HVCF_ERR_CAPACITY and nothing is launched.
+ * Every call on a device shares the one array: calls that overlap on the GPU (two streams, two threads) RACE -- serialise them. */
+HVCF_API int hvcf_cull_small_noalloc(const hvcf_cluster_forward_ubo* d_ubo, const hvcf_light_data* d_lights, uint32_t num_lights,
+	const hvcf_aabb* d_aabbs, uint32_t cluster_count, uint32_t max_lights_per_cluster, hvcf_light_cell* d_light_cells,
+	uint32_t* d_light_indices, uint64_t light_indices_capacity, uint32_t* d_total, void* stream);
+
 /* The exchange step of the z-slab sharded grid done by the GPUs themselves over NVLink peer memory (new: the
  * reference is single-GPU).  Every rank exports three allocations (light cells, light indices,
  * a small mailbox) and attaches every other rank's; after that one call per frame,
