@@ -489,6 +489,19 @@ int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n)
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_bind_lights: null context");
 	if (n > ctx->max_lights)
 		return fail(HVCF_ERR_CAPACITY, "hvcf_bind_lights: %u lights > max_lights %u", n, ctx->max_lights);
+	if (ctx->shard.on)
+	{
+		// a context of hvcf_create_sharded binds exactly the lights it OWNS: device_lights[0] is light `begin` of
+		// hvcf_shard_light_range.  Only hvcf_cull_routed reads such a buffer; the scene's light count stays what it was.
+		uint32_t lb = 0, le = 0;
+		hvcf_shard_light_range(ctx, &lb, &le);
+		if (device_lights && n != le - lb)
+			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_bind_lights: a sharded context binds the %u lights it owns, not %u", le - lb, n);
+		if (device_lights && ctx->anim_len)
+			return fail(HVCF_ERR_UNSUPPORTED, "hvcf_bind_lights: device-side light animation is not routed");
+		ctx->bound_lights = static_cast<const hvcf_light_data*>(device_lights);
+		return HVCF_OK;
+	}
 	const bool changed = ctx->bound_lights != static_cast<const hvcf_light_data*>(device_lights) || n > ctx->base_y_count;
 	ctx->bound_lights = static_cast<const hvcf_light_data*>(device_lights);
 	ctx->num_lights = device_lights ? n : 0;
@@ -510,6 +523,8 @@ int hvcf_update_light(hvcf_ctx* ctx, uint32_t index, const float xyz[3], void* s
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_update_light: null argument");
 	if (index >= ctx->num_lights)
 		return HVCF_OK; // ResourcesLight::UpdateLightPosition ignores an out-of-range index (ResourcesLight.cpp:22-25)
+	if (ctx->shard.on && ctx->bound_lights)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_update_light: the owned lights live in a bound buffer (hvcf_bind_lights); write to it directly");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	const uint32_t slot = ctx->one_light_cursor++ & 15u;
 	HVCF_CUDA(cudaEventSynchronize(ctx->one_light_events[slot])); // slot's previous copy has been consumed
@@ -527,6 +542,8 @@ int hvcf_update_lights(hvcf_ctx* ctx, const uint32_t* indices, const float* xyz,
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_update_lights: null argument");
 	if (count == 0)
 		return HVCF_OK;
+	if (ctx->shard.on && ctx->bound_lights)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_update_lights: the owned lights live in a bound buffer (hvcf_bind_lights); write to it directly");
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	if (count > ctx->upd_capacity)
@@ -582,6 +599,8 @@ int hvcf_set_light_animation(hvcf_ctx* ctx, const float* table, uint32_t table_l
 		ctx->anim_len = 0; // off; the light buffer keeps the positions of the last animated frame
 		return HVCF_OK;
 	}
+	if (ctx->shard.on && ctx->bound_lights)
+		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_set_light_animation: not with a bound buffer on a sharded context");
 	if (table_len & (table_len - 1))
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_light_animation: table_len %u is not a power of two", table_len);
 	if (table_len != ctx->anim_len)
@@ -720,6 +739,8 @@ int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who,
 		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: frame %u >= frame_count %u", who, frame, ctx->frame_count);
 	if (!ctx->ubo_set[frame])
 		return fail(HVCF_ERR_NOT_READY, "%s: hvcf_set_ubo(frame %u) has not been called", who, frame);
+	if (!routed && ctx->shard.on && ctx->bound_lights)
+		return fail(HVCF_ERR_UNSUPPORTED, "%s: the bound buffer of a sharded context holds the owned lights only (hvcf_cull_routed reads it)", who);
 	HVCF_CUDA(cudaSetDevice(ctx->device));
 	cudaStream_t s = static_cast<cudaStream_t>(stream);
 	ctx->ev_valid[frame] = false;

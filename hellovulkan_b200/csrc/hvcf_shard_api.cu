@@ -187,8 +187,6 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	ShardState& sh = ctx->shard;
 	if (ctx->anim_len)
 		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_routed: device-side light animation is not routed (frame-partitioned replicas animate)");
-	if (ctx->bound_lights)
-		return fail(HVCF_ERR_UNSUPPORTED, "hvcf_cull_routed: the owned lights live in the context's own buffer (hvcf_set_lights_range)");
 	if (!ctx->peer.world)
 	{
 		if (sh.world != 1)
@@ -225,7 +223,9 @@ int hvcf_cull_routed(hvcf_ctx* ctx, uint32_t frame, void* stream)
 			return HVCF_OK; // nothing of this phase is ours; the wait kernel that follows raises the flag all the same
 		RouteParams rp{};
 		rp.ubo = &ctx->d_ubo[frame];
-		rp.lights = ctx->d_lights;
+		// indexed by GLOBAL light index; a bound buffer (hvcf_bind_lights) starts at the first owned light, lb
+		rp.lights = ctx->bound_lights ? reinterpret_cast<const hvcf_light_data*>(reinterpret_cast<uintptr_t>(ctx->bound_lights) -
+			sizeof(hvcf_light_data) * static_cast<uintptr_t>(lb)) : ctx->d_lights;
 		const uint64_t end_light = static_cast<uint64_t>(b1) * sh.block_tiles * kTileLights;
 		rp.light_end = end_light < le ? static_cast<uint32_t>(end_light) : le;
 		rp.block_tiles = sh.block_tiles;

@@ -318,7 +318,10 @@ HVCF_API int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void
  * so ResourcesLight::UpdateLightPosition writes are seen by the next frame without a copy.
  * NULL rebinds the context's own buffer.  The buffer is read-only to the library EXCEPT with device-side light animation on
  * (hvcf_set_light_animation): the moved positions are then written back into it, as UpdateLightPosition writes them into the
- * SSBO, and binding a new buffer (or more lights) re-captures the rest heights on the default stream. */
+ * SSBO, and binding a new buffer (or more lights) re-captures the rest heights on the default stream.
+ * A context of hvcf_create_sharded binds exactly the lights it OWNS: device_lights[0] is light `begin` of hvcf_shard_light_range and
+ * n = end - begin.  hvcf_cull_routed reads it in place (e.g. two buffers bound in turn, the next frame's lights uploading into one
+ * while the other is culled); the other light calls of such a context return HVCF_ERR_UNSUPPORTED while a buffer is bound. */
 HVCF_API int hvcf_bind_lights(hvcf_ctx* ctx, const void* device_lights, uint32_t n);
 
 /* Raw device buffers for the C++ mirror of VulkanBuffer (include/hv/Context.h):

@@ -272,3 +272,54 @@ def test_routed_frame_driven_from_cpp_alone(args):
     env = {k: v for k, v in os.environ.items() if not k.startswith("HVCF_")}    # the library's defaults, as a C++ caller gets them
     r = subprocess.run([app, *args], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and r.stdout.startswith("OK "), r.stdout + r.stderr
+
+
+def test_routed_frames_read_bound_light_buffers(hv, torch_mod, oracle):
+    """hvcf_bind_lights on contexts of hvcf_create_sharded: every rank binds a device buffer holding ONLY the lights it owns
+    (two buffers in turn, with different scenes, as a host does that uploads the next frame's lights while this one is culled);
+    every rank's full grid equals the single context's frame over the scene of that frame."""
+    n, cuts = 50_000, (0, 13, 18, 24)
+    world = len(cuts) - 1
+    ubo = oracle.camera_ubo(GRID_A, SCREEN_A)
+    scenes = [oracle.init_lights(n, seed=4), oracle.init_lights(n, seed=8)]
+    wants = [run_single(hv, GRID_A, ubo, sc) for sc in scenes]
+    assert wants[0][1].tobytes() != wants[1][1].tobytes()
+    ctxs = [hv.Context(grid=GRID_A, max_lights=n, shard=(r, world, n, cuts, 0)) for r in range(world)]
+    streams = [torch_mod.cuda.Stream() for _ in range(world)]
+    bufs = []
+    try:
+        for c in ctxs:
+            b, e = c.shard_light_range()
+            bufs.append([hv.DeviceBuffer.from_array(sc[b:e]) if e > b else None for sc in scenes])
+            for f in range(2):
+                c.set_ubo(f, ubo)
+            with pytest.raises(hv.HvcfError):
+                c.bind_lights(bufs[-1][0].ptr.value, e - b + 1)       # exactly the owned lights
+        torch_mod.cuda.synchronize()
+        for r, c in enumerate(ctxs):
+            c.peer_attach_local(r, ctxs)
+        for f in range(5):
+            which = (f // 2) & 1                                       # frame slots and buffers alternate at different rates
+            for r, (c, s) in enumerate(zip(ctxs, streams)):
+                b, e = c.shard_light_range()
+                if e > b:
+                    c.bind_lights(bufs[r][which].ptr.value, e - b)
+                c.cull_routed(f & 1, stream=s.cuda_stream)
+            for c, s in zip(ctxs, streams):
+                assert c.peer_status(stream=s.cuda_stream) == 0
+            torch_mod.cuda.synchronize()
+            assert_all_equal([c.download_grid(f & 1) for c in ctxs], wants[which], f"frame {f}")
+        with pytest.raises(hv.HvcfError):
+            ctxs[0].cull(0)                                            # only the routed frame reads an owned-lights buffer
+        with pytest.raises(hv.HvcfError):
+            ctxs[0].update_light(0, (0.0, 0.0, 0.0))
+        for c in ctxs:
+            c.bind_lights(None, 0)
+            c.peer_detach()
+    finally:
+        for c in ctxs:
+            c.close()
+        for pair in bufs:
+            for b in pair:
+                if b is not None:
+                    b.close()
