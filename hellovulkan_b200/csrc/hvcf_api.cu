@@ -29,24 +29,6 @@ int fail(int code, const char* fmt, ...)
 }
 } // namespace hvcf
 
-static void peer_unmap(hvcf_ctx* c)
-{
-	if (c->peer_ipc)
-		for (uint32_t r = 0; r < c->peer.world; ++r)
-			if (r != c->peer.rank)
-			{
-				cudaIpcCloseMemHandle(c->peer.cells[r]);
-				cudaIpcCloseMemHandle(c->peer.indices[r]);
-				cudaIpcCloseMemHandle(c->peer.mail[r]);
-				if (c->shard.inbox_peer[r])
-					cudaIpcCloseMemHandle(c->shard.inbox_peer[r]);
-			}
-	for (auto& q : c->shard.inbox_peer)
-		q = nullptr;
-	c->peer = PeerParams{};
-	c->peer_ipc = false;
-}
-
 static void free_ctx(hvcf_ctx* c)
 {
 	if (!c)
@@ -1331,288 +1313,6 @@ int hvcf_cull_finish(hvcf_ctx* ctx, uint32_t frame, const uint32_t* d_index_base
 	return HVCF_OK;
 }
 
-// ---- exchange step of the sharded grid over peer memory ---------------------------------------------------
-static int peer_alloc(hvcf_ctx* ctx)
-{
-	if (ctx->d_mail && ctx->d_index_base && ctx->d_peer_totals)
-		return HVCF_OK; // nothing to do -- and no synchronisation: getters may be called between stream-ordered peer calls
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	if (!ctx->d_mail)
-	{
-		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_mail), sizeof(PeerMailbox)));
-		HVCF_CUDA(cudaMemset(ctx->d_mail, 0, sizeof(PeerMailbox)));
-	}
-	if (!ctx->d_index_base)
-	{
-		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_index_base), sizeof(uint32_t)));
-		HVCF_CUDA(cudaMemset(ctx->d_index_base, 0, sizeof(uint32_t)));
-	}
-	if (!ctx->d_peer_totals)
-	{
-		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_peer_totals), sizeof(uint32_t) * kMaxPeers));
-		HVCF_CUDA(cudaMemset(ctx->d_peer_totals, 0, sizeof(uint32_t) * kMaxPeers));
-	}
-	HVCF_CUDA(cudaDeviceSynchronize());
-	return HVCF_OK;
-}
-
-int hvcf_peer_export(hvcf_ctx* ctx, hvcf_peer_handle* out)
-{
-	static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(hvcf_peer_handle) == 256, "hvcf_peer_handle holds four 64-byte IPC handles");
-	static_assert(HVCF_MAX_PEERS == kMaxPeers, "HVCF_MAX_PEERS");
-	if (!ctx || !out)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_export: null argument");
-	const int rc = peer_alloc(ctx);
-	if (rc != HVCF_OK)
-		return rc;
-	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->cells), ctx->d_cells));
-	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->indices), ctx->d_indices));
-	HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->mailbox), ctx->d_mail));
-	memset(out->inbox, 0, sizeof(out->inbox));
-	if (ctx->shard.on)
-		HVCF_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->inbox), ctx->shard.d_inbox));
-	return HVCF_OK;
-}
-
-static int peer_check_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const void* p, const char* who)
-{
-	if (!ctx || !p)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null argument", who);
-	if (world == 0 || world > kMaxPeers || rank >= world)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: rank %u of world %u (at most %u peers)", who, rank, world, kMaxPeers);
-	if (ctx->peer.world)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: already attached; call hvcf_peer_detach first", who);
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(preload_basic_kernels());
-	HVCF_CUDA(preload_hier_kernels());
-	HVCF_CUDA(preload_bin_kernels());
-	HVCF_CUDA(preload_small_kernels());
-	HVCF_CUDA(preload_peer_kernels());
-	HVCF_CUDA(preload_shard_kernels());
-	if (ctx->shard.on && (ctx->shard.world != world || ctx->shard.rank != rank))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: rank %u of %u, but the context was created as rank %u of %u", who, rank, world, ctx->shard.rank,
-			ctx->shard.world);
-	return peer_alloc(ctx);
-}
-
-int hvcf_peer_attach(hvcf_ctx* ctx, uint32_t rank, uint32_t world, const hvcf_peer_handle* handles)
-{
-	const int rc = peer_check_attach(ctx, rank, world, handles, "hvcf_peer_attach");
-	if (rc != HVCF_OK)
-		return rc;
-	PeerParams pp{};
-	pp.world = world;
-	pp.rank = rank;
-	for (uint32_t r = 0; r < world; ++r)
-	{
-		if (r == rank)
-		{
-			pp.cells[r] = ctx->d_cells;
-			pp.indices[r] = ctx->d_indices;
-			pp.mail[r] = ctx->d_mail;
-			continue;
-		}
-		void* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
-		const unsigned char* h[4] = {handles[r].cells, handles[r].indices, handles[r].mailbox, handles[r].inbox};
-		const int nh = ctx->shard.on ? 4 : 3;
-		for (int k = 0; k < nh; ++k)
-		{
-			cudaIpcMemHandle_t handle;
-			memcpy(&handle, h[k], sizeof(handle));
-			const cudaError_t e = cudaIpcOpenMemHandle(&ptr[k], handle, cudaIpcMemLazyEnablePeerAccess);
-			if (e != cudaSuccess)
-			{
-				for (int j = 0; j < k; ++j)
-					cudaIpcCloseMemHandle(ptr[j]);
-				for (uint32_t q = 0; q < r; ++q) // the ranks mapped so far
-					if (q != rank)
-					{
-						cudaIpcCloseMemHandle(pp.cells[q]);
-						cudaIpcCloseMemHandle(pp.indices[q]);
-						cudaIpcCloseMemHandle(pp.mail[q]);
-						if (ctx->shard.inbox_peer[q])
-							cudaIpcCloseMemHandle(ctx->shard.inbox_peer[q]);
-						ctx->shard.inbox_peer[q] = nullptr;
-					}
-				return fail(HVCF_ERR_CUDA, "hvcf_peer_attach: cudaIpcOpenMemHandle(rank %u, buffer %d): %s", r, k, cudaGetErrorString(e));
-			}
-		}
-		pp.cells[r] = static_cast<hvcf_light_cell*>(ptr[0]);
-		pp.indices[r] = static_cast<uint32_t*>(ptr[1]);
-		pp.mail[r] = static_cast<PeerMailbox*>(ptr[2]);
-		ctx->shard.inbox_peer[r] = static_cast<unsigned char*>(ptr[3]);
-	}
-	if (ctx->shard.on)
-		ctx->shard.inbox_peer[rank] = ctx->shard.d_inbox;
-	ctx->peer = pp;
-	ctx->peer_ipc = true;
-	ctx->peer_epoch = 0;
-	ctx->shard.epoch = 0;
-	return HVCF_OK;
-}
-
-int hvcf_peer_attach_local(hvcf_ctx* ctx, uint32_t rank, uint32_t world, hvcf_ctx* const* contexts)
-{
-	const int rc = peer_check_attach(ctx, rank, world, contexts, "hvcf_peer_attach_local");
-	if (rc != HVCF_OK)
-		return rc;
-	PeerParams pp{};
-	pp.world = world;
-	pp.rank = rank;
-	for (uint32_t r = 0; r < world; ++r)
-	{
-		hvcf_ctx* o = r == rank ? ctx : contexts[r];
-		if (!o)
-			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] is null", r);
-		if (o->cluster_total != ctx->cluster_total || o->cap != ctx->cap)
-			return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] has a different grid or cap", r);
-		const int rc2 = peer_alloc(o);
-		if (rc2 != HVCF_OK)
-			return rc2;
-		if (o->device != ctx->device)
-		{
-			int can = 0;
-			HVCF_CUDA(cudaDeviceCanAccessPeer(&can, ctx->device, o->device));
-			if (!can)
-				return fail(HVCF_ERR_UNSUPPORTED, "hvcf_peer_attach_local: device %d cannot access device %d", ctx->device, o->device);
-			HVCF_CUDA(cudaSetDevice(ctx->device));
-			const cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
-			if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
-				return fail(HVCF_ERR_CUDA, "hvcf_peer_attach_local: cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
-			(void)cudaGetLastError();
-		}
-		pp.cells[r] = o->d_cells;
-		pp.indices[r] = o->d_indices;
-		pp.mail[r] = o->d_mail;
-		if (ctx->shard.on)
-		{
-			if (!o->shard.on || o->shard.parity_bytes != ctx->shard.parity_bytes || o->shard.world != world)
-				return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_attach_local: contexts[%u] was not created with the same hvcf_shard_desc", r);
-			ctx->shard.inbox_peer[r] = o->shard.d_inbox;
-		}
-	}
-	ctx->peer = pp;
-	ctx->peer_ipc = false;
-	ctx->peer_epoch = 0;
-	ctx->shard.epoch = 0;
-	return HVCF_OK;
-}
-
-int hvcf_peer_detach(hvcf_ctx* ctx)
-{
-	if (!ctx)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_detach: null context");
-	cudaSetDevice(ctx->device);
-	cudaDeviceSynchronize();
-	peer_unmap(ctx);
-	if (ctx->d_mail)
-		cudaMemset(ctx->d_mail, 0, sizeof(PeerMailbox));
-	return HVCF_OK;
-}
-
-int hvcf_peer_totals_step(hvcf_ctx* ctx, void* stream, uint32_t what)
-{
-	if (!ctx || !ctx->peer.world)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_exchange_totals: no peers attached");
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	if (what & 1u) // a new exchange starts with the post
-	{
-		ctx->peer_epoch = ctx->peer_epoch >= 0x7fffffffu ? 1u : ctx->peer_epoch + 1u;
-		ctx->peer.epoch = ctx->peer_epoch;
-	}
-	HVCF_CUDA(launch_peer_totals(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->d_peer_totals, static_cast<cudaStream_t>(stream), what));
-	if (what == 3u && ctx->ktimes && ctx->range_frame < ctx->frame_count) // (posted early / waited late: the write pass does not wait)
-	{
-		HVCF_CUDA(hvcf_kmark(ctx, ctx->range_frame, 6, static_cast<cudaStream_t>(stream)));
-		ctx->kev_exchange[ctx->range_frame] = true;
-	}
-	return HVCF_OK;
-}
-
-int hvcf_peer_exchange_totals(hvcf_ctx* ctx, void* stream) { return hvcf_peer_totals_step(ctx, stream, 3u); }
-
-int hvcf_peer_push_grid(hvcf_ctx* ctx, void* stream)
-{
-	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_push_grid: no peers attached or no totals exchanged");
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	// enough CTAs to keep the NVLink ports busy: 4 per SM by default (HVCF_PEER_BLOCKS overrides, for sweeps)
-	static const uint32_t blocks = static_cast<uint32_t>(env_int("HVCF_PEER_BLOCKS", 592) > 0 ? env_int("HVCF_PEER_BLOCKS", 592) : 592);
-	HVCF_CUDA(launch_peer_push(ctx->peer, ctx->d_shard_total, ctx->d_index_base, ctx->cluster_begin, ctx->cluster_count, blocks,
-		static_cast<cudaStream_t>(stream)));
-	return HVCF_OK;
-}
-
-int hvcf_peer_wait_grid(hvcf_ctx* ctx, void* stream)
-{
-	if (!ctx || !ctx->peer.world || !ctx->peer.epoch)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_wait_grid: no peers attached or no totals exchanged");
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(launch_peer_wait(ctx->peer, ctx->d_peer_totals, &ctx->d_global_index[ctx->range_frame < ctx->frame_count ? ctx->range_frame : 0],
-		static_cast<cudaStream_t>(stream)));
-	return HVCF_OK;
-}
-
-int hvcf_cull_sharded(hvcf_ctx* ctx, uint32_t frame, void* stream)
-{
-	if (!ctx || !ctx->peer.world)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_cull_sharded: no peers attached (hvcf_peer_attach)");
-	int rc = hvcf_cull_begin(ctx, frame, stream);
-	if (rc == HVCF_OK)
-		rc = hvcf_peer_exchange_totals(ctx, stream);
-	if (rc == HVCF_OK)
-		rc = hvcf_cull_finish(ctx, frame, ctx->d_index_base, stream);
-	if (rc == HVCF_OK)
-		rc = hvcf_peer_push_grid(ctx, stream);
-	if (rc == HVCF_OK)
-		rc = hvcf_peer_wait_grid(ctx, stream);
-	return rc;
-}
-
-int hvcf_peer_totals_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
-{
-	if (!ctx || !out_device_ptr)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_totals_ptr: null argument");
-	const int rc = peer_alloc(ctx);
-	if (rc != HVCF_OK)
-		return rc;
-	*out_device_ptr = ctx->d_peer_totals;
-	return HVCF_OK;
-}
-
-int hvcf_peer_index_base_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
-{
-	if (!ctx || !out_device_ptr)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_index_base_ptr: null argument");
-	const int rc = peer_alloc(ctx);
-	if (rc != HVCF_OK)
-		return rc;
-	*out_device_ptr = ctx->d_index_base;
-	return HVCF_OK;
-}
-
-int hvcf_peer_status(hvcf_ctx* ctx, void* stream, int* out_error)
-{
-	if (!ctx || !out_error)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_peer_status: null argument");
-	*out_error = 0;
-	if (!ctx->d_mail)
-		return HVCF_OK;
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
-	unsigned int err = 0;
-	HVCF_CUDA(cudaMemcpy(&err, &ctx->d_mail->error, sizeof(err), cudaMemcpyDeviceToHost));
-	*out_error = static_cast<int>(err);
-	if (err)
-	{
-		static const char* const kinds[] = {"?", "index total", "grid segment", "routed lights", "error report"};
-		const unsigned int kind = err >> 28;
-		return fail(HVCF_ERR_NOT_READY, "hvcf_peer_status: rank %u %s the %s of rank %u in sharded frame %u (mod 2^20)", ctx->peer.rank,
-			kind == 4 ? "received" : "waited in vain for", kinds[kind < 5 ? kind : 0], (err >> 20) & 0xffu, err & 0xfffffu);
-	}
-	return HVCF_OK;
-}
-
 // frames of a few thousand lights on an unsharded context: the whole frame as one kernel (hvcf_small.cu)
 static bool small_frame_ok(const hvcf_ctx* ctx)
 {
@@ -1679,526 +1379,6 @@ int hvcf_cull(hvcf_ctx* ctx, uint32_t frame, void* stream)
 	if (rc != HVCF_OK)
 		return rc;
 	return hvcf_cull_finish(ctx, frame, nullptr, stream);
-}
-
-int hvcf_shard_total_ptr(hvcf_ctx* ctx, uint32_t** out_device_ptr)
-{
-	if (!ctx || !out_device_ptr)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shard_total_ptr: null argument");
-	*out_device_ptr = ctx->d_shard_total;
-	return HVCF_OK;
-}
-
-int hvcf_get_device_buffers(hvcf_ctx* ctx, hvcf_buffers* out)
-{
-	if (!ctx || !out)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_device_buffers: null argument");
-	memset(out, 0, sizeof(*out));
-	out->aabb = ctx->d_aabb;
-	out->light_cells = ctx->d_cells;
-	out->light_indices = ctx->d_indices;
-	out->global_index_count = ctx->d_global_index;
-	out->lights = ctx->bound_lights ? const_cast<hvcf_light_data*>(ctx->bound_lights) : ctx->d_lights;
-	out->lights_view = reinterpret_cast<float*>(ctx->d_lights_view);
-	out->light_indices_capacity = static_cast<uint64_t>(ctx->cluster_total) * ctx->cap;
-	out->cluster_count = ctx->cluster_total;
-	out->light_count = ctx->num_lights;
-	out->cluster_begin = ctx->cluster_begin;
-	out->cluster_end = ctx->cluster_end;
-	return HVCF_OK;
-}
-
-// Sharded contexts: a download is the caller's next synchronisation point after a frame, so a wait that timed out inside
-// the frame (hvcf_peer.cu; the push kernels then skipped their stores) is reported here instead of handing out a stale grid.
-// Called after the stream has been synchronised.  One 4-byte read, only when peers are attached.
-int hvcf_peer_error_after_sync(hvcf_ctx* ctx, const char* what)
-{
-	if (!ctx->d_mail || ctx->peer.world < 2)
-		return HVCF_OK;
-	unsigned int err = 0;
-	HVCF_CUDA(cudaMemcpy(&err, &ctx->d_mail->error, sizeof(err), cudaMemcpyDeviceToHost));
-	if (err)
-		return fail(HVCF_ERR_NOT_READY, "%s: the sharded frame failed on rank %u (peer error 0x%08x: kind %u, rank %u, frame %u mod 2^20); hvcf_peer_status has the details",
-			what, ctx->peer.rank, err, err >> 28, (err >> 20) & 0xffu, err & 0xfffffu);
-	return HVCF_OK;
-}
-
-static int download(hvcf_ctx* ctx, void* dst, const void* src, size_t bytes, size_t limit, void* stream, const char* what)
-{
-	if (!ctx || (bytes && !dst))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: null argument", what);
-	if (bytes > limit)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "%s: %zu bytes > buffer size %zu", what, bytes, limit);
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	cudaStream_t s = static_cast<cudaStream_t>(stream);
-	if (bytes)
-		HVCF_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s));
-	HVCF_CUDA(cudaStreamSynchronize(s));
-	return hvcf_peer_error_after_sync(ctx, what);
-}
-
-int hvcf_download_aabbs(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
-{
-	return download(ctx, dst, ctx ? ctx->d_aabb : nullptr, bytes, ctx ? sizeof(hvcf_aabb) * ctx->cluster_total : 0, stream,
-		"hvcf_download_aabbs");
-}
-int hvcf_download_light_cells(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
-{
-	return download(ctx, dst, ctx ? ctx->d_cells : nullptr, bytes, ctx ? sizeof(hvcf_light_cell) * ctx->cluster_total : 0, stream,
-		"hvcf_download_light_cells");
-}
-int hvcf_download_light_indices(hvcf_ctx* ctx, void* dst, size_t bytes, void* stream)
-{
-	return download(ctx, dst, ctx ? ctx->d_indices : nullptr, bytes,
-		ctx ? sizeof(uint32_t) * static_cast<size_t>(ctx->cluster_total) * ctx->cap : 0, stream, "hvcf_download_light_indices");
-}
-int hvcf_download_total(hvcf_ctx* ctx, uint32_t frame, uint32_t* out_total, void* stream)
-{
-	if (ctx && frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_total: frame %u >= frame_count %u", frame, ctx->frame_count);
-	return download(ctx, out_total, ctx ? &ctx->d_global_index[frame] : nullptr, sizeof(uint32_t), sizeof(uint32_t), stream,
-		"hvcf_download_total");
-}
-
-// is p pinned host memory the device can store to at the same address?  Asked on every call (well under a microsecond): a
-// remembered answer would go stale when the caller frees a pinned buffer and pageable memory takes its address.
-static bool mapped_host_ptr(const void* p)
-{
-	if (!p || (reinterpret_cast<uintptr_t>(p) & 15u))
-		return false;
-	cudaPointerAttributes a{};
-	const bool ok = cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer == p;
-	cudaGetLastError(); // unregistered memory is not an error here
-	return ok;
-}
-
-int hvcf_download_grid(hvcf_ctx* ctx, uint32_t frame, void* cells_dst, size_t cells_bytes, void* indices_dst,
-	size_t indices_capacity_bytes, uint32_t* out_total, void* stream)
-{
-	if (!ctx || !out_total || (cells_bytes && !cells_dst))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: null argument");
-	if (frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: frame %u >= frame_count %u", frame, ctx->frame_count);
-	if (cells_bytes > sizeof(hvcf_light_cell) * static_cast<size_t>(ctx->cluster_total))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_download_grid: %zu bytes of cells > buffer size", cells_bytes);
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	cudaStream_t s = static_cast<cudaStream_t>(stream);
-	if (!ctx->h_total)
-		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_total), sizeof(uint32_t) * 16));
-	// both destinations in pinned (mapped) host memory, 16 B aligned: one kernel stores count, cells and indices[0, count)
-	// across PCIe -- no host round trip between "how many" and "copy them" (HVCF_DOWNLOAD_KERNEL=0: the two-copy path)
-	if (ctx->download_kernel && cells_bytes % 4 == 0 && mapped_host_ptr(cells_dst) && (indices_capacity_bytes == 0 || mapped_host_ptr(indices_dst)))
-	{
-		const size_t cap_words = indices_capacity_bytes / sizeof(uint32_t);
-		HVCF_CUDA(launch_grid_download(ctx->d_cells, cells_bytes, ctx->d_indices, &ctx->d_global_index[frame],
-			static_cast<uint32_t>(cap_words < 0xffffffffull ? cap_words : 0xffffffffull), ctx->download_max_words, cells_dst, static_cast<uint32_t*>(indices_dst),
-			&ctx->h_total[frame], ctx->download_blocks, s));
-		HVCF_CUDA(cudaStreamSynchronize(s));
-		if (const int prc = hvcf_peer_error_after_sync(ctx, "hvcf_download_grid"))
-			return prc;
-		const uint32_t total = ctx->h_total[frame];
-		*out_total = total;
-		if (sizeof(uint32_t) * static_cast<size_t>(total) > indices_capacity_bytes)
-			return fail(HVCF_ERR_CAPACITY, "hvcf_download_grid: %u indices do not fit in %zu bytes", total, indices_capacity_bytes);
-		const uint32_t by_kernel = ctx->download_max_words & ~3u;
-		if (total > by_kernel) // a long list: the copy engine takes what the kernel left
-		{
-			HVCF_CUDA(cudaMemcpyAsync(static_cast<uint32_t*>(indices_dst) + by_kernel, ctx->d_indices + by_kernel,
-				sizeof(uint32_t) * static_cast<size_t>(total - by_kernel), cudaMemcpyDeviceToHost, s));
-			HVCF_CUDA(cudaStreamSynchronize(s));
-		}
-		return HVCF_OK;
-	}
-	HVCF_CUDA(cudaMemcpyAsync(&ctx->h_total[frame], &ctx->d_global_index[frame], sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-	if (cells_bytes)
-		HVCF_CUDA(cudaMemcpyAsync(cells_dst, ctx->d_cells, cells_bytes, cudaMemcpyDeviceToHost, s));
-	HVCF_CUDA(cudaStreamSynchronize(s));
-	if (const int prc = hvcf_peer_error_after_sync(ctx, "hvcf_download_grid"))
-		return prc;
-	const uint32_t total = ctx->h_total[frame];
-	*out_total = total;
-	const size_t need = sizeof(uint32_t) * static_cast<size_t>(total);
-	if (need > indices_capacity_bytes || (need && !indices_dst))
-		return fail(HVCF_ERR_CAPACITY, "hvcf_download_grid: %u indices do not fit in %zu bytes", total, indices_capacity_bytes);
-	if (need)
-	{
-		HVCF_CUDA(cudaMemcpyAsync(indices_dst, ctx->d_indices, need, cudaMemcpyDeviceToHost, s));
-		HVCF_CUDA(cudaStreamSynchronize(s));
-	}
-	return HVCF_OK;
-}
-
-int hvcf_get_stats(hvcf_ctx* ctx, uint32_t frame, hvcf_stats* out, void* stream)
-{
-	if (!ctx || !out)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_stats: null argument");
-	if (frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_stats: frame %u >= frame_count %u", frame, ctx->frame_count);
-	DeviceStats ds;
-	const int rc = download(ctx, &ds, &ctx->d_stats[frame], sizeof(ds), sizeof(ds), stream, "hvcf_get_stats");
-	if (rc != HVCF_OK)
-		return rc;
-	memset(out, 0, sizeof(*out));
-	out->nominal_tests = static_cast<uint64_t>(ctx->cluster_count) * ctx->num_lights;
-	out->executed_tests = ds.executed_tests;
-	out->prefilter_tests = ds.prefilter_tests;
-	out->bin_tests = ds.bin_tests;
-	out->write_pass_tests = ds.write_tests;
-	{
-		const size_t C = ctx->cluster_total;
-		const uint64_t ref_bytes = sizeof(hvcf_light_data) * static_cast<uint64_t>(ctx->max_lights) + (sizeof(hvcf_aabb) + sizeof(hvcf_light_cell)) * C +
-			sizeof(uint32_t) * C * ctx->cap + (sizeof(uint32_t) + sizeof(hvcf_cluster_forward_ubo)) * ctx->frame_count;
-		out->device_bytes = ctx->device_bytes;
-		out->scratch_bytes = ctx->device_bytes > ref_bytes ? ctx->device_bytes - ref_bytes : 0;
-	}
-	if (ctx->hier)
-	{
-		out->plan_groups = ctx->hp.ncb;
-		out->plan_blocks_per_program = ctx->hp.K;
-		out->plan_segments = ctx->h_num_segs;
-		out->plan_rounds = ctx->h_num_rounds >= 2 ? ctx->h_num_rounds : 1;
-		out->plan_flags = ctx->last_plan_flags;
-	}
-	out->total_indices = ds.total_indices;
-	out->overflow_clusters = ds.overflow_clusters;
-	out->kernel_launches = ctx->last_launches[frame];
-	return HVCF_OK;
-}
-
-int hvcf_debug_trace(hvcf_ctx* ctx, unsigned long long* out_words, size_t max_words, size_t* out_ctas_per_pass)
-{
-	if (!ctx || !out_words || !out_ctas_per_pass)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_trace: null argument");
-	if (!ctx->d_trace)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_trace: create the context with HVCF_HIER_TRACE=1 (hierarchical mode)");
-	const size_t ctas = static_cast<size_t>(ctx->hp.ncb) * 2 * ctx->h_num_segs;
-	const size_t words = ctas * 8 < max_words ? ctas * 8 : max_words;
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(cudaDeviceSynchronize());
-	HVCF_CUDA(cudaMemcpy(out_words, ctx->d_trace, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-	*out_ctas_per_pass = ctas;
-	return HVCF_OK;
-}
-
-int hvcf_debug_kernel_times(hvcf_ctx* ctx, uint32_t frame, float out_ms[5])
-{
-	if (!ctx || !out_ms || frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_kernel_times: bad argument");
-	if (!ctx->ktimes || !ctx->kev[frame][5])
-		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_kernel_times: needs HVCF_KERNEL_TIMES=1 at hvcf_create and a hierarchical hvcf_cull on this frame");
-	HVCF_CUDA(cudaEventSynchronize(ctx->kev[frame][5]));
-	for (int i = 0; i < 5; ++i)
-		HVCF_CUDA(cudaEventElapsedTime(&out_ms[i], ctx->kev[frame][i], ctx->kev[frame][i + 1]));
-	if (ctx->h_num_rounds >= 2 && ctx->kev_round[frame][0][2]) // rounds: bin = the rounds' alive + binning launches, count = their count passes
-	{
-		out_ms[1] = out_ms[2] = 0.0f;
-		for (uint32_t r = 0; r < ctx->h_num_rounds; ++r)
-		{
-			float a = 0.0f, b = 0.0f;
-			HVCF_CUDA(cudaEventElapsedTime(&a, ctx->kev_round[frame][r][0], ctx->kev_round[frame][r][1]));
-			HVCF_CUDA(cudaEventElapsedTime(&b, ctx->kev_round[frame][r][1], ctx->kev_round[frame][r][2]));
-			out_ms[1] += a, out_ms[2] += b;
-		}
-		HVCF_CUDA(cudaEventElapsedTime(&out_ms[3], ctx->kev_round[frame][ctx->h_num_rounds - 1][2], ctx->kev[frame][4]));
-		if (ctx->routed_frame && ctx->kev_phase2[frame][1]) // the second route of a two-phase frame sits inside a round's binning interval
-		{
-			float ph = 0.0f;
-			if (cudaEventElapsedTime(&ph, ctx->kev_phase2[frame][0], ctx->kev_phase2[frame][1]) == cudaSuccess && ph > 0.0f && ph < out_ms[1])
-				out_ms[0] += ph, out_ms[1] -= ph;
-			(void)cudaGetLastError();
-		}
-	}
-	if (ctx->kev_exchange[frame]) // sharded frames: the wait for the other ranks' totals sits between finalize and the write pass
-		HVCF_CUDA(cudaEventElapsedTime(&out_ms[4], ctx->kev[frame][6], ctx->kev[frame][5]));
-	return HVCF_OK;
-}
-
-int hvcf_debug_rounds(hvcf_ctx* ctx, uint32_t plan[68], uint32_t what, void* dst, size_t bytes)
-{
-	if (!ctx || !plan)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: null argument");
-	if (!ctx->hier)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_debug_rounds: hierarchical mode only");
-	memset(plan, 0, sizeof(uint32_t) * 68);
-	plan[0] = ctx->hp.ncb, plan[1] = ctx->hp.K, plan[2] = ctx->tiles_cap, plan[3] = ctx->h_num_rounds;
-	for (uint32_t r = 0; r < ctx->h_num_rounds && r < kHMaxChunks; ++r)
-	{
-		const hvcf_ctx::Round& rd = ctx->h_rounds[r];
-		uint32_t* o = plan + 4 + 8 * r;
-		o[0] = rd.seg_begin, o[1] = rd.seg_end, o[2] = rd.tile_begin, o[3] = rd.tile_end, o[4] = rd.tiles_per_seg, o[5] = rd.pipe, o[6] = rd.macro_shift;
-	}
-	if (!dst)
-		return HVCF_OK;
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	HVCF_CUDA(cudaDeviceSynchronize());
-	const void* src = nullptr;
-	size_t have = 0;
-	switch (what)
-	{
-	case 0: src = ctx->d_group_alive, have = sizeof(uint32_t) * ctx->hp.ncb * kHMaxChunks; break;
-	case 1: src = ctx->d_bin_count, have = sizeof(uint32_t) * static_cast<size_t>(ctx->hp.ncb) * ctx->tiles_cap; break;
-	case 2: src = ctx->d_alive_union, have = sizeof(float) * 8 * ctx->hp.ncb; break;
-	default: return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: what = %u", what);
-	}
-	if (bytes > have)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_debug_rounds: %zu bytes > %zu", bytes, have);
-	HVCF_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
-	return HVCF_OK;
-}
-
-int hvcf_set_timing(hvcf_ctx* ctx, int enabled)
-{
-	if (!ctx)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_set_timing: null context");
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	if (enabled)
-		for (uint32_t f = 0; f < ctx->frame_count; ++f)
-			for (auto& e : ctx->ev[f])
-				if (!e)
-					HVCF_CUDA(cudaEventCreate(&e));
-	ctx->timing = enabled != 0;
-	return HVCF_OK;
-}
-
-int hvcf_get_timing(hvcf_ctx* ctx, uint32_t frame, float* out_cull_kernel_ms, float* out_total_ms)
-{
-	if (!ctx || !out_cull_kernel_ms || !out_total_ms)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_get_timing: null argument");
-	if (frame >= ctx->frame_count || !ctx->timing)
-		return fail(HVCF_ERR_NOT_READY, "hvcf_get_timing: timing disabled or bad frame");
-	HVCF_CUDA(cudaEventSynchronize(ctx->ev[frame][3]));
-	*out_cull_kernel_ms = 0.0f;
-	if (ctx->ev_valid[frame])
-		HVCF_CUDA(cudaEventElapsedTime(out_cull_kernel_ms, ctx->ev[frame][1], ctx->ev[frame][2]));
-	HVCF_CUDA(cudaEventElapsedTime(out_total_ms, ctx->ev[frame][0], ctx->ev[frame][3]));
-	return HVCF_OK;
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// consumer: Scene.frag light loop over a device G-buffer
-// ---------------------------------------------------------------------------------------------------------
-namespace
-{
-// Scene.frag:65 on the host, with the libm the oracle uses: uint(max(log2(linDepth) * scaling + bias, 0.0))
-inline uint32_t host_z_index(float lin, float scaling, float bias)
-{
-	const float v = fmaxf(log2f(lin) * scaling + bias, 0.0f);
-	return v >= 4294967040.0f ? 0xffffffffu : static_cast<uint32_t>(v);
-}
-
-// thr[k] = the smallest positive float whose zIndex is >= k (bisection over the bit patterns of positive floats:
-// log2f is monotone, and so is the rounded multiply-add), +inf when no finite depth reaches slice k.
-void build_slice_thresholds(float scaling, float bias, uint32_t Z, float* thr)
-{
-	thr[0] = 0.0f;
-	for (uint32_t k = 1; k <= Z; ++k)
-	{
-		uint32_t lo = 0x00800000u, hi = 0x7f7fffffu; // smallest normal .. FLT_MAX
-		float f;
-		memcpy(&f, &hi, 4);
-		if (host_z_index(f, scaling, bias) < k)
-		{
-			thr[k] = INFINITY;
-			continue;
-		}
-		memcpy(&f, &lo, 4);
-		if (host_z_index(f, scaling, bias) >= k)
-		{
-			thr[k] = f;
-			continue;
-		}
-		while (hi - lo > 1) // invariant: zIndex(lo) < k <= zIndex(hi)
-		{
-			const uint32_t mid = lo + (hi - lo) / 2;
-			memcpy(&f, &mid, 4);
-			if (host_z_index(f, scaling, bias) >= k)
-				hi = mid;
-			else
-				lo = mid;
-		}
-		memcpy(&thr[k], &hi, 4);
-	}
-}
-} // namespace
-
-int hvcf_shade(hvcf_ctx* ctx, uint32_t frame, const hvcf_gbuffer* g, const hvcf_push_const_pbr* pc, const float camera_position[3],
-	float* out_color, uint32_t* out_cluster_index, void* stream)
-{
-	if (!ctx || !g || !pc || !camera_position || !out_color)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shade: null argument");
-	if (frame >= ctx->frame_count)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shade: frame %u >= frame_count %u", frame, ctx->frame_count);
-	if (!ctx->ubo_set[frame])
-		return fail(HVCF_ERR_NOT_READY, "hvcf_shade: hvcf_set_ubo(frame %u) has not been called", frame);
-	if (!g->width || !g->height || !g->frag_depth || !g->world_pos || !g->normal_rough || !g->albedo_metal)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_shade: incomplete G-buffer");
-	HVCF_CUDA(cudaSetDevice(ctx->device));
-	cudaStream_t s = static_cast<cudaStream_t>(stream);
-	const size_t tab = ctx->Z + 1;
-	if (!ctx->d_slice_thr)
-	{
-		HVCF_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->d_slice_thr), sizeof(float) * tab * ctx->frame_count));
-		HVCF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_slice_thr), sizeof(float) * tab * ctx->frame_count));
-	}
-	const hvcf_cluster_forward_ubo& u = ctx->h_ubo[frame];
-	if (!ctx->slice_valid[frame] || ctx->slice_key[frame][0] != u.slice_scaling || ctx->slice_key[frame][1] != u.slice_bias)
-	{
-		// the slot's previous table may still be in flight on `stream` only if the caller reuses a frame slot before its
-		// work finished, which the 2-deep frame ring forbids (AppBase.cpp:96-100)
-		build_slice_thresholds(u.slice_scaling, u.slice_bias, ctx->Z, ctx->h_slice_thr + tab * frame);
-		HVCF_CUDA(cudaMemcpyAsync(ctx->d_slice_thr + tab * frame, ctx->h_slice_thr + tab * frame, sizeof(float) * tab,
-			cudaMemcpyHostToDevice, s));
-		ctx->slice_key[frame][0] = u.slice_scaling;
-		ctx->slice_key[frame][1] = u.slice_bias;
-		ctx->slice_valid[frame] = true;
-	}
-	ShadeParams p{};
-	p.cells = ctx->d_cells;
-	p.indices = ctx->d_indices;
-	p.lights = ctx->bound_lights ? ctx->bound_lights : ctx->d_lights;
-	p.slice_thresholds = ctx->d_slice_thr + tab * frame;
-	p.pc = *pc;
-	p.cam[0] = camera_position[0], p.cam[1] = camera_position[1], p.cam[2] = camera_position[2];
-	p.near_plane = u.camera_near, p.far_plane = u.camera_far;
-	p.slice_scaling = u.slice_scaling, p.slice_bias = u.slice_bias;
-	p.tile_w = u.screen_size[0] / static_cast<float>(u.slice_count_x); // Scene.frag:66-68
-	p.tile_h = u.screen_size[1] / static_cast<float>(u.slice_count_y);
-	p.X = ctx->X, p.Y = ctx->Y, p.Z = ctx->Z;
-	p.width = g->width, p.height = g->height;
-	p.frag_depth = g->frag_depth;
-	p.world_pos = reinterpret_cast<const float4*>(g->world_pos);
-	p.normal_rough = reinterpret_cast<const float4*>(g->normal_rough);
-	p.albedo_metal = reinterpret_cast<const float4*>(g->albedo_metal);
-	p.out_color = reinterpret_cast<float4*>(out_color);
-	p.out_cluster = out_cluster_index;
-	HVCF_CUDA(launch_cluster_shade(p, s));
-	return HVCF_OK;
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// FrustumCulling.comp
-// ---------------------------------------------------------------------------------------------------------
-int hvcf_frustum_cull(int device, const hvcf_frustum_ubo* frustum, const hvcf_aabb* boxes, uint32_t count,
-	hvcf_draw_indirect_command* commands, void* stream)
-{
-	if (!frustum || (count && (!boxes || !commands)))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_frustum_cull: null argument");
-	if (device >= 0)
-		HVCF_CUDA(cudaSetDevice(device));
-	FrustumParams f{};
-	memcpy(f.planes, frustum->planes, sizeof(f.planes));
-	for (int a = 0; a < 3; ++a)
-	{
-		float mn = INFINITY, mx = -INFINITY;
-		bool nan = false;
-		for (int i = 0; i < 8; ++i)
-		{
-			const float c = frustum->corners[i][a];
-			nan = nan || c != c;
-			mn = fminf(mn, c);
-			mx = fmaxf(mx, c);
-		}
-		// a NaN corner makes every `corner > max` / `corner < min` sum fall short of 8 in the shader (:36-41)
-		f.corner_min[a] = nan ? -INFINITY : mn;
-		f.corner_max[a] = nan ? INFINITY : mx;
-	}
-	HVCF_CUDA(launch_frustum_cull(f, boxes, count, commands, static_cast<cudaStream_t>(stream)));
-	return HVCF_OK;
-}
-
-int hvcf_measure_fp32_issue_rate(int device, double* out_lane_ops_per_second)
-{
-	if (!out_lane_ops_per_second)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_measure_fp32_issue_rate: null argument");
-	if (device >= 0)
-		HVCF_CUDA(cudaSetDevice(device));
-	cudaDeviceProp prop;
-	int dev = 0;
-	HVCF_CUDA(cudaGetDevice(&dev));
-	HVCF_CUDA(cudaGetDeviceProperties(&prop, dev));
-	float* sink = nullptr;
-	HVCF_CUDA(cudaMalloc(&sink, 16));
-	cudaEvent_t e0, e1;
-	HVCF_CUDA(cudaEventCreate(&e0));
-	HVCF_CUDA(cudaEventCreate(&e1));
-	const uint32_t blocks = static_cast<uint32_t>(prop.multiProcessorCount) * 8, iters = 1u << 15;
-	double best = 0.0;
-	for (int rep = 0; rep < 5; ++rep)
-	{
-		HVCF_CUDA(cudaEventRecord(e0, 0));
-		HVCF_CUDA(launch_fp32_issue_rate(sink, blocks, iters, 0));
-		HVCF_CUDA(cudaEventRecord(e1, 0));
-		HVCF_CUDA(cudaEventSynchronize(e1));
-		float ms = 0.0f;
-		HVCF_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-		const double ops = static_cast<double>(blocks) * 256.0 * iters * 16.0;
-		if (rep > 0 && ms > 0.0f && ops / (ms * 1e-3) > best)
-			best = ops / (ms * 1e-3);
-	}
-	cudaEventDestroy(e0);
-	cudaEventDestroy(e1);
-	cudaFree(sink);
-	*out_lane_ops_per_second = best;
-	return HVCF_OK;
-}
-
-int hvcf_device_alloc(int device, size_t bytes, void** out_device_ptr)
-{
-	if (!out_device_ptr)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_alloc: null argument");
-	if (device >= 0)
-		HVCF_CUDA(cudaSetDevice(device));
-	HVCF_CUDA(cudaMalloc(out_device_ptr, bytes ? bytes : 16));
-	return HVCF_OK;
-}
-
-int hvcf_device_free(void* device_ptr)
-{
-	if (device_ptr)
-		HVCF_CUDA(cudaFree(device_ptr));
-	return HVCF_OK;
-}
-
-int hvcf_device_upload(void* device_dst, size_t offset, const void* host_src, size_t bytes, void* stream)
-{
-	if (!device_dst || (bytes && !host_src))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_upload: null argument");
-	if (bytes)
-		HVCF_CUDA(cudaMemcpyAsync(static_cast<char*>(device_dst) + offset, host_src, bytes, cudaMemcpyHostToDevice,
-			static_cast<cudaStream_t>(stream)));
-	return HVCF_OK;
-}
-
-int hvcf_device_download(void* host_dst, const void* device_src, size_t offset, size_t bytes, void* stream)
-{
-	if (!device_src || (bytes && !host_dst))
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_device_download: null argument");
-	cudaStream_t s = static_cast<cudaStream_t>(stream);
-	if (bytes)
-		HVCF_CUDA(cudaMemcpyAsync(host_dst, static_cast<const char*>(device_src) + offset, bytes, cudaMemcpyDeviceToHost, s));
-	HVCF_CUDA(cudaStreamSynchronize(s));
-	return HVCF_OK;
-}
-
-int hvcf_stream_synchronize(void* stream)
-{
-	HVCF_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
-	return HVCF_OK;
-}
-
-int hvcf_host_alloc(size_t bytes, void** out_ptr)
-{
-	if (!out_ptr)
-		return fail(HVCF_ERR_INVALID_ARGUMENT, "hvcf_host_alloc: null argument");
-	HVCF_CUDA(cudaMallocHost(out_ptr, bytes ? bytes : 16));
-	return HVCF_OK;
-}
-
-int hvcf_host_free(void* ptr)
-{
-	if (ptr)
-		HVCF_CUDA(cudaFreeHost(ptr));
-	return HVCF_OK;
 }
 
 } // extern "C"

@@ -1,5 +1,6 @@
 // hvcf_ctx.cuh -- the context behind the opaque hvcf_ctx* of include/hvcf.h and the error helpers, shared by the translation
-// units that implement the C ABI (hvcf_api.cu: single-GPU frame, downloads, next rows; hvcf_shard_api.cu: the sharded frame).
+// units that implement the C ABI (hvcf_api.cu: context, lights, UBOs, the frame; hvcf_api_peer.cu: the peer exchange; hvcf_api_io.cu:
+// downloads, counters, raw buffers; hvcf_api_next.cu: consumer + frustum culling; hvcf_shard_api.cu: the routed frame; hvcf_noalloc.cu).
 #pragma once
 
 #include "../../include/hvcf.h"
@@ -33,6 +34,7 @@ struct NvtxZone
 } // namespace hvcf
 
 struct hvcf_ctx;
+void peer_unmap(hvcf_ctx* c); // hvcf_api_peer.cu: closes the IPC mappings of the peers (also on hvcf_destroy)
 // pieces of the frame shared by hvcf_api.cu (hvcf_cull*) and hvcf_shard_api.cu (hvcf_cull_routed)
 extern "C" {
 int hvcf_cull_open(hvcf_ctx* ctx, uint32_t frame, void* stream, const char* who, bool routed, bool allow_rounds);
