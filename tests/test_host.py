@@ -129,3 +129,28 @@ def test_sub_tile_segments_partition_every_slot_in_order():
             for q in range(P):
                 got += list(range(q * nb // P, (q + 1) * nb // P))
             assert got == list(range(nb)), (nb, P)
+
+
+def test_public_headers_compile_as_plain_c_and_cpp(tmp_path):
+    """The drop-in boundary is a C ABI: include/hvcf.h (+ hvcf_types.h) must compile as C11 and as C++17 on their own, with no CUDA
+    header and no torch type in sight; the C++ mirror of the reference classes (include/hv/*.h) must compile as C++20 with nothing
+    but the C ABI underneath."""
+    import shutil
+    import subprocess
+    inc = os.path.join(ROOT, "include")
+    src = tmp_path / "t.c"
+    src.write_text('#include "hvcf.h"\nint main(void) { hvcf_config c; c.struct_size = sizeof c; return (int)c.struct_size * 0; }\n')
+    cc, cxx = shutil.which("gcc"), shutil.which("g++")
+    assert cc and cxx
+    for cmd in ([cc, "-std=c11", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", str(src)],
+                [cxx, "-std=c++17", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-fsyntax-only", "-x", "c++", str(src)]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    cpp = tmp_path / "u.cpp"
+    cpp.write_text('#include "hv/Camera.h"\n#include "hv/ClusterForward.h"\nint main() { return 0; }\n')
+    r = subprocess.run([cxx, "-std=c++20", "-Wall", "-Werror", "-I", inc, "-fsyntax-only", str(cpp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for name in ("hvcf.h", "hvcf_types.h"):
+        text = open(os.path.join(inc, name)).read()
+        includes = re.findall(r"^\s*#\s*include\s*[<\"]([^>\"]+)", text, re.M)
+        assert set(includes) <= {"stddef.h", "stdint.h", "hvcf_types.h"}, includes
