@@ -756,6 +756,14 @@ def run_routed(args, hvcf, torch, dist, world, rank, local, dev, barrier, K, W, 
     ref_hash = allgather(ref_hash)[0]
     out["sharded_bytes_equal"] = bool(all(h == ref_hash for h in hashes))
     out["grid_hash"] = f"{ref_hash & 0xffffffffffffffff:016x}"
+    if not out["sharded_bytes_equal"]:
+        # failure reproduction: the scene is seeded, so the cuts, the route block size and the library's switches replay the frame
+        out["repro"] = {"ranks_differing": [r for r, h in enumerate(hashes) if h != ref_hash],
+                        "command": f"python -m torch.distributed.run --nnodes=1 --nproc-per-node {world} --master-addr 127.0.0.1 bench.py --gpus {world} "
+                                   f"--workload {args.workload} --steps {K} --warmup {W} --row-cuts {','.join(str(c) for c in cuts)} "
+                                   f"--block-tiles {args.block_tiles} --no-compare --no-flythrough --no-cpu-baseline",
+                        "env": {k: v for k, v in os.environ.items() if k.startswith("HVCF_")}}
+        log("SHARDED GRID DIFFERS FROM THE UNSHARDED FRAME; to replay:", json.dumps(out["repro"]))
 
     # ---- e2e: HOST buffers; every rank uploads its own lights + UBO and downloads its own slab's cells + index segment ----
     lb, le = state["range"]
@@ -1156,7 +1164,7 @@ def run_ours(args):
         parallelism = (f"{world} ranks: clusters sharded into row slabs {head['row_cuts']} (row = y + z * {grid[1]}), lights owned in shards and routed over NVLink peer "
                        f"memory (hvcf_cull_routed); no collective call in the frame")
         detail = {k: head[k] for k in ("row_cuts", "rows_per_slice", "balance_iterations", "inbox_records_per_rank", "light_range_per_rank", "own_kernels_ms_per_rank",
-                                       "kernel_ms_per_rank", "route_kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks")}
+                                       "kernel_ms_per_rank", "route_kernel_ms_per_rank", "sharded_bytes_equal", "grid_hash", "peer_error", "executed_tests_all_ranks", "repro") if k in head}
         inbox = head["inbox_records_per_rank"]
         own = head["own_kernels_ms_per_rank"]
         summary["routed"] = {"ms": round(ms_per_step, 4), "bytes_equal": head["sharded_bytes_equal"], "row_cuts": head["row_cuts"],
